@@ -1,0 +1,141 @@
+// Kernel (c): bias absorption (bias_absorption.py:9-80) with an optional fused weight clip
+// (clip_weight.py:4-33), plus BN folding (utils/layer_transform.py:240-285) and the stand-alone clip.
+// One pass over W2: a warp owns one output row, forms c = max(0, beta - N*gamma) on the fly, reduces
+// (sum_k W2[o,i,k]) * c[i] and, when asked, writes the clamped row back.  8 B/elt with clip, 4 B/elt
+// without.  The bias updates then run in relation order per element (fp32 adds do not commute).
+#include "common.cuh"
+
+namespace dfq {
+
+__device__ __forceinline__ float absorb_c(float beta, float gamma, float N) {
+    float v = __fsub_rn(beta, __fmul_rn(N, gamma));       // :48
+    return (v < 0.0f) ? 0.0f : v;                          // clamp_(0), NaN propagates (:49)
+}
+
+__global__ void __launch_bounds__(kThreads)
+absorb_wc_kernel(const DfqAbsorbPair *__restrict__ pairs, int n_pairs, int total_rows, float N,
+                 int do_clip, float lo_c, float hi_c) {
+    int row = blockIdx.x * kWarps + (threadIdx.x >> 5);
+    if (row >= total_rows) return;
+    int lo = 0, hi = n_pairs - 1;
+    while (lo < hi) {
+        int mid = (lo + hi + 1) >> 1;
+        if (pairs[mid].first_row <= row) lo = mid; else hi = mid - 1;
+    }
+    const DfqAbsorbPair &p = pairs[lo];
+    const int o = row - p.first_row, lane = threadIdx.x & 31;
+    const int G = p.C1 / p.I2, Og = p.O2 / G, g = o / Og, KK = p.KK;
+    float *w = p.W2 + (int64_t)o * p.I2 * KK;
+    double acc = 0.0;
+    for (int it = lane; it < p.I2; it += 32) {
+        int ci = g * p.I2 + it;
+        float c = absorb_c(p.bn_b[ci], p.bn_w[ci], N);
+        float rs = 0.0f;
+        for (int k = 0; k < KK; ++k) {                     // torch.sum(W2.view(O, I, -1), -1), :52,:65
+            float v = w[it * KK + k];
+            rs = __fadd_rn(rs, v);
+            if (do_clip) w[it * KK + k] = fminf(fmaxf(v, lo_c), hi_c);
+        }
+        acc += (double)rs * (double)c;                     // matmul(., c), :64-67
+    }
+    acc = warp_sum(acc);
+    if (lane == 0) p.wc[o] = (float)acc;
+}
+
+// b1 -= c ; fake_bias -= c ; b2 += wc  (:78-80), relations in list order for every element.
+__global__ void absorb_bias_kernel(const DfqAbsorbPair *__restrict__ pairs, int n_pairs, float N) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    for (int r = 0; r < n_pairs; ++r) {
+        const DfqAbsorbPair &p = pairs[r];
+        if (i < p.C1) {
+            float c = absorb_c(p.bn_b[i], p.bn_w[i], N);
+            p.b1[i] = __fadd_rn(p.b1[i], -c);
+            p.bn_b[i] = __fadd_rn(p.bn_b[i], -c);
+            if (p.c) p.c[i] = c;
+        }
+        if (i < p.O2) p.b2[i] = __fadd_rn(p.b2[i], p.wc[i]);
+    }
+}
+
+__global__ void __launch_bounds__(kThreads) clip_kernel(float *w, int64_t n, float lo, float hi) {
+    int64_t begin = (int64_t)blockIdx.x * kChunk, end = min(begin + (int64_t)kChunk, n);
+    float *p = w + begin;
+    int64_t m = end - begin;
+    if ((((uintptr_t)p) & 15) == 0) {
+        float4 *p4 = reinterpret_cast<float4 *>(p);
+        int64_t m4 = m >> 2;
+        for (int64_t k = threadIdx.x; k < m4; k += kThreads) {
+            float4 v = p4[k];
+            v.x = fminf(fmaxf(v.x, lo), hi); v.y = fminf(fmaxf(v.y, lo), hi);
+            v.z = fminf(fmaxf(v.z, lo), hi); v.w = fminf(fmaxf(v.w, lo), hi);
+            p4[k] = v;
+        }
+        for (int64_t k = (m4 << 2) + threadIdx.x; k < m; k += kThreads) p[k] = fminf(fmaxf(p[k], lo), hi);
+    } else {
+        for (int64_t k = threadIdx.x; k < m; k += kThreads) p[k] = fminf(fmaxf(p[k], lo), hi);
+    }
+}
+
+// utils/layer_transform.py:255-274 for one (conv, BN) pair; a warp owns one output channel.
+__global__ void __launch_bounds__(kThreads)
+merge_bn_kernel(float *W, float *b, int64_t O, int64_t K, const float *gamma, const float *beta,
+                const float *mean, const float *var, float eps, float *fake_w, float *fake_b) {
+    int64_t o = (int64_t)blockIdx.x * kWarps + (threadIdx.x >> 5);
+    if (o >= O) return;
+    int lane = threadIdx.x & 31;
+    float sd = __fsqrt_rn(__fadd_rn(var[o], eps));
+    float f = __fdiv_rn(gamma[o], sd);
+    float *row = W + o * K;
+    for (int64_t k = lane; k < K; k += 32) row[k] = __fmul_rn(row[k], f);      // :260
+    if (lane == 0) {
+        float sh = __fsub_rn(beta[o], __fdiv_rn(__fmul_rn(gamma[o], mean[o]), sd));
+        b[o] = __fadd_rn(__fmul_rn(b[o], f), sh);                                // :269-270
+        if (fake_w) fake_w[o] = fabsf(gamma[o]);                                 // :273
+        if (fake_b) fake_b[o] = beta[o];                                         // :274
+    }
+}
+
+}  // namespace dfq
+
+using namespace dfq;
+
+extern "C" int dfq_absorb_plan_host(DfqAbsorbPair *p, int n, int *total_rows) {
+    int r = 0;
+    for (int i = 0; i < n; ++i) {
+        if (p[i].I2 <= 0 || p[i].C1 % p[i].I2 || p[i].O2 % (p[i].C1 / p[i].I2)) return (int)cudaErrorInvalidValue;
+        p[i].first_row = r;
+        r += p[i].O2;
+    }
+    *total_rows = r;
+    return 0;
+}
+
+extern "C" int dfq_absorb_clip(const DfqAbsorbPair *pairs_dev, int n_pairs, int total_rows, int max_dim, float N,
+                               int do_clip, float clip_lo, float clip_hi, void *stream) {
+    if (n_pairs <= 0) return 0;
+    cudaStream_t st = (cudaStream_t)stream;
+    absorb_wc_kernel<<<(total_rows + kWarps - 1) / kWarps, kThreads, 0, st>>>(pairs_dev, n_pairs, total_rows, N,
+                                                                              do_clip, clip_lo, clip_hi);
+    absorb_bias_kernel<<<(max_dim + 255) / 256, 256, 0, st>>>(pairs_dev, n_pairs, N);
+    g_launches += 2;
+    return (int)cudaGetLastError();
+}
+
+extern "C" int dfq_clip_f32(float *w, int64_t n, float lo, float hi, void *stream) {
+    if (n <= 0) return 0;
+    int64_t blocks = (n + kChunk - 1) / kChunk;
+    if (blocks > 0x7fffffffll) return (int)cudaErrorInvalidValue;
+    clip_kernel<<<(unsigned)blocks, kThreads, 0, (cudaStream_t)stream>>>(w, n, lo, hi);
+    g_launches += 1;
+    return (int)cudaGetLastError();
+}
+
+extern "C" int dfq_merge_bn(float *W, float *b, int64_t O, int64_t K, const float *gamma, const float *beta,
+                            const float *mean, const float *var, float eps, float *fake_weight,
+                            float *fake_bias, void *stream) {
+    if (O <= 0) return 0;
+    merge_bn_kernel<<<(unsigned)((O + kWarps - 1) / kWarps), kThreads, 0, (cudaStream_t)stream>>>(
+        W, b, O, K, gamma, beta, mean, var, eps, fake_weight, fake_bias);
+    g_launches += 1;
+    return (int)cudaGetLastError();
+}

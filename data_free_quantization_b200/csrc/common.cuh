@@ -1,0 +1,169 @@
+// Shared device helpers of libdfq_b200 (sm_100a only).
+// Bit-exactness rules: every fp32 operation of the reference's elementwise
+// chains is issued as an explicitly rounded intrinsic (__fadd_rn/__fmul_rn/...), which nvcc never
+// contracts into an FMA; the build also passes -fmad=false.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <math.h>
+#include "../../include/dfq_b200.h"
+
+namespace dfq {
+
+constexpr int kThreads = 256;
+constexpr int kWarps = kThreads / 32;
+constexpr int kChunk = 4096;            // fp32 elements per block of the streaming kernels
+
+extern long long g_launches;            // host-side launch counter (api.cu)
+
+// Monotone float -> uint map (larger float => larger code); 0 is below every real value.
+__device__ __forceinline__ unsigned enc_ordered(float f) {
+    unsigned u = __float_as_uint(f);
+    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+__device__ __forceinline__ float dec_ordered(unsigned e) {
+    unsigned u = (e & 0x80000000u) ? (e & 0x7fffffffu) : ~e;
+    return __uint_as_float(u);
+}
+
+__device__ __forceinline__ float warp_min(float v) {
+#pragma unroll
+    for (int o = 16; o; o >>= 1) v = fminf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+    for (int o = 16; o; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o; o >>= 1) v = __fadd_rn(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+    for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// Block-wide min/max with one shared-memory round; result valid in every thread.
+__device__ __forceinline__ void block_minmax(float &lo, float &hi, float *smem /* 2*kWarps */) {
+    lo = warp_min(lo);
+    hi = warp_max(hi);
+    int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+    __syncthreads();
+    if (l == 0) { smem[w] = lo; smem[kWarps + w] = hi; }
+    __syncthreads();
+    lo = smem[0];
+    hi = smem[kWarps];
+#pragma unroll
+    for (int i = 1; i < kWarps; ++i) { lo = fminf(lo, smem[i]); hi = fmaxf(hi, smem[kWarps + i]); }
+}
+
+// min/max of [begin,end) of x; vectorised when the address allows it.
+__device__ __forceinline__ void chunk_minmax(const float *__restrict__ x, int64_t begin, int64_t end,
+                                             float &lo, float &hi) {
+    const float *p = x + begin;
+    int64_t n = end - begin;
+    if ((((uintptr_t)p) & 15) == 0) {
+        const float4 *p4 = reinterpret_cast<const float4 *>(p);
+        int64_t n4 = n >> 2;
+        float4 v[4];
+        int64_t i = threadIdx.x;
+        // kChunk/4 = 1024 float4 per block = 4 per thread: issue all loads, then reduce
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            int64_t k = i + (int64_t)u * kThreads;
+            v[u] = (k < n4) ? __ldg(p4 + k) : make_float4(INFINITY, INFINITY, INFINITY, INFINITY);
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            int64_t k = i + (int64_t)u * kThreads;
+            if (k < n4) {
+                lo = fminf(lo, fminf(fminf(v[u].x, v[u].y), fminf(v[u].z, v[u].w)));
+                hi = fmaxf(hi, fmaxf(fmaxf(v[u].x, v[u].y), fmaxf(v[u].z, v[u].w)));
+            }
+        }
+        for (int64_t k = (n4 << 2) + threadIdx.x; k < n; k += kThreads) {
+            float t = p[k]; lo = fminf(lo, t); hi = fmaxf(hi, t);
+        }
+    } else {
+        for (int64_t k = threadIdx.x; k < n; k += kThreads) {
+            float t = p[k]; lo = fminf(lo, t); hi = fmaxf(hi, t);
+        }
+    }
+}
+
+// The five constants of utils/quantize.py:51-68, computed exactly as the host does
+// (double arithmetic for the Python-float path, fp32 for the min/max=None path).
+__host__ __device__ inline DfqQuantParams make_quant_params(double mn, double mx, int bits, int flags) {
+    double qlo, qhi, sc;
+    if (flags & DFQ_Q_SYMMETRIC) {
+        qhi = (double)(1ll << (bits - 1)) - 1.0;
+        qlo = -(double)(1ll << (bits - 1));
+        double a = fabs(mx), b = fabs(mn);
+        if (a < b) a = b;
+        sc = (flags & DFQ_Q_RANGE_F32) ? (double)((float)a / (float)qhi) : a / qhi;
+        mn = 0.0;
+    } else {
+        qlo = 0.0;
+        qhi = (double)(1ll << bits) - 1.0;
+        sc = (flags & DFQ_Q_RANGE_F32) ? (double)(((float)mx - (float)mn) / (float)(qhi - qlo))
+                                       : (mx - mn) / (qhi - qlo);
+    }
+    if (!(sc > 1e-8)) sc = 1e-8;
+    DfqQuantParams p;
+    p.neg_min = (float)(-mn);
+    p.scale = (float)sc;
+    p.qmin = (float)qlo;
+    p.qmax = (float)qhi;
+    p.add_back = (float)mn;
+    return p;
+}
+
+// Correctly rounded a / b for a constant divisor b > 0 with rb = RN(1/b).
+// Markstein's sequence: two FMA refinements make q faithful, the last one makes it the
+// IEEE-rounded quotient; operands outside the safe exponent window take __fdiv_rn.
+__device__ __forceinline__ float div_const_rn(float a, float b, float rb) {
+    float aa = fabsf(a);
+    if (a == 0.0f) return a;
+    if (!(aa > 1e-30f && aa < 1e30f)) return __fdiv_rn(a, b);
+    float q = __fmul_rn(a, rb);
+    float r = __fmaf_rn(-q, b, a);
+    q = __fmaf_rn(r, rb, q);
+    r = __fmaf_rn(-q, b, a);
+    return __fmaf_rn(r, rb, q);
+}
+
+// round-half-even for |c| < 2^22 without the quarter-rate F2F instruction
+__device__ __forceinline__ float rint_small(float c) {
+    const float magic = 12582912.0f;    // 1.5 * 2^23
+    return __fadd_rn(__fadd_rn(c, magic), -magic);
+}
+
+struct QuantConsts {
+    float neg_min, scale, rscale, qmin, qmax, add_back, clip_lo, clip_hi;
+    int small_grid;                     // qmax < 2^22: rint_small is exact
+};
+
+__device__ __forceinline__ QuantConsts make_consts(const DfqQuantParams &p, float clip_lo, float clip_hi) {
+    QuantConsts c;
+    c.neg_min = p.neg_min; c.scale = p.scale; c.rscale = __frcp_rn(p.scale);
+    c.qmin = p.qmin; c.qmax = p.qmax; c.add_back = p.add_back;
+    c.clip_lo = clip_lo; c.clip_hi = clip_hi;
+    c.small_grid = (p.qmax < 4194304.0f && p.qmin > -4194304.0f);
+    return c;
+}
+
+// utils/quantize.py:72-76, one element.  Returns the dequantised value; q receives the grid value.
+__device__ __forceinline__ float fake_quant_elem(float x, const QuantConsts &c, float &q) {
+    float t = __fadd_rn(x, c.neg_min);
+    t = div_const_rn(t, c.scale, c.rscale);
+    float cl = fminf(fmaxf(t, c.qmin), c.qmax);
+    cl = (t != t) ? t : cl;                             // torch.clamp propagates NaN
+    q = c.small_grid ? rint_small(cl) : rintf(cl);
+    return __fadd_rn(__fmul_rn(q, c.scale), c.add_back);
+}
+
+}  // namespace dfq

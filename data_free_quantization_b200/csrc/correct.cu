@@ -1,0 +1,161 @@
+// Kernel (d): bias correction -- bias_correction.py:111-144 (eps = Q(W) - W) fused with the
+// reduction against a per-input-channel vector v (E[x] from the preceding BatchNorm), so eps never
+// reaches HBM:  out[o] = sum_{i,k} (Q(W[o,i,k]) - W[o,i,k]) * v[i].   HBM-bound: 4 B/elt for the
+// range pass + 4 B/elt for the reduction (outputs are 4*O bytes).
+#include "common.cuh"
+
+namespace dfq {
+
+constexpr int kCorrSmallRow = 1024;
+
+__device__ __forceinline__ int find_corr(const DfqCorrDesc *d, int n, int64_t b, bool by_block) {
+    int lo = 0, hi = n - 1;
+    while (lo < hi) {
+        int mid = (lo + hi + 1) >> 1;
+        int64_t f = by_block ? d[mid].first_block : d[mid].first_unit;
+        if (f <= b) lo = mid; else hi = mid - 1;
+    }
+    return lo;
+}
+
+__global__ void __launch_bounds__(kThreads)
+corr_minmax_kernel(const DfqCorrDesc *__restrict__ descs, int n_desc, unsigned *__restrict__ ranges) {
+    __shared__ float sm[2 * kWarps];
+    int t = find_corr(descs, n_desc, blockIdx.x, true);
+    const DfqCorrDesc &d = descs[t];
+    int64_t n = (int64_t)d.O * d.I2 * d.KK;
+    int64_t begin = (blockIdx.x - d.first_block) * (int64_t)kChunk;
+    int64_t end = min(begin + (int64_t)kChunk, n);
+    float lo = INFINITY, hi = -INFINITY;
+    chunk_minmax(d.W, begin, end, lo, hi);
+    block_minmax(lo, hi, sm);
+    if (threadIdx.x == 0) {
+        atomicMax(ranges + 2 * d.range_slot, enc_ordered(-lo));
+        atomicMax(ranges + 2 * d.range_slot + 1, enc_ordered(hi));
+    }
+}
+
+__global__ void corr_decode_kernel(unsigned *ranges, int64_t slots) {
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i >= slots) return;
+    float mn = -dec_ordered(ranges[2 * i]), mx = dec_ordered(ranges[2 * i + 1]);
+    reinterpret_cast<float *>(ranges)[2 * i] = mn;
+    reinterpret_cast<float *>(ranges)[2 * i + 1] = mx;
+}
+
+__global__ void corr_zero_kernel(const DfqCorrDesc *__restrict__ descs) {
+    const DfqCorrDesc &d = descs[blockIdx.x];
+    for (int o = threadIdx.x; o < d.O; o += blockDim.x) d.out[o] = 0.0f;
+}
+
+// partial sum over elements [b, e) of one row (indices relative to the row start)
+__device__ __forceinline__ double row_partial(const float *__restrict__ row, const float *__restrict__ v,
+                                              int64_t b, int64_t e, int KK, float inv_I,
+                                              const QuantConsts &c, int tid, int nthr) {
+    double acc = 0.0;
+    const float *p = row + b;
+    int64_t n = e - b;
+    bool vec = ((((uintptr_t)p) & 15) == 0);
+    int64_t n4 = vec ? (n >> 2) : 0;
+    const float4 *p4 = reinterpret_cast<const float4 *>(p);
+    for (int64_t k = tid; k < n4; k += nthr) {
+        float4 w = __ldg(p4 + k);
+        float xs[4] = {w.x, w.y, w.z, w.w};
+        int64_t idx = b + 4 * k;
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            float q;
+            float dq = fake_quant_elem(xs[u], c, q);
+            float eps = __fsub_rn(dq, xs[u]);                       // :130
+            float vi = v ? v[(KK == 1) ? (idx + u) : (idx + u) / KK] : inv_I;
+            acc += (double)eps * (double)vi;
+        }
+    }
+    for (int64_t k = (n4 << 2) + tid; k < n; k += nthr) {
+        float x = p[k], q;
+        float eps = __fsub_rn(fake_quant_elem(x, c, q), x);
+        float vi = v ? v[(KK == 1) ? (b + k) : (b + k) / KK] : inv_I;
+        acc += (double)eps * (double)vi;
+    }
+    return acc;
+}
+
+__global__ void __launch_bounds__(kThreads)
+corr_reduce_kernel(const DfqCorrDesc *__restrict__ descs, int n_desc, const float *__restrict__ ranges) {
+    __shared__ double smd[kWarps];
+    int t = find_corr(descs, n_desc, blockIdx.x, false);
+    const DfqCorrDesc &d = descs[t];
+    const int64_t row_len = (int64_t)d.I2 * d.KK;
+    const float *rg = ranges + 2 * d.range_slot;
+    DfqQuantParams p = make_quant_params((double)rg[0], (double)rg[1], d.bits, d.flags);   // :128
+    QuantConsts c = make_consts(p, 0.f, 0.f);
+    const float inv_I = 1.0f / (float)d.I2;
+    int64_t j = blockIdx.x - d.first_unit;
+    if (row_len <= kCorrSmallRow) {                       // one warp per row
+        int64_t o = j * kWarps + (threadIdx.x >> 5);
+        if (o >= d.O) return;
+        double acc = row_partial(d.W + o * row_len, d.v, 0, row_len, d.KK, inv_I, c, threadIdx.x & 31, 32);
+        acc = warp_sum(acc);
+        if ((threadIdx.x & 31) == 0) d.out[o] = (float)acc;
+    } else {                                              // one block per (row, chunk)
+        int64_t cpr = (row_len + kChunk - 1) / kChunk;
+        int64_t o = j / cpr, b = (j % cpr) * kChunk;
+        int64_t e = min(b + (int64_t)kChunk, row_len);
+        double acc = row_partial(d.W + o * row_len, d.v, b, e, d.KK, inv_I, c, threadIdx.x, kThreads);
+        acc = warp_sum(acc);
+        if ((threadIdx.x & 31) == 0) smd[threadIdx.x >> 5] = acc;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            double s = 0.0;
+#pragma unroll
+            for (int w = 0; w < kWarps; ++w) s += smd[w];
+            if (cpr == 1) d.out[o] = (float)s; else atomicAdd(d.out + o, (float)s);
+        }
+    }
+}
+
+__global__ void corr_finalize_kernel(const DfqCorrDesc *__restrict__ descs) {
+    const DfqCorrDesc &d = descs[blockIdx.x];
+    if (!d.bias) return;
+    for (int o = threadIdx.x; o < d.O; o += blockDim.x)
+        d.bias[o] = __fadd_rn(d.bias[o], __fmul_rn(d.alpha, d.out[o]));
+}
+
+}  // namespace dfq
+
+using namespace dfq;
+
+extern "C" int dfq_corr_plan_host(DfqCorrDesc *d, int n, int64_t *total_units, int64_t *total_blocks) {
+    int64_t u = 0, b = 0;
+    for (int i = 0; i < n; ++i) {
+        if (d[i].O <= 0 || d[i].I2 <= 0 || d[i].KK <= 0 || !d[i].out) return (int)cudaErrorInvalidValue;
+        int64_t row_len = (int64_t)d[i].I2 * d[i].KK, numel = row_len * d[i].O;
+        d[i].first_unit = u;
+        d[i].first_block = b;
+        d[i].range_slot = i;
+        u += (row_len <= kCorrSmallRow) ? (d[i].O + kWarps - 1) / kWarps
+                                        : (int64_t)d[i].O * ((row_len + kChunk - 1) / kChunk);
+        b += (numel + kChunk - 1) / kChunk;
+    }
+    *total_units = u;
+    *total_blocks = b;
+    return (u > 0x7fffffffll || b > 0x7fffffffll) ? (int)cudaErrorInvalidValue : 0;
+}
+
+extern "C" int dfq_bias_correct(const DfqCorrDesc *descs_dev, int n_desc, int64_t total_units, int64_t total_blocks,
+                                float *ranges_dev, int range_given, void *stream) {
+    if (n_desc <= 0) return 0;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (!range_given) {
+        cudaError_t e = cudaMemsetAsync(ranges_dev, 0, sizeof(float) * 2 * n_desc, st);
+        if (e != cudaSuccess) return (int)e;
+        corr_minmax_kernel<<<(unsigned)total_blocks, kThreads, 0, st>>>(descs_dev, n_desc, (unsigned *)ranges_dev);
+        corr_decode_kernel<<<(n_desc + 255) / 256, 256, 0, st>>>((unsigned *)ranges_dev, n_desc);
+        g_launches += 2;
+    }
+    corr_zero_kernel<<<n_desc, 256, 0, st>>>(descs_dev);
+    corr_reduce_kernel<<<(unsigned)total_units, kThreads, 0, st>>>(descs_dev, n_desc, ranges_dev);
+    corr_finalize_kernel<<<n_desc, 256, 0, st>>>(descs_dev);
+    g_launches += 3;
+    return (int)cudaGetLastError();
+}

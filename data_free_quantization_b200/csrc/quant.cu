@@ -1,0 +1,280 @@
+// Kernel (a): uniform fake-quantisation -- utils/quantize.py:24-78, utils/layer_transform.py:288-305.
+// HBM-bound streaming passes: 128-bit coalesced loads, 4 independent loads per thread in flight,
+// warp-shuffle + shared-memory block reductions, grid-level finish with atomicMax on an
+// order-preserving integer encoding.  Algorithmic bytes: 4 B/elt (range pass) + 8 B/elt (apply).
+#include "common.cuh"
+
+namespace dfq {
+
+// ---------------------------------------------------------------------------------------------
+// Work decomposition of the multi-tensor launches.  A block owns either one kChunk-element chunk of
+// one range segment (per-tensor, or per-channel rows longer than kSmallRow) or kWarps short rows.
+constexpr int kSmallRow = 1024;
+
+struct BlockWork {
+    int desc;
+    int64_t row;        // first row (per-channel) or 0
+    int64_t begin, end; // element range inside the tensor (chunk mode); begin<0 => warp-per-row mode
+    int64_t cols;
+};
+
+__device__ __forceinline__ int find_desc(const DfqQuantDesc *d, int n, int64_t b) {
+    int lo = 0, hi = n - 1;
+    while (lo < hi) {
+        int mid = (lo + hi + 1) >> 1;
+        if (d[mid].first_block <= b) lo = mid; else hi = mid - 1;
+    }
+    return lo;
+}
+
+__device__ __forceinline__ BlockWork decode_work1(const DfqQuantDesc &d, int64_t j) {
+    BlockWork w;
+    w.desc = 0;
+    if (!(d.flags & DFQ_Q_PER_CHANNEL)) {
+        w.row = 0; w.cols = d.n;
+        w.begin = j * kChunk;
+        w.end = min(w.begin + (int64_t)kChunk, d.n);
+    } else {
+        w.cols = d.n / d.rows;
+        if (w.cols > kSmallRow) {
+            int64_t cpr = (w.cols + kChunk - 1) / kChunk;
+            w.row = j / cpr;
+            int64_t c0 = (j % cpr) * kChunk;
+            w.begin = w.row * w.cols + c0;
+            w.end = w.row * w.cols + min(c0 + (int64_t)kChunk, w.cols);
+        } else {
+            w.row = j * kWarps;
+            w.begin = -1; w.end = -1;
+        }
+    }
+    return w;
+}
+
+__device__ __forceinline__ BlockWork decode_work(const DfqQuantDesc *descs, int n_desc, int64_t b) {
+    int t = find_desc(descs, n_desc, b);
+    BlockWork w = decode_work1(descs[t], b - descs[t].first_block);
+    w.desc = t;
+    return w;
+}
+
+__device__ __forceinline__ void minmax_block(const DfqQuantDesc &d, const BlockWork &w,
+                                             unsigned *__restrict__ ranges, float *sm) {
+    if (w.begin >= 0) {
+        float lo = INFINITY, hi = -INFINITY;
+        chunk_minmax(d.x, w.begin, w.end, lo, hi);
+        block_minmax(lo, hi, sm);
+        if (threadIdx.x == 0) {
+            unsigned *slot = ranges + 2 * (d.range_slot + w.row);
+            atomicMax(slot, enc_ordered(-lo));
+            atomicMax(slot + 1, enc_ordered(hi));
+        }
+    } else {                                   // one warp per short row
+        int64_t r = w.row + (threadIdx.x >> 5);
+        if (r >= d.rows) return;
+        const float *p = d.x + r * w.cols;
+        float lo = INFINITY, hi = -INFINITY;
+        for (int64_t k = threadIdx.x & 31; k < w.cols; k += 32) {
+            float t = p[k]; lo = fminf(lo, t); hi = fmaxf(hi, t);
+        }
+        lo = warp_min(lo); hi = warp_max(hi);
+        if ((threadIdx.x & 31) == 0) {
+            unsigned *slot = ranges + 2 * (d.range_slot + r);
+            slot[0] = enc_ordered(-lo);
+            slot[1] = enc_ordered(hi);
+        }
+    }
+}
+
+__global__ void __launch_bounds__(kThreads)
+minmax_multi_kernel(const DfqQuantDesc *__restrict__ descs, int n_desc, unsigned *__restrict__ ranges) {
+    __shared__ float sm[2 * kWarps];
+    BlockWork w = decode_work(descs, n_desc, blockIdx.x);
+    minmax_block(descs[w.desc], w, ranges, sm);
+}
+
+// one tensor, descriptor passed by value (dfq_minmax_f32 / dfq_minmax_rows_f32)
+__global__ void __launch_bounds__(kThreads)
+minmax_single_kernel(DfqQuantDesc d, unsigned *__restrict__ ranges) {
+    __shared__ float sm[2 * kWarps];
+    BlockWork w = decode_work1(d, blockIdx.x);
+    minmax_block(d, w, ranges, sm);
+}
+
+// encoded (max(-x), max(x)) -> plain (min, max) floats, in place
+__global__ void decode_ranges_kernel(unsigned *ranges, int64_t slots) {
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i >= slots) return;
+    float mn = -dec_ordered(ranges[2 * i]);
+    float mx = dec_ordered(ranges[2 * i + 1]);
+    reinterpret_cast<float *>(ranges)[2 * i] = mn;
+    reinterpret_cast<float *>(ranges)[2 * i + 1] = mx;
+}
+
+template <typename CodeT>
+__device__ __forceinline__ void apply_range(const float *x, float *y, CodeT *codes, int64_t begin, int64_t end,
+                                            const QuantConsts &c, bool clamp_out, int tid, int nthr) {
+    const float *p = x + begin;
+    float *o = y + begin;
+    int64_t n = end - begin;
+    bool vec = ((((uintptr_t)p) | ((uintptr_t)o)) & 15) == 0;
+    int64_t n4 = vec ? (n >> 2) : 0;
+    const float4 *p4 = reinterpret_cast<const float4 *>(p);
+    float4 *o4 = reinterpret_cast<float4 *>(o);
+    for (int64_t base = 0; base < n4; base += 4 * (int64_t)nthr) {
+        float4 v[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            int64_t k = base + tid + (int64_t)u * nthr;
+            if (k < n4) v[u] = p4[k];        // plain load: y may alias x
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            int64_t k = base + tid + (int64_t)u * nthr;
+            if (k >= n4) continue;
+            float q0, q1, q2, q3;
+            float4 r;
+            r.x = fake_quant_elem(v[u].x, c, q0);
+            r.y = fake_quant_elem(v[u].y, c, q1);
+            r.z = fake_quant_elem(v[u].z, c, q2);
+            r.w = fake_quant_elem(v[u].w, c, q3);
+            if (clamp_out) {
+                r.x = fminf(fmaxf(r.x, c.clip_lo), c.clip_hi); r.y = fminf(fmaxf(r.y, c.clip_lo), c.clip_hi);
+                r.z = fminf(fmaxf(r.z, c.clip_lo), c.clip_hi); r.w = fminf(fmaxf(r.w, c.clip_lo), c.clip_hi);
+            }
+            o4[k] = r;
+            if (codes) {
+                CodeT *cp = codes + begin + 4 * k;
+                unsigned c0 = (unsigned)(int)(q0 - c.qmin), c1 = (unsigned)(int)(q1 - c.qmin);
+                unsigned c2 = (unsigned)(int)(q2 - c.qmin), c3 = (unsigned)(int)(q3 - c.qmin);
+                if ((((uintptr_t)cp) & (4 * sizeof(CodeT) - 1)) == 0) {   // one packed store per 4 codes
+                    if (sizeof(CodeT) == 1)
+                        *reinterpret_cast<unsigned *>(cp) = c0 | (c1 << 8) | (c2 << 16) | (c3 << 24);
+                    else
+                        *reinterpret_cast<uint2 *>(cp) = make_uint2(c0 | (c1 << 16), c2 | (c3 << 16));
+                } else {
+                    cp[0] = (CodeT)c0; cp[1] = (CodeT)c1; cp[2] = (CodeT)c2; cp[3] = (CodeT)c3;
+                }
+            }
+        }
+    }
+    for (int64_t k = (n4 << 2) + tid; k < n; k += nthr) {
+        float q;
+        float r = fake_quant_elem(p[k], c, q);
+        if (clamp_out) r = fminf(fmaxf(r, c.clip_lo), c.clip_hi);
+        o[k] = r;
+        if (codes) codes[begin + k] = (CodeT)(int)(q - c.qmin);
+    }
+}
+
+__global__ void __launch_bounds__(kThreads)
+fake_quant_multi_kernel(const DfqQuantDesc *__restrict__ descs, int n_desc, const float *__restrict__ ranges) {
+    BlockWork w = decode_work(descs, n_desc, blockIdx.x);
+    const DfqQuantDesc &d = descs[w.desc];
+    bool clamp_out = d.flags & DFQ_Q_CLAMP_OUT;
+    if (w.begin >= 0) {
+        const float *rg = ranges + 2 * (d.range_slot + w.row);
+        DfqQuantParams p = make_quant_params((double)rg[0], (double)rg[1], d.bits, d.flags);
+        QuantConsts c = make_consts(p, d.clip_lo, d.clip_hi);
+        if (d.bits <= 8) apply_range<uint8_t>(d.x, d.y, (uint8_t *)d.codes, w.begin, w.end, c, clamp_out, threadIdx.x, kThreads);
+        else apply_range<uint16_t>(d.x, d.y, (uint16_t *)d.codes, w.begin, w.end, c, clamp_out, threadIdx.x, kThreads);
+    } else {
+        int64_t r = w.row + (threadIdx.x >> 5);
+        if (r >= d.rows) return;
+        const float *rg = ranges + 2 * (d.range_slot + r);
+        DfqQuantParams p = make_quant_params((double)rg[0], (double)rg[1], d.bits, d.flags);
+        QuantConsts c = make_consts(p, d.clip_lo, d.clip_hi);
+        int64_t b = r * w.cols, e = b + w.cols;
+        if (d.bits <= 8) apply_range<uint8_t>(d.x, d.y, (uint8_t *)d.codes, b, e, c, clamp_out, threadIdx.x & 31, 32);
+        else apply_range<uint16_t>(d.x, d.y, (uint16_t *)d.codes, b, e, c, clamp_out, threadIdx.x & 31, 32);
+    }
+}
+
+// Single-tensor elementwise pass with host-supplied constants (QuantMeasure / activations).
+template <typename CodeT>
+__global__ void __launch_bounds__(kThreads)
+fake_quant_apply_kernel(const float *__restrict__ x, float *__restrict__ y, CodeT *__restrict__ codes,
+                        int64_t n, DfqQuantParams p) {
+    QuantConsts c = make_consts(p, 0.f, 0.f);
+    int64_t begin = (int64_t)blockIdx.x * kChunk;
+    int64_t end = min(begin + (int64_t)kChunk, n);
+    apply_range<CodeT>(x, y, codes, begin, end, c, false, threadIdx.x, kThreads);
+}
+
+}  // namespace dfq
+
+using namespace dfq;
+
+static inline int64_t desc_blocks(const DfqQuantDesc &d) {
+    if (!(d.flags & DFQ_Q_PER_CHANNEL)) return (d.n + kChunk - 1) / kChunk;
+    int64_t cols = d.n / d.rows;
+    if (cols > kSmallRow) return d.rows * ((cols + kChunk - 1) / kChunk);
+    return (d.rows + kWarps - 1) / kWarps;
+}
+
+extern "C" void dfq_quant_params_host(double mn, double mx, int bits, int flags, DfqQuantParams *out) {
+    *out = make_quant_params(mn, mx, bits, flags);
+}
+
+extern "C" int dfq_quant_plan_host(DfqQuantDesc *d, int n, int64_t *total_blocks, int64_t *total_slots) {
+    int64_t b = 0, s = 0;
+    for (int i = 0; i < n; ++i) {
+        if (d[i].rows < 1) d[i].rows = 1;
+        if (!(d[i].flags & DFQ_Q_PER_CHANNEL)) d[i].rows = 1;
+        if (d[i].n <= 0 || d[i].n % d[i].rows) return (int)cudaErrorInvalidValue;
+        d[i].first_block = b;
+        d[i].range_slot = s;
+        b += desc_blocks(d[i]);
+        s += d[i].rows;
+    }
+    *total_blocks = b;
+    *total_slots = s;
+    return b > 0x7fffffffll ? (int)cudaErrorInvalidValue : 0;
+}
+
+extern "C" int dfq_fake_quant_multi_f32(const DfqQuantDesc *descs_dev, int n_desc, int64_t total_blocks,
+                                        int64_t total_slots, float *ranges_dev, void *stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    if (n_desc <= 0 || total_blocks <= 0) return 0;
+    cudaError_t e = cudaMemsetAsync(ranges_dev, 0, sizeof(float) * 2 * total_slots, st);
+    if (e != cudaSuccess) return (int)e;
+    minmax_multi_kernel<<<(unsigned)total_blocks, kThreads, 0, st>>>(descs_dev, n_desc, (unsigned *)ranges_dev);
+    decode_ranges_kernel<<<(unsigned)((total_slots + 255) / 256), 256, 0, st>>>((unsigned *)ranges_dev, total_slots);
+    fake_quant_multi_kernel<<<(unsigned)total_blocks, kThreads, 0, st>>>(descs_dev, n_desc, ranges_dev);
+    g_launches += 3;
+    return (int)cudaGetLastError();
+}
+
+extern "C" int dfq_fake_quant_apply_f32(const float *x, float *y, void *codes, int64_t n, int bits,
+                                        const DfqQuantParams *p, void *stream) {
+    if (n <= 0) return 0;
+    int64_t blocks = (n + kChunk - 1) / kChunk;
+    if (blocks > 0x7fffffffll) return (int)cudaErrorInvalidValue;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (bits <= 8) fake_quant_apply_kernel<uint8_t><<<(unsigned)blocks, kThreads, 0, st>>>(x, y, (uint8_t *)codes, n, *p);
+    else fake_quant_apply_kernel<uint16_t><<<(unsigned)blocks, kThreads, 0, st>>>(x, y, (uint16_t *)codes, n, *p);
+    g_launches += 1;
+    return (int)cudaGetLastError();
+}
+
+static int minmax_single(const float *x, int64_t n, int64_t rows, float *out, void *stream) {
+    if (n <= 0 || rows <= 0 || n % rows) return (int)cudaErrorInvalidValue;
+    DfqQuantDesc d = {};
+    d.x = x; d.n = n; d.rows = rows; d.flags = rows > 1 ? DFQ_Q_PER_CHANNEL : 0;
+    int64_t blocks = desc_blocks(d);
+    if (blocks > 0x7fffffffll) return (int)cudaErrorInvalidValue;
+    cudaStream_t st = (cudaStream_t)stream;
+    cudaError_t e = cudaMemsetAsync(out, 0, sizeof(float) * 2 * rows, st);
+    if (e != cudaSuccess) return (int)e;
+    minmax_single_kernel<<<(unsigned)blocks, kThreads, 0, st>>>(d, (unsigned *)out);
+    decode_ranges_kernel<<<(unsigned)((rows + 255) / 256), 256, 0, st>>>((unsigned *)out, rows);
+    g_launches += 2;
+    return (int)cudaGetLastError();
+}
+
+extern "C" int dfq_minmax_f32(const float *x, int64_t n, float *out_minmax, void *stream) {
+    return minmax_single(x, n, 1, out_minmax, stream);
+}
+
+extern "C" int dfq_minmax_rows_f32(const float *x, int64_t rows, int64_t cols, float *out_minmax, void *stream) {
+    return minmax_single(x, rows * cols, rows, out_minmax, stream);
+}

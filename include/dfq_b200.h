@@ -1,0 +1,168 @@
+/*
+ * dfq_b200.h -- C ABI of libdfq_b200.so (sm_100a), the drop-in boundary of the DFQ hot path.
+ *
+ * The reference (KadAMRN/Data_Free_Quantization) is pure Python/PyTorch: it has no FFI.  The
+ * entry points below are what a maintainer binds (ctypes) underneath the
+ * reference's own Python functions; each one names the reference code it replaces.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless the name ends in _host;
+ *   - tensors are contiguous fp32: weights OIHW [O, I/groups, kh, kw] (or [O, I]),
+ *     activations NCHW;
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream);
+ *   - return value is a cudaError_t (0 = success); nothing allocates, nothing synchronises
+ *     unless stated;
+ *   - there is no CPU fallback: without a CUDA device every call returns an error.
+ */
+#ifndef DFQ_B200_H
+#define DFQ_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DFQ_ABI_VERSION 1
+
+/* flags of DfqQuantDesc.flags */
+#define DFQ_Q_SYMMETRIC   1   /* utils/quantize.py:51-60 */
+#define DFQ_Q_RANGE_F32   2   /* scale formed in fp32 (min/max=None path, utils/quantize.py:27-37,66) */
+#define DFQ_Q_PER_CHANNEL 4   /* one range per row of x.view(rows, -1) (new capability) */
+#define DFQ_Q_CLAMP_OUT   8   /* clamp the dequantised output to [clip_lo, clip_hi]: clip_weight.py:29
+                                 fused behind quantize_targ_layer, as main_dfq.py:214,227 orders them */
+
+/* fp32 constants of the elementwise pass  x -> round(clamp((x+neg_min)/scale, qmin, qmax))*scale+add_back
+ * (utils/quantize.py:72-76). */
+typedef struct DfqQuantParams {
+    float neg_min, scale, qmin, qmax, add_back;
+} DfqQuantParams;
+
+/* One tensor of a multi-tensor fake-quant launch (utils/layer_transform.py:288-305 loops these). */
+typedef struct DfqQuantDesc {
+    const float *x;      /* input                                                     */
+    float *y;            /* dequantised output (may alias x)                          */
+    void *codes;         /* optional integer codes q-qmin: uint8 if bits<=8 else uint16 */
+    int64_t n;           /* elements                                                  */
+    int64_t rows;        /* per-channel: number of rows (n % rows == 0); else 1       */
+    int32_t bits;
+    int32_t flags;
+    float clip_lo, clip_hi;
+    int64_t first_block; /* filled by dfq_quant_plan_host                             */
+    int64_t range_slot;  /* filled by dfq_quant_plan_host: index into the range array */
+} DfqQuantDesc;
+
+/* One relation of cross-layer equalisation (utils/relation.py:6-33 + Cross_layer_equal.py:11-59). */
+typedef struct DfqClePair {
+    float *W1;           /* [C1, K1]  layer_first.weight                             */
+    float *W2;           /* [O2, I2, KK] layer_second.weight                          */
+    float *b1;           /* [C1] layer_first.bias (never NULL: reference adds zeros, :93-94) */
+    float *bn_w;         /* [C1] BN fake_weight or NULL                               */
+    float *bn_b;         /* [C1] BN fake_bias or NULL                                 */
+    float *S;            /* [C1] Relation.S, multiplied by every iteration's s (utils/relation.py:26-30);
+                            the caller fills it with ones when the relation has no S yet            */
+    int32_t C1, K1, O2, I2, KK;
+    int32_t stage;       /* position of the pair inside its chain (pairs of one stage are independent) */
+    int32_t first_unit;  /* filled by dfq_cle_plan_host                               */
+    int32_t n_units;     /* filled by dfq_cle_plan_host                               */
+} DfqClePair;
+
+/* One target layer whose weight enters the convergence metric (Cross_layer_equal.py:107). */
+typedef struct DfqCleLayer {
+    float *W;
+    float *W_old;        /* scratch of the same size                                  */
+    int64_t n;
+    int32_t first_chunk; /* filled by dfq_cle_layers_plan_host                        */
+    int32_t n_chunks;
+} DfqCleLayer;
+
+/* Result block of dfq_cle_run (device memory, dfq_cle_result_bytes(max_iters) = 16 + 8*max_iters):
+ *   int32 iters; int32 stall; double last_diff; double diffs[max_iters]              */
+
+/* One relation of bias absorption (bias_absorption.py:22-80). */
+typedef struct DfqAbsorbPair {
+    float *W2;           /* [O2, I2, KK]; clipped in place when clip is requested    */
+    float *b1;           /* [C1] */
+    float *b2;           /* [O2] */
+    const float *bn_w;   /* [C1] fake_weight (gamma) */
+    float *bn_b;         /* [C1] fake_bias (beta), updated */
+    float *c;            /* [C1] scratch: absorbed vector */
+    float *wc;           /* [O2] scratch: W2 . c */
+    int32_t C1, O2, I2, KK;
+    int32_t first_row;   /* filled by dfq_absorb_plan_host */
+} DfqAbsorbPair;
+
+/* One layer of bias correction (bias_correction.py:224-251). */
+typedef struct DfqCorrDesc {
+    const float *W;      /* [O, I2, KK] the FP weights (epsilon = Q(W) - W is recomputed in registers) */
+    const float *v;      /* [I2] per-input-channel vector (E[x]); NULL => 1/I2 (row mean of eps) */
+    float *out;          /* [O] sum_i eps[o,i] * v[i]                                 */
+    float *bias;         /* [O] optional: bias[o] += alpha * out[o]                   */
+    int32_t O, I2, KK, bits;
+    int32_t flags;       /* DFQ_Q_SYMMETRIC */
+    float alpha;
+    int64_t first_unit;  /* filled by dfq_corr_plan_host: first block of the reduction pass */
+    int64_t first_block; /* filled by dfq_corr_plan_host: first block of the range pass     */
+    int64_t range_slot;  /* filled by dfq_corr_plan_host: (min,max) pair in ranges_dev       */
+} DfqCorrDesc;
+
+int dfq_abi_version(void);
+const char *dfq_error_string(int err);
+/* number of kernels launched by this library since load (bench.py's gpu_launches) */
+int64_t dfq_launch_count(void);
+
+/* ---- (a) uniform fake-quantisation: utils/quantize.py:24-78 ------------------------ */
+/* host helper: the five fp32 constants from Python-float min/max (utils/quantize.py:51-68) */
+void dfq_quant_params_host(double min_value, double max_value, int bits, int flags, DfqQuantParams *out);
+/* global min/max of x -> out[0]=min, out[1]=max (float(W.min()), float(W.max())) */
+int dfq_minmax_f32(const float *x, int64_t n, float *out_minmax, void *stream);
+/* per-row min/max of x.view(rows, cols) -> out[2*r], out[2*r+1]
+ * (QuantMeasure's per-sample extrema, utils/quantize.py:110-111; per-channel ranges) */
+int dfq_minmax_rows_f32(const float *x, int64_t rows, int64_t cols, float *out_minmax, void *stream);
+/* elementwise pass with host-supplied constants (QuantMeasure.forward, utils/quantize.py:123) */
+int dfq_fake_quant_apply_f32(const float *x, float *y, void *codes, int64_t n, int bits,
+                             const DfqQuantParams *params_host, void *stream);
+/* plan + launch of the multi-tensor path (quantize_targ_layer, utils/layer_transform.py:288-305):
+ *   descs_host[T] is filled in (first_block, range_slot) and the totals returned;
+ *   the caller copies descs to the device and provides ranges_dev[2*total_slots] floats. */
+int dfq_quant_plan_host(DfqQuantDesc *descs_host, int n_desc, int64_t *total_blocks, int64_t *total_slots);
+int dfq_fake_quant_multi_f32(const DfqQuantDesc *descs_dev, int n_desc, int64_t total_blocks,
+                             int64_t total_slots, float *ranges_dev, void *stream);
+
+/* ---- (b) cross-layer equalisation: Cross_layer_equal.py:63-115 ---------------------- */
+/* sorts pairs by stage (stable) and fills first_unit/n_units */
+int dfq_cle_plan_host(DfqClePair *pairs_host, int n_pairs, int *n_stages, int *total_units);
+int dfq_cle_layers_plan_host(DfqCleLayer *layers_host, int n_layers, int *total_chunks);
+int64_t dfq_cle_result_bytes(int max_iters);
+/* Runs the whole `while diff > threshold and stall < count` loop in ONE cooperative launch.
+ * pairs must be sorted by stage (dfq_cle_plan_host does it).  result_dev: see above.
+ * smin/smax: s_min_max; is_signed: :34-35; eps: :42.  max_iters bounds the loop (the
+ * reference is unbounded).  scratch_dev: 2*n_layers doubles, zero-initialised by the call. */
+int dfq_cle_run(const DfqClePair *pairs_dev, int n_pairs, int n_stages, const DfqCleLayer *layers_dev,
+                int n_layers, int total_chunks, double smin, double smax, int is_signed, float eps,
+                double threshold, int count, int max_iters, double *scratch_dev, void *result_dev,
+                void *stream);
+
+/* ---- (c) bias absorption (+ optional weight clip): bias_absorption.py:9-80, clip_weight.py:4-33 */
+int dfq_absorb_plan_host(DfqAbsorbPair *pairs_host, int n_pairs, int *total_rows);
+/* max_dim = max over pairs of max(C1, O2) (sizes the per-element bias pass) */
+int dfq_absorb_clip(const DfqAbsorbPair *pairs_dev, int n_pairs, int total_rows, int max_dim, float N,
+                    int do_clip, float clip_lo, float clip_hi, void *stream);
+int dfq_clip_f32(float *w, int64_t n, float lo, float hi, void *stream);
+
+/* ---- (d) bias correction: bias_correction.py:111-144, 224-251 ---------------------- */
+int dfq_corr_plan_host(DfqCorrDesc *descs_host, int n_desc, int64_t *total_units, int64_t *total_blocks);
+/* ranges_dev: 2*n_desc floats (min,max per layer).  range_given != 0: the caller filled them
+ * (4 B/elt); otherwise the call reduces them first (8 B/elt).  `out` must be non-NULL.      */
+int dfq_bias_correct(const DfqCorrDesc *descs_dev, int n_desc, int64_t total_units, int64_t total_blocks,
+                     float *ranges_dev, int range_given, void *stream);
+
+/* ---- BN folding: utils/layer_transform.py:240-285 ----------------------------------- */
+int dfq_merge_bn(float *W, float *b, int64_t O, int64_t K, const float *gamma, const float *beta,
+                 const float *mean, const float *var, float eps, float *fake_weight, float *fake_bias,
+                 void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DFQ_B200_H */
