@@ -1,0 +1,120 @@
+"""Cross-layer equalisation on B200 -- host mirror of the reference's Cross_layer_equal.py.
+
+`cross_layer_equalization` keeps the reference signature (Cross_layer_equal.py:63) and runs the whole
+`while diff > Treshhold and iter_count < Count` loop in ONE cooperative persistent launch
+(csrc/cle.cu, dfq_cle_run).  Relations that touch a common tensor are ordered exactly as the reference's
+sequential loop orders them (they get increasing `stage` numbers); relations that share nothing run in
+the same stage, in parallel.
+"""
+import ctypes
+
+import torch
+import torch.nn as nn
+
+from . import _lib as L
+
+MAX_ITERS = 8192          # the reference loop is unbounded; MobileNetV2 converges in 44 iterations
+
+
+def _ensure_bias(layer):
+    if layer.bias is None:   # Cross_layer_equal.py:93-94
+        layer.bias = nn.Parameter(data=torch.zeros((layer.weight.size(0)), dtype=torch.float32,
+                                                   device=layer.weight.device), requires_grad=False)
+
+
+def _stages(relations):
+    """stage[r] = 1 + max stage of every earlier relation that touches one of r's tensors."""
+    last_use = {}
+    stages = []
+    for rel in relations:
+        first, second, bn = rel.get_idxs()
+        keys = (first, second, ("bn", bn))
+        st = max((last_use[k] + 1 for k in keys if k in last_use), default=0)
+        for k in keys:
+            last_use[k] = st
+        stages.append(st)
+    return stages
+
+
+def _w2_dims(w):
+    O2, I2 = w.shape[0], w.shape[1]
+    return O2, I2, w.numel() // (O2 * I2)
+
+
+def cross_layer_equalization(graph, relations, Target_list, s_min_max=[1e-8, 1e8], Treshhold=2e-7, Count=20,
+                             signed=False, eps=0, Save_state=True, max_iters=MAX_ITERS, return_info=False):
+    """Cross_layer_equal.py:63-115.  Weights, biases, BN fake_weight/fake_bias and Relation.S are updated in
+    place on the GPU.  Save_state (per-iteration weight plots) is a visualisation feature and is ignored."""
+    print("Cross layer equalization")
+    if len(relations) == 0:
+        return {"iters": 0, "diffs": []} if return_info else None
+    with torch.no_grad():
+        stages = _stages(relations)
+        n = len(relations)
+        pairs = (L.DfqClePair * n)()
+        keep = []
+        metric = OrderedDictNoDup()
+        dev = None
+        for i, rel in enumerate(relations):
+            first, second, bn = rel.get_idxs()
+            l1, l2, bnm = graph[first], graph[second], graph[bn]
+            _ensure_bias(l1)
+            dev = l1.weight.device
+            W1, W2 = l1.weight.data, l2.weight.data
+            C1 = W1.shape[0]
+            O2, I2, KK = _w2_dims(W2)
+            if rel.S is None:
+                rel.S = torch.ones(C1, dtype=torch.float32, device=dev)
+            elif not rel.S.is_cuda:
+                rel.S = rel.S.to(dev)
+            p = pairs[i]
+            p.W1, p.W2 = L.dev_f32(W1, "layer_first.weight"), L.dev_f32(W2, "layer_second.weight")
+            p.b1 = L.dev_f32(l1.bias.data, "layer_first.bias")
+            p.bn_w = L.dev_f32(bnm.fake_weight, "fake_weight")
+            p.bn_b = L.dev_f32(bnm.fake_bias, "fake_bias")
+            p.S = L.dev_f32(rel.S, "Relation.S")
+            p.C1, p.K1, p.O2, p.I2, p.KK, p.stage = C1, W1.numel() // C1, O2, I2, KK, stages[i]
+            metric.add(first, W1)
+            metric.add(second, W2)
+            keep.append((W1, W2))
+        # layers outside every relation never change: their mean|dW| term is exactly 0 (:107)
+        ns, tu = ctypes.c_int(), ctypes.c_int()
+        L.check(L.lib().dfq_cle_plan_host(pairs, n, ctypes.byref(ns), ctypes.byref(tu)), "dfq_cle_plan_host")
+        ws = metric.values()
+        layers = (L.DfqCleLayer * len(ws))()
+        scratch = torch.empty(sum(w.numel() for w in ws), dtype=torch.float32, device=dev)
+        off = 0
+        for i, w in enumerate(ws):
+            layers[i].W, layers[i].n = w.data_ptr(), w.numel()
+            layers[i].W_old = scratch.data_ptr() + 4 * off
+            off += w.numel()
+        tc = ctypes.c_int()
+        L.check(L.lib().dfq_cle_layers_plan_host(layers, len(ws), ctypes.byref(tc)), "dfq_cle_layers_plan_host")
+        pairs_dev, layers_dev = L.table_to_device(pairs, dev), L.table_to_device(layers, dev)
+        acc = torch.empty(2 * len(ws), dtype=torch.float64, device=dev)
+        nbytes = int(L.lib().dfq_cle_result_bytes(max_iters + 1))
+        result = torch.zeros(nbytes, dtype=torch.uint8, device=dev)
+        L.check(L.lib().dfq_cle_run(pairs_dev.data_ptr(), n, ns.value, layers_dev.data_ptr(), len(ws), tc.value,
+                                    float(s_min_max[0]), float(s_min_max[1]), int(bool(signed)), float(eps),
+                                    float(Treshhold), int(Count), int(max_iters), acc.data_ptr(), result.data_ptr(),
+                                    L.stream()), "dfq_cle_run")
+        if not return_info:
+            return None
+        host = result.cpu().numpy()
+        iters = int(host[:4].view("int32")[0])
+        diffs = host[8:].view("float64")
+        return {"iters": iters, "stall": int(host[4:8].view("int32")[0]), "diff": float(diffs[0]),
+                "diffs": diffs[1:1 + iters].tolist(), "stages": ns.value}
+
+
+class OrderedDictNoDup:
+    """Insertion-ordered set of weight tensors keyed by graph key."""
+
+    def __init__(self):
+        self._d = {}
+
+    def add(self, key, w):
+        self._d.setdefault(key, w)
+
+    def values(self):
+        return list(self._d.values())

@@ -1,0 +1,137 @@
+"""ctypes binding of libdfq_b200.so -- the C ABI declared in include/dfq_b200.h.
+
+There is no CPU fallback: if the shared object is missing or a tensor is not a contiguous fp32 CUDA
+tensor, the call raises.  PyTorch is used for device memory and streams only.
+"""
+import ctypes
+import os
+
+import torch
+
+from . import _build
+
+c_f32p = ctypes.POINTER(ctypes.c_float)
+c_void = ctypes.c_void_p
+i32, i64, f32, f64 = ctypes.c_int32, ctypes.c_int64, ctypes.c_float, ctypes.c_double
+
+
+class DfqQuantParams(ctypes.Structure):
+    _fields_ = [("neg_min", f32), ("scale", f32), ("qmin", f32), ("qmax", f32), ("add_back", f32)]
+
+
+class DfqQuantDesc(ctypes.Structure):
+    _fields_ = [("x", c_void), ("y", c_void), ("codes", c_void), ("n", i64), ("rows", i64), ("bits", i32),
+                ("flags", i32), ("clip_lo", f32), ("clip_hi", f32), ("first_block", i64), ("range_slot", i64)]
+
+
+class DfqClePair(ctypes.Structure):
+    _fields_ = [("W1", c_void), ("W2", c_void), ("b1", c_void), ("bn_w", c_void), ("bn_b", c_void), ("S", c_void),
+                ("C1", i32), ("K1", i32), ("O2", i32), ("I2", i32), ("KK", i32), ("stage", i32),
+                ("first_unit", i32), ("n_units", i32)]
+
+
+class DfqCleLayer(ctypes.Structure):
+    _fields_ = [("W", c_void), ("W_old", c_void), ("n", i64), ("first_chunk", i32), ("n_chunks", i32)]
+
+
+class DfqAbsorbPair(ctypes.Structure):
+    _fields_ = [("W2", c_void), ("b1", c_void), ("b2", c_void), ("bn_w", c_void), ("bn_b", c_void), ("c", c_void),
+                ("wc", c_void), ("C1", i32), ("O2", i32), ("I2", i32), ("KK", i32), ("first_row", i32)]
+
+
+class DfqCorrDesc(ctypes.Structure):
+    _fields_ = [("W", c_void), ("v", c_void), ("out", c_void), ("bias", c_void), ("O", i32), ("I2", i32),
+                ("KK", i32), ("bits", i32), ("flags", i32), ("alpha", f32), ("first_unit", i64),
+                ("first_block", i64), ("range_slot", i64)]
+
+
+Q_SYMMETRIC, Q_RANGE_F32, Q_PER_CHANNEL, Q_CLAMP_OUT = 1, 2, 4, 8
+ABI_VERSION = 2
+
+# every symbol include/dfq_b200.h declares: (restype, argtypes)
+P = ctypes.POINTER
+PROTOTYPES = {
+    "dfq_abi_version": (ctypes.c_int, []),
+    "dfq_error_string": (ctypes.c_char_p, [ctypes.c_int]),
+    "dfq_launch_count": (i64, []),
+    "dfq_quant_params_host": (None, [f64, f64, ctypes.c_int, ctypes.c_int, P(DfqQuantParams)]),
+    "dfq_minmax_f32": (ctypes.c_int, [c_void, i64, c_void, c_void]),
+    "dfq_minmax_rows_f32": (ctypes.c_int, [c_void, i64, i64, c_void, c_void]),
+    "dfq_fake_quant_apply_f32": (ctypes.c_int, [c_void, c_void, c_void, i64, ctypes.c_int, P(DfqQuantParams), c_void]),
+    "dfq_quant_plan_host": (ctypes.c_int, [P(DfqQuantDesc), ctypes.c_int, P(i64), P(i64)]),
+    "dfq_fake_quant_multi_f32": (ctypes.c_int, [c_void, ctypes.c_int, i64, i64, c_void, c_void]),
+    "dfq_cle_plan_host": (ctypes.c_int, [P(DfqClePair), ctypes.c_int, P(ctypes.c_int), P(ctypes.c_int)]),
+    "dfq_cle_layers_plan_host": (ctypes.c_int, [P(DfqCleLayer), ctypes.c_int, P(ctypes.c_int)]),
+    "dfq_cle_result_bytes": (i64, [ctypes.c_int]),
+    "dfq_cle_run": (ctypes.c_int, [c_void, ctypes.c_int, ctypes.c_int, c_void, ctypes.c_int, ctypes.c_int, f64, f64,
+                                   ctypes.c_int, f32, f64, ctypes.c_int, ctypes.c_int, c_void, c_void, c_void]),
+    "dfq_absorb_plan_host": (ctypes.c_int, [P(DfqAbsorbPair), ctypes.c_int, P(ctypes.c_int)]),
+    "dfq_absorb_clip": (ctypes.c_int, [c_void, ctypes.c_int, ctypes.c_int, ctypes.c_int, f32, ctypes.c_int, f32, f32,
+                                       c_void]),
+    "dfq_clip_f32": (ctypes.c_int, [c_void, i64, f32, f32, c_void]),
+    "dfq_corr_plan_host": (ctypes.c_int, [P(DfqCorrDesc), ctypes.c_int, P(i64), P(i64)]),
+    "dfq_bias_correct": (ctypes.c_int, [c_void, ctypes.c_int, i64, i64, c_void, ctypes.c_int, c_void]),
+    "dfq_merge_bn": (ctypes.c_int, [c_void, c_void, i64, i64, c_void, c_void, c_void, c_void, f32, c_void, c_void,
+                                    c_void]),
+}
+
+_lib = None
+
+
+def so_path():
+    return _build.SO
+
+
+def lib():
+    """Load libdfq_b200.so (once).  Raises if it has not been built: there is no fallback path."""
+    global _lib
+    if _lib is None:
+        path = so_path()
+        if not os.path.exists(path):
+            raise RuntimeError(
+                f"{path} is missing: build it with `python -m data_free_quantization_b200._build` "
+                "(the DFQ hot path has no CPU/PyTorch fallback)")
+        h = ctypes.CDLL(path)
+        for name, (res, args) in PROTOTYPES.items():
+            fn = getattr(h, name)               # AttributeError if the .so is stale
+            fn.restype = res
+            fn.argtypes = args
+        _lib = h
+    return _lib
+
+
+def check(err, what=""):
+    if err != 0:
+        msg = lib().dfq_error_string(int(err)).decode()
+        raise RuntimeError(f"libdfq_b200 {what}: CUDA error {err}: {msg}")
+
+
+def stream():
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def dev_f32(t, name="tensor", allow_none=False):
+    """data_ptr of a contiguous fp32 CUDA tensor; anything else is an error (no CPU path)."""
+    if t is None:
+        if allow_none:
+            return None
+        raise ValueError(f"{name} is None")
+    if not isinstance(t, torch.Tensor):
+        raise TypeError(f"{name}: expected a torch.Tensor, got {type(t)}")
+    if not t.is_cuda:
+        raise RuntimeError(f"{name} lives on {t.device}: the DFQ kernels run on CUDA only (no CPU fallback)")
+    if t.dtype != torch.float32:
+        raise TypeError(f"{name}: expected float32, got {t.dtype}")
+    if not t.is_contiguous():
+        raise ValueError(f"{name} must be contiguous")
+    return t.data_ptr()
+
+
+def table_to_device(arr, device):
+    """ctypes array of descriptor structs -> uint8 CUDA tensor holding the same bytes."""
+    raw = torch.frombuffer(bytearray(bytes(arr)), dtype=torch.uint8)
+    return raw.to(device, non_blocking=False)
+
+
+def launch_count():
+    return int(lib().dfq_launch_count())

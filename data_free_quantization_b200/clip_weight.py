@@ -1,0 +1,24 @@
+"""Weight clipping on B200 -- host mirror of the reference's clip_weight.py (clip_weight.py:4-33)."""
+import torch.nn as nn
+
+from . import _lib as L
+
+
+def clip_weight(graph, range_clip=None, targ_type=[nn.Conv2d, nn.Linear], verbose=False):
+    """layer.weight.data.clamp_(lo, hi) for every target layer, in place on the GPU.
+
+    The reference prints one warning line per non-target graph node (:32-33); pass verbose=True for that."""
+    if range_clip is None:
+        range_clip = [-15, 15]
+    assert isinstance(range_clip, (list, tuple)) and len(range_clip) == 2, \
+        "range_clip should be a list or tuple of two elements"
+    for idx, layer in graph.items():
+        if isinstance(layer, tuple(targ_type)):
+            if hasattr(layer, 'weight'):
+                w = layer.weight.data
+                L.check(L.lib().dfq_clip_f32(L.dev_f32(w, "weight"), w.numel(), float(range_clip[0]),
+                                             float(range_clip[1]), L.stream()), "dfq_clip_f32")
+            else:
+                print(f"Warning: Layer at index {idx} does not have 'weight' attribute")
+        elif verbose:
+            print(f"Warning: Layer at index {idx} is not in the target type list for clipping")

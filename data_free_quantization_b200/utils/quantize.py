@@ -1,0 +1,263 @@
+"""Host mirror of the reference's utils/quantize.py on top of libdfq_b200 (sm_100a).
+
+Same names, signatures and error behaviour as the reference module; the arithmetic runs in the
+hand-written CUDA kernels of csrc/quant.cu and csrc/act.cu through the C ABI (include/dfq_b200.h).
+Inputs must be contiguous fp32 CUDA tensors: there is no CPU path.
+"""
+import ctypes
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+from torch.autograd.function import InplaceFunction
+
+from .. import _lib as L
+
+
+def _params(min_value, max_value, num_bits, flags):
+    p = L.DfqQuantParams()
+    L.lib().dfq_quant_params_host(float(min_value), float(max_value), int(num_bits), int(flags), ctypes.byref(p))
+    return p
+
+
+def _apply(x, out, num_bits, params, codes=None):
+    n = x.numel()
+    if n == 0:
+        return out
+    L.check(L.lib().dfq_fake_quant_apply_f32(L.dev_f32(x, "input"), L.dev_f32(out, "output"),
+                                             None if codes is None else codes.data_ptr(), n, int(num_bits),
+                                             ctypes.byref(params), L.stream()), "dfq_fake_quant_apply_f32")
+    return out
+
+
+def minmax(x):
+    """[min, max] of x as a 2-element fp32 CUDA tensor (float(W.min()), float(W.max()))."""
+    out = torch.empty(2, dtype=torch.float32, device=x.device)
+    L.check(L.lib().dfq_minmax_f32(L.dev_f32(x, "input"), x.numel(), out.data_ptr(), L.stream()), "dfq_minmax_f32")
+    return out
+
+
+def minmax_rows(x, rows):
+    """Per-row [min, max] of x.view(rows, -1) -> [rows, 2] fp32 CUDA tensor."""
+    out = torch.empty(rows, 2, dtype=torch.float32, device=x.device)
+    L.check(L.lib().dfq_minmax_rows_f32(L.dev_f32(x, "input"), rows, x.numel() // rows, out.data_ptr(), L.stream()),
+            "dfq_minmax_rows_f32")
+    return out
+
+
+def fake_quant_tensors(tensors, bits, flags=0, outs=None, codes=None, clip=None, rows=None):
+    """One multi-tensor launch (range reduce + apply) over a list of tensors.
+
+    bits / flags / rows may be scalars or per-tensor lists.  Returns the [slots, 2] fp32 ranges tensor
+    (min, max per tensor, or per row for DFQ_Q_PER_CHANNEL).  utils/layer_transform.py:288-305.
+    """
+    T = len(tensors)
+    if T == 0:
+        return None
+    as_list = lambda v: list(v) if isinstance(v, (list, tuple)) else [v] * T
+    bits, flags, rows = as_list(bits), as_list(flags), as_list(rows if rows is not None else 1)
+    descs = (L.DfqQuantDesc * T)()
+    dev = tensors[0].device
+    for i, t in enumerate(tensors):
+        d = descs[i]
+        d.x = L.dev_f32(t, f"tensor[{i}]")
+        d.y = L.dev_f32(outs[i] if outs is not None else t, f"out[{i}]")
+        d.codes = codes[i].data_ptr() if codes is not None and codes[i] is not None else None
+        d.n, d.rows, d.bits = t.numel(), int(rows[i]), int(bits[i])
+        d.flags = int(flags[i]) | (L.Q_CLAMP_OUT if clip is not None else 0)
+        if clip is not None:
+            d.clip_lo, d.clip_hi = float(clip[0]), float(clip[1])
+    tb, ts = L.i64(), L.i64()
+    L.check(L.lib().dfq_quant_plan_host(descs, T, ctypes.byref(tb), ctypes.byref(ts)), "dfq_quant_plan_host")
+    table = L.table_to_device(descs, dev)
+    ranges = torch.empty(ts.value, 2, dtype=torch.float32, device=dev)
+    L.check(L.lib().dfq_fake_quant_multi_f32(table.data_ptr(), T, tb.value, ts.value, ranges.data_ptr(), L.stream()),
+            "dfq_fake_quant_multi_f32")
+    return ranges
+
+
+class UniformQuantize(InplaceFunction):
+    """utils/quantize.py:16-85 -- uniform fake-quantisation, straight-through backward."""
+
+    @staticmethod
+    def forward(ctx, input, num_bits=8, min_value=None, max_value=None, inplace=False, symmetric=False,
+                num_chunks=None):
+        x = input.detach()
+        L.dev_f32(x, "input")
+        ctx.inplace, ctx.num_bits = inplace, num_bits
+        if inplace:
+            ctx.mark_dirty(input)
+            output = input
+        else:
+            output = torch.empty_like(x)
+        if x.numel() == 0:
+            return output
+        flags = L.Q_SYMMETRIC if symmetric else 0
+        if min_value is not None and max_value is not None:
+            # Python-float range: scale formed in double (utils/quantize.py:51-68)
+            return _apply(x, output, num_bits, _params(min_value, max_value, num_bits, flags))
+        # min/max=None: 0-dim fp32 tensor statistics, scale formed in fp32 (:26-37)
+        B = x.shape[0]
+        num_chunks = B if num_chunks is None else num_chunks
+        rows = B // num_chunks
+        if rows == 1 and min_value is None and max_value is None:
+            fake_quant_tensors([x], num_bits, flags | L.Q_RANGE_F32, outs=[output])
+            return output
+        mm = minmax_rows(x, rows).mean(0)                   # y.min(-1)[0].mean(-1), y.max(-1)[0].mean(-1)
+        lo, hi = (float(v) for v in mm.tolist())
+        lo = lo if min_value is None else float(min_value)
+        hi = hi if max_value is None else float(max_value)
+        return _apply(x, output, num_bits, _params(lo, hi, num_bits, flags | L.Q_RANGE_F32))
+
+    @staticmethod
+    def backward(ctx, grad_output):
+        return grad_output, None, None, None, None, None, None
+
+
+def quantize(x, num_bits=8, min_value=None, max_value=None, inplace=False, symmetric=False, num_chunks=None):
+    """utils/quantize.py:88-89."""
+    return UniformQuantize().apply(x, num_bits, min_value, max_value, inplace, symmetric, num_chunks)
+
+
+def quantize_codes(x, num_bits=8, min_value=None, max_value=None, symmetric=False):
+    """Fake-quantise and also return the integer codes q - qmin (uint8 for <=8 bits, else int16 storage).
+
+    Returns (dequantised fp32, codes, (scale, min)) -- the packed form SURVEY.md 8(f).4 asks for.
+    """
+    L.dev_f32(x, "input")
+    flags = L.Q_SYMMETRIC if symmetric else 0
+    if min_value is None or max_value is None:
+        lo, hi = (float(v) for v in minmax(x).tolist())
+        min_value = lo if min_value is None else min_value
+        max_value = hi if max_value is None else max_value
+    p = _params(min_value, max_value, num_bits, flags)
+    out = torch.empty_like(x)
+    codes = torch.empty(x.shape, dtype=torch.uint8 if num_bits <= 8 else torch.int16, device=x.device)
+    _apply(x, out, num_bits, p, codes)
+    return out, codes, (p.scale, p.add_back)
+
+
+def sample_minmax_mean(x):
+    """(mean_n min_chw x, mean_n max_chw x) as a [2] fp32 CUDA tensor -- utils/quantize.py:110-111."""
+    n = x.size(0)
+    return minmax_rows(x.detach(), n).mean(0)
+
+
+class QuantMeasure(nn.Module):
+    """utils/quantize.py:94-126 -- activation range tracker + fake-quant of the activation."""
+
+    def __init__(self, update_stat=False, num_bits=8, momentum=0.1):
+        super(QuantMeasure, self).__init__()
+        self.register_buffer('running_min', torch.zeros(1))
+        self.register_buffer('running_max', torch.zeros(1))
+        self.momentum = momentum
+        self.num_bits = num_bits
+        self.update_stat = update_stat
+
+    def forward(self, input):
+        if self.update_stat or self.training:
+            mm = sample_minmax_mean(input)
+        if self.update_stat:
+            # Python max()/min() on tensors: the running value is kept unless strictly improved (:110-111)
+            self.running_max = torch.where(mm[1] > self.running_max, mm[1], self.running_max)
+            self.running_min = torch.where(mm[0] < self.running_min, mm[0], self.running_min)
+        if self.training:
+            min_value, max_value = mm[0], mm[1]
+            self.running_min.mul_(1 - self.momentum).add_(min_value * self.momentum)
+            self.running_max.mul_(1 - self.momentum).add_(max_value * self.momentum)
+        else:
+            min_value, max_value = self.running_min, self.running_max
+        return quantize(input, self.num_bits, min_value=float(min_value), max_value=float(max_value), num_chunks=16)
+
+    def set_update_stat(self, update_stat):
+        self.update_stat = update_stat
+
+
+def _quant_weight(weight, num_bits):
+    """quantize(W, bits, float(W.min()), float(W.max())) without the two host round trips."""
+    out = torch.empty_like(weight)
+    fake_quant_tensors([weight.detach()], num_bits, 0, outs=[out])
+    return out
+
+
+class QuantConv2d(nn.Conv2d):
+    """utils/quantize.py:213-238 -- activation, weight and bias re-quantised on every forward."""
+
+    def __init__(self, in_channels, out_channels, kernel_size, stride=1, padding=0, dilation=1, groups=1, bias=True,
+                 num_bits=8, num_bits_act=8, num_bits_bias=16, momentum=0.1):
+        super(QuantConv2d, self).__init__(in_channels, out_channels, kernel_size, stride, padding, dilation, groups,
+                                          bias)
+        self.num_bits = num_bits
+        self.num_bits_bias = num_bits_bias
+        self.quant = QuantMeasure(num_bits=num_bits_act, momentum=momentum)
+
+    def forward(self, input):
+        input = self.quant(input)
+        qweight = _quant_weight(self.weight, self.num_bits)
+        qbias = quantize(self.bias, num_bits=self.num_bits_bias) if self.bias is not None else None
+        return F.conv2d(input, qweight, qbias, self.stride, self.padding, self.dilation, self.groups)
+
+
+class QuantNConv2d(nn.Conv2d):
+    """utils/quantize.py:240-256 -- only the activation is quantised (weights were quantised offline)."""
+
+    def __init__(self, in_channels, out_channels, kernel_size, stride=1, padding=0, dilation=1, groups=1, bias=True,
+                 num_bits=8, num_bits_act=8, momentum=0.1):
+        super(QuantNConv2d, self).__init__(in_channels, out_channels, kernel_size, stride, padding, dilation, groups,
+                                           bias)
+        self.quant = QuantMeasure(num_bits=num_bits_act, momentum=momentum)
+
+    def forward(self, input):
+        input = self.quant(input)
+        return F.conv2d(input, self.weight, self.bias, self.stride, self.padding, self.dilation, self.groups)
+
+
+class QuantLinear(nn.Linear):
+    """utils/quantize.py:326-348."""
+
+    def __init__(self, in_features, out_features, bias=True, num_bits=8, num_bits_act=8, num_bits_bias=16,
+                 momentum=0.1):
+        super(QuantLinear, self).__init__(in_features, out_features, bias)
+        self.num_bits = num_bits
+        self.num_bits_bias = num_bits_bias
+        self.quant = QuantMeasure(num_bits=num_bits_act, momentum=momentum)
+
+    def forward(self, input):
+        input = self.quant(input)
+        qweight = _quant_weight(self.weight, self.num_bits)
+        qbias = quantize(self.bias, num_bits=self.num_bits_bias) if self.bias is not None else None
+        return F.linear(input, qweight, qbias)
+
+
+class QuantNLinear(nn.Linear):
+    """utils/quantize.py:350-363."""
+
+    def __init__(self, in_features, out_features, bias=True, num_bits=8, num_bits_act=8, momentum=0.1):
+        super(QuantNLinear, self).__init__(in_features, out_features, bias)
+        self.quant = QuantMeasure(num_bits=num_bits_act, momentum=momentum)
+
+    def forward(self, input):
+        input = self.quant(input)
+        return F.linear(input, self.weight, self.bias)
+
+
+# The reference's QConv2d / QLinear (:129-210, :260-323) add per-channel `scale`/`scale_prev` merging on top of
+# QuantConv2d / QuantLinear; no script of the hot path instantiates them with scales, so they alias the plain forms.
+QConv2d = QuantConv2d
+QLinear = QuantLinear
+
+
+def set_layer_bits(graph, bits_weight=8, bits_activation=8, bits_bias=16, targ_type=None):
+    """utils/quantize.py:366-379, bug-compatible: QuantMeasure(bits_activation) sets `update_stat`
+    (first positional argument), not `num_bits`."""
+    print("Setting num_bits for targ layers...")
+    assert targ_type != None, "targ_type cannot be None"
+    for idx in graph:
+        if type(graph[idx]) in targ_type:
+            if hasattr(graph[idx], 'quant'):
+                old = graph[idx].quant
+                graph[idx].quant = QuantMeasure(bits_activation).to(old.running_min.device)
+            if hasattr(graph[idx], 'num_bits'):
+                graph[idx].num_bits = bits_weight
+            if hasattr(graph[idx], 'num_bits_bias'):
+                graph[idx].num_bits_bias = bits_bias

@@ -25,6 +25,10 @@ extern "C" {
 
 #define DFQ_ABI_VERSION 1
 
+#if defined(__GNUC__)
+#pragma GCC visibility push(default)   /* the library is built with -fvisibility=hidden */
+#endif
+
 /* flags of DfqQuantDesc.flags */
 #define DFQ_Q_SYMMETRIC   1   /* utils/quantize.py:51-60 */
 #define DFQ_Q_RANGE_F32   2   /* scale formed in fp32 (min/max=None path, utils/quantize.py:27-37,66) */
@@ -161,6 +165,10 @@ int dfq_bias_correct(const DfqCorrDesc *descs_dev, int n_desc, int64_t total_uni
 int dfq_merge_bn(float *W, float *b, int64_t O, int64_t K, const float *gamma, const float *beta,
                  const float *mean, const float *var, float eps, float *fake_weight, float *fake_bias,
                  void *stream);
+
+#if defined(__GNUC__)
+#pragma GCC visibility pop
+#endif
 
 #ifdef __cplusplus
 }
