@@ -1,0 +1,451 @@
+"""bench.py -- MobileNetV2 W8A8 DFQ pipeline on B200 (BASELINE.json metric, configs[1]).
+
+A "step" is one pass of the weight-side DFQ hot path over the seeded synthetic MobileNetV2:
+merge_batchnorm -> cross_layer_equalization -> bias_absorption -> set_layer_bits -> merge_batchnorm ->
+quantize_targ_layer -> set_quant_minmax -> clip_weight -> bias_correction  (main_dfq.py:188-231; graph tracing /
+switch_layers is out of scope and happens once, outside the timed region).
+
+  python bench.py [--gpus N --steps K --warmup W]      one JSON line (rank 0)
+  python bench.py --impl reference ...                 the CPU port of the reference path (oracle/), same line shape
+
+value = ms per pipeline pass with the weights already in HBM (each rank runs its own pipeline; N ranks finish N
+pipelines per step, so value = max-over-ranks step time / N: weak scaling over independent models);
+e2e    = the same through the public API from pinned HOST state dict to HOST quantised state dict.
+The line also carries the other two parts of BASELINE.json's metric: fake-quant / bias-correction GB/s on a
+tensor larger than L2 (`kernels`) and W8A8 eval images/s at batch 256 per GPU (`eval`).
+"""
+import argparse
+import ctypes
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "MobileNetV2 W8A8 DFQ pipeline ms"
+UNIT = "ms"
+WORKLOAD = "MobileNetV2 DFQ W8A8 per-tensor (--relu --equalize --absorption --clip_weight --quantize --correction)"
+EVAL_BATCH = 256
+MICRO_ELEMS = 1 << 28            # 1 GiB fp32 > 126 MB L2
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-eval", action="store_true")
+    ap.add_argument("--no-micro", action="store_true")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--micro-elems", type=int, default=MICRO_ELEMS)
+    return ap.parse_args()
+
+
+class Args:
+    """main_dfq.py flags of the benchmarked configuration."""
+    quantize = relu = equalize = absorption = clip_weight = correction = True
+    visualize = False
+    bits_weight = bits_activation = bits_bias = 8
+    correction_mode = "ref"
+
+
+# ------------------------------------------------------------------------------------------ clocks
+class ClockSampler:
+    """nvidia-smi sampled every 200 ms while the timed region runs (B200_PROFILING.md clocks line)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def __enter__(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+        return self
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def __exit__(self, *exc):
+        if self.proc is not None:
+            time.sleep(0.25)
+            self.proc.terminate()
+            self.t.join(timeout=2)
+        return False
+
+    def summary(self):
+        sm, mx, reasons = [], 0.0, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[1]))
+                mx = max(mx, float(r[2]))
+            except (ValueError, IndexError):
+                continue
+            for n, v in zip(names, r[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx or None, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------ the workload
+class PipelineCase:
+    """Seeded synthetic MobileNetV2 on one GPU; parameters and BN buffers are views into one flat HBM buffer so a
+    step can be re-armed with one device copy (value) or one pinned-host copy (e2e)."""
+
+    def __init__(self, dev):
+        import torch
+        import torch.nn as nn
+        from data_free_quantization_b200.fixtures import synthetic_state_dict
+        from data_free_quantization_b200.graph import TorchTransformer
+        from data_free_quantization_b200.modeling.mobilenetv2 import mobilenet_v2
+        from data_free_quantization_b200.utils.layer_transform import switch_layers
+        from data_free_quantization_b200.utils.quantize import QuantConv2d, QuantLinear, QuantMeasure
+        self.torch, self.dev = torch, dev
+        torch.manual_seed(0)
+        model = mobilenet_v2(None)
+        model.load_state_dict(synthetic_state_dict(model, seed=0, bn_seed=1))
+        model = model.to(dev).eval()
+        md = {1: [(nn.Conv2d, QuantConv2d), (nn.Linear, QuantLinear)], 0: [(nn.ReLU6, nn.ReLU)]}
+        self.targ = (QuantConv2d, QuantLinear)
+        self.model, self.tr = switch_layers(model, TorchTransformer(), torch.ones(4, 3, 224, 224, device=dev), md,
+                                            ignore_layer=[QuantMeasure], quant_op=True)
+        self.graph, self.bottoms = self.tr.log.getGraph(), self.tr.log.getBottoms()
+        # flat layout: every float tensor of the (un-merged) model, 16-byte aligned
+        self.slots, off = [], 0
+        self.no_bias = []
+        for name, m in self.model.named_modules():
+            if isinstance(m, (nn.Conv2d, nn.Linear, nn.BatchNorm2d)):
+                if isinstance(m, (nn.Conv2d, nn.Linear)) and m.bias is None:
+                    self.no_bias.append(m)
+                for attr in ("weight", "bias", "running_mean", "running_var"):
+                    t = getattr(m, attr, None)
+                    if t is None:
+                        continue
+                    self.slots.append((m, attr, off, t.numel(), tuple(t.shape)))
+                    off += (t.numel() + 3) // 4 * 4
+        self.flat = torch.zeros(off, dtype=torch.float32, device=dev)
+        for m, attr, o, n, shape in self.slots:
+            view = self.flat[o:o + n].view(shape)
+            view.copy_(getattr(m, attr).data)
+            getattr(m, attr).data = view
+        self.pristine = self.flat.clone()
+        self.host_in = torch.empty(off, dtype=torch.float32).pin_memory()
+        self.host_in.copy_(self.pristine)
+        self.bn_eps = {m: m.eps for m in self.model.modules() if isinstance(m, nn.BatchNorm2d)}
+        self.targets = [m for m in self.graph.values() if type(m) in self.targ]
+        self.n_bias = sum(m.weight.shape[0] for m in self.targets)
+        self.host_out = torch.empty(off + self.n_bias, dtype=torch.float32).pin_memory()
+        self.dev_bias = torch.empty(self.n_bias, dtype=torch.float32, device=dev)
+        self.weight_elems = sum(m.weight.numel() for m in self.targets)
+
+    def rearm(self, from_host=False):
+        """Undo the previous pass: original weights/BN statistics, no folded biases, fresh relations."""
+        if from_host:
+            self.flat.copy_(self.host_in, non_blocking=True)
+        else:
+            self.flat.copy_(self.pristine)
+        for m in self.no_bias:
+            m.bias = None
+        for m, eps in self.bn_eps.items():
+            m.eps = eps
+
+    def step(self):
+        from data_free_quantization_b200.main_dfq import run_dfq_steps
+        return run_dfq_steps(self.model, self.graph, self.bottoms, Args, self.targ)
+
+    def result_to_host(self):
+        """Quantised state dict -> pinned host memory (weights + BN buffers in one copy, biases in another)."""
+        torch = self.torch
+        torch.cat([m.bias.data for m in self.targets], out=self.dev_bias)
+        n = self.flat.numel()
+        self.host_out[:n].copy_(self.flat, non_blocking=True)
+        self.host_out[n:].copy_(self.dev_bias, non_blocking=True)
+
+    def h2d_bytes(self):
+        return self.flat.numel() * 4
+
+    def d2h_bytes(self):
+        return self.host_out.numel() * 4
+
+
+def flush_l2(torch, scratch):
+    scratch.add_(1.0)            # 256 MiB read+write > 126 MB L2
+
+
+def time_steps(torch, fn, steps, before=None):
+    """Sum of per-step CUDA-event durations (ms); `before` (re-arm + L2 flush) runs outside the timed events."""
+    total = 0.0
+    for _ in range(steps):
+        if before is not None:
+            before()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        fn()
+        b.record()
+        b.synchronize()
+        total += a.elapsed_time(b)
+    return total
+
+
+# ------------------------------------------------------------------------------------------ kernel rooflines
+def kernel_rooflines(torch, dev, peak_gbs, n_elems, reps=10):
+    """HBM-bound kernels on one tensor larger than L2, each timed alone with CUDA events on the launch stream.
+    Algorithmic bytes per element: fake-quant with range given 8, with range reduction 12,
+    fused bias correction 8, absorb+clip 8, min/max 4."""
+    from data_free_quantization_b200 import _lib as L
+    from data_free_quantization_b200.bias_correction import eps_dot
+    from data_free_quantization_b200.utils.quantize import fake_quant_tensors, minmax, quantize
+    import torch.nn as nn
+    g = torch.Generator(device=dev).manual_seed(3)
+    x = torch.randn(n_elems, device=dev, generator=g) * 0.1
+    y = torch.empty_like(x)
+    lo, hi = (float(v) for v in minmax(x).tolist())
+    lin = nn.Linear(2, 2)
+    lin.weight = nn.Parameter(x.view(1024, -1), requires_grad=False)
+    v = torch.randn(n_elems // 1024, device=dev, generator=g)
+    cases = [
+        ("fake_quant_apply (range given)", 8, lambda: quantize(x, 8, lo, hi)),
+        ("fake_quant_multi (min/max reduce + apply)", 12, lambda: fake_quant_tensors([x], 8, 0, outs=[y])),
+        ("minmax", 4, lambda: minmax(x)),
+        ("bias_correct (range reduce + eps.E[x])", 8, lambda: eps_dot([lin], [v], 8)),
+    ]
+    out = []
+    for name, bpe, fn in cases:
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize()
+        ts = []
+        for _ in range(reps):
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            fn()
+            b.record()
+            b.synchronize()
+            ts.append(a.elapsed_time(b))
+        ms = sum(ts) / len(ts)
+        gbs = bpe * n_elems / (ms * 1e-3) / 1e9
+        out.append({"kernel": name, "bytes_per_elt": bpe, "elems": n_elems, "ms": round(ms, 4),
+                    "achieved": round(gbs, 1), "best": round(bpe * n_elems / (min(ts) * 1e-3) / 1e9, 1),
+                    "peak": peak_gbs, "unit": "GB/s", "frac": round(gbs / peak_gbs, 4)})
+    return out
+
+
+# ------------------------------------------------------------------------------------------ quantised eval
+def eval_images_per_s(torch, case, batch, steps, warmup):
+    """W8A8 eval of the quantised model on a synthetic batch (main_dfq.py:66-113 loop body, one batch per step)."""
+    from data_free_quantization_b200.utils.layer_transform import replace_op, restore_op
+    dev = case.dev
+    x = torch.randn(batch, 3, 224, 224, generator=torch.Generator().manual_seed(2)).to(dev)
+    replace_op()
+    try:
+        with torch.no_grad():
+            for _ in range(warmup):
+                case.model(x)
+            torch.cuda.synchronize()
+            ms = time_steps(torch, lambda: case.model(x), steps)
+    finally:
+        restore_op()
+    return batch * steps / (ms * 1e-3), ms / steps
+
+
+# ------------------------------------------------------------------------------------------ CPU baseline
+def oracle_pipeline_once():
+    """The reference path restated in C (oracle/, 1 host thread) on the same seeded MobileNetV2.  Returns ms."""
+    import json as _json
+    import torch
+    from oracle import oracle as O
+    from oracle import pipeline as P
+    from data_free_quantization_b200.fixtures import synthetic_state_dict
+    from data_free_quantization_b200.modeling.mobilenetv2 import mobilenet_v2
+    O.build()
+    gold = _json.load(open(os.path.join(ROOT, "tests", "golden", "mobilenetv2_dfq.json")))
+    topo = {"targets": gold["topo"]["targets"], "conv_bn": gold["topo"]["conv_bn"],
+            "relations": [tuple(r) for r in gold["topo"]["relations"]]}
+    torch.manual_seed(0)
+    model = mobilenet_v2(None)
+    sd = synthetic_state_dict(model, seed=0, bn_seed=1)
+    st = {k: v.numpy().copy() for k, v in sd.items() if v.dtype == torch.float32}
+    t = time.perf_counter()
+    P.merge_batchnorm(st, topo)
+    iters, _, _ = P.cross_layer_equalization(st, topo)
+    P.bias_absorption(st, topo, 3)
+    for bn in set(topo["conv_bn"].values()):
+        st[bn + ".fake_weight"].fill(1.0)
+        st[bn + ".fake_bias"].fill(0.0)
+    P.quantize_targ_layer(st, topo, 8, 8)
+    P.clip_weight(st, topo)
+    return (time.perf_counter() - t) * 1e3, iters
+
+
+def reference_arm(args):
+    """--impl reference: the CPU port of the reference path, timed on this box's host cores."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    for _ in range(min(args.warmup, 1)):
+        oracle_pipeline_once()
+    ts = [oracle_pipeline_once()[0] for _ in range(max(1, min(args.steps, 10)))]
+    ms = sum(ts) / len(ts)
+    sample = ("full pipeline (merge+CLE 44 iterations+absorb+quantize+clip) on the seeded MobileNetV2, "
+              f"{len(ts)} passes; C restatement of the reference (oracle/dfq_oracle.c), not the Python original "
+              "(that takes ~80-110 s per pass, BASELINE.md)")
+    line = {"impl": "reference", "metric": METRIC, "value": round(ms, 3), "unit": UNIT, "n_gpus": args.gpus,
+            "steps": len(ts), "warmup": min(args.warmup, 1), "ms_per_step": round(ms, 3), "higher_is_better": False,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": WORKLOAD},
+            "cpu_baseline": {"value": round(ms, 3), "unit": UNIT, "cores": 1, "kind": "port", "sample": sample},
+            "e2e": {"value": round(ms, 3), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def measured_peak():
+    try:
+        p = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        return float(p["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs, copy)"
+    except (OSError, KeyError, ValueError):
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        return reference_arm(args)
+    import torch
+    import torch.distributed as dist
+    from data_free_quantization_b200 import _lib as L
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (the DFQ hot path has no CPU fallback)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    L.lib()
+    peak, peak_src = measured_peak()
+    case = PipelineCase(dev)
+    scratch = torch.zeros(64 << 20, dtype=torch.float32, device=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    import contextlib
+    import io
+    quiet = contextlib.redirect_stdout(io.StringIO())      # the reference-shaped API prints progress lines
+
+    def rearm_dev():
+        case.rearm(False)
+        flush_l2(torch, scratch)
+
+    def rearm_host():
+        flush_l2(torch, scratch)
+        for m in case.no_bias:
+            m.bias = None
+        for m, eps in case.bn_eps.items():
+            m.eps = eps
+
+    def e2e_step():
+        case.flat.copy_(case.host_in, non_blocking=True)
+        case.step()
+        case.result_to_host()
+
+    with quiet:
+        for _ in range(args.warmup):
+            rearm_dev()
+            case.step()
+        barrier()
+        l0 = L.launch_count()
+        with ClockSampler(local) as clocks:
+            t_dev = time_steps(torch, case.step, args.steps, before=rearm_dev)
+            barrier()
+            launches = L.launch_count() - l0
+            for _ in range(args.warmup):
+                rearm_host()
+                e2e_step()
+            barrier()
+            t_e2e = time_steps(torch, e2e_step, args.steps, before=rearm_host)
+            barrier()
+    ms_dev, ms_e2e = t_dev / args.steps, t_e2e / args.steps
+    if world > 1:
+        t = torch.tensor([ms_dev, ms_e2e], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_dev, ms_e2e = t.tolist()
+
+    # per-step breakdown (separate pass, host-synchronised per stage; not part of the timed numbers)
+    stages = {}
+    with quiet:
+        from data_free_quantization_b200.main_dfq import run_dfq_steps
+        rearm_dev()
+        run_dfq_steps(case.model, case.graph, case.bottoms, Args, case.targ, timings=stages)
+        cle_ms = stages.get("cross_layer_equalization", 0.0)
+
+    ev = None
+    if not args.no_eval:
+        with quiet:
+            ips, ev_ms = eval_images_per_s(torch, case, EVAL_BATCH, max(3, args.steps // 4), 3)
+        if world > 1:
+            t = torch.tensor([ev_ms], device=dev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ev_ms = float(t[0])
+        ev = {"images_per_s": round(EVAL_BATCH * world / (ev_ms * 1e-3), 1), "batch_per_gpu": EVAL_BATCH,
+              "ms_per_batch": round(ev_ms, 3),
+              "path": "QuantMeasure/fake-quant: libdfq_b200 kernels; conv/linear arithmetic: cuDNN/cuBLAS fp32 "
+                      "(library) until the tcgen05 u8 kernels land"}
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    kernels = kernel_rooflines(torch, dev, peak, args.micro_elems) if not args.no_micro else []
+    # roofline of the step's dominant kernel: the persistent CLE kernel (algorithmic 12 B x 4 252 832 elements per
+    # outer iteration x 44 iterations) over its host-synchronised duration
+    cle_bytes = 12 * 4252832 * 44
+    roof = {"kernel": "cle_persistent_kernel (44 iterations in one cooperative launch)", "bound": "hbm",
+            "achieved": round(cle_bytes / (cle_ms * 1e-3) / 1e9, 1) if cle_ms else None, "peak": peak,
+            "unit": "GB/s", "frac": round(cle_bytes / (cle_ms * 1e-3) / 1e9 / peak, 4) if cle_ms else None,
+            "traffic": None, "peak_source": peak_src,
+            "note": "14 MB working set lives in L2; the kernel is grid-barrier/latency-bound at this model size. "
+                    "The HBM-bound kernels are measured on a 1 GiB tensor in `kernels`."}
+    cpu = None
+    if not args.no_cpu_baseline:
+        ms_cpu, iters = oracle_pipeline_once()
+        cpu = {"value": round(ms_cpu, 3), "unit": UNIT, "cores": 1, "kind": "port",
+               "sample": f"one full pipeline pass (CLE {iters} iterations) of the C restatement of the reference "
+                         "(oracle/dfq_oracle.c) on the same seeded MobileNetV2; the Python original needs "
+                         "80-110 s per pass (BASELINE.md)"}
+    line = {"metric": METRIC, "value": round(ms_dev / world, 4), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": round(ms_dev, 4), "higher_is_better": False, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "weights": case.weight_elems, "pipelines_per_step": world,
+                       "l2": "flushed between timed steps (256 MiB scratch write)",
+                       "excluded": "graph tracing / switch_layers (out of scope, SURVEY.md 8d)"},
+            "e2e": {"value": round(ms_e2e / world, 4), "unit": UNIT, "h2d_bytes_per_step": case.h2d_bytes(),
+                    "d2h_bytes_per_step": case.d2h_bytes()},
+            "gpu_launches": int(launches), "stages_ms": {k: round(v, 3) for k, v in stages.items()},
+            "roofline": roof, "kernels": kernels, "eval": ev, "cpu_baseline": cpu, "clocks": clocks.summary()}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

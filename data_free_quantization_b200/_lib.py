@@ -40,8 +40,9 @@ class DfqAbsorbPair(ctypes.Structure):
 
 
 class DfqCorrDesc(ctypes.Structure):
-    _fields_ = [("W", c_void), ("v", c_void), ("out", c_void), ("bias", c_void), ("O", i32), ("I2", i32),
-                ("KK", i32), ("bits", i32), ("flags", i32), ("alpha", f32), ("first_unit", i64),
+    _fields_ = [("W", c_void), ("v", c_void), ("out", c_void), ("bias", c_void), ("fold", c_void), ("O", i32),
+                ("I2", i32), ("KK", i32), ("bits", i32), ("flags", i32), ("alpha", f32), ("fold_mod", i32),
+                ("groups", i32), ("first_unit", i64),
                 ("first_block", i64), ("range_slot", i64)]
 
 

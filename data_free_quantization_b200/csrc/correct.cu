@@ -46,12 +46,15 @@ __global__ void corr_decode_kernel(unsigned *ranges, int64_t slots) {
 __global__ void corr_zero_kernel(const DfqCorrDesc *__restrict__ descs) {
     const DfqCorrDesc &d = descs[blockIdx.x];
     for (int o = threadIdx.x; o < d.O; o += blockDim.x) d.out[o] = 0.0f;
+    if (d.fold)
+        for (int c = threadIdx.x; c < d.fold_mod; c += blockDim.x) d.fold[c] = 0.0f;
 }
 
 // partial sum over elements [b, e) of one row (indices relative to the row start)
 __device__ __forceinline__ double row_partial(const float *__restrict__ row, const float *__restrict__ v,
                                               int64_t b, int64_t e, int KK, float inv_I,
-                                              const QuantConsts &c, int tid, int nthr) {
+                                              const QuantConsts &c, int tid, int nthr,
+                                              float *fold, int fold_mod, int64_t row_chan0) {
     double acc = 0.0;
     const float *p = row + b;
     int64_t n = e - b;
@@ -67,15 +70,19 @@ __device__ __forceinline__ double row_partial(const float *__restrict__ row, con
             float q;
             float dq = fake_quant_elem(xs[u], c, q);
             float eps = __fsub_rn(dq, xs[u]);                       // :130
-            float vi = v ? v[(KK == 1) ? (idx + u) : (idx + u) / KK] : inv_I;
+            int64_t ch = (KK == 1) ? (idx + u) : (idx + u) / KK;
+            float vi = v ? v[ch] : inv_I;
             acc += (double)eps * (double)vi;
+            if (fold) atomicAdd(fold + (row_chan0 + ch) % fold_mod, eps);
         }
     }
     for (int64_t k = (n4 << 2) + tid; k < n; k += nthr) {
         float x = p[k], q;
         float eps = __fsub_rn(fake_quant_elem(x, c, q), x);
-        float vi = v ? v[(KK == 1) ? (b + k) : (b + k) / KK] : inv_I;
+        int64_t ch = (KK == 1) ? (b + k) : (b + k) / KK;
+        float vi = v ? v[ch] : inv_I;
         acc += (double)eps * (double)vi;
+        if (fold) atomicAdd(fold + (row_chan0 + ch) % fold_mod, eps);
     }
     return acc;
 }
@@ -94,14 +101,18 @@ corr_reduce_kernel(const DfqCorrDesc *__restrict__ descs, int n_desc, const floa
     if (row_len <= kCorrSmallRow) {                       // one warp per row
         int64_t o = j * kWarps + (threadIdx.x >> 5);
         if (o >= d.O) return;
-        double acc = row_partial(d.W + o * row_len, d.v, 0, row_len, d.KK, inv_I, c, threadIdx.x & 31, 32);
+        const float *vrow = (d.v && d.groups > 1) ? d.v + (o / (d.O / d.groups)) * d.I2 : d.v;
+        double acc = row_partial(d.W + o * row_len, vrow, 0, row_len, d.KK, inv_I, c, threadIdx.x & 31, 32,
+                                 d.fold, d.fold_mod, o * d.I2);
         acc = warp_sum(acc);
         if ((threadIdx.x & 31) == 0) d.out[o] = (float)acc;
     } else {                                              // one block per (row, chunk)
         int64_t cpr = (row_len + kChunk - 1) / kChunk;
         int64_t o = j / cpr, b = (j % cpr) * kChunk;
         int64_t e = min(b + (int64_t)kChunk, row_len);
-        double acc = row_partial(d.W + o * row_len, d.v, b, e, d.KK, inv_I, c, threadIdx.x, kThreads);
+        const float *vrow = (d.v && d.groups > 1) ? d.v + (o / (d.O / d.groups)) * d.I2 : d.v;
+        double acc = row_partial(d.W + o * row_len, vrow, b, e, d.KK, inv_I, c, threadIdx.x, kThreads,
+                                 d.fold, d.fold_mod, o * d.I2);
         acc = warp_sum(acc);
         if ((threadIdx.x & 31) == 0) smd[threadIdx.x >> 5] = acc;
         __syncthreads();

