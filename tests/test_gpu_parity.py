@@ -114,8 +114,9 @@ def test_clip_and_merge_bn(oracle):
     mu, var = rng.standard_normal(O).astype(np.float32), (rng.random(O) + 0.5).astype(np.float32)
     Wd, bd = _t(W), _t(b)
     fw, fb = torch.empty(O, device=DEV), torch.empty(O, device=DEV)
-    L.check(L.lib().dfq_merge_bn(Wd.data_ptr(), bd.data_ptr(), O, K, _t(g).data_ptr(), _t(be).data_ptr(),
-                                 _t(mu).data_ptr(), _t(var).data_ptr(), 1e-5, fw.data_ptr(), fb.data_ptr(), L.stream()))
+    gd, bed, mud, vard = _t(g), _t(be), _t(mu), _t(var)
+    L.check(L.lib().dfq_merge_bn(Wd.data_ptr(), bd.data_ptr(), O, K, gd.data_ptr(), bed.data_ptr(),
+                                 mud.data_ptr(), vard.data_ptr(), 1e-5, fw.data_ptr(), fb.data_ptr(), L.stream()))
     oracle.merge_bn(W, b, g, be, mu, var, 1e-5)
     assert Wd.cpu().numpy().tobytes() == W.tobytes() and bd.cpu().numpy().tobytes() == b.tobytes()
     assert np.array_equal(fw.cpu().numpy(), np.abs(g)) and np.array_equal(fb.cpu().numpy(), be)
