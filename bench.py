@@ -440,7 +440,7 @@ def main():
                        "excluded": "graph tracing / switch_layers (out of scope, SURVEY.md 8d)"},
             "e2e": {"value": round(ms_e2e / world, 4), "unit": UNIT, "h2d_bytes_per_step": case.h2d_bytes(),
                     "d2h_bytes_per_step": case.d2h_bytes()},
-            "gpu_launches": int(launches), "stages_ms": {k: round(v, 3) for k, v in stages.items()},
+            "gpu_launches": int(launches) // max(1, args.steps), "stages_ms": {k: round(v, 3) for k, v in stages.items()},
             "roofline": roof, "kernels": kernels, "eval": ev, "cpu_baseline": cpu, "clocks": clocks.summary()}
     print(json.dumps(line), flush=True)
     if world > 1:

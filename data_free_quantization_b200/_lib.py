@@ -46,8 +46,18 @@ class DfqCorrDesc(ctypes.Structure):
                 ("first_block", i64), ("range_slot", i64)]
 
 
+class DfqMergeDesc(ctypes.Structure):
+    _fields_ = [("W", c_void), ("b", c_void), ("gamma", c_void), ("beta", c_void), ("mean", c_void), ("var", c_void),
+                ("fake_weight", c_void), ("fake_bias", c_void), ("O", i64), ("K", i64), ("eps", f32),
+                ("first_row", i32)]
+
+
+class DfqClipDesc(ctypes.Structure):
+    _fields_ = [("w", c_void), ("n", i64), ("first_block", i64)]
+
+
 Q_SYMMETRIC, Q_RANGE_F32, Q_PER_CHANNEL, Q_CLAMP_OUT = 1, 2, 4, 8
-ABI_VERSION = 2
+ABI_VERSION = 3
 
 # every symbol include/dfq_b200.h declares: (restype, argtypes)
 P = ctypes.POINTER
@@ -70,6 +80,10 @@ PROTOTYPES = {
     "dfq_absorb_clip": (ctypes.c_int, [c_void, ctypes.c_int, ctypes.c_int, ctypes.c_int, f32, ctypes.c_int, f32, f32,
                                        c_void]),
     "dfq_clip_f32": (ctypes.c_int, [c_void, i64, f32, f32, c_void]),
+    "dfq_clip_plan_host": (ctypes.c_int, [P(DfqClipDesc), ctypes.c_int, P(i64)]),
+    "dfq_clip_multi_f32": (ctypes.c_int, [c_void, ctypes.c_int, i64, f32, f32, c_void]),
+    "dfq_merge_plan_host": (ctypes.c_int, [P(DfqMergeDesc), ctypes.c_int, P(ctypes.c_int)]),
+    "dfq_merge_bn_multi": (ctypes.c_int, [c_void, ctypes.c_int, ctypes.c_int, ctypes.c_int, c_void]),
     "dfq_corr_plan_host": (ctypes.c_int, [P(DfqCorrDesc), ctypes.c_int, P(i64), P(i64)]),
     "dfq_bias_correct": (ctypes.c_int, [c_void, ctypes.c_int, i64, i64, c_void, ctypes.c_int, c_void]),
     "dfq_merge_bn": (ctypes.c_int, [c_void, c_void, i64, i64, c_void, c_void, c_void, c_void, f32, c_void, c_void,

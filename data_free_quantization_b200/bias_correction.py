@@ -92,7 +92,7 @@ def eps_dot(layers, vectors, bits_weight=8, signed=False, alphas=None, biases=No
     tu, tb = L.i64(), L.i64()
     L.check(L.lib().dfq_corr_plan_host(descs, n, ctypes.byref(tu), ctypes.byref(tb)), "dfq_corr_plan_host")
     table = L.table_to_device(descs, dev)
-    ranges = torch.empty(n, 2, dtype=torch.float32, device=dev)
+    ranges = torch.empty(n, 4, dtype=torch.float32, device=dev)
     L.check(L.lib().dfq_bias_correct(table.data_ptr(), n, tu.value, tb.value, ranges.data_ptr(), 0, L.stream()),
             "dfq_bias_correct")
     return (outs, folds) if fold_mods is not None else outs
@@ -122,6 +122,12 @@ def bias_correction(graph, bottoms, targ_type, bits_weight=8, bn_type=torch.nn.B
     bias_prev = None
     before, after = {}, {}
     keys = list(graph.keys())
+    if not any(i in bottoms for i in range(len(keys))):
+        # the reference logs one warning per layer here (:186); one summary line keeps the hot path quiet
+        logger.warning(f"Layer indices 0..{len(keys) - 1} not found in bottoms (graph keyed by id(module)): "
+                       "bias correction as wired in the reference is a no-op")
+        logger.info("Bias correction completed.")
+        return before, after
     with torch.no_grad():
         for idx_layer, layer in enumerate(graph.values()):
             layer_name = f"layer_{idx_layer}"
@@ -157,14 +163,27 @@ def bias_correction(graph, bottoms, targ_type, bits_weight=8, bn_type=torch.nn.B
                 for kind, expect in (expected_input(b) for b in branches.values()):
                     if kind == 'cat':
                         raise RuntimeError("Tensors must have same number of dimensions: got 2 and 1")  # :74
-                    # bias += mean_i(eps[o,i] + E[x][i])   (:76-77, :98-104)
-                    (rowmean,), (fold,) = eps_dot([node], [None], bits_weight, signed, fold_mods=[C])
-                    node.bias.data.add_(rowmean + float(expect.mean()))
-                    # bias_prev = -(eps + E[x]) folded onto the next BN's channels (:206-213, :251)
-                    if C:
-                        tiled = expect.repeat(O) if expect.numel() == I2 else expect.expand(O, I2).reshape(-1)
-                        efold = tiled.view(-1, C).mean(dim=0) if O * I2 != C else tiled
-                        fold_total = -(fold.cpu() / float(O * I2 // C) + efold)
+                    E = expect.numel()
+                    if E == I2:
+                        # bias += mean_i(eps[o,i] + E[x][i])   (:76-77, :98-104); eps never leaves the kernel
+                        (rowmean,), (fold,) = eps_dot([node], [None], bits_weight, signed, fold_mods=[C])
+                        node.bias.data.add_(rowmean + float(expect.mean()))
+                        # bias_prev = -(eps + E[x]) folded onto the next BN's channels (:206-213, :251)
+                        if C:
+                            tiled = expect.repeat(O)
+                            efold = tiled.view(-1, C).mean(dim=0) if O * I2 != C else tiled
+                            fold_total = -(fold.cpu() / float(O * I2 // C) + efold)
+                    elif I2 == 1:
+                        # depthwise: eps [O,1] + E[x] [E] broadcasts to [O,E] in the reference (:77)
+                        (eps_o,) = eps_dot([node], [None], bits_weight, signed)
+                        M = eps_o.cpu()[:, None] + expect[None, :]
+                        node.bias.data.add_(M.mean(dim=1).to(node.bias.device))
+                        if C:
+                            flat = M.reshape(-1)
+                            fold_total = -(flat.view(-1, C).mean(dim=0) if flat.numel() != C else flat)
+                    else:
+                        raise RuntimeError(f"The size of tensor a ({I2}) must match the size of tensor b ({E}) "
+                                           "at non-singleton dimension 1")
                 bias_prev = fold_total
                 if hasattr(layer, 'bias') and layer.bias is not None:
                     after[layer_name] = layer.bias.data.clone()

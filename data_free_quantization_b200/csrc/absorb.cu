@@ -95,9 +95,103 @@ merge_bn_kernel(float *W, float *b, int64_t O, int64_t K, const float *gamma, co
     }
 }
 
+// all (conv, BN) pairs of a model: a warp owns one output channel of one pair
+__global__ void __launch_bounds__(kThreads)
+merge_bn_multi_kernel(const DfqMergeDesc *__restrict__ descs, int n_desc, int total_rows, int reset_bn) {
+    int row = blockIdx.x * kWarps + (threadIdx.x >> 5);
+    if (row >= total_rows) return;
+    int lo = 0, hi = n_desc - 1;
+    while (lo < hi) {
+        int mid = (lo + hi + 1) >> 1;
+        if (descs[mid].first_row <= row) lo = mid; else hi = mid - 1;
+    }
+    const DfqMergeDesc &d = descs[lo];
+    const int64_t o = row - d.first_row;
+    const int lane = threadIdx.x & 31;
+    const float g = d.gamma[o], be = d.beta[o], mu = d.mean[o], va = d.var[o];
+    float sd = __fsqrt_rn(__fadd_rn(va, d.eps));
+    float f = __fdiv_rn(g, sd);
+    float *rowp = d.W + o * d.K;
+    for (int64_t k = lane; k < d.K; k += 32) rowp[k] = __fmul_rn(rowp[k], f);        // :260
+    __syncwarp();
+    if (lane == 0) {
+        float sh = __fsub_rn(be, __fdiv_rn(__fmul_rn(g, mu), sd));
+        d.b[o] = __fadd_rn(__fmul_rn(d.b[o], f), sh);                               // :269-270
+        if (d.fake_weight) d.fake_weight[o] = fabsf(g);                              // :273
+        if (d.fake_bias) d.fake_bias[o] = be;                                        // :274
+        if (reset_bn) { d.gamma[o] = 1.0f; d.var[o] = 1.0f; d.beta[o] = 0.0f; d.mean[o] = 0.0f; }   // :277-280
+    }
+}
+
+__global__ void __launch_bounds__(kThreads)
+clip_multi_kernel(const DfqClipDesc *__restrict__ descs, int n_desc, float lo_c, float hi_c) {
+    int lo = 0, hi = n_desc - 1;
+    while (lo < hi) {
+        int mid = (lo + hi + 1) >> 1;
+        if (descs[mid].first_block <= (int64_t)blockIdx.x) lo = mid; else hi = mid - 1;
+    }
+    const DfqClipDesc &d = descs[lo];
+    int64_t begin = ((int64_t)blockIdx.x - d.first_block) * kChunk, end = min(begin + (int64_t)kChunk, d.n);
+    float *p = d.w + begin;
+    int64_t m = end - begin;
+    if ((((uintptr_t)p) & 15) == 0) {
+        float4 *p4 = reinterpret_cast<float4 *>(p);
+        int64_t m4 = m >> 2;
+        for (int64_t k = threadIdx.x; k < m4; k += kThreads) {
+            float4 v = p4[k];
+            v.x = fminf(fmaxf(v.x, lo_c), hi_c); v.y = fminf(fmaxf(v.y, lo_c), hi_c);
+            v.z = fminf(fmaxf(v.z, lo_c), hi_c); v.w = fminf(fmaxf(v.w, lo_c), hi_c);
+            p4[k] = v;
+        }
+        for (int64_t k = (m4 << 2) + threadIdx.x; k < m; k += kThreads) p[k] = fminf(fmaxf(p[k], lo_c), hi_c);
+    } else {
+        for (int64_t k = threadIdx.x; k < m; k += kThreads) p[k] = fminf(fmaxf(p[k], lo_c), hi_c);
+    }
+}
+
 }  // namespace dfq
 
 using namespace dfq;
+
+extern "C" int dfq_merge_plan_host(DfqMergeDesc *d, int n, int *total_rows) {
+    int64_t r = 0;
+    for (int i = 0; i < n; ++i) {
+        if (d[i].O <= 0 || d[i].K <= 0) return (int)cudaErrorInvalidValue;
+        d[i].first_row = (int32_t)r;
+        r += d[i].O;
+    }
+    if (r > 0x7fffffffll) return (int)cudaErrorInvalidValue;
+    *total_rows = (int)r;
+    return 0;
+}
+
+extern "C" int dfq_merge_bn_multi(const DfqMergeDesc *descs_dev, int n_desc, int total_rows, int reset_bn,
+                                  void *stream) {
+    if (n_desc <= 0 || total_rows <= 0) return 0;
+    merge_bn_multi_kernel<<<(total_rows + kWarps - 1) / kWarps, kThreads, 0, (cudaStream_t)stream>>>(
+        descs_dev, n_desc, total_rows, reset_bn);
+    g_launches += 1;
+    return (int)cudaGetLastError();
+}
+
+extern "C" int dfq_clip_plan_host(DfqClipDesc *d, int n, int64_t *total_blocks) {
+    int64_t b = 0;
+    for (int i = 0; i < n; ++i) {
+        if (d[i].n < 0) return (int)cudaErrorInvalidValue;
+        d[i].first_block = b;
+        b += (d[i].n + kChunk - 1) / kChunk;
+    }
+    *total_blocks = b;
+    return b > 0x7fffffffll ? (int)cudaErrorInvalidValue : 0;
+}
+
+extern "C" int dfq_clip_multi_f32(const DfqClipDesc *descs_dev, int n_desc, int64_t total_blocks, float lo, float hi,
+                                  void *stream) {
+    if (n_desc <= 0 || total_blocks <= 0) return 0;
+    clip_multi_kernel<<<(unsigned)total_blocks, kThreads, 0, (cudaStream_t)stream>>>(descs_dev, n_desc, lo, hi);
+    g_launches += 1;
+    return (int)cudaGetLastError();
+}
 
 extern "C" int dfq_absorb_plan_host(DfqAbsorbPair *p, int n, int *total_rows) {
     int r = 0;

@@ -15,6 +15,12 @@ constexpr int kWarps = kThreads / 32;
 constexpr int kChunk = 4096;            // fp32 elements per block of the streaming kernels
 
 extern long long g_launches;            // host-side launch counter (api.cu)
+int sm_count();                         // SMs of the current device, cached (api.cu)
+// grid of a grid-stride reduction pass: 8 resident 256-thread blocks per SM (148 x 8 on B200)
+inline unsigned reduce_grid(int64_t virtual_blocks) {
+    int64_t g = (int64_t)sm_count() * 8;
+    return (unsigned)(virtual_blocks < g ? virtual_blocks : g);
+}
 
 // Monotone float -> uint map (larger float => larger code); 0 is below every real value.
 __device__ __forceinline__ unsigned enc_ordered(float f) {
@@ -122,13 +128,11 @@ __host__ __device__ inline DfqQuantParams make_quant_params(double mn, double mx
     return p;
 }
 
-// Correctly rounded a / b for a constant divisor b > 0 with rb = RN(1/b).
-// Markstein's sequence: two FMA refinements make q faithful, the last one makes it the
-// IEEE-rounded quotient; operands outside the safe exponent window take __fdiv_rn.
+// Correctly rounded a / b for a constant divisor b > 0 with rb = RN(1/b) (Markstein): two FMA refinements make
+// q faithful, the third makes it the IEEE-rounded quotient.  Valid while a, q*b and the residuals stay clear of
+// overflow; underflowing residuals only occur for |a/b| << 0.5 where the rounded code is 0 either way.  The
+// caller guarantees both by clamping the numerator first (QuantConsts.t_lo / t_hi).
 __device__ __forceinline__ float div_const_rn(float a, float b, float rb) {
-    float aa = fabsf(a);
-    if (a == 0.0f) return a;
-    if (!(aa > 1e-30f && aa < 1e30f)) return __fdiv_rn(a, b);
     float q = __fmul_rn(a, rb);
     float r = __fmaf_rn(-q, b, a);
     q = __fmaf_rn(r, rb, q);
@@ -144,7 +148,8 @@ __device__ __forceinline__ float rint_small(float c) {
 
 struct QuantConsts {
     float neg_min, scale, rscale, qmin, qmax, add_back, clip_lo, clip_hi;
-    int small_grid;                     // qmax < 2^22: rint_small is exact
+    float t_lo, t_hi;                   // numerator clamp: quotients beyond [qmin-2, qmax+2] clamp to the ends anyway
+    int fast;                           // 0: exotic scale or > 22-bit grid -> __fdiv_rn / rintf path
 };
 
 __device__ __forceinline__ QuantConsts make_consts(const DfqQuantParams &p, float clip_lo, float clip_hi) {
@@ -152,18 +157,44 @@ __device__ __forceinline__ QuantConsts make_consts(const DfqQuantParams &p, floa
     c.neg_min = p.neg_min; c.scale = p.scale; c.rscale = __frcp_rn(p.scale);
     c.qmin = p.qmin; c.qmax = p.qmax; c.add_back = p.add_back;
     c.clip_lo = clip_lo; c.clip_hi = clip_hi;
-    c.small_grid = (p.qmax < 4194304.0f && p.qmin > -4194304.0f);
+    c.t_lo = __fmul_rn(p.qmin - 2.0f, p.scale);
+    c.t_hi = __fmul_rn(p.qmax + 2.0f, p.scale);
+    c.fast = (p.qmax < 4194304.0f && p.qmin > -4194304.0f && p.scale >= 1e-8f && p.scale < 1e25f);
     return c;
+}
+
+// One slot of the device-side range table written by the range pass: the five constants follow from it in fp32.
+struct RangeSlot { float mn, mx, scale, pad; };
+
+__device__ __forceinline__ QuantConsts consts_from_slot(const RangeSlot &r, int bits, int flags, float clip_lo,
+                                                        float clip_hi) {
+    DfqQuantParams p;
+    const bool sym = flags & DFQ_Q_SYMMETRIC;
+    p.scale = r.scale;
+    p.qmin = sym ? -(float)(1 << (bits - 1)) : 0.0f;
+    p.qmax = sym ? (float)((1 << (bits - 1)) - 1) : (float)((1ll << bits) - 1);
+    p.neg_min = sym ? -0.0f : -r.mn;
+    p.add_back = sym ? 0.0f : r.mn;
+    return make_consts(p, clip_lo, clip_hi);
 }
 
 // utils/quantize.py:72-76, one element.  Returns the dequantised value; q receives the grid value.
 __device__ __forceinline__ float fake_quant_elem(float x, const QuantConsts &c, float &q) {
     float t = __fadd_rn(x, c.neg_min);
-    t = div_const_rn(t, c.scale, c.rscale);
-    float cl = fminf(fmaxf(t, c.qmin), c.qmax);
-    cl = (t != t) ? t : cl;                             // torch.clamp propagates NaN
-    q = c.small_grid ? rint_small(cl) : rintf(cl);
-    return __fadd_rn(__fmul_rn(q, c.scale), c.add_back);
+    float cl;
+    if (c.fast) {                                           // block-uniform
+        float tc = fminf(fmaxf(t, c.t_lo), c.t_hi);
+        float d = div_const_rn(tc, c.scale, c.rscale);
+        cl = fminf(fmaxf(d, c.qmin), c.qmax);
+        q = rint_small(cl);
+    } else {
+        float d = __fdiv_rn(t, c.scale);
+        cl = fminf(fmaxf(d, c.qmin), c.qmax);
+        q = rintf(cl);
+    }
+    float y = __fadd_rn(__fmul_rn(q, c.scale), c.add_back);
+    if (x != x) { q = x; y = x; }                           // torch.clamp propagates NaN
+    return y;
 }
 
 }  // namespace dfq

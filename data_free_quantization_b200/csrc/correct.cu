@@ -19,28 +19,54 @@ __device__ __forceinline__ int find_corr(const DfqCorrDesc *d, int n, int64_t b,
 }
 
 __global__ void __launch_bounds__(kThreads)
-corr_minmax_kernel(const DfqCorrDesc *__restrict__ descs, int n_desc, unsigned *__restrict__ ranges) {
+corr_minmax_kernel(const DfqCorrDesc *__restrict__ descs, int n_desc, int64_t total_blocks,
+                   unsigned *__restrict__ ranges) {
     __shared__ float sm[2 * kWarps];
-    int t = find_corr(descs, n_desc, blockIdx.x, true);
-    const DfqCorrDesc &d = descs[t];
-    int64_t n = (int64_t)d.O * d.I2 * d.KK;
-    int64_t begin = (blockIdx.x - d.first_block) * (int64_t)kChunk;
-    int64_t end = min(begin + (int64_t)kChunk, n);
     float lo = INFINITY, hi = -INFINITY;
-    chunk_minmax(d.W, begin, end, lo, hi);
-    block_minmax(lo, hi, sm);
-    if (threadIdx.x == 0) {
-        atomicMax(ranges + 2 * d.range_slot, enc_ordered(-lo));
-        atomicMax(ranges + 2 * d.range_slot + 1, enc_ordered(hi));
+    int cur = -1;
+    // grid-stride over 16 KB chunks; one block reduction + atomic pair per layer change
+    for (int64_t vb = blockIdx.x; vb < total_blocks; vb += gridDim.x) {
+        int t = find_corr(descs, n_desc, vb, true);
+        const DfqCorrDesc &d = descs[t];
+        if (t != cur) {
+            if (cur >= 0) {
+                block_minmax(lo, hi, sm);
+                if (threadIdx.x == 0) {
+                    atomicMax(ranges + 4 * descs[cur].range_slot, enc_ordered(-lo));
+                    atomicMax(ranges + 4 * descs[cur].range_slot + 1, enc_ordered(hi));
+                }
+            }
+            lo = INFINITY; hi = -INFINITY; cur = t;
+        }
+        int64_t n = (int64_t)d.O * d.I2 * d.KK;
+        int64_t begin = (vb - d.first_block) * (int64_t)kChunk;
+        int64_t end = min(begin + (int64_t)kChunk, n);
+        chunk_minmax(d.W, begin, end, lo, hi);
+    }
+    if (cur >= 0) {
+        block_minmax(lo, hi, sm);
+        if (threadIdx.x == 0) {
+            atomicMax(ranges + 4 * descs[cur].range_slot, enc_ordered(-lo));
+            atomicMax(ranges + 4 * descs[cur].range_slot + 1, enc_ordered(hi));
+        }
     }
 }
 
-__global__ void corr_decode_kernel(unsigned *ranges, int64_t slots) {
+// {enc(-min), enc(max)} (encoded != 0) or caller-given {min, max} (given != 0) -> RangeSlot {min, max, scale, 0}
+__global__ void corr_decode_kernel(const DfqCorrDesc *__restrict__ descs, unsigned *ranges, int64_t slots, int given) {
     int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     if (i >= slots) return;
-    float mn = -dec_ordered(ranges[2 * i]), mx = dec_ordered(ranges[2 * i + 1]);
-    reinterpret_cast<float *>(ranges)[2 * i] = mn;
-    reinterpret_cast<float *>(ranges)[2 * i + 1] = mx;
+    float mn, mx;
+    if (given) {
+        mn = reinterpret_cast<float *>(ranges)[4 * i];
+        mx = reinterpret_cast<float *>(ranges)[4 * i + 1];
+    } else {
+        mn = -dec_ordered(ranges[4 * i]);
+        mx = dec_ordered(ranges[4 * i + 1]);
+    }
+    DfqQuantParams p = make_quant_params((double)mn, (double)mx, descs[i].bits, descs[i].flags);   // :128
+    RangeSlot r = {mn, mx, p.scale, 0.0f};
+    reinterpret_cast<RangeSlot *>(ranges)[i] = r;
 }
 
 __global__ void corr_zero_kernel(const DfqCorrDesc *__restrict__ descs) {
@@ -55,25 +81,43 @@ __device__ __forceinline__ double row_partial(const float *__restrict__ row, con
                                               int64_t b, int64_t e, int KK, float inv_I,
                                               const QuantConsts &c, int tid, int nthr,
                                               float *fold, int fold_mod, int64_t row_chan0) {
-    double acc = 0.0;
+    // a thread owns <= 32 elements of a chunk: fp32 partial (error ~1e-7 of the partial), widened once
+    float acc = 0.0f;
     const float *p = row + b;
     int64_t n = e - b;
     bool vec = ((((uintptr_t)p) & 15) == 0);
     int64_t n4 = vec ? (n >> 2) : 0;
     const float4 *p4 = reinterpret_cast<const float4 *>(p);
-    for (int64_t k = tid; k < n4; k += nthr) {
-        float4 w = __ldg(p4 + k);
-        float xs[4] = {w.x, w.y, w.z, w.w};
-        int64_t idx = b + 4 * k;
+    // pointwise / linear weights (KK == 1): v is read with the same 128-bit pattern as W
+    const bool vfast = v && KK == 1 && (((uintptr_t)(v + b)) & 15) == 0;
+    const float4 *v4 = reinterpret_cast<const float4 *>(v + b);
+    for (int64_t base = 0; base < n4; base += 4 * (int64_t)nthr) {
+        float4 w[4], vv[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {                      // 4 independent 128-bit loads in flight per thread
+            int64_t k = base + tid + (int64_t)u * nthr;
+            if (k < n4) {
+                w[u] = __ldg(p4 + k);
+                if (vfast) vv[u] = __ldg(v4 + k);
+            }
+        }
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
-            float q;
-            float dq = fake_quant_elem(xs[u], c, q);
-            float eps = __fsub_rn(dq, xs[u]);                       // :130
-            int64_t ch = (KK == 1) ? (idx + u) : (idx + u) / KK;
-            float vi = v ? v[ch] : inv_I;
-            acc += (double)eps * (double)vi;
-            if (fold) atomicAdd(fold + (row_chan0 + ch) % fold_mod, eps);
+            int64_t k = base + tid + (int64_t)u * nthr;
+            if (k >= n4) continue;
+            float xs[4] = {w[u].x, w[u].y, w[u].z, w[u].w};
+            float vs[4] = {vv[u].x, vv[u].y, vv[u].z, vv[u].w};
+            int64_t idx = b + 4 * k;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                float q;
+                float dq = fake_quant_elem(xs[j], c, q);
+                float eps = __fsub_rn(dq, xs[j]);                   // bias_correction.py:130
+                int64_t ch = (KK == 1) ? (idx + j) : (idx + j) / KK;
+                float vi = vfast ? vs[j] : (v ? v[ch] : inv_I);
+                acc = __fmaf_rn(eps, vi, acc);
+                if (fold) atomicAdd(fold + (row_chan0 + ch) % fold_mod, eps);
+            }
         }
     }
     for (int64_t k = (n4 << 2) + tid; k < n; k += nthr) {
@@ -81,21 +125,19 @@ __device__ __forceinline__ double row_partial(const float *__restrict__ row, con
         float eps = __fsub_rn(fake_quant_elem(x, c, q), x);
         int64_t ch = (KK == 1) ? (b + k) : (b + k) / KK;
         float vi = v ? v[ch] : inv_I;
-        acc += (double)eps * (double)vi;
+        acc = __fmaf_rn(eps, vi, acc);
         if (fold) atomicAdd(fold + (row_chan0 + ch) % fold_mod, eps);
     }
-    return acc;
+    return (double)acc;
 }
 
 __global__ void __launch_bounds__(kThreads)
-corr_reduce_kernel(const DfqCorrDesc *__restrict__ descs, int n_desc, const float *__restrict__ ranges) {
+corr_reduce_kernel(const DfqCorrDesc *__restrict__ descs, int n_desc, const RangeSlot *__restrict__ ranges) {
     __shared__ double smd[kWarps];
     int t = find_corr(descs, n_desc, blockIdx.x, false);
     const DfqCorrDesc &d = descs[t];
     const int64_t row_len = (int64_t)d.I2 * d.KK;
-    const float *rg = ranges + 2 * d.range_slot;
-    DfqQuantParams p = make_quant_params((double)rg[0], (double)rg[1], d.bits, d.flags);   // :128
-    QuantConsts c = make_consts(p, 0.f, 0.f);
+    QuantConsts c = consts_from_slot(ranges[d.range_slot], d.bits, d.flags, 0.f, 0.f);
     const float inv_I = 1.0f / (float)d.I2;
     int64_t j = blockIdx.x - d.first_unit;
     if (row_len <= kCorrSmallRow) {                       // one warp per row
@@ -158,14 +200,16 @@ extern "C" int dfq_bias_correct(const DfqCorrDesc *descs_dev, int n_desc, int64_
     if (n_desc <= 0) return 0;
     cudaStream_t st = (cudaStream_t)stream;
     if (!range_given) {
-        cudaError_t e = cudaMemsetAsync(ranges_dev, 0, sizeof(float) * 2 * n_desc, st);
+        cudaError_t e = cudaMemsetAsync(ranges_dev, 0, sizeof(float) * 4 * n_desc, st);
         if (e != cudaSuccess) return (int)e;
-        corr_minmax_kernel<<<(unsigned)total_blocks, kThreads, 0, st>>>(descs_dev, n_desc, (unsigned *)ranges_dev);
-        corr_decode_kernel<<<(n_desc + 255) / 256, 256, 0, st>>>((unsigned *)ranges_dev, n_desc);
-        g_launches += 2;
+        corr_minmax_kernel<<<reduce_grid(total_blocks), kThreads, 0, st>>>(descs_dev, n_desc, total_blocks,
+                                                                           (unsigned *)ranges_dev);
+        g_launches += 1;
     }
+    corr_decode_kernel<<<(n_desc + 255) / 256, 256, 0, st>>>(descs_dev, (unsigned *)ranges_dev, n_desc, range_given);
+    g_launches += 1;
     corr_zero_kernel<<<n_desc, 256, 0, st>>>(descs_dev);
-    corr_reduce_kernel<<<(unsigned)total_units, kThreads, 0, st>>>(descs_dev, n_desc, ranges_dev);
+    corr_reduce_kernel<<<(unsigned)total_units, kThreads, 0, st>>>(descs_dev, n_desc, (const RangeSlot *)ranges_dev);
     corr_finalize_kernel<<<n_desc, 256, 0, st>>>(descs_dev);
     g_launches += 3;
     return (int)cudaGetLastError();

@@ -57,47 +57,78 @@ __device__ __forceinline__ BlockWork decode_work(const DfqQuantDesc *descs, int 
     return w;
 }
 
-__device__ __forceinline__ void minmax_block(const DfqQuantDesc &d, const BlockWork &w,
-                                             unsigned *__restrict__ ranges, float *sm) {
-    if (w.begin >= 0) {
-        float lo = INFINITY, hi = -INFINITY;
-        chunk_minmax(d.x, w.begin, w.end, lo, hi);
-        block_minmax(lo, hi, sm);
-        if (threadIdx.x == 0) {
-            unsigned *slot = ranges + 2 * (d.range_slot + w.row);
-            atomicMax(slot, enc_ordered(-lo));
-            atomicMax(slot + 1, enc_ordered(hi));
-        }
-    } else {                                   // one warp per short row
-        int64_t r = w.row + (threadIdx.x >> 5);
-        if (r >= d.rows) return;
-        const float *p = d.x + r * w.cols;
-        float lo = INFINITY, hi = -INFINITY;
-        for (int64_t k = threadIdx.x & 31; k < w.cols; k += 32) {
-            float t = p[k]; lo = fminf(lo, t); hi = fmaxf(hi, t);
-        }
-        lo = warp_min(lo); hi = warp_max(hi);
-        if ((threadIdx.x & 31) == 0) {
-            unsigned *slot = ranges + 2 * (d.range_slot + r);
-            slot[0] = enc_ordered(-lo);
-            slot[1] = enc_ordered(hi);
-        }
+// Grid-stride range pass.  A block walks virtual chunks vb = blockIdx.x, +gridDim.x, ... and keeps a running
+// (min, max) in registers while consecutive chunks belong to the same range slot; the block reduction and the
+// two atomics happen once per slot change (once per block for a single big tensor) instead of once per 16 KB.
+template <int kStride>
+__device__ __forceinline__ void flush_slot(unsigned *__restrict__ ranges, int64_t slot, float lo, float hi, float *sm) {
+    block_minmax(lo, hi, sm);
+    if (threadIdx.x == 0) {
+        atomicMax(ranges + kStride * slot, enc_ordered(-lo));
+        atomicMax(ranges + kStride * slot + 1, enc_ordered(hi));
+    }
+}
+
+template <int kStride>
+__device__ __forceinline__ void warp_rows_minmax(const DfqQuantDesc &d, const BlockWork &w, unsigned *__restrict__ ranges) {
+    int64_t r = w.row + (threadIdx.x >> 5);                 // one warp per short row, plain stores
+    if (r >= d.rows) return;
+    const float *p = d.x + r * w.cols;
+    float lo = INFINITY, hi = -INFINITY;
+    for (int64_t k = threadIdx.x & 31; k < w.cols; k += 32) {
+        float t = p[k]; lo = fminf(lo, t); hi = fmaxf(hi, t);
+    }
+    lo = warp_min(lo); hi = warp_max(hi);
+    if ((threadIdx.x & 31) == 0) {
+        unsigned *slot = ranges + kStride * (d.range_slot + r);
+        slot[0] = enc_ordered(-lo);
+        slot[1] = enc_ordered(hi);
     }
 }
 
 __global__ void __launch_bounds__(kThreads)
-minmax_multi_kernel(const DfqQuantDesc *__restrict__ descs, int n_desc, unsigned *__restrict__ ranges) {
+minmax_multi_kernel(const DfqQuantDesc *__restrict__ descs, int n_desc, int64_t total_blocks,
+                    unsigned *__restrict__ ranges) {
     __shared__ float sm[2 * kWarps];
-    BlockWork w = decode_work(descs, n_desc, blockIdx.x);
-    minmax_block(descs[w.desc], w, ranges, sm);
+    float lo = INFINITY, hi = -INFINITY;
+    int64_t cur = -1;
+    for (int64_t vb = blockIdx.x; vb < total_blocks; vb += gridDim.x) {
+        BlockWork w = decode_work(descs, n_desc, vb);
+        const DfqQuantDesc &d = descs[w.desc];
+        if (w.begin >= 0) {
+            int64_t slot = d.range_slot + w.row;
+            if (slot != cur) {
+                if (cur >= 0) flush_slot<4>(ranges, cur, lo, hi, sm);
+                lo = INFINITY; hi = -INFINITY; cur = slot;
+            }
+            chunk_minmax(d.x, w.begin, w.end, lo, hi);
+        } else {
+            warp_rows_minmax<4>(d, w, ranges);
+        }
+    }
+    if (cur >= 0) flush_slot<4>(ranges, cur, lo, hi, sm);
 }
 
 // one tensor, descriptor passed by value (dfq_minmax_f32 / dfq_minmax_rows_f32)
 __global__ void __launch_bounds__(kThreads)
-minmax_single_kernel(DfqQuantDesc d, unsigned *__restrict__ ranges) {
+minmax_single_kernel(DfqQuantDesc d, int64_t total_blocks, unsigned *__restrict__ ranges) {
     __shared__ float sm[2 * kWarps];
-    BlockWork w = decode_work1(d, blockIdx.x);
-    minmax_block(d, w, ranges, sm);
+    float lo = INFINITY, hi = -INFINITY;
+    int64_t cur = -1;
+    for (int64_t vb = blockIdx.x; vb < total_blocks; vb += gridDim.x) {
+        BlockWork w = decode_work1(d, vb);
+        if (w.begin >= 0) {
+            int64_t slot = d.range_slot + w.row;
+            if (slot != cur) {
+                if (cur >= 0) flush_slot<2>(ranges, cur, lo, hi, sm);
+                lo = INFINITY; hi = -INFINITY; cur = slot;
+            }
+            chunk_minmax(d.x, w.begin, w.end, lo, hi);
+        } else {
+            warp_rows_minmax<2>(d, w, ranges);
+        }
+    }
+    if (cur >= 0) flush_slot<2>(ranges, cur, lo, hi, sm);
 }
 
 // encoded (max(-x), max(x)) -> plain (min, max) floats, in place
@@ -108,6 +139,23 @@ __global__ void decode_ranges_kernel(unsigned *ranges, int64_t slots) {
     float mx = dec_ordered(ranges[2 * i + 1]);
     reinterpret_cast<float *>(ranges)[2 * i] = mn;
     reinterpret_cast<float *>(ranges)[2 * i + 1] = mx;
+}
+
+// range table of the multi-tensor path: 4 floats per slot.  In: encoded (max(-x), max(x)) in [0], [1];
+// out: RangeSlot {min, max, scale, 0} with the scale formed exactly as the host does (utils/quantize.py:51-68).
+__global__ void decode_slots_kernel(const DfqQuantDesc *__restrict__ descs, int n_desc, unsigned *ranges, int64_t slots) {
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i >= slots) return;
+    int lo = 0, hi = n_desc - 1;
+    while (lo < hi) {
+        int mid = (lo + hi + 1) >> 1;
+        if (descs[mid].range_slot <= i) lo = mid; else hi = mid - 1;
+    }
+    float mn = -dec_ordered(ranges[4 * i]);
+    float mx = dec_ordered(ranges[4 * i + 1]);
+    DfqQuantParams p = make_quant_params((double)mn, (double)mx, descs[lo].bits, descs[lo].flags);
+    RangeSlot r = {mn, mx, p.scale, 0.0f};
+    reinterpret_cast<RangeSlot *>(ranges)[i] = r;
 }
 
 template <typename CodeT>
@@ -167,22 +215,18 @@ __device__ __forceinline__ void apply_range(const float *x, float *y, CodeT *cod
 }
 
 __global__ void __launch_bounds__(kThreads)
-fake_quant_multi_kernel(const DfqQuantDesc *__restrict__ descs, int n_desc, const float *__restrict__ ranges) {
+fake_quant_multi_kernel(const DfqQuantDesc *__restrict__ descs, int n_desc, const RangeSlot *__restrict__ ranges) {
     BlockWork w = decode_work(descs, n_desc, blockIdx.x);
     const DfqQuantDesc &d = descs[w.desc];
     bool clamp_out = d.flags & DFQ_Q_CLAMP_OUT;
     if (w.begin >= 0) {
-        const float *rg = ranges + 2 * (d.range_slot + w.row);
-        DfqQuantParams p = make_quant_params((double)rg[0], (double)rg[1], d.bits, d.flags);
-        QuantConsts c = make_consts(p, d.clip_lo, d.clip_hi);
+        QuantConsts c = consts_from_slot(ranges[d.range_slot + w.row], d.bits, d.flags, d.clip_lo, d.clip_hi);
         if (d.bits <= 8) apply_range<uint8_t>(d.x, d.y, (uint8_t *)d.codes, w.begin, w.end, c, clamp_out, threadIdx.x, kThreads);
         else apply_range<uint16_t>(d.x, d.y, (uint16_t *)d.codes, w.begin, w.end, c, clamp_out, threadIdx.x, kThreads);
     } else {
         int64_t r = w.row + (threadIdx.x >> 5);
         if (r >= d.rows) return;
-        const float *rg = ranges + 2 * (d.range_slot + r);
-        DfqQuantParams p = make_quant_params((double)rg[0], (double)rg[1], d.bits, d.flags);
-        QuantConsts c = make_consts(p, d.clip_lo, d.clip_hi);
+        QuantConsts c = consts_from_slot(ranges[d.range_slot + r], d.bits, d.flags, d.clip_lo, d.clip_hi);
         int64_t b = r * w.cols, e = b + w.cols;
         if (d.bits <= 8) apply_range<uint8_t>(d.x, d.y, (uint8_t *)d.codes, b, e, c, clamp_out, threadIdx.x & 31, 32);
         else apply_range<uint16_t>(d.x, d.y, (uint16_t *)d.codes, b, e, c, clamp_out, threadIdx.x & 31, 32);
@@ -205,6 +249,7 @@ fake_quant_apply_kernel(const float *__restrict__ x, float *__restrict__ y, Code
 using namespace dfq;
 
 static inline int64_t desc_blocks(const DfqQuantDesc &d) {
+    // virtual chunks of the range / apply passes
     if (!(d.flags & DFQ_Q_PER_CHANNEL)) return (d.n + kChunk - 1) / kChunk;
     int64_t cols = d.n / d.rows;
     if (cols > kSmallRow) return d.rows * ((cols + kChunk - 1) / kChunk);
@@ -235,11 +280,14 @@ extern "C" int dfq_fake_quant_multi_f32(const DfqQuantDesc *descs_dev, int n_des
                                         int64_t total_slots, float *ranges_dev, void *stream) {
     cudaStream_t st = (cudaStream_t)stream;
     if (n_desc <= 0 || total_blocks <= 0) return 0;
-    cudaError_t e = cudaMemsetAsync(ranges_dev, 0, sizeof(float) * 2 * total_slots, st);
+    cudaError_t e = cudaMemsetAsync(ranges_dev, 0, sizeof(float) * 4 * total_slots, st);
     if (e != cudaSuccess) return (int)e;
-    minmax_multi_kernel<<<(unsigned)total_blocks, kThreads, 0, st>>>(descs_dev, n_desc, (unsigned *)ranges_dev);
-    decode_ranges_kernel<<<(unsigned)((total_slots + 255) / 256), 256, 0, st>>>((unsigned *)ranges_dev, total_slots);
-    fake_quant_multi_kernel<<<(unsigned)total_blocks, kThreads, 0, st>>>(descs_dev, n_desc, ranges_dev);
+    minmax_multi_kernel<<<reduce_grid(total_blocks), kThreads, 0, st>>>(descs_dev, n_desc, total_blocks,
+                                                                        (unsigned *)ranges_dev);
+    decode_slots_kernel<<<(unsigned)((total_slots + 255) / 256), 256, 0, st>>>(descs_dev, n_desc, (unsigned *)ranges_dev,
+                                                                               total_slots);
+    fake_quant_multi_kernel<<<(unsigned)total_blocks, kThreads, 0, st>>>(descs_dev, n_desc,
+                                                                         (const RangeSlot *)ranges_dev);
     g_launches += 3;
     return (int)cudaGetLastError();
 }
@@ -265,7 +313,7 @@ static int minmax_single(const float *x, int64_t n, int64_t rows, float *out, vo
     cudaStream_t st = (cudaStream_t)stream;
     cudaError_t e = cudaMemsetAsync(out, 0, sizeof(float) * 2 * rows, st);
     if (e != cudaSuccess) return (int)e;
-    minmax_single_kernel<<<(unsigned)blocks, kThreads, 0, st>>>(d, (unsigned *)out);
+    minmax_single_kernel<<<reduce_grid(blocks), kThreads, 0, st>>>(d, blocks, (unsigned *)out);
     decode_ranges_kernel<<<(unsigned)((rows + 255) / 256), 256, 0, st>>>((unsigned *)out, rows);
     g_launches += 2;
     return (int)cudaGetLastError();

@@ -18,34 +18,46 @@ IDENTITY_BN_EPS = 1e-12
 
 def merge_batchnorm(model, graph, bottoms, targ_type=[QConv2d]):
     """utils/layer_transform.py:240-285: fold BatchNorm into the preceding target layer (in place, on the GPU),
-    stash |gamma| / beta as the BN's fake_weight / fake_bias buffers, turn the BN into an identity."""
+    stash |gamma| / beta as the BN's fake_weight / fake_bias buffers, turn the BN into an identity.
+    Every (conv, BN) pair of the model goes through ONE launch (dfq_merge_bn_multi)."""
+    import ctypes
+    pairs = []
+    for layer_idx in graph:
+        if bottoms[layer_idx] is None:
+            continue
+        for bot_idx in bottoms[layer_idx]:
+            if type(graph[layer_idx]) == nn.BatchNorm2d and type(graph[bot_idx]) in targ_type:
+                pairs.append((graph[bot_idx], graph[layer_idx]))
+                break
+    if not pairs:
+        return model
     with torch.no_grad():
-        for layer_idx in graph:
-            if bottoms[layer_idx] is None:
-                continue
-            for bot_idx in bottoms[layer_idx]:
-                bn, conv = graph[layer_idx], graph[bot_idx]
-                if type(bn) == nn.BatchNorm2d and type(conv) in targ_type:
-                    W = conv.weight.data
-                    O = W.size(0)
-                    if conv.bias is None:           # :262-263
-                        conv.bias = nn.Parameter(data=torch.zeros(O, dtype=torch.float32, device=W.device),
-                                                 requires_grad=False)
-                    fake_w = torch.empty(O, dtype=torch.float32, device=W.device)
-                    fake_b = torch.empty(O, dtype=torch.float32, device=W.device)
-                    L.check(L.lib().dfq_merge_bn(
-                        L.dev_f32(W, "weight"), L.dev_f32(conv.bias.data, "bias"), O, W.numel() // O,
-                        L.dev_f32(bn.weight.data, "bn.weight"), L.dev_f32(bn.bias.data, "bn.bias"),
-                        L.dev_f32(bn.running_mean, "bn.running_mean"), L.dev_f32(bn.running_var, "bn.running_var"),
-                        float(bn.eps), fake_w.data_ptr(), fake_b.data_ptr(), L.stream()), "dfq_merge_bn")
-                    bn.register_buffer('fake_weight', fake_w)    # :273-274
-                    bn.register_buffer('fake_bias', fake_b)
-                    bn.weight.fill_(1)                           # :277-281
-                    bn.running_var.fill_(1)
-                    bn.bias.fill_(0)
-                    bn.running_mean.fill_(0)
-                    bn.eps = IDENTITY_BN_EPS
-                    break
+        dev = pairs[0][0].weight.device
+        total = sum(conv.weight.size(0) for conv, _ in pairs)
+        stash = torch.empty(2, total, dtype=torch.float32, device=dev)     # all fake_weight | all fake_bias
+        descs = (L.DfqMergeDesc * len(pairs))()
+        off = 0
+        for d, (conv, bn) in zip(descs, pairs):
+            W = conv.weight.data
+            O = W.size(0)
+            if conv.bias is None:                   # :262-263
+                conv.bias = nn.Parameter(data=torch.zeros(O, dtype=torch.float32, device=dev), requires_grad=False)
+            fake_w, fake_b = stash[0, off:off + O], stash[1, off:off + O]
+            off += O
+            d.W, d.b = L.dev_f32(W, "weight"), L.dev_f32(conv.bias.data, "bias")
+            d.gamma, d.beta = L.dev_f32(bn.weight.data, "bn.weight"), L.dev_f32(bn.bias.data, "bn.bias")
+            d.mean, d.var = L.dev_f32(bn.running_mean, "bn.running_mean"), L.dev_f32(bn.running_var, "bn.running_var")
+            d.fake_weight, d.fake_bias = fake_w.data_ptr(), fake_b.data_ptr()
+            d.O, d.K, d.eps = O, W.numel() // O, float(bn.eps)
+            bn.register_buffer('fake_weight', fake_w)            # :273-274
+            bn.register_buffer('fake_bias', fake_b)
+            bn.eps = IDENTITY_BN_EPS                             # :281 (see IDENTITY_BN_EPS)
+        rows = ctypes.c_int()
+        L.check(L.lib().dfq_merge_plan_host(descs, len(pairs), ctypes.byref(rows)), "dfq_merge_plan_host")
+        table = L.table_to_device(descs, dev)
+        # reset_bn=1: gamma=1, var=1, beta=0, mean=0 (:277-280) written by the same kernel
+        L.check(L.lib().dfq_merge_bn_multi(table.data_ptr(), len(pairs), rows.value, 1, L.stream()),
+                "dfq_merge_bn_multi")
     return model
 
 

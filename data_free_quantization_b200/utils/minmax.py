@@ -5,9 +5,12 @@ Scalar graph logic over per-channel BatchNorm statistics (<= ~1k floats per node
 scipy.stats.norm in fp64 exactly as the reference does, and the resulting (min, max) pairs are written into
 the QuantMeasure buffers wherever those live.
 """
+import math
+
+import numpy as np
 import torch
 import torch.nn as nn
-from scipy.stats import norm
+from scipy.special import ndtr
 
 from .quantize import (QConv2d, QLinear, QuantConv2d, QuantLinear, QuantNConv2d, QuantNLinear)
 
@@ -52,12 +55,19 @@ def find_prev_bn(bn_module, relu_attached, graph, bottoms, bot):
 
 
 # ---- moments of a (clipped) rectified Gaussian, fp64 pdf/cdf rounded to fp32 like the reference (:413-431)
+_SQRT_2PI = math.sqrt(2 * math.pi)
+
+
 def _pdf(x):
-    return torch.from_numpy(norm(0, 1).pdf(x)).float()
+    # scipy.stats.norm(0, 1).pdf(x) == exp(-x**2 / 2) / sqrt(2 pi) in fp64 (scipy/stats/_continuous_distns.py
+    # _norm_pdf), without the per-call frozen-distribution set-up
+    x = np.asarray(x, dtype=np.float64)
+    return torch.from_numpy(np.exp(-x ** 2 / 2.0) / _SQRT_2PI).float()
 
 
 def _cdf(x):
-    return torch.from_numpy(norm.cdf(x)).float()
+    # scipy.stats.norm.cdf(x) == scipy.special.ndtr(x) in fp64
+    return torch.from_numpy(ndtr(np.asarray(x, dtype=np.float64))).float()
 
 
 def relu_mean(w, b):
@@ -88,8 +98,30 @@ def _lo(bias, weight, n):
     return float(torch.min(bias - n * weight))
 
 
+_ctx = {"stats": None, "pending": None}
+
+
 def _bn_stats(bn):
+    """(fake_bias, fake_weight) of a BatchNorm as fresh CPU tensors (one batched D2H copy per call of
+    set_quant_minmax, see _gather_stats)."""
+    cache = _ctx["stats"]
+    if cache is not None and bn in cache:
+        b, w = cache[bn]
+        return b.clone(), w.clone()
     return bn.fake_bias.detach().cpu().clone(), bn.fake_weight.detach().cpu().clone()
+
+
+def _gather_stats(graph, bn_type):
+    bns = [m for m in graph.values() if type(m) == bn_type and hasattr(m, "fake_bias")]
+    if not bns:
+        return {}
+    flat = torch.cat([t.detach().reshape(-1) for m in bns for t in (m.fake_bias, m.fake_weight)]).cpu()
+    out, off = {}, 0
+    for m in bns:
+        n = m.fake_bias.numel()
+        out[m] = (flat[off:off + n], flat[off + n:off + 2 * n])
+        off += 2 * n
+    return out
 
 
 def _clipped_range(bias, weight, relu, N):
@@ -183,8 +215,26 @@ def _range_of(res, N, eps):
 
 
 def _set(qm, lo, hi):
+    if _ctx["pending"] is not None:
+        _ctx["pending"][qm] = (lo, hi)
+        return
     qm.running_max.fill_(hi)
     qm.running_min.fill_(lo)
+
+
+def _flush_pending():
+    """running_min.fill_(lo) / running_max.fill_(hi) for every QuantMeasure with ONE host->device copy: the
+    buffers become [1]-views of a shared [n, 2] tensor (contiguous (min, max) table, reused by the eval plan)."""
+    pending, _ctx["pending"] = _ctx["pending"], None
+    if not pending:
+        return None
+    qms = list(pending)
+    dev = qms[0].running_min.device
+    table = torch.tensor([pending[q] for q in qms], dtype=torch.float32).to(dev)
+    for i, q in enumerate(qms):
+        q.running_min = table[i, 0:1]
+        q.running_max = table[i, 1:2]
+    return table
 
 
 def set_quant_minmax(graph, bottoms, is_detection=False, bn_type=torch.nn.BatchNorm2d, N=6, verbose=True):
@@ -196,6 +246,15 @@ def set_quant_minmax(graph, bottoms, is_detection=False, bn_type=torch.nn.BatchN
     top = G._state.get("module_tensor_op")
     bn_module, relu_attached = {}, {}
     eps = 1e-6
+    _ctx["stats"], _ctx["pending"] = _gather_stats(graph, bn_type), {}
+    try:
+        _walk(graph, bottoms, is_detection, bn_type, N, top, bn_module, relu_attached, eps)
+    finally:
+        _ctx["stats"] = None
+        _flush_pending()
+
+
+def _walk(graph, bottoms, is_detection, bn_type, N, top, bn_module, relu_attached, eps):
     for key in graph:
         node, bot = graph[key], bottoms[key]
         if bot is None:

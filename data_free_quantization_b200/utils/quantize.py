@@ -70,7 +70,7 @@ def fake_quant_tensors(tensors, bits, flags=0, outs=None, codes=None, clip=None,
     tb, ts = L.i64(), L.i64()
     L.check(L.lib().dfq_quant_plan_host(descs, T, ctypes.byref(tb), ctypes.byref(ts)), "dfq_quant_plan_host")
     table = L.table_to_device(descs, dev)
-    ranges = torch.empty(ts.value, 2, dtype=torch.float32, device=dev)
+    ranges = torch.empty(ts.value, 4, dtype=torch.float32, device=dev)   # {min, max, scale, 0} per slot
     L.check(L.lib().dfq_fake_quant_multi_f32(table.data_ptr(), T, tb.value, ts.value, ranges.data_ptr(), L.stream()),
             "dfq_fake_quant_multi_f32")
     return ranges

@@ -23,7 +23,7 @@
 extern "C" {
 #endif
 
-#define DFQ_ABI_VERSION 2
+#define DFQ_ABI_VERSION 3
 
 #if defined(__GNUC__)
 #pragma GCC visibility push(default)   /* the library is built with -fvisibility=hidden */
@@ -114,6 +114,25 @@ typedef struct DfqCorrDesc {
     int64_t range_slot;  /* filled by dfq_corr_plan_host: (min,max) pair in ranges_dev       */
 } DfqCorrDesc;
 
+/* One (conv, BatchNorm) pair of merge_batchnorm (utils/layer_transform.py:255-281). */
+typedef struct DfqMergeDesc {
+    float *W;            /* [O, K] layer weight, scaled in place                       */
+    float *b;            /* [O] layer bias (never NULL: the reference adds zeros, :262-263) */
+    float *gamma, *beta, *mean, *var;   /* [O] BatchNorm tensors; reset to 1, 0, 0, 1 when reset_bn != 0 (:277-280) */
+    float *fake_weight;  /* [O] out: |gamma| (:273) */
+    float *fake_bias;    /* [O] out: beta    (:274) */
+    int64_t O, K;
+    float eps;
+    int32_t first_row;   /* filled by dfq_merge_plan_host */
+} DfqMergeDesc;
+
+/* One tensor of a multi-tensor clamp (clip_weight.py:27-29). */
+typedef struct DfqClipDesc {
+    float *w;
+    int64_t n;
+    int64_t first_block; /* filled by dfq_clip_plan_host */
+} DfqClipDesc;
+
 int dfq_abi_version(void);
 const char *dfq_error_string(int err);
 /* number of kernels launched by this library since load (bench.py's gpu_launches) */
@@ -132,7 +151,8 @@ int dfq_fake_quant_apply_f32(const float *x, float *y, void *codes, int64_t n, i
                              const DfqQuantParams *params_host, void *stream);
 /* plan + launch of the multi-tensor path (quantize_targ_layer, utils/layer_transform.py:288-305):
  *   descs_host[T] is filled in (first_block, range_slot) and the totals returned;
- *   the caller copies descs to the device and provides ranges_dev[2*total_slots] floats. */
+ *   the caller copies descs to the device and provides ranges_dev[4*total_slots] floats, which come back as
+ *   {min, max, scale, 0} per slot (per tensor, or per row for DFQ_Q_PER_CHANNEL). */
 int dfq_quant_plan_host(DfqQuantDesc *descs_host, int n_desc, int64_t *total_blocks, int64_t *total_slots);
 int dfq_fake_quant_multi_f32(const DfqQuantDesc *descs_dev, int n_desc, int64_t total_blocks,
                              int64_t total_slots, float *ranges_dev, void *stream);
@@ -157,10 +177,14 @@ int dfq_absorb_plan_host(DfqAbsorbPair *pairs_host, int n_pairs, int *total_rows
 int dfq_absorb_clip(const DfqAbsorbPair *pairs_dev, int n_pairs, int total_rows, int max_dim, float N,
                     int do_clip, float clip_lo, float clip_hi, void *stream);
 int dfq_clip_f32(float *w, int64_t n, float lo, float hi, void *stream);
+/* every target layer of a model in one launch */
+int dfq_clip_plan_host(DfqClipDesc *descs_host, int n_desc, int64_t *total_blocks);
+int dfq_clip_multi_f32(const DfqClipDesc *descs_dev, int n_desc, int64_t total_blocks, float lo, float hi,
+                       void *stream);
 
 /* ---- (d) bias correction: bias_correction.py:111-144, 224-251 ---------------------- */
 int dfq_corr_plan_host(DfqCorrDesc *descs_host, int n_desc, int64_t *total_units, int64_t *total_blocks);
-/* ranges_dev: 2*n_desc floats (min,max per layer).  range_given != 0: the caller filled them
+/* ranges_dev: 4*n_desc floats, {min, max, scale, 0} per layer.  range_given != 0: the caller filled min and max
  * (4 B/elt); otherwise the call reduces them first (8 B/elt).  `out` must be non-NULL.      */
 int dfq_bias_correct(const DfqCorrDesc *descs_dev, int n_desc, int64_t total_units, int64_t total_blocks,
                      float *ranges_dev, int range_given, void *stream);
@@ -169,6 +193,9 @@ int dfq_bias_correct(const DfqCorrDesc *descs_dev, int n_desc, int64_t total_uni
 int dfq_merge_bn(float *W, float *b, int64_t O, int64_t K, const float *gamma, const float *beta,
                  const float *mean, const float *var, float eps, float *fake_weight, float *fake_bias,
                  void *stream);
+/* every (conv, BN) pair of a model in one launch; reset_bn also turns each BN into the identity */
+int dfq_merge_plan_host(DfqMergeDesc *descs_host, int n_desc, int *total_rows);
+int dfq_merge_bn_multi(const DfqMergeDesc *descs_dev, int n_desc, int total_rows, int reset_bn, void *stream);
 
 #if defined(__GNUC__)
 #pragma GCC visibility pop
