@@ -57,7 +57,7 @@ class DfqClipDesc(ctypes.Structure):
 
 
 Q_SYMMETRIC, Q_RANGE_F32, Q_PER_CHANNEL, Q_CLAMP_OUT = 1, 2, 4, 8
-ABI_VERSION = 3
+ABI_VERSION = 4
 
 # every symbol include/dfq_b200.h declares: (restype, argtypes)
 P = ctypes.POINTER
@@ -69,6 +69,10 @@ PROTOTYPES = {
     "dfq_minmax_f32": (ctypes.c_int, [c_void, i64, c_void, c_void]),
     "dfq_minmax_rows_f32": (ctypes.c_int, [c_void, i64, i64, c_void, c_void]),
     "dfq_fake_quant_apply_f32": (ctypes.c_int, [c_void, c_void, c_void, i64, ctypes.c_int, P(DfqQuantParams), c_void]),
+    "dfq_measure_update": (ctypes.c_int, [c_void, i64, i64, c_void, c_void, c_void, ctypes.c_int, ctypes.c_int,
+                                          ctypes.c_int, c_void, c_void]),
+    "dfq_fake_quant_apply_slot_f32": (ctypes.c_int, [c_void, c_void, c_void, i64, ctypes.c_int, ctypes.c_int, c_void,
+                                                     c_void]),
     "dfq_quant_plan_host": (ctypes.c_int, [P(DfqQuantDesc), ctypes.c_int, P(i64), P(i64)]),
     "dfq_fake_quant_multi_f32": (ctypes.c_int, [c_void, ctypes.c_int, i64, i64, c_void, c_void]),
     "dfq_cle_plan_host": (ctypes.c_int, [P(DfqClePair), ctypes.c_int, P(ctypes.c_int), P(ctypes.c_int)]),

@@ -1,0 +1,96 @@
+// Activation-side pieces of the quantised eval forward (kernel e, part 1): QuantMeasure with the range kept on
+// the device -- utils/quantize.py:94-126.  No host round trip per layer: the per-sample extrema, their mean over
+// the batch, the running-range update (Python max()/min() semantics, :110-111) and the scale all stay in HBM, so
+// a whole forward can be captured in a CUDA graph.
+#include "common.cuh"
+#include "apply.cuh"
+
+namespace dfq {
+
+// One block: mean over samples of the per-sample (min, max) (fp64 accumulate), running-range update, scale.
+//   stats   : [n_samples, 2] from minmax_single_kernel (may be NULL when !update_stat)
+//   running : {running_min, running_max} device pointers (QuantMeasure buffers, updated in place)
+//   slot    : RangeSlot {min, max, scale, 0} consumed by the apply kernel
+__global__ void measure_update_kernel(const float *__restrict__ stats, int64_t n_samples, float *running_min,
+                                      float *running_max, RangeSlot *slot, int bits, int flags, int update_stat) {
+    __shared__ double smin[kWarps], smax[kWarps];
+    float rmin = *running_min, rmax = *running_max;
+    if (update_stat) {                                       // block-uniform
+        double lo = 0.0, hi = 0.0;
+        for (int64_t i = threadIdx.x; i < n_samples; i += blockDim.x) {
+            lo += (double)stats[2 * i];
+            hi += (double)stats[2 * i + 1];
+        }
+        lo = warp_sum(lo); hi = warp_sum(hi);
+        if ((threadIdx.x & 31) == 0) { smin[threadIdx.x >> 5] = lo; smax[threadIdx.x >> 5] = hi; }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            double a = 0.0, b = 0.0;
+            for (int w = 0; w < (int)(blockDim.x >> 5); ++w) { a += smin[w]; b += smax[w]; }
+            float mean_min = (float)(a / (double)n_samples), mean_max = (float)(b / (double)n_samples);
+            // running_max = max(running_max, t): Python keeps the first argument unless t > it (NaN keeps it)
+            if (mean_max > rmax) rmax = mean_max;
+            if (mean_min < rmin) rmin = mean_min;
+            *running_min = rmin;
+            *running_max = rmax;
+        }
+    }
+    if (threadIdx.x == 0) {
+        // quantize(input, num_bits, float(min), float(max)): Python-float path, scale in double (:51-68)
+        DfqQuantParams p = make_quant_params((double)rmin, (double)rmax, bits, flags);
+        RangeSlot r = {rmin, rmax, p.scale, 0.0f};
+        *slot = r;
+    }
+}
+
+// Elementwise pass with the range read from the device slot (QuantMeasure.forward, :123).
+template <typename CodeT>
+__global__ void __launch_bounds__(kThreads)
+fake_quant_slot_kernel(const float *__restrict__ x, float *__restrict__ y, CodeT *__restrict__ codes, int64_t n,
+                       const RangeSlot *__restrict__ slot, int bits, int flags) {
+    QuantConsts c = consts_from_slot(*slot, bits, flags, 0.f, 0.f);
+    int64_t begin = (int64_t)blockIdx.x * kChunk;
+    int64_t end = min(begin + (int64_t)kChunk, n);
+    apply_range<CodeT>(x, y, codes, begin, end, c, false, threadIdx.x, kThreads);
+}
+
+// defined in quant.cu
+__global__ void minmax_single_kernel(DfqQuantDesc d, int64_t total_blocks, unsigned *__restrict__ ranges);
+__global__ void decode_ranges_kernel(unsigned *ranges, int64_t slots);
+
+}  // namespace dfq
+
+using namespace dfq;
+
+extern "C" int dfq_minmax_rows_f32(const float *x, int64_t rows, int64_t cols, float *out_minmax, void *stream);
+
+extern "C" int dfq_measure_update(const float *x, int64_t n_samples, int64_t chw, float *running_min,
+                                  float *running_max, float *slot_dev, int bits, int flags, int update_stat,
+                                  float *stats_scratch, void *stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    if (update_stat) {
+        if (n_samples <= 0 || chw <= 0 || !stats_scratch) return (int)cudaErrorInvalidValue;
+        int e = dfq_minmax_rows_f32(x, n_samples, chw, stats_scratch, stream);      // per-sample extrema (:110-111)
+        if (e) return e;
+    }
+    measure_update_kernel<<<1, 256, 0, st>>>(stats_scratch, n_samples, running_min, running_max,
+                                             (RangeSlot *)slot_dev, bits, flags, update_stat);
+    g_launches += 1;
+    return (int)cudaGetLastError();
+}
+
+extern "C" int dfq_fake_quant_apply_slot_f32(const float *x, float *y, void *codes, int64_t n, int bits, int flags,
+                                             const float *slot_dev, void *stream) {
+    if (n <= 0) return 0;
+    int64_t blocks = (n + kChunk - 1) / kChunk;
+    if (blocks > 0x7fffffffll) return (int)cudaErrorInvalidValue;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (bits <= 8)
+        fake_quant_slot_kernel<uint8_t><<<(unsigned)blocks, kThreads, 0, st>>>(x, y, (uint8_t *)codes, n,
+                                                                               (const RangeSlot *)slot_dev, bits, flags);
+    else
+        fake_quant_slot_kernel<uint16_t><<<(unsigned)blocks, kThreads, 0, st>>>(x, y, (uint16_t *)codes, n,
+                                                                                (const RangeSlot *)slot_dev, bits, flags);
+    g_launches += 1;
+    return (int)cudaGetLastError();
+}

@@ -155,22 +155,48 @@ class QuantMeasure(nn.Module):
         self.update_stat = update_stat
 
     def forward(self, input):
-        if self.update_stat or self.training:
-            mm = sample_minmax_mean(input)
+        if not self.training:
+            return self._forward_eval(input)
+        mm = sample_minmax_mean(input)
         if self.update_stat:
             # Python max()/min() on tensors: the running value is kept unless strictly improved (:110-111)
             self.running_max = torch.where(mm[1] > self.running_max, mm[1], self.running_max)
             self.running_min = torch.where(mm[0] < self.running_min, mm[0], self.running_min)
-        if self.training:
-            min_value, max_value = mm[0], mm[1]
-            self.running_min.mul_(1 - self.momentum).add_(min_value * self.momentum)
-            self.running_max.mul_(1 - self.momentum).add_(max_value * self.momentum)
-        else:
-            min_value, max_value = self.running_min, self.running_max
+        min_value, max_value = mm[0], mm[1]
+        self.running_min.mul_(1 - self.momentum).add_(min_value * self.momentum)
+        self.running_max.mul_(1 - self.momentum).add_(max_value * self.momentum)
         return quantize(input, self.num_bits, min_value=float(min_value), max_value=float(max_value), num_chunks=16)
+
+    def _forward_eval(self, input):
+        """Eval mode (:107-111, :119-123) with the range resident on the device: per-sample extrema, their batch
+        mean, the running-range update and the scale are formed by dfq_measure_update; no float() round trip."""
+        x = input.detach()
+        L.dev_f32(x, "input")
+        out = torch.empty_like(x)
+        if x.numel() == 0:
+            return out
+        n = x.size(0)
+        slot = torch.empty(4, dtype=torch.float32, device=x.device)
+        stats = torch.empty(2 * n, dtype=torch.float32, device=x.device) if self.update_stat else None
+        L.check(L.lib().dfq_measure_update(
+            x.data_ptr(), n, x.numel() // n, L.dev_f32(self.running_min, "running_min"),
+            L.dev_f32(self.running_max, "running_max"), slot.data_ptr(), int(self.num_bits), 0,
+            1 if self.update_stat else 0, None if stats is None else stats.data_ptr(), L.stream()),
+            "dfq_measure_update")
+        L.check(L.lib().dfq_fake_quant_apply_slot_f32(x.data_ptr(), out.data_ptr(), None, x.numel(),
+                                                      int(self.num_bits), 0, slot.data_ptr(), L.stream()),
+                "dfq_fake_quant_apply_slot_f32")
+        return out
 
     def set_update_stat(self, update_stat):
         self.update_stat = update_stat
+
+
+def _conv2d_fp32(input, weight, bias, stride, padding, dilation, groups):
+    """F.conv2d in true fp32: cuDNN would otherwise pick TF32 tensor-core kernels (10-bit mantissa), which breaks
+    the 1e-3 logits tolerance against the reference's CPU fp32 convolution."""
+    with torch.backends.cudnn.flags(enabled=True, allow_tf32=False):
+        return F.conv2d(input, weight, bias, stride, padding, dilation, groups)
 
 
 def _quant_weight(weight, num_bits):
@@ -195,7 +221,7 @@ class QuantConv2d(nn.Conv2d):
         input = self.quant(input)
         qweight = _quant_weight(self.weight, self.num_bits)
         qbias = quantize(self.bias, num_bits=self.num_bits_bias) if self.bias is not None else None
-        return F.conv2d(input, qweight, qbias, self.stride, self.padding, self.dilation, self.groups)
+        return _conv2d_fp32(input, qweight, qbias, self.stride, self.padding, self.dilation, self.groups)
 
 
 class QuantNConv2d(nn.Conv2d):
@@ -209,7 +235,7 @@ class QuantNConv2d(nn.Conv2d):
 
     def forward(self, input):
         input = self.quant(input)
-        return F.conv2d(input, self.weight, self.bias, self.stride, self.padding, self.dilation, self.groups)
+        return _conv2d_fp32(input, self.weight, self.bias, self.stride, self.padding, self.dilation, self.groups)
 
 
 class QuantLinear(nn.Linear):

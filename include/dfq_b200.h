@@ -23,7 +23,7 @@
 extern "C" {
 #endif
 
-#define DFQ_ABI_VERSION 3
+#define DFQ_ABI_VERSION 4
 
 #if defined(__GNUC__)
 #pragma GCC visibility push(default)   /* the library is built with -fvisibility=hidden */
@@ -156,6 +156,16 @@ int dfq_fake_quant_apply_f32(const float *x, float *y, void *codes, int64_t n, i
 int dfq_quant_plan_host(DfqQuantDesc *descs_host, int n_desc, int64_t *total_blocks, int64_t *total_slots);
 int dfq_fake_quant_multi_f32(const DfqQuantDesc *descs_dev, int n_desc, int64_t total_blocks,
                              int64_t total_slots, float *ranges_dev, void *stream);
+
+/* ---- QuantMeasure with the range resident on the device: utils/quantize.py:94-126 (no host round trip) -----
+ * running_min / running_max: the module's [1] buffers (device), updated in place when update_stat != 0 with
+ *   running_max = max(running_max, mean_n max_chw x), running_min = min(...)  (:110-111, Python max/min semantics);
+ * slot_dev: 4 floats {min, max, scale, 0} written for dfq_fake_quant_apply_slot_f32;
+ * stats_scratch: 2*n_samples floats (per-sample extrema), needed when update_stat != 0. */
+int dfq_measure_update(const float *x, int64_t n_samples, int64_t chw, float *running_min, float *running_max,
+                       float *slot_dev, int bits, int flags, int update_stat, float *stats_scratch, void *stream);
+int dfq_fake_quant_apply_slot_f32(const float *x, float *y, void *codes, int64_t n, int bits, int flags,
+                                  const float *slot_dev, void *stream);
 
 /* ---- (b) cross-layer equalisation: Cross_layer_equal.py:63-115 ---------------------- */
 /* sorts pairs by stage (stable) and fills first_unit/n_units */

@@ -1,0 +1,66 @@
+"""GPU: W8A8 quantised eval forward against the logits the UNMODIFIED reference produced on the same seeded
+model and input (tests/golden: eval/logits_b4, quant_minmax_after_eval).  north_star tolerance: logits within
+1e-3 relative, identical top-1."""
+import numpy as np
+import pytest
+import torch
+
+from helpers import fresh_model, names_of, switch
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+@pytest.fixture(scope="module")
+def quantised(gold_npz):
+    """The full DFQ pipeline (main_dfq.py:188-231) with QuantN* layers, as oracle/gen_golden.py ran it."""
+    from data_free_quantization_b200.bias_absorption import bias_absorption
+    from data_free_quantization_b200.clip_weight import clip_weight
+    from data_free_quantization_b200.Cross_layer_equal import cross_layer_equalization
+    from data_free_quantization_b200.utils.layer_transform import (merge_batchnorm, quantize_targ_layer,
+                                                                   set_quant_minmax)
+    from data_free_quantization_b200.utils.quantize import set_layer_bits
+    from data_free_quantization_b200.utils.relation import create_relation
+    model, _ = fresh_model()
+    model, tr, targ = switch(model, DEV)
+    graph, bottoms = tr.log.getGraph(), tr.log.getBottoms()
+    merge_batchnorm(model, graph, bottoms, targ)
+    rels = create_relation(graph, bottoms, targ)
+    cross_layer_equalization(graph, rels, targ, Save_state=False, Treshhold=2e-7)
+    bias_absorption(graph, rels, bottoms, N=3)
+    mods = dict(model.named_modules())
+    for k in gold_npz.files:                       # carry the reference's absorbed biases forward (gen_golden.py)
+        if k.startswith("absorb/"):
+            mod, attr = k[len("absorb/"):].rsplit(".", 1)
+            getattr(mods[mod], attr).data.copy_(torch.from_numpy(gold_npz[k]))
+    set_layer_bits(graph, 8, 8, 8, targ)
+    merge_batchnorm(model, graph, bottoms, targ)
+    quantize_targ_layer(graph, 8, 8, targ)
+    set_quant_minmax(graph, bottoms, verbose=False)
+    clip_weight(graph, [-15, 15], targ)
+    return model, graph, targ
+
+
+def test_eval_logits_match_reference(gold, gold_npz, quantised):
+    from data_free_quantization_b200.utils.layer_transform import replace_op, restore_op
+    model, graph, targ = quantised
+    x = torch.randn(4, 3, 224, 224, generator=torch.Generator().manual_seed(2)).to(DEV)
+    replace_op()
+    try:
+        with torch.no_grad():
+            logits = model(x)
+    finally:
+        restore_op()
+    want = gold_npz["eval/logits_b4"]
+    got = logits.cpu().numpy()
+    assert got.shape == want.shape
+    err = np.abs(got - want).max() / np.abs(want).max()
+    assert err <= 1e-3, err
+    assert np.array_equal(got.argmax(1), want.argmax(1))
+    # update_stat (set_layer_bits bug) widened the running ranges exactly as in the reference
+    names = names_of(model)
+    for key, m in graph.items():
+        if type(m) in targ:
+            lo, hi = gold["quant_minmax_after_eval"][names[key]]
+            assert abs(float(m.quant.running_min) - lo) <= 1e-4 * max(1.0, abs(lo)), names[key]
+            assert abs(float(m.quant.running_max) - hi) <= 1e-4 * max(1.0, abs(hi)), names[key]

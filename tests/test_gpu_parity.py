@@ -145,3 +145,25 @@ def test_bias_correction_eps_dot(oracle, bits, signed):
         W = m.weight.detach().cpu().numpy()
         _, eps = oracle.bias_correct(W, np.ones(W.shape[1], np.float32), bits, signed, want_eps=True)
         assert rel_err(eps.astype(np.float64).mean(1).astype(np.float32), o.cpu().numpy()) <= 1e-5
+
+
+@pytest.mark.parametrize("update_stat", [False, True, 8])
+def test_quant_measure_eval_device_range(oracle, update_stat):
+    """QuantMeasure.forward in eval mode (utils/quantize.py:106-123): running-range update with Python max/min
+    semantics, then quantize() with the Python-float range -- all on the device."""
+    from data_free_quantization_b200.utils.quantize import QuantMeasure
+    rng = np.random.default_rng(17)
+    qm = QuantMeasure(update_stat).to(DEV).eval()
+    qm.running_min.fill_(-0.5)
+    qm.running_max.fill_(0.75)
+    rmin, rmax = np.float32(-0.5), np.float32(0.75)
+    for step, scale in enumerate((0.1, 1.0, 0.3)):
+        x = (rng.standard_normal((6, 3, 17, 19)) * scale).astype(np.float32)
+        if update_stat:
+            lo, hi = oracle.sample_minmax_mean(x)
+            rmax = np.float32(hi) if np.float32(hi) > rmax else rmax
+            rmin = np.float32(lo) if np.float32(lo) < rmin else rmin
+        want = oracle.fake_quant(x, 8, float(rmin), float(rmax))
+        got = qm(_t(x))
+        assert float(qm.running_min) == float(rmin) and float(qm.running_max) == float(rmax), step
+        assert got.cpu().numpy().tobytes() == want.tobytes(), step
