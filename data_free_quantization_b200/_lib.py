@@ -56,8 +56,15 @@ class DfqClipDesc(ctypes.Structure):
     _fields_ = [("w", c_void), ("n", i64), ("first_block", i64)]
 
 
+class DfqConvDesc(ctypes.Structure):
+    _fields_ = [("x", c_void), ("y", c_void), ("w", c_void), ("bias", c_void), ("in_slot", c_void),
+                ("out_stats", c_void)] + [(n, i32) for n in (
+                    "N", "C_in", "H", "W", "C_out", "OH", "OW", "kh", "kw", "stride", "pad", "dil", "groups", "relu",
+                    "bits", "reserved")]
+
+
 Q_SYMMETRIC, Q_RANGE_F32, Q_PER_CHANNEL, Q_CLAMP_OUT = 1, 2, 4, 8
-ABI_VERSION = 4
+ABI_VERSION = 5
 
 # every symbol include/dfq_b200.h declares: (restype, argtypes)
 P = ctypes.POINTER
@@ -73,6 +80,15 @@ PROTOTYPES = {
                                           ctypes.c_int, c_void, c_void]),
     "dfq_fake_quant_apply_slot_f32": (ctypes.c_int, [c_void, c_void, c_void, i64, ctypes.c_int, ctypes.c_int, c_void,
                                                      c_void]),
+    "dfq_measure_from_stats": (ctypes.c_int, [c_void, ctypes.c_int, i64, c_void, c_void, c_void, ctypes.c_int,
+                                              ctypes.c_int, ctypes.c_int, c_void]),
+    "dfq_qconv2d_f32": (ctypes.c_int, [P(DfqConvDesc), c_void]),
+    "dfq_qlinear_f32": (ctypes.c_int, [c_void, c_void, c_void, c_void, i64, ctypes.c_int, ctypes.c_int, c_void,
+                                       ctypes.c_int, ctypes.c_int, c_void, c_void]),
+    "dfq_qadd_f32": (ctypes.c_int, [c_void, c_void, c_void, i64, i64, c_void, c_void, ctypes.c_int, ctypes.c_int,
+                                    c_void, c_void]),
+    "dfq_qmean_f32": (ctypes.c_int, [c_void, c_void, i64, ctypes.c_int, ctypes.c_int, c_void, ctypes.c_int, c_void,
+                                     c_void]),
     "dfq_quant_plan_host": (ctypes.c_int, [P(DfqQuantDesc), ctypes.c_int, P(i64), P(i64)]),
     "dfq_fake_quant_multi_f32": (ctypes.c_int, [c_void, ctypes.c_int, i64, i64, c_void, c_void]),
     "dfq_cle_plan_host": (ctypes.c_int, [P(DfqClePair), ctypes.c_int, P(ctypes.c_int), P(ctypes.c_int)]),

@@ -12,14 +12,21 @@ namespace dfq {
 //   running : {running_min, running_max} device pointers (QuantMeasure buffers, updated in place)
 //   slot    : RangeSlot {min, max, scale, 0} consumed by the apply kernel
 __global__ void measure_update_kernel(const float *__restrict__ stats, int64_t n_samples, float *running_min,
-                                      float *running_max, RangeSlot *slot, int bits, int flags, int update_stat) {
+                                      float *running_max, RangeSlot *slot, int bits, int flags, int update_stat,
+                                      int encoded) {
     __shared__ double smin[kWarps], smax[kWarps];
     float rmin = *running_min, rmax = *running_max;
     if (update_stat) {                                       // block-uniform
         double lo = 0.0, hi = 0.0;
         for (int64_t i = threadIdx.x; i < n_samples; i += blockDim.x) {
-            lo += (double)stats[2 * i];
-            hi += (double)stats[2 * i + 1];
+            if (encoded) {       // {enc(max(-y)), enc(max(y))} accumulated by a producing conv's epilogue
+                const unsigned *e = reinterpret_cast<const unsigned *>(stats);
+                lo += (double)(-dec_ordered(e[2 * i]));
+                hi += (double)dec_ordered(e[2 * i + 1]);
+            } else {
+                lo += (double)stats[2 * i];
+                hi += (double)stats[2 * i + 1];
+            }
         }
         lo = warp_sum(lo); hi = warp_sum(hi);
         if ((threadIdx.x & 31) == 0) { smin[threadIdx.x >> 5] = lo; smax[threadIdx.x >> 5] = hi; }
@@ -54,10 +61,6 @@ fake_quant_slot_kernel(const float *__restrict__ x, float *__restrict__ y, CodeT
     apply_range<CodeT>(x, y, codes, begin, end, c, false, threadIdx.x, kThreads);
 }
 
-// defined in quant.cu
-__global__ void minmax_single_kernel(DfqQuantDesc d, int64_t total_blocks, unsigned *__restrict__ ranges);
-__global__ void decode_ranges_kernel(unsigned *ranges, int64_t slots);
-
 }  // namespace dfq
 
 using namespace dfq;
@@ -74,7 +77,18 @@ extern "C" int dfq_measure_update(const float *x, int64_t n_samples, int64_t chw
         if (e) return e;
     }
     measure_update_kernel<<<1, 256, 0, st>>>(stats_scratch, n_samples, running_min, running_max,
-                                             (RangeSlot *)slot_dev, bits, flags, update_stat);
+                                             (RangeSlot *)slot_dev, bits, flags, update_stat, 0);
+    g_launches += 1;
+    return (int)cudaGetLastError();
+}
+
+extern "C" int dfq_measure_from_stats(const void *stats, int encoded, int64_t n_samples, float *running_min,
+                                      float *running_max, float *slot_dev, int bits, int flags, int update_stat,
+                                      void *stream) {
+    if (update_stat && (!stats || n_samples <= 0)) return (int)cudaErrorInvalidValue;
+    measure_update_kernel<<<1, 256, 0, (cudaStream_t)stream>>>((const float *)stats, n_samples, running_min,
+                                                               running_max, (RangeSlot *)slot_dev, bits, flags,
+                                                               update_stat, encoded);
     g_launches += 1;
     return (int)cudaGetLastError();
 }

@@ -1,0 +1,387 @@
+// Kernel (e), CUDA-core part: the quantised eval forward of utils/quantize.py:225-256 / 336-363 without tensor
+// cores -- depthwise 3x3, small-Cin dense kxk (first layer), a reference fp32 pointwise/linear path, the
+// quantised residual add and mean (utils/layer_transform.py:18-32, 79-94).  Every kernel
+//   * fake-quantises its input ON LOAD with the consumer's QuantMeasure range (RangeSlot on the device), exactly
+//     the fp32 recipe of utils/quantize.py:72-76, so no quantised copy of the activation is ever written;
+//   * fuses bias (+ identity BatchNorm) + ReLU into the epilogue;
+//   * optionally reduces the per-sample min/max of what it writes (the next QuantMeasure's update_stat
+//     statistics, utils/quantize.py:110-111) into an encoded [N,2] table with one atomic pair per block.
+// Accumulation is fp32 in a fixed order (not the reference's ATen order): parity is the 1e-3 logits tolerance.
+#include "common.cuh"
+
+namespace dfq {
+
+struct ConvArgs {
+    const float *x; float *y; const float *w; const float *bias; const RangeSlot *slot; unsigned *stats;
+    int N, C, H, W, O, OH, OW, stride, pad, dil, relu, bits, kh, kw;
+    int cb, rows;          // depthwise: channels per block, output rows per block
+    int strips;            // row strips per plane
+};
+
+__device__ __forceinline__ float quant_or_pass(float v, const QuantConsts &c, bool on) {
+    float q;
+    return on ? fake_quant_elem(v, c, q) : v;
+}
+
+// block-level min/max of `lo/hi` into stats[n] (encoded max(-y), max(y))
+__device__ __forceinline__ void stats_flush(unsigned *stats, int n, float lo, float hi, float *sm) {
+    block_minmax(lo, hi, sm);
+    if (threadIdx.x == 0) {
+        atomicMax(stats + 2 * n, enc_ordered(-lo));
+        atomicMax(stats + 2 * n + 1, enc_ordered(hi));
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Depthwise 3x3 (groups == C == O), stride 1 or 2, zero padding `pad`, dilation `dil`.
+// A block owns `cb` consecutive channels x `rows` output rows of one image; the needed input rows are
+// quantised once into shared memory with the zero padding materialised (real 0.0, utils/quantize.py quantises
+// before F.conv2d pads), then every thread produces outputs from shared memory.
+__global__ void __launch_bounds__(kThreads)
+dwconv3x3_kernel(ConvArgs a) {
+    extern __shared__ float smem[];
+    __shared__ float red[2 * kWarps];
+    const int tid = threadIdx.x;
+    int b = blockIdx.x;
+    const int strip = b % a.strips; b /= a.strips;
+    const int cgroups = (a.C + a.cb - 1) / a.cb;
+    const int cg = b % cgroups;
+    const int n = b / cgroups;
+    const int c0 = cg * a.cb, nc = min(a.cb, a.C - c0);
+    const int r0 = strip * a.rows, nr = min(a.rows, a.OH - r0);
+    const int in_r0 = r0 * a.stride - a.pad;                       // first input row (may be negative)
+    const int in_rows = (nr - 1) * a.stride + 2 * a.dil + 1;
+    const int pw = a.W + 2 * a.pad;                                 // padded row length in smem
+    const bool on = a.slot != nullptr;
+    QuantConsts qc;
+    if (on) qc = consts_from_slot(*a.slot, a.bits, 0, 0.f, 0.f);
+    // ---- stage: smem[c][r][pad + col]
+    const int plane = in_rows * pw;
+    for (int idx = tid; idx < nc * plane; idx += kThreads) {
+        int c = idx / plane, rem = idx - c * plane;
+        int r = rem / pw, col = rem - r * pw - a.pad;
+        int gr = in_r0 + r;
+        float v = 0.0f;
+        if (gr >= 0 && gr < a.H && col >= 0 && col < a.W)
+            v = quant_or_pass(__ldg(a.x + (((int64_t)n * a.C + c0 + c) * a.H + gr) * a.W + col), qc, on);
+        smem[idx] = v;
+    }
+    __syncthreads();
+    float lo = INFINITY, hi = -INFINITY;
+    const int outs = nr * a.OW;
+    for (int idx = tid; idx < nc * outs; idx += kThreads) {
+        int c = idx / outs, rem = idx - c * outs;
+        int orow = rem / a.OW, ocol = rem - orow * a.OW;
+        const float *w = a.w + (int64_t)(c0 + c) * 9;
+        const float *s = smem + c * plane + (orow * a.stride) * pw + ocol * a.stride;
+        float acc = 0.0f;
+#pragma unroll
+        for (int i = 0; i < 3; ++i)
+#pragma unroll
+            for (int j = 0; j < 3; ++j) acc = __fmaf_rn(s[i * a.dil * pw + j * a.dil], __ldg(w + i * 3 + j), acc);
+        if (a.bias) acc = __fadd_rn(acc, __ldg(a.bias + c0 + c));
+        if (a.relu) acc = fmaxf(acc, 0.0f);
+        a.y[(((int64_t)n * a.O + c0 + c) * a.OH + r0 + orow) * a.OW + ocol] = acc;
+        lo = fminf(lo, acc); hi = fmaxf(hi, acc);
+    }
+    if (a.stats) stats_flush(a.stats, n, lo, hi, red);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Dense kxk convolution, direct form, for small C*kh*kw (MobileNetV2's first layer: 3 -> 32, 3x3, stride 2).
+// A block owns `rows` output rows of one image for all O output channels: the quantised, zero-padded input strip
+// and the whole weight tensor sit in shared memory; a thread owns one output pixel and walks the output channels
+// 8 at a time (stores for a fixed channel are contiguous across the warp).
+constexpr int kOT = 8;
+
+__global__ void __launch_bounds__(kThreads)
+conv_direct_kernel(ConvArgs a) {
+    extern __shared__ float smem[];
+    __shared__ float red[2 * kWarps];
+    const int tid = threadIdx.x;
+    const int strip = blockIdx.x % a.strips, n = blockIdx.x / a.strips;
+    const int r0 = strip * a.rows, nr = min(a.rows, a.OH - r0);
+    const int in_r0 = r0 * a.stride - a.pad;
+    const int in_rows = (nr - 1) * a.stride + (a.kh - 1) * a.dil + 1;
+    const int pw = a.W + 2 * a.pad;
+    const int plane = in_rows * pw;
+    const int kk = a.kh * a.kw, ckk = a.C * kk;
+    float *sw = smem;                                   // [O][C*kh*kw]
+    float *sx = smem + a.O * ckk;                       // [C][in_rows][pw]
+    const bool on = a.slot != nullptr;
+    QuantConsts qc;
+    if (on) qc = consts_from_slot(*a.slot, a.bits, 0, 0.f, 0.f);
+    for (int idx = tid; idx < a.O * ckk; idx += kThreads) sw[idx] = __ldg(a.w + idx);
+    for (int idx = tid; idx < a.C * plane; idx += kThreads) {
+        int c = idx / plane, rem = idx - c * plane;
+        int r = rem / pw, col = rem - r * pw - a.pad;
+        int gr = in_r0 + r;
+        float v = 0.0f;
+        if (gr >= 0 && gr < a.H && col >= 0 && col < a.W)
+            v = quant_or_pass(__ldg(a.x + (((int64_t)n * a.C + c) * a.H + gr) * a.W + col), qc, on);
+        sx[idx] = v;
+    }
+    __syncthreads();
+    float lo = INFINITY, hi = -INFINITY;
+    const int outs = nr * a.OW;
+    for (int p = tid; p < outs; p += kThreads) {
+        int orow = p / a.OW, ocol = p - orow * a.OW;
+        const float *s0 = sx + (orow * a.stride) * pw + ocol * a.stride;
+        for (int o0 = 0; o0 < a.O; o0 += kOT) {
+            float acc[kOT];
+#pragma unroll
+            for (int t = 0; t < kOT; ++t) acc[t] = 0.0f;
+            for (int c = 0; c < a.C; ++c)
+                for (int i = 0; i < a.kh; ++i)
+                    for (int j = 0; j < a.kw; ++j) {
+                        float v = s0[c * plane + i * a.dil * pw + j * a.dil];
+                        const float *wp = sw + (int64_t)o0 * ckk + c * kk + i * a.kw + j;
+#pragma unroll
+                        for (int t = 0; t < kOT; ++t)
+                            if (o0 + t < a.O) acc[t] = __fmaf_rn(v, wp[t * ckk], acc[t]);
+                    }
+#pragma unroll
+            for (int t = 0; t < kOT; ++t) {
+                if (o0 + t >= a.O) break;
+                float r = acc[t];
+                if (a.bias) r = __fadd_rn(r, __ldg(a.bias + o0 + t));
+                if (a.relu) r = fmaxf(r, 0.0f);
+                a.y[(((int64_t)n * a.O + o0 + t) * a.OH + r0 + orow) * a.OW + ocol] = r;
+                lo = fminf(lo, r); hi = fmaxf(hi, r);
+            }
+        }
+    }
+    if (a.stats) stats_flush(a.stats, n, lo, hi, red);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Pointwise (1x1) convolution / linear layer in fp32 on CUDA cores: the exact-semantics path for layers whose
+// weights are not on an 8-bit grid (QuantNConv2d with arbitrary weights) and the on-device comparator of the
+// tcgen05 path.  Y[n,o,p] = sum_i W[o,i] * Q(X[n,i,p]) + b[o].
+// Generic element addressing: X element (n, i, p) at x + n*xs_n + i*xs_i + p*xs_p (conv: xs_i = HW, xs_p = 1;
+// linear: one "image", p = sample, xs_p = K, xs_i = 1); Y likewise.
+struct PwArgs {
+    const float *x; float *y; const float *w; const float *bias; const RangeSlot *slot; unsigned *stats;
+    int N, K, O, P;                       // images, input channels, output channels, pixels per image
+    int64_t xs_n, xs_i, xs_p, ys_n, ys_o, ys_p;
+    int relu, bits, stats_per_pixel;      // stats_per_pixel: linear layer, the "sample" is the pixel index
+};
+
+constexpr int kPwPix = kThreads, kPwK = 32, kPwO = 16;
+
+__global__ void __launch_bounds__(kPwPix)
+pw_fp32_kernel(PwArgs a) {
+    __shared__ float sx[kPwK][kPwPix];
+    __shared__ float sw[kPwO][kPwK + 1];
+    __shared__ float red[2 * kWarps];
+    const int tid = threadIdx.x;
+    const int ptiles = (a.P + kPwPix - 1) / kPwPix;
+    const int pt = blockIdx.x % ptiles, n = blockIdx.x / ptiles;
+    const int p = pt * kPwPix + tid;
+    const bool live = p < a.P;
+    const bool on = a.slot != nullptr;
+    QuantConsts qc;
+    if (on) qc = consts_from_slot(*a.slot, a.bits, 0, 0.f, 0.f);
+    float lo = INFINITY, hi = -INFINITY;
+    for (int o0 = 0; o0 < a.O; o0 += kPwO) {
+        float acc[kPwO];
+#pragma unroll
+        for (int t = 0; t < kPwO; ++t) acc[t] = 0.0f;
+        for (int k0 = 0; k0 < a.K; k0 += kPwK) {
+            __syncthreads();
+            for (int kk = 0; kk < kPwK; ++kk) {
+                float v = 0.0f;
+                if (live && k0 + kk < a.K)
+                    v = quant_or_pass(__ldg(a.x + n * a.xs_n + (int64_t)(k0 + kk) * a.xs_i + p * a.xs_p), qc, on);
+                sx[kk][tid] = v;
+            }
+            for (int idx = tid; idx < kPwO * kPwK; idx += kPwPix) {
+                int t = idx / kPwK, kk = idx - t * kPwK;
+                sw[t][kk] = (o0 + t < a.O && k0 + kk < a.K) ? __ldg(a.w + (int64_t)(o0 + t) * a.K + k0 + kk) : 0.0f;
+            }
+            __syncthreads();
+#pragma unroll 4
+            for (int kk = 0; kk < kPwK; ++kk) {
+                float v = sx[kk][tid];
+#pragma unroll
+                for (int t = 0; t < kPwO; ++t) acc[t] = __fmaf_rn(v, sw[t][kk], acc[t]);
+            }
+        }
+        if (live) {
+#pragma unroll
+            for (int t = 0; t < kPwO; ++t) {
+                if (o0 + t >= a.O) break;
+                float r = acc[t];
+                if (a.bias) r = __fadd_rn(r, __ldg(a.bias + o0 + t));
+                if (a.relu) r = fmaxf(r, 0.0f);
+                a.y[n * a.ys_n + (int64_t)(o0 + t) * a.ys_o + p * a.ys_p] = r;
+                lo = fminf(lo, r); hi = fmaxf(hi, r);
+            }
+        }
+    }
+    if (a.stats) {
+        if (a.stats_per_pixel) {               // linear: every "pixel" is a sample with its own extrema
+            if (live) {
+                atomicMax(a.stats + 2 * p, enc_ordered(-lo));
+                atomicMax(a.stats + 2 * p + 1, enc_ordered(hi));
+            }
+        } else {
+            stats_flush(a.stats, n, lo, hi, red);
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Quantised residual add (utils/layer_transform.py:18-32): out = Q_a(a) + Q_b(b), each operand through its own
+// QuantMeasure; per-sample extrema of `out` for the next layer's QuantMeasure.
+__global__ void __launch_bounds__(kThreads)
+qadd_kernel(const float *__restrict__ xa, const float *__restrict__ xb, float *__restrict__ out, int64_t chw,
+            int chunks, const RangeSlot *sa, const RangeSlot *sb, int bits_a, int bits_b, unsigned *stats) {
+    __shared__ float red[2 * kWarps];
+    const int n = blockIdx.x / chunks, ch = blockIdx.x % chunks;
+    QuantConsts ca, cb;
+    if (sa) ca = consts_from_slot(*sa, bits_a, 0, 0.f, 0.f);
+    if (sb) cb = consts_from_slot(*sb, bits_b, 0, 0.f, 0.f);
+    const int64_t base = (int64_t)n * chw;
+    const int64_t begin = (int64_t)ch * kChunk, end = min(begin + (int64_t)kChunk, chw);
+    float lo = INFINITY, hi = -INFINITY;
+    const bool vec = (((uintptr_t)(xa + base + begin) | (uintptr_t)(xb + base + begin) | (uintptr_t)(out + base + begin)) & 15) == 0;
+    int64_t n4 = vec ? ((end - begin) >> 2) : 0;
+    const float4 *a4 = reinterpret_cast<const float4 *>(xa + base + begin);
+    const float4 *b4 = reinterpret_cast<const float4 *>(xb + base + begin);
+    float4 *o4 = reinterpret_cast<float4 *>(out + base + begin);
+    for (int64_t k = threadIdx.x; k < n4; k += kThreads) {
+        float4 va = __ldg(a4 + k), vb = __ldg(b4 + k), r;
+        r.x = __fadd_rn(quant_or_pass(va.x, ca, sa), quant_or_pass(vb.x, cb, sb));
+        r.y = __fadd_rn(quant_or_pass(va.y, ca, sa), quant_or_pass(vb.y, cb, sb));
+        r.z = __fadd_rn(quant_or_pass(va.z, ca, sa), quant_or_pass(vb.z, cb, sb));
+        r.w = __fadd_rn(quant_or_pass(va.w, ca, sa), quant_or_pass(vb.w, cb, sb));
+        o4[k] = r;
+        lo = fminf(lo, fminf(fminf(r.x, r.y), fminf(r.z, r.w)));
+        hi = fmaxf(hi, fmaxf(fmaxf(r.x, r.y), fmaxf(r.z, r.w)));
+    }
+    for (int64_t k = begin + (n4 << 2) + threadIdx.x; k < end; k += kThreads) {
+        float r = __fadd_rn(quant_or_pass(xa[base + k], ca, sa), quant_or_pass(xb[base + k], cb, sb));
+        out[base + k] = r;
+        lo = fminf(lo, r); hi = fmaxf(hi, r);
+    }
+    if (stats) stats_flush(stats, n, lo, hi, red);
+}
+
+// Quantised spatial mean (utils/layer_transform.py:79-94 + MobileNetV2.py:112): out[n,c] = mean_hw Q(x[n,c,:]).
+// A block owns 32 channels of one image (a warp walks 4 of them); fp32 tree sum, one division.
+__global__ void __launch_bounds__(kThreads)
+qmean_kernel(const float *__restrict__ x, float *__restrict__ out, int C, int HW, const RangeSlot *slot, int bits,
+             unsigned *stats) {
+    __shared__ float red[2 * kWarps];
+    const int groups = (C + 31) / 32;
+    const int n = blockIdx.x / groups, c0 = (blockIdx.x % groups) * 32;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    QuantConsts qc;
+    if (slot) qc = consts_from_slot(*slot, bits, 0, 0.f, 0.f);
+    float lo = INFINITY, hi = -INFINITY;
+    for (int t = 0; t < 4; ++t) {
+        int c = c0 + warp * 4 + t;
+        if (c >= C) break;
+        const float *p = x + ((int64_t)n * C + c) * HW;
+        float s = 0.0f;
+        for (int k = lane; k < HW; k += 32) s = __fadd_rn(s, quant_or_pass(__ldg(p + k), qc, slot));
+        s = warp_sum(s);
+        float m = __fdiv_rn(s, (float)HW);
+        if (lane == 0) out[(int64_t)n * C + c] = m;
+        lo = fminf(lo, m); hi = fmaxf(hi, m);
+    }
+    if (stats) stats_flush(stats, n, lo, hi, red);
+}
+
+}  // namespace dfq
+
+using namespace dfq;
+
+// Chooses the kernel for one layer: depthwise 3x3 / small dense kxk / pointwise (fp32 CUDA-core form).
+extern "C" int dfq_qconv2d_f32(const DfqConvDesc *d, void *stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    if (!d || d->N <= 0) return (int)cudaErrorInvalidValue;
+    const int OH = (d->H + 2 * d->pad - d->dil * (d->kh - 1) - 1) / d->stride + 1;
+    const int OW = (d->W + 2 * d->pad - d->dil * (d->kw - 1) - 1) / d->stride + 1;
+    if (OH != d->OH || OW != d->OW) return (int)cudaErrorInvalidValue;
+    if (d->kh == 1 && d->kw == 1 && d->groups == 1 && d->stride == 1 && d->pad == 0) {
+        PwArgs a;
+        a.x = d->x; a.y = d->y; a.w = d->w; a.bias = d->bias; a.slot = (const RangeSlot *)d->in_slot;
+        a.stats = d->out_stats;
+        a.N = d->N; a.K = d->C_in; a.O = d->C_out; a.P = d->H * d->W;
+        a.xs_n = (int64_t)d->C_in * a.P; a.xs_i = a.P; a.xs_p = 1;
+        a.ys_n = (int64_t)d->C_out * a.P; a.ys_o = a.P; a.ys_p = 1;
+        a.relu = d->relu; a.bits = d->bits; a.stats_per_pixel = 0;
+        int ptiles = (a.P + kPwPix - 1) / kPwPix;
+        pw_fp32_kernel<<<(unsigned)(ptiles * d->N), kPwPix, 0, st>>>(a);
+        g_launches += 1;
+        return (int)cudaGetLastError();
+    }
+    ConvArgs a;
+    a.x = d->x; a.y = d->y; a.w = d->w; a.bias = d->bias; a.slot = (const RangeSlot *)d->in_slot; a.stats = d->out_stats;
+    a.N = d->N; a.C = d->C_in; a.H = d->H; a.W = d->W; a.O = d->C_out; a.OH = OH; a.OW = OW;
+    a.stride = d->stride; a.pad = d->pad; a.dil = d->dil; a.relu = d->relu; a.bits = d->bits; a.kh = d->kh; a.kw = d->kw;
+    const int pw = d->W + 2 * d->pad;
+    if (d->groups == d->C_in && d->C_in == d->C_out && d->kh == 3 && d->kw == 3) {
+        // strip height: about 2048 outputs per block; small planes take several channels per block
+        int rows = OH, cb = 1;
+        if (OH * OW > 2048) rows = max(1, 2048 / OW);
+        else cb = max(1, min(d->C_in, 2048 / (OH * OW)));
+        auto smem_of = [&](int r, int c) { return (size_t)c * ((r - 1) * d->stride + 2 * d->dil + 1) * pw * sizeof(float); };
+        while (smem_of(rows, cb) > 96 * 1024 && (cb > 1 || rows > 1)) { if (cb > 1) cb = (cb + 1) / 2; else rows = (rows + 1) / 2; }
+        a.rows = rows; a.cb = cb; a.strips = (OH + rows - 1) / rows;
+        size_t smem = smem_of(rows, cb);
+        if (smem > 48 * 1024) cudaFuncSetAttribute(dwconv3x3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
+        int blocks = d->N * ((d->C_in + cb - 1) / cb) * a.strips;
+        dwconv3x3_kernel<<<(unsigned)blocks, kThreads, smem, st>>>(a);
+        g_launches += 1;
+        return (int)cudaGetLastError();
+    }
+    if (d->groups == 1) {
+        size_t wbytes = (size_t)d->C_out * d->C_in * d->kh * d->kw * sizeof(float);
+        int rows = max(1, 1024 / OW);
+        auto smem_of = [&](int r) { return wbytes + (size_t)d->C_in * ((r - 1) * d->stride + (d->kh - 1) * d->dil + 1) * pw * sizeof(float); };
+        while (smem_of(rows) > 96 * 1024 && rows > 1) rows = (rows + 1) / 2;
+        if (smem_of(rows) > 96 * 1024) return (int)cudaErrorInvalidValue;   // large dense kxk: tensor-core path (not built yet)
+        a.rows = rows; a.cb = 0; a.strips = (OH + rows - 1) / rows;
+        if (smem_of(rows) > 48 * 1024) cudaFuncSetAttribute(conv_direct_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
+        conv_direct_kernel<<<(unsigned)(d->N * a.strips), kThreads, smem_of(rows), st>>>(a);
+        g_launches += 1;
+        return (int)cudaGetLastError();
+    }
+    return (int)cudaErrorInvalidValue;
+}
+
+// Linear layer through the same fp32 path: x [N, K], w [O, K], y [N, O]; out_stats per sample.
+extern "C" int dfq_qlinear_f32(const float *x, float *y, const float *w, const float *bias, int64_t N, int K, int O,
+                               const float *in_slot, int bits, int relu, unsigned *out_stats, void *stream) {
+    if (N <= 0) return 0;
+    PwArgs a;
+    a.x = x; a.y = y; a.w = w; a.bias = bias; a.slot = (const RangeSlot *)in_slot; a.stats = out_stats;
+    a.N = 1; a.K = K; a.O = O; a.P = (int)N;
+    a.xs_n = 0; a.xs_i = 1; a.xs_p = K; a.ys_n = 0; a.ys_o = 1; a.ys_p = O;
+    a.relu = relu; a.bits = bits; a.stats_per_pixel = 1;
+    pw_fp32_kernel<<<(unsigned)((N + kPwPix - 1) / kPwPix), kPwPix, 0, (cudaStream_t)stream>>>(a);
+    g_launches += 1;
+    return (int)cudaGetLastError();
+}
+
+extern "C" int dfq_qadd_f32(const float *a, const float *b, float *out, int64_t N, int64_t chw, const float *slot_a,
+                            const float *slot_b, int bits_a, int bits_b, unsigned *out_stats, void *stream) {
+    if (N <= 0 || chw <= 0) return 0;
+    int chunks = (int)((chw + kChunk - 1) / kChunk);
+    qadd_kernel<<<(unsigned)(N * chunks), kThreads, 0, (cudaStream_t)stream>>>(
+        a, b, out, chw, chunks, (const RangeSlot *)slot_a, (const RangeSlot *)slot_b, bits_a, bits_b, out_stats);
+    g_launches += 1;
+    return (int)cudaGetLastError();
+}
+
+extern "C" int dfq_qmean_f32(const float *x, float *out, int64_t N, int C, int HW, const float *slot, int bits,
+                             unsigned *out_stats, void *stream) {
+    if (N <= 0) return 0;
+    qmean_kernel<<<(unsigned)(N * ((C + 31) / 32)), kThreads, 0, (cudaStream_t)stream>>>(
+        x, out, C, HW, (const RangeSlot *)slot, bits, out_stats);
+    g_launches += 1;
+    return (int)cudaGetLastError();
+}

@@ -1,0 +1,292 @@
+"""Static plan of the quantised eval forward: the traced graph compiled once into a flat list of
+libdfq_b200 launches with preallocated HBM buffers -- no Python graph interpretation, no inspect.stack(), no
+host synchronisation per layer, capturable in a CUDA graph.
+
+Semantics are those of the reference's eval path (utils/quantize.py:106-123, 225-256, 336-363 and the patched
+tensor ops of utils/layer_transform.py:18-125) with replace_op() in force:
+  * every target layer fake-quantises its input with its own QuantMeasure (running range widened by the batch
+    statistics when `update_stat` is truthy -- the set_layer_bits bug);
+  * both operands of a residual add and the operand of the spatial mean go through the CustomTensorOP measures;
+  * identity BatchNorms (after merge_batchnorm) vanish, ReLU is fused into the producing kernel.
+Quantisation happens on load inside the consuming kernel; producers accumulate the per-sample extrema the next
+measure needs in their epilogue.
+"""
+import ctypes
+import operator
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from . import _lib as L
+from .graph import _ADD
+
+_PASS_METHODS = {"view", "reshape", "contiguous", "flatten"}
+
+
+class _T:
+    """A tensor of the plan: shape, buffer, optional per-sample stats table."""
+
+    def __init__(self, shape):
+        self.shape = tuple(shape)
+        self.buf = None
+        self.stats = None
+        self.stats_encoded = True
+        self.relu_of = None
+        self.relu_done = False
+        self.need_stats = False
+
+    @property
+    def numel(self):
+        n = 1
+        for s in self.shape:
+            n *= s
+        return n
+
+
+class EvalPlan:
+    def __init__(self, model, transformer, batch, in_shape=(3, 224, 224), pw_impl="fp32"):
+        self.model, self.fxg = model, transformer.fx_graph
+        self.dev = next(model.parameters()).device
+        self.N = int(batch)
+        self.pw_impl = pw_impl
+        self.ops = []                # (name, callable)
+        self.measures = []           # (qm, slot index, input tensor)
+        self.keep = []               # ctypes objects / tensors that must outlive the plan
+        self._build(in_shape)
+
+    # ------------------------------------------------------------------------------------------------ build
+    def _slot_for(self, qm, t):
+        """Slot of QuantMeasure `qm` applied to tensor `t`; schedules the measure kernel before the consumer."""
+        idx = len(self.measures)
+        self.measures.append((qm, idx, t))
+        if qm.update_stat:
+            t.need_stats = True
+        return idx
+
+    def _build(self, in_shape):
+        mods = dict(self.model.named_modules())
+        top = getattr(self.model, "custom_tensor_op", None)
+        top_qms = list(top.children()) if top is not None else []
+        top_i = 0
+        env = {}
+        steps = []                   # symbolic ops, resolved to launches after buffer assignment
+        for node in self.fxg.nodes:
+            if node.op == "placeholder":
+                t = _T((self.N,) + tuple(in_shape))
+                t.stats_encoded = False
+                env[node] = t
+                self.input = t
+            elif node.op == "call_module":
+                m = mods[node.target]
+                src = env[node.args[0]]
+                if isinstance(m, nn.BatchNorm2d):
+                    if not hasattr(m, "fake_weight"):
+                        raise NotImplementedError(f"{node.target}: BatchNorm not merged (run merge_batchnorm first)")
+                    env[node] = src                      # identity after merge_batchnorm
+                elif isinstance(m, (nn.ReLU, nn.ReLU6)):
+                    if isinstance(m, nn.ReLU6) or src.relu_of is None or src.relu_done:
+                        raise NotImplementedError(f"{node.target}: stand-alone activation is not supported by the plan")
+                    src.relu_of["relu"] = 1              # fuse into the producing conv
+                    src.relu_done = True
+                    env[node] = src
+                elif isinstance(m, nn.Conv2d):
+                    N, C, H, W = src.shape
+                    kh, kw = m.kernel_size
+                    s, p, d = m.stride[0], m.padding[0], m.dilation[0]
+                    OH = (H + 2 * p - d * (kh - 1) - 1) // s + 1
+                    OW = (W + 2 * p - d * (kw - 1) - 1) // s + 1
+                    out = _T((N, m.out_channels, OH, OW))
+                    step = {"kind": "conv", "m": m, "src": src, "out": out, "relu": 0, "name": node.target,
+                            "geom": (kh, kw, s, p, d, m.groups)}
+                    step["slot"] = self._slot_for(m.quant, src) if hasattr(m, "quant") else None
+                    out.relu_of, out.relu_done = step, False
+                    steps.append(step)
+                    env[node] = out
+                elif isinstance(m, nn.Linear):
+                    out = _T((src.shape[0], m.out_features))
+                    step = {"kind": "linear", "m": m, "src": src, "out": out, "relu": 0, "name": node.target}
+                    step["slot"] = self._slot_for(m.quant, src) if hasattr(m, "quant") else None
+                    out.relu_of, out.relu_done = step, False
+                    steps.append(step)
+                    env[node] = out
+                elif isinstance(m, (nn.Dropout, nn.Identity)):
+                    env[node] = src
+                else:
+                    raise NotImplementedError(f"{node.target}: {type(m).__name__} is not supported by the eval plan")
+            elif node.op in ("call_function", "call_method"):
+                key = node.meta.get("dfq_key")
+                if key is not None and (node.target in _ADD or node.target in ("add", "add_")):
+                    a, b = (env[x] for x in node.meta["dfq_operands"])
+                    out = _T(a.shape)
+                    qa, qb = top_qms[top_i], top_qms[top_i + 1]
+                    top_i += 2
+                    steps.append({"kind": "add", "a": a, "b": b, "out": out, "name": key,
+                                  "slot_a": self._slot_for(qa, a), "slot_b": self._slot_for(qb, b),
+                                  "bits": (qa.num_bits, qb.num_bits)})
+                    env[node] = out
+                elif key is not None and key.startswith("torch.mean"):
+                    src = env[node.meta["dfq_operands"][0]]
+                    N, C = src.shape[0], src.shape[1]
+                    out = _T((N, C))
+                    qm = top_qms[top_i]
+                    top_i += 1
+                    steps.append({"kind": "mean", "src": src, "out": out, "name": key, "bits": qm.num_bits,
+                                  "slot": self._slot_for(qm, src)})
+                    env[node] = out
+                elif key is not None:
+                    raise NotImplementedError(f"{key}: tensor op not supported by the eval plan yet")
+                elif node.op == "call_method" and node.target in ("size", "dim"):
+                    env[node] = None
+                elif (node.op == "call_method" and node.target in _PASS_METHODS) or node.target is operator.getitem:
+                    first = node.args[0]
+                    env[node] = env.get(first) if isinstance(first, torch.fx.Node) else None
+                else:
+                    raise NotImplementedError(f"{node.target}: not supported by the eval plan")
+            elif node.op == "output":
+                self.output = env[node.args[0]]
+        self._assign(steps)
+
+    # ------------------------------------------------------------------------------------- buffers + launches
+    def _assign(self, steps):
+        dev, N = self.dev, self.N
+        lib = L.lib()
+        f32 = lambda *shape: torch.empty(*shape, dtype=torch.float32, device=dev)
+        self.slots = torch.zeros(max(1, len(self.measures)), 4, dtype=torch.float32, device=dev)
+        # last use of every tensor -> simple free-list reuse of activation buffers
+        last = {}
+        for i, st in enumerate(steps):
+            for k in ("src", "a", "b"):
+                if k in st:
+                    last[id(st[k])] = i
+        last[id(self.output)] = len(steps)
+        pool = {}
+        self.input.buf = f32(*self.input.shape)
+        tensors = [self.input]
+        for i, st in enumerate(steps):
+            out = st["out"]
+            free = pool.get(out.numel)
+            out.buf = free.pop() if free else f32(*out.shape)
+            tensors.append(out)
+            for k in ("src", "a", "b"):
+                t = st.get(k)
+                if t is not None and last[id(t)] == i and t is not self.input and t.buf is not None:
+                    pool.setdefault(t.numel, []).append(t.buf)
+        need = [t for t in tensors if t.need_stats]
+        self.stats = torch.zeros(max(1, len(need)), N, 2, dtype=torch.int32, device=dev)
+        for i, t in enumerate(need):
+            t.stats = self.stats[i]
+        self.hbm_bytes = sum(b.numel() * 4 for b in {id(t.buf): t.buf for t in tensors}.values())
+        stream = L.stream
+        slot_ptr = lambda i: None if i is None else self.slots[i].data_ptr()
+        stats_ptr = lambda t: None if t.stats is None else t.stats.data_ptr()
+        done = set()
+
+        def measure(idx):
+            """Launch closure of the measure kernel feeding slot `idx` (dynamic ranges run every forward)."""
+            qm, _, t = self.measures[idx]
+            upd = 1 if qm.update_stat else 0
+            args = (stats_ptr(t) if upd else None, 1 if t.stats_encoded else 0, N, qm.running_min.data_ptr(),
+                    qm.running_max.data_ptr(), slot_ptr(idx), int(qm.num_bits), 0, upd)
+            self.keep.append(qm)
+            return lambda: L.check(lib.dfq_measure_from_stats(*args, stream()), "dfq_measure_from_stats")
+
+        self.static_measures = []
+        if self.input.need_stats:       # per-sample extrema of the network input (utils/quantize.py:110-111)
+            in_args = (self.input.buf.data_ptr(), N, self.input.numel // N, self.input.stats.data_ptr())
+            self.ops.append(("input_stats", lambda: L.check(
+                lib.dfq_minmax_rows_f32(*in_args, stream()), "dfq_minmax_rows_f32")))
+        for st in steps:
+            for key in ("slot", "slot_a", "slot_b"):
+                idx = st.get(key)
+                if idx is None or idx in done:
+                    continue
+                done.add(idx)
+                fn = measure(idx)
+                if self.measures[idx][0].update_stat:
+                    self.ops.append((f"measure[{st['name']}]", fn))
+                else:
+                    self.static_measures.append(fn)
+            if st["kind"] == "conv":
+                m, src, out = st["m"], st["src"], st["out"]
+                kh, kw, s, p, d, g = st["geom"]
+                desc = L.DfqConvDesc()
+                wq, bq = self._params(m)
+                desc.x, desc.y, desc.w = src.buf.data_ptr(), out.buf.data_ptr(), L.dev_f32(wq, "weight")
+                desc.bias = None if bq is None else L.dev_f32(bq, "bias")
+                desc.in_slot, desc.out_stats = slot_ptr(st["slot"]), stats_ptr(out)
+                (desc.N, desc.C_in, desc.H, desc.W), (_, desc.C_out, desc.OH, desc.OW) = src.shape, out.shape
+                desc.kh, desc.kw, desc.stride, desc.pad, desc.dil, desc.groups = kh, kw, s, p, d, g
+                desc.relu, desc.bits = st["relu"], int(m.quant.num_bits) if hasattr(m, "quant") else 8
+                self.keep.append(desc)
+                self.ops.append((st["name"], self._conv_launch(desc, st)))
+            elif st["kind"] == "linear":
+                m, src, out = st["m"], st["src"], st["out"]
+                wq, bq = self._params(m)
+                args = (src.buf.data_ptr(), out.buf.data_ptr(), L.dev_f32(wq, "weight"),
+                        None if bq is None else L.dev_f32(bq, "bias"), src.shape[0], m.in_features,
+                        m.out_features, slot_ptr(st["slot"]), int(m.quant.num_bits) if hasattr(m, "quant") else 8,
+                        st["relu"], stats_ptr(out))
+                self.ops.append((st["name"], (lambda a: lambda: L.check(lib.dfq_qlinear_f32(*a, stream()),
+                                                                       "dfq_qlinear_f32"))(args)))
+            elif st["kind"] == "add":
+                a, b, out = st["a"], st["b"], st["out"]
+                args = (a.buf.data_ptr(), b.buf.data_ptr(), out.buf.data_ptr(), N, out.numel // N,
+                        slot_ptr(st["slot_a"]), slot_ptr(st["slot_b"]), int(st["bits"][0]), int(st["bits"][1]),
+                        stats_ptr(out))
+                self.ops.append((st["name"], (lambda a_: lambda: L.check(lib.dfq_qadd_f32(*a_, stream()),
+                                                                        "dfq_qadd_f32"))(args)))
+            elif st["kind"] == "mean":
+                src, out = st["src"], st["out"]
+                args = (src.buf.data_ptr(), out.buf.data_ptr(), N, src.shape[1], src.shape[2] * src.shape[3],
+                        slot_ptr(st["slot"]), int(st["bits"]), stats_ptr(out))
+                self.ops.append((st["name"], (lambda a_: lambda: L.check(lib.dfq_qmean_f32(*a_, stream()),
+                                                                        "dfq_qmean_f32"))(args)))
+        self.refresh_static()
+
+    def _params(self, m):
+        """Weight / bias the layer's forward uses.  QuantN* layers use the stored parameters (quantised offline by
+        quantize_targ_layer); Quant* layers re-quantise them on every forward (utils/quantize.py:227-231) -- the
+        parameters are constant during eval, so that is done once here."""
+        from .utils.quantize import _quant_weight, quantize
+        w, b = m.weight.data, (None if m.bias is None else m.bias.data)
+        if hasattr(m, "num_bits_bias"):
+            with torch.no_grad():
+                w = _quant_weight(w, m.num_bits)
+                b = None if b is None else quantize(b, num_bits=m.num_bits_bias)
+            self.keep += [w, b]
+        return w, b
+
+    def _conv_launch(self, desc, st):
+        lib, stream = L.lib(), L.stream
+        return lambda: L.check(lib.dfq_qconv2d_f32(ctypes.byref(desc), stream()), "dfq_qconv2d_f32")
+
+    # ------------------------------------------------------------------------------------------------- run
+    def refresh_static(self):
+        """Recompute the slots of measures with update_stat == False (call after their ranges were changed)."""
+        for fn in self.static_measures:
+            fn()
+
+    def launch(self):
+        """All launches of one forward on the current stream (inputs already in self.input.buf)."""
+        self.stats.zero_()
+        for _name, fn in self.ops:
+            fn()
+
+    def __call__(self, x):
+        self.input.buf.copy_(x, non_blocking=True)
+        self.launch()
+        return self.output.buf
+
+    def capture(self):
+        """Capture launch() into a CUDA graph; returns a callable replaying it."""
+        g = torch.cuda.CUDAGraph()
+        s = torch.cuda.Stream()
+        s.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(s):
+            self.launch()                       # warm-up outside capture
+        torch.cuda.current_stream().wait_stream(s)
+        with torch.cuda.graph(g):
+            self.launch()
+        self.graph = g
+        return g.replay

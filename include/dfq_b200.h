@@ -23,7 +23,7 @@
 extern "C" {
 #endif
 
-#define DFQ_ABI_VERSION 4
+#define DFQ_ABI_VERSION 5
 
 #if defined(__GNUC__)
 #pragma GCC visibility push(default)   /* the library is built with -fvisibility=hidden */
@@ -166,6 +166,34 @@ int dfq_measure_update(const float *x, int64_t n_samples, int64_t chw, float *ru
                        float *slot_dev, int bits, int flags, int update_stat, float *stats_scratch, void *stream);
 int dfq_fake_quant_apply_slot_f32(const float *x, float *y, void *codes, int64_t n, int bits, int flags,
                                   const float *slot_dev, void *stream);
+
+/* the same from already reduced per-sample statistics: stats = [n_samples, 2] floats (encoded == 0), or the
+ * order-preserving integer encoding {enc(max(-y)), enc(max(y))} a producing dfq_q* kernel accumulated in its
+ * epilogue (encoded != 0; the table must be zero before the producer runs). */
+int dfq_measure_from_stats(const void *stats, int encoded, int64_t n_samples, float *running_min, float *running_max,
+                           float *slot_dev, int bits, int flags, int update_stat, void *stream);
+
+/* ---- (e) quantised eval forward, CUDA-core kernels: utils/quantize.py:225-256, 336-363; residual add and mean of
+ * utils/layer_transform.py:18-32, 79-94.  Every kernel fake-quantises its input on load with the range in
+ * in_slot (4 floats {min, max, scale, 0} on the device; NULL = input used as is), fuses bias + ReLU, and, when
+ * out_stats != NULL, accumulates the per-sample min/max of its output (encoded, see dfq_measure_from_stats). */
+typedef struct DfqConvDesc {
+    const float *x;          /* [N, C_in, H, W]                                         */
+    float *y;                /* [N, C_out, OH, OW]                                      */
+    const float *w;          /* [C_out, C_in/groups, kh, kw]                            */
+    const float *bias;       /* [C_out] or NULL                                         */
+    const float *in_slot;    /* QuantMeasure range of the input or NULL                 */
+    unsigned *out_stats;     /* [N, 2] or NULL                                          */
+    int32_t N, C_in, H, W, C_out, OH, OW, kh, kw, stride, pad, dil, groups, relu, bits;
+    int32_t reserved;
+} DfqConvDesc;
+int dfq_qconv2d_f32(const DfqConvDesc *desc_host, void *stream);
+int dfq_qlinear_f32(const float *x, float *y, const float *w, const float *bias, int64_t N, int K, int O,
+                    const float *in_slot, int bits, int relu, unsigned *out_stats, void *stream);
+int dfq_qadd_f32(const float *a, const float *b, float *out, int64_t N, int64_t chw, const float *slot_a,
+                 const float *slot_b, int bits_a, int bits_b, unsigned *out_stats, void *stream);
+int dfq_qmean_f32(const float *x, float *out, int64_t N, int C, int HW, const float *slot, int bits,
+                  unsigned *out_stats, void *stream);
 
 /* ---- (b) cross-layer equalisation: Cross_layer_equal.py:63-115 ---------------------- */
 /* sorts pairs by stage (stable) and fills first_unit/n_units */

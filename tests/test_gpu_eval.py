@@ -13,6 +13,11 @@ DEV = "cuda:0"
 
 @pytest.fixture(scope="module")
 def quantised(gold_npz):
+    model, graph, targ, _ = _quantised_fresh(gold_npz)
+    return model, graph, targ
+
+
+def _quantised_fresh(gold_npz):
     """The full DFQ pipeline (main_dfq.py:188-231) with QuantN* layers, as oracle/gen_golden.py ran it."""
     from data_free_quantization_b200.bias_absorption import bias_absorption
     from data_free_quantization_b200.clip_weight import clip_weight
@@ -38,7 +43,7 @@ def quantised(gold_npz):
     quantize_targ_layer(graph, 8, 8, targ)
     set_quant_minmax(graph, bottoms, verbose=False)
     clip_weight(graph, [-15, 15], targ)
-    return model, graph, targ
+    return model, graph, targ, tr
 
 
 def test_eval_logits_match_reference(gold, gold_npz, quantised):
@@ -64,3 +69,30 @@ def test_eval_logits_match_reference(gold, gold_npz, quantised):
             lo, hi = gold["quant_minmax_after_eval"][names[key]]
             assert abs(float(m.quant.running_min) - lo) <= 1e-4 * max(1.0, abs(lo)), names[key]
             assert abs(float(m.quant.running_max) - hi) <= 1e-4 * max(1.0, abs(hi)), names[key]
+
+
+def test_eval_plan_matches_reference(gold, gold_npz):
+    """The static eval plan (own CUDA kernels for every layer, quantise-on-load, fused bias/ReLU/stats) against
+    the reference logits; and, as a CUDA graph, against itself."""
+    from data_free_quantization_b200.eval_plan import EvalPlan
+    model, graph, targ, tr = _quantised_fresh(gold_npz)
+    x = torch.randn(4, 3, 224, 224, generator=torch.Generator().manual_seed(2)).to(DEV)
+    plan = EvalPlan(model, tr, batch=4)
+    got = plan(x).cpu().numpy()
+    want = gold_npz["eval/logits_b4"]
+    err = np.abs(got - want).max() / np.abs(want).max()
+    assert err <= 1e-3, err
+    assert np.array_equal(got.argmax(1), want.argmax(1))
+    names = names_of(model)
+    for key, m in graph.items():
+        if type(m) in targ:
+            lo, hi = gold["quant_minmax_after_eval"][names[key]]
+            assert abs(float(m.quant.running_min) - lo) <= 1e-4 * max(1.0, abs(lo)), names[key]
+            assert abs(float(m.quant.running_max) - hi) <= 1e-4 * max(1.0, abs(hi)), names[key]
+    # second forward on the same input: ranges are already wide enough -> same logits; replayed from a CUDA graph
+    again = plan(x).cpu().numpy()
+    replay = plan.capture()
+    plan.input.buf.copy_(x)
+    replay()
+    torch.cuda.synchronize()
+    assert np.array_equal(plan.output.buf.cpu().numpy(), again)
