@@ -196,6 +196,7 @@ class EvalPlan:
             in_args = (self.input.buf.data_ptr(), N, self.input.numel // N, self.input.stats.data_ptr())
             self.ops.append(("input_stats", lambda: L.check(
                 lib.dfq_minmax_rows_f32(*in_args, stream()), "dfq_minmax_rows_f32")))
+        self.out_of = {st["name"]: st["out"] for st in steps}
         for st in steps:
             for key in ("slot", "slot_a", "slot_b"):
                 idx = st.get(key)
@@ -272,6 +273,17 @@ class EvalPlan:
         self.stats.zero_()
         for _name, fn in self.ops:
             fn()
+
+    def debug_run(self, x):
+        """Forward that also returns a clone of every op's output (diagnostics; buffers are reused in the plan)."""
+        self.input.buf.copy_(x)
+        self.stats.zero_()
+        outs = {}
+        for name, fn in self.ops:
+            fn()
+            if name in self.out_of:
+                outs[name] = self.out_of[name].buf.clone()
+        return outs
 
     def __call__(self, x):
         self.input.buf.copy_(x, non_blocking=True)

@@ -193,9 +193,19 @@ def main():
     if not args.skip_eval:
         g = torch.Generator().manual_seed(2)
         x = torch.randn(4, 3, 224, 224, generator=g)
+        # strided samples of the first target layers' outputs: the quantised random-init network amplifies
+        # rounding noise chaotically, so tight parity is checked near the input
+        taps, hooks = {}, []
+        for n, m in run.targets()[:6]:
+            hooks.append(m.register_forward_hook(
+                lambda mod, inp, out, n=n: taps.__setitem__(n, out.detach().clone())))
         t = time.perf_counter()
         logits = run.forward_quantized(x)
         gold["timing_s"]["eval_b4"] = time.perf_counter() - t
+        for h in hooks:
+            h.remove()
+        for n, v in taps.items():
+            small[f"eval/tap/{n}"] = v.numpy().ravel()[::SAMPLE_STRIDE]
         small["eval/logits_b4"] = logits.numpy()
         acts = {}
         for n, m in run.targets():

@@ -159,6 +159,9 @@ class RefRun:
 
     def forward_quantized(self, x):
         self.fix_bn_eps()
+        # main_dfq.py:240 calls model.eval() after the DFQ steps: the QuantMeasures that set_layer_bits created
+        # (utils/quantize.py:373, born in training mode) must be in eval mode for inference
+        self.model.eval()
         self.ns.lt.replace_op()
         try:
             with torch.no_grad():
