@@ -251,6 +251,7 @@ def eval_images_per_s(torch, case, batch, steps, warmup):
     """W8A8 eval of the quantised model on a synthetic batch (main_dfq.py:66-113 loop body, one batch per step)."""
     from data_free_quantization_b200.utils.layer_transform import replace_op, restore_op
     dev = case.dev
+    case.model.eval()                # main_dfq.py:240 (set_layer_bits' new QuantMeasures are born in training mode)
     x = torch.randn(batch, 3, 224, 224, generator=torch.Generator().manual_seed(2)).to(dev)
     replace_op()
     try:
@@ -262,6 +263,33 @@ def eval_images_per_s(torch, case, batch, steps, warmup):
     finally:
         restore_op()
     return batch * steps / (ms * 1e-3), ms / steps
+
+
+def eval_plan_images_per_s(torch, case, batch, steps, warmup):
+    """The same forward through the static eval plan (eval_plan.py: every layer a libdfq_b200 kernel, one CUDA
+    graph per batch).  The timed step includes the H2D copy of the batch from pinned host memory and the D2H read
+    of the top-1 indices (main_dfq.py:96-103)."""
+    from data_free_quantization_b200.eval_plan import EvalPlan
+    plan = EvalPlan(case.model, case.tr, batch=batch)
+    x = torch.randn(batch, 3, 224, 224, generator=torch.Generator().manual_seed(2)).pin_memory()
+    top1 = torch.empty(batch, dtype=torch.int64).pin_memory()
+    plan.input.buf.copy_(x)
+    replay = plan.capture()
+
+    def step():
+        plan.input.buf.copy_(x, non_blocking=True)
+        replay()
+        top1.copy_(plan.output.buf.argmax(1), non_blocking=True)
+
+    def dev_step():
+        replay()
+
+    for _ in range(warmup):
+        step()
+    torch.cuda.synchronize()
+    ms_dev = time_steps(torch, dev_step, steps) / steps
+    ms_e2e = time_steps(torch, step, steps) / steps
+    return ms_dev, ms_e2e, len(plan.ops), plan.hbm_bytes
 
 
 # ------------------------------------------------------------------------------------------ CPU baseline
@@ -407,10 +435,22 @@ def main():
             t = torch.tensor([ev_ms], device=dev, dtype=torch.float64)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             ev_ms = float(t[0])
-        ev = {"images_per_s": round(EVAL_BATCH * world / (ev_ms * 1e-3), 1), "batch_per_gpu": EVAL_BATCH,
-              "ms_per_batch": round(ev_ms, 3),
-              "path": "QuantMeasure/fake-quant: libdfq_b200 kernels; conv/linear arithmetic: cuDNN/cuBLAS fp32 "
-                      "(library) until the tcgen05 u8 kernels land"}
+        with quiet:
+            pl_dev, pl_e2e, pl_ops, pl_bytes = eval_plan_images_per_s(torch, case, EVAL_BATCH, max(5, args.steps // 2), 3)
+        if world > 1:
+            t = torch.tensor([pl_dev, pl_e2e], device=dev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            pl_dev, pl_e2e = t.tolist()
+        ev = {"images_per_s": round(EVAL_BATCH * world / (pl_dev * 1e-3), 1),
+              "e2e_images_per_s": round(EVAL_BATCH * world / (pl_e2e * 1e-3), 1),
+              "batch_per_gpu": EVAL_BATCH, "ms_per_batch": round(pl_dev, 3), "e2e_ms_per_batch": round(pl_e2e, 3),
+              "launches_per_batch": pl_ops, "activation_hbm_bytes": pl_bytes,
+              "path": "static eval plan: every layer a libdfq_b200 kernel (quantise-on-load, fused bias/ReLU/"
+                      "per-sample range statistics), replayed as one CUDA graph; batch-sharded across ranks",
+              "module_path": {"images_per_s": round(EVAL_BATCH * world / (ev_ms * 1e-3), 1),
+                              "ms_per_batch": round(ev_ms, 3),
+                              "path": "reference-shaped nn.Module forward: QuantMeasure on libdfq_b200 kernels, "
+                                      "conv/linear arithmetic through F.conv2d (cuDNN fp32, library)"}}
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()

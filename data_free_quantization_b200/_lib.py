@@ -43,7 +43,7 @@ class DfqCorrDesc(ctypes.Structure):
     _fields_ = [("W", c_void), ("v", c_void), ("out", c_void), ("bias", c_void), ("fold", c_void), ("O", i32),
                 ("I2", i32), ("KK", i32), ("bits", i32), ("flags", i32), ("alpha", f32), ("fold_mod", i32),
                 ("groups", i32), ("first_unit", i64),
-                ("first_block", i64), ("range_slot", i64)]
+                ("first_block", i64), ("range_slot", i64), ("first_stream", i64)]
 
 
 class DfqMergeDesc(ctypes.Structure):
@@ -64,7 +64,7 @@ class DfqConvDesc(ctypes.Structure):
 
 
 Q_SYMMETRIC, Q_RANGE_F32, Q_PER_CHANNEL, Q_CLAMP_OUT = 1, 2, 4, 8
-ABI_VERSION = 5
+ABI_VERSION = 6
 
 # every symbol include/dfq_b200.h declares: (restype, argtypes)
 P = ctypes.POINTER
@@ -104,8 +104,8 @@ PROTOTYPES = {
     "dfq_clip_multi_f32": (ctypes.c_int, [c_void, ctypes.c_int, i64, f32, f32, c_void]),
     "dfq_merge_plan_host": (ctypes.c_int, [P(DfqMergeDesc), ctypes.c_int, P(ctypes.c_int)]),
     "dfq_merge_bn_multi": (ctypes.c_int, [c_void, ctypes.c_int, ctypes.c_int, ctypes.c_int, c_void]),
-    "dfq_corr_plan_host": (ctypes.c_int, [P(DfqCorrDesc), ctypes.c_int, P(i64), P(i64)]),
-    "dfq_bias_correct": (ctypes.c_int, [c_void, ctypes.c_int, i64, i64, c_void, ctypes.c_int, c_void]),
+    "dfq_corr_plan_host": (ctypes.c_int, [P(DfqCorrDesc), ctypes.c_int, P(i64), P(i64), P(i64)]),
+    "dfq_bias_correct": (ctypes.c_int, [c_void, ctypes.c_int, i64, i64, i64, c_void, ctypes.c_int, c_void]),
     "dfq_merge_bn": (ctypes.c_int, [c_void, c_void, i64, i64, c_void, c_void, c_void, c_void, f32, c_void, c_void,
                                     c_void]),
 }

@@ -89,11 +89,13 @@ def eps_dot(layers, vectors, bits_weight=8, signed=False, alphas=None, biases=No
             d.fold, d.fold_mod = f.data_ptr(), int(fold_mods[i])
         else:
             folds.append(None)
-    tu, tb = L.i64(), L.i64()
-    L.check(L.lib().dfq_corr_plan_host(descs, n, ctypes.byref(tu), ctypes.byref(tb)), "dfq_corr_plan_host")
+    tu, tb, ts = L.i64(), L.i64(), L.i64()
+    L.check(L.lib().dfq_corr_plan_host(descs, n, ctypes.byref(tu), ctypes.byref(tb), ctypes.byref(ts)),
+            "dfq_corr_plan_host")
     table = L.table_to_device(descs, dev)
     ranges = torch.empty(n, 4, dtype=torch.float32, device=dev)
-    L.check(L.lib().dfq_bias_correct(table.data_ptr(), n, tu.value, tb.value, ranges.data_ptr(), 0, L.stream()),
+    L.check(L.lib().dfq_bias_correct(table.data_ptr(), n, tu.value, tb.value, ts.value, ranges.data_ptr(), 0,
+                                     L.stream()),
             "dfq_bias_correct")
     return (outs, folds) if fold_mods is not None else outs
 

@@ -23,7 +23,7 @@
 extern "C" {
 #endif
 
-#define DFQ_ABI_VERSION 5
+#define DFQ_ABI_VERSION 6
 
 #if defined(__GNUC__)
 #pragma GCC visibility push(default)   /* the library is built with -fvisibility=hidden */
@@ -112,6 +112,9 @@ typedef struct DfqCorrDesc {
     int64_t first_unit;  /* filled by dfq_corr_plan_host: first block of the reduction pass */
     int64_t first_block; /* filled by dfq_corr_plan_host: first block of the range pass     */
     int64_t range_slot;  /* filled by dfq_corr_plan_host: (min,max) pair in ranges_dev       */
+    int64_t first_stream;/* filled by dfq_corr_plan_host: first 16 KB chunk of the streaming reduction (long
+                            pointwise / linear rows); layers that do not qualify own zero chunks there and
+                            `first_unit` units of the generic reduction instead                            */
 } DfqCorrDesc;
 
 /* One (conv, BatchNorm) pair of merge_batchnorm (utils/layer_transform.py:255-281). */
@@ -221,11 +224,12 @@ int dfq_clip_multi_f32(const DfqClipDesc *descs_dev, int n_desc, int64_t total_b
                        void *stream);
 
 /* ---- (d) bias correction: bias_correction.py:111-144, 224-251 ---------------------- */
-int dfq_corr_plan_host(DfqCorrDesc *descs_host, int n_desc, int64_t *total_units, int64_t *total_blocks);
+int dfq_corr_plan_host(DfqCorrDesc *descs_host, int n_desc, int64_t *total_units, int64_t *total_blocks,
+                       int64_t *total_stream);
 /* ranges_dev: 4*n_desc floats, {min, max, scale, 0} per layer.  range_given != 0: the caller filled min and max
  * (4 B/elt); otherwise the call reduces them first (8 B/elt).  `out` must be non-NULL.      */
 int dfq_bias_correct(const DfqCorrDesc *descs_dev, int n_desc, int64_t total_units, int64_t total_blocks,
-                     float *ranges_dev, int range_given, void *stream);
+                     int64_t total_stream, float *ranges_dev, int range_given, void *stream);
 
 /* ---- BN folding: utils/layer_transform.py:240-285 ----------------------------------- */
 int dfq_merge_bn(float *W, float *b, int64_t O, int64_t K, const float *gamma, const float *beta,

@@ -33,7 +33,7 @@ def test_struct_sizes_match_header_layout():
     assert ctypes.sizeof(L.DfqClePair) == 80
     assert ctypes.sizeof(L.DfqCleLayer) == 32
     assert ctypes.sizeof(L.DfqAbsorbPair) == 80
-    assert ctypes.sizeof(L.DfqCorrDesc) == 96
+    assert ctypes.sizeof(L.DfqCorrDesc) == 104
 
 
 def test_host_quant_params_match_oracle(oracle):
