@@ -63,8 +63,15 @@ class DfqConvDesc(ctypes.Structure):
                     "bits", "reserved")]
 
 
+class DfqPwI8Desc(ctypes.Structure):
+    _fields_ = [("x", c_void), ("y", c_void), ("wpk", c_void), ("wr", c_void), ("bias", c_void), ("in_slot", c_void),
+                ("out_stats", c_void), ("G", i64), ("xs_n", i64), ("xs_k", i64), ("xs_p", i64), ("ys_n", i64),
+                ("ys_o", i64), ("ys_p", i64), ("P", i32), ("K", i32), ("O", i32), ("bits", i32), ("relu", i32),
+                ("s_w", f32), ("c_w", f32), ("reserved", i32)]
+
+
 Q_SYMMETRIC, Q_RANGE_F32, Q_PER_CHANNEL, Q_CLAMP_OUT = 1, 2, 4, 8
-ABI_VERSION = 6
+ABI_VERSION = 7
 
 # every symbol include/dfq_b200.h declares: (restype, argtypes)
 P = ctypes.POINTER
@@ -89,6 +96,10 @@ PROTOTYPES = {
                                     c_void, c_void]),
     "dfq_qmean_f32": (ctypes.c_int, [c_void, c_void, i64, ctypes.c_int, ctypes.c_int, c_void, ctypes.c_int, c_void,
                                      c_void]),
+    "dfq_pw_i8_plan_host": (ctypes.c_int, [ctypes.c_int, ctypes.c_int, P(ctypes.c_int), P(ctypes.c_int),
+                                           P(ctypes.c_int), P(ctypes.c_int), P(i64)]),
+    "dfq_pw_i8_pack_host": (ctypes.c_int, [c_void, ctypes.c_int, ctypes.c_int, c_void]),
+    "dfq_pw_i8": (ctypes.c_int, [P(DfqPwI8Desc), c_void]),
     "dfq_quant_plan_host": (ctypes.c_int, [P(DfqQuantDesc), ctypes.c_int, P(i64), P(i64)]),
     "dfq_fake_quant_multi_f32": (ctypes.c_int, [c_void, ctypes.c_int, i64, i64, c_void, c_void]),
     "dfq_cle_plan_host": (ctypes.c_int, [P(DfqClePair), ctypes.c_int, P(ctypes.c_int), P(ctypes.c_int)]),

@@ -1,0 +1,318 @@
+// Kernel (e), tensor-core part: pointwise (1x1) convolutions and linear layers of the quantised eval forward
+// (utils/quantize.py:225-256, 336-363) as s8 x s8 -> s32 tcgen05.mma.kind::i8 with the accumulator in TMEM.
+//
+//   x_hat[p,k] = s_x * a[p,k] + c_x      a = code(x) - 128  (code = the integer of utils/quantize.py:74, computed
+//   w_hat[o,k] = s_w * b[o,k] + c_w      b = code(w) - 128   on load with the consumer's QuantMeasure range;
+//                                        grids of fewer than 8 bits are centred and scaled up to the s8 range)
+//   y[p,o] = s_x s_w  SUM_k a b  +  s_x c_w SUM_k a[p,k]  +  c_x s_w SUM_k b[o,k]  +  K c_x c_w  +  bias[o]
+//
+// so the K-long dot products are exact 32-bit integer sums on the tensor pipe and the fp32 work is one FMA chain
+// per output.  One CTA = 128 "pixels" (GEMM M, TMEM lanes) x one pass of <= 256 output channels (GEMM N, TMEM
+// columns), K walked in 64-byte slabs through a 2-deep shared-memory ring:
+//   * the weight codes of a slab arrive by the bulk async-copy engine (cp.async.bulk, TMA without a tensor map:
+//     dfq_pw_i8_pack_host stores every slab already in the UMMA canonical K-major order) on an mbarrier;
+//   * the activation slab is read as fp32 (coalesced along the pixel axis), quantised in registers, its code sum
+//     accumulated with dp4a, and written to shared memory in the same canonical order with 16-byte stores;
+//   * one thread issues the MMAs of the slab and commits them to the ring's "free" mbarrier.
+// Epilogue: tcgen05.ld 32x32b (lane = pixel), the FMA chain above, bias, ReLU, per-sample min/max of the output
+// for the next QuantMeasure (utils/quantize.py:110-111), coalesced fp32 stores.
+#include "common.cuh"
+
+namespace dfq {
+
+constexpr int kI8M = 128;            // pixels per CTA (UMMA M)
+constexpr int kI8Slab = 64;          // K bytes per ring stage (2 MMAs of K = 32)
+constexpr int kI8ASlab = kI8M * kI8Slab;
+constexpr int kI8Spin = 1 << 22;     // bounded mbarrier spin: a protocol bug traps instead of hanging the GPU
+
+struct PwI8Args {
+    const float *x; float *y; const int8_t *wpk; const float *wr; const float *bias; const RangeSlot *slot;
+    unsigned *stats;
+    int64_t G;                        // pixels in total (images x pixels per image)
+    int64_t xs_n, xs_k, xs_p, ys_n, ys_o, ys_p;
+    int P, K, O, bits, relu;
+    int n_pass, o_per_pass, npass, slabs, tmem_cols;
+    float s_w, c_w;
+};
+
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    uint32_t ok = 0;
+    for (int spin = 0; spin < kI8Spin; ++spin) {
+        asm volatile("{\n\t.reg .pred p;\n\t"
+                     "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+                     "selp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+        if (ok) return;
+    }
+    __trap();
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void *src, uint32_t bytes, uint32_t bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+// shared-memory matrix descriptor, no swizzle, K-major: 8-row x 16-byte core matrices (128 contiguous bytes);
+// LBO = byte step between the two 16-byte K chunks of one MMA, SBO = byte step between 8-row groups
+__device__ __forceinline__ uint64_t umma_desc(uint32_t addr, uint32_t lbo, uint32_t sbo) {
+    return (uint64_t)((addr & 0x3FFFFu) >> 4) | ((uint64_t)(lbo >> 4) << 16) | ((uint64_t)(sbo >> 4) << 32) |
+           (1ull << 46);
+}
+__device__ __forceinline__ void umma_i8(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                        uint32_t accumulate) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n\t}"
+                 ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+// The integer code of utils/quantize.py:72-74 in the low byte of the result (block-uniform fast / exact paths).
+__device__ __forceinline__ uint32_t quant_code_bits(float x, const QuantConsts &c) {
+    float t = __fadd_rn(x, c.neg_min);
+    if (c.fast) {
+        float tc = fminf(fmaxf(t, c.t_lo), c.t_hi);
+        float d = div_const_rn(tc, c.scale, c.rscale);
+        float cl = fminf(fmaxf(d, c.qmin), c.qmax);
+        return __float_as_uint(__fadd_rn(cl, 12582912.0f));        // 1.5 * 2^23 + q: the mantissa's low byte is q
+    }
+    float cl = fminf(fmaxf(__fdiv_rn(t, c.scale), c.qmin), c.qmax);
+    return (uint32_t)__float2int_rn(cl);
+}
+
+__global__ void __launch_bounds__(kThreads)
+pw_i8_kernel(PwI8Args a) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    __shared__ __align__(8) uint64_t bars[4];           // full[2] (weights landed), done[2] (MMAs of the stage retired)
+    __shared__ uint32_t tmem_base_s;
+    __shared__ int colsum_s[2][kI8M];
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int pass = blockIdx.x % a.n_pass;
+    const int64_t tile = blockIdx.x / a.n_pass;
+    uint8_t *sA = smem;                                  // [2][4 K-chunks][128 rows][16 B]
+    uint8_t *sB = smem + 2 * kI8ASlab;                   // [2][4 K-chunks][npass rows][16 B]
+    const uint32_t bslab = (uint32_t)a.npass * kI8Slab;
+    const uint32_t sA_u = smem_u32(sA), sB_u = smem_u32(sB);
+    const uint32_t full0 = smem_u32(&bars[0]), done0 = smem_u32(&bars[2]);
+
+    if (tid == 0) {
+        mbar_init(full0, 1); mbar_init(full0 + 8, 1); mbar_init(done0, 1); mbar_init(done0 + 8, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
+                     ::"r"(smem_u32(&tmem_base_s)), "r"((uint32_t)a.tmem_cols) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = tmem_base_s;
+
+    // ---- this thread's pixel (GEMM row) and K half -------------------------------------------------------
+    const int r = tid & (kI8M - 1), h = tid >> 7;
+    const int64_t g = tile * kI8M + r;
+    const bool valid = g < a.G;
+    const int64_t n = valid ? g / a.P : 0;
+    const int p = valid ? (int)(g - n * a.P) : 0;
+    const float *xb = a.x + n * a.xs_n + (int64_t)p * a.xs_p;
+    const QuantConsts qc = consts_from_slot(*a.slot, a.bits, 0, 0.f, 0.f);
+    const int8_t *wsrc = a.wpk + (int64_t)pass * a.slabs * bslab;
+    // instruction descriptor: D = s32, A = B = s8, both K-major, N = npass, M = 128
+    const uint32_t idesc = (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(a.npass >> 3) << 17) |
+                           ((uint32_t)(kI8M >> 4) << 24);
+    const int sh = 8 - a.bits;                          // < 8-bit grids: a = (code - 2^(bits-1)) << sh, s_x >> sh
+    int csum = 0;
+
+    for (int s = 0; s < a.slabs; ++s) {
+        const int buf = s & 1;
+        // 1. this stage's activations: two 16-wide K chunks per thread, all loads in flight before any use
+        float v[2][16];
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+            const int k0 = s * kI8Slab + (h + 2 * c) * 16;
+#pragma unroll
+            for (int j = 0; j < 16; ++j)
+                v[c][j] = (valid && k0 + j < a.K) ? __ldg(xb + (int64_t)(k0 + j) * a.xs_k) : 0.0f;
+        }
+        // 2. the ring stage is free once the MMAs issued two slabs ago have retired
+        if (s >= 2) mbar_wait(done0 + 8 * buf, ((s >> 1) - 1) & 1);
+        if (tid == 0) {
+            mbar_expect_tx(full0 + 8 * buf, bslab);
+            bulk_g2s(sB_u + buf * bslab, wsrc + (int64_t)s * bslab, bslab, full0 + 8 * buf);
+        }
+        // 3. quantise on load (utils/quantize.py:72-74), centre to s8, pack, canonical-order store
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+            const int k0 = s * kI8Slab + (h + 2 * c) * 16;
+            uint32_t w4[4];
+#pragma unroll
+            for (int q4 = 0; q4 < 4; ++q4) {
+                uint32_t b[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const int k = k0 + 4 * q4 + j;
+                    b[j] = (valid && k < a.K) ? quant_code_bits(v[c][4 * q4 + j], qc) : (128u >> sh);
+                }
+                const uint32_t lo = __byte_perm(b[0], b[1], 0x0040), hi = __byte_perm(b[2], b[3], 0x0040);
+                w4[q4] = (__byte_perm(lo, hi, 0x5410) << sh) ^ 0x80808080u;
+                csum = __dp4a((int)w4[q4], 0x01010101, csum);
+            }
+            *reinterpret_cast<uint4 *>(sA + buf * kI8ASlab + (h + 2 * c) * (kI8M * 16) + r * 16) =
+                make_uint4(w4[0], w4[1], w4[2], w4[3]);
+        }
+        // 4. generic-proxy stores -> visible to the tensor core's async proxy, then one thread issues
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        __syncthreads();
+        if (tid == 0) {
+            mbar_wait(full0 + 8 * buf, (s >> 1) & 1);
+            tc_fence_after();
+#pragma unroll
+            for (int kk = 0; kk < 2; ++kk) {
+                const uint64_t ad = umma_desc(sA_u + buf * kI8ASlab + kk * 2 * (kI8M * 16), kI8M * 16, 128);
+                const uint64_t bd = umma_desc(sB_u + buf * bslab + kk * 2 * (a.npass * 16), a.npass * 16, 128);
+                umma_i8(tmem, ad, bd, idesc, (s | kk) != 0);
+            }
+            umma_commit(done0 + 8 * buf);
+        }
+    }
+    colsum_s[h][r] = csum;
+    {   // MMAs retire in order: the last stage's barrier covers the whole accumulation
+        const int last = a.slabs - 1;
+        mbar_wait(done0 + 8 * (last & 1), (last >> 1) & 1);
+    }
+    tc_fence_after();
+    __syncthreads();
+
+    // ---- epilogue: warp w reads TMEM lanes 32*(w%4).., 16-column chunks w/4, w/4+2, ... ---------------------
+    const int er = (warp & 3) * 32 + lane;
+    const int64_t eg = tile * kI8M + er;
+    const bool ev = eg < a.G;
+    const int64_t en = ev ? eg / a.P : 0;
+    const int ep = ev ? (int)(eg - en * a.P) : 0;
+    float *yb = a.y + en * a.ys_n + (int64_t)ep * a.ys_p;
+    const float sx = __fmul_rn(qc.scale, 1.0f / (float)(1 << sh));
+    const float cx = __fmaf_rn(128.0f, sx, qc.add_back);
+    const float fa = __fmul_rn(sx, a.s_w);
+    const float row_c = __fmaf_rn(__fmul_rn(sx, a.c_w), (float)(colsum_s[0][er] + colsum_s[1][er]),
+                                  __fmul_rn(__fmul_rn((float)a.K, a.c_w), cx));
+    const int o0 = pass * a.o_per_pass, o_end = min(a.O, o0 + a.o_per_pass);
+    float lo = INFINITY, hi = -INFINITY;
+    for (int chunk = warp >> 2; chunk * 16 < a.npass; chunk += 2) {
+        const int oc = o0 + chunk * 16;
+        if (oc >= o_end) break;                                   // warp-uniform
+        uint32_t d[16];
+        asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, "
+                     "%13, %14, %15}, [%16];"
+                     : "=r"(d[0]), "=r"(d[1]), "=r"(d[2]), "=r"(d[3]), "=r"(d[4]), "=r"(d[5]), "=r"(d[6]), "=r"(d[7]),
+                       "=r"(d[8]), "=r"(d[9]), "=r"(d[10]), "=r"(d[11]), "=r"(d[12]), "=r"(d[13]), "=r"(d[14]),
+                       "=r"(d[15])
+                     : "r"(tmem + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)(chunk * 16)));
+        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+            const int o = oc + j;
+            if (o < o_end) {
+                float yv = __fmaf_rn(fa, (float)(int)d[j], __fmaf_rn(cx, __ldg(a.wr + o), row_c));
+                if (a.bias) yv = __fadd_rn(yv, __ldg(a.bias + o));
+                if (a.relu) yv = fmaxf(yv, 0.0f);
+                if (ev) {
+                    yb[(int64_t)o * a.ys_o] = yv;
+                    lo = fminf(lo, yv); hi = fmaxf(hi, yv);
+                }
+            }
+        }
+    }
+    if (a.stats) {                                                // per-sample extrema, encoded (common.cuh)
+        const int64_t n0 = __shfl_sync(0xffffffffu, en, 0);
+        const bool uni = __all_sync(0xffffffffu, ev && en == n0);
+        if (uni) {
+            lo = warp_min(lo); hi = warp_max(hi);
+            if (lane == 0 && hi >= lo) {
+                atomicMax(a.stats + 2 * en, enc_ordered(-lo));
+                atomicMax(a.stats + 2 * en + 1, enc_ordered(hi));
+            }
+        } else if (ev && hi >= lo) {
+            atomicMax(a.stats + 2 * en, enc_ordered(-lo));
+            atomicMax(a.stats + 2 * en + 1, enc_ordered(hi));
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0)
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"((uint32_t)a.tmem_cols)
+                     : "memory");
+}
+
+}  // namespace dfq
+
+using namespace dfq;
+
+// Split of the output channels into passes of <= 256 (one UMMA N each, padded to a multiple of 16) and the K
+// padding to whole 64-byte slabs.  packed_bytes = n_pass * slabs * npass * 64.
+extern "C" int dfq_pw_i8_plan_host(int O, int K, int *n_pass, int *o_per_pass, int *npass, int *slabs,
+                                   int64_t *packed_bytes) {
+    if (O <= 0 || K <= 0) return (int)cudaErrorInvalidValue;
+    int np = (O + 255) / 256;
+    int opp = ((O + np - 1) / np + 15) / 16 * 16;
+    np = (O + opp - 1) / opp;
+    *n_pass = np; *o_per_pass = opp; *npass = opp;
+    *slabs = (K + kI8Slab - 1) / kI8Slab;
+    *packed_bytes = (int64_t)np * *slabs * opp * kI8Slab;
+    return 0;
+}
+
+// codes: [O, K] centred weight codes (code - 128) on the host.  packed: the layout the kernel's bulk copies read,
+// [pass][slab][K chunk of 16][row within pass][16 B], zero padded (a zero code adds nothing to the dot product).
+extern "C" int dfq_pw_i8_pack_host(const int8_t *codes, int O, int K, int8_t *packed) {
+    int np, opp, npass, slabs; int64_t bytes;
+    int e = dfq_pw_i8_plan_host(O, K, &np, &opp, &npass, &slabs, &bytes);
+    if (e) return e;
+    for (int64_t i = 0; i < bytes; ++i) packed[i] = 0;
+    for (int o = 0; o < O; ++o) {
+        const int pass = o / opp, ol = o - pass * opp;
+        for (int k = 0; k < K; ++k) {
+            const int slab = k / kI8Slab, kc = (k % kI8Slab) / 16, kb = k % 16;
+            packed[((((int64_t)pass * slabs + slab) * 4 + kc) * npass + ol) * 16 + kb] = codes[(int64_t)o * K + k];
+        }
+    }
+    return 0;
+}
+
+extern "C" int dfq_pw_i8(const DfqPwI8Desc *d, void *stream) {
+    if (!d || !d->x || !d->y || !d->wpk || !d->wr || !d->in_slot || d->G <= 0 || d->bits < 1 || d->bits > 8)
+        return (int)cudaErrorInvalidValue;
+    PwI8Args a;
+    int64_t bytes;
+    int e = dfq_pw_i8_plan_host(d->O, d->K, &a.n_pass, &a.o_per_pass, &a.npass, &a.slabs, &bytes);
+    if (e) return e;
+    a.x = d->x; a.y = d->y; a.wpk = d->wpk; a.wr = d->wr; a.bias = d->bias; a.slot = (const RangeSlot *)d->in_slot;
+    a.stats = d->out_stats; a.G = d->G;
+    a.xs_n = d->xs_n; a.xs_k = d->xs_k; a.xs_p = d->xs_p; a.ys_n = d->ys_n; a.ys_o = d->ys_o; a.ys_p = d->ys_p;
+    a.P = d->P; a.K = d->K; a.O = d->O; a.bits = d->bits; a.relu = d->relu;
+    a.s_w = d->s_w; a.c_w = d->c_w;
+    a.tmem_cols = 32;
+    while (a.tmem_cols < a.npass) a.tmem_cols *= 2;
+    const size_t smem = 2 * (size_t)kI8ASlab + 2 * (size_t)a.npass * kI8Slab;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t ce = cudaFuncSetAttribute(pw_i8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+        if (ce != cudaSuccess) return (int)ce;
+        attr_set = true;
+    }
+    const int64_t tiles = (d->G + kI8M - 1) / kI8M;
+    if (tiles * a.n_pass > 0x7fffffffll) return (int)cudaErrorInvalidValue;
+    pw_i8_kernel<<<(unsigned)(tiles * a.n_pass), kThreads, smem, (cudaStream_t)stream>>>(a);
+    g_launches += 1;
+    return (int)cudaGetLastError();
+}

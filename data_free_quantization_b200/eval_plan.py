@@ -45,7 +45,9 @@ class _T:
 
 
 class EvalPlan:
-    def __init__(self, model, transformer, batch, in_shape=(3, 224, 224), pw_impl="fp32"):
+    def __init__(self, model, transformer, batch, in_shape=(3, 224, 224), pw_impl="i8"):
+        """pw_impl: "i8" = pointwise convs / linear layers on the tcgen05 s8 kernel (csrc/pw_i8.cu) wherever the
+        layer's weights sit on an integer grid of <= 8 bits, "fp32" = the CUDA-core comparator everywhere."""
         self.model, self.fxg = model, transformer.fx_graph
         self.dev = next(model.parameters()).device
         self.N = int(batch)
@@ -53,6 +55,7 @@ class EvalPlan:
         self.ops = []                # (name, callable)
         self.measures = []           # (qm, slot index, input tensor)
         self.keep = []               # ctypes objects / tensors that must outlive the plan
+        self.i8_layers = []          # layers running on the tensor-core kernel
         self._build(in_shape)
 
     # ------------------------------------------------------------------------------------------------ build
@@ -197,6 +200,15 @@ class EvalPlan:
             self.ops.append(("input_stats", lambda: L.check(
                 lib.dfq_minmax_rows_f32(*in_args, stream()), "dfq_minmax_rows_f32")))
         self.out_of = {st["name"]: st["out"] for st in steps}
+        self.op_info = {}
+        for st in steps:
+            kind = st["kind"]
+            if kind == "conv":
+                kh, _, _, _, _, g = st["geom"]
+                kind = "pw" if (kh == 1 and g == 1) else ("dw" if g > 1 else "dense")
+            ins = [st[k] for k in ("src", "a", "b") if k in st]
+            self.op_info[st["name"]] = {"kind": kind, "bytes": 4 * (sum(t.numel for t in ins) + st["out"].numel),
+                                        "shape": tuple(ins[0].shape[1:]) + ("->",) + tuple(st["out"].shape[1:])}
         for st in steps:
             for key in ("slot", "slot_a", "slot_b"):
                 idx = st.get(key)
@@ -220,7 +232,11 @@ class EvalPlan:
                 desc.kh, desc.kw, desc.stride, desc.pad, desc.dil, desc.groups = kh, kw, s, p, d, g
                 desc.relu, desc.bits = st["relu"], int(m.quant.num_bits) if hasattr(m, "quant") else 8
                 self.keep.append(desc)
-                self.ops.append((st["name"], self._conv_launch(desc, st)))
+                i8 = None
+                if (self.pw_impl == "i8" and kh == 1 and kw == 1 and g == 1 and s == 1 and p == 0
+                        and st["slot"] is not None):
+                    i8 = self._i8_launch(m, wq, bq, src, out, st, N, src.shape[2] * src.shape[3], linear=False)
+                self.ops.append((st["name"], i8 or self._conv_launch(desc, st)))
             elif st["kind"] == "linear":
                 m, src, out = st["m"], st["src"], st["out"]
                 wq, bq = self._params(m)
@@ -228,8 +244,11 @@ class EvalPlan:
                         None if bq is None else L.dev_f32(bq, "bias"), src.shape[0], m.in_features,
                         m.out_features, slot_ptr(st["slot"]), int(m.quant.num_bits) if hasattr(m, "quant") else 8,
                         st["relu"], stats_ptr(out))
-                self.ops.append((st["name"], (lambda a: lambda: L.check(lib.dfq_qlinear_f32(*a, stream()),
-                                                                       "dfq_qlinear_f32"))(args)))
+                i8 = None
+                if self.pw_impl == "i8" and st["slot"] is not None:
+                    i8 = self._i8_launch(m, wq, bq, src, out, st, src.shape[0], 1, linear=True)
+                self.ops.append((st["name"], i8 or (lambda a: lambda: L.check(lib.dfq_qlinear_f32(*a, stream()),
+                                                                             "dfq_qlinear_f32"))(args)))
             elif st["kind"] == "add":
                 a, b, out = st["a"], st["b"], st["out"]
                 args = (a.buf.data_ptr(), b.buf.data_ptr(), out.buf.data_ptr(), N, out.numel // N,
@@ -257,6 +276,19 @@ class EvalPlan:
                 b = None if b is None else quantize(b, num_bits=m.num_bits_bias)
             self.keep += [w, b]
         return w, b
+
+    def _i8_launch(self, m, wq, bq, src, out, st, images, P, linear):
+        """Launch closure of the tensor-core kernel for this layer, or None when its weights are not on a grid."""
+        from . import pw_i8
+        pk = pw_i8.pack_weight(wq, getattr(m, "num_bits", None))
+        if pk is None:
+            return None
+        stats = None if out.stats is None else out.stats.data_ptr()
+        desc = pw_i8.make_desc(src.buf.data_ptr(), out.buf.data_ptr(), pk, bq, self.slots[st["slot"]].data_ptr(),
+                               stats, images, P, st["relu"], int(m.quant.num_bits), linear=linear)
+        self.keep += [pk, desc]
+        self.i8_layers.append(st["name"])
+        return lambda: pw_i8.launch(desc)
 
     def _conv_launch(self, desc, st):
         lib, stream = L.lib(), L.stream

@@ -1,0 +1,84 @@
+"""Host side of the tensor-core pointwise / linear kernel (csrc/pw_i8.cu, dfq_pw_i8): weight-code recovery and
+packing at plan time, and the launch wrapper.  The arithmetic it replaces is F.conv2d / F.linear on fake-quantised
+tensors in QuantNConv2d.forward / QuantNLinear.forward (utils/quantize.py:250-256, 358-363)."""
+import ctypes
+
+import numpy as np
+import torch
+
+from . import _lib as L
+
+
+class PackedWeight:
+    """Weights of one layer on an integer grid: w[o,k] = s_w * code[o,k] + min_w, code in [0, 2^bits - 1]."""
+
+    def __init__(self, wpk, wr, s_w, c_w, O, K, codes):
+        self.wpk, self.wr, self.s_w, self.c_w, self.O, self.K, self.codes = wpk, wr, s_w, c_w, O, K, codes
+
+
+def pack_weight(w, bits=None):
+    """pack_weight_bits for the layer's weight width, or -- QuantN* layers do not record one -- for the widest grid
+    of <= 8 bits the tensor sits on."""
+    for b in ([bits] if bits else (8, 7, 6, 5, 4, 3, 2)):
+        pk = pack_weight_bits(w, int(b))
+        if pk is not None:
+            return pk
+    return None
+
+
+def pack_weight_bits(w, bits=8):
+    """Recover the integer codes of an already fake-quantised weight (what quantize_targ_layer stored,
+    utils/layer_transform.py:288-305, or what QuantConv2d derives per forward, utils/quantize.py:227) and lay them
+    out for the kernel.  Returns None when the tensor is not on a `bits`-bit grid (then the fp32 kernel applies)."""
+    if not (1 <= bits <= 8) or not w.is_cuda:
+        return None
+    O = w.shape[0]
+    w2 = w.detach().reshape(O, -1)
+    K = w2.shape[1]
+    lo, hi = float(w2.min()), float(w2.max())
+    levels = float(2 ** bits - 1)
+    s = max((hi - lo) / levels, 1e-8)
+    s32 = float(np.float32(s))
+    q = torch.round((w2.double() - lo) / s32).clamp_(0, levels)
+    back = q * s32 + lo
+    tol = 4 * 1.2e-7 * max(abs(lo), abs(hi)) + 1e-7 * (hi - lo)
+    if float((back - w2.double()).abs().max()) > tol:
+        return None
+    # centred and scaled to the s8 range: b = (code - 2^(bits-1)) * 2^(8-bits), w = (s / 2^(8-bits)) * b + c_w
+    up = 2 ** (8 - bits)
+    codes = ((q - 2 ** (bits - 1)) * up).to(torch.int8).cpu().numpy()
+    n_pass, opp, npass, slabs, nbytes = (ctypes.c_int(), ctypes.c_int(), ctypes.c_int(), ctypes.c_int(), L.i64())
+    lib = L.lib()
+    L.check(lib.dfq_pw_i8_plan_host(O, K, ctypes.byref(n_pass), ctypes.byref(opp), ctypes.byref(npass),
+                                    ctypes.byref(slabs), ctypes.byref(nbytes)), "dfq_pw_i8_plan_host")
+    packed = np.empty(nbytes.value, dtype=np.int8)
+    codes = np.ascontiguousarray(codes)
+    L.check(lib.dfq_pw_i8_pack_host(codes.ctypes.data, O, K, packed.ctypes.data), "dfq_pw_i8_pack_host")
+    s_eff = s32 / up
+    wr = (codes.astype(np.int64).sum(1).astype(np.float64) * s_eff).astype(np.float32)
+    dev = w.device
+    pk = PackedWeight(torch.from_numpy(packed).to(dev), torch.from_numpy(wr).to(dev), s_eff,
+                      float(np.float32(lo + 2 ** (bits - 1) * s32)), O, K, codes)
+    pk.grid = (s32, lo, q.to(torch.int16).cpu().numpy())       # w = s * code + lo, code in [0, 2^bits - 1]
+    return pk
+
+
+def make_desc(x_ptr, y_ptr, pk, bias, slot_ptr, stats_ptr, images, P, relu, bits, linear=False):
+    """DfqPwI8Desc for a conv ([images, K, P] -> [images, O, P]) or a linear layer ([images, K] -> [images, O])."""
+    d = L.DfqPwI8Desc()
+    d.x, d.y, d.wpk, d.wr = x_ptr, y_ptr, pk.wpk.data_ptr(), pk.wr.data_ptr()
+    d.bias = None if bias is None else L.dev_f32(bias, "bias")
+    d.in_slot, d.out_stats = slot_ptr, stats_ptr
+    d.K, d.O, d.bits, d.relu = pk.K, pk.O, int(bits), int(relu)
+    d.s_w, d.c_w = pk.s_w, pk.c_w
+    if linear:
+        d.G, d.P = images, 1
+        d.xs_n, d.xs_k, d.xs_p, d.ys_n, d.ys_o, d.ys_p = pk.K, 1, 0, pk.O, 1, 0
+    else:
+        d.G, d.P = images * P, P
+        d.xs_n, d.xs_k, d.xs_p, d.ys_n, d.ys_o, d.ys_p = pk.K * P, P, 1, pk.O * P, P, 1
+    return d
+
+
+def launch(desc):
+    L.check(L.lib().dfq_pw_i8(ctypes.byref(desc), L.stream()), "dfq_pw_i8")

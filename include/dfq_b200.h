@@ -23,7 +23,7 @@
 extern "C" {
 #endif
 
-#define DFQ_ABI_VERSION 6
+#define DFQ_ABI_VERSION 7
 
 #if defined(__GNUC__)
 #pragma GCC visibility push(default)   /* the library is built with -fvisibility=hidden */
@@ -197,6 +197,30 @@ int dfq_qadd_f32(const float *a, const float *b, float *out, int64_t N, int64_t 
                  const float *slot_b, int bits_a, int bits_b, unsigned *out_stats, void *stream);
 int dfq_qmean_f32(const float *x, float *out, int64_t N, int C, int HW, const float *slot, int bits,
                   unsigned *out_stats, void *stream);
+
+/* Tensor-core form of a pointwise (1x1, stride 1) convolution or a linear layer of the same forward
+ * (utils/quantize.py:250-256, 358-363): s8 x s8 -> s32 tcgen05.mma.kind::i8, accumulator in TMEM.
+ * Needs the weights on an integer grid of <= 8 bits: w[o,k] = s_w * code + min_w (what quantize_targ_layer
+ * leaves, or what QuantConv2d re-derives every forward).  A "pixel" g = n * P + p is one GEMM row; element
+ * (g, k) of the input is x[n*xs_n + k*xs_k + p*xs_p], output (g, o) is y[n*ys_n + o*ys_o + p*ys_p] (conv:
+ * P = H*W, xs_k = ys_o = P, xs_p = ys_p = 1; linear: P = 1, xs_n = K, xs_k = 1, ys_n = O, ys_o = 1). */
+typedef struct DfqPwI8Desc {
+    const float *x;
+    float *y;
+    const int8_t *wpk;       /* device copy of dfq_pw_i8_pack_host's output (code - 128, slab-major) */
+    const float *wr;         /* [O] s_w * sum_k (code[o,k] - 128)                              */
+    const float *bias;       /* [O] or NULL                                                    */
+    const float *in_slot;    /* QuantMeasure range of the input {min, max, scale, 0}; required */
+    unsigned *out_stats;     /* [samples, 2] encoded per-sample extrema of y, or NULL          */
+    int64_t G;               /* pixels in total                                                */
+    int64_t xs_n, xs_k, xs_p, ys_n, ys_o, ys_p;   /* element strides                          */
+    int32_t P, K, O, bits, relu;
+    float s_w, c_w;          /* weight scale and centred offset min_w + 128 * s_w             */
+    int32_t reserved;
+} DfqPwI8Desc;
+int dfq_pw_i8_plan_host(int O, int K, int *n_pass, int *o_per_pass, int *npass, int *slabs, int64_t *packed_bytes);
+int dfq_pw_i8_pack_host(const int8_t *codes_host, int O, int K, int8_t *packed_host);
+int dfq_pw_i8(const DfqPwI8Desc *desc_host, void *stream);
 
 /* ---- (b) cross-layer equalisation: Cross_layer_equal.py:63-115 ---------------------- */
 /* sorts pairs by stage (stable) and fills first_unit/n_units */
