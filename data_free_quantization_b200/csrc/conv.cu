@@ -88,6 +88,129 @@ dwconv3x3_kernel(ConvArgs a) {
 }
 
 // ---------------------------------------------------------------------------------------------------------
+// Depthwise 3x3, pad 1, dilation 1, stride 1 or 2 (every depthwise layer of MobileNetV2): the streaming form.
+// A block owns either a strip of output rows of ONE channel plane or `cb` whole planes of consecutive channels, so
+// its input is one contiguous run of floats: it is read with 128-bit loads, quantised once and written to a
+// zero-initialised shared tile whose rows are [3 unused | left pad | W values | right pad ...] (the interior
+// starts on a 16-byte boundary).  A thread then produces 4 adjacent outputs of one row from 3 x (1 scalar + 1 or
+// 2 vector) shared loads with the 9 weights in registers, and stores them as one 128-bit word.
+// Index decoding uses float reciprocals (exact here: every quotient is < 2^12 and the numerators are offset by
+// one half).
+struct DwArgs {
+    const float *x; float *y; const float *w; const float *bias; const RangeSlot *slot; unsigned *stats;
+    int C, H, W, OH, OW, stride, relu, bits;
+    int cb, rows, strips, RS, G4;
+    float inv_W, inv_W4, inv_G4;
+};
+
+__device__ __forceinline__ int fdiv_small(int x, float inv) { return (int)(((float)x + 0.5f) * inv); }
+
+template <bool kVec>
+__global__ void __launch_bounds__(kThreads)
+dwconv3x3_stream_kernel(DwArgs a) {
+    extern __shared__ __align__(16) float smem[];
+    __shared__ float red[2 * kWarps];
+    const int tid = threadIdx.x;
+    int b = blockIdx.x;
+    const int strip = b % a.strips; b /= a.strips;
+    const int cgroups = (a.C + a.cb - 1) / a.cb;
+    const int cg = b % cgroups;
+    const int n = b / cgroups;
+    const int c0 = cg * a.cb, nc = min(a.cb, a.C - c0);
+    const int r0 = strip * a.rows, nr = min(a.rows, a.OH - r0);
+    const int in_r0 = r0 * a.stride - 1;
+    const int in_rows = (nr - 1) * a.stride + 3;
+    const int gr0 = max(in_r0, 0), gr1 = min(in_r0 + in_rows, a.H);     // rows that exist
+    const int plane = in_rows * a.RS;
+    const bool on = a.slot != nullptr;
+    QuantConsts qc;
+    if (on) qc = consts_from_slot(*a.slot, a.bits, 0, 0.f, 0.f);
+    // ---- zero the tile (pads, halo rows beyond the image, slack)
+    const int tile4 = (nc * plane + 4 + 3) >> 2;
+    for (int i = tid; i < tile4; i += kThreads) reinterpret_cast<float4 *>(smem)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    __syncthreads();
+    // ---- stage: one contiguous run of nc * Lc floats
+    const int Lc = (gr1 - gr0) * a.W;
+    const float *src = a.x + (((int64_t)n * a.C + c0) * a.H + gr0) * a.W;
+    const int row_shift = gr0 - in_r0;
+    if (kVec) {                                   // W % 4 == 0: a 128-bit word never leaves its row
+        const int W4 = a.W >> 2, Lc4 = Lc >> 2;
+        const float inv_Lc4 = 1.0f / (float)Lc4;
+        const float4 *src4 = reinterpret_cast<const float4 *>(src);
+        for (int i = tid; i < nc * Lc4; i += kThreads) {
+            float4 v = __ldg(src4 + i);
+            int c = 0, rem = i;
+            if (nc > 1) { c = fdiv_small(i, inv_Lc4); rem = i - c * Lc4; }
+            const int rr = fdiv_small(rem, a.inv_W4), c4 = rem - rr * W4;
+            float4 o;
+            o.x = quant_or_pass(v.x, qc, on); o.y = quant_or_pass(v.y, qc, on);
+            o.z = quant_or_pass(v.z, qc, on); o.w = quant_or_pass(v.w, qc, on);
+            *reinterpret_cast<float4 *>(smem + c * plane + (rr + row_shift) * a.RS + 4 + 4 * c4) = o;
+        }
+    } else {
+        const float inv_Lc = 1.0f / (float)Lc;
+        for (int i = tid; i < nc * Lc; i += kThreads) {
+            float v = __ldg(src + i);
+            int c = 0, rem = i;
+            if (nc > 1) { c = fdiv_small(i, inv_Lc); rem = i - c * Lc; }
+            const int rr = fdiv_small(rem, a.inv_W), col = rem - rr * a.W;
+            smem[c * plane + (rr + row_shift) * a.RS + 4 + col] = quant_or_pass(v, qc, on);
+        }
+    }
+    __syncthreads();
+    // ---- compute: item = (channel, output row, group of 4 output columns)
+    float lo = INFINITY, hi = -INFINITY;
+    const int per_c = nr * a.G4;
+    const float inv_per_c = 1.0f / (float)per_c;
+    for (int it = tid; it < nc * per_c; it += kThreads) {
+        int c = 0, rem = it;
+        if (nc > 1) { c = fdiv_small(it, inv_per_c); rem = it - c * per_c; }
+        const int orow = fdiv_small(rem, a.inv_G4), ox0 = (rem - orow * a.G4) * 4;
+        const float *wp = a.w + (int64_t)(c0 + c) * 9;
+        float acc[4] = {0.f, 0.f, 0.f, 0.f};
+        const float *srow = smem + c * plane + (orow * a.stride) * a.RS;
+#pragma unroll
+        for (int i = 0; i < 3; ++i) {
+            const float w0 = __ldg(wp + 3 * i), w1 = __ldg(wp + 3 * i + 1), w2 = __ldg(wp + 3 * i + 2);
+            const float *s = srow + i * a.RS;
+            if (a.stride == 1) {
+                const float L = s[ox0 + 3], R = s[ox0 + 8];
+                const float4 M = *reinterpret_cast<const float4 *>(s + ox0 + 4);
+                acc[0] = __fmaf_rn(M.y, w2, __fmaf_rn(M.x, w1, __fmaf_rn(L, w0, acc[0])));
+                acc[1] = __fmaf_rn(M.z, w2, __fmaf_rn(M.y, w1, __fmaf_rn(M.x, w0, acc[1])));
+                acc[2] = __fmaf_rn(M.w, w2, __fmaf_rn(M.z, w1, __fmaf_rn(M.y, w0, acc[2])));
+                acc[3] = __fmaf_rn(R, w2, __fmaf_rn(M.w, w1, __fmaf_rn(M.z, w0, acc[3])));
+            } else {
+                const float L = s[2 * ox0 + 3];
+                const float4 M0 = *reinterpret_cast<const float4 *>(s + 2 * ox0 + 4);
+                const float4 M1 = *reinterpret_cast<const float4 *>(s + 2 * ox0 + 8);
+                acc[0] = __fmaf_rn(M0.y, w2, __fmaf_rn(M0.x, w1, __fmaf_rn(L, w0, acc[0])));
+                acc[1] = __fmaf_rn(M0.w, w2, __fmaf_rn(M0.z, w1, __fmaf_rn(M0.y, w0, acc[1])));
+                acc[2] = __fmaf_rn(M1.y, w2, __fmaf_rn(M1.x, w1, __fmaf_rn(M0.w, w0, acc[2])));
+                acc[3] = __fmaf_rn(M1.w, w2, __fmaf_rn(M1.z, w1, __fmaf_rn(M1.y, w0, acc[3])));
+            }
+        }
+        const float bv = a.bias ? __ldg(a.bias + c0 + c) : 0.0f;
+        float *yp = a.y + (((int64_t)n * a.C + c0 + c) * a.OH + r0 + orow) * a.OW + ox0;
+#pragma unroll
+        for (int t = 0; t < 4; ++t) {
+            if (a.bias) acc[t] = __fadd_rn(acc[t], bv);
+            if (a.relu) acc[t] = fmaxf(acc[t], 0.0f);
+        }
+        if ((a.OW & 3) == 0) {
+            *reinterpret_cast<float4 *>(yp) = make_float4(acc[0], acc[1], acc[2], acc[3]);
+            lo = fminf(lo, fminf(fminf(acc[0], acc[1]), fminf(acc[2], acc[3])));
+            hi = fmaxf(hi, fmaxf(fmaxf(acc[0], acc[1]), fmaxf(acc[2], acc[3])));
+        } else {
+#pragma unroll
+            for (int t = 0; t < 4; ++t)
+                if (ox0 + t < a.OW) { yp[t] = acc[t]; lo = fminf(lo, acc[t]); hi = fmaxf(hi, acc[t]); }
+        }
+    }
+    if (a.stats) stats_flush(a.stats, n, lo, hi, red);
+}
+
+// ---------------------------------------------------------------------------------------------------------
 // Dense kxk convolution, direct form, for small C*kh*kw (MobileNetV2's first layer: 3 -> 32, 3x3, stride 2).
 // A block owns `rows` output rows of one image for all O output channels: the quantised, zero-padded input strip
 // and the whole weight tensor sit in shared memory; a thread owns one output pixel and walks the output channels
@@ -323,6 +446,31 @@ extern "C" int dfq_qconv2d_f32(const DfqConvDesc *d, void *stream) {
     a.N = d->N; a.C = d->C_in; a.H = d->H; a.W = d->W; a.O = d->C_out; a.OH = OH; a.OW = OW;
     a.stride = d->stride; a.pad = d->pad; a.dil = d->dil; a.relu = d->relu; a.bits = d->bits; a.kh = d->kh; a.kw = d->kw;
     const int pw = d->W + 2 * d->pad;
+    if (d->groups == d->C_in && d->C_in == d->C_out && d->kh == 3 && d->kw == 3 && d->pad == 1 && d->dil == 1 &&
+        (d->stride == 1 || d->stride == 2)) {
+        DwArgs w;
+        w.x = d->x; w.y = d->y; w.w = d->w; w.bias = d->bias; w.slot = (const RangeSlot *)d->in_slot; w.stats = d->out_stats;
+        w.C = d->C_in; w.H = d->H; w.W = d->W; w.OH = OH; w.OW = OW; w.stride = d->stride; w.relu = d->relu; w.bits = d->bits;
+        w.RS = (d->W + 5 + 3) / 4 * 4;
+        w.G4 = (OW + 3) / 4;
+        auto tile_bytes = [&](int rows, int cb) {
+            return ((size_t)cb * ((rows - 1) * d->stride + 3) * w.RS + 8) * sizeof(float);
+        };
+        // a strip of one plane (about 512 four-output items) or, for small planes, several whole planes
+        int rows = OH, cb = 1;
+        if (OH * w.G4 > 768) rows = max(1, 512 / w.G4);
+        else cb = max(1, min(d->C_in, 512 / (OH * w.G4)));
+        while (tile_bytes(rows, cb) > 40 * 1024 && (cb > 1 || rows > 1)) { if (cb > 1) cb = (cb + 1) / 2; else rows = (rows + 1) / 2; }
+        // whole planes of several channels must start on a 16-byte boundary for the vector path
+        const bool vec = (d->W % 4) == 0 && ((uintptr_t)d->x % 16) == 0;
+        w.rows = rows; w.cb = cb; w.strips = (OH + rows - 1) / rows;
+        w.inv_W = 1.0f / (float)d->W; w.inv_W4 = 4.0f / (float)d->W; w.inv_G4 = 1.0f / (float)w.G4;
+        const int blocks = d->N * ((d->C_in + cb - 1) / cb) * w.strips;
+        if (vec) dwconv3x3_stream_kernel<true><<<(unsigned)blocks, kThreads, tile_bytes(rows, cb), st>>>(w);
+        else dwconv3x3_stream_kernel<false><<<(unsigned)blocks, kThreads, tile_bytes(rows, cb), st>>>(w);
+        g_launches += 1;
+        return (int)cudaGetLastError();
+    }
     if (d->groups == d->C_in && d->C_in == d->C_out && d->kh == 3 && d->kw == 3) {
         // strip height: about 2048 outputs per block; small planes take several channels per block
         int rows = OH, cb = 1;
