@@ -95,6 +95,7 @@ pw_i8_kernel(PwI8Args a) {
     __shared__ __align__(8) uint64_t bars[4];           // full[2] (weights landed), done[2] (MMAs of the stage retired)
     __shared__ uint32_t tmem_base_s;
     __shared__ int colsum_s[2][kI8M];
+    __shared__ __align__(16) float chan_c[256];          // per output channel of this pass: c_x*wr[o] + K c_x c_w + bias[o]
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int pass = blockIdx.x % a.n_pass;
@@ -114,6 +115,20 @@ pw_i8_kernel(PwI8Args a) {
                      ::"r"(smem_u32(&tmem_base_s)), "r"((uint32_t)a.tmem_cols) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
+    const QuantConsts qc = consts_from_slot(*a.slot, a.bits, 0, 0.f, 0.f);
+    const int sh = 8 - a.bits;                          // < 8-bit grids: a = (code - 2^(bits-1)) << sh, s_x >> sh
+    const float sx = __fmul_rn(qc.scale, 1.0f / (float)(1 << sh));
+    const float cx = __fmaf_rn(128.0f, sx, qc.add_back);
+    const int o0 = pass * a.o_per_pass, o_end = min(a.O, o0 + a.o_per_pass);
+    if (tid < a.npass) {
+        const int o = o0 + tid;
+        float c = 0.0f;
+        if (o < o_end) {
+            c = __fmaf_rn(cx, __ldg(a.wr + o), __fmul_rn(__fmul_rn((float)a.K, a.c_w), cx));
+            if (a.bias) c = __fadd_rn(c, __ldg(a.bias + o));
+        }
+        chan_c[tid] = c;
+    }
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
@@ -126,12 +141,11 @@ pw_i8_kernel(PwI8Args a) {
     const int64_t n = valid ? g / a.P : 0;
     const int p = valid ? (int)(g - n * a.P) : 0;
     const float *xb = a.x + n * a.xs_n + (int64_t)p * a.xs_p;
-    const QuantConsts qc = consts_from_slot(*a.slot, a.bits, 0, 0.f, 0.f);
+    const int xs_k = (int)a.xs_k;                        // K * P < 2^31 elements per image
     const int8_t *wsrc = a.wpk + (int64_t)pass * a.slabs * bslab;
     // instruction descriptor: D = s32, A = B = s8, both K-major, N = npass, M = 128
     const uint32_t idesc = (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(a.npass >> 3) << 17) |
                            ((uint32_t)(kI8M >> 4) << 24);
-    const int sh = 8 - a.bits;                          // < 8-bit grids: a = (code - 2^(bits-1)) << sh, s_x >> sh
     int csum = 0;
 
     for (int s = 0; s < a.slabs; ++s) {
@@ -141,9 +155,11 @@ pw_i8_kernel(PwI8Args a) {
 #pragma unroll
         for (int c = 0; c < 2; ++c) {
             const int k0 = s * kI8Slab + (h + 2 * c) * 16;
+            if (k0 < a.K) {                                           // warp-uniform: padded chunks cost nothing
+                const float *px = xb + (int64_t)k0 * xs_k;
 #pragma unroll
-            for (int j = 0; j < 16; ++j)
-                v[c][j] = (valid && k0 + j < a.K) ? __ldg(xb + (int64_t)(k0 + j) * a.xs_k) : 0.0f;
+                for (int j = 0; j < 16; ++j) v[c][j] = (valid && k0 + j < a.K) ? __ldg(px + j * xs_k) : 0.0f;
+            }
         }
         // 2. the ring stage is free once the MMAs issued two slabs ago have retired
         if (s >= 2) mbar_wait(done0 + 8 * buf, ((s >> 1) - 1) & 1);
@@ -155,18 +171,20 @@ pw_i8_kernel(PwI8Args a) {
 #pragma unroll
         for (int c = 0; c < 2; ++c) {
             const int k0 = s * kI8Slab + (h + 2 * c) * 16;
-            uint32_t w4[4];
+            uint32_t w4[4] = {0u, 0u, 0u, 0u};
+            if (k0 < a.K) {
 #pragma unroll
-            for (int q4 = 0; q4 < 4; ++q4) {
-                uint32_t b[4];
+                for (int q4 = 0; q4 < 4; ++q4) {
+                    uint32_t b[4];
 #pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    const int k = k0 + 4 * q4 + j;
-                    b[j] = (valid && k < a.K) ? quant_code_bits(v[c][4 * q4 + j], qc) : (128u >> sh);
+                    for (int j = 0; j < 4; ++j) {
+                        const int k = k0 + 4 * q4 + j;
+                        b[j] = (valid && k < a.K) ? quant_code_bits(v[c][4 * q4 + j], qc) : (128u >> sh);
+                    }
+                    const uint32_t lo = __byte_perm(b[0], b[1], 0x0040), hi = __byte_perm(b[2], b[3], 0x0040);
+                    w4[q4] = (__byte_perm(lo, hi, 0x5410) << sh) ^ 0x80808080u;
+                    csum = __dp4a((int)w4[q4], 0x01010101, csum);
                 }
-                const uint32_t lo = __byte_perm(b[0], b[1], 0x0040), hi = __byte_perm(b[2], b[3], 0x0040);
-                w4[q4] = (__byte_perm(lo, hi, 0x5410) << sh) ^ 0x80808080u;
-                csum = __dp4a((int)w4[q4], 0x01010101, csum);
             }
             *reinterpret_cast<uint4 *>(sA + buf * kI8ASlab + (h + 2 * c) * (kI8M * 16) + r * 16) =
                 make_uint4(w4[0], w4[1], w4[2], w4[3]);
@@ -201,12 +219,10 @@ pw_i8_kernel(PwI8Args a) {
     const int64_t en = ev ? eg / a.P : 0;
     const int ep = ev ? (int)(eg - en * a.P) : 0;
     float *yb = a.y + en * a.ys_n + (int64_t)ep * a.ys_p;
-    const float sx = __fmul_rn(qc.scale, 1.0f / (float)(1 << sh));
-    const float cx = __fmaf_rn(128.0f, sx, qc.add_back);
+    const int ys_o = (int)a.ys_o;
     const float fa = __fmul_rn(sx, a.s_w);
-    const float row_c = __fmaf_rn(__fmul_rn(sx, a.c_w), (float)(colsum_s[0][er] + colsum_s[1][er]),
-                                  __fmul_rn(__fmul_rn((float)a.K, a.c_w), cx));
-    const int o0 = pass * a.o_per_pass, o_end = min(a.O, o0 + a.o_per_pass);
+    const float row_c = __fmul_rn(__fmul_rn(sx, a.c_w), (float)(colsum_s[0][er] + colsum_s[1][er]));
+    const float floor_v = a.relu ? 0.0f : -INFINITY;
     float lo = INFINITY, hi = -INFINITY;
     for (int chunk = warp >> 2; chunk * 16 < a.npass; chunk += 2) {
         const int oc = o0 + chunk * 16;
@@ -219,20 +235,25 @@ pw_i8_kernel(PwI8Args a) {
                        "=r"(d[15])
                      : "r"(tmem + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)(chunk * 16)));
         asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+        float *py = yb + (int64_t)oc * ys_o;
+        const float4 *cc = reinterpret_cast<const float4 *>(chan_c + chunk * 16);
+        const int nvalid = min(16, o_end - oc);                   // warp-uniform
 #pragma unroll
-        for (int j = 0; j < 16; ++j) {
-            const int o = oc + j;
-            if (o < o_end) {
-                float yv = __fmaf_rn(fa, (float)(int)d[j], __fmaf_rn(cx, __ldg(a.wr + o), row_c));
-                if (a.bias) yv = __fadd_rn(yv, __ldg(a.bias + o));
-                if (a.relu) yv = fmaxf(yv, 0.0f);
-                if (ev) {
-                    yb[(int64_t)o * a.ys_o] = yv;
+        for (int j4 = 0; j4 < 4; ++j4) {
+            const float4 c4 = cc[j4];
+            const float cj[4] = {c4.x, c4.y, c4.z, c4.w};
+#pragma unroll
+            for (int t = 0; t < 4; ++t) {
+                const int j = 4 * j4 + t;
+                const float yv = fmaxf(__fmaf_rn(fa, (float)(int)d[j], __fadd_rn(row_c, cj[t])), floor_v);
+                if (j < nvalid) {
+                    if (ev) py[j * ys_o] = yv;
                     lo = fminf(lo, yv); hi = fmaxf(hi, yv);
                 }
             }
         }
     }
+    if (!ev) { lo = INFINITY; hi = -INFINITY; }
     if (a.stats) {                                                // per-sample extrema, encoded (common.cuh)
         const int64_t n0 = __shfl_sync(0xffffffffu, en, 0);
         const bool uni = __all_sync(0xffffffffu, ev && en == n0);
