@@ -246,6 +246,45 @@ def kernel_rooflines(torch, dev, peak_gbs, n_elems, reps=10):
     return out
 
 
+def sharded_microbench(torch, dev, world, peak_gbs, elems=1 << 26, per_rank=2, reps=5):
+    """BASELINE.json configs[4]: a list of world*per_rank equal fp32 tensors (256 MiB each, larger than L2 together)
+    dealt to the ranks; every rank fake-quantises its share (range reduce + apply, 12 B/elt) and the quantised
+    state is assembled everywhere by one NCCL all-gather of u8 codes + ranges and a local dequantisation
+    (dist.quantize_targ_layer_sharded).  Returns aggregate GB/s over the algorithmic 12 B/elt of ALL tensors."""
+    import torch.nn as nn
+    import torch.distributed as dist
+    from data_free_quantization_b200.dist import quantize_targ_layer_sharded
+    g = torch.Generator(device=dev).manual_seed(3)
+    graph = {}
+    for i in range(world * per_rank):
+        lin = nn.Linear(2, 2, bias=False)
+        lin.weight = nn.Parameter(torch.randn(1024, elems // 1024, device=dev, generator=g) * 0.1, requires_grad=False)
+        graph[i] = lin
+    ts = []
+    for it in range(reps + 2):
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        info = quantize_targ_layer_sharded(graph, 8, 32, [nn.Linear])
+        b.record()
+        b.synchronize()
+        if it >= 2:
+            ts.append(a.elapsed_time(b))
+    ms = sum(ts) / len(ts)
+    if world > 1:
+        t = torch.tensor([ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t[0])
+    total = elems * world * per_rank
+    gbs = 12 * total / (ms * 1e-3) / 1e9
+    return {"kernel": "layer-sharded fake-quant + all-gather of u8 codes + local dequant", "tensors": world * per_rank,
+            "elems_per_tensor": elems, "bytes_per_elt": 12, "ms": round(ms, 4), "achieved": round(gbs, 1),
+            "per_gpu": round(gbs / world, 1), "peak_per_gpu": peak_gbs, "unit": "GB/s",
+            "gathered_bytes_per_rank": int(info["bytes_gathered"])}
+
+
 # ------------------------------------------------------------------------------------------ quantised eval
 def eval_images_per_s(torch, case, batch, steps, warmup):
     """W8A8 eval of the quantised model on a synthetic batch (main_dfq.py:66-113 loop body, one batch per step)."""
@@ -451,6 +490,10 @@ def main():
                               "ms_per_batch": round(ev_ms, 3),
                               "path": "reference-shaped nn.Module forward: QuantMeasure on libdfq_b200 kernels, "
                                       "conv/linear arithmetic through F.conv2d (cuDNN fp32, library)"}}
+    sharded = None
+    if not args.no_micro:
+        with quiet:
+            sharded = sharded_microbench(torch, dev, world, peak)
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -481,7 +524,7 @@ def main():
             "e2e": {"value": round(ms_e2e / world, 4), "unit": UNIT, "h2d_bytes_per_step": case.h2d_bytes(),
                     "d2h_bytes_per_step": case.d2h_bytes()},
             "gpu_launches": int(launches) // max(1, args.steps), "stages_ms": {k: round(v, 3) for k, v in stages.items()},
-            "roofline": roof, "kernels": kernels, "eval": ev, "cpu_baseline": cpu, "clocks": clocks.summary()}
+            "roofline": roof, "kernels": kernels, "kernels_sharded": sharded, "eval": ev, "cpu_baseline": cpu, "clocks": clocks.summary()}
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

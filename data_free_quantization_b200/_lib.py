@@ -102,6 +102,7 @@ PROTOTYPES = {
     "dfq_pw_i8": (ctypes.c_int, [P(DfqPwI8Desc), c_void]),
     "dfq_quant_plan_host": (ctypes.c_int, [P(DfqQuantDesc), ctypes.c_int, P(i64), P(i64)]),
     "dfq_fake_quant_multi_f32": (ctypes.c_int, [c_void, ctypes.c_int, i64, i64, c_void, c_void]),
+    "dfq_dequant_codes_f32": (ctypes.c_int, [c_void, ctypes.c_int, c_void, i64, i64, c_void, c_void]),
     "dfq_cle_plan_host": (ctypes.c_int, [P(DfqClePair), ctypes.c_int, P(ctypes.c_int), P(ctypes.c_int)]),
     "dfq_cle_layers_plan_host": (ctypes.c_int, [P(DfqCleLayer), ctypes.c_int, P(ctypes.c_int)]),
     "dfq_cle_result_bytes": (i64, [ctypes.c_int]),

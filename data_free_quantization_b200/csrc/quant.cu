@@ -189,9 +189,40 @@ fake_quant_apply_kernel(const float *__restrict__ x, float *__restrict__ y, Code
     apply_range<CodeT>(x, y, codes, begin, end, c, false, threadIdx.x, kThreads);
 }
 
+// codes -> fp32 with the two rounded operations that end the fake-quant chain (utils/quantize.py:76: q * scale, then
+// + min), so a tensor shipped as codes + {min, max, scale} reproduces the sender's dequantised weights bit for bit.
+// slots: one RangeSlot per row (per-channel) or one for the tensor; asymmetric grids (code = q - qmin = q).
+template <typename CodeT>
+__global__ void __launch_bounds__(kThreads)
+dequant_codes_kernel(const CodeT *__restrict__ codes, float *__restrict__ y, int64_t n, int64_t cols,
+                     const RangeSlot *__restrict__ slots, int per_row) {
+    const int64_t begin = (int64_t)blockIdx.x * kChunk, end = min(begin + (int64_t)kChunk, n);
+    for (int64_t k = begin + threadIdx.x; k < end; k += kThreads) {
+        const RangeSlot r = slots[per_row ? k / cols : 0];
+        y[k] = __fadd_rn(__fmul_rn((float)codes[k], r.scale), r.mn);
+    }
+}
+
 }  // namespace dfq
 
 using namespace dfq;
+
+extern "C" int dfq_dequant_codes_f32(const void *codes, int code_bytes, float *y, int64_t n, int64_t rows,
+                                     const float *slots_dev, void *stream) {
+    if (n <= 0) return 0;
+    if (rows < 1 || n % rows || (code_bytes != 1 && code_bytes != 2)) return (int)cudaErrorInvalidValue;
+    const int64_t blocks = (n + kChunk - 1) / kChunk;
+    if (blocks > 0x7fffffffll) return (int)cudaErrorInvalidValue;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (code_bytes == 1)
+        dequant_codes_kernel<uint8_t><<<(unsigned)blocks, kThreads, 0, st>>>((const uint8_t *)codes, y, n, n / rows,
+                                                                          (const RangeSlot *)slots_dev, rows > 1);
+    else
+        dequant_codes_kernel<uint16_t><<<(unsigned)blocks, kThreads, 0, st>>>((const uint16_t *)codes, y, n, n / rows,
+                                                                           (const RangeSlot *)slots_dev, rows > 1);
+    g_launches += 1;
+    return (int)cudaGetLastError();
+}
 
 static inline int64_t desc_blocks(const DfqQuantDesc &d) {
     // virtual chunks of the range / apply passes

@@ -159,6 +159,11 @@ int dfq_fake_quant_apply_f32(const float *x, float *y, void *codes, int64_t n, i
 int dfq_quant_plan_host(DfqQuantDesc *descs_host, int n_desc, int64_t *total_blocks, int64_t *total_slots);
 int dfq_fake_quant_multi_f32(const DfqQuantDesc *descs_dev, int n_desc, int64_t total_blocks,
                              int64_t total_slots, float *ranges_dev, void *stream);
+/* Inverse of the optional code output: y = code * scale + min with the fake-quant chain's own two roundings
+ * (utils/quantize.py:76), slots_dev = {min, max, scale, 0} per tensor (rows == 1) or per row.  Used to rebuild the
+ * quantised state dict from the all-gathered codes of the layer-sharded pass. */
+int dfq_dequant_codes_f32(const void *codes, int code_bytes, float *y, int64_t n, int64_t rows,
+                          const float *slots_dev, void *stream);
 
 /* ---- QuantMeasure with the range resident on the device: utils/quantize.py:94-126 (no host round trip) -----
  * running_min / running_max: the module's [1] buffers (device), updated in place when update_stat != 0 with
