@@ -372,14 +372,13 @@ def reference_arm(args):
     sample = ("full pipeline (merge+CLE 44 iterations+absorb+quantize+clip) on the seeded MobileNetV2, "
               f"{len(ts)} passes; C restatement of the reference (oracle/dfq_oracle.c), not the Python original "
               "(that takes ~80-110 s per pass, BASELINE.md)")
-    line = {"impl": "reference", "metric": METRIC, "value": round(ms, 3), "unit": UNIT, "n_gpus": args.gpus,
+    return {"impl": "reference", "metric": METRIC, "value": round(ms, 3), "unit": UNIT, "n_gpus": args.gpus,
             "steps": len(ts), "warmup": min(args.warmup, 1), "ms_per_step": round(ms, 3), "higher_is_better": False,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": WORKLOAD},
             "cpu_baseline": {"value": round(ms, 3), "unit": UNIT, "cores": 1, "kind": "port", "sample": sample},
             "e2e": {"value": round(ms, 3), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
 
 
 def measured_peak():
@@ -392,6 +391,20 @@ def measured_peak():
 
 def main():
     args = parse()
+    # the JSON line is the only thing on stdout: libraries (NCCL's version banner, ...) get stderr
+    out = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+    sys.stdout = sys.stderr
+    try:
+        line = _main(args)
+    finally:
+        sys.stdout.flush()
+    if line is not None:
+        out.write(json.dumps(line) + "\n")
+        out.flush()
+
+
+def _main(args):
     if args.impl == "reference":
         return reference_arm(args)
     import torch
@@ -525,9 +538,9 @@ def main():
                     "d2h_bytes_per_step": case.d2h_bytes()},
             "gpu_launches": int(launches) // max(1, args.steps), "stages_ms": {k: round(v, 3) for k, v in stages.items()},
             "roofline": roof, "kernels": kernels, "kernels_sharded": sharded, "eval": ev, "cpu_baseline": cpu, "clocks": clocks.summary()}
-    print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
+    return line
 
 
 if __name__ == "__main__":
