@@ -7,12 +7,14 @@ sequential loop orders them (they get increasing `stage` numbers); relations tha
 the same stage, in parallel.
 """
 import ctypes
+import os
 
 import torch
 import torch.nn as nn
 
 from . import _lib as L
 
+DEBUG_STAMPS = None       # tuning aid: an int64 CUDA tensor [blocks * phases * 3] receives per-phase timer stamps
 MAX_ITERS = 8192          # the reference loop is unbounded; MobileNetV2 converges in 44 iterations
 
 
@@ -90,21 +92,64 @@ def cross_layer_equalization(graph, relations, Target_list, s_min_max=[1e-8, 1e8
             off += w.numel()
         tc = ctypes.c_int()
         L.check(L.lib().dfq_cle_layers_plan_host(layers, len(ws), ctypes.byref(tc)), "dfq_cle_layers_plan_host")
-        pairs_dev, layers_dev = L.table_to_device(pairs, dev), L.table_to_device(layers, dev)
+        pairs_dev = L.table_to_device(pairs, dev)
         acc = torch.empty(2 * len(ws), dtype=torch.float64, device=dev)
         nbytes = int(L.lib().dfq_cle_result_bytes(max_iters + 1))
         result = torch.zeros(nbytes, dtype=torch.uint8, device=dev)
-        L.check(L.lib().dfq_cle_run(pairs_dev.data_ptr(), n, ns.value, layers_dev.data_ptr(), len(ws), tc.value,
-                                    float(s_min_max[0]), float(s_min_max[1]), int(bool(signed)), float(eps),
-                                    float(Treshhold), int(Count), int(max_iters), acc.data_ptr(), result.data_ptr(),
-                                    L.stream()), "dfq_cle_run")
+        impl = "stream" if os.environ.get("DFQ_CLE_IMPL", "stream") == "stream" and _run_streaming(
+            pairs, n, pairs_dev, layers, len(ws), s_min_max, signed, eps, Treshhold, Count, max_iters, acc, result,
+            dev) else "units"
+        if impl == "units":
+            layers_dev = L.table_to_device(layers, dev)
+            L.check(L.lib().dfq_cle_run(pairs_dev.data_ptr(), n, ns.value, layers_dev.data_ptr(), len(ws), tc.value,
+                                        float(s_min_max[0]), float(s_min_max[1]), int(bool(signed)), float(eps),
+                                        float(Treshhold), int(Count), int(max_iters), acc.data_ptr(),
+                                        result.data_ptr(), L.stream()), "dfq_cle_run")
         if not return_info:
             return None
         host = result.cpu().numpy()
         iters = int(host[:4].view("int32")[0])
         diffs = host[8:].view("float64")
         return {"iters": iters, "stall": int(host[4:8].view("int32")[0]), "diff": float(diffs[0]),
-                "diffs": diffs[1:1 + iters].tolist(), "stages": ns.value}
+                "diffs": diffs[1:1 + iters].tolist(), "stages": ns.value, "impl": impl}
+
+
+def _run_streaming(pairs, n, pairs_dev, layers, n_layers, s_min_max, signed, eps, Treshhold, Count, max_iters, acc,
+                   result, dev):
+    """The streaming form (csrc/cle2.cu).  Returns False when the relations are not simple chains (the plan says
+    cudaErrorNotSupported); the caller then runs the per-channel-unit kernel."""
+    lib = L.lib()
+    tensors = (L.DfqCleTensor * n_layers)()
+    max_tasks = 3 * sum((int(layers[i].n) // 512) + 8 for i in range(n_layers)) + 3 * sum(
+        int(pairs[i].C1) // 8 + int(pairs[i].O2) // 8 + 8 for i in range(n))
+    tasks = (L.DfqCleTask * max_tasks)()
+    nt, ni, nph = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
+    phase_begin = (L.i32 * 65)()
+    chan_off = (L.i32 * (n + 1))()
+    err = lib.dfq_cle2_plan_host(pairs, n, layers, n_layers, tensors, tasks, max_tasks, ctypes.byref(nt),
+                                 ctypes.byref(ni), phase_begin, ctypes.byref(nph), chan_off)
+    if err == 801:                                  # cudaErrorNotSupported
+        return False
+    L.check(err, "dfq_cle2_plan_host")
+    used = nt.value + ni.value
+    tasks_dev = L.table_to_device((L.DfqCleTask * used).from_buffer(tasks), dev)
+    tensors_dev = L.table_to_device(tensors, dev)
+    chan_dev = L.table_to_device(chan_off, dev)
+    total_c = int(chan_off[n])
+    r1 = torch.empty(2 * total_c, dtype=torch.float32, device=dev)
+    r2 = torch.empty(4 * total_c, dtype=torch.int32, device=dev)
+    L.check(lib.dfq_cle2_run(pairs_dev.data_ptr(), n, tensors_dev.data_ptr(), n_layers, tasks_dev.data_ptr(), nt.value,
+                             ni.value, phase_begin, nph.value, chan_dev.data_ptr(), total_c, r1.data_ptr(),
+                             r2.data_ptr(), float(s_min_max[0]), float(s_min_max[1]), int(bool(signed)), float(eps),
+                             float(Treshhold), int(Count), int(max_iters), acc.data_ptr(), result.data_ptr(),
+                             int(os.environ.get("DFQ_CLE_BLOCKS_PER_SM", "2")),
+                             None if DEBUG_STAMPS is None else DEBUG_STAMPS.data_ptr(), L.stream()), "dfq_cle2_run")
+    if DEBUG_STAMPS is not None:
+        DEBUG_STAMPS.n_phases = nph.value
+        DEBUG_STAMPS.tasks = [(tasks[i].tensor, tasks[i].row0, tasks[i].nrows, tasks[i].kind & 255, tasks[i].kind >> 8,
+                               tensors[tasks[i].tensor].O, tensors[tasks[i].tensor].row_len,
+                               tensors[tasks[i].tensor].up, tensors[tasks[i].tensor].down) for i in range(used)]
+    return True
 
 
 class OrderedDictNoDup:

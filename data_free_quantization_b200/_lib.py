@@ -34,6 +34,15 @@ class DfqCleLayer(ctypes.Structure):
     _fields_ = [("W", c_void), ("W_old", c_void), ("n", i64), ("first_chunk", i32), ("n_chunks", i32)]
 
 
+class DfqCleTensor(ctypes.Structure):
+    _fields_ = [("W", c_void), ("W_old", c_void), ("O", i32), ("row_len", i32), ("KK", i32), ("I2", i32), ("Og", i32),
+                ("up", i32), ("down", i32), ("layer", i32)]
+
+
+class DfqCleTask(ctypes.Structure):
+    _fields_ = [("tensor", i32), ("row0", i32), ("nrows", i32), ("kind", i32)]
+
+
 class DfqAbsorbPair(ctypes.Structure):
     _fields_ = [("W2", c_void), ("b1", c_void), ("b2", c_void), ("bn_w", c_void), ("bn_b", c_void), ("c", c_void),
                 ("wc", c_void), ("C1", i32), ("O2", i32), ("I2", i32), ("KK", i32), ("first_row", i32)]
@@ -71,7 +80,7 @@ class DfqPwI8Desc(ctypes.Structure):
 
 
 Q_SYMMETRIC, Q_RANGE_F32, Q_PER_CHANNEL, Q_CLAMP_OUT = 1, 2, 4, 8
-ABI_VERSION = 7
+ABI_VERSION = 8
 
 # every symbol include/dfq_b200.h declares: (restype, argtypes)
 P = ctypes.POINTER
@@ -108,6 +117,12 @@ PROTOTYPES = {
     "dfq_cle_result_bytes": (i64, [ctypes.c_int]),
     "dfq_cle_run": (ctypes.c_int, [c_void, ctypes.c_int, ctypes.c_int, c_void, ctypes.c_int, ctypes.c_int, f64, f64,
                                    ctypes.c_int, f32, f64, ctypes.c_int, ctypes.c_int, c_void, c_void, c_void]),
+    "dfq_cle2_plan_host": (ctypes.c_int, [P(DfqClePair), ctypes.c_int, P(DfqCleLayer), ctypes.c_int, P(DfqCleTensor),
+                                          P(DfqCleTask), ctypes.c_int, P(ctypes.c_int), P(ctypes.c_int), P(i32),
+                                          P(ctypes.c_int), P(i32)]),
+    "dfq_cle2_run": (ctypes.c_int, [c_void, ctypes.c_int, c_void, ctypes.c_int, c_void, ctypes.c_int, ctypes.c_int,
+                                    P(i32), ctypes.c_int, c_void, ctypes.c_int, c_void, c_void, f64, f64, ctypes.c_int,
+                                    f32, f64, ctypes.c_int, ctypes.c_int, c_void, c_void, ctypes.c_int, c_void, c_void]),
     "dfq_absorb_plan_host": (ctypes.c_int, [P(DfqAbsorbPair), ctypes.c_int, P(ctypes.c_int)]),
     "dfq_absorb_clip": (ctypes.c_int, [c_void, ctypes.c_int, ctypes.c_int, ctypes.c_int, f32, ctypes.c_int, f32, f32,
                                        c_void]),

@@ -23,7 +23,7 @@
 extern "C" {
 #endif
 
-#define DFQ_ABI_VERSION 7
+#define DFQ_ABI_VERSION 8
 
 #if defined(__GNUC__)
 #pragma GCC visibility push(default)   /* the library is built with -fvisibility=hidden */
@@ -79,6 +79,22 @@ typedef struct DfqCleLayer {
     int32_t first_chunk; /* filled by dfq_cle_layers_plan_host                        */
     int32_t n_chunks;
 } DfqCleLayer;
+
+/* Streaming form of the same loop (csrc/cle2.cu): one weight tensor of a chain and one row tile of work. */
+typedef struct DfqCleTensor {
+    float *W;
+    float *W_old;
+    int32_t O, row_len;  /* rows and elements per row                                  */
+    int32_t KK, I2;      /* taps and input channels per group (as W2 of its up pair)   */
+    int32_t Og;          /* output rows per group of the up pair (O when ungrouped)    */
+    int32_t up, down;    /* index of the pair where it is W2 / W1, or -1               */
+    int32_t layer;       /* slot of the convergence metric                             */
+} DfqCleTensor;
+typedef struct DfqCleTask {
+    int32_t tensor, row0, nrows;
+    int32_t kind;        /* low byte 0: column scaling + row ranges, 1: row/column scaling + metric + next column
+                            ranges; bits 8..: 64-column strip of a 2-D tile                                  */
+} DfqCleTask;
 
 /* Result block of dfq_cle_run (device memory, dfq_cle_result_bytes(max_iters) = 16 + 8*max_iters):
  *   int32 iters; int32 stall; double last_diff; double diffs[max_iters]              */
@@ -240,6 +256,20 @@ int dfq_cle_run(const DfqClePair *pairs_dev, int n_pairs, int n_stages, const Df
                 int n_layers, int total_chunks, double smin, double smax, int is_signed, float eps,
                 double threshold, int count, int max_iters, double *scratch_dev, void *result_dev,
                 void *stream);
+/* Streaming form: every tensor is read twice per iteration in coalesced row tiles, one grid barrier per chain
+ * position.  dfq_cle2_plan_host returns cudaErrorNotSupported (801) for relation sets that are not simple chains;
+ * use dfq_cle_run then.  tensors_host: n_layers entries; tasks_host: max_tasks entries (n_tasks phase tasks followed
+ * by n_init prologue tasks); phase_begin_host: 65 ints; chan_off_host: n_pairs + 1 ints.  r1_dev: 2 * total_C floats,
+ * r2_dev: 4 * total_C uints, acc_dev: 2 * n_layers doubles (all zeroed by the call).  debug_dev: NULL, or
+ * blocks * n_phases * 5 uint64 for per-phase timer stamps (tuning aid). */
+int dfq_cle2_plan_host(const DfqClePair *pairs_host, int n_pairs, const DfqCleLayer *layers_host, int n_layers,
+                       DfqCleTensor *tensors_host, DfqCleTask *tasks_host, int max_tasks, int *n_tasks, int *n_init,
+                       int32_t *phase_begin_host, int *n_phases, int32_t *chan_off_host);
+int dfq_cle2_run(const DfqClePair *pairs_dev, int n_pairs, const DfqCleTensor *tensors_dev, int n_tensors,
+                 const DfqCleTask *tasks_dev, int n_tasks, int n_init, const int32_t *phase_begin_host, int n_phases,
+                 const int32_t *chan_off_dev, int total_C, float *r1_dev, unsigned *r2_dev, double smin, double smax,
+                 int is_signed, float eps, double threshold, int count, int max_iters, double *acc_dev,
+                 void *result_dev, int blocks_per_sm, void *debug_dev, void *stream);
 
 /* ---- (c) bias absorption (+ optional weight clip): bias_absorption.py:9-80, clip_weight.py:4-33 */
 int dfq_absorb_plan_host(DfqAbsorbPair *pairs_host, int n_pairs, int *total_rows);
