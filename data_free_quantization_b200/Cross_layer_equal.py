@@ -138,11 +138,12 @@ def _run_streaming(pairs, n, pairs_dev, layers, n_layers, s_min_max, signed, eps
     total_c = int(chan_off[n])
     r1 = torch.empty(2 * total_c, dtype=torch.float32, device=dev)
     r2 = torch.empty(4 * total_c, dtype=torch.int32, device=dev)
+    fat = torch.empty(int(lib.dfq_cle2_fat_bytes(used)) // 16 + 1, 4, dtype=torch.int32, device=dev)   # 16 B aligned
     L.check(lib.dfq_cle2_run(pairs_dev.data_ptr(), n, tensors_dev.data_ptr(), n_layers, tasks_dev.data_ptr(), nt.value,
                              ni.value, phase_begin, nph.value, chan_dev.data_ptr(), total_c, r1.data_ptr(),
                              r2.data_ptr(), float(s_min_max[0]), float(s_min_max[1]), int(bool(signed)), float(eps),
                              float(Treshhold), int(Count), int(max_iters), acc.data_ptr(), result.data_ptr(),
-                             int(os.environ.get("DFQ_CLE_BLOCKS_PER_SM", "2")),
+                             int(os.environ.get("DFQ_CLE_BLOCKS_PER_SM", "2")), fat.data_ptr(),
                              None if DEBUG_STAMPS is None else DEBUG_STAMPS.data_ptr(), L.stream()), "dfq_cle2_run")
     if DEBUG_STAMPS is not None:
         DEBUG_STAMPS.n_phases = nph.value

@@ -80,7 +80,7 @@ class DfqPwI8Desc(ctypes.Structure):
 
 
 Q_SYMMETRIC, Q_RANGE_F32, Q_PER_CHANNEL, Q_CLAMP_OUT = 1, 2, 4, 8
-ABI_VERSION = 8
+ABI_VERSION = 9
 
 # every symbol include/dfq_b200.h declares: (restype, argtypes)
 P = ctypes.POINTER
@@ -122,7 +122,8 @@ PROTOTYPES = {
                                           P(ctypes.c_int), P(i32)]),
     "dfq_cle2_run": (ctypes.c_int, [c_void, ctypes.c_int, c_void, ctypes.c_int, c_void, ctypes.c_int, ctypes.c_int,
                                     P(i32), ctypes.c_int, c_void, ctypes.c_int, c_void, c_void, f64, f64, ctypes.c_int,
-                                    f32, f64, ctypes.c_int, ctypes.c_int, c_void, c_void, ctypes.c_int, c_void, c_void]),
+                                    f32, f64, ctypes.c_int, ctypes.c_int, c_void, c_void, ctypes.c_int, c_void, c_void, c_void]),
+    "dfq_cle2_fat_bytes": (i64, [ctypes.c_int]),
     "dfq_absorb_plan_host": (ctypes.c_int, [P(DfqAbsorbPair), ctypes.c_int, P(ctypes.c_int)]),
     "dfq_absorb_clip": (ctypes.c_int, [c_void, ctypes.c_int, ctypes.c_int, ctypes.c_int, f32, ctypes.c_int, f32, f32,
                                        c_void]),

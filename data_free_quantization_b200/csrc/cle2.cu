@@ -27,10 +27,25 @@ constexpr int kC2ColRows = 32;       // rows of a 2-D tile
 constexpr int kC2Strip = 64;         // columns of a 2-D tile
 constexpr int kC2Tile = 2048;        // elements per tile (a column-owner tile has at least 4 rows)
 
+// One self-contained work item: everything a block needs arrives with ONE struct load (the planned DfqCleTask /
+// DfqCleTensor / DfqClePair tables are expanded into these records by cle2_expand_kernel before the loop starts), so
+// a task costs two dependent memory round trips (record, data) instead of five (task, tensor, pair, offsets, data).
+struct __align__(16) Cle2Fat {
+    float *W, *W_old;                // tile base: row0 (and the column strip of a 2-D tile) applied
+    float *s_tab;                    // down pair: s of row0.. (1/s at + total_C); rows pass writes, cols pass reads
+    const float *sinv_up;            // up pair: 1/s by channel, or NULL
+    unsigned *r2_up;                 // up pair: encoded column ranges of parity 0 (max at + total_C, parity 1 at + 2 total_C)
+    unsigned *r2_down;               // down pair: same table at row0
+    float *S, *b1, *bn_w, *bn_b;     // down pair's per-channel vectors at row0
+    double *acc;                     // metric slot of parity 0 (parity 1 at + n_tensors)
+    int row0, nrows, L, KK, I2, Og, O, kind, strip, up, down, pad;
+};
+
 struct Cle2Args {
     const DfqClePair *pairs; int n_pairs;
     const DfqCleTensor *tensors; int n_tensors;
     const DfqCleTask *tasks; int n_tasks;
+    Cle2Fat *fat;
     int phase_begin[kC2MaxPhases + 1]; int n_phases;
     int n_init;                      // tasks [n_tasks, n_tasks + n_init) are the prologue's "cols" tasks of all tensors
     const int *chan_off;             // [n_pairs + 1] prefix of C1
@@ -41,8 +56,37 @@ struct Cle2Args {
     int is_signed; float eps; double threshold; int count; int max_iters;
     double *acc;                     // [2][n_tensors]
     int *res_i; double *res_d;
-    unsigned long long *dbg;         // optional [blocks][phases][3] globaltimer stamps of iteration 2 (tuning aid)
+    unsigned long long *dbg;         // optional [blocks][phases][5] globaltimer stamps of iteration 2 (tuning aid)
 };
+
+__global__ void cle2_expand_kernel(Cle2Args a) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= a.n_tasks + a.n_init) return;
+    const DfqCleTask k = a.tasks[t];
+    const DfqCleTensor T = a.tensors[k.tensor];
+    Cle2Fat f;
+    f.kind = k.kind & 0xff; f.strip = k.kind >> 8;
+    f.row0 = k.row0; f.nrows = k.nrows; f.L = T.row_len; f.KK = T.KK; f.I2 = T.I2; f.Og = T.Og; f.O = T.O;
+    f.up = T.up; f.down = T.down; f.pad = 0;
+    const bool tile2d = f.kind == 1 && T.row_len >= 128 && T.Og >= T.O;
+    const int64_t base = (int64_t)k.row0 * T.row_len + (tile2d ? f.strip * kC2Strip : 0);
+    f.W = T.W + base; f.W_old = T.W_old + base;
+    f.acc = a.acc + T.layer;
+    f.s_tab = nullptr; f.r2_down = nullptr; f.S = f.b1 = f.bn_w = f.bn_b = nullptr;
+    f.sinv_up = nullptr; f.r2_up = nullptr;
+    if (T.down >= 0) {
+        const DfqClePair p = a.pairs[T.down];
+        const int off = a.chan_off[T.down] + k.row0;
+        f.s_tab = a.r1 + off; f.r2_down = a.r2 + off;
+        f.S = p.S + k.row0; f.b1 = p.b1 + k.row0;
+        f.bn_w = p.bn_w ? p.bn_w + k.row0 : nullptr; f.bn_b = p.bn_b ? p.bn_b + k.row0 : nullptr;
+    }
+    if (T.up >= 0) {
+        f.sinv_up = a.r1 + a.total_C + a.chan_off[T.up];
+        f.r2_up = a.r2 + a.chan_off[T.up];
+    }
+    a.fat[t] = f;
+}
 
 // Cross_layer_equal.py:34-43 for one channel
 __device__ __forceinline__ void cle2_scale(const Cle2Args &a, float r1, float r2, float &s, float &sinv) {
@@ -56,52 +100,66 @@ __device__ __forceinline__ void cle2_scale(const Cle2Args &a, float r1, float r2
     else { s = a.smin_f; sinv = a.inv_smin_f; }
 }
 
-// s and 1/s of channel c of `pair` from its row range r1 and the column range left by the previous iteration;
-// the row owner also scales the per-channel vectors.  Called once per channel and iteration (rows pass).
-__device__ __forceinline__ void cle2_finish_row(const Cle2Args &a, int pair, int c, int par, float r1) {
-    const int idx = a.chan_off[pair] + c;
-    const unsigned *r2 = a.r2 + (size_t)par * 2 * a.total_C;
-    const float lo2 = -dec_ordered(r2[idx]), hi2 = dec_ordered(r2[a.total_C + idx]);
+// What the row owner needs besides the row range, fetched while the row itself is still in flight.
+struct Cle2RowPre { unsigned lo, hi; float S, b1, bw, bb; };
+
+__device__ __forceinline__ Cle2RowPre cle2_prefetch_row(const Cle2Args &a, const Cle2Fat &k, int r, int par) {
+    Cle2RowPre q;
+    const unsigned *r2 = k.r2_down + (size_t)par * 2 * a.total_C;
+    q.lo = r2[r]; q.hi = r2[a.total_C + r];
+    q.S = k.S[r]; q.b1 = k.b1[r];
+    q.bw = k.bn_w ? k.bn_w[r] : 0.0f; q.bb = k.bn_b ? k.bn_b[r] : 0.0f;
+    return q;
+}
+
+// s and 1/s of row r from its range and the column range left by the previous iteration; the per-channel vectors
+// follow (relation.py:26-30, Cross_layer_equal.py:48-55).  Once per channel and iteration.
+__device__ __forceinline__ void cle2_finish_row(const Cle2Args &a, const Cle2Fat &k, int r, float r1,
+                                                const Cle2RowPre &q) {
+    const float lo2 = -dec_ordered(q.lo), hi2 = dec_ordered(q.hi);
     const float r2v = a.is_signed ? hi2 : __fsub_rn(hi2, lo2);
     float s, sinv;
     cle2_scale(a, r1, r2v, s, sinv);
-    a.r1[idx] = s;                                               // s | 1/s tables read by the next phase
-    a.r1[a.total_C + idx] = sinv;
-    const DfqClePair &p = a.pairs[pair];
-    p.S[c] = __fmul_rn(p.S[c], s);                               // Relation.set_scale_vec, relation.py:26-30
-    p.b1[c] = __fmul_rn(p.b1[c], s);                             // :48-49
-    if (p.bn_w) p.bn_w[c] = __fmul_rn(p.bn_w[c], s);             // :51-52
-    if (p.bn_b) p.bn_b[c] = __fmul_rn(p.bn_b[c], s);             // :54-55
+    k.s_tab[r] = s;
+    k.s_tab[a.total_C + r] = sinv;
+    k.S[r] = __fmul_rn(q.S, s);
+    k.b1[r] = __fmul_rn(q.b1, s);
+    if (k.bn_w) k.bn_w[r] = __fmul_rn(q.bw, s);
+    if (k.bn_b) k.bn_b[r] = __fmul_rn(q.bb, s);
 }
 
-__device__ __forceinline__ int cle2_cidx(const DfqCleTensor &T, int o, int j) {
+__device__ __forceinline__ int cle2_cidx(const Cle2Fat &T, int o, int j) {
     const int i = (T.KK == 1) ? j : j / T.KK;
     return (T.Og >= T.O) ? i : (o / T.Og) * T.I2 + i;       // one group: the column is the input channel
 }
 
 // ---- "rows" pass: optional column scaling by 1/s of the up pair, row ranges, s of the down pair
-__device__ void cle2_rows_pass(const Cle2Args &a, const DfqCleTask &k, int par) {
-    const DfqCleTensor &T = a.tensors[k.tensor];
-    const bool cs = T.up >= 0;
+__device__ void cle2_rows_pass(const Cle2Args &a, const Cle2Fat &k, int par) {
+    const bool cs = k.up >= 0;
     const bool sgn = a.is_signed;
-    const float *__restrict__ sinv_up = cs ? a.r1 + a.total_C + a.chan_off[T.up] : nullptr;
-    const int L = T.row_len;
+    const float *__restrict__ sinv_up = k.sinv_up;
+    const int L = k.L;
+    const bool one_group = k.Og >= k.O;
     if (L > 9) {                                             // warp per row
         const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-        float my_range = 0.0f;                               // lane i keeps the i-th row of this warp: the per-row
-        int my_row = -1, cnt = 0;                            // epilogue (division, sqrt, 4 updates) runs lane-parallel
+        // lane i owns the epilogue (division, sqrt, vector updates) of this warp's i-th row, r = warp + 8 i
+        const int my_r = warp + kWarps * lane;
+        Cle2RowPre pre = {};
+        if (my_r < k.nrows) pre = cle2_prefetch_row(a, k, my_r, par);
+        float my_range = 0.0f;
+        int cnt = 0;
         if (L <= 256) {                                      // 4 rows of the warp in flight together
             for (int rb = warp; rb < k.nrows; rb += 4 * kWarps) {
                 float w[4][8], f[8];
 #pragma unroll
                 for (int u = 0; u < 8; ++u) {
                     const int j = lane + 32 * u;
-                    f[u] = (cs && j < L && T.Og >= T.O) ? __ldg(sinv_up + cle2_cidx(T, 0, j)) : 1.0f;
+                    f[u] = (cs && j < L && one_group) ? __ldg(sinv_up + cle2_cidx(k, 0, j)) : 1.0f;
                 }
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
                     const int r = rb + q * kWarps;
-                    const float *row = T.W + (int64_t)(k.row0 + r) * L;
+                    const float *row = k.W + (int64_t)r * L;
 #pragma unroll
                     for (int u = 0; u < 8; ++u) {
                         const int j = lane + 32 * u;
@@ -112,8 +170,7 @@ __device__ void cle2_rows_pass(const Cle2Args &a, const DfqCleTask &k, int par) 
                 for (int q = 0; q < 4; ++q) {
                     const int r = rb + q * kWarps;
                     if (r >= k.nrows) break;                 // warp-uniform
-                    const int o = k.row0 + r;
-                    float *row = T.W + (int64_t)o * L;
+                    float *row = k.W + (int64_t)r * L;
                     float lo = INFINITY, hi = -INFINITY;
 #pragma unroll
                     for (int u = 0; u < 8; ++u) {
@@ -121,115 +178,109 @@ __device__ void cle2_rows_pass(const Cle2Args &a, const DfqCleTask &k, int par) 
                         if (j >= L) break;
                         float v = w[q][u];
                         if (cs) {
-                            const float fj = (T.Og >= T.O) ? f[u] : __ldg(sinv_up + cle2_cidx(T, o, j));
+                            const float fj = one_group ? f[u] : __ldg(sinv_up + cle2_cidx(k, k.row0 + r, j));
                             v = __fmul_rn(v, fj); row[j] = v;
                         }
                         if (sgn) v = fabsf(v);
                         lo = fminf(lo, v); hi = fmaxf(hi, v);
                     }
                     lo = warp_min(lo); hi = warp_max(hi);
-                    if (lane == cnt) { my_range = sgn ? hi : __fsub_rn(hi, lo); my_row = o; }
-                    if (++cnt == 32) {
-                        cle2_finish_row(a, T.down, my_row, par, my_range);
-                        my_row = -1; cnt = 0;
+                    if (lane == cnt) my_range = sgn ? hi : __fsub_rn(hi, lo);
+                    ++cnt;
+                }
+            }
+        } else {
+            for (int r = warp; r < k.nrows; r += kWarps) {
+                float *__restrict__ row = k.W + (int64_t)r * L;
+                float lo = INFINITY, hi = -INFINITY;
+                for (int jb = lane; jb < L; jb += 32 * 16) {
+                    float w[16], f[16];
+#pragma unroll
+                    for (int u = 0; u < 16; ++u) {
+                        const int j = jb + 32 * u;
+                        w[u] = (j < L) ? row[j] : 0.0f;
+                        f[u] = (cs && j < L) ? __ldg(sinv_up + cle2_cidx(k, k.row0 + r, j)) : 1.0f;
+                    }
+#pragma unroll
+                    for (int u = 0; u < 16; ++u) {
+                        const int j = jb + 32 * u;
+                        if (j >= L) break;
+                        float v = w[u];
+                        if (cs) { v = __fmul_rn(v, f[u]); row[j] = v; }
+                        if (sgn) v = fabsf(v);
+                        lo = fminf(lo, v); hi = fmaxf(hi, v);
                     }
                 }
-            }
-        } else
-        for (int r = warp; r < k.nrows; r += kWarps) {
-            const int o = k.row0 + r;
-            float *__restrict__ row = T.W + (int64_t)o * L;
-            float lo = INFINITY, hi = -INFINITY;
-            for (int jb = lane; jb < L; jb += 32 * 16) {
-                float w[16], f[16];
-#pragma unroll
-                for (int u = 0; u < 16; ++u) {
-                    const int j = jb + 32 * u;
-                    w[u] = (j < L) ? row[j] : 0.0f;
-                    f[u] = (cs && j < L) ? __ldg(sinv_up + cle2_cidx(T, o, j)) : 1.0f;
-                }
-#pragma unroll
-                for (int u = 0; u < 16; ++u) {
-                    const int j = jb + 32 * u;
-                    if (j >= L) break;
-                    float v = w[u];
-                    if (cs) { v = __fmul_rn(v, f[u]); row[j] = v; }
-                    if (sgn) v = fabsf(v);
-                    lo = fminf(lo, v); hi = fmaxf(hi, v);
-                }
-            }
-            lo = warp_min(lo); hi = warp_max(hi);
-            if (lane == cnt) { my_range = sgn ? hi : __fsub_rn(hi, lo); my_row = o; }
-            if (++cnt == 32) {
-                cle2_finish_row(a, T.down, my_row, par, my_range);
-                my_row = -1; cnt = 0;
+                lo = warp_min(lo); hi = warp_max(hi);
+                if (lane == cnt) my_range = sgn ? hi : __fsub_rn(hi, lo);
+                ++cnt;
             }
         }
-        if (my_row >= 0) cle2_finish_row(a, T.down, my_row, par, my_range);
+        if (my_r < k.nrows) cle2_finish_row(a, k, my_r, my_range, pre);
     } else if (L == 9) {                                     // thread per row, depthwise 3x3: all 9 loads in flight
         for (int r = threadIdx.x; r < k.nrows; r += kThreads) {
             const int o = k.row0 + r;
-            float *__restrict__ row = T.W + (int64_t)o * 9;
+            float *__restrict__ row = k.W + (int64_t)r * 9;
             float w[9];
 #pragma unroll
             for (int j = 0; j < 9; ++j) w[j] = row[j];
-            const float f = cs ? __ldg(sinv_up + cle2_cidx(T, o, 0)) : 1.0f;    // KK == 9: one channel per row
+            const float f = cs ? __ldg(sinv_up + cle2_cidx(k, o, 0)) : 1.0f;    // KK == 9: one channel per row
+            const Cle2RowPre pre = cle2_prefetch_row(a, k, r, par);
             float lo = INFINITY, hi = -INFINITY;
 #pragma unroll
             for (int j = 0; j < 9; ++j) {
                 float v = w[j];
                 if (cs) {
-                    const float fj = (T.KK == 9) ? f : __ldg(sinv_up + cle2_cidx(T, o, j));
+                    const float fj = (k.KK == 9) ? f : __ldg(sinv_up + cle2_cidx(k, o, j));
                     v = __fmul_rn(v, fj); row[j] = v;
                 }
                 if (sgn) v = fabsf(v);
                 lo = fminf(lo, v); hi = fmaxf(hi, v);
             }
-            cle2_finish_row(a, T.down, o, par, sgn ? hi : __fsub_rn(hi, lo));
+            cle2_finish_row(a, k, r, sgn ? hi : __fsub_rn(hi, lo), pre);
         }
-    } else {                                                 // thread per row (first conv and other short rows)
+    } else {                                                 // thread per row (rows shorter than 9)
         for (int r = threadIdx.x; r < k.nrows; r += kThreads) {
             const int o = k.row0 + r;
-            float *row = T.W + (int64_t)o * L;
+            float *row = k.W + (int64_t)r * L;
+            const Cle2RowPre pre = cle2_prefetch_row(a, k, r, par);
             float lo = INFINITY, hi = -INFINITY;
             for (int j = 0; j < L; ++j) {
                 float v = row[j];
-                if (cs) { v = __fmul_rn(v, __ldg(sinv_up + cle2_cidx(T, o, j))); row[j] = v; }
+                if (cs) { v = __fmul_rn(v, __ldg(sinv_up + cle2_cidx(k, o, j))); row[j] = v; }
                 if (sgn) v = fabsf(v);
                 lo = fminf(lo, v); hi = fmaxf(hi, v);
             }
-            cle2_finish_row(a, T.down, o, par, sgn ? hi : __fsub_rn(hi, lo));
+            cle2_finish_row(a, k, r, sgn ? hi : __fsub_rn(hi, lo), pre);
         }
     }
 }
 
 // ---- "cols" pass: optional row scaling (s of the down pair) or column scaling (tail), metric, W_old, next column ranges.
 // init: prologue -- no scaling, no metric, W_old <- W, column ranges into parity `par_next`.
-__device__ void cle2_cols_pass(const Cle2Args &a, const DfqCleTask &k, int par_next, bool init, double *acc,
-                               double *smd) {
-    const DfqCleTensor &T = a.tensors[k.tensor];
-    const bool rs = !init && T.down >= 0;
-    const bool cs = !init && T.down < 0 && T.up >= 0;
-    const bool cr = T.up >= 0;                               // column ranges wanted (T is some pair's W2)
+__device__ void cle2_cols_pass(const Cle2Args &a, const Cle2Fat &k, int par, int par_next, bool init, double *smd) {
+    const bool rs = !init && k.down >= 0;
+    const bool cs = !init && k.down < 0 && k.up >= 0;
+    const bool cr = k.up >= 0;                               // column ranges wanted (the tensor is some pair's W2)
     const bool sgn = a.is_signed;
-    const int L = T.row_len;
-    const float *__restrict__ s_rows = rs ? a.r1 + a.chan_off[T.down] + k.row0 : nullptr;
-    const float *__restrict__ sinv_up = cs ? a.r1 + a.total_C + a.chan_off[T.up] : nullptr;
+    const int L = k.L;
+    const float *__restrict__ s_rows = k.s_tab;
+    const float *__restrict__ sinv_up = k.sinv_up;
     unsigned *r2lo = nullptr, *r2hi = nullptr;
     if (cr) {
-        r2lo = a.r2 + (size_t)par_next * 2 * a.total_C + a.chan_off[T.up];
+        r2lo = k.r2_up + (size_t)par_next * 2 * a.total_C;
         r2hi = r2lo + a.total_C;
     }
     double part = 0.0;
-    const bool one_group = T.Og >= T.O;
+    const bool one_group = k.Og >= k.O;
     constexpr int U = 8;                                     // loads in flight per thread before any store
     if (L >= 128 && one_group) {                             // 2-D tile: 32 rows x 64 columns, 8 rows per thread
-        const int j = (k.kind >> 8) * kC2Strip + (threadIdx.x & (kC2Strip - 1));
+        const int j = k.strip * kC2Strip + (threadIdx.x & (kC2Strip - 1));
         const int rg = threadIdx.x / kC2Strip;               // 4 row groups
         if (j < L) {
-            const int c = (T.KK == 1) ? j : j / T.KK;
-            float *__restrict__ wp = T.W + (int64_t)k.row0 * L + j;
-            float *__restrict__ op = T.W_old + (int64_t)k.row0 * L + j;
+            const int c = (k.KK == 1) ? j : j / k.KK;
+            float *__restrict__ wp = k.W + (threadIdx.x & (kC2Strip - 1));
+            float *__restrict__ op = k.W_old + (threadIdx.x & (kC2Strip - 1));
             float w[U], wo[U], sr[U];
             const float cf = cs ? __ldg(sinv_up + c) : 1.0f;
 #pragma unroll
@@ -238,7 +289,7 @@ __device__ void cle2_cols_pass(const Cle2Args &a, const DfqCleTask &k, int par_n
                 const bool ok = r < k.nrows;
                 w[u] = ok ? wp[(int64_t)r * L] : 0.0f;
                 wo[u] = (ok && !init) ? op[(int64_t)r * L] : 0.0f;
-                sr[u] = (ok && rs) ? __ldg(s_rows + r) : 1.0f;
+                sr[u] = (ok && rs) ? s_rows[r] : 1.0f;
             }
             float lo = INFINITY, hi = -INFINITY;
 #pragma unroll
@@ -256,16 +307,16 @@ __device__ void cle2_cols_pass(const Cle2Args &a, const DfqCleTask &k, int par_n
             }
             if (cr && hi >= lo) { atomicMax(r2lo + c, enc_ordered(-lo)); atomicMax(r2hi + c, enc_ordered(hi)); }
         }
-    } else if (L == 9 && T.KK == 9 && T.Og == 1 && T.I2 == 1) {     // depthwise 3x3: the row is its own "column"
+    } else if (L == 9 && k.KK == 9 && k.Og == 1 && k.I2 == 1) {     // depthwise 3x3: the row is its own "column"
         for (int r = threadIdx.x; r < k.nrows; r += kThreads) {
             const int o = k.row0 + r;
-            float *__restrict__ wp = T.W + (int64_t)o * 9;
-            float *__restrict__ op = T.W_old + (int64_t)o * 9;
+            float *__restrict__ wp = k.W + (int64_t)r * 9;
+            float *__restrict__ op = k.W_old + (int64_t)r * 9;
             float w[9], wo[9];
 #pragma unroll
             for (int j = 0; j < 9; ++j) { w[j] = wp[j]; wo[j] = init ? 0.0f : op[j]; }
             float f = 1.0f;
-            if (rs) f = __ldg(s_rows + r);
+            if (rs) f = s_rows[r];
             if (cs) f = __ldg(sinv_up + o);
             float lo = INFINITY, hi = -INFINITY;
 #pragma unroll
@@ -282,8 +333,8 @@ __device__ void cle2_cols_pass(const Cle2Args &a, const DfqCleTask &k, int par_n
     } else {                                                 // short rows or grouped: flat, per-element column atomics
         const int n = k.nrows * L;
         const float inv_L = 1.0f / (float)L;
-        float *__restrict__ wp = T.W + (int64_t)k.row0 * L;
-        float *__restrict__ op = T.W_old + (int64_t)k.row0 * L;
+        float *__restrict__ wp = k.W;
+        float *__restrict__ op = k.W_old;
         for (int eb = threadIdx.x; eb < n; eb += U * kThreads) {
             float w[U], wo[U], fs[U];
             int cc[U];
@@ -294,9 +345,9 @@ __device__ void cle2_cols_pass(const Cle2Args &a, const DfqCleTask &k, int par_n
                 w[u] = ok ? wp[e] : 0.0f;
                 wo[u] = (ok && !init) ? op[e] : 0.0f;
                 const int r = (int)(((float)e + 0.5f) * inv_L), j = e - r * L;
-                cc[u] = (ok && (cs || cr)) ? cle2_cidx(T, k.row0 + r, j) : 0;
+                cc[u] = (ok && (cs || cr)) ? cle2_cidx(k, k.row0 + r, j) : 0;
                 fs[u] = 1.0f;
-                if (ok && rs) fs[u] = __ldg(s_rows + r);
+                if (ok && rs) fs[u] = s_rows[r];
                 if (ok && cs) fs[u] = __ldg(sinv_up + cc[u]);
             }
 #pragma unroll
@@ -323,7 +374,7 @@ __device__ void cle2_cols_pass(const Cle2Args &a, const DfqCleTask &k, int par_n
             double t = 0.0;
 #pragma unroll
             for (int w = 0; w < kWarps; ++w) t += smd[w];
-            atomicAdd(acc + T.layer, t);
+            atomicAdd(k.acc + (size_t)par * a.n_tensors, t);
         }
     }
 }
@@ -340,7 +391,7 @@ cle2_kernel(Cle2Args a) {
     for (int i = gtid; i < 2 * a.n_tensors; i += gsize) a.acc[i] = 0.0;
     grid.sync();
     for (int t = a.n_tasks + blockIdx.x; t < a.n_tasks + a.n_init; t += gridDim.x)   // old_graph = deepcopy, :83
-        cle2_cols_pass(a, a.tasks[t], 0, true, nullptr, smd);
+        cle2_cols_pass(a, a.fat[t], 0, 0, true, smd);
     grid.sync();
 
     double diff = 1e8;                                // :67
@@ -359,11 +410,11 @@ cle2_kernel(Cle2Args a) {
             // (phase 0 holds no "cols" pass, so the zeroing above is ordered before every atomic by its barrier)
             unsigned long long worst = 0, worst_id = 0;
             for (int t = a.phase_begin[ph] + blockIdx.x; t < a.phase_begin[ph + 1]; t += gridDim.x) {
-                const DfqCleTask &k = a.tasks[t];
+                const Cle2Fat k = a.fat[t];
                 unsigned long long ta = 0, tb = 0;
                 if (stamp) asm volatile("mov.u64 %0, %globaltimer;" : "=l"(ta));
-                if ((k.kind & 0xff) == 0) cle2_rows_pass(a, k, par);
-                else cle2_cols_pass(a, k, par_next, false, acc, smd);
+                if (k.kind == 0) cle2_rows_pass(a, k, par);
+                else cle2_cols_pass(a, k, par, par_next, false, smd);
                 if (a.dbg && iters == 2) {                   // block-uniform
                     __syncthreads();
                     if (stamp) {
@@ -508,11 +559,13 @@ extern "C" int dfq_cle2_plan_host(const DfqClePair *pairs, int n_pairs, const Df
     return overflow ? (int)cudaErrorInvalidValue : 0;
 }
 
+extern "C" int64_t dfq_cle2_fat_bytes(int n_tasks_total) { return (int64_t)n_tasks_total * (int64_t)sizeof(Cle2Fat); }
+
 extern "C" int dfq_cle2_run(const DfqClePair *pairs_dev, int n_pairs, const DfqCleTensor *tensors_dev, int n_tensors,
                             const DfqCleTask *tasks_dev, int n_tasks, int n_init, const int32_t *phase_begin_host,
                             int n_phases, const int32_t *chan_off_dev, int total_C, float *r1_dev, unsigned *r2_dev,
                             double smin, double smax, int is_signed, float eps, double threshold, int count,
-                            int max_iters, double *acc_dev, void *result_dev, int blocks_per_sm, void *debug_dev, void *stream) {
+                            int max_iters, double *acc_dev, void *result_dev, int blocks_per_sm, void *fat_dev, void *debug_dev, void *stream) {
     if (n_phases > kC2MaxPhases || n_phases < 1) return (int)cudaErrorInvalidValue;
     Cle2Args a;
     a.pairs = pairs_dev; a.n_pairs = n_pairs; a.tensors = tensors_dev; a.n_tensors = n_tensors;
@@ -527,6 +580,10 @@ extern "C" int dfq_cle2_run(const DfqClePair *pairs_dev, int n_pairs, const DfqC
     a.res_i = (int *)result_dev;
     a.res_d = (double *)((char *)result_dev + 8);
     a.dbg = (unsigned long long *)debug_dev;
+    a.fat = (Cle2Fat *)fat_dev;
+    if (!fat_dev) return (int)cudaErrorInvalidValue;
+    cle2_expand_kernel<<<(n_tasks + n_init + 127) / 128, 128, 0, (cudaStream_t)stream>>>(a);
+    g_launches += 1;
     int occ = 0;
     cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, cle2_kernel, kThreads, 0);
     if (e != cudaSuccess) return (int)e;

@@ -35,13 +35,17 @@ def merge_batchnorm(model, graph, bottoms, targ_type=[QConv2d]):
         dev = pairs[0][0].weight.device
         total = sum(conv.weight.size(0) for conv, _ in pairs)
         stash = torch.empty(2, total, dtype=torch.float32, device=dev)     # all fake_weight | all fake_bias
+        missing = sum(conv.weight.size(0) for conv, _ in pairs if conv.bias is None)
+        zeros = torch.zeros(missing, dtype=torch.float32, device=dev) if missing else None   # one fill for all
+        zoff = 0
         descs = (L.DfqMergeDesc * len(pairs))()
         off = 0
         for d, (conv, bn) in zip(descs, pairs):
             W = conv.weight.data
             O = W.size(0)
             if conv.bias is None:                   # :262-263
-                conv.bias = nn.Parameter(data=torch.zeros(O, dtype=torch.float32, device=dev), requires_grad=False)
+                conv.bias = nn.Parameter(data=zeros[zoff:zoff + O], requires_grad=False)
+                zoff += O
             fake_w, fake_b = stash[0, off:off + O], stash[1, off:off + O]
             off += O
             d.W, d.b = L.dev_f32(W, "weight"), L.dev_f32(conv.bias.data, "bias")

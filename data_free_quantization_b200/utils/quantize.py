@@ -146,10 +146,14 @@ def sample_minmax_mean(x):
 class QuantMeasure(nn.Module):
     """utils/quantize.py:94-126 -- activation range tracker + fake-quant of the activation."""
 
-    def __init__(self, update_stat=False, num_bits=8, momentum=0.1):
+    def __init__(self, update_stat=False, num_bits=8, momentum=0.1, *, _storage=None):
+        """`_storage` (internal): a zeroed [2] tensor whose halves become running_min / running_max, so that a whole
+        model's measures can live in one device allocation (set_layer_bits)."""
         super(QuantMeasure, self).__init__()
-        self.register_buffer('running_min', torch.zeros(1))
-        self.register_buffer('running_max', torch.zeros(1))
+        if _storage is None:
+            _storage = torch.zeros(2)
+        self.register_buffer('running_min', _storage[0:1])
+        self.register_buffer('running_max', _storage[1:2])
         self.momentum = momentum
         self.num_bits = num_bits
         self.update_stat = update_stat
@@ -278,11 +282,16 @@ def set_layer_bits(graph, bits_weight=8, bits_activation=8, bits_bias=16, targ_t
     (first positional argument), not `num_bits`."""
     print("Setting num_bits for targ layers...")
     assert targ_type != None, "targ_type cannot be None"
+    with_quant = [graph[idx] for idx in graph if type(graph[idx]) in targ_type and hasattr(graph[idx], 'quant')]
+    pool = None
+    if with_quant:          # one zeroed device table for all the new measures instead of 2 tiny copies per layer
+        pool = torch.zeros(len(with_quant), 2, dtype=torch.float32, device=with_quant[0].quant.running_min.device)
+    slot = 0
     for idx in graph:
         if type(graph[idx]) in targ_type:
             if hasattr(graph[idx], 'quant'):
-                old = graph[idx].quant
-                graph[idx].quant = QuantMeasure(bits_activation).to(old.running_min.device)
+                graph[idx].quant = QuantMeasure(bits_activation, _storage=pool[slot])
+                slot += 1
             if hasattr(graph[idx], 'num_bits'):
                 graph[idx].num_bits = bits_weight
             if hasattr(graph[idx], 'num_bits_bias'):

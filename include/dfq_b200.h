@@ -23,7 +23,7 @@
 extern "C" {
 #endif
 
-#define DFQ_ABI_VERSION 8
+#define DFQ_ABI_VERSION 9
 
 #if defined(__GNUC__)
 #pragma GCC visibility push(default)   /* the library is built with -fvisibility=hidden */
@@ -269,7 +269,9 @@ int dfq_cle2_run(const DfqClePair *pairs_dev, int n_pairs, const DfqCleTensor *t
                  const DfqCleTask *tasks_dev, int n_tasks, int n_init, const int32_t *phase_begin_host, int n_phases,
                  const int32_t *chan_off_dev, int total_C, float *r1_dev, unsigned *r2_dev, double smin, double smax,
                  int is_signed, float eps, double threshold, int count, int max_iters, double *acc_dev,
-                 void *result_dev, int blocks_per_sm, void *debug_dev, void *stream);
+                 void *result_dev, int blocks_per_sm, void *fat_dev, void *debug_dev, void *stream);
+/* bytes of fat_dev (16-byte aligned scratch for the expanded task records) for n_tasks + n_init tasks */
+int64_t dfq_cle2_fat_bytes(int n_tasks_total);
 
 /* ---- (c) bias absorption (+ optional weight clip): bias_absorption.py:9-80, clip_weight.py:4-33 */
 int dfq_absorb_plan_host(DfqAbsorbPair *pairs_host, int n_pairs, int *total_rows);
