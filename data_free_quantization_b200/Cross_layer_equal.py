@@ -96,6 +96,10 @@ def cross_layer_equalization(graph, relations, Target_list, s_min_max=[1e-8, 1e8
         acc = torch.empty(2 * len(ws), dtype=torch.float64, device=dev)
         nbytes = int(L.lib().dfq_cle_result_bytes(max_iters + 1))
         result = torch.zeros(nbytes, dtype=torch.uint8, device=dev)
+        ev0 = ev1 = None
+        if return_info:                 # device time of the loop itself (CUDA events on the launch stream)
+            ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            ev0.record()
         impl = "stream" if os.environ.get("DFQ_CLE_IMPL", "stream") == "stream" and _run_streaming(
             pairs, n, pairs_dev, layers, len(ws), s_min_max, signed, eps, Treshhold, Count, max_iters, acc, result,
             dev) else "units"
@@ -107,11 +111,13 @@ def cross_layer_equalization(graph, relations, Target_list, s_min_max=[1e-8, 1e8
                                         result.data_ptr(), L.stream()), "dfq_cle_run")
         if not return_info:
             return None
+        ev1.record()
         host = result.cpu().numpy()
         iters = int(host[:4].view("int32")[0])
         diffs = host[8:].view("float64")
         return {"iters": iters, "stall": int(host[4:8].view("int32")[0]), "diff": float(diffs[0]),
-                "diffs": diffs[1:1 + iters].tolist(), "stages": ns.value, "impl": impl}
+                "diffs": diffs[1:1 + iters].tolist(), "stages": ns.value, "impl": impl,
+                "kernel_ms": ev0.elapsed_time(ev1)}
 
 
 def _run_streaming(pairs, n, pairs_dev, layers, n_layers, s_min_max, signed, eps, Treshhold, Count, max_iters, acc,

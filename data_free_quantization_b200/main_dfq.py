@@ -70,8 +70,13 @@ def run_dfq_steps(model, graph, bottoms, args, targ_pair=(QuantConv2d, QuantLine
     res = []
     if args.equalize:
         res = create_relation(graph, bottoms, targ_layer, delete_single=False)
-        timed("cross_layer_equalization",
-              lambda: cross_layer_equalization(graph, res, targ_layer, Save_state=False, Treshhold=2e-7))
+        info = timed("cross_layer_equalization",
+                     lambda: cross_layer_equalization(graph, res, targ_layer, Save_state=False, Treshhold=2e-7,
+                                                      return_info=timings is not None))
+        if timings is not None and info:
+            timings["cle_kernel"] = info["kernel_ms"]
+            timings["cle_iters"] = info["iters"]
+            timings["cle_impl"] = info["impl"]
     if args.absorption:
         timed("bias_absorption", lambda: bias_absorption(graph, res, bottoms, N=3, visualize=args.visualize))
     if args.quantize:
