@@ -57,6 +57,23 @@ def cross_layer_equalization(graph, relations, Target_list, s_min_max=[1e-8, 1e8
         keep = []
         metric = OrderedDictNoDup()
         dev = None
+        # one fill for every missing bias / scale vector instead of a tiny launch per relation
+        dev = graph[relations[0].get_idxs()[0]].weight.device
+        need_b = [graph[r.get_idxs()[0]] for r in relations if graph[r.get_idxs()[0]].bias is None]
+        need_b = list({id(m): m for m in need_b}.values())
+        need_s = [r for r in relations if r.S is None]
+        zeros = torch.zeros(sum(m.weight.size(0) for m in need_b), dtype=torch.float32, device=dev)
+        ones = torch.ones(sum(graph[r.get_idxs()[0]].weight.size(0) for r in need_s), dtype=torch.float32, device=dev)
+        off = 0
+        for m in need_b:                            # Cross_layer_equal.py:93-94
+            c = m.weight.size(0)
+            m.bias = nn.Parameter(data=zeros[off:off + c], requires_grad=False)
+            off += c
+        off = 0
+        for r in need_s:
+            c = graph[r.get_idxs()[0]].weight.size(0)
+            r.S = ones[off:off + c]
+            off += c
         for i, rel in enumerate(relations):
             first, second, bn = rel.get_idxs()
             l1, l2, bnm = graph[first], graph[second], graph[bn]

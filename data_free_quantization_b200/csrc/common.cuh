@@ -149,6 +149,7 @@ __device__ __forceinline__ float rint_small(float c) {
 struct QuantConsts {
     float neg_min, scale, rscale, qmin, qmax, add_back, clip_lo, clip_hi;
     float t_lo, t_hi;                   // numerator clamp: quotients beyond [qmin-2, qmax+2] clamp to the ends anyway
+    float amb;                          // |quotient - code| above this: too close to a tie for the reciprocal estimate
     int fast;                           // 0: exotic scale or > 22-bit grid -> __fdiv_rn / rintf path
 };
 
@@ -159,6 +160,7 @@ __device__ __forceinline__ QuantConsts make_consts(const DfqQuantParams &p, floa
     c.clip_lo = clip_lo; c.clip_hi = clip_hi;
     c.t_lo = __fmul_rn(p.qmin - 2.0f, p.scale);
     c.t_hi = __fmul_rn(p.qmax + 2.0f, p.scale);
+    c.amb = 0.5f - (2e-5f + 1e-6f * fmaxf(fabsf(p.qmax), fabsf(p.qmin)));
     c.fast = (p.qmax < 4194304.0f && p.qmin > -4194304.0f && p.scale >= 1e-8f && p.scale < 1e25f);
     return c;
 }
@@ -195,6 +197,27 @@ __device__ __forceinline__ float fake_quant_elem(float x, const QuantConsts &c, 
     float y = __fadd_rn(__fmul_rn(q, c.scale), c.add_back);
     if (x != x) { q = x; y = x; }                           // torch.clamp propagates NaN
     return y;
+}
+
+// The integer code of utils/quantize.py:72-74 as an integer-valued float, for the eval kernels that quantise on load
+// (instruction-bound).  t * RN(1/s) is within 2 ulp of the correctly rounded quotient, so both round to the same
+// integer unless the estimate sits within a few ulp of a tie; only then (probability ~3e-4 per element) the exact
+// Markstein division decides.  Same results as fake_quant_elem for every finite input, 9 instead of 15 operations.
+__device__ __forceinline__ float quant_code(float x, const QuantConsts &c) {
+    const float t = __fadd_rn(x, c.neg_min);
+    if (c.fast) {                                           // block-uniform
+        const float cl = fminf(fmaxf(__fmul_rn(t, c.rscale), c.qmin), c.qmax);
+        float q = rint_small(cl);
+        if (fabsf(__fsub_rn(cl, q)) > c.amb) {
+            const float tc = fminf(fmaxf(t, c.t_lo), c.t_hi);
+            q = rint_small(fminf(fmaxf(div_const_rn(tc, c.scale, c.rscale), c.qmin), c.qmax));
+        }
+        return q;
+    }
+    return rintf(fminf(fmaxf(__fdiv_rn(t, c.scale), c.qmin), c.qmax));
+}
+__device__ __forceinline__ float quant_dequant(float x, const QuantConsts &c) {     // :72-76, finite inputs
+    return __fadd_rn(__fmul_rn(quant_code(x, c), c.scale), c.add_back);
 }
 
 }  // namespace dfq

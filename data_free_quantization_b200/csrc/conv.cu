@@ -19,8 +19,7 @@ struct ConvArgs {
 };
 
 __device__ __forceinline__ float quant_or_pass(float v, const QuantConsts &c, bool on) {
-    float q;
-    return on ? fake_quant_elem(v, c, q) : v;
+    return on ? quant_dequant(v, c) : v;
 }
 
 // block-level min/max of `lo/hi` into stats[n] (encoded max(-y), max(y))

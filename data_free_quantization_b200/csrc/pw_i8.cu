@@ -76,17 +76,22 @@ __device__ __forceinline__ void umma_commit(uint32_t bar) {
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 
-// The integer code of utils/quantize.py:72-74 in the low byte of the result (block-uniform fast / exact paths).
+// The integer code of utils/quantize.py:72-74 in the low byte of the result.
+// quant_code() of common.cuh with the magic-number add kept: 1.5 * 2^23 + q has q in its mantissa's low byte, so no
+// float-to-int conversion is needed.
 __device__ __forceinline__ uint32_t quant_code_bits(float x, const QuantConsts &c) {
-    float t = __fadd_rn(x, c.neg_min);
-    if (c.fast) {
-        float tc = fminf(fmaxf(t, c.t_lo), c.t_hi);
-        float d = div_const_rn(tc, c.scale, c.rscale);
-        float cl = fminf(fmaxf(d, c.qmin), c.qmax);
-        return __float_as_uint(__fadd_rn(cl, 12582912.0f));        // 1.5 * 2^23 + q: the mantissa's low byte is q
+    const float t = __fadd_rn(x, c.neg_min);
+    if (c.fast) {                                           // block-uniform
+        const float magic = 12582912.0f;
+        const float cl = fminf(fmaxf(__fmul_rn(t, c.rscale), c.qmin), c.qmax);
+        float m = __fadd_rn(cl, magic);
+        if (fabsf(__fsub_rn(cl, __fadd_rn(m, -magic))) > c.amb) {          // within a few ulp of a tie: exact division
+            const float tc = fminf(fmaxf(t, c.t_lo), c.t_hi);
+            m = __fadd_rn(fminf(fmaxf(div_const_rn(tc, c.scale, c.rscale), c.qmin), c.qmax), magic);
+        }
+        return __float_as_uint(m);
     }
-    float cl = fminf(fmaxf(__fdiv_rn(t, c.scale), c.qmin), c.qmax);
-    return (uint32_t)__float2int_rn(cl);
+    return (uint32_t)__float2int_rn(fminf(fmaxf(__fdiv_rn(t, c.scale), c.qmin), c.qmax));
 }
 
 __global__ void __launch_bounds__(kThreads)

@@ -64,15 +64,30 @@ def main():
     ap.add_argument("--skip-eval", action="store_true")
     ap.add_argument("--bits", type=int, default=8)
     ap.add_argument("--cle-cache", default=None, help="cache of the reference's post-CLE state (dev aid)")
+    ap.add_argument("--model", default="mobilenetv2", choices=["mobilenetv2", "deeplab"])
     args = ap.parse_args()
     ns = RH.import_reference()
     torch.manual_seed(0)
-    model = ns.mobilenet_v2(None)
-    sd = synthetic_state_dict(model, seed=0, bn_seed=1)
-    model.load_state_dict(sd)
-    run = RH.RefRun(ns, model, torch.ones(4, 3, 224, 224))
+    if args.model == "deeplab":
+        # BASELINE.json configs[3].  The reference model registers the backbone twice more under aliasing names
+        # (backbone/mobilenet.py:113-114), so the seeded state comes from our alias-free twin (same names, same
+        # shapes, bit-identical forward) and is loaded non-strictly; only alias keys may be missing.
+        from modeling.segmentation.deeplab import DeepLab as RefDeepLab
+        from data_free_quantization_b200.modeling.deeplab import DeepLab
+        sd = synthetic_state_dict(DeepLab(), seed=0, bn_seed=1)
+        model = RefDeepLab(sync_bn=False)
+        missing, unexpected = model.load_state_dict(sd, strict=False)
+        assert not unexpected and all("level_features" in k for k in missing), (missing[:3], unexpected[:3])
+        run = RH.RefRun(ns, model, torch.ones(1, 3, 129, 129))    # the graph does not depend on the trace size
+        args.skip_eval = True
+    else:
+        model = ns.mobilenet_v2(None)
+        sd = synthetic_state_dict(model, seed=0, bn_seed=1)
+        model.load_state_dict(sd)
+        run = RH.RefRun(ns, model, torch.ones(4, 3, 224, 224))
+    out_stem = {"mobilenetv2": "mobilenetv2_dfq", "deeplab": "deeplab_dfq"}[args.model]
 
-    gold = {"model": "mobilenetv2", "seed": 0, "bn_seed": 1, "torch": torch.__version__,
+    gold = {"model": args.model, "seed": 0, "bn_seed": 1, "torch": torch.__version__,
             "parity": {}, "steps": {}, "timing_s": {}}
     small = {}
     st = to_np_state(sd)
@@ -213,9 +228,9 @@ def main():
         gold["quant_minmax_after_eval"] = acts
 
     os.makedirs(os.path.join(ROOT, "tests", "golden"), exist_ok=True)
-    with open(os.path.join(ROOT, "tests", "golden", "mobilenetv2_dfq.json"), "w") as f:
+    with open(os.path.join(ROOT, "tests", "golden", out_stem + ".json"), "w") as f:
         json.dump(gold, f, indent=1)
-    np.savez_compressed(os.path.join(ROOT, "tests", "golden", "mobilenetv2_dfq.npz"), **small)
+    np.savez_compressed(os.path.join(ROOT, "tests", "golden", out_stem + ".npz"), **small)
     print("golden written", {k: round(v, 3) for k, v in gold["timing_s"].items()})
 
 

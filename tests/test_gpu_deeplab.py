@@ -1,0 +1,112 @@
+"""GPU: BASELINE.json configs[3] -- the DFQ weight-side pipeline on DeepLabV3+ (MobileNetV2 backbone: 61 target
+layers, 35 relations, dense 3x3 / dilated / depthwise / pointwise weights, F.pad / interpolate / cat in the graph)
+against the golden digests taken from the UNMODIFIED reference (tests/golden/deeplab_dfq.*, oracle/gen_golden.py
+--model deeplab).  Same bars as the MobileNetV2 pipeline test: merge / CLE (weights, S, iteration count) /
+quantised weights, biases and u8 codes / clip bit-exact, absorption 1e-5, QuantMeasure ranges equal."""
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+import torch.nn as nn
+
+from helpers import names_of, rel_err, sha, snapshot
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+@pytest.fixture(scope="module")
+def dgold():
+    with open(os.path.join(GOLD, "deeplab_dfq.json")) as f:
+        return json.load(f), np.load(os.path.join(GOLD, "deeplab_dfq.npz"))
+
+
+@pytest.fixture(scope="module")
+def run():
+    from data_free_quantization_b200 import graph as G
+    from data_free_quantization_b200.Cross_layer_equal import cross_layer_equalization
+    from data_free_quantization_b200.fixtures import synthetic_state_dict
+    from data_free_quantization_b200.modeling.deeplab import DeepLab
+    from data_free_quantization_b200.utils import quantize as Q
+    from data_free_quantization_b200.utils.layer_transform import merge_batchnorm
+    from data_free_quantization_b200.utils.relation import create_relation
+    torch.manual_seed(0)
+    model = DeepLab()
+    model.load_state_dict(synthetic_state_dict(model, seed=0, bn_seed=1))
+    model = model.eval().to(DEV)
+    targ = [Q.QuantNConv2d, Q.QuantNLinear]
+    md = {0: [(nn.ReLU6, nn.ReLU)], 1: [(nn.Conv2d, targ[0]), (nn.Linear, targ[1])]}
+    model, tr = G.switch_layers(model, G.TorchTransformer(), torch.ones(1, 3, 129, 129, device=DEV), md,
+                                ignore_layer=[Q.QuantMeasure], quant_op=True)
+    graph, bottoms = tr.log.getGraph(), tr.log.getBottoms()
+    merge_batchnorm(model, graph, bottoms, targ)
+    out = {"model": model, "graph": graph, "bottoms": bottoms, "targ": targ}
+    out["merge"] = {k: sha(v) for k, v in snapshot(model, graph, targ).items()}
+    rels = create_relation(graph, bottoms, targ)
+    info = cross_layer_equalization(graph, rels, targ, Save_state=False, Treshhold=2e-7, return_info=True)
+    out["rels"], out["info"] = rels, info
+    out["cle"] = {k: sha(v) for k, v in snapshot(model, graph, targ).items()}
+    return out
+
+
+def test_graph_and_relations_match_reference(dgold, run):
+    gold, _ = dgold
+    names = names_of(run["model"])
+    assert len(run["graph"]) == len(gold["graph"]) == 201
+    mine = [[names[a], names[b], names[c]] for a, b, c in (r.get_idxs() for r in run["rels"])]
+    assert mine == [r[:3] for r in gold["topo"]["relations"]]
+    assert [names[k] for k, m in run["graph"].items() if type(m) in run["targ"]] == gold["topo"]["targets"]
+
+
+def test_merge_and_cle_bit_exact(dgold, run):
+    gold, npz = dgold
+    for k, d in gold["steps"]["merge_batchnorm"].items():
+        assert run["merge"][k] == d, k
+    assert run["info"]["iters"] == gold["cle_iters"]
+    np.testing.assert_allclose(run["info"]["diffs"], gold["cle_diffs"], rtol=1e-9)
+    for k, d in gold["steps"]["cross_layer_equalization"].items():
+        assert run["cle"][k] == d, k
+    names = names_of(run["model"])
+    for r in run["rels"]:
+        a, b, _ = r.get_idxs()
+        assert r.S.cpu().numpy().tobytes() == npz[f"S/{names[a]}->{names[b]}"].tobytes()
+
+
+def test_absorb_quantize_minmax_clip(dgold, run):
+    from data_free_quantization_b200.bias_absorption import bias_absorption
+    from data_free_quantization_b200.clip_weight import clip_weight
+    from data_free_quantization_b200.utils.layer_transform import (merge_batchnorm, quantize_targ_layer,
+                                                                   set_quant_minmax)
+    from data_free_quantization_b200.utils.quantize import set_layer_bits
+    gold, npz = dgold
+    model, graph, bottoms, targ = run["model"], run["graph"], run["bottoms"], run["targ"]
+    bias_absorption(graph, run["rels"], bottoms, N=3)
+    snap = snapshot(model, graph, targ)
+    mods = dict(model.named_modules())
+    for k in npz.files:
+        if k.startswith("absorb/"):
+            name = k[len("absorb/"):]
+            assert rel_err(npz[k], snap[name]) <= 1e-5, name
+            mod, attr = name.rsplit(".", 1)          # carry the reference's values forward (gen_golden.py)
+            getattr(mods[mod], attr).data.copy_(torch.from_numpy(npz[k]))
+    set_layer_bits(graph, 8, 8, 8, targ)
+    merge_batchnorm(model, graph, bottoms, targ)
+    codes = quantize_targ_layer(graph, 8, 8, targ, want_codes=True)
+    snap = snapshot(model, graph, targ)
+    for k, d in gold["steps"]["quantize_targ_layer"].items():
+        assert sha(snap[k]) == d, k
+    names = names_of(model)
+    for key, (c, _rng) in codes.items():
+        assert sha(c.cpu().numpy()) == gold["codes"][names[key]], names[key]
+    set_quant_minmax(graph, bottoms, verbose=False)
+    for key, m in graph.items():
+        if type(m) in targ:
+            lo, hi = gold["quant_minmax"][names[key]]
+            assert float(m.quant.running_min) == lo and float(m.quant.running_max) == hi, names[key]
+    clip_weight(graph, [-15, 15], targ)
+    snap = snapshot(model, graph, targ)
+    for k, d in gold["steps"]["final"].items():
+        assert sha(snap[k]) == d, k
