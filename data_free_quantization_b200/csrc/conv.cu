@@ -161,16 +161,25 @@ dwconv3x3_stream_kernel(DwArgs a) {
     float lo = INFINITY, hi = -INFINITY;
     const int per_c = nr * a.G4;
     const float inv_per_c = 1.0f / (float)per_c;
+    float wreg[9], bv = 0.0f;
+#pragma unroll
+    for (int t = 0; t < 9; ++t) wreg[t] = __ldg(a.w + (int64_t)c0 * 9 + t);
+    if (a.bias) bv = __ldg(a.bias + c0);
     for (int it = tid; it < nc * per_c; it += kThreads) {
         int c = 0, rem = it;
         if (nc > 1) { c = fdiv_small(it, inv_per_c); rem = it - c * per_c; }
         const int orow = fdiv_small(rem, a.inv_G4), ox0 = (rem - orow * a.G4) * 4;
-        const float *wp = a.w + (int64_t)(c0 + c) * 9;
+        if (nc > 1) {                                         // one channel per block keeps its 9 weights in registers
+            const float *wp = a.w + (int64_t)(c0 + c) * 9;
+#pragma unroll
+            for (int t = 0; t < 9; ++t) wreg[t] = __ldg(wp + t);
+            bv = a.bias ? __ldg(a.bias + c0 + c) : 0.0f;
+        }
         float acc[4] = {0.f, 0.f, 0.f, 0.f};
         const float *srow = smem + c * plane + (orow * a.stride) * a.RS;
 #pragma unroll
         for (int i = 0; i < 3; ++i) {
-            const float w0 = __ldg(wp + 3 * i), w1 = __ldg(wp + 3 * i + 1), w2 = __ldg(wp + 3 * i + 2);
+            const float w0 = wreg[3 * i], w1 = wreg[3 * i + 1], w2 = wreg[3 * i + 2];
             const float *s = srow + i * a.RS;
             if (a.stride == 1) {
                 const float L = s[ox0 + 3], R = s[ox0 + 8];
@@ -189,7 +198,6 @@ dwconv3x3_stream_kernel(DwArgs a) {
                 acc[3] = __fmaf_rn(M1.w, w2, __fmaf_rn(M1.z, w1, __fmaf_rn(M1.y, w0, acc[3])));
             }
         }
-        const float bv = a.bias ? __ldg(a.bias + c0 + c) : 0.0f;
         float *yp = a.y + (((int64_t)n * a.C + c0 + c) * a.OH + r0 + orow) * a.OW + ox0;
 #pragma unroll
         for (int t = 0; t < 4; ++t) {
@@ -270,6 +278,106 @@ conv_direct_kernel(ConvArgs a) {
                 if (a.relu) r = fmaxf(r, 0.0f);
                 a.y[(((int64_t)n * a.O + o0 + t) * a.OH + r0 + orow) * a.OW + ocol] = r;
                 lo = fminf(lo, r); hi = fmaxf(hi, r);
+            }
+        }
+    }
+    if (a.stats) stats_flush(a.stats, n, lo, hi, red);
+}
+
+// Register-blocked form of the direct convolution for tiny C*kh*kw (the 3 -> 32, 3x3, stride 2 stem): the thread's
+// C*KH*KW quantised inputs live in registers, the weights are read as [tap][O] rows with 128-bit broadcast loads, 16
+// output channels accumulate at a time.  Same tap order per output as conv_direct_kernel.
+template <int C, int KH, int KW>
+__global__ void __launch_bounds__(kThreads)
+conv_direct_reg_kernel(ConvArgs a) {
+    constexpr int TAPS = C * KH * KW;
+    extern __shared__ __align__(16) float smem[];
+    __shared__ float red[2 * kWarps];
+    const int tid = threadIdx.x;
+    const int strip = blockIdx.x % a.strips, n = blockIdx.x / a.strips;
+    const int r0 = strip * a.rows, nr = min(a.rows, a.OH - r0);
+    const int in_r0 = r0 * a.stride - a.pad;
+    const int in_rows = (nr - 1) * a.stride + (KH - 1) * a.dil + 1;
+    const int pw = a.W + 2 * a.pad;
+    const int plane = in_rows * pw;
+    const int Op = (a.O + 3) & ~3;                      // weight row length, padded to 128-bit words
+    float *sw = smem;                                   // [TAPS][Op]
+    float *sb = smem + TAPS * Op;                       // [Op] bias
+    float *sx = sb + Op;                                // [C][in_rows][pw]
+    const bool on = a.slot != nullptr;
+    QuantConsts qc;
+    if (on) qc = consts_from_slot(*a.slot, a.bits, 0, 0.f, 0.f);
+    for (int idx = tid; idx < TAPS * Op; idx += kThreads) {
+        const int t = idx / Op, o = idx - t * Op;
+        sw[idx] = (o < a.O) ? __ldg(a.w + (int64_t)o * TAPS + t) : 0.0f;
+    }
+    for (int o = tid; o < Op; o += kThreads) sb[o] = (a.bias && o < a.O) ? __ldg(a.bias + o) : 0.0f;
+    {   // warp per input row: 128-bit loads, quantise, scalar stores behind the left pad; no per-element division
+        const int warp = tid >> 5, lane = tid & 31;
+        const bool vec = (a.W & 3) == 0 && (((uintptr_t)a.x) & 15) == 0;
+        for (int rid = warp; rid < C * in_rows; rid += kWarps) {
+            const int c = rid / in_rows, r = rid - c * in_rows;
+            const int gr = in_r0 + r;
+            float *dst = sx + c * plane + r * pw;
+            if (gr < 0 || gr >= a.H) {
+                for (int col = lane; col < pw; col += 32) dst[col] = 0.0f;
+                continue;
+            }
+            const float *src = a.x + (((int64_t)n * C + c) * a.H + gr) * a.W;
+            for (int col = lane; col < a.pad; col += 32) { dst[col] = 0.0f; dst[a.pad + a.W + col] = 0.0f; }
+            if (vec) {
+                for (int v4 = lane; v4 < (a.W >> 2); v4 += 32) {
+                    const float4 v = __ldg(reinterpret_cast<const float4 *>(src) + v4);
+                    float *d = dst + a.pad + 4 * v4;
+                    d[0] = quant_or_pass(v.x, qc, on); d[1] = quant_or_pass(v.y, qc, on);
+                    d[2] = quant_or_pass(v.z, qc, on); d[3] = quant_or_pass(v.w, qc, on);
+                }
+            } else {
+                for (int col = lane; col < a.W; col += 32) dst[a.pad + col] = quant_or_pass(__ldg(src + col), qc, on);
+            }
+        }
+    }
+    __syncthreads();
+    float lo = INFINITY, hi = -INFINITY;
+    const int outs = nr * a.OW;
+    for (int p = tid; p < outs; p += kThreads) {
+        const int orow = p / a.OW, ocol = p - orow * a.OW;
+        const float *s0 = sx + (orow * a.stride) * pw + ocol * a.stride;
+        float xin[TAPS];
+#pragma unroll
+        for (int c = 0; c < C; ++c)
+#pragma unroll
+            for (int i = 0; i < KH; ++i)
+#pragma unroll
+                for (int j = 0; j < KW; ++j) xin[(c * KH + i) * KW + j] = s0[c * plane + i * a.dil * pw + j * a.dil];
+        float *yp = a.y + (((int64_t)n * a.O) * a.OH + r0 + orow) * a.OW + ocol;
+        const int64_t ostride = (int64_t)a.OH * a.OW;
+        for (int o0 = 0; o0 < a.O; o0 += 16) {
+            float acc[16];
+#pragma unroll
+            for (int t = 0; t < 16; ++t) acc[t] = 0.0f;
+#pragma unroll
+            for (int t = 0; t < TAPS; ++t) {
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    if (o0 + 4 * q < Op) {
+                        const float4 w = *reinterpret_cast<const float4 *>(sw + t * Op + o0 + 4 * q);
+                        acc[4 * q] = __fmaf_rn(xin[t], w.x, acc[4 * q]);
+                        acc[4 * q + 1] = __fmaf_rn(xin[t], w.y, acc[4 * q + 1]);
+                        acc[4 * q + 2] = __fmaf_rn(xin[t], w.z, acc[4 * q + 2]);
+                        acc[4 * q + 3] = __fmaf_rn(xin[t], w.w, acc[4 * q + 3]);
+                    }
+                }
+            }
+#pragma unroll
+            for (int t = 0; t < 16; ++t) {
+                if (o0 + t < a.O) {
+                    float r = acc[t];
+                    if (a.bias) r = __fadd_rn(r, sb[o0 + t]);
+                    if (a.relu) r = fmaxf(r, 0.0f);
+                    yp[(o0 + t) * ostride] = r;
+                    lo = fminf(lo, r); hi = fmaxf(hi, r);
+                }
             }
         }
     }
@@ -455,10 +563,10 @@ extern "C" int dfq_qconv2d_f32(const DfqConvDesc *d, void *stream) {
         auto tile_bytes = [&](int rows, int cb) {
             return ((size_t)cb * ((rows - 1) * d->stride + 3) * w.RS + 8) * sizeof(float);
         };
-        // a strip of one plane (about 512 four-output items) or, for small planes, several whole planes
+        // a strip of one plane (about 1024 four-output items) or, for small planes, several whole planes
         int rows = OH, cb = 1;
-        if (OH * w.G4 > 768) rows = max(1, 512 / w.G4);
-        else cb = max(1, min(d->C_in, 512 / (OH * w.G4)));
+        if (OH * w.G4 > 1536) rows = max(1, 1024 / w.G4);
+        else cb = max(1, min(d->C_in, 1024 / (OH * w.G4)));
         while (tile_bytes(rows, cb) > 40 * 1024 && (cb > 1 || rows > 1)) { if (cb > 1) cb = (cb + 1) / 2; else rows = (rows + 1) / 2; }
         // whole planes of several channels must start on a 16-byte boundary for the vector path
         const bool vec = (d->W % 4) == 0 && ((uintptr_t)d->x % 16) == 0;
@@ -491,6 +599,25 @@ extern "C" int dfq_qconv2d_f32(const DfqConvDesc *d, void *stream) {
         auto smem_of = [&](int r) { return wbytes + (size_t)d->C_in * ((r - 1) * d->stride + (d->kh - 1) * d->dil + 1) * pw * sizeof(float); };
         while (smem_of(rows) > 96 * 1024 && rows > 1) rows = (rows + 1) / 2;
         if (smem_of(rows) > 96 * 1024) return (int)cudaErrorInvalidValue;   // large dense kxk: tensor-core path (not built yet)
+        if (d->C_in == 3 && d->kh == 3 && d->kw == 3) {      // the stem: register-blocked form
+            const int Op = (d->C_out + 3) & ~3;
+            int rr = max(1, 1024 / OW);
+            auto smem_reg = [&](int r) {
+                return ((size_t)27 * Op + Op + (size_t)3 * ((r - 1) * d->stride + 2 * d->dil + 1) * pw) * sizeof(float);
+            };
+            while (smem_reg(rr) > 64 * 1024 && rr > 1) rr = (rr + 1) / 2;
+            if (smem_reg(rr) <= 64 * 1024) {
+                a.rows = rr; a.cb = 0; a.strips = (OH + rr - 1) / rr;
+                static bool attr = false;
+                if (!attr) {
+                    cudaFuncSetAttribute(conv_direct_reg_kernel<3, 3, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+                    attr = true;
+                }
+                conv_direct_reg_kernel<3, 3, 3><<<(unsigned)(d->N * a.strips), kThreads, smem_reg(rr), st>>>(a);
+                g_launches += 1;
+                return (int)cudaGetLastError();
+            }
+        }
         a.rows = rows; a.cb = 0; a.strips = (OH + rows - 1) / rows;
         if (smem_of(rows) > 48 * 1024) cudaFuncSetAttribute(conv_direct_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
         conv_direct_kernel<<<(unsigned)(d->N * a.strips), kThreads, smem_of(rows), st>>>(a);
