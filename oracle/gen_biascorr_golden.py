@@ -6,9 +6,9 @@ Build container only (needs /root/reference).  Two fixtures on the seeded Mobile
              (SURVEY.md 8c.iv; with the id()-keyed graph every script builds it is a no-op);
   paper    : b - eps . E[x], assembled from the reference's own helpers (_quantize_error,
              find_prev_bn, _calculate_bias_correction_for_branches) on the id()-keyed graph.
-Usage: python -m oracle.gen_biascorr_golden
+Usage: python -m oracle.gen_biascorr_golden [--bits 4 --tag _w4]     (bit-width sweep, BASELINE.json configs[2])
 """
-import copy
+import argparse
 import os
 import sys
 
@@ -32,6 +32,10 @@ def fresh(ns):
 
 
 def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--bits", type=int, default=8)
+    ap.add_argument("--tag", default="")
+    args = ap.parse_args()
     ns = RH.import_reference()
     out = {}
     # ---- ref-body ---------------------------------------------------------------------------------
@@ -41,7 +45,7 @@ def main():
     re = lambda k: k if isinstance(run.graph[k], str) else pos[k]
     graph_pos = type(run.graph)((re(k), v) for k, v in run.graph.items())
     bottoms_pos = {re(k): (None if v is None else [re(b) for b in v]) for k, v in run.bottoms.items()}
-    before, after = ns.bc.bias_correction(graph_pos, bottoms_pos, tuple(run.targ_layer), bits_weight=8)
+    before, after = ns.bc.bias_correction(graph_pos, bottoms_pos, tuple(run.targ_layer), bits_weight=args.bits)
     print("ref-body: corrected", len(after), "layers")
     for name, t in run.snapshot().items():
         if name.endswith("bias"):
@@ -71,7 +75,7 @@ def main():
                 branch = {"0": [(bn, relu_list[i], kind_list[i]) for i, (bn, _b) in enumerate(bn_list)]}
                 (_kind, expect), = bc._calculate_bias_correction_for_branches(branch, calc_mean).values()
                 W = node.weight.detach()
-                eps = bc._quantize_error(W, 8, reduction=None, signed=False)
+                eps = bc._quantize_error(W, args.bits, reduction=None, signed=False)
                 eps = eps.view(W.size(0), W.size(1), -1).sum(-1).double()          # [O, I/g]
                 groups = getattr(node, "groups", 1)
                 e = expect.double().view(groups, -1)                                # [g, I/g]
@@ -81,7 +85,7 @@ def main():
     for name, t in run.snapshot().items():
         if name.endswith(".bias"):
             out["paper/" + name] = t.numpy()
-    np.savez_compressed(os.path.join(ROOT, "tests", "golden", "biascorr_mobilenetv2.npz"), **out)
+    np.savez_compressed(os.path.join(ROOT, "tests", "golden", "biascorr_mobilenetv2" + args.tag + ".npz"), **out)
     print("written", len(out), "tensors")
 
 

@@ -65,6 +65,7 @@ def main():
     ap.add_argument("--bits", type=int, default=8)
     ap.add_argument("--cle-cache", default=None, help="cache of the reference's post-CLE state (dev aid)")
     ap.add_argument("--model", default="mobilenetv2", choices=["mobilenetv2", "deeplab"])
+    ap.add_argument("--tag", default="", help="suffix of the output files (bit-width sweep: --bits 4 --tag _w4)")
     args = ap.parse_args()
     ns = RH.import_reference()
     torch.manual_seed(0)
@@ -85,7 +86,9 @@ def main():
         sd = synthetic_state_dict(model, seed=0, bn_seed=1)
         model.load_state_dict(sd)
         run = RH.RefRun(ns, model, torch.ones(4, 3, 224, 224))
-    out_stem = {"mobilenetv2": "mobilenetv2_dfq", "deeplab": "deeplab_dfq"}[args.model]
+    out_stem = {"mobilenetv2": "mobilenetv2_dfq", "deeplab": "deeplab_dfq"}[args.model] + args.tag
+    if args.tag:
+        args.skip_eval = True
 
     gold = {"model": args.model, "seed": 0, "bn_seed": 1, "torch": torch.__version__,
             "parity": {}, "steps": {}, "timing_s": {}}
@@ -230,6 +233,12 @@ def main():
     os.makedirs(os.path.join(ROOT, "tests", "golden"), exist_ok=True)
     with open(os.path.join(ROOT, "tests", "golden", out_stem + ".json"), "w") as f:
         json.dump(gold, f, indent=1)
+    if args.tag:            # sweep files keep only what differs from the W8 golden: the quantised state
+        gold = {k: gold[k] for k in ("model", "seed", "bn_seed", "torch", "parity", "codes", "quant_minmax")} | {
+            "bits": args.bits, "steps": {k: gold["steps"][k] for k in ("quantize_targ_layer", "final")}}
+        small = {k: v for k, v in small.items() if k.startswith("quant/") and k.endswith("bias")}
+        with open(os.path.join(ROOT, "tests", "golden", out_stem + ".json"), "w") as f:
+            json.dump(gold, f, indent=1)
     np.savez_compressed(os.path.join(ROOT, "tests", "golden", out_stem + ".npz"), **small)
     print("golden written", {k: round(v, 3) for k, v in gold["timing_s"].items()})
 

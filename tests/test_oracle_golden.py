@@ -96,3 +96,34 @@ def test_edge_cases(oracle):
     assert oracle.fake_quant(np.zeros(0, np.float32), 8, 0.0, 1.0).size == 0
     one = oracle.fake_quant(np.array([3.0], np.float32), 4)
     assert one.shape == (1,)
+
+
+@pytest.mark.parametrize("bits", [4, 6])
+def test_bit_width_sweep_per_tensor(gold_npz, oracle_run, oracle, bits):
+    """BASELINE.json configs[2]: the W4 / W6 quantised state of the unmodified reference
+    (oracle/gen_golden.py --bits b --tag _wb) from the same post-absorption state as the W8 golden."""
+    import json
+    import os
+    from conftest import ROOT
+    from oracle import pipeline as P
+    with open(os.path.join(ROOT, "tests", "golden", f"mobilenetv2_dfq_w{bits}.json")) as f:
+        sweep = json.load(f)
+    assert sweep["bits"] == bits
+    st = {k: (v.copy() if hasattr(v, "copy") else v) for k, v in oracle_run["st"].items()}
+    topo = oracle_run["topo"]
+    P.bias_absorption(st, topo, 3)
+    for k in gold_npz.files:
+        if k.startswith("absorb/"):
+            st[k[len("absorb/"):]] = gold_npz[k].copy()
+    for bn in set(topo["conv_bn"].values()):
+        st[bn + ".fake_weight"].fill(1.0)
+        st[bn + ".fake_bias"].fill(0.0)
+    codes = P.quantize_targ_layer(st, topo, bits, 8, want_codes=True)
+    for k, d in sweep["steps"]["quantize_targ_layer"].items():
+        assert sha(st[k]) == d, k
+    for k, d in sweep["codes"].items():
+        assert int(codes[k].max()) <= 2 ** bits - 1
+        assert sha(codes[k].astype(np.uint8)) == d, k
+    P.clip_weight(st, topo)
+    for k, d in sweep["steps"]["final"].items():
+        assert sha(st[k]) == d, k
