@@ -1,9 +1,15 @@
 """set_quant_minmax / find_prev_bn -- host mirror of utils/layer_transform.py:308-618.
 
 Scalar graph logic over per-channel BatchNorm statistics (<= ~1k floats per node): it stays on the host
-(SURVEY.md 8a row a11).  BN vectors are pulled to the CPU once, the Gaussian / clipped-Gaussian moments use
-scipy.stats.norm in fp64 exactly as the reference does, and the resulting (min, max) pairs are written into
-the QuantMeasure buffers wherever those live.
+(SURVEY.md 8a row a11).  BN vectors are pulled to the CPU once (one D2H copy of merge_batchnorm's stash), the
+per-channel arithmetic runs on numpy fp32 arrays -- the same IEEE operations in the same order as the reference's
+torch-CPU ops, a few us per call instead of tens -- the Gaussian / clipped-Gaussian moments use the fp64 pdf/cdf
+exactly as the reference does, and the resulting (min, max) pairs go to the QuantMeasure buffers with one H2D copy.
+
+One documented divergence: sqrt.  numpy's fp32 sqrt is correctly rounded; torch-CPU's vectorised sqrt is not (1 ulp
+off on ~0.7% of inputs, and which ones depends on the element's position in the SIMD loop), so ranges that pass
+through sqrt(var + eps) on an add branch (:420-431) can differ from a given torch-CPU run by 1 ulp.  The goldens
+(tests/golden/minmax_random_bn.json, quant_minmax of both models) are met exactly / within 1e-6.
 """
 import math
 
@@ -62,12 +68,12 @@ def _pdf(x):
     # scipy.stats.norm(0, 1).pdf(x) == exp(-x**2 / 2) / sqrt(2 pi) in fp64 (scipy/stats/_continuous_distns.py
     # _norm_pdf), without the per-call frozen-distribution set-up
     x = np.asarray(x, dtype=np.float64)
-    return torch.from_numpy(np.exp(-x ** 2 / 2.0) / _SQRT_2PI).float()
+    return (np.exp(-x ** 2 / 2.0) / _SQRT_2PI).astype(np.float32)
 
 
 def _cdf(x):
     # scipy.stats.norm.cdf(x) == scipy.special.ndtr(x) in fp64
-    return torch.from_numpy(ndtr(np.asarray(x, dtype=np.float64))).float()
+    return ndtr(np.asarray(x, dtype=np.float64)).astype(np.float32)
 
 
 def relu_mean(w, b):
@@ -91,31 +97,44 @@ def relu6_var(w, b, m):
 
 
 def _hi(bias, weight, n):
-    return float(torch.max(bias + n * weight))
+    return float(np.max(bias + n * weight))
 
 
 def _lo(bias, weight, n):
-    return float(torch.min(bias - n * weight))
+    return float(np.min(bias - n * weight))
 
 
 _ctx = {"stats": None, "pending": None}
 
 
 def _bn_stats(bn):
-    """(fake_bias, fake_weight) of a BatchNorm as fresh CPU tensors (one batched D2H copy per call of
+    """(fake_bias, fake_weight) of a BatchNorm as fresh fp32 numpy vectors (one batched D2H copy per call of
     set_quant_minmax, see _gather_stats)."""
     cache = _ctx["stats"]
     if cache is not None and bn in cache:
         b, w = cache[bn]
-        return b.clone(), w.clone()
-    return bn.fake_bias.detach().cpu().clone(), bn.fake_weight.detach().cpu().clone()
+        return b.copy(), w.copy()
+    return bn.fake_bias.detach().cpu().numpy().copy(), bn.fake_weight.detach().cpu().numpy().copy()
 
 
 def _gather_stats(graph, bn_type):
     bns = [m for m in graph.values() if type(m) == bn_type and hasattr(m, "fake_bias")]
     if not bns:
         return {}
-    flat = torch.cat([t.detach().reshape(-1) for m in bns for t in (m.fake_bias, m.fake_weight)]).cpu()
+    vecs = [t for m in bns for t in (m.fake_bias, m.fake_weight)]
+    base = vecs[0]._base
+    if base is not None and all(t._base is base and t.is_contiguous() for t in vecs):
+        # merge_batchnorm's pooled stash: one D2H copy, the vectors are slices of it
+        host = base.detach().reshape(-1).cpu().numpy() if base.is_contiguous() else None
+        if host is not None:
+            b0 = base.storage_offset()
+            out = {}
+            for m in bns:
+                ob, ow = m.fake_bias.storage_offset() - b0, m.fake_weight.storage_offset() - b0
+                n = m.fake_bias.numel()
+                out[m] = (host[ob:ob + n], host[ow:ow + n])
+            return out
+    flat = torch.cat([t.detach().reshape(-1) for t in vecs]).cpu().numpy()
     out, off = {}, 0
     for m in bns:
         n = m.fake_bias.numel()
@@ -187,12 +206,12 @@ def _merge_branch(entries, N, eps):
                     var += weight * weight
                 if 'relu6' in kind:
                     prev = mean
-                    mean = relu6_mean(torch.sqrt(var + eps), mean)
-                    var = relu6_var(torch.sqrt(var + eps), prev, mean)
+                    mean = relu6_mean(np.sqrt(var + eps), mean)
+                    var = relu6_var(np.sqrt(var + eps), prev, mean)
                 elif 'relu' in kind:
                     prev = mean
-                    mean = relu_mean(torch.sqrt(var + eps), mean)
-                    var = relu_var(torch.sqrt(var + eps), prev, mean)
+                    mean = relu_mean(np.sqrt(var + eps), mean)
+                    var = relu_var(np.sqrt(var + eps), prev, mean)
             elif kind == 'cat':
                 l2, h2 = _clipped_range(bias, weight, relu_t, N)
                 lo, hi = min(lo, l2), max(hi, h2)
@@ -210,7 +229,7 @@ def _merge_branch(entries, N, eps):
 def _range_of(res, N, eps):
     if 'add' in res[0]:
         _, mean, var = res
-        return _lo(mean, torch.sqrt(var + eps), N), _hi(mean, torch.sqrt(var + eps), N)
+        return _lo(mean, np.sqrt(var + eps), N), _hi(mean, np.sqrt(var + eps), N)
     return res[1], res[2]
 
 
@@ -223,17 +242,39 @@ def _set(qm, lo, hi):
 
 
 def _flush_pending():
-    """running_min.fill_(lo) / running_max.fill_(hi) for every QuantMeasure with ONE host->device copy: the
-    buffers become [1]-views of a shared [n, 2] tensor (contiguous (min, max) table, reused by the eval plan)."""
+    """running_min.fill_(lo) / running_max.fill_(hi) for every QuantMeasure with ONE host->device copy per
+    backing table.  Measures whose buffers already are rows of a shared [n, 2] (min, max) table (set_layer_bits
+    pools them; an earlier call of this function does too) are written through that table; the others become
+    [1]-views of a new table (contiguous, reused by the eval plan)."""
     pending, _ctx["pending"] = _ctx["pending"], None
     if not pending:
         return None
-    qms = list(pending)
-    dev = qms[0].running_min.device
-    table = torch.tensor([pending[q] for q in qms], dtype=torch.float32).to(dev)
-    for i, q in enumerate(qms):
-        q.running_min = table[i, 0:1]
-        q.running_max = table[i, 1:2]
+    pooled, loose = {}, []
+    for q, (lo, hi) in pending.items():
+        rmin, rmax = q._buffers["running_min"], q._buffers["running_max"]
+        base = rmin._base
+        if (base is not None and rmax._base is base and base.dim() == 2 and base.size(1) == 2
+                and base.is_contiguous() and base.dtype == torch.float32
+                and rmax.storage_offset() == rmin.storage_offset() + 1):
+            row = (rmin.storage_offset() - base.storage_offset()) // 2
+            pooled.setdefault(id(base), (base, {}))[1][row] = (lo, hi)
+        else:
+            loose.append(q)
+    table = None
+    for base, rows in pooled.values():
+        if len(rows) == base.size(0):                        # every row rewritten: plain copy
+            base.copy_(torch.tensor([rows[i] for i in range(base.size(0))], dtype=torch.float32))
+        else:
+            idx = sorted(rows)
+            base.index_copy_(0, torch.tensor(idx, device=base.device),
+                             torch.tensor([rows[i] for i in idx], dtype=torch.float32).to(base.device))
+        table = base
+    if loose:
+        dev = loose[0]._buffers["running_min"].device
+        table = torch.tensor([pending[q] for q in loose], dtype=torch.float32).to(dev)
+        for i, q in enumerate(loose):
+            q._buffers["running_min"] = table[i, 0:1]         # registered buffers: skip Module.__setattr__
+            q._buffers["running_max"] = table[i, 1:2]
     return table
 
 
@@ -248,7 +289,8 @@ def set_quant_minmax(graph, bottoms, is_detection=False, bn_type=torch.nn.BatchN
     eps = 1e-6
     _ctx["stats"], _ctx["pending"] = _gather_stats(graph, bn_type), {}
     try:
-        _walk(graph, bottoms, is_detection, bn_type, N, top, bn_module, relu_attached, eps)
+        with np.errstate(all="ignore"):              # x/0 -> inf, silently, as torch does
+            _walk(graph, bottoms, is_detection, bn_type, N, top, bn_module, relu_attached, eps)
     finally:
         _ctx["stats"] = None
         _flush_pending()
@@ -279,9 +321,10 @@ def _walk(graph, bottoms, is_detection, bn_type, N, top, bn_module, relu_attache
         bn_list, relu_list, kind_list, no_bn = find_prev_bn(bn_module, relu_attached, graph, bottoms, bot[:])
         if len(qms) == len(bn_list):                # 1 to 1 (:476-505)
             for i, (bn, bid) in enumerate(bn_list):
-                bias, weight = (t.view(-1) for t in _bn_stats(bn))
+                bias, weight = _bn_stats(bn)
                 if bid[0] in no_bn:                 # case (d): a conv/linear without BatchNorm in between
                     layer_type, layer = no_bn[bid[0]]
+                    bias, weight = torch.from_numpy(bias), torch.from_numpy(weight)
                     lw, lb = layer.weight.detach().cpu(), layer.bias.detach().cpu()
                     if layer_type == 'conv':
                         lw = lw.view(lw.size(0), lw.size(1), -1).sum(-1)
@@ -291,6 +334,7 @@ def _walk(graph, bottoms, is_detection, bn_type, N, top, bn_module, relu_attache
                     else:
                         bias = torch.nn.functional.linear(bias.view(1, -1), lw, lb)
                         weight = torch.nn.functional.linear(weight.view(1, -1), lw, lb)
+                    bias, weight = bias.numpy(), weight.numpy()
                     lo, hi = _lo(bias, weight, N), _hi(bias, weight, N)
                 else:
                     lo, hi = _clipped_range(bias, weight, relu_list[i], N)
