@@ -191,9 +191,14 @@ def dev_f32(t, name="tensor", allow_none=False):
 
 
 def table_to_device(arr, device):
-    """ctypes array of descriptor structs -> uint8 CUDA tensor holding the same bytes."""
-    raw = torch.frombuffer(bytearray(bytes(arr)), dtype=torch.uint8)
-    return raw.to(device, non_blocking=False)
+    """ctypes array of descriptor structs -> uint8 CUDA tensor holding the same bytes.  Staged through pinned
+    memory and copied asynchronously on the current stream: a pageable copy would block the host until every
+    kernel already queued (e.g. the whole CLE loop) has finished.  torch's caching host allocator keeps the
+    pinned block alive until the copy has run."""
+    n = ctypes.sizeof(arr)
+    host = torch.empty(n, dtype=torch.uint8, pin_memory=True)
+    ctypes.memmove(host.data_ptr(), ctypes.addressof(arr), n)
+    return host.to(device, non_blocking=True)
 
 
 def launch_count():

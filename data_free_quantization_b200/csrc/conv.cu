@@ -218,6 +218,225 @@ dwconv3x3_stream_kernel(DwArgs a) {
 }
 
 // ---------------------------------------------------------------------------------------------------------
+// Depthwise 3x3, pad 1, dilation 1, stride 1 or 2, rows of 4*L floats (L <= 32): the register form.  No shared
+// tile, no block barrier before the epilogue.  `lanes` = W/4 adjacent lanes own one input row as 128-bit words; a
+// warp carries G = 32/lanes such row groups, each walking `R` output rows of its own (channel, row block) of the
+// same image with a three-row window of quantised values in registers.  The left / right neighbours of a lane's
+// four columns come from the adjacent lanes by shuffle (exact 0 at the plane's edges, like the rows above and
+// below the image: the reference quantises before F.conv2d pads).  Input rows are requested two (stride 1) or
+// four (stride 2) rows ahead of their use, so the loads of later rows are in flight while the current row is
+// computed.  Tap order per output is that of the shared-memory form (bit-identical results).
+struct DwRowArgs {
+    const float *x; float *y; const float *w; const float *bias; const RangeSlot *slot; unsigned *stats;
+    int C, H, W, OH, OW, relu, bits;
+    int lanes, G, R, nblk, items, wps;   // lanes per row, row groups per warp, output rows per item, row blocks
+                                         // per plane, items per image (C * nblk), warps per image
+};
+
+struct DwRow { float4 m; float l, r; };
+
+template <int S>
+__global__ void __launch_bounds__(kThreads, 4)
+dwconv3x3_rows_kernel(DwRowArgs a) {
+    __shared__ float red[2 * kWarps];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int n = blockIdx.y;
+    const int wi = blockIdx.x * kWarps + warp;
+    const int g = lane / a.lanes, j = lane - g * a.lanes;
+    const int item = wi * a.G + g;
+    const bool active = g < a.G && wi < a.wps && item < a.items;
+    int c = 0, blk = 0;
+    if (active) { c = item / a.nblk; blk = item - c * a.nblk; }
+    const int r0 = blk * a.R;
+    const int nr = active ? min(a.R, a.OH - r0) : 0;
+    const bool on = a.slot != nullptr;
+    QuantConsts qc;
+    if (on) qc = consts_from_slot(*a.slot, a.bits, 0, 0.f, 0.f);
+    float wreg[9];
+#pragma unroll
+    for (int t = 0; t < 9; ++t) wreg[t] = __ldg(a.w + (int64_t)c * 9 + t);
+    const float bv = a.bias ? __ldg(a.bias + c) : 0.0f;
+    const float *xp = a.x + ((int64_t)n * a.C + c) * a.H * a.W + 4 * j;
+    float *yp = a.y + (((int64_t)n * a.C + c) * a.OH + r0) * a.OW + (S == 1 ? 4 : 2) * j;
+    const bool first = j == 0, last = j == a.lanes - 1;
+    const int ib = S * r0 - 1;                                   // first input row of the window
+    const int ir_last = S * (r0 + nr - 1) + 1;                   // last input row this item needs
+    auto valid = [&](int ir) { return active && ir >= 0 && ir < a.H && ir <= ir_last; };
+    auto ld = [&](int ir) {
+        return valid(ir) ? __ldg(reinterpret_cast<const float4 *>(xp + (int64_t)ir * a.W)) : make_float4(0.f, 0.f, 0.f, 0.f);
+    };
+    auto qrow = [&](float4 v, int ir) {
+        DwRow r;
+        if (on && valid(ir)) {
+            v.x = quant_dequant(v.x, qc); v.y = quant_dequant(v.y, qc);
+            v.z = quant_dequant(v.z, qc); v.w = quant_dequant(v.w, qc);
+        }
+        r.m = v;
+        const float l = __shfl_up_sync(0xffffffffu, v.w, 1), rr = __shfl_down_sync(0xffffffffu, v.x, 1);
+        r.l = first ? 0.0f : l;
+        r.r = last ? 0.0f : rr;
+        return r;
+    };
+    float lo = INFINITY, hi = -INFINITY;
+    if (S == 1) {
+        DwRow top = qrow(ld(ib), ib), mid = qrow(ld(ib + 1), ib + 1);
+        float4 p1 = ld(ib + 2), p2 = ld(ib + 3);
+        for (int t = 0; t < a.R; ++t) {
+            const float4 p3 = ld(ib + t + 4);
+            const DwRow bot = qrow(p1, ib + t + 2);
+            float acc[4] = {0.f, 0.f, 0.f, 0.f};
+            const DwRow *rows[3] = {&top, &mid, &bot};
+#pragma unroll
+            for (int i = 0; i < 3; ++i) {
+                const float w0 = wreg[3 * i], w1 = wreg[3 * i + 1], w2 = wreg[3 * i + 2];
+                const float L = rows[i]->l, R = rows[i]->r;
+                const float4 M = rows[i]->m;
+                acc[0] = __fmaf_rn(M.y, w2, __fmaf_rn(M.x, w1, __fmaf_rn(L, w0, acc[0])));
+                acc[1] = __fmaf_rn(M.z, w2, __fmaf_rn(M.y, w1, __fmaf_rn(M.x, w0, acc[1])));
+                acc[2] = __fmaf_rn(M.w, w2, __fmaf_rn(M.z, w1, __fmaf_rn(M.y, w0, acc[2])));
+                acc[3] = __fmaf_rn(R, w2, __fmaf_rn(M.w, w1, __fmaf_rn(M.z, w0, acc[3])));
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                if (a.bias) acc[u] = __fadd_rn(acc[u], bv);
+                if (a.relu) acc[u] = fmaxf(acc[u], 0.0f);
+            }
+            if (t < nr) {
+                *reinterpret_cast<float4 *>(yp + (int64_t)t * a.OW) = make_float4(acc[0], acc[1], acc[2], acc[3]);
+                lo = fminf(lo, fminf(fminf(acc[0], acc[1]), fminf(acc[2], acc[3])));
+                hi = fmaxf(hi, fmaxf(fmaxf(acc[0], acc[1]), fmaxf(acc[2], acc[3])));
+            }
+            top = mid; mid = bot; p1 = p2; p2 = p3;
+        }
+    } else {
+        DwRow top = qrow(ld(ib), ib);
+        float4 p1 = ld(ib + 1), p2 = ld(ib + 2), p3 = ld(ib + 3), p4 = ld(ib + 4);
+        for (int t = 0; t < a.R; ++t) {
+            const DwRow mid = qrow(p1, ib + 2 * t + 1), bot = qrow(p2, ib + 2 * t + 2);
+            p1 = p3; p2 = p4;
+            p3 = ld(ib + 2 * t + 5); p4 = ld(ib + 2 * t + 6);
+            float acc[2] = {0.f, 0.f};
+            const DwRow *rows[3] = {&top, &mid, &bot};
+#pragma unroll
+            for (int i = 0; i < 3; ++i) {
+                const float w0 = wreg[3 * i], w1 = wreg[3 * i + 1], w2 = wreg[3 * i + 2];
+                const float L = rows[i]->l;
+                const float4 M = rows[i]->m;
+                acc[0] = __fmaf_rn(M.y, w2, __fmaf_rn(M.x, w1, __fmaf_rn(L, w0, acc[0])));
+                acc[1] = __fmaf_rn(M.w, w2, __fmaf_rn(M.z, w1, __fmaf_rn(M.y, w0, acc[1])));
+            }
+#pragma unroll
+            for (int u = 0; u < 2; ++u) {
+                if (a.bias) acc[u] = __fadd_rn(acc[u], bv);
+                if (a.relu) acc[u] = fmaxf(acc[u], 0.0f);
+            }
+            if (t < nr) {
+                *reinterpret_cast<float2 *>(yp + (int64_t)t * a.OW) = make_float2(acc[0], acc[1]);
+                lo = fminf(lo, fminf(acc[0], acc[1]));
+                hi = fmaxf(hi, fmaxf(acc[0], acc[1]));
+            }
+            top = bot;
+        }
+    }
+    if (a.stats) stats_flush(a.stats, n, lo, hi, red);
+}
+
+// The same register form for narrow planes (W <= 32, any W: 14 x 14 and 7 x 7 in MobileNetV2): one lane per input
+// column, G = 32/W whole planes side by side in a warp, K planes one after the other per lane group.  With
+// stride 2 output column j gathers input columns 2j-1, 2j, 2j+1 from the lanes that hold them.
+struct DwColArgs {
+    const float *x; float *y; const float *w; const float *bias; const RangeSlot *slot; unsigned *stats;
+    int C, H, W, OH, OW, relu, bits;
+    int G, K, wps;                       // planes side by side, planes in sequence, warps per image
+};
+
+template <int S>
+__global__ void __launch_bounds__(kThreads, 4)
+dwconv3x3_cols_kernel(DwColArgs a) {
+    __shared__ float red[2 * kWarps];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int n = blockIdx.y;
+    const int wi = blockIdx.x * kWarps + warp;
+    const int g = lane / a.W, j = lane - g * a.W;
+    const bool on = a.slot != nullptr;
+    QuantConsts qc;
+    if (on) qc = consts_from_slot(*a.slot, a.bits, 0, 0.f, 0.f);
+    const bool first = j == 0, last = j == a.W - 1;
+    // stride 2: lanes of the three taps of output column j (clamped; masked below)
+    const int base = g * a.W;
+    const int sl = min(base + max(2 * j - 1, 0), 31), sm = min(base + 2 * j, 31), sr = min(base + 2 * j + 1, 31);
+    const bool okl = 2 * j - 1 >= 0, okr = 2 * j + 1 < a.W, outlane = j < a.OW;
+    const int ir_last = S * (a.OH - 1) + 1;
+    float lo = INFINITY, hi = -INFINITY;
+    for (int k = 0; k < a.K; ++k) {
+        const int c = (wi * a.K + k) * a.G + g;
+        const bool active = g < a.G && wi < a.wps && c < a.C;
+        const int cc = active ? c : 0;
+        float wreg[9];
+#pragma unroll
+        for (int t = 0; t < 9; ++t) wreg[t] = __ldg(a.w + (int64_t)cc * 9 + t);
+        const float bv = a.bias ? __ldg(a.bias + cc) : 0.0f;
+        const float *xp = a.x + ((int64_t)n * a.C + cc) * a.H * a.W + j;
+        float *yp = a.y + ((int64_t)n * a.C + cc) * a.OH * a.OW + j;
+        auto valid = [&](int ir) { return active && ir >= 0 && ir < a.H && ir <= ir_last; };
+        auto ld = [&](int ir) { return valid(ir) ? __ldg(xp + (int64_t)ir * a.W) : 0.0f; };
+        auto q = [&](float v, int ir) { return (on && valid(ir)) ? quant_dequant(v, qc) : v; };
+        if (S == 1) {
+            float t0 = q(ld(-1), -1), t1 = q(ld(0), 0);
+            float tl = __shfl_up_sync(0xffffffffu, t0, 1), tr = __shfl_down_sync(0xffffffffu, t0, 1);
+            float ml = __shfl_up_sync(0xffffffffu, t1, 1), mr = __shfl_down_sync(0xffffffffu, t1, 1);
+            if (first) { tl = 0.f; ml = 0.f; }
+            if (last) { tr = 0.f; mr = 0.f; }
+            float p1 = ld(1), p2 = ld(2);
+            for (int t = 0; t < a.OH; ++t) {
+                const float p3 = ld(t + 3);
+                const float b1 = q(p1, t + 1);
+                float bl = __shfl_up_sync(0xffffffffu, b1, 1), br = __shfl_down_sync(0xffffffffu, b1, 1);
+                if (first) bl = 0.f;
+                if (last) br = 0.f;
+                float acc = __fmaf_rn(tr, wreg[2], __fmaf_rn(t0, wreg[1], __fmaf_rn(tl, wreg[0], 0.0f)));
+                acc = __fmaf_rn(mr, wreg[5], __fmaf_rn(t1, wreg[4], __fmaf_rn(ml, wreg[3], acc)));
+                acc = __fmaf_rn(br, wreg[8], __fmaf_rn(b1, wreg[7], __fmaf_rn(bl, wreg[6], acc)));
+                if (a.bias) acc = __fadd_rn(acc, bv);
+                if (a.relu) acc = fmaxf(acc, 0.0f);
+                if (active) {
+                    yp[(int64_t)t * a.OW] = acc;
+                    lo = fminf(lo, acc); hi = fmaxf(hi, acc);
+                }
+                t0 = t1; tl = ml; tr = mr; t1 = b1; ml = bl; mr = br; p1 = p2; p2 = p3;
+            }
+        } else {
+            auto taps = [&](float v, float &l, float &m, float &r) {
+                l = __shfl_sync(0xffffffffu, v, sl); m = __shfl_sync(0xffffffffu, v, sm); r = __shfl_sync(0xffffffffu, v, sr);
+                if (!okl) l = 0.f;
+                if (!okr) r = 0.f;
+            };
+            float tl, tm, tr;
+            taps(q(ld(-1), -1), tl, tm, tr);
+            float p1 = ld(0), p2 = ld(1), p3 = ld(2), p4 = ld(3);
+            for (int t = 0; t < a.OH; ++t) {
+                float ml, mm, mr, bl, bm, br;
+                taps(q(p1, 2 * t), ml, mm, mr);
+                taps(q(p2, 2 * t + 1), bl, bm, br);
+                p1 = p3; p2 = p4;
+                p3 = ld(2 * t + 4); p4 = ld(2 * t + 5);
+                float acc = __fmaf_rn(tr, wreg[2], __fmaf_rn(tm, wreg[1], __fmaf_rn(tl, wreg[0], 0.0f)));
+                acc = __fmaf_rn(mr, wreg[5], __fmaf_rn(mm, wreg[4], __fmaf_rn(ml, wreg[3], acc)));
+                acc = __fmaf_rn(br, wreg[8], __fmaf_rn(bm, wreg[7], __fmaf_rn(bl, wreg[6], acc)));
+                if (a.bias) acc = __fadd_rn(acc, bv);
+                if (a.relu) acc = fmaxf(acc, 0.0f);
+                if (active && outlane) {
+                    yp[(int64_t)t * a.OW] = acc;
+                    lo = fminf(lo, acc); hi = fmaxf(hi, acc);
+                }
+                tl = bl; tm = bm; tr = br;
+            }
+        }
+    }
+    if (a.stats) stats_flush(a.stats, n, lo, hi, red);
+}
+
+// ---------------------------------------------------------------------------------------------------------
 // Dense kxk convolution, direct form, for small C*kh*kw (MobileNetV2's first layer: 3 -> 32, 3x3, stride 2).
 // A block owns `rows` output rows of one image for all O output channels: the quantised, zero-padded input strip
 // and the whole weight tensor sit in shared memory; a thread owns one output pixel and walks the output channels
@@ -555,6 +774,33 @@ extern "C" int dfq_qconv2d_f32(const DfqConvDesc *d, void *stream) {
     const int pw = d->W + 2 * d->pad;
     if (d->groups == d->C_in && d->C_in == d->C_out && d->kh == 3 && d->kw == 3 && d->pad == 1 && d->dil == 1 &&
         (d->stride == 1 || d->stride == 2)) {
+        if ((d->W % 4) == 0 && d->W >= 16 && d->W <= 128 && ((uintptr_t)d->x % 16) == 0 && ((uintptr_t)d->y % 16) == 0 &&
+            (d->stride == 1 || (d->H % 2) == 0) && d->N <= 65535) {
+            DwRowArgs r;
+            r.x = d->x; r.y = d->y; r.w = d->w; r.bias = d->bias; r.slot = (const RangeSlot *)d->in_slot; r.stats = d->out_stats;
+            r.C = d->C_in; r.H = d->H; r.W = d->W; r.OH = OH; r.OW = OW; r.relu = d->relu; r.bits = d->bits;
+            r.lanes = d->W / 4; r.G = 32 / r.lanes;
+            r.nblk = (OH + 15) / 16; r.R = (OH + r.nblk - 1) / r.nblk;
+            r.items = d->C_in * r.nblk; r.wps = (r.items + r.G - 1) / r.G;
+            dim3 grid((unsigned)((r.wps + kWarps - 1) / kWarps), (unsigned)d->N);
+            if (d->stride == 1) dwconv3x3_rows_kernel<1><<<grid, kThreads, 0, st>>>(r);
+            else dwconv3x3_rows_kernel<2><<<grid, kThreads, 0, st>>>(r);
+            g_launches += 1;
+            return (int)cudaGetLastError();
+        }
+        if (d->W <= 32 && d->N <= 65535) {
+            DwColArgs r;
+            r.x = d->x; r.y = d->y; r.w = d->w; r.bias = d->bias; r.slot = (const RangeSlot *)d->in_slot; r.stats = d->out_stats;
+            r.C = d->C_in; r.H = d->H; r.W = d->W; r.OH = OH; r.OW = OW; r.relu = d->relu; r.bits = d->bits;
+            r.G = 32 / d->W;
+            r.K = d->C_in >= 64 * r.G ? 4 : 1;
+            r.wps = (d->C_in + r.G * r.K - 1) / (r.G * r.K);
+            dim3 grid((unsigned)((r.wps + kWarps - 1) / kWarps), (unsigned)d->N);
+            if (d->stride == 1) dwconv3x3_cols_kernel<1><<<grid, kThreads, 0, st>>>(r);
+            else dwconv3x3_cols_kernel<2><<<grid, kThreads, 0, st>>>(r);
+            g_launches += 1;
+            return (int)cudaGetLastError();
+        }
         DwArgs w;
         w.x = d->x; w.y = d->y; w.w = d->w; w.bias = d->bias; w.slot = (const RangeSlot *)d->in_slot; w.stats = d->out_stats;
         w.C = d->C_in; w.H = d->H; w.W = d->W; w.OH = OH; w.OW = OW; w.stride = d->stride; w.relu = d->relu; w.bits = d->bits;

@@ -53,8 +53,11 @@ def merge_batchnorm(model, graph, bottoms, targ_type=[QConv2d]):
             d.mean, d.var = L.dev_f32(bn.running_mean, "bn.running_mean"), L.dev_f32(bn.running_var, "bn.running_var")
             d.fake_weight, d.fake_bias = fake_w.data_ptr(), fake_b.data_ptr()
             d.O, d.K, d.eps = O, W.numel() // O, float(bn.eps)
-            bn.register_buffer('fake_weight', fake_w)            # :273-274
-            bn.register_buffer('fake_bias', fake_b)
+            if 'fake_weight' in bn._buffers:                      # :273-274; re-registration: plain replacement
+                bn._buffers['fake_weight'], bn._buffers['fake_bias'] = fake_w, fake_b
+            else:
+                bn.register_buffer('fake_weight', fake_w)
+                bn.register_buffer('fake_bias', fake_b)
             bn.eps = IDENTITY_BN_EPS                             # :281 (see IDENTITY_BN_EPS)
         rows = ctypes.c_int()
         L.check(L.lib().dfq_merge_plan_host(descs, len(pairs), ctypes.byref(rows)), "dfq_merge_plan_host")

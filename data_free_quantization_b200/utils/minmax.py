@@ -117,30 +117,40 @@ def _bn_stats(bn):
     return bn.fake_bias.detach().cpu().numpy().copy(), bn.fake_weight.detach().cpu().numpy().copy()
 
 
-def _gather_stats(graph, bn_type):
+def _start_gather(graph, bn_type):
+    """Phase 1: queue the device->host copy of every BatchNorm's (fake_bias, fake_weight) and return a function
+    that waits for it and hands back {bn: (bias, weight)} as fp32 numpy vectors."""
     bns = [m for m in graph.values() if type(m) == bn_type and hasattr(m, "fake_bias")]
     if not bns:
-        return {}
+        return lambda: {}
     vecs = [t for m in bns for t in (m.fake_bias, m.fake_weight)]
     base = vecs[0]._base
-    if base is not None and all(t._base is base and t.is_contiguous() for t in vecs):
-        # merge_batchnorm's pooled stash: one D2H copy, the vectors are slices of it
-        host = base.detach().reshape(-1).cpu().numpy() if base.is_contiguous() else None
-        if host is not None:
-            b0 = base.storage_offset()
-            out = {}
-            for m in bns:
-                ob, ow = m.fake_bias.storage_offset() - b0, m.fake_weight.storage_offset() - b0
-                n = m.fake_bias.numel()
-                out[m] = (host[ob:ob + n], host[ow:ow + n])
-            return out
-    flat = torch.cat([t.detach().reshape(-1) for t in vecs]).cpu().numpy()
-    out, off = {}, 0
-    for m in bns:
-        n = m.fake_bias.numel()
-        out[m] = (flat[off:off + n], flat[off + n:off + 2 * n])
-        off += 2 * n
-    return out
+    if base is not None and base.is_contiguous() and all(t._base is base and t.is_contiguous() for t in vecs):
+        # merge_batchnorm's pooled stash: the vectors are slices of one allocation
+        src, b0 = base.detach().reshape(-1), base.storage_offset()
+        spans = [(m, m.fake_bias.storage_offset() - b0, m.fake_weight.storage_offset() - b0, m.fake_bias.numel())
+                 for m in bns]
+    else:
+        src = torch.cat([t.detach().reshape(-1) for t in vecs])
+        spans, off = [], 0
+        for m in bns:
+            n = m.fake_bias.numel()
+            spans.append((m, off, off + n, n))
+            off += 2 * n
+    if src.is_cuda:
+        host = torch.empty(src.numel(), dtype=src.dtype, pin_memory=True)
+        host.copy_(src, non_blocking=True)
+        done = torch.cuda.Event()
+        done.record()
+    else:
+        host, done = src, None
+
+    def fetch():
+        if done is not None:
+            done.synchronize()
+        flat = host.numpy()
+        return {m: (flat[ob:ob + n], flat[ow:ow + n]) for m, ob, ow, n in spans}
+    return fetch
 
 
 def _clipped_range(bias, weight, relu, N):
@@ -280,23 +290,33 @@ def _flush_pending():
 
 def set_quant_minmax(graph, bottoms, is_detection=False, bn_type=torch.nn.BatchNorm2d, N=6, verbose=True):
     """utils/layer_transform.py:356-618: fill every QuantMeasure's running_min / running_max from the statistics
-    (fake_weight = |gamma|, fake_bias = beta) of the BatchNorm(s) that feed it."""
+    (fake_weight = |gamma|, fake_bias = beta) of the BatchNorm(s) that feed it.
+
+    Three phases so that the host work overlaps the kernels still queued on the stream (the BN statistics are
+    the last thing the preceding steps write): (1) start the device->host copy of the statistics, (2) walk the
+    graph and record which BatchNorms / ReLUs / tensor ops feed which QuantMeasure -- pure graph logic --
+    (3) wait for the copy and do the per-channel arithmetic."""
     from .. import graph as G
     if verbose:
         print("SET QUANT MIN MAX")
     top = G._state.get("module_tensor_op")
-    bn_module, relu_attached = {}, {}
     eps = 1e-6
-    _ctx["stats"], _ctx["pending"] = _gather_stats(graph, bn_type), {}
+    fetch = _start_gather(graph, bn_type)
+    jobs = _walk(graph, bottoms, is_detection, bn_type, top)
+    _ctx["stats"], _ctx["pending"] = fetch(), {}
     try:
         with np.errstate(all="ignore"):              # x/0 -> inf, silently, as torch does
-            _walk(graph, bottoms, is_detection, bn_type, N, top, bn_module, relu_attached, eps)
+            for job in jobs:
+                _run_job(job, N, eps)
     finally:
         _ctx["stats"] = None
         _flush_pending()
 
 
-def _walk(graph, bottoms, is_detection, bn_type, N, top, bn_module, relu_attached, eps):
+def _walk(graph, bottoms, is_detection, bn_type, top):
+    """Phase 2: [(kind, ...)] jobs in graph order; no BatchNorm value is read here."""
+    bn_module, relu_attached = {}, {}
+    jobs = []
     for key in graph:
         node, bot = graph[key], bottoms[key]
         if bot is None:
@@ -312,44 +332,60 @@ def _walk(graph, bottoms, is_detection, bn_type, N, top, bn_module, relu_attache
         qms = _quant_modules_of(node, top)
         if len(bot) == 1 and bot[0] == 'Data':
             if is_detection:
-                _set(qms[0], -1, 1)
+                jobs.append(("const", qms[0], -1, 1))
             else:                                   # (0 - mean)/std .. (1 - mean)/std of the data preprocessing
-                _set(qms[0], -2.11790393, 2.64)
+                jobs.append(("const", qms[0], -2.11790393, 2.64))
             continue
         if qms is None:
             continue
         bn_list, relu_list, kind_list, no_bn = find_prev_bn(bn_module, relu_attached, graph, bottoms, bot[:])
         if len(qms) == len(bn_list):                # 1 to 1 (:476-505)
-            for i, (bn, bid) in enumerate(bn_list):
-                bias, weight = _bn_stats(bn)
-                if bid[0] in no_bn:                 # case (d): a conv/linear without BatchNorm in between
-                    layer_type, layer = no_bn[bid[0]]
-                    bias, weight = torch.from_numpy(bias), torch.from_numpy(weight)
-                    lw, lb = layer.weight.detach().cpu(), layer.bias.detach().cpu()
-                    if layer_type == 'conv':
-                        lw = lw.view(lw.size(0), lw.size(1), -1).sum(-1)
-                        lw = lw.view(lw.size(0), lw.size(1), 1, 1)
-                        bias = torch.nn.functional.conv2d(bias.view(1, -1, 1, 1), lw, lb, 1, 0, 1, layer.groups)
-                        weight = torch.nn.functional.conv2d(weight.view(1, -1, 1, 1), lw, lb, 1, 0, 1, layer.groups)
-                    else:
-                        bias = torch.nn.functional.linear(bias.view(1, -1), lw, lb)
-                        weight = torch.nn.functional.linear(weight.view(1, -1), lw, lb)
-                    bias, weight = bias.numpy(), weight.numpy()
-                    lo, hi = _lo(bias, weight, N), _hi(bias, weight, N)
-                else:
-                    lo, hi = _clipped_range(bias, weight, relu_list[i], N)
-                _set(qms[i], lo, hi)
+            # relu flags are snapshotted: a later ReLU node must not leak into this job
+            jobs.append(("one", qms, bn_list, list(relu_list), no_bn))
             continue
         branches = {}
         for i, item in enumerate(bn_list):
             branches.setdefault(item[1][0], []).append((item, relu_list[i], kind_list[i]))
-        res = {b: _merge_branch(entries, N, eps) for b, entries in branches.items()}
         if len(qms) == 1 and len(qms) < len(bn_list):          # 1 to many
-            assert len(res) == 1, "Error occurs when setting min/max, should be 1 to many"
-            _set(qms[0], *_range_of(list(res.values())[0], N, eps))
+            assert len(branches) == 1, "Error occurs when setting min/max, should be 1 to many"
         elif len(qms) < len(bn_list):                          # many to many
-            assert len(res) == len(qms), 'LENGTH NOT EQUAL {} vs {}'.format(len(res), len(qms))
-            for i in range(len(res)):
-                _set(qms[i], *_range_of(res[str(i)], N, eps))
+            assert len(branches) == len(qms), 'LENGTH NOT EQUAL {} vs {}'.format(len(branches), len(qms))
         else:
             assert False, "Unknown error occured while setting min/max"
+        jobs.append(("branches", qms, branches))
+    return jobs
+
+
+def _run_job(job, N, eps):
+    """Phase 3: the arithmetic of one QuantMeasure (or of the measures of one tensor op)."""
+    if job[0] == "const":
+        _set(job[1], job[2], job[3])
+    elif job[0] == "one":
+        _, qms, bn_list, relu_list, no_bn = job
+        for i, (bn, bid) in enumerate(bn_list):
+            bias, weight = _bn_stats(bn)
+            if bid[0] in no_bn:                 # case (d): a conv/linear without BatchNorm in between
+                layer_type, layer = no_bn[bid[0]]
+                bias, weight = torch.from_numpy(bias), torch.from_numpy(weight)
+                lw, lb = layer.weight.detach().cpu(), layer.bias.detach().cpu()
+                if layer_type == 'conv':
+                    lw = lw.view(lw.size(0), lw.size(1), -1).sum(-1)
+                    lw = lw.view(lw.size(0), lw.size(1), 1, 1)
+                    bias = torch.nn.functional.conv2d(bias.view(1, -1, 1, 1), lw, lb, 1, 0, 1, layer.groups)
+                    weight = torch.nn.functional.conv2d(weight.view(1, -1, 1, 1), lw, lb, 1, 0, 1, layer.groups)
+                else:
+                    bias = torch.nn.functional.linear(bias.view(1, -1), lw, lb)
+                    weight = torch.nn.functional.linear(weight.view(1, -1), lw, lb)
+                bias, weight = bias.numpy(), weight.numpy()
+                lo, hi = _lo(bias, weight, N), _hi(bias, weight, N)
+            else:
+                lo, hi = _clipped_range(bias, weight, relu_list[i], N)
+            _set(qms[i], lo, hi)
+    else:
+        _, qms, branches = job
+        res = {b: _merge_branch(entries, N, eps) for b, entries in branches.items()}
+        if len(qms) == 1:
+            _set(qms[0], *_range_of(list(res.values())[0], N, eps))
+        else:
+            for i in range(len(res)):
+                _set(qms[i], *_range_of(res[str(i)], N, eps))
