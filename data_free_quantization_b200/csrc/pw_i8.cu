@@ -94,6 +94,11 @@ __device__ __forceinline__ uint32_t quant_code_bits(float x, const QuantConsts &
     return (uint32_t)__float2int_rn(fminf(fmaxf(__fdiv_rn(t, c.scale), c.qmin), c.qmax));
 }
 
+// kPre: the activation loads of ring stage s + 1 are issued right after stage s has been quantised, so they overlap
+// the barrier, the MMA issue and the wait for the ring slot.  It costs 11 more live registers (3 resident CTAs
+// per SM instead of 4): a gain for deep-K layers on small feature maps whose grids do not fill the SMs anyway
+// (14 x 14 / 7 x 7), a 4% loss for the large shallow ones -- dfq_pw_i8 picks per layer.
+template <bool kPre>
 __global__ void __launch_bounds__(kThreads)
 pw_i8_kernel(PwI8Args a) {
     extern __shared__ __align__(128) uint8_t smem[];
@@ -120,6 +125,28 @@ pw_i8_kernel(PwI8Args a) {
                      ::"r"(smem_u32(&tmem_base_s)), "r"((uint32_t)a.tmem_cols) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
+    // ---- this thread's pixel (GEMM row) and K half -------------------------------------------------------
+    const int r = tid & (kI8M - 1), h = tid >> 7;
+    const int64_t g = tile * kI8M + r;
+    const bool valid = g < a.G;
+    const int64_t n = valid ? g / a.P : 0;
+    const int p = valid ? (int)(g - n * a.P) : 0;
+    const float *xb = a.x + n * a.xs_n + (int64_t)p * a.xs_p;
+    const int xs_k = (int)a.xs_k;                        // K * P < 2^31 elements per image
+    // activations of one ring stage: two 16-wide K chunks per thread, all loads in flight before any use
+    float v[2][16];
+    auto load_stage = [&](int s) {
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+            const int k0 = s * kI8Slab + (h + 2 * c) * 16;
+            if (k0 < a.K) {                                           // warp-uniform: padded chunks cost nothing
+                const float *px = xb + (int64_t)k0 * xs_k;
+#pragma unroll
+                for (int j = 0; j < 16; ++j) v[c][j] = (valid && k0 + j < a.K) ? __ldg(px + j * xs_k) : 0.0f;
+            }
+        }
+    };
+    if (kPre) load_stage(0);                            // in flight during the TMEM allocation and the barrier
     const QuantConsts qc = consts_from_slot(*a.slot, a.bits, 0, 0.f, 0.f);
     const int sh = 8 - a.bits;                          // < 8-bit grids: a = (code - 2^(bits-1)) << sh, s_x >> sh
     const float sx = __fmul_rn(qc.scale, 1.0f / (float)(1 << sh));
@@ -138,15 +165,6 @@ pw_i8_kernel(PwI8Args a) {
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = tmem_base_s;
-
-    // ---- this thread's pixel (GEMM row) and K half -------------------------------------------------------
-    const int r = tid & (kI8M - 1), h = tid >> 7;
-    const int64_t g = tile * kI8M + r;
-    const bool valid = g < a.G;
-    const int64_t n = valid ? g / a.P : 0;
-    const int p = valid ? (int)(g - n * a.P) : 0;
-    const float *xb = a.x + n * a.xs_n + (int64_t)p * a.xs_p;
-    const int xs_k = (int)a.xs_k;                        // K * P < 2^31 elements per image
     const int8_t *wsrc = a.wpk + (int64_t)pass * a.slabs * bslab;
     // instruction descriptor: D = s32, A = B = s8, both K-major, N = npass, M = 128
     const uint32_t idesc = (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(a.npass >> 3) << 17) |
@@ -155,17 +173,7 @@ pw_i8_kernel(PwI8Args a) {
 
     for (int s = 0; s < a.slabs; ++s) {
         const int buf = s & 1;
-        // 1. this stage's activations: two 16-wide K chunks per thread, all loads in flight before any use
-        float v[2][16];
-#pragma unroll
-        for (int c = 0; c < 2; ++c) {
-            const int k0 = s * kI8Slab + (h + 2 * c) * 16;
-            if (k0 < a.K) {                                           // warp-uniform: padded chunks cost nothing
-                const float *px = xb + (int64_t)k0 * xs_k;
-#pragma unroll
-                for (int j = 0; j < 16; ++j) v[c][j] = (valid && k0 + j < a.K) ? __ldg(px + j * xs_k) : 0.0f;
-            }
-        }
+        if (!kPre) load_stage(s);                        // 1. this stage's activations
         // 2. the ring stage is free once the MMAs issued two slabs ago have retired
         if (s >= 2) mbar_wait(done0 + 8 * buf, ((s >> 1) - 1) & 1);
         if (tid == 0) {
@@ -194,6 +202,7 @@ pw_i8_kernel(PwI8Args a) {
             *reinterpret_cast<uint4 *>(sA + buf * kI8ASlab + (h + 2 * c) * (kI8M * 16) + r * 16) =
                 make_uint4(w4[0], w4[1], w4[2], w4[3]);
         }
+        if (kPre && s + 1 < a.slabs) load_stage(s + 1);
         // 4. generic-proxy stores -> visible to the tensor core's async proxy, then one thread issues
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         __syncthreads();
@@ -240,23 +249,35 @@ pw_i8_kernel(PwI8Args a) {
                        "=r"(d[15])
                      : "r"(tmem + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)(chunk * 16)));
         asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-        float *py = yb + (int64_t)oc * ys_o;
         const float4 *cc = reinterpret_cast<const float4 *>(chan_c + chunk * 16);
         const int nvalid = min(16, o_end - oc);                   // warp-uniform
+        float *py = yb + (int64_t)oc * ys_o;
+        if (!ev) {                                                // rows past the end (last tile only)
+        } else if (nvalid == 16) {                                       // the common case: no per-column predicate
 #pragma unroll
-        for (int j4 = 0; j4 < 4; ++j4) {
-            const float4 c4 = cc[j4];
-            const float cj[4] = {c4.x, c4.y, c4.z, c4.w};
+            for (int j4 = 0; j4 < 4; ++j4) {
+                const float4 c4 = cc[j4];
+                const float cj[4] = {c4.x, c4.y, c4.z, c4.w};
 #pragma unroll
-            for (int t = 0; t < 4; ++t) {
-                const int j = 4 * j4 + t;
-                const float yv = fmaxf(__fmaf_rn(fa, (float)(int)d[j], __fadd_rn(row_c, cj[t])), floor_v);
+                for (int t = 0; t < 4; ++t) {
+                    const float yv = fmaxf(__fmaf_rn(fa, (float)(int)d[4 * j4 + t], __fadd_rn(row_c, cj[t])), floor_v);
+                    *py = yv;
+                    py += ys_o;
+                    lo = fminf(lo, yv); hi = fmaxf(hi, yv);
+                }
+            }
+        } else {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {                        // compile-time indices keep d[] in registers
                 if (j < nvalid) {
-                    if (ev) py[j * ys_o] = yv;
+                    const float yv = fmaxf(__fmaf_rn(fa, (float)(int)d[j], __fadd_rn(row_c, chan_c[chunk * 16 + j])), floor_v);
+                    *py = yv;
+                    py += ys_o;
                     lo = fminf(lo, yv); hi = fmaxf(hi, yv);
                 }
             }
         }
+        __syncwarp();                                             // tcgen05.ld is warp-collective
     }
     if (!ev) { lo = INFINITY; hi = -INFINITY; }
     if (a.stats) {                                                // per-sample extrema, encoded (common.cuh)
@@ -332,13 +353,19 @@ extern "C" int dfq_pw_i8(const DfqPwI8Desc *d, void *stream) {
     const size_t smem = 2 * (size_t)kI8ASlab + 2 * (size_t)a.npass * kI8Slab;
     static bool attr_set = false;
     if (!attr_set) {
-        cudaError_t ce = cudaFuncSetAttribute(pw_i8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+        cudaError_t ce = cudaFuncSetAttribute(pw_i8_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+        if (ce == cudaSuccess)
+            ce = cudaFuncSetAttribute(pw_i8_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
         if (ce != cudaSuccess) return (int)ce;
         attr_set = true;
     }
     const int64_t tiles = (d->G + kI8M - 1) / kI8M;
     if (tiles * a.n_pass > 0x7fffffffll) return (int)cudaErrorInvalidValue;
-    pw_i8_kernel<<<(unsigned)(tiles * a.n_pass), kThreads, smem, (cudaStream_t)stream>>>(a);
+    static int sms = 0;
+    if (!sms) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); }
+    const bool pre = a.slabs >= 2 && tiles * a.n_pass <= (int64_t)8 * sms;
+    if (pre) pw_i8_kernel<true><<<(unsigned)(tiles * a.n_pass), kThreads, smem, (cudaStream_t)stream>>>(a);
+    else pw_i8_kernel<false><<<(unsigned)(tiles * a.n_pass), kThreads, smem, (cudaStream_t)stream>>>(a);
     g_launches += 1;
     return (int)cudaGetLastError();
 }
