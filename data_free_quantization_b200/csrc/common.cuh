@@ -219,5 +219,30 @@ __device__ __forceinline__ float quant_code(float x, const QuantConsts &c) {
 __device__ __forceinline__ float quant_dequant(float x, const QuantConsts &c) {     // :72-76, finite inputs
     return __fadd_rn(__fmul_rn(quant_code(x, c), c.scale), c.add_back);
 }
+// Four elements at once for the fast grids (c.fast checked by the caller, once per kernel): the four reciprocal
+// estimates share ONE branch to the exact path, taken when any of them sits near a tie (~1e-3 per call).
+__device__ __forceinline__ float4 quant_dequant4_fast(float4 v, const QuantConsts &c) {
+    const float x[4] = {v.x, v.y, v.z, v.w};
+    float t[4], cl[4], q[4];
+    bool near_tie = false;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        t[i] = __fadd_rn(x[i], c.neg_min);
+        cl[i] = fminf(fmaxf(__fmul_rn(t[i], c.rscale), c.qmin), c.qmax);
+        q[i] = rint_small(cl[i]);
+        near_tie |= fabsf(__fsub_rn(cl[i], q[i])) > c.amb;
+    }
+    if (near_tie) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            if (fabsf(__fsub_rn(cl[i], q[i])) > c.amb) {
+                const float tc = fminf(fmaxf(t[i], c.t_lo), c.t_hi);
+                q[i] = rint_small(fminf(fmaxf(div_const_rn(tc, c.scale, c.rscale), c.qmin), c.qmax));
+            }
+        }
+    }
+    return make_float4(__fadd_rn(__fmul_rn(q[0], c.scale), c.add_back), __fadd_rn(__fmul_rn(q[1], c.scale), c.add_back),
+                       __fadd_rn(__fmul_rn(q[2], c.scale), c.add_back), __fadd_rn(__fmul_rn(q[3], c.scale), c.add_back));
+}
 
 }  // namespace dfq

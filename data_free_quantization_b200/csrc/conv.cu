@@ -235,6 +235,19 @@ struct DwRowArgs {
 
 struct DwRow { float4 m; float l, r; };
 
+// one input row's three taps into 4 adjacent outputs (stride 1) / 2 outputs (stride 2); rows are passed by value so
+// that they stay in registers
+__device__ __forceinline__ void taps4(float (&acc)[4], const DwRow rw, float w0, float w1, float w2) {
+    acc[0] = __fmaf_rn(rw.m.y, w2, __fmaf_rn(rw.m.x, w1, __fmaf_rn(rw.l, w0, acc[0])));
+    acc[1] = __fmaf_rn(rw.m.z, w2, __fmaf_rn(rw.m.y, w1, __fmaf_rn(rw.m.x, w0, acc[1])));
+    acc[2] = __fmaf_rn(rw.m.w, w2, __fmaf_rn(rw.m.z, w1, __fmaf_rn(rw.m.y, w0, acc[2])));
+    acc[3] = __fmaf_rn(rw.r, w2, __fmaf_rn(rw.m.w, w1, __fmaf_rn(rw.m.z, w0, acc[3])));
+}
+__device__ __forceinline__ void taps2(float (&acc)[2], const DwRow rw, float w0, float w1, float w2) {
+    acc[0] = __fmaf_rn(rw.m.y, w2, __fmaf_rn(rw.m.x, w1, __fmaf_rn(rw.l, w0, acc[0])));
+    acc[1] = __fmaf_rn(rw.m.w, w2, __fmaf_rn(rw.m.z, w1, __fmaf_rn(rw.m.y, w0, acc[1])));
+}
+
 template <int S>
 __global__ void __launch_bounds__(kThreads, 4)
 dwconv3x3_rows_kernel(DwRowArgs a) {
@@ -256,20 +269,30 @@ dwconv3x3_rows_kernel(DwRowArgs a) {
 #pragma unroll
     for (int t = 0; t < 9; ++t) wreg[t] = __ldg(a.w + (int64_t)c * 9 + t);
     const float bv = a.bias ? __ldg(a.bias + c) : 0.0f;
-    const float *xp = a.x + ((int64_t)n * a.C + c) * a.H * a.W + 4 * j;
     float *yp = a.y + (((int64_t)n * a.C + c) * a.OH + r0) * a.OW + (S == 1 ? 4 : 2) * j;
     const bool first = j == 0, last = j == a.lanes - 1;
     const int ib = S * r0 - 1;                                   // first input row of the window
-    const int ir_last = S * (r0 + nr - 1) + 1;                   // last input row this item needs
-    auto valid = [&](int ir) { return active && ir >= 0 && ir < a.H && ir <= ir_last; };
+    // input rows this item really reads: [ir_lo, ir_lo + span]; everything else is zero padding (an inactive
+    // lane gets an empty range).  One unsigned compare per row.
+    const int ir_lo = max(ib, 0);
+    const unsigned span = active ? (unsigned)(min(S * (r0 + nr - 1) + 1, a.H - 1) - ir_lo) : 0u;
+    const int ir_base = active ? ir_lo : (1 << 30);
+    auto valid = [&](int ir) { return (unsigned)(ir - ir_base) <= span; };
+    const float4 *xrow = reinterpret_cast<const float4 *>(a.x + ((int64_t)n * a.C + c) * a.H * a.W + 4 * j);
+    const int w4 = a.W >> 2;                                      // row pitch in 128-bit words
     auto ld = [&](int ir) {
-        return valid(ir) ? __ldg(reinterpret_cast<const float4 *>(xp + (int64_t)ir * a.W)) : make_float4(0.f, 0.f, 0.f, 0.f);
+        return valid(ir) ? __ldg(xrow + (int64_t)ir * w4) : make_float4(0.f, 0.f, 0.f, 0.f);
     };
+    const int qmode = !on ? 0 : (qc.fast ? 1 : 2);               // warp-uniform
     auto qrow = [&](float4 v, int ir) {
         DwRow r;
-        if (on && valid(ir)) {
-            v.x = quant_dequant(v.x, qc); v.y = quant_dequant(v.y, qc);
-            v.z = quant_dequant(v.z, qc); v.w = quant_dequant(v.w, qc);
+        if (qmode == 1) {
+            if (valid(ir)) v = quant_dequant4_fast(v, qc);
+        } else if (qmode == 2) {
+            if (valid(ir)) {
+                v.x = quant_dequant(v.x, qc); v.y = quant_dequant(v.y, qc);
+                v.z = quant_dequant(v.z, qc); v.w = quant_dequant(v.w, qc);
+            }
         }
         r.m = v;
         const float l = __shfl_up_sync(0xffffffffu, v.w, 1), rr = __shfl_down_sync(0xffffffffu, v.x, 1);
@@ -285,17 +308,9 @@ dwconv3x3_rows_kernel(DwRowArgs a) {
             const float4 p3 = ld(ib + t + 4);
             const DwRow bot = qrow(p1, ib + t + 2);
             float acc[4] = {0.f, 0.f, 0.f, 0.f};
-            const DwRow *rows[3] = {&top, &mid, &bot};
-#pragma unroll
-            for (int i = 0; i < 3; ++i) {
-                const float w0 = wreg[3 * i], w1 = wreg[3 * i + 1], w2 = wreg[3 * i + 2];
-                const float L = rows[i]->l, R = rows[i]->r;
-                const float4 M = rows[i]->m;
-                acc[0] = __fmaf_rn(M.y, w2, __fmaf_rn(M.x, w1, __fmaf_rn(L, w0, acc[0])));
-                acc[1] = __fmaf_rn(M.z, w2, __fmaf_rn(M.y, w1, __fmaf_rn(M.x, w0, acc[1])));
-                acc[2] = __fmaf_rn(M.w, w2, __fmaf_rn(M.z, w1, __fmaf_rn(M.y, w0, acc[2])));
-                acc[3] = __fmaf_rn(R, w2, __fmaf_rn(M.w, w1, __fmaf_rn(M.z, w0, acc[3])));
-            }
+            taps4(acc, top, wreg[0], wreg[1], wreg[2]);
+            taps4(acc, mid, wreg[3], wreg[4], wreg[5]);
+            taps4(acc, bot, wreg[6], wreg[7], wreg[8]);
 #pragma unroll
             for (int u = 0; u < 4; ++u) {
                 if (a.bias) acc[u] = __fadd_rn(acc[u], bv);
@@ -316,15 +331,9 @@ dwconv3x3_rows_kernel(DwRowArgs a) {
             p1 = p3; p2 = p4;
             p3 = ld(ib + 2 * t + 5); p4 = ld(ib + 2 * t + 6);
             float acc[2] = {0.f, 0.f};
-            const DwRow *rows[3] = {&top, &mid, &bot};
-#pragma unroll
-            for (int i = 0; i < 3; ++i) {
-                const float w0 = wreg[3 * i], w1 = wreg[3 * i + 1], w2 = wreg[3 * i + 2];
-                const float L = rows[i]->l;
-                const float4 M = rows[i]->m;
-                acc[0] = __fmaf_rn(M.y, w2, __fmaf_rn(M.x, w1, __fmaf_rn(L, w0, acc[0])));
-                acc[1] = __fmaf_rn(M.w, w2, __fmaf_rn(M.z, w1, __fmaf_rn(M.y, w0, acc[1])));
-            }
+            taps2(acc, top, wreg[0], wreg[1], wreg[2]);
+            taps2(acc, mid, wreg[3], wreg[4], wreg[5]);
+            taps2(acc, bot, wreg[6], wreg[7], wreg[8]);
 #pragma unroll
             for (int u = 0; u < 2; ++u) {
                 if (a.bias) acc[u] = __fadd_rn(acc[u], bv);

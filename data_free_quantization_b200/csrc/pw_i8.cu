@@ -99,7 +99,7 @@ __device__ __forceinline__ uint32_t quant_code_bits(float x, const QuantConsts &
 // per SM instead of 4): a gain for deep-K layers on small feature maps whose grids do not fill the SMs anyway
 // (14 x 14 / 7 x 7), a 4% loss for the large shallow ones -- dfq_pw_i8 picks per layer.
 template <bool kPre>
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, kPre ? 3 : 4)
 pw_i8_kernel(PwI8Args a) {
     extern __shared__ __align__(128) uint8_t smem[];
     __shared__ __align__(8) uint64_t bars[4];           // full[2] (weights landed), done[2] (MMAs of the stage retired)
@@ -129,8 +129,11 @@ pw_i8_kernel(PwI8Args a) {
     const int r = tid & (kI8M - 1), h = tid >> 7;
     const int64_t g = tile * kI8M + r;
     const bool valid = g < a.G;
-    const int64_t n = valid ? g / a.P : 0;
-    const int p = valid ? (int)(g - n * a.P) : 0;
+    // image and pixel of this row; 32-bit division (dfq_pw_i8 refuses G >= 2^31), shared with the epilogue: the
+    // TMEM lane a warp may read, 32 * (warp % 4) + lane, is this thread's own row
+    const uint32_t n32 = valid ? (uint32_t)g / (uint32_t)a.P : 0u;
+    const int64_t n = n32;
+    const int p = valid ? (int)((uint32_t)g - n32 * (uint32_t)a.P) : 0;
     const float *xb = a.x + n * a.xs_n + (int64_t)p * a.xs_p;
     const int xs_k = (int)a.xs_k;                        // K * P < 2^31 elements per image
     // activations of one ring stage: two 16-wide K chunks per thread, all loads in flight before any use
@@ -227,11 +230,10 @@ pw_i8_kernel(PwI8Args a) {
     __syncthreads();
 
     // ---- epilogue: warp w reads TMEM lanes 32*(w%4).., 16-column chunks w/4, w/4+2, ... ---------------------
-    const int er = (warp & 3) * 32 + lane;
-    const int64_t eg = tile * kI8M + er;
-    const bool ev = eg < a.G;
-    const int64_t en = ev ? eg / a.P : 0;
-    const int ep = ev ? (int)(eg - en * a.P) : 0;
+    const int er = r;
+    const bool ev = valid;
+    const int64_t en = n;
+    const int ep = p;
     float *yb = a.y + en * a.ys_n + (int64_t)ep * a.ys_p;
     const int ys_o = (int)a.ys_o;
     const float fa = __fmul_rn(sx, a.s_w);
@@ -360,7 +362,7 @@ extern "C" int dfq_pw_i8(const DfqPwI8Desc *d, void *stream) {
         attr_set = true;
     }
     const int64_t tiles = (d->G + kI8M - 1) / kI8M;
-    if (tiles * a.n_pass > 0x7fffffffll) return (int)cudaErrorInvalidValue;
+    if (tiles * a.n_pass > 0x7fffffffll || d->G > 0x7fffffffll) return (int)cudaErrorInvalidValue;
     static int sms = 0;
     if (!sms) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); }
     const bool pre = a.slabs >= 2 && tiles * a.n_pass <= (int64_t)8 * sms;
