@@ -33,6 +33,9 @@ struct PwI8Args {
     int P, K, O, bits, relu;
     int n_pass, o_per_pass, npass, slabs, tmem_cols;
     float s_w, c_w;
+    // dense k x k form (kConv): K above is the PADDED reduction length taps * cchunks * 16, Kreal = taps * C
+    const float *wrt;                 // [taps][O] s_w * (sum over channels of the centred codes of one tap)
+    int C, H, W, OW, kh, kw, stride, pad, dil, taps, cchunks, Kreal;
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -94,11 +97,27 @@ __device__ __forceinline__ uint32_t quant_code_bits(float x, const QuantConsts &
     return (uint32_t)__float2int_rn(fminf(fmaxf(__fdiv_rn(t, c.scale), c.qmin), c.qmax));
 }
 
+// sum of the per-tap constants of output channel `ol` over the out-of-bounds taps in `oob` (fixed tap order)
+__device__ __forceinline__ float tap_corr(const float *tap_c, uint32_t oob, int taps, int npass, int ol) {
+    float corr = 0.0f;
+    for (int t = 0; t < taps; ++t)
+        if (oob >> t & 1u) corr = __fadd_rn(corr, tap_c[t * npass + ol]);
+    return corr;
+}
+
 // kPre: the activation loads of ring stage s + 1 are issued right after stage s has been quantised, so they overlap
 // the barrier, the MMA issue and the wait for the ring slot.  It costs 11 more live registers (3 resident CTAs
 // per SM instead of 4): a gain for deep-K layers on small feature maps whose grids do not fill the SMs anyway
 // (14 x 14 / 7 x 7), a 4% loss for the large shallow ones -- dfq_pw_i8 picks per layer.
-template <bool kPre>
+//
+// kConv: dense k x k convolution (groups = 1, any stride / zero padding / dilation) as an implicit GEMM on the same
+// pipeline.  The reduction index runs tap-major, channel-minor, channels padded to a multiple of 16, so every
+// 16-byte K chunk belongs to ONE tap: a thread reads it at the tap's input pixel (coalesced along the row) or, when
+// that pixel lies in the padding, stores s8 zeros.  Zero padding is an exact 0.0 in the reference (it quantises
+// before F.conv2d pads) while an s8 zero stands for c_x, so the epilogue takes c_x * (s_w * sum_c b[o,c,t] + C c_w)
+// back out for every out-of-bounds tap t of the pixel (a [taps][channels] table in shared memory; interior pixels
+// skip it).
+template <bool kPre, bool kConv>
 __global__ void __launch_bounds__(kThreads, kPre ? 3 : 4)
 pw_i8_kernel(PwI8Args a) {
     extern __shared__ __align__(128) uint8_t smem[];
@@ -113,6 +132,7 @@ pw_i8_kernel(PwI8Args a) {
     uint8_t *sA = smem;                                  // [2][4 K-chunks][128 rows][16 B]
     uint8_t *sB = smem + 2 * kI8ASlab;                   // [2][4 K-chunks][npass rows][16 B]
     const uint32_t bslab = (uint32_t)a.npass * kI8Slab;
+    float *tap_c = reinterpret_cast<float *>(sB + 2 * bslab);   // kConv: [taps][npass] c_x * (wrt[t][o] + C c_w s_x..)
     const uint32_t sA_u = smem_u32(sA), sB_u = smem_u32(sB);
     const uint32_t full0 = smem_u32(&bars[0]), done0 = smem_u32(&bars[2]);
 
@@ -134,18 +154,40 @@ pw_i8_kernel(PwI8Args a) {
     const uint32_t n32 = valid ? (uint32_t)g / (uint32_t)a.P : 0u;
     const int64_t n = n32;
     const int p = valid ? (int)((uint32_t)g - n32 * (uint32_t)a.P) : 0;
-    const float *xb = a.x + n * a.xs_n + (int64_t)p * a.xs_p;
-    const int xs_k = (int)a.xs_k;                        // K * P < 2^31 elements per image
+    const float *xb = a.x + n * a.xs_n + (kConv ? 0 : (int64_t)p * a.xs_p);
+    const int xs_k = (int)a.xs_k;                        // K * P < 2^31 elements per image (kConv: H * W)
+    int ih0 = 0, iw0 = 0;
+    if (kConv) {
+        const int oh = p / a.OW, ow = p - oh * a.OW;
+        ih0 = oh * a.stride - a.pad; iw0 = ow * a.stride - a.pad;
+    }
+    // chunk q of the reduction (16 K bytes): is it live, may this thread read it, where, how many real channels
+    auto chunk_src = [&](int q, bool &live, bool &inb, const float *&px, int &nch) {
+        if (kConv) {
+            const int t = q / a.cchunks, cc = q - t * a.cchunks;          // warp-uniform
+            live = t < a.taps;
+            const int i = t / a.kw, j = t - i * a.kw;
+            const int ih = ih0 + i * a.dil, iw = iw0 + j * a.dil;
+            inb = valid && live && (unsigned)ih < (unsigned)a.H && (unsigned)iw < (unsigned)a.W;
+            nch = a.C - cc * 16;
+            px = xb + ((int64_t)(cc * 16) * a.H + ih) * a.W + iw;         // dereferenced only when inb
+        } else {
+            live = q * 16 < a.K;
+            inb = valid;
+            nch = a.K - q * 16;
+            px = xb + (int64_t)(q * 16) * xs_k;
+        }
+    };
     // activations of one ring stage: two 16-wide K chunks per thread, all loads in flight before any use
     float v[2][16];
     auto load_stage = [&](int s) {
 #pragma unroll
         for (int c = 0; c < 2; ++c) {
-            const int k0 = s * kI8Slab + (h + 2 * c) * 16;
-            if (k0 < a.K) {                                           // warp-uniform: padded chunks cost nothing
-                const float *px = xb + (int64_t)k0 * xs_k;
+            bool live, inb; const float *px; int nch;
+            chunk_src(s * 4 + h + 2 * c, live, inb, px, nch);
+            if (live) {                                               // warp-uniform: padded chunks cost nothing
 #pragma unroll
-                for (int j = 0; j < 16; ++j) v[c][j] = (valid && k0 + j < a.K) ? __ldg(px + j * xs_k) : 0.0f;
+                for (int j = 0; j < 16; ++j) v[c][j] = (inb && j < nch) ? __ldg(px + j * xs_k) : 0.0f;
             }
         }
     };
@@ -159,10 +201,17 @@ pw_i8_kernel(PwI8Args a) {
         const int o = o0 + tid;
         float c = 0.0f;
         if (o < o_end) {
-            c = __fmaf_rn(cx, __ldg(a.wr + o), __fmul_rn(__fmul_rn((float)a.K, a.c_w), cx));
+            c = __fmaf_rn(cx, __ldg(a.wr + o), __fmul_rn(__fmul_rn((float)(kConv ? a.Kreal : a.K), a.c_w), cx));
             if (a.bias) c = __fadd_rn(c, __ldg(a.bias + o));
         }
         chan_c[tid] = c;
+    }
+    if (kConv) {                                          // what an out-of-bounds tap contributed through c_x
+        const float ccw = __fmul_rn(__fmul_rn((float)a.C, a.c_w), cx);
+        for (int idx = tid; idx < a.taps * a.npass; idx += kThreads) {
+            const int t = idx / a.npass, ol = idx - t * a.npass, o = o0 + ol;
+            tap_c[idx] = o < o_end ? __fmaf_rn(cx, __ldg(a.wrt + (int64_t)t * a.O + o), ccw) : 0.0f;
+        }
     }
     tc_fence_before();
     __syncthreads();
@@ -186,17 +235,16 @@ pw_i8_kernel(PwI8Args a) {
         // 3. quantise on load (utils/quantize.py:72-74), centre to s8, pack, canonical-order store
 #pragma unroll
         for (int c = 0; c < 2; ++c) {
-            const int k0 = s * kI8Slab + (h + 2 * c) * 16;
+            bool live, inb; const float *px; int nch;
+            chunk_src(s * 4 + h + 2 * c, live, inb, px, nch);
             uint32_t w4[4] = {0u, 0u, 0u, 0u};
-            if (k0 < a.K) {
+            if (live && (!kConv || __any_sync(0xffffffffu, inb))) {
 #pragma unroll
                 for (int q4 = 0; q4 < 4; ++q4) {
                     uint32_t b[4];
 #pragma unroll
-                    for (int j = 0; j < 4; ++j) {
-                        const int k = k0 + 4 * q4 + j;
-                        b[j] = (valid && k < a.K) ? quant_code_bits(v[c][4 * q4 + j], qc) : (128u >> sh);
-                    }
+                    for (int j = 0; j < 4; ++j)
+                        b[j] = (inb && 4 * q4 + j < nch) ? quant_code_bits(v[c][4 * q4 + j], qc) : (128u >> sh);
                     const uint32_t lo = __byte_perm(b[0], b[1], 0x0040), hi = __byte_perm(b[2], b[3], 0x0040);
                     w4[q4] = (__byte_perm(lo, hi, 0x5410) << sh) ^ 0x80808080u;
                     csum = __dp4a((int)w4[q4], 0x01010101, csum);
@@ -240,6 +288,14 @@ pw_i8_kernel(PwI8Args a) {
     const float row_c = __fmul_rn(__fmul_rn(sx, a.c_w), (float)(colsum_s[0][er] + colsum_s[1][er]));
     const float floor_v = a.relu ? 0.0f : -INFINITY;
     float lo = INFINITY, hi = -INFINITY;
+    uint32_t oob = 0;                                             // kConv: taps of this pixel that fell in the padding
+    if (kConv && ev) {
+        for (int t = 0; t < a.taps; ++t) {
+            const int i = t / a.kw, j = t - i * a.kw;
+            const int ih = ih0 + i * a.dil, iw = iw0 + j * a.dil;
+            if (!((unsigned)ih < (unsigned)a.H && (unsigned)iw < (unsigned)a.W)) oob |= 1u << t;
+        }
+    }
     for (int chunk = warp >> 2; chunk * 16 < a.npass; chunk += 2) {
         const int oc = o0 + chunk * 16;
         if (oc >= o_end) break;                                   // warp-uniform
@@ -262,7 +318,9 @@ pw_i8_kernel(PwI8Args a) {
                 const float cj[4] = {c4.x, c4.y, c4.z, c4.w};
 #pragma unroll
                 for (int t = 0; t < 4; ++t) {
-                    const float yv = fmaxf(__fmaf_rn(fa, (float)(int)d[4 * j4 + t], __fadd_rn(row_c, cj[t])), floor_v);
+                    float cst = __fadd_rn(row_c, cj[t]);
+                    if (kConv && oob) cst = __fsub_rn(cst, tap_corr(tap_c, oob, a.taps, a.npass, chunk * 16 + 4 * j4 + t));
+                    const float yv = fmaxf(__fmaf_rn(fa, (float)(int)d[4 * j4 + t], cst), floor_v);
                     *py = yv;
                     py += ys_o;
                     lo = fminf(lo, yv); hi = fmaxf(hi, yv);
@@ -272,7 +330,9 @@ pw_i8_kernel(PwI8Args a) {
 #pragma unroll
             for (int j = 0; j < 16; ++j) {                        // compile-time indices keep d[] in registers
                 if (j < nvalid) {
-                    const float yv = fmaxf(__fmaf_rn(fa, (float)(int)d[j], __fadd_rn(row_c, chan_c[chunk * 16 + j])), floor_v);
+                    float cst = __fadd_rn(row_c, chan_c[chunk * 16 + j]);
+                    if (kConv && oob) cst = __fsub_rn(cst, tap_corr(tap_c, oob, a.taps, a.npass, chunk * 16 + j));
+                    const float yv = fmaxf(__fmaf_rn(fa, (float)(int)d[j], cst), floor_v);
                     *py = yv;
                     py += ys_o;
                     lo = fminf(lo, yv); hi = fmaxf(hi, yv);
@@ -338,10 +398,45 @@ extern "C" int dfq_pw_i8_pack_host(const int8_t *codes, int O, int K, int8_t *pa
     return 0;
 }
 
+static int pw_i8_launch(PwI8Args &a, bool conv, int64_t G, cudaStream_t stream) {
+    a.tmem_cols = 32;
+    while (a.tmem_cols < a.npass) a.tmem_cols *= 2;
+    const size_t smem = 2 * (size_t)kI8ASlab + 2 * (size_t)a.npass * kI8Slab +
+                        (conv ? (size_t)a.taps * a.npass * sizeof(float) : 0);
+    if (smem > 64 * 1024) return (int)cudaErrorInvalidValue;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t ce = cudaFuncSetAttribute(pw_i8_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+        if (ce == cudaSuccess)
+            ce = cudaFuncSetAttribute(pw_i8_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+        if (ce == cudaSuccess)
+            ce = cudaFuncSetAttribute(pw_i8_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+        if (ce == cudaSuccess)
+            ce = cudaFuncSetAttribute(pw_i8_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+        if (ce != cudaSuccess) return (int)ce;
+        attr_set = true;
+    }
+    const int64_t tiles = (G + kI8M - 1) / kI8M;
+    if (tiles * a.n_pass > 0x7fffffffll || G > 0x7fffffffll) return (int)cudaErrorInvalidValue;
+    static int sms = 0;
+    if (!sms) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); }
+    const bool pre = a.slabs >= 2 && tiles * a.n_pass <= (int64_t)8 * sms;
+    const unsigned grid = (unsigned)(tiles * a.n_pass);
+    if (conv) {
+        if (pre) pw_i8_kernel<true, true><<<grid, kThreads, smem, stream>>>(a);
+        else pw_i8_kernel<false, true><<<grid, kThreads, smem, stream>>>(a);
+    } else {
+        if (pre) pw_i8_kernel<true, false><<<grid, kThreads, smem, stream>>>(a);
+        else pw_i8_kernel<false, false><<<grid, kThreads, smem, stream>>>(a);
+    }
+    g_launches += 1;
+    return (int)cudaGetLastError();
+}
+
 extern "C" int dfq_pw_i8(const DfqPwI8Desc *d, void *stream) {
     if (!d || !d->x || !d->y || !d->wpk || !d->wr || !d->in_slot || d->G <= 0 || d->bits < 1 || d->bits > 8)
         return (int)cudaErrorInvalidValue;
-    PwI8Args a;
+    PwI8Args a = {};
     int64_t bytes;
     int e = dfq_pw_i8_plan_host(d->O, d->K, &a.n_pass, &a.o_per_pass, &a.npass, &a.slabs, &bytes);
     if (e) return e;
@@ -350,24 +445,33 @@ extern "C" int dfq_pw_i8(const DfqPwI8Desc *d, void *stream) {
     a.xs_n = d->xs_n; a.xs_k = d->xs_k; a.xs_p = d->xs_p; a.ys_n = d->ys_n; a.ys_o = d->ys_o; a.ys_p = d->ys_p;
     a.P = d->P; a.K = d->K; a.O = d->O; a.bits = d->bits; a.relu = d->relu;
     a.s_w = d->s_w; a.c_w = d->c_w;
-    a.tmem_cols = 32;
-    while (a.tmem_cols < a.npass) a.tmem_cols *= 2;
-    const size_t smem = 2 * (size_t)kI8ASlab + 2 * (size_t)a.npass * kI8Slab;
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaError_t ce = cudaFuncSetAttribute(pw_i8_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
-        if (ce == cudaSuccess)
-            ce = cudaFuncSetAttribute(pw_i8_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
-        if (ce != cudaSuccess) return (int)ce;
-        attr_set = true;
-    }
-    const int64_t tiles = (d->G + kI8M - 1) / kI8M;
-    if (tiles * a.n_pass > 0x7fffffffll || d->G > 0x7fffffffll) return (int)cudaErrorInvalidValue;
-    static int sms = 0;
-    if (!sms) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); }
-    const bool pre = a.slabs >= 2 && tiles * a.n_pass <= (int64_t)8 * sms;
-    if (pre) pw_i8_kernel<true><<<(unsigned)(tiles * a.n_pass), kThreads, smem, (cudaStream_t)stream>>>(a);
-    else pw_i8_kernel<false><<<(unsigned)(tiles * a.n_pass), kThreads, smem, (cudaStream_t)stream>>>(a);
-    g_launches += 1;
-    return (int)cudaGetLastError();
+    return pw_i8_launch(a, false, d->G, (cudaStream_t)stream);
+}
+
+// Reduction length of the dense k x k form: taps * (C rounded up to 16); feed it to dfq_pw_i8_plan_host /
+// dfq_pw_i8_pack_host with the codes laid out [O][tap][C padded with zeros].
+extern "C" int dfq_conv_i8_k_host(int C, int kh, int kw) { return kh * kw * ((C + 15) / 16 * 16); }
+
+extern "C" int dfq_conv_i8(const DfqConvI8Desc *d, void *stream) {
+    if (!d || !d->x || !d->y || !d->wpk || !d->wr || !d->wrt || !d->in_slot || d->N <= 0 || d->bits < 1 || d->bits > 8 ||
+        d->kh <= 0 || d->kw <= 0 || d->kh * d->kw > 32 || d->stride <= 0 || d->dil <= 0 || d->pad < 0)
+        return (int)cudaErrorInvalidValue;
+    const int OH = (d->H + 2 * d->pad - d->dil * (d->kh - 1) - 1) / d->stride + 1;
+    const int OW = (d->W + 2 * d->pad - d->dil * (d->kw - 1) - 1) / d->stride + 1;
+    if (OH != d->OH || OW != d->OW || OH <= 0 || OW <= 0) return (int)cudaErrorInvalidValue;
+    if ((int64_t)d->C * d->H * d->W > 0x7fffffffll) return (int)cudaErrorInvalidValue;
+    PwI8Args a = {};
+    int64_t bytes;
+    a.taps = d->kh * d->kw; a.cchunks = (d->C + 15) / 16; a.K = a.taps * a.cchunks * 16; a.Kreal = a.taps * d->C;
+    int e = dfq_pw_i8_plan_host(d->O, a.K, &a.n_pass, &a.o_per_pass, &a.npass, &a.slabs, &bytes);
+    if (e) return e;
+    a.x = d->x; a.y = d->y; a.wpk = d->wpk; a.wr = d->wr; a.wrt = d->wrt; a.bias = d->bias;
+    a.slot = (const RangeSlot *)d->in_slot; a.stats = d->out_stats;
+    a.P = OH * OW; a.G = (int64_t)d->N * a.P;
+    a.xs_n = (int64_t)d->C * d->H * d->W; a.xs_k = (int64_t)d->H * d->W; a.xs_p = 1;
+    a.ys_n = (int64_t)d->O * a.P; a.ys_o = a.P; a.ys_p = 1;
+    a.O = d->O; a.bits = d->bits; a.relu = d->relu; a.s_w = d->s_w; a.c_w = d->c_w;
+    a.C = d->C; a.H = d->H; a.W = d->W; a.OW = OW; a.kh = d->kh; a.kw = d->kw; a.stride = d->stride; a.pad = d->pad;
+    a.dil = d->dil;
+    return pw_i8_launch(a, true, a.G, (cudaStream_t)stream);
 }

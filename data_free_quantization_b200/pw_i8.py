@@ -82,3 +82,79 @@ def make_desc(x_ptr, y_ptr, pk, bias, slot_ptr, stats_ptr, images, P, relu, bits
 
 def launch(desc):
     L.check(L.lib().dfq_pw_i8(ctypes.byref(desc), L.stream()), "dfq_pw_i8")
+
+
+# ---- dense k x k convolutions (csrc/pw_i8.cu, kConv; dfq_conv_i8) --------------------------------------------------
+def pack_weight_conv(w, bits=None):
+    """pack_weight for a dense [O, C, kh, kw] weight (groups == 1): the reduction runs tap-major with the channels
+    padded to a multiple of 16 (dfq_conv_i8_k_host), plus the per-tap code sums the padding correction needs.
+    Returns None when the tensor is not on a <= 8-bit grid."""
+    O, C, kh, kw = w.shape
+    taps, Cp = kh * kw, (C + 15) // 16 * 16
+    pk = None
+    for b in ([bits] if bits else (8, 7, 6, 5, 4, 3, 2)):
+        pk = _recover_codes(w, int(b))
+        if pk is not None:
+            break
+    if pk is None:
+        return None
+    s32, lo, q, b = pk
+    up = 2 ** (8 - b)
+    codes = ((q - 2 ** (b - 1)) * up).to(torch.int8).cpu().numpy().reshape(O, C, taps)
+    lay = np.zeros((O, taps, Cp), dtype=np.int8)
+    lay[:, :, :C] = codes.transpose(0, 2, 1)
+    K = taps * Cp
+    lib = L.lib()
+    assert K == lib.dfq_conv_i8_k_host(C, kh, kw)
+    n_pass, opp, npass, slabs, nbytes = (ctypes.c_int(), ctypes.c_int(), ctypes.c_int(), ctypes.c_int(), L.i64())
+    L.check(lib.dfq_pw_i8_plan_host(O, K, ctypes.byref(n_pass), ctypes.byref(opp), ctypes.byref(npass),
+                                    ctypes.byref(slabs), ctypes.byref(nbytes)), "dfq_pw_i8_plan_host")
+    packed = np.empty(nbytes.value, dtype=np.int8)
+    lay = np.ascontiguousarray(lay.reshape(O, K))
+    L.check(lib.dfq_pw_i8_pack_host(lay.ctypes.data, O, K, packed.ctypes.data), "dfq_pw_i8_pack_host")
+    s_eff = s32 / up
+    tap_sums = codes.astype(np.int64).sum(1)                                   # [O, taps]
+    wr = (tap_sums.sum(1).astype(np.float64) * s_eff).astype(np.float32)
+    wrt = np.ascontiguousarray((tap_sums.T.astype(np.float64) * s_eff).astype(np.float32))   # [taps, O]
+    dev = w.device
+    out = PackedWeight(torch.from_numpy(packed).to(dev), torch.from_numpy(wr).to(dev), s_eff,
+                       float(np.float32(lo + 2 ** (b - 1) * s32)), O, K, codes)
+    out.wrt = torch.from_numpy(wrt).to(dev)
+    out.geom = (C, kh, kw)
+    out.grid = (s32, lo, q.to(torch.int16).cpu().numpy().reshape(O, C, kh, kw))
+    return out
+
+
+def _recover_codes(w, bits):
+    """(scale, min, codes as a double tensor [O, K], bits) of an on-grid weight, else None (pack_weight_bits)."""
+    if not (1 <= bits <= 8) or not w.is_cuda:
+        return None
+    w2 = w.detach().reshape(w.shape[0], -1)
+    lo, hi = float(w2.min()), float(w2.max())
+    levels = float(2 ** bits - 1)
+    s32 = float(np.float32(max((hi - lo) / levels, 1e-8)))
+    q = torch.round((w2.double() - lo) / s32).clamp_(0, levels)
+    tol = 4 * 1.2e-7 * max(abs(lo), abs(hi)) + 1e-7 * (hi - lo)
+    if float((q * s32 + lo - w2.double()).abs().max()) > tol:
+        return None
+    return s32, lo, q, bits
+
+
+def make_conv_desc(x, y, pk, bias, slot_ptr, stats_ptr, stride, pad, dil, relu, bits):
+    """DfqConvI8Desc for x [N, C, H, W] -> y [N, O, OH, OW] (both contiguous fp32 CUDA tensors)."""
+    C, kh, kw = pk.geom
+    d = L.DfqConvI8Desc()
+    d.x, d.y = L.dev_f32(x, "input"), L.dev_f32(y, "output")
+    d.wpk, d.wr, d.wrt = pk.wpk.data_ptr(), pk.wr.data_ptr(), pk.wrt.data_ptr()
+    d.bias = None if bias is None else L.dev_f32(bias, "bias")
+    d.in_slot, d.out_stats = slot_ptr, stats_ptr
+    d.N, d.C, d.H, d.W = x.shape
+    d.O, d.OH, d.OW = y.shape[1], y.shape[2], y.shape[3]
+    d.kh, d.kw, d.stride, d.pad, d.dil = kh, kw, int(stride), int(pad), int(dil)
+    d.bits, d.relu = int(bits), int(relu)
+    d.s_w, d.c_w = pk.s_w, pk.c_w
+    return d
+
+
+def launch_conv(desc):
+    L.check(L.lib().dfq_conv_i8(ctypes.byref(desc), L.stream()), "dfq_conv_i8")

@@ -23,7 +23,7 @@
 extern "C" {
 #endif
 
-#define DFQ_ABI_VERSION 9
+#define DFQ_ABI_VERSION 10
 
 #if defined(__GNUC__)
 #pragma GCC visibility push(default)   /* the library is built with -fvisibility=hidden */
@@ -242,6 +242,28 @@ typedef struct DfqPwI8Desc {
 int dfq_pw_i8_plan_host(int O, int K, int *n_pass, int *o_per_pass, int *npass, int *slabs, int64_t *packed_bytes);
 int dfq_pw_i8_pack_host(const int8_t *codes_host, int O, int K, int8_t *packed_host);
 int dfq_pw_i8(const DfqPwI8Desc *desc_host, void *stream);
+
+/* Dense k x k convolution of the same forward (groups == 1; DeepLab's atrous 3x3 and decoder convolutions,
+ * utils/quantize.py:250-256 with modeling/segmentation/aspp.py:50-53, decoder.py:22-30) as an implicit GEMM on the
+ * same tcgen05 pipeline: x [N,C,H,W] fp32, y [N,O,OH,OW] fp32, zero padding `pad`, any stride / dilation.
+ * Reduction order: tap-major, channels padded to a multiple of 16 -- dfq_conv_i8_k_host gives its length K;
+ * lay the centred codes out as [O][kh*kw][C padded with zeros] and pack them with dfq_pw_i8_pack_host(codes, O, K).
+ * wr as in DfqPwI8Desc; wrt[t][o] = s_w * (sum over channels of the centred codes of tap t): what a tap that falls
+ * into the zero padding must not contribute. */
+typedef struct DfqConvI8Desc {
+    const float *x;
+    float *y;
+    const int8_t *wpk;
+    const float *wr;         /* [O]                                                             */
+    const float *wrt;        /* [kh*kw][O]                                                      */
+    const float *bias;       /* [O] or NULL                                                     */
+    const float *in_slot;    /* QuantMeasure range of the input {min, max, scale, 0}; required  */
+    unsigned *out_stats;     /* [N, 2] encoded per-sample extrema of y, or NULL                 */
+    int32_t N, C, H, W, O, OH, OW, kh, kw, stride, pad, dil, bits, relu;
+    float s_w, c_w;
+} DfqConvI8Desc;
+int dfq_conv_i8_k_host(int C, int kh, int kw);
+int dfq_conv_i8(const DfqConvI8Desc *desc_host, void *stream);
 
 /* ---- (b) cross-layer equalisation: Cross_layer_equal.py:63-115 ---------------------- */
 /* sorts pairs by stage (stable) and fills first_unit/n_units */
