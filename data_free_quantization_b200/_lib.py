@@ -199,11 +199,22 @@ def dev_f32(t, name="tensor", allow_none=False):
     return t.data_ptr()
 
 
+_weights_epoch = 0
+
+
+def weights_epoch():
+    """Counter that moves whenever a multi-tensor (weight-side) pass is launched: caches derived from weight values
+    (packed integer codes of the eval kernels) are keyed on it."""
+    return _weights_epoch
+
+
 def table_to_device(arr, device):
     """ctypes array of descriptor structs -> uint8 CUDA tensor holding the same bytes.  Staged through pinned
     memory and copied asynchronously on the current stream: a pageable copy would block the host until every
     kernel already queued (e.g. the whole CLE loop) has finished.  torch's caching host allocator keeps the
     pinned block alive until the copy has run."""
+    global _weights_epoch
+    _weights_epoch += 1                       # every weight-side pass uploads a descriptor table
     n = ctypes.sizeof(arr)
     host = torch.empty(n, dtype=torch.uint8, pin_memory=True)
     ctypes.memmove(host.data_ptr(), ctypes.addressof(arr), n)

@@ -171,14 +171,12 @@ class QuantMeasure(nn.Module):
         self.running_max.mul_(1 - self.momentum).add_(max_value * self.momentum)
         return quantize(input, self.num_bits, min_value=float(min_value), max_value=float(max_value), num_chunks=16)
 
-    def _forward_eval(self, input):
-        """Eval mode (:107-111, :119-123) with the range resident on the device: per-sample extrema, their batch
-        mean, the running-range update and the scale are formed by dfq_measure_update; no float() round trip."""
+    def measure(self, input):
+        """Eval mode (:107-111): per-sample extrema, their batch mean, the running-range update and the scale, all
+        on the device (dfq_measure_update; no float() round trip).  Returns the range slot {min, max, scale, 0} a
+        consumer kernel quantises with."""
         x = input.detach()
         L.dev_f32(x, "input")
-        out = torch.empty_like(x)
-        if x.numel() == 0:
-            return out
         n = x.size(0)
         slot = torch.empty(4, dtype=torch.float32, device=x.device)
         stats = torch.empty(2 * n, dtype=torch.float32, device=x.device) if self.update_stat else None
@@ -187,6 +185,16 @@ class QuantMeasure(nn.Module):
             L.dev_f32(self.running_max, "running_max"), slot.data_ptr(), int(self.num_bits), 0,
             1 if self.update_stat else 0, None if stats is None else stats.data_ptr(), L.stream()),
             "dfq_measure_update")
+        return slot
+
+    def _forward_eval(self, input):
+        """Eval mode (:107-111, :119-123) with the range resident on the device."""
+        x = input.detach()
+        L.dev_f32(x, "input")
+        out = torch.empty_like(x)
+        if x.numel() == 0:
+            return out
+        slot = self.measure(x)
         L.check(L.lib().dfq_fake_quant_apply_slot_f32(x.data_ptr(), out.data_ptr(), None, x.numel(),
                                                       int(self.num_bits), 0, slot.data_ptr(), L.stream()),
                 "dfq_fake_quant_apply_slot_f32")
@@ -208,6 +216,99 @@ def _quant_weight(weight, num_bits):
     out = torch.empty_like(weight)
     fake_quant_tensors([weight.detach()], num_bits, 0, outs=[out])
     return out
+
+
+# ---- fused eval forward of the QuantN* layers: quantise-on-load kernels instead of quant() + F.conv2d ------------
+# QuantNConv2d / QuantNLinear.forward (utils/quantize.py:250-256, 358-363) are x_hat = quant(x); F.conv2d(x_hat, W, b).
+# In eval mode on CUDA, with W on an integer grid of <= 8 bits (what quantize_targ_layer leaves), the same values
+# come from ONE kernel that reads x, quantises it on load with the QuantMeasure's device-resident range and runs the
+# reduction as exact s8 x s8 -> s32 sums on tcgen05 (dense k x k: dfq_conv_i8; 1 x 1 / linear: dfq_pw_i8); depthwise
+# 3 x 3 goes to the CUDA-core kernel (dfq_qconv2d_f32).  FUSED_EVAL = False restores the two-step form (quant on
+# our kernel, arithmetic through cuDNN fp32) -- bench.py's `module_path` comparator.
+FUSED_EVAL = True
+fused_calls = {"conv_i8": 0, "pw_i8": 0, "depthwise": 0, "linear_i8": 0}     # launches per kind (tests, tools)
+
+
+def _packed(layer, conv):
+    """Integer codes of the layer's weight packed for the tensor-core kernels, cached until any weight-side pass
+    runs again (L.weights_epoch() moves with every descriptor-table upload) or the tensor is replaced."""
+    from .. import pw_i8
+    w = layer.weight
+    key = (w.data_ptr(), w._version, tuple(w.shape), L.weights_epoch())
+    hit = getattr(layer, "_dfq_packed", None)
+    if hit is not None and hit[0] == key:
+        return hit[1]
+    pk = pw_i8.pack_weight_conv(w.detach()) if conv else pw_i8.pack_weight(w.detach())
+    layer._dfq_packed = (key, pk)
+    return pk
+
+
+def _fused_conv_forward(layer, x):
+    """QuantNConv2d.forward in one launch, or None when this layer / input is not covered."""
+    from .. import pw_i8
+    if not (FUSED_EVAL and x.is_cuda and not layer.quant.training and x.dim() == 4 and x.numel() > 0
+            and x.dtype == torch.float32 and layer.padding_mode == "zeros" and isinstance(layer.padding, tuple)):
+        return None
+    kh, kw = layer.kernel_size
+    (sh, sw), (ph, pw_), (dh, dw) = layer.stride, layer.padding, layer.dilation
+    if sh != sw or ph != pw_ or dh != dw:
+        return None
+    N, C, H, W = x.shape
+    OH = (H + 2 * ph - dh * (kh - 1) - 1) // sh + 1
+    OW = (W + 2 * ph - dh * (kw - 1) - 1) // sh + 1
+    O = layer.out_channels
+    depthwise = layer.groups == C == O and kh == kw == 3
+    if not depthwise and layer.groups != 1:
+        return None
+    x = x.detach().contiguous()
+    bias = None if layer.bias is None else layer.bias.detach()
+    bits = int(layer.quant.num_bits)
+    if depthwise:
+        slot = layer.quant.measure(x)
+        y = torch.empty(N, O, OH, OW, dtype=torch.float32, device=x.device)
+        d = L.DfqConvDesc()
+        d.x, d.y, d.w = x.data_ptr(), y.data_ptr(), L.dev_f32(layer.weight.detach(), "weight")
+        d.bias = None if bias is None else L.dev_f32(bias, "bias")
+        d.in_slot, d.out_stats = slot.data_ptr(), None
+        d.N, d.C_in, d.H, d.W, d.C_out, d.OH, d.OW = N, C, H, W, O, OH, OW
+        d.kh, d.kw, d.stride, d.pad, d.dil, d.groups, d.relu, d.bits = kh, kw, sh, ph, dh, layer.groups, 0, bits
+        L.check(L.lib().dfq_qconv2d_f32(ctypes.byref(d), L.stream()), "dfq_qconv2d_f32")
+        fused_calls["depthwise"] += 1
+        return y
+    pointwise = kh == kw == 1 and sh == 1 and ph == 0
+    pk = _packed(layer, conv=not pointwise)
+    if pk is None:
+        return None
+    slot = layer.quant.measure(x)
+    y = torch.empty(N, O, OH, OW, dtype=torch.float32, device=x.device)
+    if pointwise:
+        d = pw_i8.make_desc(x.data_ptr(), y.data_ptr(), pk, bias, slot.data_ptr(), None, N, H * W, False, bits)
+        pw_i8.launch(d)
+        fused_calls["pw_i8"] += 1
+    else:
+        d = pw_i8.make_conv_desc(x, y, pk, bias, slot.data_ptr(), None, sh, ph, dh, False, bits)
+        pw_i8.launch_conv(d)
+        fused_calls["conv_i8"] += 1
+    return y
+
+
+def _fused_linear_forward(layer, x):
+    from .. import pw_i8
+    if not (FUSED_EVAL and x.is_cuda and not layer.quant.training and x.dim() == 2 and x.numel() > 0
+            and x.dtype == torch.float32):
+        return None
+    pk = _packed(layer, conv=False)
+    if pk is None:
+        return None
+    x = x.detach().contiguous()
+    slot = layer.quant.measure(x)
+    y = torch.empty(x.shape[0], layer.out_features, dtype=torch.float32, device=x.device)
+    bias = None if layer.bias is None else layer.bias.detach()
+    d = pw_i8.make_desc(x.data_ptr(), y.data_ptr(), pk, bias, slot.data_ptr(), None, x.shape[0], 1, False,
+                        int(layer.quant.num_bits), linear=True)
+    pw_i8.launch(d)
+    fused_calls["linear_i8"] += 1
+    return y
 
 
 class QuantConv2d(nn.Conv2d):
@@ -238,6 +339,9 @@ class QuantNConv2d(nn.Conv2d):
         self.quant = QuantMeasure(num_bits=num_bits_act, momentum=momentum)
 
     def forward(self, input):
+        fused = _fused_conv_forward(self, input)
+        if fused is not None:
+            return fused
         input = self.quant(input)
         return _conv2d_fp32(input, self.weight, self.bias, self.stride, self.padding, self.dilation, self.groups)
 
@@ -267,6 +371,9 @@ class QuantNLinear(nn.Linear):
         self.quant = QuantMeasure(num_bits=num_bits_act, momentum=momentum)
 
     def forward(self, input):
+        fused = _fused_linear_forward(self, input)
+        if fused is not None:
+            return fused
         input = self.quant(input)
         return F.linear(input, self.weight, self.bias)
 

@@ -134,6 +134,8 @@ def test_quantised_eval_matches_reference(dgold, run):
             n = k[len("eval/tap/"):]
             hooks.append(mods[n].register_forward_hook(
                 lambda mod, inp, out, n=n: taps.__setitem__(n, out.detach().clone())))
+    from data_free_quantization_b200.utils import quantize as Q
+    before = dict(Q.fused_calls)
     replace_op()
     try:
         with torch.no_grad():
@@ -142,6 +144,10 @@ def test_quantised_eval_matches_reference(dgold, run):
         restore_op()
         for h in hooks:
             h.remove()
+    # every target layer ran on its own kernel: 6 dense k x k on tcgen05 (dfq_conv_i8: stem, 3 atrous 3x3, 2 decoder
+    # 3x3), 38 pointwise on tcgen05 (dfq_pw_i8), 17 (dilated) depthwise on the CUDA-core kernel -- no cuDNN
+    used = {k: Q.fused_calls[k] - before[k] for k in before}
+    assert used == {"conv_i8": 6, "pw_i8": 38, "depthwise": 17, "linear_i8": 0}, used
     assert len(taps) == 6
     for n, v in taps.items():
         ref = npz["eval/tap/" + n]
