@@ -45,13 +45,14 @@ class _T:
 
 
 class EvalPlan:
-    def __init__(self, model, transformer, batch, in_shape=(3, 224, 224), pw_impl="i8"):
+    def __init__(self, model, transformer, batch, in_shape=(3, 224, 224), pw_impl="i8", dense_impl="i8"):
         """pw_impl: "i8" = pointwise convs / linear layers on the tcgen05 s8 kernel (csrc/pw_i8.cu) wherever the
         layer's weights sit on an integer grid of <= 8 bits, "fp32" = the CUDA-core comparator everywhere."""
         self.model, self.fxg = model, transformer.fx_graph
         self.dev = next(model.parameters()).device
         self.N = int(batch)
         self.pw_impl = pw_impl
+        self.dense_impl = dense_impl     # "i8": dense k x k on tcgen05 (dfq_conv_i8); "direct": CUDA-core direct form
         self.ops = []                # (name, callable)
         self.measures = []           # (qm, slot index, input tensor)
         self.keep = []               # ctypes objects / tensors that must outlive the plan
@@ -236,6 +237,11 @@ class EvalPlan:
                 if (self.pw_impl == "i8" and kh == 1 and kw == 1 and g == 1 and s == 1 and p == 0
                         and st["slot"] is not None):
                     i8 = self._i8_launch(m, wq, bq, src, out, st, N, src.shape[2] * src.shape[3], linear=False)
+                elif (self.pw_impl == "i8" and g == 1 and kh * kw > 1 and st["slot"] is not None
+                        and self.dense_impl == "i8" and m.in_channels >= 16):
+                    # (the 3-channel stem stays on the register-blocked direct kernel: 0.43 ms against 1.41 ms as
+                    # an implicit GEMM whose 16-byte K chunks would be 13/16 padding)
+                    i8 = self._conv_i8_launch(m, wq, bq, src, out, st, s, p, d)
                 self.ops.append((st["name"], i8 or self._conv_launch(desc, st)))
             elif st["kind"] == "linear":
                 m, src, out = st["m"], st["src"], st["out"]
@@ -289,6 +295,19 @@ class EvalPlan:
         self.keep += [pk, desc]
         self.i8_layers.append(st["name"])
         return lambda: pw_i8.launch(desc)
+
+    def _conv_i8_launch(self, m, wq, bq, src, out, st, stride, pad, dil):
+        """Dense k x k convolution as tcgen05 implicit GEMM (dfq_conv_i8), or None when the weights are off-grid."""
+        from . import pw_i8
+        pk = pw_i8.pack_weight_conv(wq, getattr(m, "num_bits", None))
+        if pk is None:
+            return None
+        stats = None if out.stats is None else out.stats.data_ptr()
+        desc = pw_i8.make_conv_desc(src.buf.view(src.shape), out.buf.view(out.shape), pk, bq, self.slots[st["slot"]].data_ptr(), stats, stride, pad,
+                                    dil, st["relu"], int(m.quant.num_bits))
+        self.keep += [pk, desc]
+        self.i8_layers.append(st["name"])
+        return lambda: pw_i8.launch_conv(desc)
 
     def _conv_launch(self, desc, st):
         lib, stream = L.lib(), L.stream

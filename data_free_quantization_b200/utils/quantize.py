@@ -226,7 +226,7 @@ def _quant_weight(weight, num_bits):
 # 3 x 3 goes to the CUDA-core kernel (dfq_qconv2d_f32).  FUSED_EVAL = False restores the two-step form (quant on
 # our kernel, arithmetic through cuDNN fp32) -- bench.py's `module_path` comparator.
 FUSED_EVAL = True
-fused_calls = {"conv_i8": 0, "pw_i8": 0, "depthwise": 0, "linear_i8": 0}     # launches per kind (tests, tools)
+fused_calls = {"conv_i8": 0, "pw_i8": 0, "depthwise": 0, "direct": 0, "linear_i8": 0}     # launches per kind (tests, tools)
 
 
 def _packed(layer, conv):
@@ -260,10 +260,13 @@ def _fused_conv_forward(layer, x):
     depthwise = layer.groups == C == O and kh == kw == 3
     if not depthwise and layer.groups != 1:
         return None
+    # few input channels (the 3 -> 32 stem): the CUDA-core direct form beats an implicit GEMM whose 16-byte K chunks
+    # would be mostly padding
+    direct = layer.groups == 1 and kh * kw > 1 and C < 16 and C * kh * kw <= 64
     x = x.detach().contiguous()
     bias = None if layer.bias is None else layer.bias.detach()
     bits = int(layer.quant.num_bits)
-    if depthwise:
+    if depthwise or direct:
         slot = layer.quant.measure(x)
         y = torch.empty(N, O, OH, OW, dtype=torch.float32, device=x.device)
         d = L.DfqConvDesc()
@@ -273,7 +276,7 @@ def _fused_conv_forward(layer, x):
         d.N, d.C_in, d.H, d.W, d.C_out, d.OH, d.OW = N, C, H, W, O, OH, OW
         d.kh, d.kw, d.stride, d.pad, d.dil, d.groups, d.relu, d.bits = kh, kw, sh, ph, dh, layer.groups, 0, bits
         L.check(L.lib().dfq_qconv2d_f32(ctypes.byref(d), L.stream()), "dfq_qconv2d_f32")
-        fused_calls["depthwise"] += 1
+        fused_calls["depthwise" if depthwise else "direct"] += 1
         return y
     pointwise = kh == kw == 1 and sh == 1 and ph == 0
     pk = _packed(layer, conv=not pointwise)

@@ -144,10 +144,10 @@ def test_quantised_eval_matches_reference(dgold, run):
         restore_op()
         for h in hooks:
             h.remove()
-    # every target layer ran on its own kernel: 6 dense k x k on tcgen05 (dfq_conv_i8: stem, 3 atrous 3x3, 2 decoder
-    # 3x3), 38 pointwise on tcgen05 (dfq_pw_i8), 17 (dilated) depthwise on the CUDA-core kernel -- no cuDNN
+    # every target layer ran on its own kernel: 5 dense 3x3 on tcgen05 (dfq_conv_i8: 3 atrous, 2 decoder), 38
+    # pointwise on tcgen05 (dfq_pw_i8), 17 (dilated) depthwise and the 3-channel stem on CUDA cores -- no cuDNN
     used = {k: Q.fused_calls[k] - before[k] for k in before}
-    assert used == {"conv_i8": 6, "pw_i8": 38, "depthwise": 17, "linear_i8": 0}, used
+    assert used == {"conv_i8": 5, "pw_i8": 38, "depthwise": 17, "direct": 1, "linear_i8": 0}, used
     assert len(taps) == 6
     for n, v in taps.items():
         ref = npz["eval/tap/" + n]
