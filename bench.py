@@ -538,7 +538,10 @@ def _main(args):
     roof = {"kernel": ("cle2_kernel" if cle_impl == "stream" else "cle_persistent_kernel") +
                       f" ({cle_iters} iterations in one cooperative launch)", "bound": "hbm",
             "achieved": round(ach, 1) if ach else None, "peak": peak, "unit": "GB/s",
-            "frac": round(ach / peak, 4) if ach else None, "traffic": None, "peak_source": peak_src,
+            "frac": round(ach / peak, 4) if ach else None,
+            # dram__bytes_read.sum + dram__bytes_write.sum of one launch, ncu --set full (profiles/r1j_ncu_cle2.md:
+            # 14.8928 MB + 1.0980 MB); the kernel has not changed since that capture
+            "traffic": 15990784 if cle_impl == "stream" else None, "peak_source": peak_src,
             "kernel_ms": round(cle_kernel_ms, 4) if cle_kernel_ms else None,
             "algorithmic_bytes": cle_bytes,
             "note": "the 14 MB of weights live in the 126 MB L2 for all iterations, so DRAM traffic is ~2 x 14 MB "
