@@ -16,6 +16,7 @@
 //   * one thread issues the MMAs of the slab and commits them to the ring's "free" mbarrier.
 // Epilogue: tcgen05.ld 32x32b (lane = pixel), the FMA chain above, bias, ReLU, per-sample min/max of the output
 // for the next QuantMeasure (utils/quantize.py:110-111), coalesced fp32 stores.
+#include <cstdlib>
 #include "common.cuh"
 
 namespace dfq {
@@ -36,6 +37,7 @@ struct PwI8Args {
     // dense k x k form (kConv): K above is the PADDED reduction length taps * cchunks * 16, Kreal = taps * C
     const float *wrt;                 // [taps][O] s_w * (sum over channels of the centred codes of one tap)
     int C, H, W, OW, kh, kw, stride, pad, dil, taps, cchunks, Kreal;
+    int64_t tiles;                    // warp-specialised form: 128-pixel tiles (work items = tiles * n_pass)
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -363,6 +365,244 @@ pw_i8_kernel(PwI8Args a) {
                      : "memory");
 }
 
+
+// ---------------------------------------------------------------------------------------------------------
+// Persistent, role-split form of the pointwise / linear kernel (same arithmetic, same packed weights).
+// A CTA walks the work items blockIdx.x, blockIdx.x + gridDim.x, ... (item = tile * n_pass + pass, gridDim.x a
+// multiple of n_pass so that the pass is fixed per CTA).  Roles meet only at mbarriers:
+//   warps 0-3 / 4-7  two worker groups taking alternate items.  Thread r of a group owns GEMM row r of its tile from
+//              start to end: per 64-byte K slab it loads its 64 activations (two rounds of 32 loads in flight),
+//              quantises, packs, stores the canonical-order rows of the group's ring stage and arrives on
+//              full_a[group][stage] (count 128); then it waits for acc_full[group] and runs the epilogue of the
+//              SAME row (its code sum never leaves its registers): tcgen05.ld, FMA chain, stores, per-sample
+//              extrema.  While one group is in its epilogue the other one is producing: loads, tensor pipe and
+//              stores of neighbouring tiles overlap whatever the layer's K : N ratio is.
+//   warp 8     lane 0 issues the MMAs in item order: waits full_a / full_b, 2 x tcgen05.mma into the group's TMEM
+//              accumulator, commits to empty_a[group][stage] and empty_b[stage]; after the last slab to acc_full.
+//   warp 9     lane 0 streams the weight slabs (3-deep ring): waits empty_b, one bulk copy per slab onto full_b.
+// The TMEM allocation (2 x npass columns), the barriers, the quantiser constants and the per-channel constants are
+// set up once per CTA instead of once per tile.
+constexpr int kWsBStages = 3;
+constexpr int kWsThreads = 320;
+
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+
+__global__ void __launch_bounds__(kWsThreads, 2)
+pw_i8_ws_kernel(PwI8Args a) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    // full_a[2][2], empty_a[2][2], acc_full[2], full_b[3], empty_b[3]
+    __shared__ __align__(8) uint64_t bars[10 + 2 * kWsBStages];
+    __shared__ uint32_t tmem_base_s;
+    __shared__ __align__(16) float chan_c[256];
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int pass = blockIdx.x % a.n_pass;
+    const int64_t items = a.tiles * a.n_pass;
+    const uint32_t bslab = (uint32_t)a.npass * kI8Slab;
+    uint8_t *sA = smem;                                   // [group][2 stages][4 K-chunks][128 rows][16 B]
+    uint8_t *sB = smem + 4 * kI8ASlab;                    // [3 stages][4 K-chunks][npass rows][16 B]
+    const uint32_t sA_u = smem_u32(sA), sB_u = smem_u32(sB);
+    const uint32_t full_a = smem_u32(&bars[0]), empty_a = smem_u32(&bars[4]), acc_full = smem_u32(&bars[8]),
+                   full_b = smem_u32(&bars[10]), empty_b = smem_u32(&bars[10 + kWsBStages]);
+    if (tid == 0) {
+        for (int i = 0; i < 4; ++i) { mbar_init(full_a + 8 * i, kI8M); mbar_init(empty_a + 8 * i, 1); }
+        for (int i = 0; i < 2; ++i) mbar_init(acc_full + 8 * i, 1);
+        for (int i = 0; i < kWsBStages; ++i) { mbar_init(full_b + 8 * i, 1); mbar_init(empty_b + 8 * i, 1); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 8) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
+                     ::"r"(smem_u32(&tmem_base_s)), "r"((uint32_t)a.tmem_cols) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    const QuantConsts qc = consts_from_slot(*a.slot, a.bits, 0, 0.f, 0.f);
+    const int sh = 8 - a.bits;
+    const float sx = __fmul_rn(qc.scale, 1.0f / (float)(1 << sh));
+    const float cx = __fmaf_rn(128.0f, sx, qc.add_back);
+    const int o0 = pass * a.o_per_pass, o_end = min(a.O, o0 + a.o_per_pass);
+    if (tid < a.npass) {
+        const int o = o0 + tid;
+        float c = 0.0f;
+        if (o < o_end) {
+            c = __fmaf_rn(cx, __ldg(a.wr + o), __fmul_rn(__fmul_rn((float)a.K, a.c_w), cx));
+            if (a.bias) c = __fadd_rn(c, __ldg(a.bias + o));
+        }
+        chan_c[tid] = c;
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = tmem_base_s;
+    const uint32_t acc_cols = (uint32_t)a.tmem_cols >> 1;        // columns per accumulator buffer (>= npass)
+
+    if (warp < 8) {
+        // ======================================================================== workers (two groups)
+        const uint32_t grp = (uint32_t)warp >> 2;
+        const int r = tid & (kI8M - 1);                          // GEMM row = TMEM lane 32 * (warp % 4) + lane
+        const int xs_k = (int)a.xs_k, ys_o = (int)a.ys_o;
+        const float fa = __fmul_rn(sx, a.s_w), sxcw = __fmul_rn(sx, a.c_w);
+        const float floor_v = a.relu ? 0.0f : -INFINITY;
+        const uint32_t fa_bar = full_a + 16 * grp, ea_bar = empty_a + 16 * grp, af_bar = acc_full + 8 * grp;
+        uint8_t *sAg = sA + grp * 2 * kI8ASlab;
+        uint32_t gs = 0, jt = 0;
+        for (int64_t item = blockIdx.x + (int64_t)grp * gridDim.x; item < items; item += 2 * (int64_t)gridDim.x, ++jt) {
+            const int64_t g = (item / a.n_pass) * kI8M + r;
+            const bool valid = g < a.G;
+            const uint32_t n32 = valid ? (uint32_t)g / (uint32_t)a.P : 0u;
+            const int p = valid ? (int)((uint32_t)g - n32 * (uint32_t)a.P) : 0;
+            const float *xb = a.x + (int64_t)n32 * a.xs_n + (int64_t)p * a.xs_p;
+            int csum = 0;
+            for (int s = 0; s < a.slabs; ++s, ++gs) {
+                const uint32_t stage = gs & 1u, use = gs >> 1;
+                if (use >= 1) mbar_wait(ea_bar + 8 * stage, (use - 1) & 1);
+#pragma unroll
+                for (int half = 0; half < 2; ++half) {
+                    const int k0 = s * kI8Slab + half * 32;
+                    float v[32];
+                    if (k0 < a.K) {                                  // uniform
+                        const float *px = xb + (int64_t)k0 * xs_k;
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) v[j] = (valid && k0 + j < a.K) ? __ldg(px + j * xs_k) : 0.0f;
+                    }
+#pragma unroll
+                    for (int c = 0; c < 2; ++c) {
+                        uint32_t w4[4] = {0u, 0u, 0u, 0u};
+                        if (k0 + 16 * c < a.K) {
+#pragma unroll
+                            for (int q4 = 0; q4 < 4; ++q4) {
+                                uint32_t b[4];
+#pragma unroll
+                                for (int j = 0; j < 4; ++j) {
+                                    const int kk = 16 * c + 4 * q4 + j;
+                                    b[j] = (valid && k0 + kk < a.K) ? quant_code_bits(v[kk], qc) : (128u >> sh);
+                                }
+                                const uint32_t lo = __byte_perm(b[0], b[1], 0x0040), hi = __byte_perm(b[2], b[3], 0x0040);
+                                w4[q4] = (__byte_perm(lo, hi, 0x5410) << sh) ^ 0x80808080u;
+                                csum = __dp4a((int)w4[q4], 0x01010101, csum);
+                            }
+                        }
+                        *reinterpret_cast<uint4 *>(sAg + stage * kI8ASlab + (2 * half + c) * (kI8M * 16) + r * 16) =
+                            make_uint4(w4[0], w4[1], w4[2], w4[3]);
+                    }
+                }
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                mbar_arrive(fa_bar + 8 * stage);
+            }
+            // ---- epilogue of the same row
+            float *yb = a.y + (int64_t)n32 * a.ys_n + (int64_t)p * a.ys_p;
+            const float row_c = __fmul_rn(sxcw, (float)csum);
+            mbar_wait(af_bar, jt & 1);
+            tc_fence_after();
+            float lo = INFINITY, hi = -INFINITY;
+            for (int chunk = 0; chunk * 16 < a.npass; ++chunk) {
+                const int oc = o0 + chunk * 16;
+                if (oc >= o_end) break;                               // uniform
+                uint32_t d[16];
+                asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, "
+                             "%12, %13, %14, %15}, [%16];"
+                             : "=r"(d[0]), "=r"(d[1]), "=r"(d[2]), "=r"(d[3]), "=r"(d[4]), "=r"(d[5]), "=r"(d[6]),
+                               "=r"(d[7]), "=r"(d[8]), "=r"(d[9]), "=r"(d[10]), "=r"(d[11]), "=r"(d[12]), "=r"(d[13]),
+                               "=r"(d[14]), "=r"(d[15])
+                             : "r"(tmem + ((uint32_t)((warp & 3) * 32) << 16) + grp * acc_cols + (uint32_t)(chunk * 16)));
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                const float4 *cc = reinterpret_cast<const float4 *>(chan_c + chunk * 16);
+                const int nvalid = min(16, o_end - oc);               // uniform
+                float *py = yb + (int64_t)oc * ys_o;
+                if (!valid) {
+                } else if (nvalid == 16) {
+#pragma unroll
+                    for (int j4 = 0; j4 < 4; ++j4) {
+                        const float4 c4 = cc[j4];
+                        const float cj[4] = {c4.x, c4.y, c4.z, c4.w};
+#pragma unroll
+                        for (int t = 0; t < 4; ++t) {
+                            const float yv = fmaxf(__fmaf_rn(fa, (float)(int)d[4 * j4 + t], __fadd_rn(row_c, cj[t])), floor_v);
+                            *py = yv;
+                            py += ys_o;
+                            lo = fminf(lo, yv); hi = fmaxf(hi, yv);
+                        }
+                    }
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) {
+                        if (j < nvalid) {
+                            const float yv = fmaxf(__fmaf_rn(fa, (float)(int)d[j], __fadd_rn(row_c, chan_c[chunk * 16 + j])), floor_v);
+                            *py = yv;
+                            py += ys_o;
+                            lo = fminf(lo, yv); hi = fmaxf(hi, yv);
+                        }
+                    }
+                }
+                __syncwarp();
+            }
+            tc_fence_before();      // our TMEM reads are done before the full_a arrival that lets the next MMA start
+            if (a.stats) {
+                const int64_t n = n32;
+                const int64_t n0 = __shfl_sync(0xffffffffu, n, 0);
+                const bool uni = __all_sync(0xffffffffu, valid && n == n0);
+                if (uni) {
+                    lo = warp_min(lo); hi = warp_max(hi);
+                    if (lane == 0 && hi >= lo) {
+                        atomicMax(a.stats + 2 * n, enc_ordered(-lo));
+                        atomicMax(a.stats + 2 * n + 1, enc_ordered(hi));
+                    }
+                } else if (valid && hi >= lo) {
+                    atomicMax(a.stats + 2 * n, enc_ordered(-lo));
+                    atomicMax(a.stats + 2 * n + 1, enc_ordered(hi));
+                }
+            }
+        }
+    } else if (warp == 8) {
+        // ==================================================================================== MMA issuer
+        if (lane == 0) {
+            const uint32_t idesc = (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(a.npass >> 3) << 17) |
+                                   ((uint32_t)(kI8M >> 4) << 24);
+            uint32_t gsa[2] = {0u, 0u}, gsb = 0, it = 0;
+            for (int64_t item = blockIdx.x; item < items; item += gridDim.x, ++it) {
+                const uint32_t grp = it & 1u;
+                for (int s = 0; s < a.slabs; ++s, ++gsb) {
+                    const uint32_t sta = gsa[grp] & 1u, usea = gsa[grp] >> 1;
+                    const uint32_t stb = gsb % kWsBStages, useb = gsb / kWsBStages;
+                    gsa[grp] += 1;
+                    mbar_wait(full_b + 8 * stb, useb & 1);
+                    mbar_wait(full_a + 16 * grp + 8 * sta, usea & 1);
+                    tc_fence_after();
+#pragma unroll
+                    for (int kk = 0; kk < 2; ++kk) {
+                        const uint64_t ad = umma_desc(sA_u + (grp * 2 + sta) * kI8ASlab + kk * 2 * (kI8M * 16), kI8M * 16, 128);
+                        const uint64_t bd = umma_desc(sB_u + stb * bslab + kk * 2 * (a.npass * 16), a.npass * 16, 128);
+                        umma_i8(tmem + grp * acc_cols, ad, bd, idesc, (s | kk) != 0);
+                    }
+                    umma_commit(empty_a + 16 * grp + 8 * sta);
+                    umma_commit(empty_b + 8 * stb);
+                }
+                umma_commit(acc_full + 8 * grp);
+            }
+        }
+    } else {
+        // ================================================================================= weight streamer
+        if (lane == 0) {
+            const int8_t *wsrc = a.wpk + (int64_t)pass * a.slabs * bslab;
+            uint32_t gsb = 0;
+            for (int64_t item = blockIdx.x; item < items; item += gridDim.x) {
+                for (int s = 0; s < a.slabs; ++s, ++gsb) {
+                    const uint32_t stb = gsb % kWsBStages, useb = gsb / kWsBStages;
+                    if (useb >= 1) mbar_wait(empty_b + 8 * stb, (useb - 1) & 1);
+                    mbar_expect_tx(full_b + 8 * stb, bslab);
+                    bulk_g2s(sB_u + stb * bslab, wsrc + (int64_t)s * bslab, bslab, full_b + 8 * stb);
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 8)
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"((uint32_t)a.tmem_cols)
+                     : "memory");
+}
+
 }  // namespace dfq
 
 using namespace dfq;
@@ -422,6 +662,36 @@ static int pw_i8_launch(PwI8Args &a, bool conv, int64_t G, cudaStream_t stream) 
     if (!sms) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); }
     const bool pre = a.slabs >= 2 && tiles * a.n_pass <= (int64_t)8 * sms;
     const unsigned grid = (unsigned)(tiles * a.n_pass);
+    // The persistent role-split kernel is OPT-IN (DFQ_PW_WS=<min work items per SM>, or =force for every layer):
+    // at batch 256 it wins on the one tiny-K / wide-N layer (16 -> 96 at 112 x 112: 0.374 -> 0.336 ms) and loses
+    // 10-140 % everywhere else -- 2 resident CTAs x 8 worker warps against 4 x 8 warps of the one-tile kernel, and
+    // 64 serial loads per thread and slab.  Kept with its parity test as the base for round 2.
+    static int ws_mode = -1;
+    static bool ws_force = false;
+    if (ws_mode < 0) {
+        const char *e = getenv("DFQ_PW_WS");
+        ws_force = e && e[0] == 'f';
+        ws_mode = ws_force ? 1 : (e ? atoi(e) : 0);
+    }
+    if (!conv && ws_mode && a.npass <= 256 && (ws_force || tiles * a.n_pass >= (int64_t)ws_mode * sms)) {
+        PwI8Args w = a;
+        w.tiles = tiles;
+        w.tmem_cols = 32;
+        while (w.tmem_cols < 2 * a.npass) w.tmem_cols *= 2;            // two accumulator buffers (<= 512 columns)
+        const size_t wsmem = 4 * (size_t)kI8ASlab + (size_t)kWsBStages * a.npass * kI8Slab;
+        static bool ws_attr = false;
+        if (!ws_attr) {
+            cudaError_t ce = cudaFuncSetAttribute(pw_i8_ws_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
+            if (ce != cudaSuccess) return (int)ce;
+            ws_attr = true;
+        }
+        int per_sm = min(2, 512 / w.tmem_cols);
+        int64_t g2 = min(tiles * a.n_pass, (int64_t)per_sm * sms);
+        g2 = max((int64_t)a.n_pass, g2 / a.n_pass * a.n_pass);
+        pw_i8_ws_kernel<<<(unsigned)g2, kWsThreads, wsmem, stream>>>(w);
+        g_launches += 1;
+        return (int)cudaGetLastError();
+    }
     if (conv) {
         if (pre) pw_i8_kernel<true, true><<<grid, kThreads, smem, stream>>>(a);
         else pw_i8_kernel<false, true><<<grid, kThreads, smem, stream>>>(a);

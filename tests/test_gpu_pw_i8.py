@@ -102,3 +102,19 @@ def test_off_grid_weight_is_refused():
     from data_free_quantization_b200 import pw_i8
     w = torch.randn(32, 64, device=DEV)
     assert pw_i8.pack_weight(w, 8) is None
+
+
+def test_role_split_persistent_variant():
+    """The opt-in persistent kernel (pw_i8_ws_kernel: two worker groups, MMA issuer and weight streamer meeting at
+    mbarriers, double-buffered TMEM accumulator) passes the same cases; the switch is read once per process, hence
+    the subprocess."""
+    import os
+    import subprocess
+    import sys
+    if os.environ.get("DFQ_PW_WS") == "force":
+        pytest.skip("already inside the forced run")
+    env = dict(os.environ, DFQ_PW_WS="force")
+    r = subprocess.run([sys.executable, "-m", "pytest", os.path.abspath(__file__), "-q", "-m", "gpu", "-x", "-k",
+                        "not role_split"], env=env, capture_output=True, text=True, timeout=600,
+                       cwd=os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
