@@ -43,14 +43,15 @@ def merge_batchnorm(model, graph, bottoms, targ_type=[QConv2d]):
         for d, (conv, bn) in zip(descs, pairs):
             W = conv.weight.data
             O = W.size(0)
-            if conv.bias is None:                   # :262-263
-                conv.bias = nn.Parameter(data=zeros[zoff:zoff + O], requires_grad=False)
+            if conv.bias is None:                   # :262-263 ('bias' is a registered, empty parameter slot)
+                conv._parameters['bias'] = nn.Parameter(data=zeros[zoff:zoff + O], requires_grad=False)
                 zoff += O
             fake_w, fake_b = stash[0, off:off + O], stash[1, off:off + O]
             off += O
-            d.W, d.b = L.dev_f32(W, "weight"), L.dev_f32(conv.bias.data, "bias")
-            d.gamma, d.beta = L.dev_f32(bn.weight.data, "bn.weight"), L.dev_f32(bn.bias.data, "bn.bias")
-            d.mean, d.var = L.dev_f32(bn.running_mean, "bn.running_mean"), L.dev_f32(bn.running_var, "bn.running_var")
+            bp, bb = bn._parameters, bn._buffers
+            d.W, d.b = L.dev_f32(W, "weight"), L.dev_f32(conv._parameters['bias'].data, "bias")
+            d.gamma, d.beta = L.dev_f32(bp['weight'].data, "bn.weight"), L.dev_f32(bp['bias'].data, "bn.bias")
+            d.mean, d.var = L.dev_f32(bb['running_mean'], "bn.running_mean"), L.dev_f32(bb['running_var'], "bn.running_var")
             d.fake_weight, d.fake_bias = fake_w.data_ptr(), fake_b.data_ptr()
             d.O, d.K, d.eps = O, W.numel() // O, float(bn.eps)
             if 'fake_weight' in bn._buffers:                      # :273-274; re-registration: plain replacement
@@ -58,7 +59,7 @@ def merge_batchnorm(model, graph, bottoms, targ_type=[QConv2d]):
             else:
                 bn.register_buffer('fake_weight', fake_w)
                 bn.register_buffer('fake_bias', fake_b)
-            bn.eps = IDENTITY_BN_EPS                             # :281 (see IDENTITY_BN_EPS)
+            bn.__dict__['eps'] = IDENTITY_BN_EPS                 # :281 (see IDENTITY_BN_EPS); plain attribute
         rows = ctypes.c_int()
         L.check(L.lib().dfq_merge_plan_host(descs, len(pairs), ctypes.byref(rows)), "dfq_merge_plan_host")
         table = L.table_to_device(descs, dev)

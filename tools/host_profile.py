@@ -18,4 +18,4 @@ with contextlib.redirect_stdout(io.StringIO()):
     torch.cuda.synchronize()
     pr.disable()
 st = pstats.Stats(pr, stream=sys.stdout)
-st.sort_stats("cumulative").print_stats(45)
+st.sort_stats(sys.argv[1] if len(sys.argv) > 1 else "cumulative").print_stats(40)
