@@ -35,6 +35,7 @@ class _T:
         self.relu_of = None
         self.relu_done = False
         self.need_stats = False
+        self.by_torch = False             # written by a torch op: its per-sample extrema need their own pass
 
     @property
     def numel(self):
@@ -116,6 +117,11 @@ class EvalPlan:
                     env[node] = out
                 elif isinstance(m, (nn.Dropout, nn.Identity)):
                     env[node] = src
+                elif isinstance(m, nn.AdaptiveAvgPool2d) and m.output_size in (1, (1, 1)):
+                    out = _T(src.shape[:2] + (1, 1))
+                    out.by_torch, out.stats_encoded = True, False
+                    steps.append({"kind": "pool", "src": src, "out": out, "name": node.target})
+                    env[node] = out
                 else:
                     raise NotImplementedError(f"{node.target}: {type(m).__name__} is not supported by the eval plan")
             elif node.op in ("call_function", "call_method"):
@@ -138,10 +144,58 @@ class EvalPlan:
                     steps.append({"kind": "mean", "src": src, "out": out, "name": key, "bits": qm.num_bits,
                                   "slot": self._slot_for(qm, src)})
                     env[node] = out
+                elif key is not None and key.startswith("F.pad"):
+                    # utils/layer_transform.py ignore_op=['pad']: recorded in the graph, never quantised
+                    src = env[node.meta["dfq_operands"][0]]
+                    pad = tuple(int(v) for v in (node.args[1] if len(node.args) > 1 else node.kwargs["pad"]))
+                    if len(pad) != 4 or node.kwargs.get("mode", "constant") != "constant" or \
+                            (node.args[3] if len(node.args) > 3 else node.kwargs.get("value", 0)) not in (0, 0.0, None):
+                        raise NotImplementedError(f"{key}: only constant zero padding of H and W")
+                    N, C, H, W = src.shape
+                    out = _T((N, C, H + pad[2] + pad[3], W + pad[0] + pad[1]))
+                    out.by_torch, out.stats_encoded = True, False
+                    steps.append({"kind": "pad", "src": src, "out": out, "name": key, "pad": pad})
+                    env[node] = out
+                elif key is not None and key.startswith("F.interpolate"):
+                    src = env[node.meta["dfq_operands"][0]]
+                    kw = {k: (env[v] if isinstance(v, torch.fx.Node) else v) for k, v in node.kwargs.items()}
+                    size = kw.get("size", env[node.args[1]] if len(node.args) > 1 and
+                                  isinstance(node.args[1], torch.fx.Node) else (node.args[1] if len(node.args) > 1 else None))
+                    if size is None or kw.get("mode", "nearest") != "bilinear":
+                        raise NotImplementedError(f"{key}: only bilinear interpolation to a given size")
+                    size = tuple(int(v) for v in size)
+                    qm = top_qms[top_i]
+                    top_i += 1
+                    out = _T(src.shape[:2] + size)
+                    out.by_torch, out.stats_encoded = True, False
+                    steps.append({"kind": "interp", "src": src, "out": out, "name": key, "size": size,
+                                  "align": bool(kw.get("align_corners", False)), "bits": [qm.num_bits],
+                                  "slots": [self._slot_for(qm, src)]})
+                    env[node] = out
+                elif key is not None and key.startswith("torch.cat"):
+                    srcs = [env[x] for x in node.meta["dfq_operands"]]
+                    dim = node.kwargs.get("dim", node.args[1] if len(node.args) > 1 else 0)
+                    if dim != 1 or any(t.shape[0] != srcs[0].shape[0] or t.shape[2:] != srcs[0].shape[2:] for t in srcs):
+                        raise NotImplementedError(f"{key}: only channel concatenation")
+                    qms = top_qms[top_i:top_i + len(srcs)]
+                    top_i += len(srcs)
+                    out = _T((srcs[0].shape[0], sum(t.shape[1] for t in srcs)) + srcs[0].shape[2:])
+                    out.by_torch, out.stats_encoded = True, False
+                    steps.append({"kind": "cat", "srcs": srcs, "out": out, "name": key,
+                                  "bits": [q.num_bits for q in qms],
+                                  "slots": [self._slot_for(q, t) for q, t in zip(qms, srcs)]})
+                    env[node] = out
                 elif key is not None:
                     raise NotImplementedError(f"{key}: tensor op not supported by the eval plan yet")
-                elif node.op == "call_method" and node.target in ("size", "dim"):
+                elif node.op == "call_method" and node.target == "size":
+                    t = env.get(node.args[0])
+                    shape = torch.Size(t.shape) if isinstance(t, _T) else None
+                    env[node] = shape if len(node.args) == 1 or shape is None else shape[node.args[1]]
+                elif node.op == "call_method" and node.target == "dim":
                     env[node] = None
+                elif node.target is operator.getitem and not isinstance(env.get(node.args[0]), _T) \
+                        and env.get(node.args[0]) is not None:
+                    env[node] = env[node.args[0]][node.args[1]]            # indexing a folded shape
                 elif (node.op == "call_method" and node.target in _PASS_METHODS) or node.target is operator.getitem:
                     first = node.args[0]
                     env[node] = env.get(first) if isinstance(first, torch.fx.Node) else None
@@ -159,10 +213,10 @@ class EvalPlan:
         self.slots = torch.zeros(max(1, len(self.measures)), 4, dtype=torch.float32, device=dev)
         # last use of every tensor -> simple free-list reuse of activation buffers
         last = {}
+        ins_of = lambda st: [st[k] for k in ("src", "a", "b") if k in st] + list(st.get("srcs", ()))
         for i, st in enumerate(steps):
-            for k in ("src", "a", "b"):
-                if k in st:
-                    last[id(st[k])] = i
+            for t in ins_of(st):
+                last[id(t)] = i
         last[id(self.output)] = len(steps)
         pool = {}
         self.input.buf = f32(*self.input.shape)
@@ -172,9 +226,8 @@ class EvalPlan:
             free = pool.get(out.numel)
             out.buf = free.pop() if free else f32(*out.shape)
             tensors.append(out)
-            for k in ("src", "a", "b"):
-                t = st.get(k)
-                if t is not None and last[id(t)] == i and t is not self.input and t.buf is not None:
+            for t in {id(t): t for t in ins_of(st)}.values():
+                if last[id(t)] == i and t is not self.input and t.buf is not None:
                     pool.setdefault(t.numel, []).append(t.buf)
         need = [t for t in tensors if t.need_stats]
         self.stats = torch.zeros(max(1, len(need)), N, 2, dtype=torch.int32, device=dev)
@@ -207,12 +260,11 @@ class EvalPlan:
             if kind == "conv":
                 kh, _, _, _, _, g = st["geom"]
                 kind = "pw" if (kh == 1 and g == 1) else ("dw" if g > 1 else "dense")
-            ins = [st[k] for k in ("src", "a", "b") if k in st]
+            ins = ins_of(st)
             self.op_info[st["name"]] = {"kind": kind, "bytes": 4 * (sum(t.numel for t in ins) + st["out"].numel),
                                         "shape": tuple(ins[0].shape[1:]) + ("->",) + tuple(st["out"].shape[1:])}
         for st in steps:
-            for key in ("slot", "slot_a", "slot_b"):
-                idx = st.get(key)
+            for idx in [st.get(key) for key in ("slot", "slot_a", "slot_b")] + list(st.get("slots", ())):
                 if idx is None or idx in done:
                     continue
                 done.add(idx)
@@ -268,7 +320,64 @@ class EvalPlan:
                         slot_ptr(st["slot"]), int(st["bits"]), stats_ptr(out))
                 self.ops.append((st["name"], (lambda a_: lambda: L.check(lib.dfq_qmean_f32(*a_, stream()),
                                                                         "dfq_qmean_f32"))(args)))
+            elif st["kind"] in ("pad", "pool", "interp", "cat"):
+                self.ops.append((st["name"], self._torch_op(st, f32, slot_ptr)))
+            out = st["out"]
+            if out.by_torch and out.need_stats:       # extrema of what the torch op wrote (plain floats)
+                sargs = (out.buf.data_ptr(), N, out.numel // N, out.stats.data_ptr())
+                self.ops.append((f"stats[{st['name']}]", (lambda a_: lambda: L.check(
+                    lib.dfq_minmax_rows_f32(*a_, stream()), "dfq_minmax_rows_f32"))(sargs)))
         self.refresh_static()
+
+    def _torch_op(self, st, f32, slot_ptr):
+        """Launch closure of a data-movement op of the graph (F.pad, adaptive average pooling, bilinear
+        interpolation, channel cat: utils/layer_transform.py:18-125 patches the last two so that their operands go
+        through QuantMeasures first).  The operands are fake-quantised with our kernel into a scratch buffer; the
+        movement itself is the torch op the reference calls, writing into the plan's preallocated buffer (capturable
+        in the CUDA graph)."""
+        lib, stream = L.lib(), L.stream
+        out = st["out"]
+        dst = out.buf.view(out.shape)
+        kind = st["kind"]
+
+        def quantised(t, slot, bits):
+            tmp = f32(*t.shape)
+            self.keep.append(tmp)
+            args = (t.buf.data_ptr(), tmp.data_ptr(), None, t.numel, int(bits), 0, slot_ptr(slot))
+            return tmp, lambda: L.check(lib.dfq_fake_quant_apply_slot_f32(*args, stream()),
+                                        "dfq_fake_quant_apply_slot_f32")
+        if kind == "pad":
+            src = st["src"].buf.view(st["src"].shape)
+            l, r, t, b = st["pad"]
+            H, W = st["src"].shape[2:]
+            inner = dst[:, :, t:t + H, l:l + W]
+
+            def run():
+                dst.zero_()
+                inner.copy_(src)
+            return run
+        if kind == "pool":
+            src = st["src"].buf.view(st["src"].shape)
+            return lambda: dst.copy_(F.adaptive_avg_pool2d(src, (1, 1)))
+        if kind == "interp":
+            tmp, q = quantised(st["src"], st["slots"][0], st["bits"][0])
+            size, align = st["size"], st["align"]
+
+            def run():
+                q()
+                dst.copy_(F.interpolate(tmp, size=size, mode="bilinear", align_corners=align))
+            return run
+        parts, c0 = [], 0
+        for t, slot, bits in zip(st["srcs"], st["slots"], st["bits"]):
+            tmp, q = quantised(t, slot, bits)
+            parts.append((q, dst[:, c0:c0 + t.shape[1]], tmp))
+            c0 += t.shape[1]
+
+        def run():
+            for q, view, tmp in parts:
+                q()
+                view.copy_(tmp)
+        return run
 
     def _params(self, m):
         """Weight / bias the layer's forward uses.  QuantN* layers use the stored parameters (quantised offline by

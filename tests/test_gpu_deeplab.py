@@ -43,7 +43,7 @@ def run():
                                 ignore_layer=[Q.QuantMeasure], quant_op=True)
     graph, bottoms = tr.log.getGraph(), tr.log.getBottoms()
     merge_batchnorm(model, graph, bottoms, targ)
-    out = {"model": model, "graph": graph, "bottoms": bottoms, "targ": targ}
+    out = {"model": model, "graph": graph, "bottoms": bottoms, "targ": targ, "tr": tr}
     out["merge"] = {k: sha(v) for k, v in snapshot(model, graph, targ).items()}
     rels = create_relation(graph, bottoms, targ)
     info = cross_layer_equalization(graph, rels, targ, Save_state=False, Treshhold=2e-7, return_info=True)
@@ -165,3 +165,38 @@ def test_quantised_eval_matches_reference(dgold, run):
             a, b = gold["quant_minmax_after_eval"][names[key]]
             assert abs(float(m.quant.running_min) - a) <= 5e-3 * max(1.0, abs(a)), names[key]
             assert abs(float(m.quant.running_max) - b) <= 5e-3 * max(1.0, abs(b)), names[key]
+
+
+def test_static_eval_plan_matches_module_path(dgold, run):
+    """The static eval plan (one launch list, CUDA-graph capturable) on DeepLab: F.pad, adaptive pooling, bilinear
+    interpolation and cat as plan ops next to the conv kernels.  Continues from the previous test's state (running
+    ranges already widened by that batch), so a second module-path forward on the same input is the comparator:
+    same kernels, same ranges -> the logits must agree to rounding."""
+    from data_free_quantization_b200.eval_plan import EvalPlan
+    from data_free_quantization_b200.utils.layer_transform import replace_op, restore_op
+    gold, npz = dgold
+    model = run["model"]
+    x = torch.randn(2, 3, 129, 129, generator=torch.Generator().manual_seed(2)).to(DEV)
+    replace_op()
+    try:
+        with torch.no_grad():
+            want = model(x).cpu().numpy()
+    finally:
+        restore_op()
+    plan = EvalPlan(model, run["tr"], batch=2, in_shape=(3, 129, 129))
+    got = plan(x).cpu().numpy().reshape(want.shape)
+    assert np.abs(got - want).max() <= 1e-5 * np.abs(want).max(), np.abs(got - want).max() / np.abs(want).max()
+    assert np.mean(got.argmax(1) == want.argmax(1)) >= 0.999
+    # against the reference's own logits, with the bars of the module-path test
+    ref = npz["eval/logits_b2"]
+    assert np.abs(got[:, :, ::4, ::4] - ref).max() / np.abs(ref).max() <= 3e-2
+    assert np.mean(got.argmax(1) == npz["eval/argmax_b2"]) >= 0.99
+    kinds = [plan.op_info[n]["kind"] for n in plan.op_info]
+    assert kinds.count("pad") == 17 and kinds.count("interp") == 3 and kinds.count("cat") == 2 and kinds.count("pool") == 1
+    # replayed from a CUDA graph
+    again = plan(x).cpu().numpy()
+    replay = plan.capture()
+    plan.input.buf.copy_(x)
+    replay()
+    torch.cuda.synchronize()
+    assert np.array_equal(plan.output.buf.cpu().numpy(), again)
