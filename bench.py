@@ -347,6 +347,66 @@ def eval_plan_images_per_s(torch, case, batch, steps, warmup):
     return ms_dev, ms_e2e, len(plan.ops), plan.hbm_bytes
 
 
+def deeplab_section(torch, dev, world):
+    """BASELINE.json configs[3]: DeepLabV3+ (MobileNetV2 backbone) W8A8 -- the DFQ pipeline on its 61 target layers,
+    then the quantised eval forward of a 16 x 3 x 513 x 513 batch split across the ranks,
+    replayed as one CUDA graph.  Extra evidence beside the headline metric; not part of `value`."""
+    import torch.nn as nn
+    from data_free_quantization_b200 import graph as G
+    from data_free_quantization_b200.Cross_layer_equal import cross_layer_equalization
+    from data_free_quantization_b200.bias_absorption import bias_absorption
+    from data_free_quantization_b200.clip_weight import clip_weight
+    from data_free_quantization_b200.eval_plan import EvalPlan
+    from data_free_quantization_b200.fixtures import synthetic_state_dict
+    from data_free_quantization_b200.modeling.deeplab import DeepLab
+    from data_free_quantization_b200.utils import quantize as Q
+    from data_free_quantization_b200.utils.layer_transform import merge_batchnorm, quantize_targ_layer, set_quant_minmax
+    from data_free_quantization_b200.utils.relation import create_relation
+    targ = [Q.QuantNConv2d, Q.QuantNLinear]
+    md = {0: [(nn.ReLU6, nn.ReLU)], 1: [(nn.Conv2d, targ[0]), (nn.Linear, targ[1])]}
+    sd = None
+    pipe_ms = None
+    for rep in range(2):                                   # first pass warms allocator and kernels, second is timed
+        torch.manual_seed(0)
+        model = DeepLab()
+        sd = sd or synthetic_state_dict(model, seed=0, bn_seed=1)
+        model.load_state_dict(sd)
+        model = model.eval().to(dev)
+        model, tr = G.switch_layers(model, G.TorchTransformer(), torch.ones(1, 3, 129, 129, device=dev), md,
+                                    ignore_layer=[Q.QuantMeasure], quant_op=True)
+        graph, bottoms = tr.log.getGraph(), tr.log.getBottoms()
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        merge_batchnorm(model, graph, bottoms, targ)
+        rels = create_relation(graph, bottoms, targ)
+        cross_layer_equalization(graph, rels, targ, Save_state=False, Treshhold=2e-7)
+        bias_absorption(graph, rels, bottoms, N=3)
+        Q.set_layer_bits(graph, 8, 8, 8, targ)
+        merge_batchnorm(model, graph, bottoms, targ)
+        quantize_targ_layer(graph, 8, 8, targ)
+        set_quant_minmax(graph, bottoms, verbose=False)
+        clip_weight(graph, [-15, 15], targ)
+        b.record()
+        b.synchronize()
+        pipe_ms = a.elapsed_time(b)
+    model.eval()
+    batch = max(1, 16 // world)
+    x = torch.randn(batch, 3, 513, 513, generator=torch.Generator().manual_seed(2)).to(dev)
+    plan = EvalPlan(model, tr, batch=batch, in_shape=(3, 513, 513))
+    plan(x)
+    replay = plan.capture()
+    for _ in range(2):
+        replay()
+    torch.cuda.synchronize()
+    ms = time_steps(torch, replay, 5) / 5
+    return {"model": "DeepLabV3+ MobileNetV2, 513x513, W8A8, random-init", "pipeline_ms": round(pipe_ms, 3),
+            "pipeline_scope": "merge_batchnorm .. clip_weight incl. create_relation (43 CLE iterations)",
+            "eval_batch_per_gpu": batch, "eval_ms_per_batch": ms, "plan_ops": len(plan.ops),
+            "path": "static eval plan as one CUDA graph: dense 3x3 (atrous / decoder) and pointwise on tcgen05, "
+                    "depthwise on CUDA cores, pad / pool / interpolate / cat as plan ops"}
+
+
 # ------------------------------------------------------------------------------------------ CPU baseline
 def oracle_pipeline_once():
     """The reference path restated in C (oracle/, 1 host thread) on the same seeded MobileNetV2.  Returns ms."""
@@ -526,6 +586,18 @@ def _main(args):
         if world > 1:
             dist.destroy_process_group()
         return
+    deeplab = None
+    if not args.no_eval:
+        with quiet:
+            deeplab = deeplab_section(torch, dev, world)
+        ms_dl = deeplab.pop("eval_ms_per_batch")
+        if world > 1:
+            t = torch.tensor([ms_dl], device=dev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms_dl = float(t[0])
+        deeplab["eval_ms_per_batch"] = round(ms_dl, 3)
+        deeplab["eval_images_per_s"] = round(deeplab["eval_batch_per_gpu"] * world / (ms_dl * 1e-3), 1)
+        deeplab["eval_scaling"] = "strong (16 images split across the ranks)"
     kernels = kernel_rooflines(torch, dev, peak, args.micro_elems) if not args.no_micro else []
     # roofline of the step's dominant kernel: the persistent CLE loop.  Algorithmic bytes: 12 B x
     # 4 252 832 pair elements per outer iteration x the iterations it ran; duration: CUDA events around its launch on
@@ -565,7 +637,7 @@ def _main(args):
                     "d2h_bytes_per_step": case.d2h_bytes()},
             "gpu_launches": int(launches) // max(1, args.steps),
             "stages_ms": {k: round(v, 3) for k, v in stages.items() if isinstance(v, float)},
-            "roofline": roof, "kernels": kernels, "kernels_sharded": sharded, "eval": ev, "cpu_baseline": cpu, "clocks": clocks.summary()}
+            "roofline": roof, "kernels": kernels, "kernels_sharded": sharded, "eval": ev, "deeplab": deeplab, "cpu_baseline": cpu, "clocks": clocks.summary()}
     if world > 1:
         dist.destroy_process_group()
     return line
