@@ -480,7 +480,17 @@ def main():
         out.flush()
 
 
+def _watchdog():
+    """DFQ_WATCHDOG_S=<seconds>: dump every thread's Python stack to stderr and exit if the run takes longer
+    (diagnosing multi-rank hangs without holding a GPU box until the outer timeout)."""
+    s = os.environ.get("DFQ_WATCHDOG_S")
+    if s:
+        import faulthandler
+        faulthandler.dump_traceback_later(int(s), exit=True, file=sys.stderr)
+
+
 def _main(args):
+    _watchdog()
     if args.impl == "reference":
         return reference_arm(args)
     import torch
@@ -578,14 +588,6 @@ def _main(args):
                               "ms_per_batch": round(ev_ms, 3),
                               "path": "reference-shaped nn.Module forward: QuantMeasure on libdfq_b200 kernels, "
                                       "conv/linear arithmetic through F.conv2d (cuDNN fp32, library)"}}
-    sharded = None
-    if not args.no_micro:
-        with quiet:
-            sharded = sharded_microbench(torch, dev, world, peak)
-    if rank != 0:
-        if world > 1:
-            dist.destroy_process_group()
-        return
     deeplab = None
     if not args.no_eval:
         with quiet:
@@ -598,6 +600,14 @@ def _main(args):
         deeplab["eval_ms_per_batch"] = round(ms_dl, 3)
         deeplab["eval_images_per_s"] = round(deeplab["eval_batch_per_gpu"] * world / (ms_dl * 1e-3), 1)
         deeplab["eval_scaling"] = "strong (16 images split across the ranks)"
+    sharded = None
+    if not args.no_micro:
+        with quiet:
+            sharded = sharded_microbench(torch, dev, world, peak)
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
     kernels = kernel_rooflines(torch, dev, peak, args.micro_elems) if not args.no_micro else []
     # roofline of the step's dominant kernel: the persistent CLE loop.  Algorithmic bytes: 12 B x
     # 4 252 832 pair elements per outer iteration x the iterations it ran; duration: CUDA events around its launch on
