@@ -83,11 +83,11 @@ class DfqConvI8Desc(ctypes.Structure):
     _fields_ = [("x", c_void), ("y", c_void), ("wpk", c_void), ("wr", c_void), ("wrt", c_void), ("bias", c_void),
                 ("in_slot", c_void), ("out_stats", c_void)] + \
                [(k, i32) for k in ("N", "C", "H", "W", "O", "OH", "OW", "kh", "kw", "stride", "pad", "dil", "bits",
-                                   "relu")] + [("s_w", f32), ("c_w", f32)]
+                                   "relu")] + [("s_w", f32), ("c_w", f32), ("scratch", c_void)]
 
 
 Q_SYMMETRIC, Q_RANGE_F32, Q_PER_CHANNEL, Q_CLAMP_OUT = 1, 2, 4, 8
-ABI_VERSION = 10
+ABI_VERSION = 11
 
 # every symbol include/dfq_b200.h declares: (restype, argtypes)
 P = ctypes.POINTER
@@ -117,6 +117,7 @@ PROTOTYPES = {
     "dfq_pw_i8_pack_host": (ctypes.c_int, [c_void, ctypes.c_int, ctypes.c_int, c_void]),
     "dfq_pw_i8": (ctypes.c_int, [P(DfqPwI8Desc), c_void]),
     "dfq_conv_i8_k_host": (ctypes.c_int, [ctypes.c_int, ctypes.c_int, ctypes.c_int]),
+    "dfq_conv_i8_scratch_bytes": (i64, [ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int]),
     "dfq_conv_i8": (ctypes.c_int, [P(DfqConvI8Desc), c_void]),
     "dfq_quant_plan_host": (ctypes.c_int, [P(DfqQuantDesc), ctypes.c_int, P(i64), P(i64)]),
     "dfq_fake_quant_multi_f32": (ctypes.c_int, [c_void, ctypes.c_int, i64, i64, c_void, c_void]),

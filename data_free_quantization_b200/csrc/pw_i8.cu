@@ -36,6 +36,7 @@ struct PwI8Args {
     float s_w, c_w;
     // dense k x k form (kConv): K above is the PADDED reduction length taps * cchunks * 16, Kreal = taps * C
     const float *wrt;                 // [taps][O] s_w * (sum over channels of the centred codes of one tap)
+    const int8_t *xq;                 // kQ: centred s8 codes [N][H][W][cchunks * 16]
     int C, H, W, OW, kh, kw, stride, pad, dil, taps, cchunks, Kreal;
     int64_t tiles;                    // warp-specialised form: 128-pixel tiles (work items = tiles * n_pass)
 };
@@ -99,6 +100,36 @@ __device__ __forceinline__ uint32_t quant_code_bits(float x, const QuantConsts &
     return (uint32_t)__float2int_rn(fminf(fmaxf(__fdiv_rn(t, c.scale), c.qmin), c.qmax));
 }
 
+// fp32 NCHW activation -> centred s8 codes, NHWC with the channels padded to a multiple of 16 (pad bytes = s8 zero).
+// A block owns 32 consecutive pixels of one image x 64 channels: coalesced fp32 reads along the pixels, transposed
+// through shared memory, 16-byte stores along the channels.
+__global__ void __launch_bounds__(kThreads)
+quant_nhwc_s8_kernel(const float *__restrict__ x, int8_t *__restrict__ q, const RangeSlot *slot, int bits, int C,
+                     int HW, int Cp) {
+    __shared__ __align__(16) uint8_t tile[32][64 + 16];
+    const int tid = threadIdx.x, px = tid & 31, cl = tid >> 5;
+    const int p0 = blockIdx.x * 32, c0 = blockIdx.y * 64, n = blockIdx.z;
+    const QuantConsts qc = consts_from_slot(*slot, bits, 0, 0.f, 0.f);
+    const int sh = 8 - bits;
+    const int p = p0 + px;
+    const float *xn = x + ((int64_t)n * C) * HW;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const int c = c0 + cl + 8 * i;
+        uint32_t b = 128u >> sh;
+        if (p < HW && c < C) b = quant_code_bits(__ldg(xn + (int64_t)c * HW + p), qc) & 0xffu;
+        tile[px][cl + 8 * i] = (uint8_t)(((b << sh) ^ 0x80u) & 0xffu);
+    }
+    __syncthreads();
+    if (tid < 128) {
+        const int pp = tid >> 2, w = tid & 3;
+        const int pg = p0 + pp, cb = c0 + 16 * w;
+        if (pg < HW && cb < Cp)
+            *reinterpret_cast<uint4 *>(q + ((int64_t)n * HW + pg) * Cp + cb) =
+                *reinterpret_cast<const uint4 *>(&tile[pp][16 * w]);
+    }
+}
+
 // sum of the per-tap constants of output channel `ol` over the out-of-bounds taps in `oob` (fixed tap order)
 __device__ __forceinline__ float tap_corr(const float *tap_c, uint32_t oob, int taps, int npass, int ol) {
     float corr = 0.0f;
@@ -119,7 +150,12 @@ __device__ __forceinline__ float tap_corr(const float *tap_c, uint32_t oob, int 
 // before F.conv2d pads) while an s8 zero stands for c_x, so the epilogue takes c_x * (s_w * sum_c b[o,c,t] + C c_w)
 // back out for every out-of-bounds tap t of the pixel (a [taps][channels] table in shared memory; interior pixels
 // skip it).
-template <bool kPre, bool kConv>
+//
+// kQ (with kConv): the input was quantised ONCE by quant_nhwc_s8_kernel into centred s8 codes laid out
+// [N][H][W][C padded to 16], so a K chunk is one aligned 16-byte word of the tap's pixel: the producer is a 128-bit
+// load, four dp4a for the code sum and the shared-memory store -- instead of 16 fp32 loads and 16 quantiser
+// evaluations per tap (9x the same activation for a 3 x 3 kernel).
+template <bool kPre, bool kConv, bool kQ>
 __global__ void __launch_bounds__(kThreads, kPre ? 3 : 4)
 pw_i8_kernel(PwI8Args a) {
     extern __shared__ __align__(128) uint8_t smem[];
@@ -180,16 +216,31 @@ pw_i8_kernel(PwI8Args a) {
             px = xb + (int64_t)(q * 16) * xs_k;
         }
     };
+    // kQ: the 16-byte word of chunk q at this thread's tap pixel (zeros in the padding / beyond the last tap)
+    const int8_t *xqb = kQ ? a.xq + n * ((int64_t)a.H * a.W * a.cchunks * 16) : nullptr;
+    auto chunk_q = [&](int q) {
+        const int t = q / a.cchunks, cc = q - t * a.cchunks;              // warp-uniform
+        const int i = t / a.kw, j = t - i * a.kw;
+        const int ih = ih0 + i * a.dil, iw = iw0 + j * a.dil;
+        const bool inb = valid && t < a.taps && (unsigned)ih < (unsigned)a.H && (unsigned)iw < (unsigned)a.W;
+        return inb ? __ldg(reinterpret_cast<const uint4 *>(xqb + (((int64_t)ih * a.W + iw) * a.cchunks + cc) * 16))
+                   : make_uint4(0u, 0u, 0u, 0u);
+    };
     // activations of one ring stage: two 16-wide K chunks per thread, all loads in flight before any use
-    float v[2][16];
+    float v[kQ ? 1 : 2][kQ ? 1 : 16];
+    uint4 vq[2];
     auto load_stage = [&](int s) {
 #pragma unroll
         for (int c = 0; c < 2; ++c) {
-            bool live, inb; const float *px; int nch;
-            chunk_src(s * 4 + h + 2 * c, live, inb, px, nch);
-            if (live) {                                               // warp-uniform: padded chunks cost nothing
+            if (kQ) {
+                vq[c] = chunk_q(s * 4 + h + 2 * c);
+            } else {
+                bool live, inb; const float *px; int nch;
+                chunk_src(s * 4 + h + 2 * c, live, inb, px, nch);
+                if (live) {                                           // warp-uniform: padded chunks cost nothing
 #pragma unroll
-                for (int j = 0; j < 16; ++j) v[c][j] = (inb && j < nch) ? __ldg(px + j * xs_k) : 0.0f;
+                    for (int j = 0; j < 16; ++j) v[c][kQ ? 0 : j] = (inb && j < nch) ? __ldg(px + j * xs_k) : 0.0f;
+                }
             }
         }
     };
@@ -237,19 +288,25 @@ pw_i8_kernel(PwI8Args a) {
         // 3. quantise on load (utils/quantize.py:72-74), centre to s8, pack, canonical-order store
 #pragma unroll
         for (int c = 0; c < 2; ++c) {
-            bool live, inb; const float *px; int nch;
-            chunk_src(s * 4 + h + 2 * c, live, inb, px, nch);
             uint32_t w4[4] = {0u, 0u, 0u, 0u};
-            if (live && (!kConv || __any_sync(0xffffffffu, inb))) {
+            if (kQ) {
+                w4[0] = vq[c].x; w4[1] = vq[c].y; w4[2] = vq[c].z; w4[3] = vq[c].w;
 #pragma unroll
-                for (int q4 = 0; q4 < 4; ++q4) {
-                    uint32_t b[4];
+                for (int q4 = 0; q4 < 4; ++q4) csum = __dp4a((int)w4[q4], 0x01010101, csum);
+            } else {
+                bool live, inb; const float *px; int nch;
+                chunk_src(s * 4 + h + 2 * c, live, inb, px, nch);
+                if (live && (!kConv || __any_sync(0xffffffffu, inb))) {
 #pragma unroll
-                    for (int j = 0; j < 4; ++j)
-                        b[j] = (inb && 4 * q4 + j < nch) ? quant_code_bits(v[c][4 * q4 + j], qc) : (128u >> sh);
-                    const uint32_t lo = __byte_perm(b[0], b[1], 0x0040), hi = __byte_perm(b[2], b[3], 0x0040);
-                    w4[q4] = (__byte_perm(lo, hi, 0x5410) << sh) ^ 0x80808080u;
-                    csum = __dp4a((int)w4[q4], 0x01010101, csum);
+                    for (int q4 = 0; q4 < 4; ++q4) {
+                        uint32_t b[4];
+#pragma unroll
+                        for (int j = 0; j < 4; ++j)
+                            b[j] = (inb && 4 * q4 + j < nch) ? quant_code_bits(v[c][kQ ? 0 : 4 * q4 + j], qc) : (128u >> sh);
+                        const uint32_t lo = __byte_perm(b[0], b[1], 0x0040), hi = __byte_perm(b[2], b[3], 0x0040);
+                        w4[q4] = (__byte_perm(lo, hi, 0x5410) << sh) ^ 0x80808080u;
+                        csum = __dp4a((int)w4[q4], 0x01010101, csum);
+                    }
                 }
             }
             *reinterpret_cast<uint4 *>(sA + buf * kI8ASlab + (h + 2 * c) * (kI8M * 16) + r * 16) =
@@ -646,14 +703,13 @@ static int pw_i8_launch(PwI8Args &a, bool conv, int64_t G, cudaStream_t stream) 
     if (smem > 64 * 1024) return (int)cudaErrorInvalidValue;
     static bool attr_set = false;
     if (!attr_set) {
-        cudaError_t ce = cudaFuncSetAttribute(pw_i8_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
-        if (ce == cudaSuccess)
-            ce = cudaFuncSetAttribute(pw_i8_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
-        if (ce == cudaSuccess)
-            ce = cudaFuncSetAttribute(pw_i8_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
-        if (ce == cudaSuccess)
-            ce = cudaFuncSetAttribute(pw_i8_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
-        if (ce != cudaSuccess) return (int)ce;
+        const void *fns[] = {(const void *)pw_i8_kernel<false, false, false>, (const void *)pw_i8_kernel<true, false, false>,
+                             (const void *)pw_i8_kernel<false, true, false>, (const void *)pw_i8_kernel<true, true, false>,
+                             (const void *)pw_i8_kernel<false, true, true>, (const void *)pw_i8_kernel<true, true, true>};
+        for (const void *fn : fns) {
+            cudaError_t ce = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+            if (ce != cudaSuccess) return (int)ce;
+        }
         attr_set = true;
     }
     const int64_t tiles = (G + kI8M - 1) / kI8M;
@@ -692,12 +748,15 @@ static int pw_i8_launch(PwI8Args &a, bool conv, int64_t G, cudaStream_t stream) 
         g_launches += 1;
         return (int)cudaGetLastError();
     }
-    if (conv) {
-        if (pre) pw_i8_kernel<true, true><<<grid, kThreads, smem, stream>>>(a);
-        else pw_i8_kernel<false, true><<<grid, kThreads, smem, stream>>>(a);
+    if (conv && a.xq) {
+        if (pre) pw_i8_kernel<true, true, true><<<grid, kThreads, smem, stream>>>(a);
+        else pw_i8_kernel<false, true, true><<<grid, kThreads, smem, stream>>>(a);
+    } else if (conv) {
+        if (pre) pw_i8_kernel<true, true, false><<<grid, kThreads, smem, stream>>>(a);
+        else pw_i8_kernel<false, true, false><<<grid, kThreads, smem, stream>>>(a);
     } else {
-        if (pre) pw_i8_kernel<true, false><<<grid, kThreads, smem, stream>>>(a);
-        else pw_i8_kernel<false, false><<<grid, kThreads, smem, stream>>>(a);
+        if (pre) pw_i8_kernel<true, false, false><<<grid, kThreads, smem, stream>>>(a);
+        else pw_i8_kernel<false, false, false><<<grid, kThreads, smem, stream>>>(a);
     }
     g_launches += 1;
     return (int)cudaGetLastError();
@@ -721,6 +780,10 @@ extern "C" int dfq_pw_i8(const DfqPwI8Desc *d, void *stream) {
 // Reduction length of the dense k x k form: taps * (C rounded up to 16); feed it to dfq_pw_i8_plan_host /
 // dfq_pw_i8_pack_host with the codes laid out [O][tap][C padded with zeros].
 extern "C" int dfq_conv_i8_k_host(int C, int kh, int kw) { return kh * kw * ((C + 15) / 16 * 16); }
+// Bytes of DfqConvI8Desc.scratch (the input as s8 codes, NHWC with C padded to 16).
+extern "C" int64_t dfq_conv_i8_scratch_bytes(int N, int C, int H, int W) {
+    return (int64_t)N * H * W * ((C + 15) / 16 * 16);
+}
 
 extern "C" int dfq_conv_i8(const DfqConvI8Desc *d, void *stream) {
     if (!d || !d->x || !d->y || !d->wpk || !d->wr || !d->wrt || !d->in_slot || d->N <= 0 || d->bits < 1 || d->bits > 8 ||
@@ -743,5 +806,13 @@ extern "C" int dfq_conv_i8(const DfqConvI8Desc *d, void *stream) {
     a.O = d->O; a.bits = d->bits; a.relu = d->relu; a.s_w = d->s_w; a.c_w = d->c_w;
     a.C = d->C; a.H = d->H; a.W = d->W; a.OW = OW; a.kh = d->kh; a.kw = d->kw; a.stride = d->stride; a.pad = d->pad;
     a.dil = d->dil;
+    if (d->scratch) {                       // quantise once, then every tap reads 16-byte code words
+        const int Cp = a.cchunks * 16, HW = d->H * d->W;
+        dim3 grid((unsigned)((HW + 31) / 32), (unsigned)((Cp + 63) / 64), (unsigned)d->N);
+        if (d->N > 65535 || grid.y > 65535) return (int)cudaErrorInvalidValue;
+        quant_nhwc_s8_kernel<<<grid, kThreads, 0, (cudaStream_t)stream>>>(d->x, d->scratch, a.slot, d->bits, d->C, HW, Cp);
+        g_launches += 1;
+        a.xq = d->scratch;
+    }
     return pw_i8_launch(a, true, a.G, (cudaStream_t)stream);
 }

@@ -363,9 +363,11 @@ class EvalPlan:
             tmp, q = quantised(st["src"], st["slots"][0], st["bits"][0])
             size, align = st["size"], st["align"]
 
+            up = torch.ops.aten.upsample_bilinear2d.out       # the kernel F.interpolate dispatches to, no temporary
+
             def run():
                 q()
-                dst.copy_(F.interpolate(tmp, size=size, mode="bilinear", align_corners=align))
+                up(tmp, list(size), align, None, None, out=dst)
             return run
         parts, c0 = [], 0
         for t, slot, bits in zip(st["srcs"], st["slots"], st["bits"]):
@@ -412,9 +414,11 @@ class EvalPlan:
         if pk is None:
             return None
         stats = None if out.stats is None else out.stats.data_ptr()
-        desc = pw_i8.make_conv_desc(src.buf.view(src.shape), out.buf.view(out.shape), pk, bq, self.slots[st["slot"]].data_ptr(), stats, stride, pad,
-                                    dil, st["relu"], int(m.quant.num_bits))
-        self.keep += [pk, desc]
+        scratch = pw_i8.conv_scratch(src.shape, self.dev)        # the input quantised once, s8 NHWC
+        desc = pw_i8.make_conv_desc(src.buf.view(src.shape), out.buf.view(out.shape), pk, bq,
+                                    self.slots[st["slot"]].data_ptr(), stats, stride, pad, dil, st["relu"],
+                                    int(m.quant.num_bits), scratch=scratch)
+        self.keep += [pk, desc, scratch]
         self.i8_layers.append(st["name"])
         return lambda: pw_i8.launch_conv(desc)
 

@@ -140,8 +140,15 @@ def _recover_codes(w, bits):
     return s32, lo, q, bits
 
 
-def make_conv_desc(x, y, pk, bias, slot_ptr, stats_ptr, stride, pad, dil, relu, bits):
-    """DfqConvI8Desc for x [N, C, H, W] -> y [N, O, OH, OW] (both contiguous fp32 CUDA tensors)."""
+def conv_scratch(x_shape, device):
+    """Device buffer for the quantise-once form of dfq_conv_i8 (the input as s8 codes, NHWC, C padded to 16)."""
+    N, C, H, W = x_shape
+    return torch.empty(int(L.lib().dfq_conv_i8_scratch_bytes(N, C, H, W)), dtype=torch.int8, device=device)
+
+
+def make_conv_desc(x, y, pk, bias, slot_ptr, stats_ptr, stride, pad, dil, relu, bits, scratch=None):
+    """DfqConvI8Desc for x [N, C, H, W] -> y [N, O, OH, OW] (both contiguous fp32 CUDA tensors).  With `scratch`
+    (conv_scratch) the input is quantised once and the taps read 16-byte code words -- the form for k x k > 1."""
     C, kh, kw = pk.geom
     d = L.DfqConvI8Desc()
     d.x, d.y = L.dev_f32(x, "input"), L.dev_f32(y, "output")
@@ -153,6 +160,7 @@ def make_conv_desc(x, y, pk, bias, slot_ptr, stats_ptr, stride, pad, dil, relu, 
     d.kh, d.kw, d.stride, d.pad, d.dil = kh, kw, int(stride), int(pad), int(dil)
     d.bits, d.relu = int(bits), int(relu)
     d.s_w, d.c_w = pk.s_w, pk.c_w
+    d.scratch = None if scratch is None else scratch.data_ptr()
     return d
 
 

@@ -289,7 +289,8 @@ def _fused_conv_forward(layer, x):
         pw_i8.launch(d)
         fused_calls["pw_i8"] += 1
     else:
-        d = pw_i8.make_conv_desc(x, y, pk, bias, slot.data_ptr(), None, sh, ph, dh, False, bits)
+        scratch = pw_i8.conv_scratch(x.shape, x.device) if kh * kw > 1 else None
+        d = pw_i8.make_conv_desc(x, y, pk, bias, slot.data_ptr(), None, sh, ph, dh, False, bits, scratch=scratch)
         pw_i8.launch_conv(d)
         fused_calls["conv_i8"] += 1
     return y

@@ -23,7 +23,7 @@
 extern "C" {
 #endif
 
-#define DFQ_ABI_VERSION 10
+#define DFQ_ABI_VERSION 11
 
 #if defined(__GNUC__)
 #pragma GCC visibility push(default)   /* the library is built with -fvisibility=hidden */
@@ -261,8 +261,11 @@ typedef struct DfqConvI8Desc {
     unsigned *out_stats;     /* [N, 2] encoded per-sample extrema of y, or NULL                 */
     int32_t N, C, H, W, O, OH, OW, kh, kw, stride, pad, dil, bits, relu;
     float s_w, c_w;
+    int8_t *scratch;         /* NULL, or dfq_conv_i8_scratch_bytes(N, C, H, W) device bytes: the input is then
+                              * quantised ONCE into s8 NHWC codes and every tap reads 16-byte words (k x k > 1) */
 } DfqConvI8Desc;
 int dfq_conv_i8_k_host(int C, int kh, int kw);
+int64_t dfq_conv_i8_scratch_bytes(int N, int C, int H, int W);
 int dfq_conv_i8(const DfqConvI8Desc *desc_host, void *stream);
 
 /* ---- (b) cross-layer equalisation: Cross_layer_equal.py:63-115 ---------------------- */

@@ -15,7 +15,8 @@ pytestmark = pytest.mark.gpu
 DEV = "cuda:0"
 
 
-def _case(oracle, N, C, O, H, W, k=3, stride=1, pad=1, dil=1, relu=True, bias=True, wbits=8, abits=8, seed=0):
+def _case(oracle, N, C, O, H, W, k=3, stride=1, pad=1, dil=1, relu=True, bias=True, wbits=8, abits=8, seed=0,
+          once=False):
     from data_free_quantization_b200 import pw_i8
     rs = np.random.default_rng(seed)
     x = (rs.standard_normal((N, C, H, W)) * 1.5 + 0.3).astype(np.float32)
@@ -37,7 +38,9 @@ def _case(oracle, N, C, O, H, W, k=3, stride=1, pad=1, dil=1, relu=True, bias=Tr
     stats = torch.zeros(N, 2, dtype=torch.int32, device=DEV)
     slot = _slot(lo, hi, abits)
     bd = None if b is None else torch.from_numpy(b).to(DEV)
-    d = pw_i8.make_conv_desc(xd, y, pk, bd, slot.data_ptr(), stats.data_ptr(), stride, pad, dil, relu, abits)
+    scratch = pw_i8.conv_scratch(xd.shape, DEV) if once else None     # quantise-once form (s8 NHWC codes)
+    d = pw_i8.make_conv_desc(xd, y, pk, bd, slot.data_ptr(), stats.data_ptr(), stride, pad, dil, relu, abits,
+                             scratch=scratch)
     pw_i8.launch_conv(d)
     torch.cuda.synchronize()
     got = y.cpu().numpy()
@@ -60,10 +63,13 @@ def _case(oracle, N, C, O, H, W, k=3, stride=1, pad=1, dil=1, relu=True, bias=Tr
     (3, 3, 32, 32, 32, 3, 2, 1, 1),         # stem-shaped: 3 channels padded to 16
     (1, 40, 272, 10, 10, 3, 1, 0, 1),       # no padding, two output passes
 ])
-def test_dense_conv(oracle, N, C, O, H, W, k, stride, pad, dil):
-    _case(oracle, N, C, O, H, W, k, stride, pad, dil)
+@pytest.mark.parametrize("once", [False, True])
+def test_dense_conv(oracle, N, C, O, H, W, k, stride, pad, dil, once):
+    _case(oracle, N, C, O, H, W, k, stride, pad, dil, once=once)
 
 
 def test_no_relu_no_bias_low_bits(oracle):
     _case(oracle, 2, 32, 48, 14, 14, relu=False, bias=False, wbits=4, abits=8, seed=3)
     _case(oracle, 1, 32, 48, 14, 14, wbits=6, abits=6, seed=4)
+    _case(oracle, 2, 32, 48, 14, 14, relu=False, bias=False, wbits=4, abits=8, seed=3, once=True)
+    _case(oracle, 1, 32, 48, 14, 14, wbits=6, abits=6, seed=4, once=True)
