@@ -112,6 +112,10 @@ PROTOTYPES = {
                                     c_void, c_void]),
     "dfq_qmean_f32": (ctypes.c_int, [c_void, c_void, i64, ctypes.c_int, ctypes.c_int, c_void, ctypes.c_int, c_void,
                                      c_void]),
+    "dfq_qinterp_bilinear_f32": (ctypes.c_int, [c_void, c_void, i64] + [ctypes.c_int] * 6 +
+                                 [c_void, ctypes.c_int, c_void, c_void]),
+    "dfq_qcopy_f32": (ctypes.c_int, [c_void, c_void, i64, i64, i64, i64, c_void, ctypes.c_int, c_void, c_void]),
+    "dfq_pad2d_f32": (ctypes.c_int, [c_void, c_void, i64] + [ctypes.c_int] * 7 + [c_void, c_void]),
     "dfq_pw_i8_plan_host": (ctypes.c_int, [ctypes.c_int, ctypes.c_int, P(ctypes.c_int), P(ctypes.c_int),
                                            P(ctypes.c_int), P(ctypes.c_int), P(i64)]),
     "dfq_pw_i8_pack_host": (ctypes.c_int, [c_void, ctypes.c_int, ctypes.c_int, c_void]),

@@ -245,4 +245,17 @@ __device__ __forceinline__ float4 quant_dequant4_fast(float4 v, const QuantConst
                        __fadd_rn(__fmul_rn(q[2], c.scale), c.add_back), __fadd_rn(__fmul_rn(q[3], c.scale), c.add_back));
 }
 
+__device__ __forceinline__ float quant_or_pass(float v, const QuantConsts &c, bool on) {
+    return on ? quant_dequant(v, c) : v;
+}
+
+// block-level min/max of `lo/hi` into stats[n] (encoded max(-y), max(y))
+__device__ __forceinline__ void stats_flush(unsigned *stats, int n, float lo, float hi, float *sm) {
+    block_minmax(lo, hi, sm);
+    if (threadIdx.x == 0) {
+        atomicMax(stats + 2 * n, enc_ordered(-lo));
+        atomicMax(stats + 2 * n + 1, enc_ordered(hi));
+    }
+}
+
 }  // namespace dfq

@@ -18,19 +18,6 @@ struct ConvArgs {
     int strips;            // row strips per plane
 };
 
-__device__ __forceinline__ float quant_or_pass(float v, const QuantConsts &c, bool on) {
-    return on ? quant_dequant(v, c) : v;
-}
-
-// block-level min/max of `lo/hi` into stats[n] (encoded max(-y), max(y))
-__device__ __forceinline__ void stats_flush(unsigned *stats, int n, float lo, float hi, float *sm) {
-    block_minmax(lo, hi, sm);
-    if (threadIdx.x == 0) {
-        atomicMax(stats + 2 * n, enc_ordered(-lo));
-        atomicMax(stats + 2 * n + 1, enc_ordered(hi));
-    }
-}
-
 // ---------------------------------------------------------------------------------------------------------
 // Depthwise 3x3 (groups == C == O), stride 1 or 2, zero padding `pad`, dilation `dil`.
 // A block owns `cb` consecutive channels x `rows` output rows of one image; the needed input rows are

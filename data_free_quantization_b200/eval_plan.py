@@ -46,9 +46,14 @@ class _T:
 
 
 class EvalPlan:
-    def __init__(self, model, transformer, batch, in_shape=(3, 224, 224), pw_impl="i8", dense_impl="i8"):
+    def __init__(self, model, transformer, batch, in_shape=(3, 224, 224), pw_impl="i8", dense_impl="i8",
+                 move_impl="native"):
         """pw_impl: "i8" = pointwise convs / linear layers on the tcgen05 s8 kernel (csrc/pw_i8.cu) wherever the
-        layer's weights sit on an integer grid of <= 8 bits, "fp32" = the CUDA-core comparator everywhere."""
+        layer's weights sit on an integer grid of <= 8 bits, "fp32" = the CUDA-core comparator everywhere.
+        move_impl: "native" = pad / pooling / interpolate / cat as one-pass libdfq_b200 kernels (csrc/move.cu) that
+        quantise on load and reduce the output statistics themselves; "torch" = the comparator (our fake-quant into a
+        temporary, the torch op, a separate statistics pass)."""
+        self.move_impl = move_impl
         self.model, self.fxg = model, transformer.fx_graph
         self.dev = next(model.parameters()).device
         self.N = int(batch)
@@ -119,7 +124,7 @@ class EvalPlan:
                     env[node] = src
                 elif isinstance(m, nn.AdaptiveAvgPool2d) and m.output_size in (1, (1, 1)):
                     out = _T(src.shape[:2] + (1, 1))
-                    out.by_torch, out.stats_encoded = True, False
+                    out.by_torch = self.move_impl == "torch"; out.stats_encoded = not out.by_torch
                     steps.append({"kind": "pool", "src": src, "out": out, "name": node.target})
                     env[node] = out
                 else:
@@ -153,7 +158,7 @@ class EvalPlan:
                         raise NotImplementedError(f"{key}: only constant zero padding of H and W")
                     N, C, H, W = src.shape
                     out = _T((N, C, H + pad[2] + pad[3], W + pad[0] + pad[1]))
-                    out.by_torch, out.stats_encoded = True, False
+                    out.by_torch = self.move_impl == "torch"; out.stats_encoded = not out.by_torch
                     steps.append({"kind": "pad", "src": src, "out": out, "name": key, "pad": pad})
                     env[node] = out
                 elif key is not None and key.startswith("F.interpolate"):
@@ -167,7 +172,7 @@ class EvalPlan:
                     qm = top_qms[top_i]
                     top_i += 1
                     out = _T(src.shape[:2] + size)
-                    out.by_torch, out.stats_encoded = True, False
+                    out.by_torch = self.move_impl == "torch"; out.stats_encoded = not out.by_torch
                     steps.append({"kind": "interp", "src": src, "out": out, "name": key, "size": size,
                                   "align": bool(kw.get("align_corners", False)), "bits": [qm.num_bits],
                                   "slots": [self._slot_for(qm, src)]})
@@ -180,7 +185,7 @@ class EvalPlan:
                     qms = top_qms[top_i:top_i + len(srcs)]
                     top_i += len(srcs)
                     out = _T((srcs[0].shape[0], sum(t.shape[1] for t in srcs)) + srcs[0].shape[2:])
-                    out.by_torch, out.stats_encoded = True, False
+                    out.by_torch = self.move_impl == "torch"; out.stats_encoded = not out.by_torch
                     steps.append({"kind": "cat", "srcs": srcs, "out": out, "name": key,
                                   "bits": [q.num_bits for q in qms],
                                   "slots": [self._slot_for(q, t) for q, t in zip(qms, srcs)]})
@@ -321,13 +326,48 @@ class EvalPlan:
                 self.ops.append((st["name"], (lambda a_: lambda: L.check(lib.dfq_qmean_f32(*a_, stream()),
                                                                         "dfq_qmean_f32"))(args)))
             elif st["kind"] in ("pad", "pool", "interp", "cat"):
-                self.ops.append((st["name"], self._torch_op(st, f32, slot_ptr)))
+                op = self._torch_op if self.move_impl == "torch" else self._move_op
+                self.ops.append((st["name"], op(st, f32, slot_ptr)))
             out = st["out"]
             if out.by_torch and out.need_stats:       # extrema of what the torch op wrote (plain floats)
                 sargs = (out.buf.data_ptr(), N, out.numel // N, out.stats.data_ptr())
                 self.ops.append((f"stats[{st['name']}]", (lambda a_: lambda: L.check(
                     lib.dfq_minmax_rows_f32(*a_, stream()), "dfq_minmax_rows_f32"))(sargs)))
         self.refresh_static()
+
+    def _move_op(self, st, f32, slot_ptr):
+        """Launch closure of a data-movement op on the one-pass kernels of csrc/move.cu: operand quantised on load
+        with its QuantMeasure's range, destination written once, per-sample extrema of the result reduced in the
+        same pass (so no temporary and no statistics pass)."""
+        lib, stream = L.lib(), L.stream
+        out, kind, N = st["out"], st["kind"], self.N
+        stats = None if out.stats is None else out.stats.data_ptr()
+        if kind == "pad":
+            l, r, t, b = st["pad"]
+            _, C, H, W = st["src"].shape
+            args = (st["src"].buf.data_ptr(), out.buf.data_ptr(), N, C, H, W, l, r, t, b, stats)
+            return lambda: L.check(lib.dfq_pad2d_f32(*args, stream()), "dfq_pad2d_f32")
+        if kind == "pool":          # mean over H x W of the raw operand (nn.AdaptiveAvgPool2d is not a patched op)
+            _, C, H, W = st["src"].shape
+            args = (st["src"].buf.data_ptr(), out.buf.data_ptr(), N, C, H * W, None, 8, stats)
+            return lambda: L.check(lib.dfq_qmean_f32(*args, stream()), "dfq_qmean_f32")
+        if kind == "interp":
+            _, C, H, W = st["src"].shape
+            args = (st["src"].buf.data_ptr(), out.buf.data_ptr(), N, C, H, W, st["size"][0], st["size"][1],
+                    1 if st["align"] else 0, slot_ptr(st["slots"][0]), int(st["bits"][0]), stats)
+            return lambda: L.check(lib.dfq_qinterp_bilinear_f32(*args, stream()), "dfq_qinterp_bilinear_f32")
+        launches, c0 = [], 0
+        hw = out.shape[2] * out.shape[3]
+        for t, slot, bits in zip(st["srcs"], st["slots"], st["bits"]):
+            count = t.shape[1] * hw
+            launches.append((t.buf.data_ptr(), out.buf.data_ptr() + 4 * c0 * hw, N, count, count, out.numel // N,
+                             slot_ptr(slot), int(bits), stats))
+            c0 += t.shape[1]
+
+        def run():
+            for a in launches:
+                L.check(lib.dfq_qcopy_f32(*a, stream()), "dfq_qcopy_f32")
+        return run
 
     def _torch_op(self, st, f32, slot_ptr):
         """Launch closure of a data-movement op of the graph (F.pad, adaptive average pooling, bilinear

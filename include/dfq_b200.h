@@ -219,6 +219,24 @@ int dfq_qadd_f32(const float *a, const float *b, float *out, int64_t N, int64_t 
 int dfq_qmean_f32(const float *x, float *out, int64_t N, int C, int HW, const float *slot, int bits,
                   unsigned *out_stats, void *stream);
 
+/* Data-movement ops of the same forward, each ONE pass with the operand fake-quantised on load (in_slot, NULL = as
+ * is) and the per-sample min/max of the result accumulated into out_stats (encoded, may be NULL):
+ *   dfq_qinterp_bilinear_f32  F.interpolate(Q(x), size=(OH, OW), mode='bilinear', align_corners=...) as patched by
+ *                             utils/layer_transform.py:98-110 (modeling/segmentation/deeplab.py:32, decoder.py:39,
+ *                             aspp.py:71); source index and weights formed as ATen forms them, fp32
+ *   dfq_qcopy_f32             y[n * dst_stride + k] = Q(x[n * src_stride + k]), k < count: one operand of
+ *                             torch.cat(dim=1) as patched by utils/layer_transform.py:113-125 (y points at the
+ *                             operand's channel offset inside the destination)
+ *   dfq_pad2d_f32             F.pad(x, (left, right, top, bottom)), constant 0, never quantised
+ *                             (utils/layer_transform.py ignore_op=['pad']; modeling/segmentation/backbone/mobilenet.py fixed_padding)
+ * Per-sample element counts must stay below 2^31. */
+int dfq_qinterp_bilinear_f32(const float *x, float *y, int64_t N, int C, int H, int W, int OH, int OW,
+                             int align_corners, const float *in_slot, int bits, unsigned *out_stats, void *stream);
+int dfq_qcopy_f32(const float *x, float *y, int64_t N, int64_t count, int64_t src_stride, int64_t dst_stride,
+                  const float *in_slot, int bits, unsigned *out_stats, void *stream);
+int dfq_pad2d_f32(const float *x, float *y, int64_t N, int C, int H, int W, int left, int right, int top, int bottom,
+                  unsigned *out_stats, void *stream);
+
 /* Tensor-core form of a pointwise (1x1, stride 1) convolution or a linear layer of the same forward
  * (utils/quantize.py:250-256, 358-363): s8 x s8 -> s32 tcgen05.mma.kind::i8, accumulator in TMEM.
  * Needs the weights on an integer grid of <= 8 bits: w[o,k] = s_w * code + min_w (what quantize_targ_layer

@@ -183,10 +183,20 @@ def test_static_eval_plan_matches_module_path(dgold, run):
             want = model(x).cpu().numpy()
     finally:
         restore_op()
+    # (1) movement ops through torch, as the module path runs them: same kernels, same ranges -> equal to rounding
+    plan_t = EvalPlan(model, run["tr"], batch=2, in_shape=(3, 129, 129), move_impl="torch")
+    got_t = plan_t(x).cpu().numpy().reshape(want.shape)
+    assert np.abs(got_t - want).max() <= 1e-5 * np.abs(want).max(), np.abs(got_t - want).max() / np.abs(want).max()
+    assert np.mean(got_t.argmax(1) == want.argmax(1)) >= 0.999
+    # (2) the default: pad / pool / interpolate / cat on csrc/move.cu.  Each op agrees with ATen to 1e-6 of the
+    # operand range (tests/test_gpu_move.py), but the interpolated decoder features are re-quantised by the next
+    # QuantMeasure, so a last-bit difference flips an 8-bit code now and then (measured 1.2e-2 of the largest logit,
+    # 99.9 % of the pixels keep their class): the bars are those of the comparison with the reference below.
     plan = EvalPlan(model, run["tr"], batch=2, in_shape=(3, 129, 129))
     got = plan(x).cpu().numpy().reshape(want.shape)
-    assert np.abs(got - want).max() <= 1e-5 * np.abs(want).max(), np.abs(got - want).max() / np.abs(want).max()
-    assert np.mean(got.argmax(1) == want.argmax(1)) >= 0.999
+    assert np.abs(got - want).max() <= 3e-2 * np.abs(want).max(), np.abs(got - want).max() / np.abs(want).max()
+    assert np.mean(got.argmax(1) == want.argmax(1)) >= 0.995
+    assert not any(name.startswith("stats[") for name, _ in plan.ops)      # no separate statistics pass left
     # against the reference's own logits, with the bars of the module-path test
     ref = npz["eval/logits_b2"]
     assert np.abs(got[:, :, ::4, ::4] - ref).max() / np.abs(ref).max() <= 3e-2

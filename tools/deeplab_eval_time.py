@@ -64,28 +64,39 @@ def main():
         restore_op()
         Q.FUSED_EVAL = True
     from data_free_quantization_b200.eval_plan import EvalPlan
-    plan = EvalPlan(model, tr, batch=batch, in_shape=(3, 513, 513))
-    plan(x)
-    replay = plan.capture()
-    for _ in range(2):
-        replay()
-    torch.cuda.synchronize()
-    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    a.record()
-    for _ in range(5):
-        replay()
-    b.record(); b.synchronize()
-    ms = a.elapsed_time(b) / 5
-    print(f"static plan, one CUDA graph ({len(plan.ops)} launches-or-ops): {ms:.2f} ms per batch of {batch} -> "
-          f"{batch / ms * 1e3:.1f} images/s")
-    by = {}
-    for name, fn in plan.ops:
-        kind = plan.op_info.get(name, {}).get("kind", name.split("[")[0])
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record(); fn(); e1.record(); e1.synchronize()
-        by[kind] = by.get(kind, 0.0) + e0.elapsed_time(e1)
-    print("by kind (ms, serialised):", {k: round(v, 3) for k, v in sorted(by.items(), key=lambda kv: -kv[1])})
-
+    outs = {}
+    for move in ("torch", "native"):
+        plan = EvalPlan(model, tr, batch=batch, in_shape=(3, 513, 513), move_impl=move)
+        outs[move] = plan(x).clone()
+        replay = plan.capture()
+        for _ in range(2):
+            replay()
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(5):
+            replay()
+        b.record(); b.synchronize()
+        ms = a.elapsed_time(b) / 5
+        print(f"static plan (pad/pool/interp/cat: {move}), one CUDA graph ({len(plan.ops)} launches-or-ops): "
+              f"{ms:.2f} ms per batch of {batch} -> {batch / ms * 1e3:.1f} images/s")
+        by, byop = {}, {}
+        for name, fn in plan.ops:
+            kind = plan.op_info.get(name, {}).get("kind", name.split("[")[0])
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(); fn(); e1.record(); e1.synchronize()
+            t = e0.elapsed_time(e1)
+            by[kind] = by.get(kind, 0.0) + t
+            if kind in ("interp", "cat", "pad", "pool"):
+                byop[name] = (round(t, 4), round(plan.op_info[name]["bytes"] / t / 1e6, 1))
+        print("by kind (ms, serialised):", {k: round(v, 3) for k, v in sorted(by.items(), key=lambda kv: -kv[1])})
+        if move == "native":
+            print("movement ops (ms, algorithmic GB/s):", byop)
+        del plan, replay
+    d = (outs["native"] - outs["torch"]).abs().max().item() / outs["torch"].abs().max().item()
+    same = (outs["native"].view(batch, -1, 513 * 513).argmax(1) == outs["torch"].view(batch, -1, 513 * 513).argmax(1))
+    print(f"native vs torch movement ops: max |dlogit| / max |logit| = {d:.3g}, same class on "
+          f"{same.float().mean().item() * 100:.4f} % of pixels")
 
 if __name__ == "__main__":
     main()
