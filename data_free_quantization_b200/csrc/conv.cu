@@ -74,6 +74,88 @@ dwconv3x3_kernel(ConvArgs a) {
 }
 
 // ---------------------------------------------------------------------------------------------------------
+// Depthwise 3x3 WITHOUT padding, stride S, dilation D, any plane size (odd widths, no alignment): DeepLab's backbone
+// pads with F.pad first (modeling/segmentation/backbone/mobilenet.py:16-22, 62), so its 17 depthwise layers are
+// valid convolutions of 259/131/67/35/37-wide planes.  A block owns `cb` channels x `rows` output rows; their input
+// is one contiguous run per channel, copied flat (no index arithmetic per element), quantised once, into shared
+// memory.  A thread then owns 4 vertically adjacent outputs of ONE column: lanes walk adjacent columns, so shared
+// loads are conflict-free scalars (3 S + 2 D + 1 input rows x 3 taps = 18 loads for 36 FMAs at S = D = 1), global
+// stores are coalesced whatever the row length, and the 9 weights come from shared memory as broadcasts.  Same
+// accumulation order as dwconv3x3_kernel (bit-identical results).
+template <int S, int D>
+__global__ void __launch_bounds__(kThreads)
+dwconv3x3_valid_kernel(ConvArgs a) {
+    extern __shared__ float smem[];
+    __shared__ float red[2 * kWarps];
+    constexpr int R = 3 * S + 2 * D + 1;                          // input rows under 4 stacked outputs
+    const int tid = threadIdx.x;
+    int b = blockIdx.x;
+    const int strip = b % a.strips; b /= a.strips;
+    const int cgroups = (a.C + a.cb - 1) / a.cb;
+    const int cg = b % cgroups;
+    const int n = b / cgroups;
+    const int c0 = cg * a.cb, nc = min(a.cb, a.C - c0);
+    const int r0 = strip * a.rows, nr = min(a.rows, a.OH - r0);
+    const int in_rows = (nr - 1) * S + 2 * D + 1;
+    const int plane = in_rows * a.W;
+    const int plane_s = ((a.rows - 1) * S + 2 * D + 1) * a.W;     // allocation stride per channel
+    float *wsm = smem + a.cb * plane_s;                           // [cb][10]: 9 taps + bias
+    const bool on = a.slot != nullptr;
+    QuantConsts qc;
+    if (on) qc = consts_from_slot(*a.slot, a.bits, 0, 0.f, 0.f);
+    for (int c = 0; c < nc; ++c) {
+        const float *p = a.x + (((int64_t)n * a.C + c0 + c) * a.H + (int64_t)r0 * S) * a.W;
+        float *q = smem + c * plane_s;
+        for (int i = tid; i < plane; i += kThreads) q[i] = quant_or_pass(__ldg(p + i), qc, on);
+    }
+    for (int i = tid; i < nc * 10; i += kThreads) {
+        const int c = i / 10, t = i - c * 10;
+        wsm[i] = t < 9 ? __ldg(a.w + (int64_t)(c0 + c) * 9 + t) : (a.bias ? __ldg(a.bias + c0 + c) : 0.0f);
+    }
+    __syncthreads();
+    float lo = INFINITY, hi = -INFINITY;
+    const int ngroups = (nr + 3) >> 2, per_c = ngroups * a.OW;
+    const float inv_per_c = 1.0f / (float)per_c, inv_OW = 1.0f / (float)a.OW;
+    for (int it = tid; it < nc * per_c; it += kThreads) {
+        int c = (int)(((float)it + 0.5f) * inv_per_c), rem = it - c * per_c;
+        if (rem < 0) { --c; rem += per_c; } else if (rem >= per_c) { ++c; rem -= per_c; }
+        int rg = (int)(((float)rem + 0.5f) * inv_OW), col = rem - rg * a.OW;
+        if (col < 0) { --rg; col += a.OW; } else if (col >= a.OW) { ++rg; col -= a.OW; }
+        const int orow = rg << 2, nv = min(4, nr - orow);
+        const float *sp = smem + c * plane_s + orow * S * a.W + col * S;
+        const float *w = wsm + c * 10;
+        float v[R][3];
+        const int last = (nv - 1) * S + 2 * D;                    // last input row this item may touch
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const float *row = sp + min(r, last) * a.W;
+#pragma unroll
+            for (int k = 0; k < 3; ++k) v[r][k] = row[k * D];
+        }
+        float wr[9];
+#pragma unroll
+        for (int t = 0; t < 9; ++t) wr[t] = w[t];
+        const float bias = w[9];
+        float *yp = a.y + (((int64_t)n * a.O + c0 + c) * a.OH + r0 + orow) * a.OW + col;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            float acc = 0.0f;
+#pragma unroll
+            for (int j = 0; j < 3; ++j)
+#pragma unroll
+                for (int k = 0; k < 3; ++k) acc = __fmaf_rn(v[i * S + j * D][k], wr[j * 3 + k], acc);
+            if (a.bias) acc = __fadd_rn(acc, bias);
+            if (a.relu) acc = fmaxf(acc, 0.0f);
+            if (i < nv) {
+                yp[(int64_t)i * a.OW] = acc;
+                lo = fminf(lo, acc); hi = fmaxf(hi, acc);
+            }
+        }
+    }
+    if (a.stats) stats_flush(a.stats, n, lo, hi, red);
+}
+
+// ---------------------------------------------------------------------------------------------------------
 // Depthwise 3x3, pad 1, dilation 1, stride 1 or 2 (every depthwise layer of MobileNetV2): the streaming form.
 // A block owns either a strip of output rows of ONE channel plane or `cb` whole planes of consecutive channels, so
 // its input is one contiguous run of floats: it is read with 128-bit loads, quantised once and written to a
@@ -819,6 +901,27 @@ extern "C" int dfq_qconv2d_f32(const DfqConvDesc *d, void *stream) {
         else dwconv3x3_stream_kernel<false><<<(unsigned)blocks, kThreads, tile_bytes(rows, cb), st>>>(w);
         g_launches += 1;
         return (int)cudaGetLastError();
+    }
+    if (d->groups == d->C_in && d->C_in == d->C_out && d->kh == 3 && d->kw == 3 && d->pad == 0 &&
+        ((d->stride == 1 && (d->dil == 1 || d->dil == 2)) || (d->stride == 2 && d->dil == 1))) {
+        // valid depthwise (DeepLab after F.pad): about 4096 outputs per block in row groups of 4, <= 48 KB of input
+        const int S = d->stride, D = d->dil;
+        int rows = OH, cb = 1;
+        if (OH * OW > 4096) rows = max(4, (4096 / OW) & ~3);
+        else cb = max(1, min(d->C_in, 4096 / (OH * OW)));
+        auto smem_of = [&](int r, int c) { return ((size_t)c * ((r - 1) * S + 2 * D + 1) * d->W + (size_t)c * 10) * sizeof(float); };
+        while (smem_of(rows, cb) > 48 * 1024 && (cb > 1 || rows > 4)) { if (cb > 1) cb = (cb + 1) / 2; else rows = max(4, (rows / 2 + 3) & ~3); }
+        if (smem_of(rows, cb) <= 48 * 1024) {
+            a.rows = rows; a.cb = cb; a.strips = (OH + rows - 1) / rows;
+            const int64_t blocks = (int64_t)d->N * ((d->C_in + cb - 1) / cb) * a.strips;
+            if (blocks > 0x7fffffffll) return (int)cudaErrorInvalidValue;
+            const size_t smem = smem_of(rows, cb);
+            if (S == 1 && D == 1) dwconv3x3_valid_kernel<1, 1><<<(unsigned)blocks, kThreads, smem, st>>>(a);
+            else if (S == 2) dwconv3x3_valid_kernel<2, 1><<<(unsigned)blocks, kThreads, smem, st>>>(a);
+            else dwconv3x3_valid_kernel<1, 2><<<(unsigned)blocks, kThreads, smem, st>>>(a);
+            g_launches += 1;
+            return (int)cudaGetLastError();
+        }
     }
     if (d->groups == d->C_in && d->C_in == d->C_out && d->kh == 3 && d->kw == 3) {
         // strip height: about 2048 outputs per block; small planes take several channels per block

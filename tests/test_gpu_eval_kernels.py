@@ -72,6 +72,21 @@ def test_depthwise3x3(oracle, C, H, stride, N, quant):
     _conv(x, w, b, stride, 1, 1, C, True, (0.0, 2.5) if quant else None, oracle)
 
 
+@pytest.mark.parametrize("C,H,W,stride,dil,N", [(32, 67, 67, 1, 1, 2), (96, 67, 67, 2, 1, 2), (144, 35, 35, 1, 1, 3),
+                                                (192, 37, 37, 1, 2, 2), (7, 9, 12, 1, 1, 1), (5, 10, 7, 2, 1, 2),
+                                                (3, 5, 5, 1, 2, 1), (16, 131, 131, 2, 1, 1), (8, 259, 259, 1, 1, 1),
+                                                (4, 300, 40, 1, 3, 1)])
+@pytest.mark.parametrize("quant", [False, True])
+def test_depthwise3x3_valid(oracle, C, H, W, stride, dil, N, quant):
+    """pad 0 (DeepLab pads with F.pad first, modeling/segmentation/backbone/mobilenet.py:16-22): the column-per-lane
+    kernel for (stride, dilation) in {(1,1), (2,1), (1,2)}, the generic kernel for the rest (dilation 3 here)."""
+    rng = np.random.default_rng(C + H + W)
+    x = np.maximum(rng.standard_normal((N, C, H, W)), 0).astype(np.float32)
+    w = rng.standard_normal((C, 1, 3, 3)).astype(np.float32)
+    b = rng.standard_normal(C).astype(np.float32)
+    _conv(x, w, b if C != 7 else None, stride, 0, dil, C, C % 2 == 0, (0.0, 2.5) if quant else None, oracle)
+
+
 @pytest.mark.parametrize("quant", [False, True])
 def test_first_layer_dense3x3(oracle, quant):
     rng = np.random.default_rng(1)
