@@ -98,15 +98,42 @@ dwconv3x3_valid_kernel(ConvArgs a) {
     const int r0 = strip * a.rows, nr = min(a.rows, a.OH - r0);
     const int in_rows = (nr - 1) * S + 2 * D + 1;
     const int plane = in_rows * a.W;
-    const int plane_s = ((a.rows - 1) * S + 2 * D + 1) * a.W;     // allocation stride per channel
+    // allocation stride per channel: the run is stored at the 16-byte phase of its source, so that 128-bit global
+    // loads pair with 128-bit shared stores
+    const int plane_s = (((a.rows - 1) * S + 2 * D + 1) * a.W + 3 + 3) & ~3;
     float *wsm = smem + a.cb * plane_s;                           // [cb][10]: 9 taps + bias
     const bool on = a.slot != nullptr;
     QuantConsts qc;
     if (on) qc = consts_from_slot(*a.slot, a.bits, 0, 0.f, 0.f);
+    const bool fast4 = on && qc.fast;
     for (int c = 0; c < nc; ++c) {
         const float *p = a.x + (((int64_t)n * a.C + c0 + c) * a.H + (int64_t)r0 * S) * a.W;
-        float *q = smem + c * plane_s;
-        for (int i = tid; i < plane; i += kThreads) q[i] = quant_or_pass(__ldg(p + i), qc, on);
+        const int m = (int)((((uintptr_t)p) >> 2) & 3);
+        float *q = smem + c * plane_s + m;                        // q - m and p - m are 16-byte aligned
+        const int j_end = m + plane;
+        // groups of 4 floats in the shifted coordinate; two 128-bit loads in flight per thread
+        for (int j0 = 4 * tid; j0 < j_end; j0 += 8 * kThreads) {
+            const int j1 = j0 + 4 * kThreads;
+            const bool full0 = j0 >= m && j0 + 4 <= j_end, full1 = j1 >= m && j1 + 4 <= j_end;
+            float4 t0 = make_float4(0.f, 0.f, 0.f, 0.f), t1 = t0;
+            if (full0) t0 = __ldg(reinterpret_cast<const float4 *>(p - m + j0));
+            if (full1) t1 = __ldg(reinterpret_cast<const float4 *>(p - m + j1));
+#pragma unroll
+            for (int u = 0; u < 2; ++u) {
+                const int j = u ? j1 : j0;
+                const bool full = u ? full1 : full0;
+                const float4 t = u ? t1 : t0;
+                if (full) {
+                    float4 r;
+                    if (fast4) r = quant_dequant4_fast(t, qc);
+                    else r = make_float4(quant_or_pass(t.x, qc, on), quant_or_pass(t.y, qc, on),
+                                         quant_or_pass(t.z, qc, on), quant_or_pass(t.w, qc, on));
+                    *reinterpret_cast<float4 *>(q - m + j) = r;
+                } else if (j < j_end) {
+                    for (int k = max(j, m); k < min(j + 4, j_end); ++k) q[k - m] = quant_or_pass(__ldg(p - m + k), qc, on);
+                }
+            }
+        }
     }
     for (int i = tid; i < nc * 10; i += kThreads) {
         const int c = i / 10, t = i - c * 10;
@@ -122,15 +149,23 @@ dwconv3x3_valid_kernel(ConvArgs a) {
         int rg = (int)(((float)rem + 0.5f) * inv_OW), col = rem - rg * a.OW;
         if (col < 0) { --rg; col += a.OW; } else if (col >= a.OW) { ++rg; col -= a.OW; }
         const int orow = rg << 2, nv = min(4, nr - orow);
-        const float *sp = smem + c * plane_s + orow * S * a.W + col * S;
+        const int mc = (int)(((uintptr_t)(a.x + (((int64_t)n * a.C + c0 + c) * a.H + (int64_t)r0 * S) * a.W) >> 2) & 3);
+        const float *sp = smem + c * plane_s + mc + orow * S * a.W + col * S;
         const float *w = wsm + c * 10;
         float v[R][3];
-        const int last = (nv - 1) * S + 2 * D;                    // last input row this item may touch
+        if (nv == 4) {
 #pragma unroll
-        for (int r = 0; r < R; ++r) {
-            const float *row = sp + min(r, last) * a.W;
+            for (int r = 0; r < R; ++r)
 #pragma unroll
-            for (int k = 0; k < 3; ++k) v[r][k] = row[k * D];
+                for (int k = 0; k < 3; ++k) v[r][k] = sp[r * a.W + k * D];
+        } else {
+            const int last = (nv - 1) * S + 2 * D;                // last input row this item may touch
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                const float *row = sp + min(r, last) * a.W;
+#pragma unroll
+                for (int k = 0; k < 3; ++k) v[r][k] = row[k * D];
+            }
         }
         float wr[9];
 #pragma unroll
@@ -909,7 +944,7 @@ extern "C" int dfq_qconv2d_f32(const DfqConvDesc *d, void *stream) {
         int rows = OH, cb = 1;
         if (OH * OW > 4096) rows = max(4, (4096 / OW) & ~3);
         else cb = max(1, min(d->C_in, 4096 / (OH * OW)));
-        auto smem_of = [&](int r, int c) { return ((size_t)c * ((r - 1) * S + 2 * D + 1) * d->W + (size_t)c * 10) * sizeof(float); };
+        auto smem_of = [&](int r, int c) { return ((size_t)c * ((((r - 1) * S + 2 * D + 1) * d->W + 6) & ~3) + (size_t)c * 10) * sizeof(float); };
         while (smem_of(rows, cb) > 48 * 1024 && (cb > 1 || rows > 4)) { if (cb > 1) cb = (cb + 1) / 2; else rows = max(4, (rows / 2 + 3) & ~3); }
         if (smem_of(rows, cb) <= 48 * 1024) {
             a.rows = rows; a.cb = cb; a.strips = (OH + rows - 1) / rows;

@@ -87,11 +87,14 @@ def main():
             e0.record(); fn(); e1.record(); e1.synchronize()
             t = e0.elapsed_time(e1)
             by[kind] = by.get(kind, 0.0) + t
-            if kind in ("interp", "cat", "pad", "pool"):
-                byop[name] = (round(t, 4), round(plan.op_info[name]["bytes"] / t / 1e6, 1))
+            if name in plan.op_info:
+                byop[name] = (kind, round(t, 4), round(plan.op_info[name]["bytes"] / t / 1e6, 1),
+                              plan.op_info[name]["shape"])
         print("by kind (ms, serialised):", {k: round(v, 3) for k, v in sorted(by.items(), key=lambda kv: -kv[1])})
         if move == "native":
-            print("movement ops (ms, algorithmic GB/s):", byop)
+            print("per op (kind, ms, algorithmic GB/s, shape), slowest first:")
+            for name, v in sorted(byop.items(), key=lambda kv: -kv[1][1])[:int(os.environ.get("DFQ_TOP", "40"))]:
+                print(f"  {name:40s} {v[0]:7s} {v[1]:8.4f} {v[2]:8.1f}  {v[3]}")
         del plan, replay
     d = (outs["native"] - outs["torch"]).abs().max().item() / outs["torch"].abs().max().item()
     same = (outs["native"].view(batch, -1, 513 * 513).argmax(1) == outs["torch"].view(batch, -1, 513 * 513).argmax(1))
