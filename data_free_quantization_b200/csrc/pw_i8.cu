@@ -217,14 +217,30 @@ pw_i8_kernel(PwI8Args a) {
         }
     };
     // kQ: the 16-byte word of chunk q at this thread's tap pixel (zeros in the padding / beyond the last tap)
+    // The chunks a thread reads are q = h, h + 2, h + 4, ... in this order (load_stage is called for s = 0, 1, 2, ...),
+    // so the tap and the channel chunk are STEPPED, not divided out: ncu charged 35 % of the kernel's instructions to
+    // the two integer divisions per 16-byte load (profiles/r1zz_conv_i8_ncu.md).  q_tap is the word of channel chunk 0
+    // at the current tap's pixel, or NULL in the padding / past the last tap.
     const int8_t *xqb = kQ ? a.xq + n * ((int64_t)a.H * a.W * a.cchunks * 16) : nullptr;
-    auto chunk_q = [&](int q) {
-        const int t = q / a.cchunks, cc = q - t * a.cchunks;              // warp-uniform
-        const int i = t / a.kw, j = t - i * a.kw;
-        const int ih = ih0 + i * a.dil, iw = iw0 + j * a.dil;
-        const bool inb = valid && t < a.taps && (unsigned)ih < (unsigned)a.H && (unsigned)iw < (unsigned)a.W;
-        return inb ? __ldg(reinterpret_cast<const uint4 *>(xqb + (((int64_t)ih * a.W + iw) * a.cchunks + cc) * 16))
-                   : make_uint4(0u, 0u, 0u, 0u);
+    int q_t = 0, q_cc = h, q_i = 0, q_j = 0;
+    const int8_t *q_tap = nullptr;
+    auto tap_ptr = [&]() {
+        const int ih = ih0 + q_i * a.dil, iw = iw0 + q_j * a.dil;
+        const bool inb = valid && q_t < a.taps && (unsigned)ih < (unsigned)a.H && (unsigned)iw < (unsigned)a.W;
+        q_tap = inb ? xqb + ((int64_t)ih * a.W + iw) * (a.cchunks * 16) : nullptr;
+    };
+    if (kQ) {
+        while (q_cc >= a.cchunks) { q_cc -= a.cchunks; ++q_t; if (++q_j == a.kw) { q_j = 0; ++q_i; } }
+        tap_ptr();
+    }
+    auto chunk_q = [&](int) {
+        const uint4 w = q_tap ? __ldg(reinterpret_cast<const uint4 *>(q_tap + q_cc * 16)) : make_uint4(0u, 0u, 0u, 0u);
+        q_cc += 2;
+        if (q_cc >= a.cchunks) {                                          // warp-uniform
+            do { q_cc -= a.cchunks; ++q_t; if (++q_j == a.kw) { q_j = 0; ++q_i; } } while (q_cc >= a.cchunks);
+            tap_ptr();
+        }
+        return w;
     };
     // activations of one ring stage: two 16-wide K chunks per thread, all loads in flight before any use
     float v[kQ ? 1 : 2][kQ ? 1 : 16];
@@ -371,6 +387,23 @@ pw_i8_kernel(PwI8Args a) {
         float *py = yb + (int64_t)oc * ys_o;
         if (!ev) {                                                // rows past the end (last tile only)
         } else if (nvalid == 16) {                                       // the common case: no per-column predicate
+            // padding correction of this pixel for the chunk's 16 channels: tap-outer, channel-inner (the same
+            // ascending tap order per channel as tap_corr), 128-bit shared loads -- the per-output form walked all
+            // taps for every output of every warp that touches an image border (23 % of the instructions)
+            float corr[16];
+            if (kConv && oob) {
+#pragma unroll
+                for (int j = 0; j < 16; ++j) corr[j] = 0.0f;
+                for (uint32_t mm = oob; mm; mm &= mm - 1) {
+                    const float4 *tc = reinterpret_cast<const float4 *>(tap_c + (__ffs(mm) - 1) * a.npass + chunk * 16);
+#pragma unroll
+                    for (int j4 = 0; j4 < 4; ++j4) {
+                        const float4 v4 = tc[j4];
+                        corr[4 * j4] = __fadd_rn(corr[4 * j4], v4.x); corr[4 * j4 + 1] = __fadd_rn(corr[4 * j4 + 1], v4.y);
+                        corr[4 * j4 + 2] = __fadd_rn(corr[4 * j4 + 2], v4.z); corr[4 * j4 + 3] = __fadd_rn(corr[4 * j4 + 3], v4.w);
+                    }
+                }
+            }
 #pragma unroll
             for (int j4 = 0; j4 < 4; ++j4) {
                 const float4 c4 = cc[j4];
@@ -378,7 +411,7 @@ pw_i8_kernel(PwI8Args a) {
 #pragma unroll
                 for (int t = 0; t < 4; ++t) {
                     float cst = __fadd_rn(row_c, cj[t]);
-                    if (kConv && oob) cst = __fsub_rn(cst, tap_corr(tap_c, oob, a.taps, a.npass, chunk * 16 + 4 * j4 + t));
+                    if (kConv && oob) cst = __fsub_rn(cst, corr[4 * j4 + t]);
                     const float yv = fmaxf(__fmaf_rn(fa, (float)(int)d[4 * j4 + t], cst), floor_v);
                     *py = yv;
                     py += ys_o;
