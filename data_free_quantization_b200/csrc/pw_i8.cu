@@ -159,7 +159,11 @@ template <bool kPre, bool kConv, bool kQ>
 __global__ void __launch_bounds__(kThreads, kPre ? 3 : 4)
 pw_i8_kernel(PwI8Args a) {
     extern __shared__ __align__(128) uint8_t smem[];
-    __shared__ __align__(8) uint64_t bars[4];           // full[2] (weights landed), done[2] (MMAs of the stage retired)
+    // Weight ring: kBS stages, the bulk copy of slab s + kAhead is issued at step s.  With the two-stage ring the copy
+    // of a slab was only issued in the step that consumes it, so its L2 latency (~1.5 k cycles for 16 KB) sat on every
+    // step's critical path -- 3.5 k cycles per 64-byte slab on the decoder's 3 x 3 layers against 256 cycles of MMA.
+    constexpr int kBS = kQ ? 4 : 2, kAhead = kBS - 2;
+    __shared__ __align__(8) uint64_t bars[6];           // full[kBS] (weights landed), done[2] at [4] (MMAs of the stage retired)
     __shared__ uint32_t tmem_base_s;
     __shared__ int colsum_s[2][kI8M];
     __shared__ __align__(16) float chan_c[256];          // per output channel of this pass: c_x*wr[o] + K c_x c_w + bias[o]
@@ -170,12 +174,13 @@ pw_i8_kernel(PwI8Args a) {
     uint8_t *sA = smem;                                  // [2][4 K-chunks][128 rows][16 B]
     uint8_t *sB = smem + 2 * kI8ASlab;                   // [2][4 K-chunks][npass rows][16 B]
     const uint32_t bslab = (uint32_t)a.npass * kI8Slab;
-    float *tap_c = reinterpret_cast<float *>(sB + 2 * bslab);   // kConv: [taps][npass] c_x * (wrt[t][o] + C c_w s_x..)
+    float *tap_c = reinterpret_cast<float *>(sB + kBS * bslab);   // kConv: [taps][npass] c_x * (wrt[t][o] + C c_w s_x..)
     const uint32_t sA_u = smem_u32(sA), sB_u = smem_u32(sB);
-    const uint32_t full0 = smem_u32(&bars[0]), done0 = smem_u32(&bars[2]);
+    const uint32_t full0 = smem_u32(&bars[0]), done0 = smem_u32(&bars[4]);
 
     if (tid == 0) {
-        mbar_init(full0, 1); mbar_init(full0 + 8, 1); mbar_init(done0, 1); mbar_init(done0 + 8, 1);
+        for (int i = 0; i < kBS; ++i) mbar_init(full0 + 8 * i, 1);
+        mbar_init(done0, 1); mbar_init(done0 + 8, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 0) {
@@ -287,6 +292,12 @@ pw_i8_kernel(PwI8Args a) {
     tc_fence_after();
     const uint32_t tmem = tmem_base_s;
     const int8_t *wsrc = a.wpk + (int64_t)pass * a.slabs * bslab;
+    if (tid == 0) {
+        for (int s0 = 0; s0 < kAhead && s0 < a.slabs; ++s0) {
+            mbar_expect_tx(full0 + 8 * s0, bslab);
+            bulk_g2s(sB_u + s0 * bslab, wsrc + (int64_t)s0 * bslab, bslab, full0 + 8 * s0);
+        }
+    }
     // instruction descriptor: D = s32, A = B = s8, both K-major, N = npass, M = 128
     const uint32_t idesc = (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(a.npass >> 3) << 17) |
                            ((uint32_t)(kI8M >> 4) << 24);
@@ -297,9 +308,11 @@ pw_i8_kernel(PwI8Args a) {
         if (!kPre) load_stage(s);                        // 1. this stage's activations
         // 2. the ring stage is free once the MMAs issued two slabs ago have retired
         if (s >= 2) mbar_wait(done0 + 8 * buf, ((s >> 1) - 1) & 1);
-        if (tid == 0) {
-            mbar_expect_tx(full0 + 8 * buf, bslab);
-            bulk_g2s(sB_u + buf * bslab, wsrc + (int64_t)s * bslab, bslab, full0 + 8 * buf);
+        const int bbuf = s & (kBS - 1);
+        if (tid == 0 && s + kAhead < a.slabs) {          // its stage was last read by slab s - 2, retired above
+            const int s2 = s + kAhead, b2 = s2 & (kBS - 1);
+            mbar_expect_tx(full0 + 8 * b2, bslab);
+            bulk_g2s(sB_u + b2 * bslab, wsrc + (int64_t)s2 * bslab, bslab, full0 + 8 * b2);
         }
         // 3. quantise on load (utils/quantize.py:72-74), centre to s8, pack, canonical-order store
 #pragma unroll
@@ -333,12 +346,12 @@ pw_i8_kernel(PwI8Args a) {
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         __syncthreads();
         if (tid == 0) {
-            mbar_wait(full0 + 8 * buf, (s >> 1) & 1);
+            mbar_wait(full0 + 8 * bbuf, (s / kBS) & 1);
             tc_fence_after();
 #pragma unroll
             for (int kk = 0; kk < 2; ++kk) {
                 const uint64_t ad = umma_desc(sA_u + buf * kI8ASlab + kk * 2 * (kI8M * 16), kI8M * 16, 128);
-                const uint64_t bd = umma_desc(sB_u + buf * bslab + kk * 2 * (a.npass * 16), a.npass * 16, 128);
+                const uint64_t bd = umma_desc(sB_u + bbuf * bslab + kk * 2 * (a.npass * 16), a.npass * 16, 128);
                 umma_i8(tmem, ad, bd, idesc, (s | kk) != 0);
             }
             umma_commit(done0 + 8 * buf);
@@ -731,16 +744,16 @@ extern "C" int dfq_pw_i8_pack_host(const int8_t *codes, int O, int K, int8_t *pa
 static int pw_i8_launch(PwI8Args &a, bool conv, int64_t G, cudaStream_t stream) {
     a.tmem_cols = 32;
     while (a.tmem_cols < a.npass) a.tmem_cols *= 2;
-    const size_t smem = 2 * (size_t)kI8ASlab + 2 * (size_t)a.npass * kI8Slab +
+    const size_t smem = 2 * (size_t)kI8ASlab + (conv && a.xq ? 4 : 2) * (size_t)a.npass * kI8Slab +
                         (conv ? (size_t)a.taps * a.npass * sizeof(float) : 0);
-    if (smem > 64 * 1024) return (int)cudaErrorInvalidValue;
+    if (smem > 100 * 1024) return (int)cudaErrorInvalidValue;
     static bool attr_set = false;
     if (!attr_set) {
         const void *fns[] = {(const void *)pw_i8_kernel<false, false, false>, (const void *)pw_i8_kernel<true, false, false>,
                              (const void *)pw_i8_kernel<false, true, false>, (const void *)pw_i8_kernel<true, true, false>,
                              (const void *)pw_i8_kernel<false, true, true>, (const void *)pw_i8_kernel<true, true, true>};
         for (const void *fn : fns) {
-            cudaError_t ce = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+            cudaError_t ce = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
             if (ce != cudaSuccess) return (int)ce;
         }
         attr_set = true;
@@ -782,6 +795,14 @@ static int pw_i8_launch(PwI8Args &a, bool conv, int64_t G, cudaStream_t stream) 
         return (int)cudaGetLastError();
     }
     if (conv && a.xq) {
+        // a 256-column accumulator admits two CTAs per SM whatever the register count, so the prefetching form's 79
+        // registers cost nothing there (DFQ_CONV_PRE=0/1 overrides for A/B runs)
+        static int conv_pre = -2;
+        if (conv_pre == -2) { const char *e = getenv("DFQ_CONV_PRE"); conv_pre = e ? atoi(e) : -1; }
+        const bool pre_q = conv_pre >= 0 ? (conv_pre != 0 && a.slabs >= 2) : (pre || (a.slabs >= 2 && a.tmem_cols >= 256));
+        if (pre_q) pw_i8_kernel<true, true, true><<<grid, kThreads, smem, stream>>>(a);
+        else pw_i8_kernel<false, true, true><<<grid, kThreads, smem, stream>>>(a);
+    } else if (false) {
         if (pre) pw_i8_kernel<true, true, true><<<grid, kThreads, smem, stream>>>(a);
         else pw_i8_kernel<false, true, true><<<grid, kThreads, smem, stream>>>(a);
     } else if (conv) {
