@@ -68,7 +68,11 @@ qinterp_kernel(const float *__restrict__ x, float *__restrict__ y, int C, int H,
     extern __shared__ float sm_dyn[];
     __shared__ float red[2 * kWarps];
     float *src = sm_dyn;                                          // [src_rows_max * W] quantised source rows
-    int2 *xtab = reinterpret_cast<int2 *>(sm_dyn + ((src_rows_max * W + 1) & ~1));      // [OW] {x0 | x1 << 16, l1x}
+    // [OW] {x0 | x1 << 16, l1x}, column ox at (ox % 4) * ceil(OW / 4) + ox / 4: lane L reads column base + 4 L + i, so
+    // the lanes of one load touch CONSECUTIVE entries (in column order they sat 32 bytes apart: 8-way bank conflicts,
+    // more shared-memory cycles than the four taps together)
+    int2 *xtab = reinterpret_cast<int2 *>(sm_dyn + ((src_rows_max * W + 1) & ~1));
+    const int xq = (OW + 3) >> 2;
     int b = blockIdx.x;
     const int bi = b % bands; b /= bands;
     const int c = b % C, n = b / C;
@@ -86,7 +90,7 @@ qinterp_kernel(const float *__restrict__ x, float *__restrict__ y, int C, int H,
     for (int ox = threadIdx.x; ox < OW; ox += kThreads) {
         int x0, x1; float l1;
         interp_index(ox, sx, W, align, x0, x1, l1);
-        xtab[ox] = make_int2(x0 | (x1 << 16), __float_as_int(l1));
+        xtab[(ox & 3) * xq + (ox >> 2)] = make_int2(x0 | (x1 << 16), __float_as_int(l1));
     }
     __syncthreads();
     float *dst = y + ((int64_t)n * C + c) * OH * OW + (int64_t)r0 * OW;
@@ -105,7 +109,7 @@ qinterp_kernel(const float *__restrict__ x, float *__restrict__ y, int C, int H,
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
             if (j0 + i < ja || j0 + i >= jb) { v[i] = 0.0f; continue; }
-            const int2 e = xtab[ox];
+            const int2 e = xtab[(ox & 3) * xq + (ox >> 2)];
             const int x0 = e.x & 0xffff, x1 = e.x >> 16;
             const float l1x = __int_as_float(e.y), l0x = __fsub_rn(1.0f, l1x);
             const float top = __fadd_rn(__fmul_rn(l0x, s0[x0]), __fmul_rn(l1x, s0[x1]));
@@ -231,7 +235,7 @@ extern "C" int dfq_qinterp_bilinear_f32(const float *x, float *y, int64_t N, int
     if (band > OH) band = OH;
     auto rows_of = [&](int bd) { int r = (int)ceilf((float)bd * fmaxf(sy, 0.0f)) + 3; return r < H ? r : H; };
     const size_t budget = 96 * 1024;
-    auto smem_of = [&](int bd) { return (size_t)(((rows_of(bd) * W + 1) & ~1)) * 4 + (size_t)OW * 8; };
+    auto smem_of = [&](int bd) { return (size_t)(((rows_of(bd) * W + 1) & ~1)) * 4 + (size_t)(4 * ((OW + 3) / 4)) * 8; };
     while (band > 1 && smem_of(band) > budget) band = (band + 1) / 2;
     const size_t smem = smem_of(band);
     if (smem > 200 * 1024) return (int)cudaErrorInvalidValue;

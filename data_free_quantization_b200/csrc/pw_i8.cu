@@ -106,22 +106,29 @@ __device__ __forceinline__ uint32_t quant_code_bits(float x, const QuantConsts &
 __global__ void __launch_bounds__(kThreads)
 quant_nhwc_s8_kernel(const float *__restrict__ x, int8_t *__restrict__ q, const RangeSlot *slot, int bits, int C,
                      int HW, int Cp) {
-    __shared__ __align__(16) uint8_t tile[32][64 + 16];
-    const int tid = threadIdx.x, px = tid & 31, cl = tid >> 5;
-    const int p0 = blockIdx.x * 32, c0 = blockIdx.y * 64, n = blockIdx.z;
+    // 64 pixels x 64 channels per block: 16 coalesced fp32 loads in flight per thread, one 16-byte store per thread
+    __shared__ __align__(16) uint8_t tile[64][64 + 16];
+    const int tid = threadIdx.x, px = tid & 63, cl = tid >> 6;
+    const int p0 = blockIdx.x * 64, c0 = blockIdx.y * 64, n = blockIdx.z;
     const QuantConsts qc = consts_from_slot(*slot, bits, 0, 0.f, 0.f);
     const int sh = 8 - bits;
     const int p = p0 + px;
     const float *xn = x + ((int64_t)n * C) * HW;
+    float v[16];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-        const int c = c0 + cl + 8 * i;
+    for (int i = 0; i < 16; ++i) {
+        const int c = c0 + cl + 4 * i;
+        v[i] = (p < HW && c < C) ? __ldg(xn + (int64_t)c * HW + p) : 0.0f;
+    }
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+        const int c = c0 + cl + 4 * i;
         uint32_t b = 128u >> sh;
-        if (p < HW && c < C) b = quant_code_bits(__ldg(xn + (int64_t)c * HW + p), qc) & 0xffu;
-        tile[px][cl + 8 * i] = (uint8_t)(((b << sh) ^ 0x80u) & 0xffu);
+        if (p < HW && c < C) b = quant_code_bits(v[i], qc) & 0xffu;
+        tile[px][cl + 4 * i] = (uint8_t)(((b << sh) ^ 0x80u) & 0xffu);
     }
     __syncthreads();
-    if (tid < 128) {
+    {
         const int pp = tid >> 2, w = tid & 3;
         const int pg = p0 + pp, cb = c0 + 16 * w;
         if (pg < HW && cb < Cp)
@@ -862,7 +869,7 @@ extern "C" int dfq_conv_i8(const DfqConvI8Desc *d, void *stream) {
     a.dil = d->dil;
     if (d->scratch) {                       // quantise once, then every tap reads 16-byte code words
         const int Cp = a.cchunks * 16, HW = d->H * d->W;
-        dim3 grid((unsigned)((HW + 31) / 32), (unsigned)((Cp + 63) / 64), (unsigned)d->N);
+        dim3 grid((unsigned)((HW + 63) / 64), (unsigned)((Cp + 63) / 64), (unsigned)d->N);
         if (d->N > 65535 || grid.y > 65535) return (int)cudaErrorInvalidValue;
         quant_nhwc_s8_kernel<<<grid, kThreads, 0, (cudaStream_t)stream>>>(d->x, d->scratch, a.slot, d->bits, d->C, HW, Cp);
         g_launches += 1;
