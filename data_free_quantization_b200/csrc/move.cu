@@ -65,14 +65,12 @@ __global__ void __launch_bounds__(kThreads)
 qinterp_kernel(const float *__restrict__ x, float *__restrict__ y, int C, int H, int W, int OH, int OW, int align,
                float sy, float sx, int band, int bands, int src_rows_max, const RangeSlot *slot, int bits,
                unsigned *stats) {
-    extern __shared__ float sm_dyn[];
+    extern __shared__ __align__(16) float sm_dyn[];
     __shared__ float red[2 * kWarps];
     float *src = sm_dyn;                                          // [src_rows_max * W] quantised source rows
-    // [OW] {x0 | x1 << 16, l1x}, column ox at (ox % 4) * ceil(OW / 4) + ox / 4: lane L reads column base + 4 L + i, so
-    // the lanes of one load touch CONSECUTIVE entries (in column order they sat 32 bytes apart: 8-way bank conflicts,
-    // more shared-memory cycles than the four taps together)
-    int2 *xtab = reinterpret_cast<int2 *>(sm_dyn + ((src_rows_max * W + 1) & ~1));
-    const int xq = (OW + 3) >> 2;
+    // tables: per output column {x0 | x1 << 16, l1x}, per output row of the band {row offsets of y0 / y1, l1y}
+    int2 *xtab = reinterpret_cast<int2 *>(sm_dyn + ((src_rows_max * W + 3) & ~3));      // 16-byte aligned
+    int4 *ytab = reinterpret_cast<int4 *>(xtab + ((OW + 1) & ~1));
     int b = blockIdx.x;
     const int bi = b % bands; b /= bands;
     const int c = b % C, n = b / C;
@@ -90,46 +88,37 @@ qinterp_kernel(const float *__restrict__ x, float *__restrict__ y, int C, int H,
     for (int ox = threadIdx.x; ox < OW; ox += kThreads) {
         int x0, x1; float l1;
         interp_index(ox, sx, W, align, x0, x1, l1);
-        xtab[(ox & 3) * xq + (ox >> 2)] = make_int2(x0 | (x1 << 16), __float_as_int(l1));
+        xtab[ox] = make_int2(x0 | (x1 << 16), __float_as_int(l1));
+    }
+    for (int r = threadIdx.x; r < r1 - r0; r += kThreads) {
+        int y0, y1; float l1;
+        interp_index(r0 + r, sy, H, align, y0, y1, l1);
+        ytab[r] = make_int4((y0 - ys0) * W, (y1 - ys0) * W, __float_as_int(l1), 0);
     }
     __syncthreads();
+    // One output per thread and step, lanes on CONSECUTIVE outputs of the band's flat run: the column table is read
+    // conflict-free, the row table as a broadcast, the store is a coalesced 4-byte store whatever the row length (the
+    // previous form gave a thread 4 adjacent outputs for a 16-byte store: 86 thread-instructions per output, 87 %
+    // issue-active -- ncu, profiles/r1zz_move_ncu.md).  (row, column) advance by a fixed step, no division.
     float *dst = y + ((int64_t)n * C + c) * OH * OW + (int64_t)r0 * OW;
     const int count = (r1 - r0) * OW;
-    const int m = (int)((((uintptr_t)dst) >> 2) & 3);             // dst - m is 16-byte aligned
-    const int j_end = m + count;
+    const int dq = kThreads / OW, dr = kThreads - dq * OW;
+    int row = (int)threadIdx.x / OW, ox = (int)threadIdx.x - row * OW;
     float lo = INFINITY, hi = -INFINITY;
-    for (int j0 = 4 * (int)threadIdx.x; j0 < j_end; j0 += 4 * kThreads) {
-        const int ja = max(j0, m), jb = min(j0 + 4, j_end);
-        int row = (ja - m) / OW, ox = (ja - m) - row * OW;
-        int y0, y1; float l1y;
-        interp_index(r0 + row, sy, H, align, y0, y1, l1y);
-        const float *s0 = src + (y0 - ys0) * W, *s1 = src + (y1 - ys0) * W;
-        float l0y = __fsub_rn(1.0f, l1y);
-        float v[4];
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            if (j0 + i < ja || j0 + i >= jb) { v[i] = 0.0f; continue; }
-            const int2 e = xtab[(ox & 3) * xq + (ox >> 2)];
-            const int x0 = e.x & 0xffff, x1 = e.x >> 16;
-            const float l1x = __int_as_float(e.y), l0x = __fsub_rn(1.0f, l1x);
-            const float top = __fadd_rn(__fmul_rn(l0x, s0[x0]), __fmul_rn(l1x, s0[x1]));
-            const float bot = __fadd_rn(__fmul_rn(l0x, s1[x0]), __fmul_rn(l1x, s1[x1]));
-            v[i] = __fadd_rn(__fmul_rn(l0y, top), __fmul_rn(l1y, bot));
-            lo = fminf(lo, v[i]); hi = fmaxf(hi, v[i]);
-            if (++ox == OW) {                                     // next row of the band
-                ox = 0; ++row;
-                interp_index(min(r0 + row, OH - 1), sy, H, align, y0, y1, l1y);
-                s0 = src + (y0 - ys0) * W; s1 = src + (y1 - ys0) * W;
-                l0y = __fsub_rn(1.0f, l1y);
-            }
-        }
-        if (ja == j0 && jb == j0 + 4) {
-            *reinterpret_cast<float4 *>(dst - m + j0) = make_float4(v[0], v[1], v[2], v[3]);
-        } else {
-#pragma unroll
-            for (int i = 0; i < 4; ++i)
-                if (j0 + i >= ja && j0 + i < jb) dst[j0 + i - m] = v[i];
-        }
+    for (int j = threadIdx.x; j < count; j += kThreads) {
+        const int2 e = xtab[ox];
+        const int4 yy = ytab[row];
+        const int x0 = e.x & 0xffff, x1 = e.x >> 16;
+        const float l1x = __int_as_float(e.y), l0x = __fsub_rn(1.0f, l1x);
+        const float l1y = __int_as_float(yy.z), l0y = __fsub_rn(1.0f, l1y);
+        const float *s0 = src + yy.x, *s1 = src + yy.y;
+        const float top = __fadd_rn(__fmul_rn(l0x, s0[x0]), __fmul_rn(l1x, s0[x1]));
+        const float bot = __fadd_rn(__fmul_rn(l0x, s1[x0]), __fmul_rn(l1x, s1[x1]));
+        const float v = __fadd_rn(__fmul_rn(l0y, top), __fmul_rn(l1y, bot));
+        dst[j] = v;
+        lo = fminf(lo, v); hi = fmaxf(hi, v);
+        ox += dr; row += dq;
+        if (ox >= OW) { ox -= OW; ++row; }
     }
     if (stats) stats_flush(stats, n, lo, hi, red);
 }
@@ -235,7 +224,7 @@ extern "C" int dfq_qinterp_bilinear_f32(const float *x, float *y, int64_t N, int
     if (band > OH) band = OH;
     auto rows_of = [&](int bd) { int r = (int)ceilf((float)bd * fmaxf(sy, 0.0f)) + 3; return r < H ? r : H; };
     const size_t budget = 96 * 1024;
-    auto smem_of = [&](int bd) { return (size_t)(((rows_of(bd) * W + 1) & ~1)) * 4 + (size_t)(4 * ((OW + 3) / 4)) * 8; };
+    auto smem_of = [&](int bd) { return (size_t)(((rows_of(bd) * W + 3) & ~3)) * 4 + (size_t)((OW + 1) & ~1) * 8 + (size_t)bd * 16; };
     while (band > 1 && smem_of(band) > budget) band = (band + 1) / 2;
     const size_t smem = smem_of(band);
     if (smem > 200 * 1024) return (int)cudaErrorInvalidValue;
