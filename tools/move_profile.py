@@ -26,7 +26,8 @@ def main():
         ms = sorted(ts)[len(ts) // 2]
         print(f"{name:44s} {ms:7.4f} ms  {nbytes / ms / 1e6:8.1f} GB/s (algorithmic, L2 flushed)")
 
-    for C, H, OH, st in ((256, 33, 129, True), (21, 129, 513, False), (256, 1, 33, True)):
+    for C, H, OH, st in ((256, 33, 129, True), (21, 129, 513, False), (256, 1, 33, True), (256, 32, 128, True),
+                         (21, 128, 512, False)):
         x = torch.randn(N, C, H, H, device=dev)
         y = torch.empty(N, C, OH, OH, device=dev)
         args = (x.data_ptr(), y.data_ptr(), N, C, H, H, OH, OH, 1, slot.data_ptr(), 8, stats.data_ptr() if st else None)
