@@ -76,18 +76,18 @@ class DfqPwI8Desc(ctypes.Structure):
     _fields_ = [("x", c_void), ("y", c_void), ("wpk", c_void), ("wr", c_void), ("bias", c_void), ("in_slot", c_void),
                 ("out_stats", c_void), ("G", i64), ("xs_n", i64), ("xs_k", i64), ("xs_p", i64), ("ys_n", i64),
                 ("ys_o", i64), ("ys_p", i64), ("P", i32), ("K", i32), ("O", i32), ("bits", i32), ("relu", i32),
-                ("s_w", f32), ("c_w", f32), ("reserved", i32)]
+                ("s_w", f32), ("c_w", f32), ("o_cap", i32)]
 
 
 class DfqConvI8Desc(ctypes.Structure):
     _fields_ = [("x", c_void), ("y", c_void), ("wpk", c_void), ("wr", c_void), ("wrt", c_void), ("bias", c_void),
                 ("in_slot", c_void), ("out_stats", c_void)] + \
                [(k, i32) for k in ("N", "C", "H", "W", "O", "OH", "OW", "kh", "kw", "stride", "pad", "dil", "bits",
-                                   "relu")] + [("s_w", f32), ("c_w", f32), ("scratch", c_void)]
+                                   "relu")] + [("s_w", f32), ("c_w", f32), ("scratch", c_void), ("o_cap", i32), ("reserved", i32)]
 
 
 Q_SYMMETRIC, Q_RANGE_F32, Q_PER_CHANNEL, Q_CLAMP_OUT = 1, 2, 4, 8
-ABI_VERSION = 11
+ABI_VERSION = 12
 
 # every symbol include/dfq_b200.h declares: (restype, argtypes)
 P = ctypes.POINTER
@@ -119,6 +119,9 @@ PROTOTYPES = {
     "dfq_pw_i8_plan_host": (ctypes.c_int, [ctypes.c_int, ctypes.c_int, P(ctypes.c_int), P(ctypes.c_int),
                                            P(ctypes.c_int), P(ctypes.c_int), P(i64)]),
     "dfq_pw_i8_pack_host": (ctypes.c_int, [c_void, ctypes.c_int, ctypes.c_int, c_void]),
+    "dfq_pw_i8_plan_cap_host": (ctypes.c_int, [ctypes.c_int, ctypes.c_int, ctypes.c_int, P(ctypes.c_int),
+                                               P(ctypes.c_int), P(ctypes.c_int), P(ctypes.c_int), P(i64)]),
+    "dfq_pw_i8_pack_cap_host": (ctypes.c_int, [c_void, ctypes.c_int, ctypes.c_int, ctypes.c_int, c_void]),
     "dfq_pw_i8": (ctypes.c_int, [P(DfqPwI8Desc), c_void]),
     "dfq_conv_i8_k_host": (ctypes.c_int, [ctypes.c_int, ctypes.c_int, ctypes.c_int]),
     "dfq_conv_i8_scratch_bytes": (i64, [ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int]),

@@ -719,10 +719,14 @@ using namespace dfq;
 
 // Split of the output channels into passes of <= 256 (one UMMA N each, padded to a multiple of 16) and the K
 // padding to whole 64-byte slabs.  packed_bytes = n_pass * slabs * npass * 64.
-extern "C" int dfq_pw_i8_plan_host(int O, int K, int *n_pass, int *o_per_pass, int *npass, int *slabs,
-                                   int64_t *packed_bytes) {
-    if (O <= 0 || K <= 0) return (int)cudaErrorInvalidValue;
-    int np = (O + 255) / 256;
+// o_cap: most output channels one pass (= one CTA's accumulator) may hold, 16..256 (0 = 256).  A narrower pass means
+// more CTAs for the same layer -- the A tile is quantised once per pass, so it only pays when the default grid
+// leaves SMs idle (the 256 x 1280 -> 1000 classifier is 2 tiles x 4 passes = 8 CTAs at 256 channels per pass).
+static int plan_cap(int O, int K, int o_cap, int *n_pass, int *o_per_pass, int *npass, int *slabs,
+                    int64_t *packed_bytes) {
+    if (O <= 0 || K <= 0 || o_cap < 0) return (int)cudaErrorInvalidValue;
+    int cap = (o_cap == 0 || o_cap > 256) ? 256 : (o_cap < 16 ? 16 : o_cap / 16 * 16);
+    int np = (O + cap - 1) / cap;
     int opp = ((O + np - 1) / np + 15) / 16 * 16;
     np = (O + opp - 1) / opp;
     *n_pass = np; *o_per_pass = opp; *npass = opp;
@@ -730,12 +734,24 @@ extern "C" int dfq_pw_i8_plan_host(int O, int K, int *n_pass, int *o_per_pass, i
     *packed_bytes = (int64_t)np * *slabs * opp * kI8Slab;
     return 0;
 }
+extern "C" int dfq_pw_i8_plan_host(int O, int K, int *n_pass, int *o_per_pass, int *npass, int *slabs,
+                                   int64_t *packed_bytes) {
+    return plan_cap(O, K, 0, n_pass, o_per_pass, npass, slabs, packed_bytes);
+}
+extern "C" int dfq_pw_i8_plan_cap_host(int O, int K, int o_cap, int *n_pass, int *o_per_pass, int *npass, int *slabs,
+                                       int64_t *packed_bytes) {
+    return plan_cap(O, K, o_cap, n_pass, o_per_pass, npass, slabs, packed_bytes);
+}
 
 // codes: [O, K] centred weight codes (code - 128) on the host.  packed: the layout the kernel's bulk copies read,
 // [pass][slab][K chunk of 16][row within pass][16 B], zero padded (a zero code adds nothing to the dot product).
+extern "C" int dfq_pw_i8_pack_cap_host(const int8_t *codes, int O, int K, int o_cap, int8_t *packed);
 extern "C" int dfq_pw_i8_pack_host(const int8_t *codes, int O, int K, int8_t *packed) {
+    return dfq_pw_i8_pack_cap_host(codes, O, K, 0, packed);
+}
+extern "C" int dfq_pw_i8_pack_cap_host(const int8_t *codes, int O, int K, int o_cap, int8_t *packed) {
     int np, opp, npass, slabs; int64_t bytes;
-    int e = dfq_pw_i8_plan_host(O, K, &np, &opp, &npass, &slabs, &bytes);
+    int e = plan_cap(O, K, o_cap, &np, &opp, &npass, &slabs, &bytes);
     if (e) return e;
     for (int64_t i = 0; i < bytes; ++i) packed[i] = 0;
     for (int o = 0; o < O; ++o) {
@@ -828,7 +844,7 @@ extern "C" int dfq_pw_i8(const DfqPwI8Desc *d, void *stream) {
         return (int)cudaErrorInvalidValue;
     PwI8Args a = {};
     int64_t bytes;
-    int e = dfq_pw_i8_plan_host(d->O, d->K, &a.n_pass, &a.o_per_pass, &a.npass, &a.slabs, &bytes);
+    int e = plan_cap(d->O, d->K, d->o_cap, &a.n_pass, &a.o_per_pass, &a.npass, &a.slabs, &bytes);
     if (e) return e;
     a.x = d->x; a.y = d->y; a.wpk = d->wpk; a.wr = d->wr; a.bias = d->bias; a.slot = (const RangeSlot *)d->in_slot;
     a.stats = d->out_stats; a.G = d->G;
@@ -857,7 +873,7 @@ extern "C" int dfq_conv_i8(const DfqConvI8Desc *d, void *stream) {
     PwI8Args a = {};
     int64_t bytes;
     a.taps = d->kh * d->kw; a.cchunks = (d->C + 15) / 16; a.K = a.taps * a.cchunks * 16; a.Kreal = a.taps * d->C;
-    int e = dfq_pw_i8_plan_host(d->O, a.K, &a.n_pass, &a.o_per_pass, &a.npass, &a.slabs, &bytes);
+    int e = plan_cap(d->O, a.K, d->o_cap, &a.n_pass, &a.o_per_pass, &a.npass, &a.slabs, &bytes);
     if (e) return e;
     a.x = d->x; a.y = d->y; a.wpk = d->wpk; a.wr = d->wr; a.wrt = d->wrt; a.bias = d->bias;
     a.slot = (const RangeSlot *)d->in_slot; a.stats = d->out_stats;

@@ -12,21 +12,34 @@ from . import _lib as L
 class PackedWeight:
     """Weights of one layer on an integer grid: w[o,k] = s_w * code[o,k] + min_w, code in [0, 2^bits - 1]."""
 
-    def __init__(self, wpk, wr, s_w, c_w, O, K, codes):
+    def __init__(self, wpk, wr, s_w, c_w, O, K, codes, o_cap=0):
         self.wpk, self.wr, self.s_w, self.c_w, self.O, self.K, self.codes = wpk, wr, s_w, c_w, O, K, codes
+        self.o_cap = int(o_cap)        # output channels per pass the layout was packed for (0 = 256)
 
 
-def pack_weight(w, bits=None):
+def choose_o_cap(G, O, sms=148):
+    """Output channels per pass (dfq_pw_i8_plan_cap_host) for a layer of G pixels x O channels.  The default, 256,
+    gives ceil(G / 128) * ceil(O / 256) CTAs; when that leaves SMs idle the passes are narrowed until about two CTAs
+    per SM exist.  Every pass quantises its own copy of the A tile, so full grids keep the default."""
+    tiles = (int(G) + 127) // 128
+    if tiles * ((O + 255) // 256) >= sms:
+        return 0
+    n_pass = min((2 * sms + tiles - 1) // tiles, (O + 15) // 16)
+    cap = ((O + n_pass - 1) // n_pass + 15) // 16 * 16
+    return 0 if cap >= 256 else max(16, cap)
+
+
+def pack_weight(w, bits=None, o_cap=0):
     """pack_weight_bits for the layer's weight width, or -- QuantN* layers do not record one -- for the widest grid
     of <= 8 bits the tensor sits on."""
     for b in ([bits] if bits else (8, 7, 6, 5, 4, 3, 2)):
-        pk = pack_weight_bits(w, int(b))
+        pk = pack_weight_bits(w, int(b), o_cap)
         if pk is not None:
             return pk
     return None
 
 
-def pack_weight_bits(w, bits=8):
+def pack_weight_bits(w, bits=8, o_cap=0):
     """Recover the integer codes of an already fake-quantised weight (what quantize_targ_layer stored,
     utils/layer_transform.py:288-305, or what QuantConv2d derives per forward, utils/quantize.py:227) and lay them
     out for the kernel.  Returns None when the tensor is not on a `bits`-bit grid (then the fp32 kernel applies)."""
@@ -49,16 +62,17 @@ def pack_weight_bits(w, bits=8):
     codes = ((q - 2 ** (bits - 1)) * up).to(torch.int8).cpu().numpy()
     n_pass, opp, npass, slabs, nbytes = (ctypes.c_int(), ctypes.c_int(), ctypes.c_int(), ctypes.c_int(), L.i64())
     lib = L.lib()
-    L.check(lib.dfq_pw_i8_plan_host(O, K, ctypes.byref(n_pass), ctypes.byref(opp), ctypes.byref(npass),
-                                    ctypes.byref(slabs), ctypes.byref(nbytes)), "dfq_pw_i8_plan_host")
+    L.check(lib.dfq_pw_i8_plan_cap_host(O, K, int(o_cap), ctypes.byref(n_pass), ctypes.byref(opp), ctypes.byref(npass),
+                                        ctypes.byref(slabs), ctypes.byref(nbytes)), "dfq_pw_i8_plan_cap_host")
     packed = np.empty(nbytes.value, dtype=np.int8)
     codes = np.ascontiguousarray(codes)
-    L.check(lib.dfq_pw_i8_pack_host(codes.ctypes.data, O, K, packed.ctypes.data), "dfq_pw_i8_pack_host")
+    L.check(lib.dfq_pw_i8_pack_cap_host(codes.ctypes.data, O, K, int(o_cap), packed.ctypes.data),
+            "dfq_pw_i8_pack_cap_host")
     s_eff = s32 / up
     wr = (codes.astype(np.int64).sum(1).astype(np.float64) * s_eff).astype(np.float32)
     dev = w.device
     pk = PackedWeight(torch.from_numpy(packed).to(dev), torch.from_numpy(wr).to(dev), s_eff,
-                      float(np.float32(lo + 2 ** (bits - 1) * s32)), O, K, codes)
+                      float(np.float32(lo + 2 ** (bits - 1) * s32)), O, K, codes, o_cap)
     pk.grid = (s32, lo, q.to(torch.int16).cpu().numpy())       # w = s * code + lo, code in [0, 2^bits - 1]
     return pk
 
@@ -71,6 +85,7 @@ def make_desc(x_ptr, y_ptr, pk, bias, slot_ptr, stats_ptr, images, P, relu, bits
     d.in_slot, d.out_stats = slot_ptr, stats_ptr
     d.K, d.O, d.bits, d.relu = pk.K, pk.O, int(bits), int(relu)
     d.s_w, d.c_w = pk.s_w, pk.c_w
+    d.o_cap = pk.o_cap
     if linear:
         d.G, d.P = images, 1
         d.xs_n, d.xs_k, d.xs_p, d.ys_n, d.ys_o, d.ys_p = pk.K, 1, 0, pk.O, 1, 0
@@ -85,7 +100,7 @@ def launch(desc):
 
 
 # ---- dense k x k convolutions (csrc/pw_i8.cu, kConv; dfq_conv_i8) --------------------------------------------------
-def pack_weight_conv(w, bits=None):
+def pack_weight_conv(w, bits=None, o_cap=0):
     """pack_weight for a dense [O, C, kh, kw] weight (groups == 1): the reduction runs tap-major with the channels
     padded to a multiple of 16 (dfq_conv_i8_k_host), plus the per-tap code sums the padding correction needs.
     Returns None when the tensor is not on a <= 8-bit grid."""
@@ -107,18 +122,19 @@ def pack_weight_conv(w, bits=None):
     lib = L.lib()
     assert K == lib.dfq_conv_i8_k_host(C, kh, kw)
     n_pass, opp, npass, slabs, nbytes = (ctypes.c_int(), ctypes.c_int(), ctypes.c_int(), ctypes.c_int(), L.i64())
-    L.check(lib.dfq_pw_i8_plan_host(O, K, ctypes.byref(n_pass), ctypes.byref(opp), ctypes.byref(npass),
-                                    ctypes.byref(slabs), ctypes.byref(nbytes)), "dfq_pw_i8_plan_host")
+    L.check(lib.dfq_pw_i8_plan_cap_host(O, K, int(o_cap), ctypes.byref(n_pass), ctypes.byref(opp), ctypes.byref(npass),
+                                        ctypes.byref(slabs), ctypes.byref(nbytes)), "dfq_pw_i8_plan_cap_host")
     packed = np.empty(nbytes.value, dtype=np.int8)
     lay = np.ascontiguousarray(lay.reshape(O, K))
-    L.check(lib.dfq_pw_i8_pack_host(lay.ctypes.data, O, K, packed.ctypes.data), "dfq_pw_i8_pack_host")
+    L.check(lib.dfq_pw_i8_pack_cap_host(lay.ctypes.data, O, K, int(o_cap), packed.ctypes.data),
+            "dfq_pw_i8_pack_cap_host")
     s_eff = s32 / up
     tap_sums = codes.astype(np.int64).sum(1)                                   # [O, taps]
     wr = (tap_sums.sum(1).astype(np.float64) * s_eff).astype(np.float32)
     wrt = np.ascontiguousarray((tap_sums.T.astype(np.float64) * s_eff).astype(np.float32))   # [taps, O]
     dev = w.device
     out = PackedWeight(torch.from_numpy(packed).to(dev), torch.from_numpy(wr).to(dev), s_eff,
-                       float(np.float32(lo + 2 ** (b - 1) * s32)), O, K, codes)
+                       float(np.float32(lo + 2 ** (b - 1) * s32)), O, K, codes, o_cap)
     out.wrt = torch.from_numpy(wrt).to(dev)
     out.geom = (C, kh, kw)
     out.grid = (s32, lo, q.to(torch.int16).cpu().numpy().reshape(O, C, kh, kw))
@@ -161,6 +177,7 @@ def make_conv_desc(x, y, pk, bias, slot_ptr, stats_ptr, stride, pad, dil, relu, 
     d.bits, d.relu = int(bits), int(relu)
     d.s_w, d.c_w = pk.s_w, pk.c_w
     d.scratch = None if scratch is None else scratch.data_ptr()
+    d.o_cap = pk.o_cap
     return d
 
 

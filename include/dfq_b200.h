@@ -23,7 +23,7 @@
 extern "C" {
 #endif
 
-#define DFQ_ABI_VERSION 11
+#define DFQ_ABI_VERSION 12
 
 #if defined(__GNUC__)
 #pragma GCC visibility push(default)   /* the library is built with -fvisibility=hidden */
@@ -255,10 +255,16 @@ typedef struct DfqPwI8Desc {
     int64_t xs_n, xs_k, xs_p, ys_n, ys_o, ys_p;   /* element strides                          */
     int32_t P, K, O, bits, relu;
     float s_w, c_w;          /* weight scale and centred offset min_w + 128 * s_w             */
-    int32_t reserved;
+    int32_t o_cap;           /* the o_cap wpk was packed with (0 = 256 channels per pass)      */
 } DfqPwI8Desc;
 int dfq_pw_i8_plan_host(int O, int K, int *n_pass, int *o_per_pass, int *npass, int *slabs, int64_t *packed_bytes);
 int dfq_pw_i8_pack_host(const int8_t *codes_host, int O, int K, int8_t *packed_host);
+/* The same with at most o_cap (16..256, 0 = 256) output channels per pass: a pass is one CTA's accumulator, so a
+ * narrower pass spreads a layer with few pixel tiles over more SMs (the 1280 -> 1000 classifier at batch 256 is
+ * 2 tiles: 8 CTAs at 256 channels per pass, 126 at 16).  Desc.o_cap must repeat the value used for packing. */
+int dfq_pw_i8_plan_cap_host(int O, int K, int o_cap, int *n_pass, int *o_per_pass, int *npass, int *slabs,
+                            int64_t *packed_bytes);
+int dfq_pw_i8_pack_cap_host(const int8_t *codes_host, int O, int K, int o_cap, int8_t *packed_host);
 int dfq_pw_i8(const DfqPwI8Desc *desc_host, void *stream);
 
 /* Dense k x k convolution of the same forward (groups == 1; DeepLab's atrous 3x3 and decoder convolutions,
@@ -281,6 +287,8 @@ typedef struct DfqConvI8Desc {
     float s_w, c_w;
     int8_t *scratch;         /* NULL, or dfq_conv_i8_scratch_bytes(N, C, H, W) device bytes: the input is then
                               * quantised ONCE into s8 NHWC codes and every tap reads 16-byte words (k x k > 1) */
+    int32_t o_cap;           /* the o_cap wpk was packed with (0 = 256 channels per pass)       */
+    int32_t reserved;
 } DfqConvI8Desc;
 int dfq_conv_i8_k_host(int C, int kh, int kw);
 int64_t dfq_conv_i8_scratch_bytes(int N, int C, int H, int W);

@@ -35,7 +35,7 @@ def test_struct_sizes_match_header_layout():
     assert ctypes.sizeof(L.DfqAbsorbPair) == 80
     assert ctypes.sizeof(L.DfqCorrDesc) == 104
     assert ctypes.sizeof(L.DfqPwI8Desc) == 144
-    assert ctypes.sizeof(L.DfqConvI8Desc) == 136
+    assert ctypes.sizeof(L.DfqConvI8Desc) == 144
 
 
 def test_host_quant_params_match_oracle(oracle):

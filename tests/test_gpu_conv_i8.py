@@ -16,7 +16,7 @@ DEV = "cuda:0"
 
 
 def _case(oracle, N, C, O, H, W, k=3, stride=1, pad=1, dil=1, relu=True, bias=True, wbits=8, abits=8, seed=0,
-          once=False):
+          once=False, o_cap=0):
     from data_free_quantization_b200 import pw_i8
     rs = np.random.default_rng(seed)
     x = (rs.standard_normal((N, C, H, W)) * 1.5 + 0.3).astype(np.float32)
@@ -31,7 +31,7 @@ def _case(oracle, N, C, O, H, W, k=3, stride=1, pad=1, dil=1, relu=True, bias=Tr
                      None if tb is None else tb.double(), stride, pad, dil).numpy()
     if relu:
         want32, exact = torch.relu(want32), np.maximum(exact, 0)
-    pk = pw_i8.pack_weight_conv(torch.from_numpy(w).to(DEV), wbits)
+    pk = pw_i8.pack_weight_conv(torch.from_numpy(w).to(DEV), wbits, o_cap=o_cap)
     assert pk is not None, "quantised weight not recognised as on-grid"
     xd = torch.from_numpy(x).to(DEV)
     y = torch.full(tuple(want32.shape), float("nan"), device=DEV)
@@ -66,6 +66,13 @@ def _case(oracle, N, C, O, H, W, k=3, stride=1, pad=1, dil=1, relu=True, bias=Tr
 @pytest.mark.parametrize("once", [False, True])
 def test_dense_conv(oracle, N, C, O, H, W, k, stride, pad, dil, once):
     _case(oracle, N, C, O, H, W, k, stride, pad, dil, once=once)
+
+
+@pytest.mark.parametrize("o_cap", [32, 96, 128])
+def test_dense_conv_narrow_passes(oracle, o_cap):
+    """ASPP branch with fewer output channels per pass (137 pixel tiles at 16 x 33 x 33 do not fill 148 SMs)."""
+    _case(oracle, 1, 320, 256, 33, 33, 3, 1, 12, 12, once=True, o_cap=o_cap)
+    _case(oracle, 2, 16, 40, 12, 12, 3, 1, 1, 1, once=False, o_cap=o_cap, seed=o_cap)
 
 
 def test_no_relu_no_bias_low_bits(oracle):

@@ -14,7 +14,7 @@ pytestmark = pytest.mark.gpu
 DEV = "cuda:0"
 
 
-def _case(oracle, images, K, O, H, W, linear=False, relu=True, bias=True, wbits=8, abits=8, seed=0):
+def _case(oracle, images, K, O, H, W, linear=False, relu=True, bias=True, wbits=8, abits=8, seed=0, o_cap=0):
     from data_free_quantization_b200 import pw_i8
     rs = np.random.default_rng(seed)
     P = 1 if linear else H * W
@@ -35,7 +35,7 @@ def _case(oracle, images, K, O, H, W, linear=False, relu=True, bias=True, wbits=
     sx = float(slot[2])
     qa = np.rint((xq.astype(np.float64) - lo) / sx).astype(np.int64)
     wd = torch.from_numpy(w).to(DEV)
-    pk = pw_i8.pack_weight(wd, wbits)
+    pk = pw_i8.pack_weight(wd, wbits, o_cap=o_cap)
     assert pk is not None, "quantised weight not recognised as on-grid"
     sw, mw, qb = pk.grid
     qb = qb.astype(np.int64)
@@ -87,6 +87,22 @@ def test_pointwise_no_relu_no_bias(oracle):
 
 def test_linear_classifier(oracle):
     _case(oracle, 5, 1280, 1000, 1, 1, linear=True, relu=False)
+
+
+@pytest.mark.parametrize("o_cap", [16, 48, 128, 250])
+def test_narrow_passes(oracle, o_cap):
+    """dfq_pw_i8_plan_cap_host: the same layer packed with fewer output channels per pass (more CTAs for layers whose
+    pixel tiles do not fill the SMs) -- the classifier (63 passes of 16 at o_cap = 16) and a 7 x 7 projection."""
+    _case(oracle, 5, 1280, 1000, 1, 1, linear=True, relu=False, o_cap=o_cap)
+    _case(oracle, 3, 960, 160, 7, 7, seed=o_cap, o_cap=o_cap)
+
+
+def test_choose_o_cap():
+    from data_free_quantization_b200.pw_i8 import choose_o_cap
+    assert choose_o_cap(256 * 112 * 112, 96) == 0            # full grids keep 256 channels per pass
+    assert choose_o_cap(256, 1000) == 16                     # classifier at batch 256: 2 tiles -> 63 passes
+    assert choose_o_cap(256 * 49, 160) in (48, 64)           # 98 tiles -> 3-4 passes
+    assert choose_o_cap(16 * 33 * 33, 256) == 96             # ASPP at 16 x 33 x 33: 137 tiles -> 3 passes
 
 
 def test_linear_many_samples(oracle):
