@@ -162,7 +162,10 @@ __device__ __forceinline__ float tap_corr(const float *tap_c, uint32_t oob, int 
 // [N][H][W][C padded to 16], so a K chunk is one aligned 16-byte word of the tap's pixel: the producer is a 128-bit
 // load, four dp4a for the code sum and the shared-memory store -- instead of 16 fp32 loads and 16 quantiser
 // evaluations per tap (9x the same activation for a 3 x 3 kernel).
-template <bool kPre, bool kConv, bool kQ>
+// kLin: the activation is row-major [G][K] with K contiguous (a linear layer): a thread's 16-float chunk is four
+// 128-bit loads.  As 16 scalar loads the 32 lanes of every load instruction hit 32 different lines -- the LSU, not
+// the latency, set the classifier's 7.5 us per slab (256 x 1280 -> 1000: 0.153 ms for 20 slabs).
+template <bool kPre, bool kConv, bool kQ, bool kLin = false>
 __global__ void __launch_bounds__(kThreads, kPre ? 3 : 4)
 pw_i8_kernel(PwI8Args a) {
     extern __shared__ __align__(128) uint8_t smem[];
@@ -265,7 +268,15 @@ pw_i8_kernel(PwI8Args a) {
             } else {
                 bool live, inb; const float *px; int nch;
                 chunk_src(s * 4 + h + 2 * c, live, inb, px, nch);
-                if (live) {                                           // warp-uniform: padded chunks cost nothing
+                if (kLin && live && inb && nch >= 16) {               // (rows past the end / a ragged last chunk: below)
+                    const float4 *p4 = reinterpret_cast<const float4 *>(px);
+#pragma unroll
+                    for (int j4 = 0; j4 < 4; ++j4) {
+                        const float4 t = __ldg(p4 + j4);
+                        v[c][kQ ? 0 : 4 * j4] = t.x; v[c][kQ ? 0 : 4 * j4 + 1] = t.y;
+                        v[c][kQ ? 0 : 4 * j4 + 2] = t.z; v[c][kQ ? 0 : 4 * j4 + 3] = t.w;
+                    }
+                } else if (live) {                                    // warp-uniform: padded chunks cost nothing
 #pragma unroll
                     for (int j = 0; j < 16; ++j) v[c][kQ ? 0 : j] = (inb && j < nch) ? __ldg(px + j * xs_k) : 0.0f;
                 }
@@ -774,7 +785,9 @@ static int pw_i8_launch(PwI8Args &a, bool conv, int64_t G, cudaStream_t stream) 
     if (!attr_set) {
         const void *fns[] = {(const void *)pw_i8_kernel<false, false, false>, (const void *)pw_i8_kernel<true, false, false>,
                              (const void *)pw_i8_kernel<false, true, false>, (const void *)pw_i8_kernel<true, true, false>,
-                             (const void *)pw_i8_kernel<false, true, true>, (const void *)pw_i8_kernel<true, true, true>};
+                             (const void *)pw_i8_kernel<false, true, true>, (const void *)pw_i8_kernel<true, true, true>,
+                             (const void *)pw_i8_kernel<false, false, false, true>,
+                             (const void *)pw_i8_kernel<true, false, false, true>};
         for (const void *fn : fns) {
             cudaError_t ce = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
             if (ce != cudaSuccess) return (int)ce;
@@ -831,6 +844,10 @@ static int pw_i8_launch(PwI8Args &a, bool conv, int64_t G, cudaStream_t stream) 
     } else if (conv) {
         if (pre) pw_i8_kernel<true, true, false><<<grid, kThreads, smem, stream>>>(a);
         else pw_i8_kernel<false, true, false><<<grid, kThreads, smem, stream>>>(a);
+    } else if (a.xs_k == 1 && a.K % 4 == 0 && a.xs_n % 4 == 0 && (a.P == 1 || a.xs_p % 4 == 0) &&
+               ((uintptr_t)a.x & 15) == 0) {                           // K-contiguous rows, 16-byte aligned chunks
+        if (pre) pw_i8_kernel<true, false, false, true><<<grid, kThreads, smem, stream>>>(a);
+        else pw_i8_kernel<false, false, false, true><<<grid, kThreads, smem, stream>>>(a);
     } else {
         if (pre) pw_i8_kernel<true, false, false><<<grid, kThreads, smem, stream>>>(a);
         else pw_i8_kernel<false, false, false><<<grid, kThreads, smem, stream>>>(a);

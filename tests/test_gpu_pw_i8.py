@@ -109,6 +109,13 @@ def test_linear_many_samples(oracle):
     _case(oracle, 300, 128, 40, 1, 1, linear=True, relu=False, seed=5)
 
 
+@pytest.mark.parametrize("K", [130, 132, 200, 1280])
+def test_linear_row_loads(oracle, K):
+    """K-contiguous rows take four 128-bit loads per 16-float chunk when K % 4 == 0 (ragged last chunk scalar:
+    K = 132, 200), the scalar form otherwise (K = 130)."""
+    _case(oracle, 257, K, 48, 1, 1, linear=True, relu=False, seed=K)
+
+
 @pytest.mark.parametrize("wbits,abits", [(4, 8), (6, 8), (8, 4)])
 def test_low_bit_grids(oracle, wbits, abits):
     _case(oracle, 2, 64, 48, 14, 14, wbits=wbits, abits=abits, seed=wbits * 10 + abits)
