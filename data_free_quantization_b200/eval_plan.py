@@ -55,11 +55,12 @@ class EvalPlan:
         quantise on load and reduce the output statistics themselves; "torch" = the comparator (our fake-quant into a
         temporary, the torch op, a separate statistics pass)."""
         self.move_impl = move_impl
-        # Narrower tensor-core passes for layers whose default grid leaves SMs idle (pw_i8.choose_o_cap): OPT-IN.
-        # Measured on B200: every pass re-quantises its A tile, and the producer, not the accumulator width, sets
-        # a CTA's time -- 576 -> 160 at 256 x 7 x 7 went 0.050 -> 0.074 ms with 4 passes of 48, DeepLab's pointwise
-        # layers 2.10 -> 2.27 ms; only the 8-CTA classifier gained (0.153 -> 0.135 ms).
-        self.narrow_passes = os.environ.get("DFQ_NARROW_PASSES", "0") != "0"
+        # Narrower tensor-core passes (pw_i8.choose_o_cap) for layers whose default grid leaves SMs idle.  Measured on
+        # B200: every pass re-quantises its A tile, and the producer, not the accumulator width, sets a CTA's time --
+        # narrowing EVERY under-filled layer made 576 -> 160 at 256 x 7 x 7 0.050 -> 0.074 ms (4 passes of 48) and
+        # DeepLab's pointwise layers 2.10 -> 2.27 ms; a layer of a handful of CTAs gains (the classifier, 2 tiles x 4
+        # passes: 0.100 -> 0.083 ms with 63 passes of 16).
+        self.narrow_passes = float(os.environ.get("DFQ_NARROW_PASSES", "0.25"))
         self.model, self.fxg = model, transformer.fx_graph
         self.dev = next(model.parameters()).device
         self.N = int(batch)
@@ -444,7 +445,8 @@ class EvalPlan:
         """Launch closure of the tensor-core kernel for this layer, or None when its weights are not on a grid."""
         from . import pw_i8
         pk = pw_i8.pack_weight(wq, getattr(m, "num_bits", None),
-                               o_cap=pw_i8.choose_o_cap(images * P, wq.shape[0]) if self.narrow_passes else 0)
+                               o_cap=pw_i8.choose_o_cap(images * P, wq.shape[0], fill=self.narrow_passes)
+                               if self.narrow_passes > 0 else 0)
         if pk is None:
             return None
         stats = None if out.stats is None else out.stats.data_ptr()
@@ -458,8 +460,9 @@ class EvalPlan:
         """Dense k x k convolution as tcgen05 implicit GEMM (dfq_conv_i8), or None when the weights are off-grid."""
         from . import pw_i8
         pk = pw_i8.pack_weight_conv(wq, getattr(m, "num_bits", None),
-                                    o_cap=pw_i8.choose_o_cap(out.numel // out.shape[1], wq.shape[0])
-                                    if self.narrow_passes else 0)
+                                    o_cap=pw_i8.choose_o_cap(out.numel // out.shape[1], wq.shape[0],
+                                                             fill=self.narrow_passes)
+                                    if self.narrow_passes > 0 else 0)
         if pk is None:
             return None
         stats = None if out.stats is None else out.stats.data_ptr()

@@ -17,12 +17,13 @@ class PackedWeight:
         self.o_cap = int(o_cap)        # output channels per pass the layout was packed for (0 = 256)
 
 
-def choose_o_cap(G, O, sms=148):
+def choose_o_cap(G, O, sms=148, fill=1.0):
     """Output channels per pass (dfq_pw_i8_plan_cap_host) for a layer of G pixels x O channels.  The default, 256,
     gives ceil(G / 128) * ceil(O / 256) CTAs; when that leaves SMs idle the passes are narrowed until about two CTAs
-    per SM exist.  Every pass quantises its own copy of the A tile, so full grids keep the default."""
+    per SM exist.  Every pass quantises its own copy of the A tile, so full grids keep the default; `fill` is the
+    fraction of the SMs the default grid must cover to be left alone."""
     tiles = (int(G) + 127) // 128
-    if tiles * ((O + 255) // 256) >= sms:
+    if tiles * ((O + 255) // 256) >= fill * sms:
         return 0
     n_pass = min((2 * sms + tiles - 1) // tiles, (O + 15) // 16)
     cap = ((O + n_pass - 1) // n_pass + 15) // 16 * 16
