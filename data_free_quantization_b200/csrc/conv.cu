@@ -842,12 +842,31 @@ qmean_kernel(const float *__restrict__ x, float *__restrict__ out, int C, int HW
     QuantConsts qc;
     if (slot) qc = consts_from_slot(*slot, bits, 0, 0.f, 0.f);
     float lo = INFINITY, hi = -INFINITY;
+    // planes of <= 64 pixels (7 x 7 at the end of MobileNetV2): the loads of the warp's 4 channels are issued
+    // together -- one channel at a time the warp waited out a memory round trip and a shuffle chain per channel
+    float pre[4][2];
+    const bool small = HW <= 64;
+    if (small) {
+#pragma unroll
+        for (int t = 0; t < 4; ++t) {
+            const int c = c0 + warp * 4 + t;
+            const float *p = x + ((int64_t)n * C + c) * HW;
+            pre[t][0] = (c < C && lane < HW) ? __ldg(p + lane) : 0.0f;
+            pre[t][1] = (c < C && lane + 32 < HW) ? __ldg(p + lane + 32) : 0.0f;
+        }
+    }
+#pragma unroll
     for (int t = 0; t < 4; ++t) {
         int c = c0 + warp * 4 + t;
         if (c >= C) break;
         const float *p = x + ((int64_t)n * C + c) * HW;
         float s = 0.0f;
-        for (int k = lane; k < HW; k += 32) s = __fadd_rn(s, quant_or_pass(__ldg(p + k), qc, slot));
+        if (small) {                                     // same order of additions as the loop below
+            if (lane < HW) s = __fadd_rn(s, quant_or_pass(pre[t][0], qc, slot));
+            if (lane + 32 < HW) s = __fadd_rn(s, quant_or_pass(pre[t][1], qc, slot));
+        } else {
+            for (int k = lane; k < HW; k += 32) s = __fadd_rn(s, quant_or_pass(__ldg(p + k), qc, slot));
+        }
         s = warp_sum(s);
         float m = __fdiv_rn(s, (float)HW);
         if (lane == 0) out[(int64_t)n * C + c] = m;
