@@ -2,14 +2,13 @@
 // with their operands fake-quantised on load (utils/layer_transform.py:98-125 route the operands of
 // F.interpolate / torch.cat through QuantMeasures first), and constant zero padding (utils/layer_transform.py
 // ignore_op=['pad']: recorded in the graph, never quantised).  Each is ONE pass: read the source once, write the
-// destination once with 128-bit stores, and reduce the per-sample min/max of what was written into the encoded
-// [N,2] table the next QuantMeasure consumes (utils/quantize.py:110-111) -- no quantised temporary, no separate
-// statistics pass.
+// destination once, and reduce the per-sample min/max of what was written into the encoded [N,2] table the next
+// QuantMeasure consumes (utils/quantize.py:110-111) -- no quantised temporary, no separate statistics pass.
 //
-// Planes of 129 x 129 or 513 x 513 floats are not 16-byte aligned, so the kernels address the destination of one
+// Planes of 129 x 129 or 513 x 513 floats are not 16-byte aligned, so cat and pad address the destination of one
 // sample as a FLAT run of floats: a block owns kChunk consecutive floats of the run (in a coordinate shifted so
-// that multiples of 4 are 16-byte aligned), a thread owns groups of 4 and decodes (plane, row, column) once per
-// group, then steps.
+// that multiples of 4 are 16-byte aligned), a thread owns groups of 4 (one 128-bit store) and decodes (plane, row,
+// column) once per group, then steps.  The interpolation works on bands of rows (see qinterp_kernel).
 #include "common.cuh"
 
 namespace dfq {
@@ -50,9 +49,7 @@ static inline int flat_chunks(int64_t count) { return (int)((count + 3 + kChunk 
 // run: it is read coalesced, quantised ONCE and kept in shared memory next to a per-column table {x0, x1, l1x}, so
 // an output costs four shared loads and the seven-operation blend (the first form of this kernel quantised its taps
 // per output and sent the one group per row that wraps to a per-element path: 120 thread-instructions per output,
-// half of every warp idle -- ncu, profiles/r1zz_move_ncu.md).  The band's destination is a flat run of floats
-// written as 16-byte words wherever the address allows; a group of four steps across a row end without leaving the
-// common path.
+// half of every warp idle -- ncu, profiles/r1zz_move_ncu.md).  The band's destination is a flat run of floats.
 __device__ __forceinline__ void interp_index(int o, float scale, int size, int align, int &i0, int &i1, float &l1) {
     const float s = align ? __fmul_rn(scale, (float)o)
                           : fmaxf(__fsub_rn(__fmul_rn(scale, __fadd_rn((float)o, 0.5f)), 0.5f), 0.0f);
