@@ -82,7 +82,11 @@ dwconv3x3_kernel(ConvArgs a) {
 // loads are conflict-free scalars (3 S + 2 D + 1 input rows x 3 taps = 18 loads for 36 FMAs at S = D = 1), global
 // stores are coalesced whatever the row length, and the 9 weights come from shared memory as broadcasts.  Same
 // accumulation order as dwconv3x3_kernel (bit-identical results).
-template <int S, int D>
+//
+// kWarp (small planes, a whole plane per channel): every WARP stages, synchronises (__syncwarp) and computes its own
+// channel, so the warps of a block drift apart and one warp's loads overlap another's arithmetic -- the block form
+// ran load phase / barrier / compute phase in lock-step on 33 x 33 planes (1.1-1.3 TB/s).
+template <int S, int D, bool kWarp>
 __global__ void __launch_bounds__(kThreads)
 dwconv3x3_valid_kernel(ConvArgs a) {
     extern __shared__ float smem[];
@@ -106,14 +110,17 @@ dwconv3x3_valid_kernel(ConvArgs a) {
     QuantConsts qc;
     if (on) qc = consts_from_slot(*a.slot, a.bits, 0, 0.f, 0.f);
     const bool fast4 = on && qc.fast;
-    for (int c = 0; c < nc; ++c) {
+    // the threads that share a channel set: the block, or one warp (channel c0 + warp)
+    const int gt = kWarp ? (tid & 31) : tid, gs = kWarp ? 32 : kThreads;
+    const int cbeg = kWarp ? (tid >> 5) : 0, cend = kWarp ? min((tid >> 5) + 1, nc) : nc;
+    for (int c = cbeg; c < cend; ++c) {
         const float *p = a.x + (((int64_t)n * a.C + c0 + c) * a.H + (int64_t)r0 * S) * a.W;
         const int m = (int)((((uintptr_t)p) >> 2) & 3);
         float *q = smem + c * plane_s + m;                        // q - m and p - m are 16-byte aligned
         const int j_end = m + plane;
         // groups of 4 floats in the shifted coordinate; two 128-bit loads in flight per thread
-        for (int j0 = 4 * tid; j0 < j_end; j0 += 8 * kThreads) {
-            const int j1 = j0 + 4 * kThreads;
+        for (int j0 = 4 * gt; j0 < j_end; j0 += 8 * gs) {
+            const int j1 = j0 + 4 * gs;
             const bool full0 = j0 >= m && j0 + 4 <= j_end, full1 = j1 >= m && j1 + 4 <= j_end;
             float4 t0 = make_float4(0.f, 0.f, 0.f, 0.f), t1 = t0;
             if (full0) t0 = __ldg(reinterpret_cast<const float4 *>(p - m + j0));
@@ -135,15 +142,15 @@ dwconv3x3_valid_kernel(ConvArgs a) {
             }
         }
     }
-    for (int i = tid; i < nc * 10; i += kThreads) {
+    for (int i = cbeg * 10 + gt; i < cend * 10; i += gs) {
         const int c = i / 10, t = i - c * 10;
         wsm[i] = t < 9 ? __ldg(a.w + (int64_t)(c0 + c) * 9 + t) : (a.bias ? __ldg(a.bias + c0 + c) : 0.0f);
     }
-    __syncthreads();
+    if (kWarp) __syncwarp(); else __syncthreads();
     float lo = INFINITY, hi = -INFINITY;
     const int ngroups = (nr + 3) >> 2, per_c = ngroups * a.OW;
     const float inv_per_c = 1.0f / (float)per_c, inv_OW = 1.0f / (float)a.OW;
-    for (int it = tid; it < nc * per_c; it += kThreads) {
+    for (int it = cbeg * per_c + gt; it < cend * per_c; it += gs) {
         int c = (int)(((float)it + 0.5f) * inv_per_c), rem = it - c * per_c;
         if (rem < 0) { --c; rem += per_c; } else if (rem >= per_c) { ++c; rem -= per_c; }
         int rg = (int)(((float)rem + 0.5f) * inv_OW), col = rem - rg * a.OW;
@@ -958,21 +965,31 @@ extern "C" int dfq_qconv2d_f32(const DfqConvDesc *d, void *stream) {
     }
     if (d->groups == d->C_in && d->C_in == d->C_out && d->kh == 3 && d->kw == 3 && d->pad == 0 &&
         ((d->stride == 1 && (d->dil == 1 || d->dil == 2)) || (d->stride == 2 && d->dil == 1))) {
-        // valid depthwise (DeepLab after F.pad): about 4096 outputs per block in row groups of 4, <= 48 KB of input
+        // valid depthwise (DeepLab after F.pad): about 4096 outputs per block in row groups of 4, <= 48 KB of input;
+        // planes of <= 2048 outputs: one plane per WARP, 8 channels per block
         const int S = d->stride, D = d->dil;
         int rows = OH, cb = 1;
-        if (OH * OW > 4096) rows = max(4, (4096 / OW) & ~3);
-        else cb = max(1, min(d->C_in, 4096 / (OH * OW)));
         auto smem_of = [&](int r, int c) { return ((size_t)c * ((((r - 1) * S + 2 * D + 1) * d->W + 6) & ~3) + (size_t)c * 10) * sizeof(float); };
+        bool warp_mode = OH * OW <= 2048 && d->C_in >= kWarps && smem_of(OH, kWarps) <= 48 * 1024;
+        if (warp_mode) cb = kWarps;
+        else if (OH * OW > 4096) rows = max(4, (4096 / OW) & ~3);
+        else cb = max(1, min(d->C_in, 4096 / (OH * OW)));
         while (smem_of(rows, cb) > 48 * 1024 && (cb > 1 || rows > 4)) { if (cb > 1) cb = (cb + 1) / 2; else rows = max(4, (rows / 2 + 3) & ~3); }
         if (smem_of(rows, cb) <= 48 * 1024) {
             a.rows = rows; a.cb = cb; a.strips = (OH + rows - 1) / rows;
             const int64_t blocks = (int64_t)d->N * ((d->C_in + cb - 1) / cb) * a.strips;
             if (blocks > 0x7fffffffll) return (int)cudaErrorInvalidValue;
             const size_t smem = smem_of(rows, cb);
-            if (S == 1 && D == 1) dwconv3x3_valid_kernel<1, 1><<<(unsigned)blocks, kThreads, smem, st>>>(a);
-            else if (S == 2) dwconv3x3_valid_kernel<2, 1><<<(unsigned)blocks, kThreads, smem, st>>>(a);
-            else dwconv3x3_valid_kernel<1, 2><<<(unsigned)blocks, kThreads, smem, st>>>(a);
+            const unsigned g = (unsigned)blocks;
+            if (warp_mode) {
+                if (S == 1 && D == 1) dwconv3x3_valid_kernel<1, 1, true><<<g, kThreads, smem, st>>>(a);
+                else if (S == 2) dwconv3x3_valid_kernel<2, 1, true><<<g, kThreads, smem, st>>>(a);
+                else dwconv3x3_valid_kernel<1, 2, true><<<g, kThreads, smem, st>>>(a);
+            } else {
+                if (S == 1 && D == 1) dwconv3x3_valid_kernel<1, 1, false><<<g, kThreads, smem, st>>>(a);
+                else if (S == 2) dwconv3x3_valid_kernel<2, 1, false><<<g, kThreads, smem, st>>>(a);
+                else dwconv3x3_valid_kernel<1, 2, false><<<g, kThreads, smem, st>>>(a);
+            }
             g_launches += 1;
             return (int)cudaGetLastError();
         }

@@ -75,7 +75,9 @@ def test_depthwise3x3(oracle, C, H, stride, N, quant):
 @pytest.mark.parametrize("C,H,W,stride,dil,N", [(32, 67, 67, 1, 1, 2), (96, 67, 67, 2, 1, 2), (144, 35, 35, 1, 1, 3),
                                                 (192, 37, 37, 1, 2, 2), (7, 9, 12, 1, 1, 1), (5, 10, 7, 2, 1, 2),
                                                 (3, 5, 5, 1, 2, 1), (16, 131, 131, 2, 1, 1), (8, 259, 259, 1, 1, 1),
-                                                (4, 300, 40, 1, 3, 1)])
+                                                (4, 300, 40, 1, 3, 1),
+                                                # one plane per warp (C >= 8, <= 2048 outputs), ragged last block
+                                                (16, 21, 21, 2, 1, 2), (20, 19, 23, 1, 1, 2), (12, 15, 15, 1, 2, 1)])
 @pytest.mark.parametrize("quant", [False, True])
 def test_depthwise3x3_valid(oracle, C, H, W, stride, dil, N, quant):
     """pad 0 (DeepLab pads with F.pad first, modeling/segmentation/backbone/mobilenet.py:16-22): the column-per-lane
