@@ -8,6 +8,7 @@
 //     statistics, utils/quantize.py:110-111) into an encoded [N,2] table with one atomic pair per block.
 // Accumulation is fp32 in a fixed order (not the reference's ATen order): parity is the 1e-3 logits tolerance.
 #include "common.cuh"
+#include <stdlib.h>
 
 namespace dfq {
 
@@ -470,8 +471,9 @@ struct DwColArgs {
     int G, K, wps;                       // planes side by side, planes in sequence, warps per image
 };
 
+constexpr int kColsPre = 16;           // planes of at most this many rows are loaded whole before use
 template <int S>
-__global__ void __launch_bounds__(kThreads, 4)
+__global__ void __launch_bounds__(kThreads, 3)
 dwconv3x3_cols_kernel(DwColArgs a) {
     __shared__ float red[2 * kWarps];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -501,7 +503,36 @@ dwconv3x3_cols_kernel(DwColArgs a) {
         auto valid = [&](int ir) { return active && ir >= 0 && ir < a.H && ir <= ir_last; };
         auto ld = [&](int ir) { return valid(ir) ? __ldg(xp + (int64_t)ir * a.W) : 0.0f; };
         auto q = [&](float v, int ir) { return (on && valid(ir)) ? quant_dequant(v, qc) : v; };
-        if (S == 1) {
+        if (S == 1 && a.H <= kColsPre) {
+            // short planes (14 x 14, 7 x 7): ALL rows of the plane are requested before the first is used -- with two
+            // rows of look-ahead a warp had ~60 instructions to cover a memory round trip
+            float pre[kColsPre + 1];
+#pragma unroll
+            for (int r = 0; r <= kColsPre; ++r) pre[r] = r < a.H ? ld(r) : 0.0f;
+            float t0 = 0.0f, t1 = q(pre[0], 0);                     // row -1 is padding
+            float tl = 0.0f, tr = 0.0f;
+            float ml = __shfl_up_sync(0xffffffffu, t1, 1), mr = __shfl_down_sync(0xffffffffu, t1, 1);
+            if (first) ml = 0.f;
+            if (last) mr = 0.f;
+#pragma unroll
+            for (int t = 0; t < kColsPre; ++t) {
+                if (t >= a.OH) break;
+                const float b1 = q(pre[t + 1], t + 1);
+                float bl = __shfl_up_sync(0xffffffffu, b1, 1), br = __shfl_down_sync(0xffffffffu, b1, 1);
+                if (first) bl = 0.f;
+                if (last) br = 0.f;
+                float acc = __fmaf_rn(tr, wreg[2], __fmaf_rn(t0, wreg[1], __fmaf_rn(tl, wreg[0], 0.0f)));
+                acc = __fmaf_rn(mr, wreg[5], __fmaf_rn(t1, wreg[4], __fmaf_rn(ml, wreg[3], acc)));
+                acc = __fmaf_rn(br, wreg[8], __fmaf_rn(b1, wreg[7], __fmaf_rn(bl, wreg[6], acc)));
+                if (a.bias) acc = __fadd_rn(acc, bv);
+                if (a.relu) acc = fmaxf(acc, 0.0f);
+                if (active) {
+                    yp[(int64_t)t * a.OW] = acc;
+                    lo = fminf(lo, acc); hi = fmaxf(hi, acc);
+                }
+                t0 = t1; tl = ml; tr = mr; t1 = b1; ml = bl; mr = br;
+            }
+        } else if (S == 1) {
             float t0 = q(ld(-1), -1), t1 = q(ld(0), 0);
             float tl = __shfl_up_sync(0xffffffffu, t0, 1), tr = __shfl_down_sync(0xffffffffu, t0, 1);
             float ml = __shfl_up_sync(0xffffffffu, t1, 1), mr = __shfl_down_sync(0xffffffffu, t1, 1);
@@ -532,6 +563,30 @@ dwconv3x3_cols_kernel(DwColArgs a) {
                 if (!okr) r = 0.f;
             };
             float tl, tm, tr;
+            if (a.H <= kColsPre) {                                  // as above: the whole plane in flight
+                float pre[kColsPre];
+#pragma unroll
+                for (int r = 0; r < kColsPre; ++r) pre[r] = r < a.H ? ld(r) : 0.0f;
+                tl = tm = tr = 0.0f;                                // row -1 is padding
+#pragma unroll
+                for (int t = 0; t < kColsPre / 2; ++t) {
+                    if (t >= a.OH) break;
+                    float ml, mm, mr, bl, bm, br;
+                    taps(q(pre[2 * t], 2 * t), ml, mm, mr);
+                    taps(q(pre[2 * t + 1], 2 * t + 1), bl, bm, br);
+                    float acc = __fmaf_rn(tr, wreg[2], __fmaf_rn(tm, wreg[1], __fmaf_rn(tl, wreg[0], 0.0f)));
+                    acc = __fmaf_rn(mr, wreg[5], __fmaf_rn(mm, wreg[4], __fmaf_rn(ml, wreg[3], acc)));
+                    acc = __fmaf_rn(br, wreg[8], __fmaf_rn(bm, wreg[7], __fmaf_rn(bl, wreg[6], acc)));
+                    if (a.bias) acc = __fadd_rn(acc, bv);
+                    if (a.relu) acc = fmaxf(acc, 0.0f);
+                    if (active && outlane) {
+                        yp[(int64_t)t * a.OW] = acc;
+                        lo = fminf(lo, acc); hi = fmaxf(hi, acc);
+                    }
+                    tl = bl; tm = bm; tr = br;
+                }
+                continue;
+            }
             taps(q(ld(-1), -1), tl, tm, tr);
             float p1 = ld(0), p2 = ld(1), p3 = ld(2), p4 = ld(3);
             for (int t = 0; t < a.OH; ++t) {
@@ -932,7 +987,9 @@ extern "C" int dfq_qconv2d_f32(const DfqConvDesc *d, void *stream) {
             r.x = d->x; r.y = d->y; r.w = d->w; r.bias = d->bias; r.slot = (const RangeSlot *)d->in_slot; r.stats = d->out_stats;
             r.C = d->C_in; r.H = d->H; r.W = d->W; r.OH = OH; r.OW = OW; r.relu = d->relu; r.bits = d->bits;
             r.G = 32 / d->W;
-            r.K = d->C_in >= 64 * r.G ? 4 : 1;
+            static int cols_k = -1;                                  // DFQ_DW_COLS_K: planes in sequence per lane group (A/B)
+            if (cols_k < 0) { const char *e = getenv("DFQ_DW_COLS_K"); cols_k = e ? atoi(e) : 0; }
+            r.K = cols_k > 0 ? cols_k : (d->C_in >= 64 * r.G ? 4 : 1);
             r.wps = (d->C_in + r.G * r.K - 1) / (r.G * r.K);
             dim3 grid((unsigned)((r.wps + kWarps - 1) / kWarps), (unsigned)d->N);
             if (d->stride == 1) dwconv3x3_cols_kernel<1><<<grid, kThreads, 0, st>>>(r);
