@@ -617,7 +617,7 @@ def _main(args):
     cle_impl = stages.pop("cle_impl", "?")
     cle_bytes = 12 * 4252832 * cle_iters
     ach = cle_bytes / (cle_kernel_ms * 1e-3) / 1e9 if cle_kernel_ms else None
-    roof = {"kernel": ("cle2_kernel" if cle_impl == "stream" else "cle_persistent_kernel") +
+    roof = {"kernel": {"resident": "cle3_kernel", "stream": "cle2_kernel"}.get(cle_impl, "cle_persistent_kernel") +
                       f" ({cle_iters} iterations in one cooperative launch)", "bound": "hbm",
             "achieved": round(ach, 1) if ach else None, "peak": peak, "unit": "GB/s",
             "frac": round(ach / peak, 4) if ach else None,

@@ -116,25 +116,70 @@ def cross_layer_equalization(graph, relations, Target_list, s_min_max=[1e-8, 1e8
         ev0 = ev1 = None
         if return_info:                 # device time of the loop itself (CUDA events on the launch stream)
             ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            ev0.record()
-        impl = "stream" if os.environ.get("DFQ_CLE_IMPL", "stream") == "stream" and _run_streaming(
-            pairs, n, pairs_dev, layers, len(ws), s_min_max, signed, eps, Treshhold, Count, max_iters, acc, result,
-            dev) else "units"
+            _EVENTS[:] = [ev0, ev1]
+        want = os.environ.get("DFQ_CLE_IMPL", "resident")
+        if want == "resident" and _run_resident(pairs, n, layers, len(ws), s_min_max, signed, eps, Treshhold, Count,
+                                                max_iters, result, dev):
+            impl = "resident"
+        elif want in ("resident", "stream") and _run_streaming(
+                pairs, n, pairs_dev, layers, len(ws), s_min_max, signed, eps, Treshhold, Count, max_iters, acc,
+                result, dev):
+            impl = "stream"
+        else:
+            impl = "units"
         if impl == "units":
             layers_dev = L.table_to_device(layers, dev)
+            _tick(0)
             L.check(L.lib().dfq_cle_run(pairs_dev.data_ptr(), n, ns.value, layers_dev.data_ptr(), len(ws), tc.value,
                                         float(s_min_max[0]), float(s_min_max[1]), int(bool(signed)), float(eps),
                                         float(Treshhold), int(Count), int(max_iters), acc.data_ptr(),
                                         result.data_ptr(), L.stream()), "dfq_cle_run")
+            _tick(1)
+        _EVENTS[:] = []
         if not return_info:
             return None
-        ev1.record()
         host = result.cpu().numpy()
         iters = int(host[:4].view("int32")[0])
         diffs = host[8:].view("float64")
         return {"iters": iters, "stall": int(host[4:8].view("int32")[0]), "diff": float(diffs[0]),
                 "diffs": diffs[1:1 + iters].tolist(), "stages": ns.value, "impl": impl,
                 "kernel_ms": ev0.elapsed_time(ev1)}
+
+
+def _run_resident(pairs, n, layers, n_layers, s_min_max, signed, eps, Treshhold, Count, max_iters, result, dev):
+    """The shared-memory-resident form (csrc/cle3.cu).  Returns False when the plan says cudaErrorNotSupported (not
+    simple chains of ungrouped / depthwise layers, or the chains do not fit the chip's shared memory)."""
+    lib = L.lib()
+    tensors = (L.DfqCle3Tensor * n_layers)()
+    chains = (L.DfqCle3Chain * n_layers)()
+    plan = L.DfqCle3Plan()
+    err = lib.dfq_cle3_plan_host(pairs, n, layers, n_layers, 0, 0, tensors, chains, ctypes.byref(plan))
+    if err == 801:                                  # cudaErrorNotSupported
+        return False
+    L.check(err, "dfq_cle3_plan_host")
+    tensors_dev = L.table_to_device(tensors, dev)
+    chains_dev = L.table_to_device((L.DfqCle3Chain * plan.n_chains).from_buffer(chains), dev)
+    scratch = torch.empty(int(lib.dfq_cle3_scratch_bytes(ctypes.byref(plan))), dtype=torch.uint8, device=dev)
+    _tick(0)
+    L.check(lib.dfq_cle3_run(tensors_dev.data_ptr(), chains_dev.data_ptr(), ctypes.byref(plan), scratch.data_ptr(),
+                             float(s_min_max[0]), float(s_min_max[1]), int(bool(signed)), float(eps),
+                             float(Treshhold), int(Count), int(max_iters), result.data_ptr(),
+                             None if DEBUG_STAMPS is None else DEBUG_STAMPS.data_ptr(), L.stream()),
+            "dfq_cle3_run")
+    _tick(1)
+    global LAST_PLAN
+    LAST_PLAN = {"grid": plan.grid, "smem_bytes": plan.smem_bytes, "chains": [(chains[i].len, chains[i].ncta)
+                                                                               for i in range(plan.n_chains)]}
+    return True
+
+
+LAST_PLAN = None
+_EVENTS = []           # [start, stop] CUDA events of a return_info call: recorded right around the kernel launch(es)
+
+
+def _tick(i):
+    if _EVENTS:
+        _EVENTS[i].record()
 
 
 def _run_streaming(pairs, n, pairs_dev, layers, n_layers, s_min_max, signed, eps, Treshhold, Count, max_iters, acc,
@@ -162,12 +207,14 @@ def _run_streaming(pairs, n, pairs_dev, layers, n_layers, s_min_max, signed, eps
     r1 = torch.empty(2 * total_c, dtype=torch.float32, device=dev)
     r2 = torch.empty(4 * total_c, dtype=torch.int32, device=dev)
     fat = torch.empty(int(lib.dfq_cle2_fat_bytes(used)) // 16 + 1, 4, dtype=torch.int32, device=dev)   # 16 B aligned
+    _tick(0)
     L.check(lib.dfq_cle2_run(pairs_dev.data_ptr(), n, tensors_dev.data_ptr(), n_layers, tasks_dev.data_ptr(), nt.value,
                              ni.value, phase_begin, nph.value, chan_dev.data_ptr(), total_c, r1.data_ptr(),
                              r2.data_ptr(), float(s_min_max[0]), float(s_min_max[1]), int(bool(signed)), float(eps),
                              float(Treshhold), int(Count), int(max_iters), acc.data_ptr(), result.data_ptr(),
                              int(os.environ.get("DFQ_CLE_BLOCKS_PER_SM", "2")), fat.data_ptr(),
                              None if DEBUG_STAMPS is None else DEBUG_STAMPS.data_ptr(), L.stream()), "dfq_cle2_run")
+    _tick(1)
     if DEBUG_STAMPS is not None:
         DEBUG_STAMPS.n_phases = nph.value
         DEBUG_STAMPS.tasks = [(tasks[i].tensor, tasks[i].row0, tasks[i].nrows, tasks[i].kind & 255, tasks[i].kind >> 8,

@@ -43,6 +43,21 @@ class DfqCleTask(ctypes.Structure):
     _fields_ = [("tensor", i32), ("row0", i32), ("nrows", i32), ("kind", i32)]
 
 
+class DfqCle3Tensor(ctypes.Structure):
+    _fields_ = [("W", c_void), ("S", c_void), ("b1", c_void), ("bn_w", c_void), ("bn_b", c_void)] + \
+               [(k, i32) for k in ("O", "L", "KK", "C", "dw", "up", "down", "s_off", "up_off", "cp_off", "dp_off",
+                                   "G", "layer")]
+
+
+class DfqCle3Chain(ctypes.Structure):
+    _fields_ = [(k, i32) for k in ("t0", "len", "cta0", "ncta")]
+
+
+class DfqCle3Plan(ctypes.Structure):
+    _fields_ = [(k, i32) for k in ("n_chains", "n_tensors", "grid", "smem_bytes", "total_C", "cp_words",
+                                   "dp_doubles", "fvec_floats", "cp_sm_words", "max_rows")]
+
+
 class DfqAbsorbPair(ctypes.Structure):
     _fields_ = [("W2", c_void), ("b1", c_void), ("b2", c_void), ("bn_w", c_void), ("bn_b", c_void), ("c", c_void),
                 ("wc", c_void), ("C1", i32), ("O2", i32), ("I2", i32), ("KK", i32), ("first_row", i32)]
@@ -87,7 +102,7 @@ class DfqConvI8Desc(ctypes.Structure):
 
 
 Q_SYMMETRIC, Q_RANGE_F32, Q_PER_CHANNEL, Q_CLAMP_OUT = 1, 2, 4, 8
-ABI_VERSION = 12
+ABI_VERSION = 13
 
 # every symbol include/dfq_b200.h declares: (restype, argtypes)
 P = ctypes.POINTER
@@ -141,6 +156,11 @@ PROTOTYPES = {
                                     P(i32), ctypes.c_int, c_void, ctypes.c_int, c_void, c_void, f64, f64, ctypes.c_int,
                                     f32, f64, ctypes.c_int, ctypes.c_int, c_void, c_void, ctypes.c_int, c_void, c_void, c_void]),
     "dfq_cle2_fat_bytes": (i64, [ctypes.c_int]),
+    "dfq_cle3_plan_host": (ctypes.c_int, [P(DfqClePair), ctypes.c_int, P(DfqCleLayer), ctypes.c_int, ctypes.c_int,
+                                          ctypes.c_int, P(DfqCle3Tensor), P(DfqCle3Chain), P(DfqCle3Plan)]),
+    "dfq_cle3_scratch_bytes": (i64, [P(DfqCle3Plan)]),
+    "dfq_cle3_run": (ctypes.c_int, [c_void, c_void, P(DfqCle3Plan), c_void, f64, f64, ctypes.c_int, f32, f64,
+                                    ctypes.c_int, ctypes.c_int, c_void, c_void, c_void]),
     "dfq_absorb_plan_host": (ctypes.c_int, [P(DfqAbsorbPair), ctypes.c_int, P(ctypes.c_int)]),
     "dfq_absorb_clip": (ctypes.c_int, [c_void, ctypes.c_int, ctypes.c_int, ctypes.c_int, f32, ctypes.c_int, f32, f32,
                                        c_void]),
@@ -216,6 +236,31 @@ def weights_epoch():
     return _weights_epoch
 
 
+_capture = None          # capture mode (pipeline_plan.py): {"arena": pinned uint8 tensor, "off": int, "keep": list}
+
+
+def bump_weights_epoch():
+    """Call after any write to layer weights that does not go through table_to_device (single-tensor kernels,
+    checkpoint unpacking, CUDA-graph replays of weight-side passes): invalidates the packed-code caches of the eval
+    kernels (utils/quantize.py _packed)."""
+    global _weights_epoch
+    _weights_epoch += 1
+
+
+def begin_capture(arena_bytes=1 << 20):
+    """Descriptor tables uploaded from now on are staged in ONE pinned arena that stays alive (and unchanged) with
+    the captured CUDA graph: a replay re-reads the host staging memory of every captured copy."""
+    global _capture
+    _capture = {"arena": torch.empty(arena_bytes, dtype=torch.uint8, pin_memory=True), "off": 0, "keep": []}
+    return _capture
+
+
+def end_capture():
+    global _capture
+    cap, _capture = _capture, None
+    return cap
+
+
 def table_to_device(arr, device):
     """ctypes array of descriptor structs -> uint8 CUDA tensor holding the same bytes.  Staged through pinned
     memory and copied asynchronously on the current stream: a pageable copy would block the host until every
@@ -224,10 +269,29 @@ def table_to_device(arr, device):
     global _weights_epoch
     _weights_epoch += 1                       # every weight-side pass uploads a descriptor table
     n = ctypes.sizeof(arr)
-    host = torch.empty(n, dtype=torch.uint8, pin_memory=True)
+    cap = _capture
+    if cap is not None and cap["off"] + n <= cap["arena"].numel():
+        host = cap["arena"][cap["off"]:cap["off"] + n]
+        cap["off"] += (n + 63) // 64 * 64
+    else:
+        host = torch.empty(n, dtype=torch.uint8, pin_memory=True)
+        if cap is not None:
+            cap["keep"].append(host)
     ctypes.memmove(host.data_ptr(), ctypes.addressof(arr), n)
-    return host.to(device, non_blocking=True)
+    out = host.to(device, non_blocking=True)
+    if cap is not None:
+        cap["keep"].append(out)
+    return out
+
+
+_replayed_launches = 0
+
+
+def add_launches(n):
+    """Kernel launches executed by replaying a captured CUDA graph (the C-side counter only sees direct calls)."""
+    global _replayed_launches
+    _replayed_launches += int(n)
 
 
 def launch_count():
-    return int(lib().dfq_launch_count())
+    return int(lib().dfq_launch_count()) + _replayed_launches

@@ -54,7 +54,13 @@ def get_argument(argv=None):
 
 def run_dfq_steps(model, graph, bottoms, args, targ_pair=(QuantConv2d, QuantLinear), timings=None):
     """main_dfq.py:188-231 on an already traced model (graph / bottoms from switch_layers).
-    Returns the relations."""
+    Returns the relations.
+
+    Without `timings`, the second pass over the same traced model in the same fresh state is recorded into CUDA
+    graphs and later passes replay them (pipeline_plan.py); results and side effects are those of the eager
+    functions below."""
+    from . import pipeline_plan as PP
+
     def timed(name, fn):
         if timings is None:
             return fn()
@@ -66,31 +72,64 @@ def run_dfq_steps(model, graph, bottoms, args, targ_pair=(QuantConv2d, QuantLine
         return out
 
     targ_layer = tuple(targ_pair) if args.quantize else (nn.Conv2d, nn.Linear)
-    timed("merge_batchnorm", lambda: merge_batchnorm(model, graph, bottoms, targ_layer))
-    res = []
-    if args.equalize:
-        res = create_relation(graph, bottoms, targ_layer, delete_single=False)
-        info = timed("cross_layer_equalization",
-                     lambda: cross_layer_equalization(graph, res, targ_layer, Save_state=False, Treshhold=2e-7,
-                                                      return_info=timings is not None))
-        if timings is not None and info:
-            timings["cle_kernel"] = info["kernel_ms"]
-            timings["cle_iters"] = info["iters"]
-            timings["cle_impl"] = info["impl"]
-    if args.absorption:
-        timed("bias_absorption", lambda: bias_absorption(graph, res, bottoms, N=3, visualize=args.visualize))
-    if args.quantize:
-        set_layer_bits(graph, args.bits_weight, args.bits_activation, args.bits_bias, targ_layer)
+
+    def weights_phase():
+        """merge_batchnorm .. quantize_targ_layer (main_dfq.py:188-214)."""
         timed("merge_batchnorm", lambda: merge_batchnorm(model, graph, bottoms, targ_layer))
-        timed("quantize_targ_layer",
-              lambda: quantize_targ_layer(graph, args.bits_weight, args.bits_bias, targ_layer))
+        res = []
+        if args.equalize:
+            res = create_relation(graph, bottoms, targ_layer, delete_single=False)
+            info = timed("cross_layer_equalization",
+                         lambda: cross_layer_equalization(graph, res, targ_layer, Save_state=False, Treshhold=2e-7,
+                                                          return_info=timings is not None))
+            if timings is not None and info:
+                timings["cle_kernel"] = info["kernel_ms"]
+                timings["cle_iters"] = info["iters"]
+                timings["cle_impl"] = info["impl"]
+        if args.absorption:
+            timed("bias_absorption", lambda: bias_absorption(graph, res, bottoms, N=3, visualize=args.visualize))
+        if args.quantize:
+            timed("set_layer_bits", lambda: set_layer_bits(graph, args.bits_weight, args.bits_activation,
+                                                           args.bits_bias, targ_layer))
+            timed("merge_batchnorm", lambda: merge_batchnorm(model, graph, bottoms, targ_layer))
+            timed("quantize_targ_layer",
+                  lambda: quantize_targ_layer(graph, args.bits_weight, args.bits_bias, targ_layer))
+        return res
+
+    def clip_phase():
+        if args.clip_weight:
+            timed("clip_weight", lambda: clip_weight(graph, range_clip=[-15, 15], targ_type=targ_layer))
+
+    def correction():
+        if args.correction:
+            timed("bias_correction", lambda: bias_correction(graph, bottoms, targ_layer, bits_weight=args.bits_weight,
+                                                             visualize=args.visualize,
+                                                             mode=getattr(args, "correction_mode", "ref")))
+
+    mode, plan = ("eager", None) if timings is not None else PP.lookup(graph, bottoms, args, targ_layer)
+    if mode == "capture":
+        snap = PP._snapshot(graph)
+        try:
+            plan = PP.PipelinePlan(model, graph, bottoms, args, targ_layer,
+                                   lambda phase: weights_phase() if phase == 1 else clip_phase())
+            PP.store(graph, plan)
+            PP.stats["captured"] += 1
+            mode = "replay"
+        except Exception as exc:                 # capture refused (e.g. a driver without cooperative graph nodes)
+            PP._restore(snap)
+            PP.store(graph, ("failed", repr(exc)))
+            mode = "eager"
+    if mode == "replay":
+        res = plan.replay()
+        PP.stats["replayed"] += 1
+        correction()
+        return res
+    PP.stats["eager"] += 1
+    res = weights_phase()
+    if args.quantize:
         timed("set_quant_minmax", lambda: set_quant_minmax(graph, bottoms))
-    if args.clip_weight:
-        timed("clip_weight", lambda: clip_weight(graph, range_clip=[-15, 15], targ_type=targ_layer))
-    if args.correction:
-        timed("bias_correction", lambda: bias_correction(graph, bottoms, targ_layer, bits_weight=args.bits_weight,
-                                                         visualize=args.visualize,
-                                                         mode=getattr(args, "correction_mode", "ref")))
+    clip_phase()
+    correction()
     return res
 
 

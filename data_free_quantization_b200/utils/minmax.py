@@ -107,6 +107,15 @@ def _lo(bias, weight, n):
 _ctx = {"stats": None, "pending": None}
 
 
+class _LayerQuant:
+    """`node.quant`, looked up when the range is written: set_layer_bits replaces the measures of every target layer
+    (utils/quantize.py:373), and a cached walk must follow it."""
+    __slots__ = ("node",)
+
+    def __init__(self, node):
+        self.node = node
+
+
 def _bn_stats(bn):
     """(fake_bias, fake_weight) of a BatchNorm as fresh fp32 numpy vectors (one batched D2H copy per call of
     set_quant_minmax, see _gather_stats)."""
@@ -117,40 +126,86 @@ def _bn_stats(bn):
     return bn.fake_bias.detach().cpu().numpy().copy(), bn.fake_weight.detach().cpu().numpy().copy()
 
 
-def _start_gather(graph, bn_type):
-    """Phase 1: queue the device->host copy of every BatchNorm's (fake_bias, fake_weight) and return a function
-    that waits for it and hands back {bn: (bias, weight)} as fp32 numpy vectors."""
-    bns = [m for m in graph.values() if type(m) == bn_type and hasattr(m, "fake_bias")]
-    if not bns:
-        return lambda: {}
-    vecs = [t for m in bns for t in (m.fake_bias, m.fake_weight)]
-    base = vecs[0]._base
-    if base is not None and base.is_contiguous() and all(t._base is base and t.is_contiguous() for t in vecs):
-        # merge_batchnorm's pooled stash: the vectors are slices of one allocation
-        src, b0 = base.detach().reshape(-1), base.storage_offset()
-        spans = [(m, m.fake_bias.storage_offset() - b0, m.fake_weight.storage_offset() - b0, m.fake_bias.numel())
-                 for m in bns]
-    else:
-        src = torch.cat([t.detach().reshape(-1) for t in vecs])
-        spans, off = [], 0
-        for m in bns:
-            n = m.fake_bias.numel()
-            spans.append((m, off, off + n, n))
-            off += 2 * n
-    if src.is_cuda:
-        host = torch.empty(src.numel(), dtype=src.dtype, pin_memory=True)
-        host.copy_(src, non_blocking=True)
-        done = torch.cuda.Event()
-        done.record()
-    else:
-        host, done = src, None
+class _Gather:
+    """Device->host copy of every BatchNorm's (fake_bias, fake_weight) through one pinned buffer.  start() queues
+    the copy on the current stream, fetch() waits for it and hands back {bn: (bias, weight)} as fp32 numpy views
+    (plus `flat` / `spans` for the vectorised 1-to-1 ranges).  The span table is rebuilt only when the vectors move
+    (merge_batchnorm's pooled stash is a new allocation per eager call, a fixed one inside a captured pipeline)."""
 
-    def fetch():
-        if done is not None:
-            done.synchronize()
-        flat = host.numpy()
-        return {m: (flat[ob:ob + n], flat[ow:ow + n]) for m, ob, ow, n in spans}
-    return fetch
+    def __init__(self, graph, bn_type):
+        self.bns = [m for m in graph.values() if type(m) == bn_type and hasattr(m, "fake_bias")]
+        self.key = None
+        self.host = self.done = self.src = None
+        self.spans, self.pooled_total = [], None
+
+    def _layout(self):
+        bns = self.bns
+        first = bns[0]._buffers["fake_bias"]
+        base = first._base
+        key = (None if base is None else base.data_ptr(), first.data_ptr(), bns[-1]._buffers["fake_weight"].data_ptr())
+        if key == self.key and base is not None:
+            return
+        vecs = [t for m in bns for t in (m._buffers["fake_bias"], m._buffers["fake_weight"])]
+        if base is not None and base.is_contiguous() and all(t._base is base and t.is_contiguous() for t in vecs):
+            # merge_batchnorm's pooled stash: the vectors are slices of one allocation
+            self.src, b0 = base.detach().reshape(-1), base.storage_offset()
+            self.spans = [(m, m._buffers["fake_bias"].storage_offset() - b0,
+                           m._buffers["fake_weight"].storage_offset() - b0, m._buffers["fake_bias"].numel()) for m in bns]
+            self.key = key
+            # [all fake_weight | all fake_bias], BatchNorms back to back: per-BN extrema by two reduceat calls
+            total = self.src.numel() // 2
+            off, ok = 0, self.src.numel() == 2 * total
+            for _m, ob, ow, n in self.spans:
+                ok = ok and ow == off and ob == total + off
+                off += n
+            self.pooled_total = total if ok and off == total else None
+        else:
+            self.src = None                     # gathered per call (torch.cat)
+            self.key = None
+            self.pooled_total = None
+            self.spans, off = [], 0
+            for m in bns:
+                n = m._buffers["fake_bias"].numel()
+                self.spans.append((m, off, off + n, n))
+                off += 2 * n
+
+    def start(self):
+        if not self.bns:
+            return
+        self._layout()
+        src = self.src
+        if src is None:
+            src = torch.cat([t.detach().reshape(-1) for m in self.bns
+                             for t in (m._buffers["fake_bias"], m._buffers["fake_weight"])])
+        if src.is_cuda:
+            if self.host is None or self.host.numel() != src.numel():
+                self.host = torch.empty(src.numel(), dtype=src.dtype, pin_memory=True)
+            self.host.copy_(src, non_blocking=True)
+            if self.done is None:
+                self.done = torch.cuda.Event()
+            self.done.record()
+            self._flat = None
+        else:
+            self._flat = src.numpy()
+
+    def fetch(self):
+        if not self.bns:
+            self.flat = None
+            return {}
+        if self._flat is None:
+            self.done.synchronize()
+            self.flat = self.host.numpy()
+        else:
+            self.flat = self._flat
+        flat = self.flat
+        return {m: (flat[ob:ob + n], flat[ow:ow + n]) for m, ob, ow, n in self.spans}
+
+
+def _start_gather(graph, bn_type):
+    """Phase 1 (uncached form): queue the device->host copy of the BatchNorm statistics, return the fetch function."""
+    g = _Gather(graph, bn_type)
+    g.start()
+    return g.fetch
 
 
 def _clipped_range(bias, weight, relu, N):
@@ -171,7 +226,7 @@ def _quant_modules_of(node, top):
                     top.add_idx_name_tensor_op()
                     return mods
     elif hasattr(node, 'quant'):
-        return [getattr(node, 'quant')]
+        return [_LayerQuant(node)]
     return None
 
 
@@ -244,11 +299,16 @@ def _range_of(res, N, eps):
 
 
 def _set(qm, lo, hi):
+    if type(qm) is _LayerQuant:
+        qm = qm.node.quant
     if _ctx["pending"] is not None:
         _ctx["pending"][qm] = (lo, hi)
         return
     qm.running_max.fill_(hi)
     qm.running_min.fill_(lo)
+
+
+_flush_cache = {}       # id(running_min) -> (running_min, running_max, table, row): layout of pooled measure buffers
 
 
 def _flush_pending():
@@ -260,14 +320,21 @@ def _flush_pending():
     if not pending:
         return None
     pooled, loose = {}, []
+    if len(_flush_cache) > 8192:
+        _flush_cache.clear()
     for q, (lo, hi) in pending.items():
         rmin, rmax = q._buffers["running_min"], q._buffers["running_max"]
+        hit = _flush_cache.get(id(rmin))
+        if hit is not None and hit[0] is rmin and hit[1] is rmax:          # same buffer objects as last time
+            pooled.setdefault(id(hit[2]), (hit[2], {}))[1][hit[3]] = (lo, hi)
+            continue
         base = rmin._base
         if (base is not None and rmax._base is base and base.dim() == 2 and base.size(1) == 2
                 and base.is_contiguous() and base.dtype == torch.float32
                 and rmax.storage_offset() == rmin.storage_offset() + 1):
             row = (rmin.storage_offset() - base.storage_offset()) // 2
             pooled.setdefault(id(base), (base, {}))[1][row] = (lo, hi)
+            _flush_cache[id(rmin)] = (rmin, rmax, base, row)
         else:
             loose.append(q)
     table = None
@@ -288,29 +355,99 @@ def _flush_pending():
     return table
 
 
+class MinmaxPlan:
+    """The graph walk of set_quant_minmax done once (it depends on the graph structure only), the arithmetic per call.
+    start() queues the device->host copy of the BatchNorm statistics; finish() waits for it, does the per-channel
+    arithmetic and writes every range.  Ranges of the 1-to-1 case (:476-505: min(beta - N gamma), max(beta + N gamma)
+    per BatchNorm) are formed for ALL BatchNorms by four vector operations over the pooled statistics -- the same
+    fp32 operations element by element -- and two reduceat calls."""
+
+    def __init__(self, graph, bottoms, is_detection=False, bn_type=torch.nn.BatchNorm2d, N=6):
+        from .. import graph as G
+        self.graph, self.bottoms = graph, bottoms
+        self.top = G._state.get("module_tensor_op")
+        self.key = self._key(graph, bottoms, is_detection, bn_type, N, self.top)
+        self.N, self.eps = N, 1e-6
+        self.jobs = _walk(graph, bottoms, is_detection, bn_type, self.top)
+        self.gather = _Gather(graph, bn_type)
+        self.bn_pos = {m: i for i, m in enumerate(self.gather.bns)}
+
+    @staticmethod
+    def _key(graph, bottoms, is_detection, bn_type, N, top):
+        return (id(graph), id(bottoms), tuple(map(id, graph.values())), bool(is_detection), bn_type, N, id(top))
+
+    def start(self):
+        self.gather.start()
+
+    def finish(self):
+        stats = self.gather.fetch()
+        _ctx["stats"], _ctx["pending"] = stats, {}
+        N, eps = self.N, self.eps
+        try:
+            with np.errstate(all="ignore"):              # x/0 -> inf, silently, as torch does
+                lo_bn = hi_bn = None
+                total = self.gather.pooled_total
+                if total:
+                    flat = self.gather.flat
+                    w_all, b_all = flat[:total], flat[total:2 * total]
+                    starts = np.fromiter((ow for _m, _ob, ow, _n in self.gather.spans), dtype=np.intp)
+                    nw = N * w_all
+                    lo_bn = np.minimum.reduceat(b_all - nw, starts).tolist()
+                    hi_bn = np.maximum.reduceat(b_all + nw, starts).tolist()
+                for job in self.jobs:
+                    if job[0] == "one" and lo_bn is not None and not job[4]:
+                        _, qms, bn_list, relu_list, _no_bn = job
+                        for i, (bn, _bid) in enumerate(bn_list):
+                            k = self.bn_pos[bn]
+                            lo, hi, relu = lo_bn[k], hi_bn[k], relu_list[i]
+                            if 'relu' in relu:
+                                lo = max(0., lo)
+                            if 'relu6' in relu:
+                                hi = min(6., hi)
+                            _set(qms[i], lo, hi)
+                    else:
+                        _run_job(job, N, eps)
+        finally:
+            _ctx["stats"] = None
+            _flush_pending()
+
+
+_plans = {}
+
+
+def minmax_plan(graph, bottoms, is_detection=False, bn_type=torch.nn.BatchNorm2d, N=6):
+    """Cached MinmaxPlan of this graph (rebuilt when the graph's nodes, the bottoms or the tensor-op table change)."""
+    from .. import graph as G
+    key = MinmaxPlan._key(graph, bottoms, is_detection, bn_type, N, G._state.get("module_tensor_op"))
+    plan = _plans.get(id(graph))
+    if plan is None or plan.key != key or plan.graph is not graph:
+        if len(_plans) >= 8:
+            _plans.clear()
+        plan = _plans[id(graph)] = MinmaxPlan(graph, bottoms, is_detection, bn_type, N)
+    return plan
+
+
 def set_quant_minmax(graph, bottoms, is_detection=False, bn_type=torch.nn.BatchNorm2d, N=6, verbose=True):
     """utils/layer_transform.py:356-618: fill every QuantMeasure's running_min / running_max from the statistics
     (fake_weight = |gamma|, fake_bias = beta) of the BatchNorm(s) that feed it.
 
     Three phases so that the host work overlaps the kernels still queued on the stream (the BN statistics are
-    the last thing the preceding steps write): (1) start the device->host copy of the statistics, (2) walk the
-    graph and record which BatchNorms / ReLUs / tensor ops feed which QuantMeasure -- pure graph logic --
-    (3) wait for the copy and do the per-channel arithmetic."""
-    from .. import graph as G
+    the last thing the preceding steps write): (1) start the device->host copy of the statistics, (2) the graph
+    walk -- which BatchNorms / ReLUs / tensor ops feed which QuantMeasure, pure graph logic, cached per graph --
+    (3) wait for the copy and do the per-channel arithmetic (MinmaxPlan)."""
     if verbose:
         print("SET QUANT MIN MAX")
-    top = G._state.get("module_tensor_op")
-    eps = 1e-6
-    fetch = _start_gather(graph, bn_type)
-    jobs = _walk(graph, bottoms, is_detection, bn_type, top)
-    _ctx["stats"], _ctx["pending"] = fetch(), {}
-    try:
-        with np.errstate(all="ignore"):              # x/0 -> inf, silently, as torch does
-            for job in jobs:
-                _run_job(job, N, eps)
-    finally:
-        _ctx["stats"] = None
-        _flush_pending()
+    cached = _plans.get(id(graph))
+    if cached is not None and cached.graph is graph and cached.bottoms is bottoms:
+        plan = minmax_plan(graph, bottoms, is_detection, bn_type, N)
+        plan.start()
+    else:                                   # first call on this graph: copy in flight while the walk runs
+        g = _Gather(graph, bn_type)
+        g.start()
+        plan = minmax_plan(graph, bottoms, is_detection, bn_type, N)
+        plan.gather = g
+        plan.bn_pos = {m: i for i, m in enumerate(g.bns)}
+    plan.finish()
 
 
 def _walk(graph, bottoms, is_detection, bn_type, top):

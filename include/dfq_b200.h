@@ -23,7 +23,7 @@
 extern "C" {
 #endif
 
-#define DFQ_ABI_VERSION 12
+#define DFQ_ABI_VERSION 13
 
 #if defined(__GNUC__)
 #pragma GCC visibility push(default)   /* the library is built with -fvisibility=hidden */
@@ -95,6 +95,26 @@ typedef struct DfqCleTask {
     int32_t kind;        /* low byte 0: column scaling + row ranges, 1: row/column scaling + metric + next column
                             ranges; bits 8..: 64-column strip of a 2-D tile                                  */
 } DfqCleTask;
+
+/* Resident form of the same loop (csrc/cle3.cu): the weights of a chain stay in the shared memory of a group of SMs
+ * for the whole loop.  One tensor of a chain (tensors of a chain are contiguous, in chain order): */
+typedef struct DfqCle3Tensor {
+    float *W;            /* [O, L] */
+    float *S, *b1, *bn_w, *bn_b;   /* per-row vectors of the pair where it is W1 (NULL without one; bn_* may be NULL) */
+    int32_t O, L;        /* rows, elements per row                                      */
+    int32_t KK, C;       /* as W2 of its up pair: taps per input channel, number of columns (channels) */
+    int32_t dw;          /* 1: depthwise, the row is its own column; 0: one group, column = input channel */
+    int32_t up, down;    /* pair where it is W2 / W1, or -1                              */
+    int32_t s_off, up_off;   /* channel offsets of the down / up pair in the s table      */
+    int32_t cp_off;      /* its column-range partials in the scratch                     */
+    int32_t dp_off;      /* its metric partials                                          */
+    int32_t G;           /* CTAs of its chain                                            */
+    int32_t layer;       /* index into the caller's layer table                          */
+} DfqCle3Tensor;
+typedef struct DfqCle3Chain { int32_t t0, len, cta0, ncta; } DfqCle3Chain;
+typedef struct DfqCle3Plan {
+    int32_t n_chains, n_tensors, grid, smem_bytes, total_C, cp_words, dp_doubles, fvec_floats, cp_sm_words, max_rows;
+} DfqCle3Plan;
 
 /* Result block of dfq_cle_run (device memory, dfq_cle_result_bytes(max_iters) = 16 + 8*max_iters):
  *   int32 iters; int32 stall; double last_diff; double diffs[max_iters]              */
@@ -323,6 +343,21 @@ int dfq_cle2_run(const DfqClePair *pairs_dev, int n_pairs, const DfqCleTensor *t
                  void *result_dev, int blocks_per_sm, void *fat_dev, void *debug_dev, void *stream);
 /* bytes of fat_dev (16-byte aligned scratch for the expanded task records) for n_tasks + n_init tasks */
 int64_t dfq_cle2_fat_bytes(int n_tasks_total);
+
+/* Resident form (csrc/cle3.cu), tried first: every chain gets a group of SMs sized by its element count, a CTA keeps
+ * whole rows of its chain's tensors in shared memory for the whole loop, groups synchronise among themselves once
+ * per chain position and the grid once per iteration.  dfq_cle3_plan_host returns cudaErrorNotSupported (801) when
+ * the relations are not simple chains of ungrouped / depthwise layers or the chains do not fit the chip's shared
+ * memory (use dfq_cle2_run then).  n_sm / smem_limit: 0 = query the current device.  tensors_host: n_layers entries,
+ * chains_host: n_layers entries (n_chains used).  scratch_dev: dfq_cle3_scratch_bytes(plan), zeroed by the call.
+ * result_dev as for dfq_cle_run.  debug_dev: NULL, or grid * 33 * 8 uint64 for globaltimer stamps (tuning aid). */
+int dfq_cle3_plan_host(const DfqClePair *pairs_host, int n_pairs, const DfqCleLayer *layers_host, int n_layers,
+                       int n_sm, int smem_limit, DfqCle3Tensor *tensors_host, DfqCle3Chain *chains_host,
+                       DfqCle3Plan *plan);
+int64_t dfq_cle3_scratch_bytes(const DfqCle3Plan *plan);
+int dfq_cle3_run(const DfqCle3Tensor *tensors_dev, const DfqCle3Chain *chains_dev, const DfqCle3Plan *plan_host,
+                 void *scratch_dev, double smin, double smax, int is_signed, float eps, double threshold, int count,
+                 int max_iters, void *result_dev, void *debug_dev, void *stream);
 
 /* ---- (c) bias absorption (+ optional weight clip): bias_absorption.py:9-80, clip_weight.py:4-33 */
 int dfq_absorb_plan_host(DfqAbsorbPair *pairs_host, int n_pairs, int *total_rows);

@@ -94,10 +94,13 @@ def _pair(rng, C1, K1, O2, I2, KK):
     return W1, W2
 
 
+@pytest.mark.parametrize("impl", ["resident", "stream", "units"])
 @pytest.mark.parametrize("signed", [False, True])
-def test_cle_pairs_against_oracle(oracle, signed):
-    """Dense->dense, dense->depthwise, depthwise->dense, ragged channel counts; 3 iterations, bit-exact."""
+def test_cle_pairs_against_oracle(oracle, signed, impl, monkeypatch):
+    """Dense->dense, dense->depthwise, depthwise->dense, ragged channel counts; 3 iterations, bit-exact -- on the
+    shared-memory-resident kernel (cle3.cu), the streaming kernel (cle2.cu) and the per-channel-unit kernel (cle.cu)."""
     from data_free_quantization_b200.Cross_layer_equal import cross_layer_equalization
+    monkeypatch.setenv("DFQ_CLE_IMPL", impl)
     from data_free_quantization_b200.utils.relation import Relation
     rng = np.random.default_rng(4)
     shapes = [(32, 27, 32, 1, 9), (32, 9, 16, 32, 1), (16, 32, 96, 16, 1), (96, 16, 96, 1, 9), (96, 9, 24, 96, 1),
@@ -119,6 +122,7 @@ def test_cle_pairs_against_oracle(oracle, signed):
     info = cross_layer_equalization(graph, rels, [nn.Conv2d], Treshhold=-1.0, Count=10 ** 9, signed=signed,
                                     Save_state=False, max_iters=3, return_info=True)
     assert info["iters"] == 3
+    assert info["impl"] == impl
     for i, (W1, W2, b1, g, be) in enumerate(ref):
         S = np.ones(W1.shape[0], np.float32)
         for _ in range(3):
@@ -164,3 +168,59 @@ def test_absorption_against_oracle(oracle, clip):
         assert rel_err(b2, graph[f"b{i}"].bias.cpu().numpy()) <= 1e-5
         want_w = np.clip(W2, *clip) if clip else W2
         assert graph[f"b{i}"].weight.cpu().numpy().tobytes() == want_w.tobytes()
+
+
+@pytest.mark.parametrize("impl", ["resident", "stream"])
+def test_cle_long_chain_many_ctas_against_oracle(oracle, impl, monkeypatch):
+    """One chain of five tensors large enough that the resident kernel spreads it over a multi-CTA group (group
+    barriers, column-range partials through L2) next to a tiny single-CTA chain; 4 iterations, bit-exact against
+    the oracle's sequential loop (Cross_layer_equal.py:85-99 order)."""
+    from data_free_quantization_b200 import Cross_layer_equal as CLE
+    from data_free_quantization_b200.utils.relation import Relation
+    monkeypatch.setenv("DFQ_CLE_IMPL", impl)
+    rng = np.random.default_rng(11)
+    # (O, I, KK, groups): pw 96->576, dw 576, pw 576->160, pw 160->960, linear-like 960->700; then a tiny pair
+    specs = [[(576, 96, 1, 1), (576, 1, 9, 576), (160, 576, 1, 1), (960, 160, 1, 1), (700, 960, 1, 1)],
+             [(8, 3, 9, 1), (8, 1, 9, 8)]]
+    graph, rels, ref = {}, [], []
+    for ci, chain in enumerate(specs):
+        Ws = []
+        for (O, I, KK, _g) in chain:
+            Ws.append((rng.standard_normal((O, I, KK)) * rng.uniform(0.05, 1.5, (O, 1, 1))).astype(np.float32))
+        for li, W in enumerate(Ws):
+            conv = nn.Conv2d(1, 1, 1, bias=False)
+            conv.weight = nn.Parameter(torch.from_numpy(W.copy()).to(DEV), requires_grad=False)
+            graph[f"c{ci}l{li}"] = conv
+            if li + 1 < len(Ws):
+                bn = nn.BatchNorm2d(W.shape[0])
+                bn.register_buffer("fake_weight", torch.from_numpy((rng.random(W.shape[0]) + 0.5).astype(np.float32)).to(DEV))
+                bn.register_buffer("fake_bias", torch.from_numpy(rng.standard_normal(W.shape[0]).astype(np.float32)).to(DEV))
+                graph[f"c{ci}n{li}"] = bn
+                rels.append(Relation(f"c{ci}l{li}", f"c{ci}l{li + 1}", f"c{ci}n{li}"))
+        ref.append(Ws)
+    state = {k: (m.fake_weight.cpu().numpy().copy(), m.fake_bias.cpu().numpy().copy())
+             for k, m in graph.items() if isinstance(m, nn.BatchNorm2d)}
+    info = CLE.cross_layer_equalization(graph, rels, [nn.Conv2d], Treshhold=-1.0, Count=10 ** 9, Save_state=False,
+                                        max_iters=4, return_info=True)
+    assert info["iters"] == 4 and info["impl"] == impl
+    if impl == "resident":
+        assert max(n for _len, n in CLE.LAST_PLAN["chains"]) > 8, CLE.LAST_PLAN      # a real multi-CTA group
+    diffs = []
+    for _ in range(4):
+        old = [[w.copy() for w in Ws] for Ws in ref]
+        for ci, Ws in enumerate(ref):
+            for li in range(len(Ws) - 1):
+                W1 = Ws[li].reshape(Ws[li].shape[0], -1)
+                b1 = np.zeros(W1.shape[0], np.float32)
+                g, be = state[f"c{ci}n{li}"]
+                oracle.cle_pair(W1, Ws[li + 1], b1, g, be)
+        diffs.append(sum(float(np.float32(np.mean(np.abs(w.astype(np.float64) - o.astype(np.float64)))))
+                         for Ws, Os in zip(ref, old) for w, o in zip(Ws, Os)))
+    for ci, Ws in enumerate(ref):
+        for li, W in enumerate(Ws):
+            got = graph[f"c{ci}l{li}"].weight.cpu().numpy()
+            assert got.tobytes() == W.tobytes(), (ci, li, int((got != W).sum()))
+    for k, (g, be) in state.items():
+        assert graph[k].fake_weight.cpu().numpy().tobytes() == g.tobytes(), k
+        assert graph[k].fake_bias.cpu().numpy().tobytes() == be.tobytes(), k
+    np.testing.assert_allclose(info["diffs"], diffs, rtol=1e-5)
