@@ -25,7 +25,7 @@ constexpr int kC3Threads = 512;
 constexpr int kC3Warps = kC3Threads / 32;
 constexpr int kC3MaxLen = 32;          // tensors per chain
 constexpr int kC3BarStride = 32;       // one 128-byte line per barrier counter
-constexpr int kC3StaticSmem = 1024;    // static __shared__ of the kernel (upper bound used by the planner)
+constexpr int kC3StaticSmem = 4096;    // static __shared__ of the kernel (upper bound used by the planner)
 
 struct Cle3Args {
     const DfqCle3Tensor *tensors; const DfqCle3Chain *chains; int n_chains, n_tensors;
@@ -61,42 +61,51 @@ __device__ __forceinline__ unsigned long long c3_now() {
 #define C3_STAMP(slot) do { if (stamp) dbgp[(slot)] = c3_now(); } while (0)
 
 __device__ __forceinline__ void c3_arrive(unsigned *bar) {     // one thread, after a __syncthreads
-    __threadfence();
+    // release at gpu scope: cumulative over everything the CTA wrote before the barrier (no separate membar)
     asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(bar) : "memory");
 }
 __device__ __forceinline__ void c3_wait(const unsigned *bar, unsigned target) {   // one thread, before a __syncthreads
+    // relaxed polls, ONE acquire fence at the end: an acquire load invalidates the L1 on every poll
     const long long t0 = clock64();
     for (;;) {
         unsigned v;
-        asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(bar) : "memory");
-        if (v >= target) return;
+        asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(bar) : "memory");
+        if (v >= target) break;
         if (clock64() - t0 > (1ll << 33)) __trap();            // ~4 s: a lost peer must not hang the GPU
     }
+    asm volatile("fence.acq_rel.gpu;" ::: "memory");
 }
 
 // Rescale pass over this CTA's rows of one tensor (in shared memory): optional column factors (fvec), optional row
 // factors (s_rows), metric, column-range partials into cp_sm (encoded, atomicMax).  Thread t keeps a fixed position j
 // inside the row, so the column factor and the column extrema live in registers; consecutive threads touch
 // consecutive words (conflict-free).
-__device__ __forceinline__ void c3_rescale(float *__restrict__ w, int nrows, int L, int KK, bool dw,
-                                           const float *__restrict__ fvec, const float *__restrict__ s_rows,
+__device__ __forceinline__ void c3_rescale(float *__restrict__ w, int nrows, int L, int KK, bool dw, bool cs,
+                                           const float *__restrict__ fvec, bool rs, const float *__restrict__ s_rows,
                                            unsigned *__restrict__ cp_sm, int cp_half, bool sgn, bool want_cp,
                                            bool want_diff, double &part) {
-    const bool cs = fvec != nullptr, rs = s_rows != nullptr;
+    // (all pointers are shared-memory addresses derived from the kernel's dynamic array and never null -- `cs` / `rs`
+    // say whether the factors apply -- so the loop compiles to LDS / STS without generic-address conversions)
+    // The metric sum_e |W - W_old| is summed in fp32 per thread (a few dozen terms) and in double across threads and
+    // CTAs: the reference's own torch.mean is an fp32 reduction, and the loop's tests (:81, :110) have margins of
+    // 7 % and 1e-9 absolute against sums of ~1e-7 .. 1e-3.
+    float acc_s = 0.0f;
     int R, j0, rsub, step;
     if (L <= kC3Threads) { R = kC3Threads / L; j0 = threadIdx.x % L; rsub = threadIdx.x / L; step = L; }
     else { R = 1; j0 = threadIdx.x; rsub = 0; step = kC3Threads; }
-    if (rsub >= R) return;
+    if (rsub >= R) { part = 0.0; return; }
     for (int j = j0; j < L; j += step) {
         const float fc = (cs && !dw) ? fvec[j] : 1.0f;
         float lo = INFINITY, hi = -INFINITY;
-        for (int r = rsub; r < nrows; r += R) {
-            const float old = w[r * L + j];
+        float *p = w + rsub * L + j;
+        const int stride = R * L;
+        for (int r = rsub; r < nrows; r += R, p += stride) {
+            const float old = *p;
             float v = old;
             if (cs) v = __fmul_rn(v, dw ? fvec[r] : fc);
             if (rs) v = __fmul_rn(v, s_rows[r]);
-            if (cs || rs) w[r * L + j] = v;
-            if (want_diff) part += (double)fabsf(__fsub_rn(v, old));
+            if (cs || rs) *p = v;
+            if (want_diff) acc_s = __fadd_rn(acc_s, fabsf(__fsub_rn(v, old)));
             if (want_cp) {
                 const float m = sgn ? fabsf(v) : v;
                 if (dw) {                                       // the row is its own column
@@ -109,6 +118,53 @@ __device__ __forceinline__ void c3_rescale(float *__restrict__ w, int nrows, int
             atomicMax(cp_sm + c, enc_ordered(-lo)); atomicMax(cp_sm + cp_half + c, enc_ordered(hi));
         }
     }
+    part = (double)acc_s;
+}
+
+// The same pass for ungrouped 1 x 1 tensors whose rows are a multiple of 4 long: a thread owns FOUR adjacent columns
+// (128-bit LDS / STS), rows strided as above; ~9 instructions per element instead of ~50.
+__device__ __forceinline__ void c3_rescale4(float *__restrict__ w, int nrows, int L, bool cs,
+                                            const float *__restrict__ fvec, bool rs, const float *__restrict__ s_rows,
+                                            unsigned *__restrict__ cp_sm, int cp_half, bool sgn, bool want_cp,
+                                            double &part) {
+    const int L4 = L >> 2;
+    float acc[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+    int R, j0, rsub, step;
+    if (L4 <= kC3Threads) { R = kC3Threads / L4; j0 = threadIdx.x % L4; rsub = threadIdx.x / L4; step = L4; }
+    else { R = 1; j0 = threadIdx.x; rsub = 0; step = kC3Threads; }
+    part = 0.0;
+    if (rsub >= R) return;
+    const float4 *f4 = reinterpret_cast<const float4 *>(fvec);
+    for (int j = j0; j < L4; j += step) {
+        const float4 f = cs ? f4[j] : make_float4(1.0f, 1.0f, 1.0f, 1.0f);
+        float lo[4] = {INFINITY, INFINITY, INFINITY, INFINITY}, hi[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+        float4 *p = reinterpret_cast<float4 *>(w) + rsub * L4 + j;
+        const int stride = R * L4;
+        for (int r = rsub; r < nrows; r += R, p += stride) {
+            const float4 old = *p;
+            float v[4] = {old.x, old.y, old.z, old.w};
+            const float o[4] = {old.x, old.y, old.z, old.w};
+            const float ff[4] = {f.x, f.y, f.z, f.w};
+            const float sr = rs ? s_rows[r] : 1.0f;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                if (cs) v[q] = __fmul_rn(v[q], ff[q]);
+                if (rs) v[q] = __fmul_rn(v[q], sr);
+                acc[q] = __fadd_rn(acc[q], fabsf(__fsub_rn(v[q], o[q])));
+                const float m = sgn ? fabsf(v[q]) : v[q];
+                lo[q] = fminf(lo[q], m); hi[q] = fmaxf(hi[q], m);
+            }
+            if (cs || rs) *p = make_float4(v[0], v[1], v[2], v[3]);
+        }
+        if (want_cp && hi[0] >= lo[0]) {
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                atomicMax(cp_sm + 4 * j + q, enc_ordered(-lo[q]));
+                atomicMax(cp_sm + cp_half + 4 * j + q, enc_ordered(hi[q]));
+            }
+        }
+    }
+    part = ((double)acc[0] + (double)acc[1]) + ((double)acc[2] + (double)acc[3]);
 }
 
 __global__ void __launch_bounds__(kC3Threads, 1)
@@ -116,6 +172,7 @@ cle3_kernel(Cle3Args a) {
     extern __shared__ __align__(16) float sm[];
     __shared__ int s_off[kC3MaxLen], s_row0[kC3MaxLen], s_nrows[kC3MaxLen], s_vec[kC3MaxLen];
     __shared__ int s_ws;
+    __shared__ DfqCle3Tensor s_T[kC3MaxLen];       // this chain's tensor records: no global metadata reads in the loop
     __shared__ double s_red[kC3Warps];
     __shared__ double st_diff;
     __shared__ int st_stall, st_iters;
@@ -129,17 +186,19 @@ cle3_kernel(Cle3Args a) {
     unsigned *gbar = a.bars + (size_t)c * kC3BarStride;
     unsigned *allbar = a.bars + (size_t)a.n_chains * kC3BarStride;
 
+    for (int i = tid; i < ch.len; i += kC3Threads) s_T[i] = a.tensors[ch.t0 + i];
+    __syncthreads();
     if (tid == 0) {
         int off = 0;
         for (int i = 0; i < ch.len; ++i) {
-            const DfqCle3Tensor &T = a.tensors[ch.t0 + i];
+            const DfqCle3Tensor &T = s_T[i];
             const int r0 = (int)((long long)g * T.O / G), r1 = (int)((long long)(g + 1) * T.O / G);
             s_row0[i] = r0; s_nrows[i] = r1 - r0; s_off[i] = off;
-            off += (r1 - r0) * T.L;
+            off += ((r1 - r0) * T.L + 3) & ~3;          // 16-byte aligned regions (128-bit accesses)
         }
         for (int i = 0; i < ch.len; ++i) {
             s_vec[i] = off;
-            if (a.tensors[ch.t0 + i].down >= 0) off += 4 * s_nrows[i];
+            if (s_T[i].down >= 0) off += 4 * s_nrows[i];
         }
         s_ws = (off + 3) & ~3;
     }
@@ -148,11 +207,19 @@ cle3_kernel(Cle3Args a) {
     unsigned *cp_sm = reinterpret_cast<unsigned *>(fvec + a.fvec_floats);
     const int cp_half = a.cp_words / 2;
     unsigned *r2_sm = cp_sm + a.cp_words;                      // [2][max_rows]
-    float *s_sm = reinterpret_cast<float *>(r2_sm + 2 * a.max_rows);   // [max_rows]
+    unsigned *rr_sm = r2_sm + 2 * a.max_rows;                  // [2][max_rows] row ranges met across warps
+    float *s_sm = reinterpret_cast<float *>(rr_sm + 2 * a.max_rows);   // [max_rows]
+    double *dp_sm = reinterpret_cast<double *>(s_sm + a.max_rows);     // [dp_doubles + n_tensors] (8-byte aligned)
+    double *dec_n = dp_sm + a.dp_doubles + a.n_tensors;               // [n_tensors] element counts
+    int *dec_off = reinterpret_cast<int *>(dec_n + a.n_tensors);      // [n_tensors] first partial | [n_tensors] partials
+    for (int t = tid; t < a.n_tensors; t += kC3Threads) {
+        const DfqCle3Tensor &T = a.tensors[t];
+        dec_n[t] = (double)T.O * (double)T.L; dec_off[t] = T.dp_off; dec_off[a.n_tensors + t] = T.G;
+    }
 
     // ---- load: this CTA's rows of every tensor of its chain, the per-channel vectors of the pairs it owns
     for (int i = 0; i < ch.len; ++i) {
-        const DfqCle3Tensor T = a.tensors[ch.t0 + i];
+        const DfqCle3Tensor &T = s_T[i];
         const int n = s_nrows[i] * T.L;
         const float *__restrict__ src = T.W + (size_t)s_row0[i] * T.L;
         float *dst = sm + s_off[i];
@@ -168,6 +235,7 @@ cle3_kernel(Cle3Args a) {
         }
     }
     for (int i = tid; i < a.cp_words; i += kC3Threads) cp_sm[i] = 0u;
+    for (int i = tid; i < 4 * a.max_rows; i += kC3Threads) r2_sm[i] = 0u;      // r2_sm and rr_sm
     __syncthreads();
 
     // column-range partials of tensor i (just written to cp_sm) -> global, cp_sm cleared for the next user
@@ -192,10 +260,10 @@ cle3_kernel(Cle3Args a) {
     {
         double dummy = 0.0;
         for (int i = 0; i < ch.len; ++i) {
-            const DfqCle3Tensor T = a.tensors[ch.t0 + i];
+            const DfqCle3Tensor &T = s_T[i];
             if (T.up < 0) continue;
-            c3_rescale(sm + s_off[i], s_nrows[i], T.L, T.KK, T.dw != 0, nullptr, nullptr, cp_sm, cp_half, sgn, true,
-                       false, dummy);
+            c3_rescale(sm + s_off[i], s_nrows[i], T.L, T.KK, T.dw != 0, false, fvec, false, s_sm, cp_sm, cp_half, sgn,
+                       true, false, dummy);
             flush_cp(T, i);
         }
     }
@@ -211,28 +279,16 @@ cle3_kernel(Cle3Args a) {
         const bool stamp = a.dbg && iters == 2 && tid == 0;
         unsigned long long *dbgp = a.dbg ? a.dbg + (size_t)blockIdx.x * (kC3MaxLen + 1) * 8 : nullptr;
         for (int i = 0; i < ch.len; ++i, dbgp += 8) {
-            const DfqCle3Tensor T = a.tensors[ch.t0 + i];
+            const DfqCle3Tensor &T = s_T[i];
             C3_STAMP(0);
             float *w = sm + s_off[i];
             const int nrows = s_nrows[i], row0 = s_row0[i], L = T.L;
             const bool up = T.up >= 0, down = T.down >= 0;
-            if (i > 0 && G > 1) {                     // s of pair i-1 published by every CTA of the group
-                ++grp_epoch;
-                if (tid == 0) c3_wait(gbar, grp_epoch * G);
-                __syncthreads();
-            }
-            C3_STAMP(1);
-            // stage the column factors 1/s_{i-1} and the column ranges of T(i+1) for my rows
-            if (up) {
-                const float *sinv = a.s_tab + a.total_C + T.up_off;
-                if (T.dw) { for (int r = tid; r < nrows; r += kC3Threads) fvec[r] = __ldcg(sinv + row0 + r); }
-                else if (T.KK == 1) { for (int j = tid; j < L; j += kC3Threads) fvec[j] = __ldcg(sinv + j); }
-                else { for (int j = tid; j < L; j += kC3Threads) fvec[j] = __ldcg(sinv + j / T.KK); }
-            }
+            const bool vec4 = (L & 3) == 0 && !T.dw && T.KK == 1 && L >= 16;     // 128-bit shared accesses
+            // column ranges of T(i+1) for my rows: left by the previous iteration, so they are fetched BEFORE waiting
+            // for this phase's barrier (r2_sm / rr_sm were cleared behind the previous phase's use)
             if (down) {
-                const DfqCle3Tensor &Tn = a.tensors[ch.t0 + i + 1];
-                for (int r = tid; r < nrows; r += kC3Threads) { r2_sm[r] = 0u; r2_sm[a.max_rows + r] = 0u; }
-                __syncthreads();
+                const DfqCle3Tensor &Tn = s_T[i + 1];
                 const unsigned *cpn = a.cp + Tn.cp_off;
                 if (Tn.dw) {
                     for (int r = tid; r < nrows; r += kC3Threads) {
@@ -245,6 +301,19 @@ cle3_kernel(Cle3Args a) {
                         atomicMax(r2_sm + r, __ldcg(p)); atomicMax(r2_sm + a.max_rows + r, __ldcg(p + Tn.C));
                     }
                 }
+            }
+            if (i > 0 && G > 1) {                     // s of pair i-1 published by every CTA of the group
+                ++grp_epoch;
+                if (tid == 0) c3_wait(gbar, grp_epoch * G);
+                __syncthreads();
+            }
+            C3_STAMP(1);
+            // the column factors 1/s_{i-1}
+            if (up) {
+                const float *sinv = a.s_tab + a.total_C + T.up_off;
+                if (T.dw) { for (int r = tid; r < nrows; r += kC3Threads) fvec[r] = __ldcg(sinv + row0 + r); }
+                else if (T.KK == 1) { for (int j = tid; j < L; j += kC3Threads) fvec[j] = __ldcg(sinv + j); }
+                else { for (int j = tid; j < L; j += kC3Threads) fvec[j] = __ldcg(sinv + j / T.KK); }
             }
             __syncthreads();
             C3_STAMP(2);
@@ -263,20 +332,64 @@ cle3_kernel(Cle3Args a) {
                     vec[nrows + r] = __fmul_rn(vec[nrows + r], s);
                     vec[2 * nrows + r] = __fmul_rn(vec[2 * nrows + r], s);
                     vec[3 * nrows + r] = __fmul_rn(vec[3 * nrows + r], s);
+                    r2_sm[r] = 0u; r2_sm[a.max_rows + r] = 0u;           // ready for the next phase's prefetch
                 };
-                if (L >= 32) {                        // warp per row
-                    for (int r = warp; r < nrows; r += kC3Warps) {
+                if (vec4) {
+                    // P lanes per row (a whole warp when the CTA owns few rows, 8 lanes otherwise), 128-bit loads of
+                    // the row and of the column factors, log2(P) shuffle steps, the group's first lane finishes
+                    const int P = nrows <= 16 ? 32 : 8;
+                    const int gid = tid / P, lp = tid % P, groups = kC3Threads / P, L4 = L >> 2;
+                    const float4 *f4 = reinterpret_cast<const float4 *>(fvec);
+                    for (int rb = 0; rb < nrows; rb += groups) {          // (uniform trip count: shuffles inside)
+                        const int r = rb + gid;
+                        float lo = INFINITY, hi = -INFINITY;
+                        if (r < nrows) {
+                            const float4 *row = reinterpret_cast<const float4 *>(w + r * L);
+                            for (int j = lp; j < L4; j += P) {
+                                float4 v = row[j];
+                                if (up) {
+                                    const float4 f = f4[j];
+                                    v.x = __fmul_rn(v.x, f.x); v.y = __fmul_rn(v.y, f.y);
+                                    v.z = __fmul_rn(v.z, f.z); v.w = __fmul_rn(v.w, f.w);
+                                }
+                                if (sgn) { v.x = fabsf(v.x); v.y = fabsf(v.y); v.z = fabsf(v.z); v.w = fabsf(v.w); }
+                                lo = fminf(fminf(lo, fminf(v.x, v.y)), fminf(v.z, v.w));
+                                hi = fmaxf(fmaxf(hi, fmaxf(v.x, v.y)), fmaxf(v.z, v.w));
+                            }
+                        }
+                        for (int o = P >> 1; o; o >>= 1) {
+                            lo = fminf(lo, __shfl_xor_sync(0xffffffffu, lo, o));
+                            hi = fmaxf(hi, __shfl_xor_sync(0xffffffffu, hi, o));
+                        }
+                        if (r < nrows && lp == 0) finish(r, sgn ? hi : __fsub_rn(hi, lo));
+                    }
+                } else if (L >= 32) {
+                    // a warp takes 128-element segments of rows (all 16 warps busy however few rows the CTA owns);
+                    // segment extrema meet in rr_sm, then one thread per row finishes (division, sqrt) in parallel
+                    const int segs = (L + 127) >> 7;
+                    for (int it = warp; it < nrows * segs; it += kC3Warps) {
+                        const int r = it / segs, j0 = (it - r * segs) << 7;
                         const float *row = w + r * L;
                         float lo = INFINITY, hi = -INFINITY;
                         const float fr = (up && T.dw) ? fvec[r] : 1.0f;
-                        for (int j = lane; j < L; j += 32) {
-                            float v = row[j];
-                            if (up) v = __fmul_rn(v, T.dw ? fr : fvec[j]);
-                            if (sgn) v = fabsf(v);
-                            lo = fminf(lo, v); hi = fmaxf(hi, v);
+#pragma unroll
+                        for (int u = 0; u < 4; ++u) {
+                            const int j = j0 + lane + 32 * u;
+                            if (j < L) {
+                                float v = row[j];
+                                if (up) v = __fmul_rn(v, T.dw ? fr : fvec[j]);
+                                if (sgn) v = fabsf(v);
+                                lo = fminf(lo, v); hi = fmaxf(hi, v);
+                            }
                         }
                         lo = warp_min(lo); hi = warp_max(hi);
-                        if (lane == 0) finish(r, sgn ? hi : __fsub_rn(hi, lo));
+                        if (lane == 0) { atomicMax(rr_sm + r, enc_ordered(-lo)); atomicMax(rr_sm + a.max_rows + r, enc_ordered(hi)); }
+                    }
+                    __syncthreads();
+                    for (int r = tid; r < nrows; r += kC3Threads) {
+                        const float lo = -dec_ordered(rr_sm[r]), hi = dec_ordered(rr_sm[a.max_rows + r]);
+                        rr_sm[r] = 0u; rr_sm[a.max_rows + r] = 0u;
+                        finish(r, sgn ? hi : __fsub_rn(hi, lo));
                     }
                 } else {                              // thread per row (depthwise 3x3, tiny pointwise)
                     for (int r = tid; r < nrows; r += kC3Threads) {
@@ -294,13 +407,13 @@ cle3_kernel(Cle3Args a) {
                 }
                 __syncthreads();
                 C3_STAMP(3);
-                if (tid == 0 && G > 1) c3_arrive(gbar);          // s_i is out: the next phase may start everywhere
+                if (tid == kC3Threads - 1 && G > 1) c3_arrive(gbar);   // s_i is out: the next phase may start everywhere
             }
             C3_STAMP(4);
             // rescale pass behind the barrier signal
             double part = 0.0;
-            c3_rescale(w, nrows, L, T.KK, T.dw != 0, up ? fvec : nullptr, down ? s_sm : nullptr, cp_sm, cp_half, sgn,
-                       up, true, part);
+            if (vec4) c3_rescale4(w, nrows, L, up, fvec, down, s_sm, cp_sm, cp_half, sgn, up, part);
+            else c3_rescale(w, nrows, L, T.KK, T.dw != 0, up, fvec, down, s_sm, cp_sm, cp_half, sgn, up, true, part);
             C3_STAMP(5);
             if (up) flush_cp(T, i);
             part = warp_sum(part);
@@ -323,21 +436,20 @@ cle3_kernel(Cle3Args a) {
         __syncthreads();
         C3_STAMP(1);
         // diff_tmp = np.sum([float(torch.mean(torch.abs(W - W_old))) ...]), :107-108 -- same value in every CTA
-        double mine = 0.0;
-        for (int t = warp; t < a.n_tensors; t += kC3Warps) {
-            const DfqCle3Tensor &T = a.tensors[t];
-            const double *p = a.dp + (size_t)par * a.dp_doubles + T.dp_off;
+        // all partials in one round trip, then one thread per tensor, then one thread over the tensors in order:
+        // every CTA does the same additions in the same order
+        for (int q = tid; q < a.dp_doubles; q += kC3Threads) dp_sm[q] = __ldcg(a.dp + (size_t)par * a.dp_doubles + q);
+        __syncthreads();
+        for (int t = tid; t < a.n_tensors; t += kC3Threads) {
+            const int q0 = dec_off[t], q1 = q0 + dec_off[a.n_tensors + t];
             double s = 0.0;
-            for (int q = lane; q < T.G; q += 32) s += __ldcg(p + q);
-            s = warp_sum(s);
-            mine += (double)(float)(s / ((double)T.O * (double)T.L));
+            for (int q = q0; q < q1; ++q) s += dp_sm[q];
+            dp_sm[a.dp_doubles + t] = (double)(float)(s / dec_n[t]);
         }
-        if (lane == 0) s_red[warp] = mine;
         __syncthreads();
         if (tid == 0) {
             double tot = 0.0;
-#pragma unroll
-            for (int q = 0; q < kC3Warps; ++q) tot += s_red[q];
+            for (int t = 0; t < a.n_tensors; ++t) tot += dp_sm[a.dp_doubles + t];
             if (fabs(diff - tot) > 1e-9) { stall = 0; diff = tot; } else { stall += 1; }   // :110-115
             iters += 1;
             st_diff = diff; st_stall = stall; st_iters = iters;
@@ -351,7 +463,7 @@ cle3_kernel(Cle3Args a) {
 
     // ---- write back
     for (int i = 0; i < ch.len; ++i) {
-        const DfqCle3Tensor T = a.tensors[ch.t0 + i];
+        const DfqCle3Tensor &T = s_T[i];
         const int n = s_nrows[i] * T.L;
         float *__restrict__ dst = T.W + (size_t)s_row0[i] * T.L;
         const float *src = sm + s_off[i];
@@ -465,7 +577,9 @@ extern "C" int dfq_cle3_plan_host(const DfqClePair *pairs, int n_pairs, const Df
                 }
             }
         fvec = (fvec + 3) & ~3; cpw = (cpw + 7) & ~7; maxrows = (maxrows + 3) & ~3;
-        return fvec + cpw + 3 * maxrows + 4;
+        int dpn = 0;
+        for (int c = 0; c < n_chains; ++c) dpn += Gs[c] * spans[c].second;
+        return fvec + cpw + 5 * maxrows + 2 * (dpn + 3 * n_layers) + 8;
     };
     auto data_floats = [&](int c, int G) {
         long long worst = 0;
@@ -474,7 +588,7 @@ extern "C" int dfq_cle3_plan_host(const DfqClePair *pairs, int n_pairs, const Df
             for (int i = 0; i < spans[c].second; ++i) {
                 const Tmp &T = tt[order[spans[c].first + i]];
                 const int nr = rows_of(T.O, g, G);
-                f += (long long)nr * T.L + (T.down >= 0 ? 4 * nr : 0);
+                f += (((long long)nr * T.L + 3) & ~3LL) + (T.down >= 0 ? 4 * nr : 0);
             }
             worst = std::max(worst, f);
         }
