@@ -267,6 +267,7 @@ class EvalPlan:
                 lib.dfq_minmax_rows_f32(*in_args, stream()), "dfq_minmax_rows_f32")))
         self.out_of = {st["name"]: st["out"] for st in steps}
         self.op_info = {}
+        self.step_io = {}            # name -> operands / range slots / output / launch closure (teacher_force)
         for st in steps:
             kind = st["kind"]
             if kind == "conv":
@@ -335,6 +336,10 @@ class EvalPlan:
             elif st["kind"] in ("pad", "pool", "interp", "cat"):
                 op = self._torch_op if self.move_impl == "torch" else self._move_op
                 self.ops.append((st["name"], op(st, f32, slot_ptr)))
+            slots_of = [st[k] for k in ("slot", "slot_a", "slot_b") if st.get(k) is not None] + list(st.get("slots", ()))
+            bits_of = [int(self.measures[i][0].num_bits) for i in slots_of]
+            self.step_io[st["name"]] = {"kind": st["kind"], "srcs": ins_of(st), "slots": slots_of, "bits": bits_of,
+                                        "out": st["out"], "relu": st.get("relu", 0), "fn": self.ops[-1][1]}
             out = st["out"]
             if out.by_torch and out.need_stats:       # extrema of what the torch op wrote (plain floats)
                 sargs = (out.buf.data_ptr(), N, out.numel // N, out.stats.data_ptr())
@@ -489,6 +494,23 @@ class EvalPlan:
         self.stats.zero_()
         for _name, fn in self.ops:
             fn()
+
+    def teacher_force(self, name, inputs, ranges):
+        """Run ONE op of the plan on given operands and given (min, max) ranges -- the reference's input activation
+        and the range its QuantMeasure quantised with (tests/golden/eval_tf_*.npz) -- and return the op's output.
+        The range slots are written directly ({min, max, scale, 0}, scale as utils/quantize.py:51-68 forms it), no
+        measure kernel runs."""
+        io = self.step_io[name]
+        assert len(inputs) == len(io["srcs"]) and len(ranges) == len(io["slots"]), name
+        for t, x in zip(io["srcs"], inputs):
+            t.buf.copy_(x.reshape(t.buf.shape))
+        for idx, bits, (lo, hi) in zip(io["slots"], io["bits"], ranges):
+            p = L.DfqQuantParams()
+            L.lib().dfq_quant_params_host(float(lo), float(hi), int(bits), 0, ctypes.byref(p))
+            self.slots[idx].copy_(torch.tensor([float(lo), float(hi), p.scale, 0.0], dtype=torch.float32))
+        self.stats.zero_()
+        io["fn"]()
+        return io["out"].buf.clone()
 
     def debug_run(self, x):
         """Forward that also returns a clone of every op's output (diagnostics; buffers are reused in the plan)."""
