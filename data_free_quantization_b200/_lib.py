@@ -101,8 +101,27 @@ class DfqConvI8Desc(ctypes.Structure):
                                    "relu")] + [("s_w", f32), ("c_w", f32), ("scratch", c_void), ("o_cap", i32), ("reserved", i32)]
 
 
+class DfqPwQ8Desc(ctypes.Structure):
+    _fields_ = [("x", c_void), ("wpk", c_void), ("wr", c_void), ("bias", c_void), ("in_slot", c_void),
+                ("y0", c_void), ("out_slot0", c_void), ("y1", c_void), ("out_slot1", c_void), ("yf", c_void),
+                ("yf_g", i64), ("yf_o", i64), ("G", i64), ("K", i32), ("O", i32), ("relu", i32), ("o_cap", i32),
+                ("s_w", f32), ("c_w", f32)]
+
+
+class DfqDwQ8Desc(ctypes.Structure):
+    _fields_ = [("x", c_void), ("w9", c_void), ("bias", c_void), ("in_slot", c_void), ("y0", c_void),
+                ("out_slot0", c_void), ("y1", c_void), ("out_slot1", c_void)] + \
+               [(k, i32) for k in ("N", "H", "W", "C", "stride", "relu")]
+
+
+class DfqStemQ8Desc(ctypes.Structure):
+    _fields_ = [("x", c_void), ("w", c_void), ("bias", c_void), ("in_slot", c_void), ("y0", c_void),
+                ("out_slot0", c_void), ("y1", c_void), ("out_slot1", c_void)] + \
+               [(k, i32) for k in ("N", "H", "W", "O", "stride", "pad", "relu", "reserved")]
+
+
 Q_SYMMETRIC, Q_RANGE_F32, Q_PER_CHANNEL, Q_CLAMP_OUT = 1, 2, 4, 8
-ABI_VERSION = 13
+ABI_VERSION = 14
 
 # every symbol include/dfq_b200.h declares: (restype, argtypes)
 P = ctypes.POINTER
@@ -141,6 +160,15 @@ PROTOTYPES = {
     "dfq_conv_i8_k_host": (ctypes.c_int, [ctypes.c_int, ctypes.c_int, ctypes.c_int]),
     "dfq_conv_i8_scratch_bytes": (i64, [ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int]),
     "dfq_conv_i8": (ctypes.c_int, [P(DfqConvI8Desc), c_void]),
+    "dfq_pw_q8_plan_host": (ctypes.c_int, [ctypes.c_int, ctypes.c_int, ctypes.c_int, P(ctypes.c_int), P(ctypes.c_int),
+                                           P(ctypes.c_int), P(ctypes.c_int), P(i64)]),
+    "dfq_pw_q8_pack_host": (ctypes.c_int, [c_void, ctypes.c_int, ctypes.c_int, ctypes.c_int, c_void]),
+    "dfq_pw_q8": (ctypes.c_int, [P(DfqPwQ8Desc), c_void]),
+    "dfq_dw_q8": (ctypes.c_int, [P(DfqDwQ8Desc), c_void]),
+    "dfq_stem_q8": (ctypes.c_int, [P(DfqStemQ8Desc), c_void]),
+    "dfq_add_q8": (ctypes.c_int, [c_void, c_void, c_void, c_void, c_void, c_void, c_void, c_void, i64, ctypes.c_int,
+                                  c_void]),
+    "dfq_mean_q8": (ctypes.c_int, [c_void, c_void, c_void, c_void, c_void, i64, ctypes.c_int, ctypes.c_int, c_void]),
     "dfq_quant_plan_host": (ctypes.c_int, [P(DfqQuantDesc), ctypes.c_int, P(i64), P(i64)]),
     "dfq_fake_quant_multi_f32": (ctypes.c_int, [c_void, ctypes.c_int, i64, i64, c_void, c_void]),
     "dfq_dequant_codes_f32": (ctypes.c_int, [c_void, ctypes.c_int, c_void, i64, i64, c_void, c_void]),

@@ -1,0 +1,717 @@
+// Kernel (e), static-range form: the quantised eval forward with every QuantMeasure in `update_stat == False` mode
+// (utils/quantize.py:119-126: the range is running_min / running_max as set_quant_minmax left them), so a consumer's
+// grid is known before its producer runs.  Activations never exist as fp32 in HBM: every producer requantises in its
+// epilogue to the grid(s) of its consumer(s) and writes CENTRED s8 CODES, NHWC with the channels padded to 16
+// (a = code - 128, x_hat = s * code + min; pad bytes are s8 zeros), 4x fewer activation bytes than the dynamic-range
+// plan (eval_plan.py) and no quantiser in front of the tensor cores:
+//
+//   pwq8_kernel   1 x 1 convolutions / linear layers: persistent, warp-specialised tcgen05 GEMM.
+//                 warp 0   one lane: the A tile (128 pixels x 128 K bytes) arrives by TENSOR-MAP TMA
+//                          (cp.async.bulk.tensor.2d, SWIZZLE_128B) straight in the UMMA K-major layout, the weight slab
+//                          by a bulk copy of the pre-packed canonical layout, both on the stage's `full` mbarrier;
+//                 warp 1   one lane: tcgen05.mma.kind::i8 (s8 x s8 -> s32) into one of TWO TMEM accumulators,
+//                          tcgen05.commit frees the stage / publishes the accumulator;
+//                 warps 2-9 epilogue: tcgen05.ld, y = s_x s_w acc + s_x c_w SUM_k a + c_x s_w SUM_k b + K c_x c_w + bias
+//                          (SUM_k a comes out of the MMA itself: the packed weights carry a row of ones), ReLU, the
+//                          consumer's exact quantiser (utils/quantize.py:72-74), 16 codes per 128-bit store; or fp32
+//                          (the classifier's logits).  The epilogue of tile i overlaps the loads and MMAs of tile i+1.
+//   dwq8_kernel   depthwise 3 x 3 (pad 1, stride 1 / 2) on CUDA cores: codes -> the exact fp32 values of the
+//                 reference's quantiser, 9 FMAs per output in the order of the fp32 kernels, requantise, pack.
+//   stemq8_kernel 3 -> O dense 3 x 3 stem from the fp32 NCHW image (quantised on load with the first measure's range).
+//   addq8_kernel  residual add of two code tensors on different grids (utils/layer_transform.py:18-32).
+//   meanq8_kernel spatial mean (utils/layer_transform.py:79-95) feeding the classifier's grid.
+#include <cuda.h>
+#include "common.cuh"
+
+namespace dfq {
+namespace {
+
+constexpr int kQM = 128;                 // pixels per tile (UMMA M, TMEM lanes)
+constexpr int kQSlab = 128;              // K bytes per ring stage (one SWIZZLE_128B row; up to 4 MMAs of K = 32)
+constexpr int kQASlab = kQM * kQSlab;    // 16 KB
+constexpr int kQThreads = 320;           // warp 0 TMA, warp 1 MMA, warps 2..9 epilogue
+constexpr int kQMaxStages = 8;
+constexpr int kQSpin = 1 << 26;          // bounded mbarrier spin: a protocol bug traps instead of hanging the GPU
+
+struct PwQ8Args {
+    const int8_t *wpk; const float *wr; const float *bias; const RangeSlot *in_slot;
+    const RangeSlot *out_slot[2]; int8_t *y[2]; int cp_out;
+    float *yf; int64_t yf_g, yf_o;
+    int64_t G, tiles;
+    int K, Kp, O, relu, n_pass, o_per_pass, npass, slabs, tmem_cols, stages;
+    float s_w, c_w;
+};
+
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    uint32_t ok = 0;
+    for (int spin = 0; spin < kQSpin; ++spin) {
+        asm volatile("{\n\t.reg .pred p;\n\t"
+                     "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+                     "selp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+        if (ok) return;
+    }
+    __trap();
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void *src, uint32_t bytes, uint32_t bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap *map, int c0, int c1, uint32_t bar) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+                 ::"r"(dst), "l"(map), "r"(c0), "r"(c1), "r"(bar) : "memory");
+}
+// K-major operand, SWIZZLE_128B: rows of 128 bytes, 8-row groups 1024 bytes apart (SBO), 16-byte chunks XOR-swizzled
+// by the row -- what the TMA writes for a {128 B, 128 rows} box.  The K offset of an MMA goes into the start address.
+__device__ __forceinline__ uint64_t desc_sw128(uint32_t addr) {
+    return (uint64_t)((addr & 0x3FFFFu) >> 4) | ((uint64_t)1 << 16) | ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) |
+           (2ull << 61);
+}
+// K-major operand, no swizzle: 8-row x 16-byte core matrices; LBO = step between 16-byte K chunks, SBO = 8-row groups
+__device__ __forceinline__ uint64_t desc_plain(uint32_t addr, uint32_t lbo, uint32_t sbo) {
+    return (uint64_t)((addr & 0x3FFFFu) >> 4) | ((uint64_t)(lbo >> 4) << 16) | ((uint64_t)(sbo >> 4) << 32) |
+           (1ull << 46);
+}
+__device__ __forceinline__ void umma_i8(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                        uint32_t accumulate) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n\t}"
+                 ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+// The integer code of utils/quantize.py:72-74 in the low byte of the result (see quant_code, common.cuh)
+__device__ __forceinline__ uint32_t code_bits(float x, const QuantConsts &c) {
+    const float t = __fadd_rn(x, c.neg_min);
+    if (c.fast) {                                           // block-uniform
+        const float magic = 12582912.0f;
+        const float cl = fminf(fmaxf(__fmul_rn(t, c.rscale), c.qmin), c.qmax);
+        float m = __fadd_rn(cl, magic);
+        if (fabsf(__fsub_rn(cl, __fadd_rn(m, -magic))) > c.amb) {          // within a few ulp of a tie: exact division
+            const float tc = fminf(fmaxf(t, c.t_lo), c.t_hi);
+            m = __fadd_rn(fminf(fmaxf(div_const_rn(tc, c.scale, c.rscale), c.qmin), c.qmax), magic);
+        }
+        return __float_as_uint(m);
+    }
+    return (uint32_t)__float2int_rn(fminf(fmaxf(__fdiv_rn(t, c.scale), c.qmin), c.qmax));
+}
+// four values -> four centred s8 codes in one word
+__device__ __forceinline__ uint32_t pack4(float v0, float v1, float v2, float v3, const QuantConsts &c) {
+    const uint32_t b0 = code_bits(v0, c), b1 = code_bits(v1, c), b2 = code_bits(v2, c), b3 = code_bits(v3, c);
+    const uint32_t lo = __byte_perm(b0, b1, 0x0040), hi = __byte_perm(b2, b3, 0x0040);
+    return __byte_perm(lo, hi, 0x5410) ^ 0x80808080u;
+}
+// centred s8 code word -> the four fp32 values the reference's quantiser produced: fl(fl(code * s) + min)
+__device__ __forceinline__ void dequant4(uint32_t w, float s, float mn, float *out) {
+    const uint32_t u = w ^ 0x80808080u;                                     // codes 0..255
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const float q = __fadd_rn(__uint_as_float(__byte_perm(u, 0x4B000000u, 0x7650 + i)), -8388608.0f);
+        out[i] = __fadd_rn(__fmul_rn(q, s), mn);
+    }
+}
+
+__global__ void __launch_bounds__(kQThreads, 1)
+pwq8_kernel(const __grid_constant__ CUtensorMap tmA, PwQ8Args a) {
+    extern __shared__ uint8_t smem_raw[];
+    __shared__ __align__(8) uint64_t bars[2 * kQMaxStages + 4];   // full[stages] | empty[stages] | tfull[2] | tempty[2]
+    __shared__ uint32_t tmem_base_s;
+    __shared__ __align__(16) float chan_c[256];
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    const uint32_t bslab = (uint32_t)a.npass * kQSlab;
+    const uint32_t sA_u = smem_u32(smem), sB_u = sA_u + (uint32_t)a.stages * kQASlab;
+    const uint32_t full0 = smem_u32(&bars[0]), empty0 = full0 + 8 * kQMaxStages, tfull0 = empty0 + 8 * kQMaxStages,
+                   tempty0 = tfull0 + 16;
+    const int pass = blockIdx.x % a.n_pass;
+    const int64_t tile0 = blockIdx.x / a.n_pass, tstep = gridDim.x / a.n_pass;
+    const int o0 = pass * a.o_per_pass, n_real = min(a.o_per_pass, a.O - o0);
+
+    if (tid == 0) {
+        for (int i = 0; i < a.stages; ++i) { mbar_init(full0 + 8 * i, 1); mbar_init(empty0 + 8 * i, 1); }
+        mbar_init(tfull0, 1); mbar_init(tfull0 + 8, 1);
+        mbar_init(tempty0, 8); mbar_init(tempty0 + 8, 8);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&tmA) : "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
+                     ::"r"(smem_u32(&tmem_base_s)), "r"((uint32_t)a.tmem_cols) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    const RangeSlot in = *a.in_slot;
+    const float sx = in.scale;
+    const float cx = __fmaf_rn(128.0f, sx, in.mn);           // x_hat = sx * a + cx with a = code - 128
+    if (tid < 256) {
+        float c = 0.0f;
+        if (tid < n_real) {
+            const int o = o0 + tid;
+            c = __fmaf_rn(cx, __ldg(a.wr + o), __fmul_rn(__fmul_rn((float)a.K, a.c_w), cx));
+            if (a.bias) c = __fadd_rn(c, __ldg(a.bias + o));
+        }
+        chan_c[tid] = c;
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = tmem_base_s;
+
+    if (warp == 0) {
+        // ===== producer: TMA tensor-map loads of A, bulk copies of the packed weight slabs
+        if (lane == 0) {
+            const int8_t *wsrc = a.wpk + (int64_t)pass * a.slabs * bslab;
+            int stage = 0; uint32_t phase = 0;
+            for (int64_t tile = tile0; tile < a.tiles; tile += tstep) {
+                for (int s = 0; s < a.slabs; ++s) {
+                    mbar_wait(empty0 + 8 * stage, phase ^ 1);
+                    mbar_expect_tx(full0 + 8 * stage, kQASlab + bslab);
+                    tma_load_2d(sA_u + stage * kQASlab, &tmA, s * kQSlab, (int)(tile * kQM), full0 + 8 * stage);
+                    bulk_g2s(sB_u + stage * bslab, wsrc + (int64_t)s * bslab, bslab, full0 + 8 * stage);
+                    if (++stage == a.stages) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===== MMA issuer
+        if (lane == 0) {
+            // D = s32, A = B = s8, both K-major, N = npass, M = 128
+            const uint32_t idesc = (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(a.npass >> 3) << 17) |
+                                   ((uint32_t)(kQM >> 4) << 24);
+            int stage = 0; uint32_t phase = 0;
+            int acc = 0; uint32_t aphase = 0;
+            for (int64_t tile = tile0; tile < a.tiles; tile += tstep) {
+                mbar_wait(tempty0 + 8 * acc, aphase ^ 1);
+                tc_fence_after();
+                const uint32_t d = tmem + (uint32_t)(acc * a.npass);
+                for (int s = 0; s < a.slabs; ++s) {
+                    mbar_wait(full0 + 8 * stage, phase);
+                    tc_fence_after();
+                    const int kb = min(kQSlab, a.Kp - s * kQSlab);
+                    const int nk = (kb + 31) >> 5;
+                    for (int kk = 0; kk < nk; ++kk) {
+                        const uint64_t ad = desc_sw128(sA_u + stage * kQASlab + kk * 32);
+                        const uint64_t bd = desc_plain(sB_u + stage * bslab + kk * 2 * (a.npass * 16), a.npass * 16, 128);
+                        umma_i8(d, ad, bd, idesc, (s | kk) != 0);
+                    }
+                    umma_commit(empty0 + 8 * stage);
+                    if (++stage == a.stages) { stage = 0; phase ^= 1; }
+                }
+                umma_commit(tfull0 + 8 * acc);
+                if (++acc == 2) { acc = 0; aphase ^= 1; }
+            }
+        }
+    } else {
+        // ===== epilogue: warp w reads TMEM lanes 32 * (w % 4) .., the two warps of a lane group take alternate chunks
+        const int lg = warp & 3, half = (warp - 2) >> 2;
+        const int row = 32 * lg + lane;
+        QuantConsts q0, q1;
+        const bool has0 = a.y[0] != nullptr, has1 = a.y[1] != nullptr;
+        if (has0) q0 = consts_from_slot(*a.out_slot[0], 8, 0, 0.f, 0.f);
+        if (has1) q1 = consts_from_slot(*a.out_slot[1], 8, 0, 0.f, 0.f);
+        const float fa = __fmul_rn(sx, a.s_w), fr = __fmul_rn(sx, a.c_w);
+        const float floor_v = a.relu ? 0.0f : -INFINITY;
+        int acc = 0; uint32_t aphase = 0;
+        for (int64_t tile = tile0; tile < a.tiles; tile += tstep) {
+            const int64_t g = tile * kQM + row;
+            const bool valid = g < a.G;
+            mbar_wait(tfull0 + 8 * acc, aphase);
+            tc_fence_after();
+            const uint32_t tbase = tmem + ((uint32_t)(32 * lg) << 16) + (uint32_t)(acc * a.npass);
+            uint32_t rs;
+            asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];" : "=r"(rs) : "r"(tbase + (uint32_t)n_real));
+            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+            const float row_c = __fmul_rn(fr, (float)(int)rs);               // s_x c_w SUM_k a[p,k]
+            for (int chunk = half; chunk * 16 < n_real; chunk += 2) {
+                uint32_t d[16];
+                asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, "
+                             "%12, %13, %14, %15}, [%16];"
+                             : "=r"(d[0]), "=r"(d[1]), "=r"(d[2]), "=r"(d[3]), "=r"(d[4]), "=r"(d[5]), "=r"(d[6]),
+                               "=r"(d[7]), "=r"(d[8]), "=r"(d[9]), "=r"(d[10]), "=r"(d[11]), "=r"(d[12]), "=r"(d[13]),
+                               "=r"(d[14]), "=r"(d[15])
+                             : "r"(tbase + (uint32_t)(chunk * 16)));
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                const int nv = min(16, n_real - chunk * 16);                 // warp-uniform
+                float yv[16];
+#pragma unroll
+                for (int j = 0; j < 16; ++j)
+                    yv[j] = fmaxf(__fmaf_rn(fa, (float)(int)d[j], __fadd_rn(row_c, chan_c[chunk * 16 + j])), floor_v);
+                if (valid) {
+                    if (a.yf) {
+                        float *py = a.yf + g * a.yf_g + (int64_t)(o0 + chunk * 16) * a.yf_o;
+#pragma unroll
+                        for (int j = 0; j < 16; ++j)
+                            if (j < nv) py[(int64_t)j * a.yf_o] = yv[j];
+                    }
+#pragma unroll
+                    for (int t = 0; t < 2; ++t) {
+                        if (!(t ? has1 : has0)) continue;
+                        const QuantConsts &qc = t ? q1 : q0;
+                        uint32_t w4[4];
+#pragma unroll
+                        for (int j4 = 0; j4 < 4; ++j4) {
+                            uint32_t w = pack4(yv[4 * j4], yv[4 * j4 + 1], yv[4 * j4 + 2], yv[4 * j4 + 3], qc);
+                            // channels past the layer's last one (padding up to a multiple of 16): s8 zero
+                            const int left = nv - 4 * j4;
+                            if (left < 4) w = left <= 0 ? 0u : (w & (0xffffffffu >> (8 * (4 - left))));
+                            w4[j4] = w;
+                        }
+                        *reinterpret_cast<uint4 *>(a.y[t] + g * a.cp_out + o0 + chunk * 16) =
+                            make_uint4(w4[0], w4[1], w4[2], w4[3]);
+                    }
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(tempty0 + 8 * acc);
+            if (++acc == 2) { acc = 0; aphase ^= 1; }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1)
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"((uint32_t)a.tmem_cols)
+                     : "memory");
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Depthwise 3 x 3, pad 1, stride 1 or 2, NHWC codes in and out.  A thread owns 4 channels (one 32-bit code word) of a
+// strip of output pixels along a row and slides a 3 x 3 window of dequantised values through registers; consecutive
+// threads take consecutive channel words (coalesced 128-byte rows of a pixel).
+struct DwQ8Args {
+    const int8_t *x; const float *w9; const float *bias; const RangeSlot *in_slot;
+    const RangeSlot *out_slot[2]; int8_t *y[2];
+    int N, H, W, OH, OW, C, Cp, stride, relu, strip, strips;
+};
+
+template <int S>
+__global__ void __launch_bounds__(kThreads)
+dwq8_kernel(DwQ8Args a) {
+    const int cw = a.Cp >> 2;                                     // channel words per pixel
+    const int64_t idx = (int64_t)blockIdx.x * kThreads + threadIdx.x;
+    const int64_t total = (int64_t)a.N * a.OH * a.strips * cw;
+    if (idx >= total) return;
+    const int cg = (int)(idx % cw);
+    int64_t rest = idx / cw;
+    const int sp = (int)(rest % a.strips); rest /= a.strips;
+    const int oy = (int)(rest % a.OH);
+    const int n = (int)(rest / a.OH);
+    const int c0 = cg * 4;
+    const RangeSlot in = *a.in_slot;
+    const float sx = in.scale, mn = in.mn;
+    const bool has1 = a.y[1] != nullptr;
+    const QuantConsts q0 = consts_from_slot(*a.out_slot[0], 8, 0, 0.f, 0.f);
+    QuantConsts q1 = q0;
+    if (has1) q1 = consts_from_slot(*a.out_slot[1], 8, 0, 0.f, 0.f);
+    float wt[9][4], b4[4];
+#pragma unroll
+    for (int t = 0; t < 9; ++t) {
+        const float4 v = __ldg(reinterpret_cast<const float4 *>(a.w9 + (int64_t)t * a.Cp + c0));
+        wt[t][0] = v.x; wt[t][1] = v.y; wt[t][2] = v.z; wt[t][3] = v.w;
+    }
+    {
+        const float4 v = a.bias ? __ldg(reinterpret_cast<const float4 *>(a.bias + c0)) : make_float4(0.f, 0.f, 0.f, 0.f);
+        b4[0] = v.x; b4[1] = v.y; b4[2] = v.z; b4[3] = v.w;
+    }
+    const int ox0 = sp * a.strip, ox1 = min(a.OW, ox0 + a.strip);
+    const int iy0 = oy * S - 1;
+    const int8_t *xn = a.x + (int64_t)n * a.H * a.W * a.Cp + c0;
+    // column `ix` of the window: three rows of four dequantised channels (exact zeros outside the image)
+    auto load_col = [&](int ix, float (&col)[3][4]) {
+#pragma unroll
+        for (int r = 0; r < 3; ++r) {
+            const int iy = iy0 + r;
+            if ((unsigned)iy < (unsigned)a.H && (unsigned)ix < (unsigned)a.W) {
+                const uint32_t w = __ldg(reinterpret_cast<const uint32_t *>(xn + ((int64_t)iy * a.W + ix) * a.Cp));
+                dequant4(w, sx, mn, col[r]);
+            } else {
+                col[r][0] = col[r][1] = col[r][2] = col[r][3] = 0.0f;
+            }
+        }
+    };
+    float win[3][3][4];                                           // [column][row][channel]
+    const int ixs = ox0 * S - 1;
+    load_col(ixs, win[0]);
+    load_col(ixs + 1, win[1]);
+    const float floor_v = a.relu ? 0.0f : -INFINITY;
+    const int64_t orow = ((int64_t)n * a.OH + oy) * a.OW;
+    for (int ox = ox0; ox < ox1; ++ox) {
+        load_col(ox * S + 1, win[2]);
+        float acc[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+        for (int i = 0; i < 3; ++i)                               // tap order (i, j) row-major, as the fp32 kernels
+#pragma unroll
+            for (int j = 0; j < 3; ++j)
+#pragma unroll
+                for (int c = 0; c < 4; ++c) acc[c] = __fmaf_rn(win[j][i][c], wt[i * 3 + j][c], acc[c]);
+        float yv[4];
+#pragma unroll
+        for (int c = 0; c < 4; ++c) yv[c] = fmaxf(__fadd_rn(acc[c], b4[c]), floor_v);
+        const int left = a.C - c0;
+        const uint32_t mask = left >= 4 ? 0xffffffffu : (left <= 0 ? 0u : (0xffffffffu >> (8 * (4 - left))));
+        const int64_t off = (orow + ox) * a.Cp + c0;
+        *reinterpret_cast<uint32_t *>(a.y[0] + off) = pack4(yv[0], yv[1], yv[2], yv[3], q0) & mask;
+        if (has1) *reinterpret_cast<uint32_t *>(a.y[1] + off) = pack4(yv[0], yv[1], yv[2], yv[3], q1) & mask;
+        if (S == 1) {
+#pragma unroll
+            for (int r = 0; r < 3; ++r)
+#pragma unroll
+                for (int c = 0; c < 4; ++c) { win[0][r][c] = win[1][r][c]; win[1][r][c] = win[2][r][c]; }
+        } else {
+#pragma unroll
+            for (int r = 0; r < 3; ++r)
+#pragma unroll
+                for (int c = 0; c < 4; ++c) win[0][r][c] = win[2][r][c];
+            if (ox + 1 < ox1) load_col((ox + 1) * S, win[1]);
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Stem: dense 3 x 3, 3 input channels, stride 2, pad 1, fp32 NCHW image in (quantised on load with the first
+// measure's static range), O <= 32 output channels, codes out.  One thread per output pixel, all channels.
+struct StemQ8Args {
+    const float *x; const float *w; const float *bias; const RangeSlot *in_slot;
+    const RangeSlot *out_slot[2]; int8_t *y[2];
+    int N, H, W, OH, OW, O, Cp, stride, pad, relu;
+};
+
+__global__ void __launch_bounds__(kThreads)
+stemq8_kernel(StemQ8Args a) {
+    __shared__ __align__(16) float sw[27][32];
+    __shared__ float sb[32];
+    for (int i = threadIdx.x; i < 27 * 32; i += kThreads) {
+        const int t = i >> 5, o = i & 31;
+        sw[t][o] = o < a.O ? __ldg(a.w + (int64_t)o * 27 + t) : 0.0f;
+    }
+    if (threadIdx.x < 32) sb[threadIdx.x] = (a.bias && threadIdx.x < a.O) ? __ldg(a.bias + threadIdx.x) : 0.0f;
+    __syncthreads();
+    const int64_t p = (int64_t)blockIdx.x * kThreads + threadIdx.x;
+    const int64_t total = (int64_t)a.N * a.OH * a.OW;
+    if (p >= total) return;
+    const int ox = (int)(p % a.OW);
+    const int oy = (int)((p / a.OW) % a.OH);
+    const int n = (int)(p / ((int64_t)a.OW * a.OH));
+    const QuantConsts qi = consts_from_slot(*a.in_slot, 8, 0, 0.f, 0.f);
+    float xin[27];
+#pragma unroll
+    for (int c = 0; c < 3; ++c)
+#pragma unroll
+        for (int i = 0; i < 3; ++i)
+#pragma unroll
+            for (int j = 0; j < 3; ++j) {
+                const int iy = oy * a.stride - a.pad + i, ix = ox * a.stride - a.pad + j;
+                float v = 0.0f;
+                if ((unsigned)iy < (unsigned)a.H && (unsigned)ix < (unsigned)a.W)
+                    v = quant_dequant(__ldg(a.x + (((int64_t)n * 3 + c) * a.H + iy) * a.W + ix), qi);
+                xin[(c * 3 + i) * 3 + j] = v;
+            }
+    const bool has1 = a.y[1] != nullptr;
+    const QuantConsts q0 = consts_from_slot(*a.out_slot[0], 8, 0, 0.f, 0.f);
+    QuantConsts q1 = q0;
+    if (has1) q1 = consts_from_slot(*a.out_slot[1], 8, 0, 0.f, 0.f);
+    const float floor_v = a.relu ? 0.0f : -INFINITY;
+    for (int ob = 0; ob < a.Cp; ob += 16) {
+        float acc[16];
+#pragma unroll
+        for (int t = 0; t < 16; ++t) acc[t] = 0.0f;
+#pragma unroll
+        for (int t = 0; t < 27; ++t) {
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const float4 w = *reinterpret_cast<const float4 *>(&sw[t][ob + 4 * q]);
+                acc[4 * q] = __fmaf_rn(xin[t], w.x, acc[4 * q]);
+                acc[4 * q + 1] = __fmaf_rn(xin[t], w.y, acc[4 * q + 1]);
+                acc[4 * q + 2] = __fmaf_rn(xin[t], w.z, acc[4 * q + 2]);
+                acc[4 * q + 3] = __fmaf_rn(xin[t], w.w, acc[4 * q + 3]);
+            }
+        }
+        float yv[16];
+#pragma unroll
+        for (int t = 0; t < 16; ++t) yv[t] = fmaxf(__fadd_rn(acc[t], sb[ob + t]), floor_v);
+#pragma unroll
+        for (int t2 = 0; t2 < 2; ++t2) {
+            if (t2 && !has1) continue;
+            const QuantConsts &qc = t2 ? q1 : q0;
+            uint32_t w4[4];
+#pragma unroll
+            for (int j4 = 0; j4 < 4; ++j4) {
+                uint32_t w = pack4(yv[4 * j4], yv[4 * j4 + 1], yv[4 * j4 + 2], yv[4 * j4 + 3], qc);
+                const int left = a.O - ob - 4 * j4;
+                if (left < 4) w = left <= 0 ? 0u : (w & (0xffffffffu >> (8 * (4 - left))));
+                w4[j4] = w;
+            }
+            *reinterpret_cast<uint4 *>(a.y[t2] + p * a.Cp + ob) = make_uint4(w4[0], w4[1], w4[2], w4[3]);
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Residual add: out = Q_a(x_a) + Q_b(x_b) from the two operands' code tensors (utils/layer_transform.py:18-32),
+// requantised to the grid(s) of the consumer(s).  16 elements per thread.
+__global__ void __launch_bounds__(kThreads)
+addq8_kernel(const int8_t *__restrict__ xa, const int8_t *__restrict__ xb, const RangeSlot *sa, const RangeSlot *sb,
+             int8_t *y0, const RangeSlot *s0, int8_t *y1, const RangeSlot *s1, int64_t n16, int C, int Cp) {
+    const int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x;
+    if (i >= n16) return;
+    const RangeSlot ra = *sa, rb = *sb;
+    const QuantConsts q0 = consts_from_slot(*s0, 8, 0, 0.f, 0.f);
+    QuantConsts q1 = q0;
+    if (y1) q1 = consts_from_slot(*s1, 8, 0, 0.f, 0.f);
+    const uint4 va = __ldg(reinterpret_cast<const uint4 *>(xa) + i), vb = __ldg(reinterpret_cast<const uint4 *>(xb) + i);
+    const uint32_t wa[4] = {va.x, va.y, va.z, va.w}, wb[4] = {vb.x, vb.y, vb.z, vb.w};
+    const int cbase = (int)((i * 16) % Cp);
+    uint32_t o0[4], o1[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        float fa[4], fb[4], s[4];
+        dequant4(wa[j], ra.scale, ra.mn, fa);
+        dequant4(wb[j], rb.scale, rb.mn, fb);
+#pragma unroll
+        for (int c = 0; c < 4; ++c) s[c] = __fadd_rn(fa[c], fb[c]);
+        const int left = C - cbase - 4 * j;
+        const uint32_t mask = left >= 4 ? 0xffffffffu : (left <= 0 ? 0u : (0xffffffffu >> (8 * (4 - left))));
+        o0[j] = pack4(s[0], s[1], s[2], s[3], q0) & mask;
+        o1[j] = y1 ? (pack4(s[0], s[1], s[2], s[3], q1) & mask) : 0u;
+    }
+    reinterpret_cast<uint4 *>(y0)[i] = make_uint4(o0[0], o0[1], o0[2], o0[3]);
+    if (y1) reinterpret_cast<uint4 *>(y1)[i] = make_uint4(o1[0], o1[1], o1[2], o1[3]);
+}
+
+// Spatial mean of Q(x) (utils/layer_transform.py:79-95 around x.mean(3).mean(2) / torch.mean): codes [N][HW][Cp] ->
+// fp32 mean per (n, c) in the order of dfq_qmean_f32 (32 partial sums over k = lane, lane + 32, ..., then the
+// shuffle tree), requantised to the consumer's grid -> codes [N][Cp_out], and / or written as fp32 [N][C].
+__global__ void __launch_bounds__(kThreads)
+meanq8_kernel(const int8_t *__restrict__ x, const RangeSlot *sin, int8_t *y, const RangeSlot *sout, float *yf,
+              int C, int Cp, int HW, int Cp_out) {
+    const int groups = (C + 7) / 8;
+    const int n = blockIdx.x / groups, c0 = (blockIdx.x % groups) * 8;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int c = c0 + warp;
+    if (c >= C) return;
+    const RangeSlot in = *sin;
+    const int8_t *p = x + (int64_t)n * HW * Cp + c;
+    float s = 0.0f;
+    for (int k = lane; k < HW; k += 32) {
+        const float q = (float)((int)p[(int64_t)k * Cp] + 128);
+        s = __fadd_rn(s, __fadd_rn(__fmul_rn(q, in.scale), in.mn));
+    }
+    s = warp_sum(s);
+    const float m = __fdiv_rn(s, (float)HW);
+    if (lane == 0) {
+        if (yf) yf[(int64_t)n * C + c] = m;
+        if (y) {
+            const QuantConsts qc = consts_from_slot(*sout, 8, 0, 0.f, 0.f);
+            y[(int64_t)n * Cp_out + c] = (int8_t)((code_bits(m, qc) & 0xffu) ^ 0x80u);
+        }
+    }
+}
+
+}  // namespace
+}  // namespace dfq
+
+using namespace dfq;
+
+// ---- host side --------------------------------------------------------------------------------------------------
+static int q8_plan(int O, int K, int o_cap, int *n_pass, int *o_per_pass, int *npass, int *slabs, int64_t *bytes) {
+    if (O <= 0 || K <= 0) return (int)cudaErrorInvalidValue;
+    int cap = o_cap > 0 ? (o_cap + 15) / 16 * 16 : 240;      // 240 real channels + the row of ones = 256 columns
+    if (cap > 240) cap = 240;
+    if (cap < 16) cap = 16;
+    int np = (O + cap - 1) / cap;
+    int opp = ((O + np - 1) / np + 15) / 16 * 16;             // equal passes, multiples of 16
+    np = (O + opp - 1) / opp;
+    const int Kp = (K + 15) / 16 * 16;
+    *n_pass = np; *o_per_pass = opp;
+    *npass = (opp + 1 + 15) / 16 * 16;                        // + the row of ones
+    *slabs = (Kp + kQSlab - 1) / kQSlab;
+    *bytes = (int64_t)np * *slabs * *npass * kQSlab;
+    return 0;
+}
+
+extern "C" int dfq_pw_q8_plan_host(int O, int K, int o_cap, int *n_pass, int *o_per_pass, int *npass, int *slabs,
+                                   int64_t *packed_bytes) {
+    return q8_plan(O, K, o_cap, n_pass, o_per_pass, npass, slabs, packed_bytes);
+}
+
+// codes: [O, K] centred weight codes (code - 128).  packed: [pass][slab][K chunk of 16 (8 per slab)][row][16 B], zero
+// padded; row n_real of every pass is the row of ones over the real K (its accumulator column is SUM_k a[p, k]).
+extern "C" int dfq_pw_q8_pack_host(const int8_t *codes, int O, int K, int o_cap, int8_t *packed) {
+    int np, opp, npass, slabs; int64_t bytes;
+    int e = q8_plan(O, K, o_cap, &np, &opp, &npass, &slabs, &bytes);
+    if (e) return e;
+    for (int64_t i = 0; i < bytes; ++i) packed[i] = 0;
+    auto at = [&](int pass, int row, int k) -> int8_t & {
+        const int slab = k / kQSlab, kc = (k % kQSlab) / 16, kb = k % 16;
+        return packed[((((int64_t)pass * slabs + slab) * 8 + kc) * npass + row) * 16 + kb];
+    };
+    for (int o = 0; o < O; ++o) {
+        const int pass = o / opp, ol = o - pass * opp;
+        for (int k = 0; k < K; ++k) at(pass, ol, k) = codes[(int64_t)o * K + k];
+    }
+    for (int pass = 0; pass < np; ++pass) {
+        const int n_real = (O - pass * opp) < opp ? (O - pass * opp) : opp;
+        for (int k = 0; k < K; ++k) at(pass, n_real, k) = 1;
+    }
+    return 0;
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn encode_tiled() {
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        void *p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = (EncodeTiledFn)p;
+    }
+    return fn;
+}
+
+extern "C" int dfq_pw_q8(const DfqPwQ8Desc *d, void *stream) {
+    if (!d || !d->x || !d->wpk || !d->wr || !d->in_slot || d->G <= 0 || (!d->y0 && !d->yf) || (d->y1 && !d->y0) ||
+        (d->y0 && !d->out_slot0) || (d->y1 && !d->out_slot1))
+        return (int)cudaErrorInvalidValue;
+    PwQ8Args a = {};
+    int64_t bytes;
+    int e = q8_plan(d->O, d->K, d->o_cap, &a.n_pass, &a.o_per_pass, &a.npass, &a.slabs, &bytes);
+    if (e) return e;
+    a.wpk = d->wpk; a.wr = d->wr; a.bias = d->bias; a.in_slot = (const RangeSlot *)d->in_slot;
+    a.out_slot[0] = (const RangeSlot *)d->out_slot0; a.out_slot[1] = (const RangeSlot *)d->out_slot1;
+    a.y[0] = d->y0; a.y[1] = d->y1; a.cp_out = (d->O + 15) / 16 * 16;
+    a.yf = d->yf; a.yf_g = d->yf_g; a.yf_o = d->yf_o;
+    a.G = d->G; a.tiles = (d->G + kQM - 1) / kQM;
+    a.K = d->K; a.Kp = (d->K + 15) / 16 * 16; a.O = d->O; a.relu = d->relu; a.s_w = d->s_w; a.c_w = d->c_w;
+    if (a.tiles * kQM > 0x7fffffffll) return (int)cudaErrorInvalidValue;
+    a.tmem_cols = 32;
+    while (a.tmem_cols < 2 * a.npass) a.tmem_cols *= 2;
+    const size_t stage_bytes = (size_t)kQASlab + (size_t)a.npass * kQSlab;
+    int stages = (int)((200 * 1024) / stage_bytes);
+    if (stages > kQMaxStages) stages = kQMaxStages;
+    const int64_t need = (int64_t)a.slabs * 2;                   // two tiles' worth of slabs in flight is plenty
+    if (stages > need && need >= 2) stages = (int)need;
+    if (stages < 2) return (int)cudaErrorInvalidValue;
+    a.stages = stages;
+    // one CTA per SM when the two accumulators need all 512 TMEM columns, else as many as fit (the allocation of a
+    // second CTA would otherwise spin): the shared-memory request is padded to enforce it
+    size_t smem = (size_t)stages * stage_bytes + 1024;
+    const int ctas_tmem = 512 / a.tmem_cols;
+    const size_t smem_cap = 227 * 1024;
+    {
+        const size_t floor_bytes = smem_cap / (size_t)(ctas_tmem + 1) + 1024;
+        if (smem < floor_bytes) smem = floor_bytes;
+    }
+    static size_t configured = 0;
+    if (configured < smem) {
+        cudaError_t ce = cudaFuncSetAttribute(pwq8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_cap);
+        if (ce != cudaSuccess) return (int)ce;
+        configured = smem_cap;
+    }
+    EncodeTiledFn enc = encode_tiled();
+    if (!enc) return (int)cudaErrorNotSupported;
+    CUtensorMap tm;
+    const cuuint64_t gdim[2] = {(cuuint64_t)a.Kp, (cuuint64_t)d->G};
+    const cuuint64_t gstr[1] = {(cuuint64_t)a.Kp};
+    const cuuint32_t box[2] = {(cuuint32_t)kQSlab, (cuuint32_t)kQM};
+    const cuuint32_t estr[2] = {1, 1};
+    CUresult r = enc(&tm, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, (void *)d->x, gdim, gstr, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return (int)cudaErrorInvalidValue;
+    int occ = 0;
+    cudaError_t ce = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, pwq8_kernel, kQThreads, smem);
+    if (ce != cudaSuccess) return (int)ce;
+    if (occ < 1) return (int)cudaErrorLaunchOutOfResources;
+    if (occ > ctas_tmem) occ = ctas_tmem;
+    int64_t per_pass = ((int64_t)sm_count() * occ) / a.n_pass;
+    if (per_pass < 1) per_pass = 1;
+    if (per_pass > a.tiles) per_pass = a.tiles;
+    const unsigned grid = (unsigned)(per_pass * a.n_pass);
+    pwq8_kernel<<<grid, kQThreads, smem, (cudaStream_t)stream>>>(tm, a);
+    g_launches += 1;
+    return (int)cudaGetLastError();
+}
+
+extern "C" int dfq_dw_q8(const DfqDwQ8Desc *d, void *stream) {
+    if (!d || !d->x || !d->w9 || !d->in_slot || !d->y0 || !d->out_slot0 || (d->y1 && !d->out_slot1) || d->N <= 0 ||
+        (d->stride != 1 && d->stride != 2))
+        return (int)cudaErrorInvalidValue;
+    DwQ8Args a = {};
+    a.x = d->x; a.w9 = d->w9; a.bias = d->bias; a.in_slot = (const RangeSlot *)d->in_slot;
+    a.out_slot[0] = (const RangeSlot *)d->out_slot0; a.out_slot[1] = (const RangeSlot *)d->out_slot1;
+    a.y[0] = d->y0; a.y[1] = d->y1;
+    a.N = d->N; a.H = d->H; a.W = d->W; a.C = d->C; a.Cp = (d->C + 15) / 16 * 16; a.stride = d->stride; a.relu = d->relu;
+    a.OH = (d->H + 2 - 3) / d->stride + 1; a.OW = (d->W + 2 - 3) / d->stride + 1;
+    a.strip = a.OW >= 56 ? 14 : (a.OW >= 14 ? 7 : a.OW);
+    a.strips = (a.OW + a.strip - 1) / a.strip;
+    const int64_t total = (int64_t)a.N * a.OH * a.strips * (a.Cp / 4);
+    const unsigned grid = (unsigned)((total + kThreads - 1) / kThreads);
+    if (d->stride == 1) dwq8_kernel<1><<<grid, kThreads, 0, (cudaStream_t)stream>>>(a);
+    else dwq8_kernel<2><<<grid, kThreads, 0, (cudaStream_t)stream>>>(a);
+    g_launches += 1;
+    return (int)cudaGetLastError();
+}
+
+extern "C" int dfq_stem_q8(const DfqStemQ8Desc *d, void *stream) {
+    if (!d || !d->x || !d->w || !d->in_slot || !d->y0 || !d->out_slot0 || (d->y1 && !d->out_slot1) || d->N <= 0 ||
+        d->O < 1 || d->O > 32)
+        return (int)cudaErrorInvalidValue;
+    StemQ8Args a = {};
+    a.x = d->x; a.w = d->w; a.bias = d->bias; a.in_slot = (const RangeSlot *)d->in_slot;
+    a.out_slot[0] = (const RangeSlot *)d->out_slot0; a.out_slot[1] = (const RangeSlot *)d->out_slot1;
+    a.y[0] = d->y0; a.y[1] = d->y1;
+    a.N = d->N; a.H = d->H; a.W = d->W; a.O = d->O; a.Cp = (d->O + 15) / 16 * 16; a.stride = d->stride; a.pad = d->pad;
+    a.relu = d->relu;
+    a.OH = (d->H + 2 * d->pad - 3) / d->stride + 1; a.OW = (d->W + 2 * d->pad - 3) / d->stride + 1;
+    const int64_t total = (int64_t)a.N * a.OH * a.OW;
+    stemq8_kernel<<<(unsigned)((total + kThreads - 1) / kThreads), kThreads, 0, (cudaStream_t)stream>>>(a);
+    g_launches += 1;
+    return (int)cudaGetLastError();
+}
+
+extern "C" int dfq_add_q8(const int8_t *xa, const int8_t *xb, const float *slot_a, const float *slot_b, int8_t *y0,
+                          const float *out_slot0, int8_t *y1, const float *out_slot1, int64_t pixels, int C,
+                          void *stream) {
+    if (!xa || !xb || !slot_a || !slot_b || !y0 || !out_slot0 || (y1 && !out_slot1) || pixels <= 0 || C <= 0)
+        return (int)cudaErrorInvalidValue;
+    const int Cp = (C + 15) / 16 * 16;
+    const int64_t n16 = pixels * (Cp / 16);
+    addq8_kernel<<<(unsigned)((n16 + kThreads - 1) / kThreads), kThreads, 0, (cudaStream_t)stream>>>(
+        xa, xb, (const RangeSlot *)slot_a, (const RangeSlot *)slot_b, y0, (const RangeSlot *)out_slot0, y1,
+        (const RangeSlot *)out_slot1, n16, C, Cp);
+    g_launches += 1;
+    return (int)cudaGetLastError();
+}
+
+extern "C" int dfq_mean_q8(const int8_t *x, const float *in_slot, int8_t *y, const float *out_slot, float *yf,
+                           int64_t N, int C, int HW, void *stream) {
+    if (!x || !in_slot || (!y && !yf) || (y && !out_slot) || N <= 0 || C <= 0 || HW <= 0)
+        return (int)cudaErrorInvalidValue;
+    const int Cp = (C + 15) / 16 * 16;
+    if (y) {
+        cudaError_t e = cudaMemsetAsync(y, 0, (size_t)N * Cp, (cudaStream_t)stream);     // pad channels: s8 zero
+        if (e != cudaSuccess) return (int)e;
+    }
+    meanq8_kernel<<<(unsigned)(N * ((C + 7) / 8)), kThreads, 0, (cudaStream_t)stream>>>(
+        x, (const RangeSlot *)in_slot, y, (const RangeSlot *)out_slot, yf, C, Cp, HW, Cp);
+    g_launches += 1;
+    return (int)cudaGetLastError();
+}

@@ -23,7 +23,7 @@
 extern "C" {
 #endif
 
-#define DFQ_ABI_VERSION 13
+#define DFQ_ABI_VERSION 14
 
 #if defined(__GNUC__)
 #pragma GCC visibility push(default)   /* the library is built with -fvisibility=hidden */
@@ -313,6 +313,60 @@ typedef struct DfqConvI8Desc {
 int dfq_conv_i8_k_host(int C, int kh, int kw);
 int64_t dfq_conv_i8_scratch_bytes(int N, int C, int H, int W);
 int dfq_conv_i8(const DfqConvI8Desc *desc_host, void *stream);
+
+/* ---- (e) static-range W8A8 eval (csrc/q8.cu): QuantMeasure with update_stat == False, utils/quantize.py:119-126 ----
+ * Activations are CENTRED s8 CODES (code - 128 of utils/quantize.py:72-74 on the CONSUMER's grid), NHWC, channels
+ * padded to a multiple of 16 with zero bytes; a range slot is {min, max, scale, 0} as fp32.  Every producer writes
+ * the codes for up to two consumers (y0 / y1 with their slots; y1 may be NULL). */
+typedef struct DfqPwQ8Desc {
+    const int8_t *x;         /* [G][Kp] codes on this layer's grid (Kp = K rounded up to 16)            */
+    const int8_t *wpk;       /* dfq_pw_q8_pack_host                                                      */
+    const float *wr;         /* [O] s_w * sum_k (code_w - 128)                                           */
+    const float *bias;       /* [O] or NULL                                                              */
+    const float *in_slot;    /* this layer's QuantMeasure range                                          */
+    int8_t *y0; const float *out_slot0;
+    int8_t *y1; const float *out_slot1;
+    float *yf;               /* optional fp32 output y[g * yf_g + o * yf_o] (the classifier's logits)    */
+    int64_t yf_g, yf_o;
+    int64_t G;               /* pixels (images x H x W) or rows of a linear layer                        */
+    int32_t K, O, relu, o_cap;
+    float s_w, c_w;          /* w_hat = s_w * (code_w - 128) + c_w                                       */
+} DfqPwQ8Desc;
+int dfq_pw_q8_plan_host(int O, int K, int o_cap, int *n_pass, int *o_per_pass, int *npass, int *slabs,
+                        int64_t *packed_bytes);
+int dfq_pw_q8_pack_host(const int8_t *codes_host, int O, int K, int o_cap, int8_t *packed_host);
+/* 1 x 1 convolution / linear layer: tensor-map TMA feed, tcgen05.mma.kind::i8, requantising epilogue. */
+int dfq_pw_q8(const DfqPwQ8Desc *desc_host, void *stream);
+
+typedef struct DfqDwQ8Desc {
+    const int8_t *x;         /* [N][H][W][Cp]                                                            */
+    const float *w9;         /* [9][Cp] fp32 (fake-quantised) weights, tap-major, zero padded            */
+    const float *bias;       /* [Cp] or NULL                                                             */
+    const float *in_slot;
+    int8_t *y0; const float *out_slot0;
+    int8_t *y1; const float *out_slot1;
+    int32_t N, H, W, C, stride, relu;
+} DfqDwQ8Desc;
+/* depthwise 3 x 3, padding 1, stride 1 or 2 */
+int dfq_dw_q8(const DfqDwQ8Desc *desc_host, void *stream);
+
+typedef struct DfqStemQ8Desc {
+    const float *x;          /* [N][3][H][W] fp32 image                                                  */
+    const float *w;          /* [O][3][3][3]                                                             */
+    const float *bias;
+    const float *in_slot;
+    int8_t *y0; const float *out_slot0;
+    int8_t *y1; const float *out_slot1;
+    int32_t N, H, W, O, stride, pad, relu, reserved;
+} DfqStemQ8Desc;
+/* dense 3 x 3 stem on 3 input channels, O <= 32 */
+int dfq_stem_q8(const DfqStemQ8Desc *desc_host, void *stream);
+/* residual add of two code tensors [pixels][Cp] on their own grids (utils/layer_transform.py:18-32) */
+int dfq_add_q8(const int8_t *xa, const int8_t *xb, const float *slot_a, const float *slot_b, int8_t *y0,
+               const float *out_slot0, int8_t *y1, const float *out_slot1, int64_t pixels, int C, void *stream);
+/* spatial mean of Q(x): codes [N][HW][Cp] -> codes [N][Cp] on out_slot's grid (y) and / or fp32 [N][C] (yf) */
+int dfq_mean_q8(const int8_t *x, const float *in_slot, int8_t *y, const float *out_slot, float *yf, int64_t N, int C,
+                int HW, void *stream);
 
 /* ---- (b) cross-layer equalisation: Cross_layer_equal.py:63-115 ---------------------- */
 /* sorts pairs by stage (stable) and fills first_unit/n_units */

@@ -242,6 +242,24 @@ def main():
         json.dump(meta, open(os.path.join(gdir, f"eval_tf_{args.model}.json"), "w"), indent=1)
         print("teacher-forced records:", len(meta["layers"]), "layers,", len(meta["tensor_ops"]), "tensor ops", flush=True)
 
+    if "tf_static" in what:
+        # the same records with every measure in static mode (utils/quantize.py:125-126): the codes a layer's
+        # QuantMeasure produces ARE what the producer of its input must emit in the static-range u8 pipeline
+        g = torch.Generator().manual_seed(2)
+        x = (torch.randn(2, 3, 129, 129, generator=g) if dl else torch.randn(4, 3, 224, 224, generator=g))[:1].clone()
+        load_ranges(run, fresh)
+        for m in measures_of(run):
+            m.set_update_stat(False)
+        rec, meta, logits = teacher_forced(run, x)
+        meta["input"] = "torch.randn(seed 2)[:1]"
+        meta["mode"] = "set_update_stat(False) on every QuantMeasure"
+        rec["logits"] = logits.numpy()[:, :, ::4, ::4] if dl else logits.numpy()
+        np.savez_compressed(os.path.join(gdir, f"eval_tf_static_{args.model}.npz"), **rec)
+        json.dump(meta, open(os.path.join(gdir, f"eval_tf_static_{args.model}.json"), "w"), indent=1)
+        load_ranges(run, fresh)
+        print("static teacher-forced records:", len(meta["layers"]), "layers,", len(meta["tensor_ops"]), "tensor ops",
+              flush=True)
+
     if "top1" in what:
         n_img = args.images or (4 if dl else 1024)
         batch = 2 if dl else 256                           # main_dfq.py:92 batch size 256 (seg: per-rank share)

@@ -1,0 +1,261 @@
+"""GPU: the static-range u8 kernels (csrc/q8.cu) one by one against restatements built from the oracle's quantiser, then
+the whole static plan (eval_q8.EvalPlanQ8) against the UNMODIFIED reference run with set_update_stat(False) on every
+QuantMeasure (utils/quantize.py:125-126; goldens from oracle/gen_eval_golden.py --what tf_static,static).
+
+Codes are integers: the bar is IDENTICAL codes.  A producer's fp32 value differs from the reference's by the summation
+order of its convolution (~1e-7 relative), which moves a value across a rounding boundary of the consumer's 8-bit
+grid for about one element in 10^4; such elements may differ by ONE code, never more."""
+import ctypes
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from helpers import dfq_quantised
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def slot(lo, hi):
+    from data_free_quantization_b200 import _lib as L
+    p = L.DfqQuantParams()
+    L.lib().dfq_quant_params_host(float(lo), float(hi), 8, 0, ctypes.byref(p))
+    return torch.tensor([float(np.float32(lo)), float(np.float32(hi)), p.scale, 0.0], dtype=torch.float32, device=DEV), p.scale
+
+
+def deq(codes, lo, scale):
+    return (codes.astype(np.float32) * np.float32(scale)).astype(np.float32) + np.float32(lo)
+
+
+def check_codes(got, want, what, max_frac=2e-3):
+    got, want = np.asarray(got, np.int32), np.asarray(want, np.int32)
+    assert got.shape == want.shape, (what, got.shape, want.shape)
+    d = np.abs(got - want)
+    assert d.max() <= 1, (what, int(d.max()))
+    assert d.mean() <= max_frac, (what, float(d.mean()))
+    return float(d.mean())
+
+
+@pytest.mark.parametrize("G,K,O,o_cap,relu,dual", [
+    (1000, 16, 96, 0, 1, False), (777, 24, 144, 0, 0, True), (4096, 96, 24, 0, 0, True), (300, 144, 32, 0, 1, False),
+    (12544, 320, 1280, 0, 1, False), (256, 1280, 1000, 32, 0, False), (129, 960, 160, 0, 0, True),
+    (5000, 32, 16, 0, 0, False), (640, 576, 250, 64, 1, True)])
+def test_pointwise_q8_against_integer_restatement(oracle, G, K, O, o_cap, relu, dual):
+    from data_free_quantization_b200 import _lib as L
+    from data_free_quantization_b200.eval_q8 import PackedQ8, to_codes_nhwc, from_codes_nhwc
+    rng = np.random.default_rng(G + K + O)
+    xc = rng.integers(0, 256, (G, K)).astype(np.uint8)
+    lo_x, hi_x = -1.7, 2.9
+    in_slot, sx = slot(lo_x, hi_x)
+    w0 = (rng.standard_normal((O, K)) * 0.2).astype(np.float32)
+    w, wq = oracle.fake_quant(w0, 8, float(w0.min()), float(w0.max()), want_codes=True)
+    sw, mw = float(oracle.quant_params(float(w0.min()), float(w0.max()), 8)[1]), float(w0.min())
+    bias = (rng.standard_normal(O) * 0.5).astype(np.float32)
+    A, B = xc.astype(np.int64), wq.astype(np.int64)
+    exact = sx * sw * (A @ B.T) + sx * mw * A.sum(1, keepdims=True) + lo_x * sw * B.sum(1)[None, :] + K * lo_x * mw
+    exact = exact + bias[None, :].astype(np.float64)
+    if relu:
+        exact = np.maximum(exact, 0)
+    pk = PackedQ8(torch.from_numpy(w).to(DEV), o_cap=o_cap)
+    x = to_codes_nhwc(torch.from_numpy(xc)).reshape(-1).to(DEV)
+    Cp = (O + 15) // 16 * 16
+    y0 = torch.full((G * Cp,), 77, dtype=torch.int8, device=DEV)
+    y1 = torch.full((G * Cp,), 77, dtype=torch.int8, device=DEV)
+    yf = torch.full((G, O), float("nan"), device=DEV)
+    ranges = [(float(exact.min()) - 0.1, float(exact.max()) * 0.8), (-0.5, float(exact.max()) + 1.0)]
+    s0, sc0 = slot(*ranges[0])
+    s1, sc1 = slot(*ranges[1])
+    bd = torch.from_numpy(bias).to(DEV)
+    d = L.DfqPwQ8Desc()
+    d.x, d.wpk, d.wr, d.bias, d.in_slot = x.data_ptr(), pk.wpk.data_ptr(), pk.wr.data_ptr(), bd.data_ptr(), in_slot.data_ptr()
+    d.y0, d.out_slot0 = y0.data_ptr(), s0.data_ptr()
+    if dual:
+        d.y1, d.out_slot1 = y1.data_ptr(), s1.data_ptr()
+    d.yf, d.yf_g, d.yf_o = yf.data_ptr(), O, 1
+    d.G, d.K, d.O, d.relu, d.o_cap, d.s_w, d.c_w = G, K, O, relu, o_cap, pk.s_w, pk.c_w
+    L.check(L.lib().dfq_pw_q8(ctypes.byref(d), L.stream()), "dfq_pw_q8")
+    torch.cuda.synchronize()
+    got = yf.cpu().numpy()
+    err = np.abs(got - exact).max() / np.abs(exact).max()
+    assert err <= 3e-6, err
+    for t, (yb, (lo, hi)) in enumerate(zip((y0, y1), ranges)):
+        if t == 1 and not dual:
+            break
+        codes = from_codes_nhwc(yb.cpu(), (G, O)).numpy()
+        _q, want = oracle.fake_quant(got.astype(np.float32), 8, float(np.float32(lo)), float(np.float32(hi)), want_codes=True)
+        assert np.array_equal(codes, want.astype(np.uint8)), int((codes != want).sum())     # exact quantiser of OUR fp32
+        raw = yb.cpu().view(G, Cp)[:, O:]
+        assert not raw.any(), "pad channels must be s8 zero"
+    if not dual:
+        assert bool((y1 == 77).all())
+
+
+@pytest.mark.parametrize("N,C,H,W,stride,relu,dual", [(2, 32, 112, 112, 1, 1, False), (3, 96, 56, 56, 2, 1, True),
+                                                     (2, 144, 29, 31, 1, 0, False), (4, 960, 7, 7, 1, 1, True),
+                                                     (1, 24, 14, 14, 2, 0, False), (2, 576, 14, 14, 2, 1, False)])
+def test_depthwise_q8(oracle, N, C, H, W, stride, relu, dual):
+    from data_free_quantization_b200 import _lib as L
+    from data_free_quantization_b200.eval_q8 import to_codes_nhwc, from_codes_nhwc
+    rng = np.random.default_rng(C + H)
+    xc = rng.integers(0, 256, (N, C, H, W)).astype(np.uint8)
+    lo_x, hi_x = -0.3, 5.2
+    in_slot, sx = slot(lo_x, hi_x)
+    xq = deq(xc, np.float32(lo_x), sx)
+    w = (rng.standard_normal((C, 1, 3, 3)) * 0.3).astype(np.float32)
+    bias = (rng.standard_normal(C) * 0.2).astype(np.float32)
+    ref = torch.nn.functional.conv2d(torch.from_numpy(xq).double(), torch.from_numpy(w).double(),
+                                     torch.from_numpy(bias).double(), stride, 1, 1, C).numpy()
+    if relu:
+        ref = np.maximum(ref, 0)
+    Cp = (C + 15) // 16 * 16
+    w9 = torch.zeros(9, Cp, device=DEV); w9[:, :C] = torch.from_numpy(w.reshape(C, 9).T.copy()).to(DEV)
+    bp = torch.zeros(Cp, device=DEV); bp[:C] = torch.from_numpy(bias).to(DEV)
+    OH, OW = ref.shape[2], ref.shape[3]
+    x = to_codes_nhwc(torch.from_numpy(xc)).reshape(-1).to(DEV)
+    y0 = torch.full((N * OH * OW * Cp,), 55, dtype=torch.int8, device=DEV)
+    y1 = torch.full((N * OH * OW * Cp,), 55, dtype=torch.int8, device=DEV)
+    ranges = [(float(ref.min()) * 0.9, float(ref.max()) * 0.9), (0.0, float(ref.max()) * 1.1 + 0.1)]
+    s0, _ = slot(*ranges[0]); s1, _ = slot(*ranges[1])
+    d = L.DfqDwQ8Desc()
+    d.x, d.w9, d.bias, d.in_slot, d.y0, d.out_slot0 = x.data_ptr(), w9.data_ptr(), bp.data_ptr(), in_slot.data_ptr(), y0.data_ptr(), s0.data_ptr()
+    if dual:
+        d.y1, d.out_slot1 = y1.data_ptr(), s1.data_ptr()
+    d.N, d.H, d.W, d.C, d.stride, d.relu = N, H, W, C, stride, relu
+    L.check(L.lib().dfq_dw_q8(ctypes.byref(d), L.stream()), "dfq_dw_q8")
+    torch.cuda.synchronize()
+    for t, (yb, (lo, hi)) in enumerate(zip((y0, y1), ranges)):
+        if t == 1 and not dual:
+            break
+        codes = from_codes_nhwc(yb.cpu(), ref.shape).numpy()
+        _q, want = oracle.fake_quant(ref.astype(np.float32), 8, float(np.float32(lo)), float(np.float32(hi)), want_codes=True)
+        check_codes(codes, want, f"dw out {t}")
+        assert not yb.cpu().view(-1, Cp)[:, C:].any()
+
+
+def test_stem_add_mean_q8(oracle):
+    from data_free_quantization_b200 import _lib as L
+    from data_free_quantization_b200.eval_q8 import to_codes_nhwc, from_codes_nhwc
+    lib = L.lib()
+    rng = np.random.default_rng(9)
+    # ---- stem: fp32 image, quantised on load
+    N, H, W, O = 3, 64, 48, 32
+    img = (rng.standard_normal((N, 3, H, W)) * 1.2).astype(np.float32)
+    lo_i, hi_i = -2.11790393, 2.64
+    in_slot, _ = slot(lo_i, hi_i)
+    xq = oracle.fake_quant(img, 8, float(np.float32(lo_i)), float(np.float32(hi_i)))
+    w = (rng.standard_normal((O, 3, 3, 3)) * 0.3).astype(np.float32)
+    bias = (rng.standard_normal(O) * 0.2).astype(np.float32)
+    ref = np.maximum(torch.nn.functional.conv2d(torch.from_numpy(xq).double(), torch.from_numpy(w).double(),
+                                                torch.from_numpy(bias).double(), 2, 1).numpy(), 0)
+    OH, OW = ref.shape[2:]
+    y0 = torch.zeros(N * OH * OW * 32, dtype=torch.int8, device=DEV)
+    lo, hi = 0.0, float(ref.max()) * 0.95
+    s0, _ = slot(lo, hi)
+    xd, wd, bd = torch.from_numpy(img).to(DEV), torch.from_numpy(w).to(DEV), torch.from_numpy(bias).to(DEV)
+    d = L.DfqStemQ8Desc()
+    d.x, d.w, d.bias, d.in_slot, d.y0, d.out_slot0 = xd.data_ptr(), wd.data_ptr(), bd.data_ptr(), in_slot.data_ptr(), y0.data_ptr(), s0.data_ptr()
+    d.N, d.H, d.W, d.O, d.stride, d.pad, d.relu = N, H, W, O, 2, 1, 1
+    L.check(lib.dfq_stem_q8(ctypes.byref(d), L.stream()), "dfq_stem_q8")
+    _q, want = oracle.fake_quant(ref.astype(np.float32), 8, float(np.float32(lo)), float(np.float32(hi)), want_codes=True)
+    check_codes(from_codes_nhwc(y0.cpu(), ref.shape).numpy(), want, "stem")
+    # ---- residual add of two grids into two grids
+    N, C, H, W = 2, 24, 20, 12
+    ca, cb = rng.integers(0, 256, (N, C, H, W)).astype(np.uint8), rng.integers(0, 256, (N, C, H, W)).astype(np.uint8)
+    (sa, sca), (sb, scb) = slot(-3.0, 2.0), slot(-0.7, 4.4)
+    s = deq(ca, np.float32(-3.0), sca) + deq(cb, np.float32(-0.7), scb)
+    outs = [(-4.0, 5.0), (-2.5, 6.6)]
+    (t0, _), (t1, _) = slot(*outs[0]), slot(*outs[1])
+    xa, xb = to_codes_nhwc(torch.from_numpy(ca)).reshape(-1).to(DEV), to_codes_nhwc(torch.from_numpy(cb)).reshape(-1).to(DEV)
+    y0, y1 = torch.zeros_like(xa), torch.zeros_like(xa)
+    L.check(lib.dfq_add_q8(xa.data_ptr(), xb.data_ptr(), sa.data_ptr(), sb.data_ptr(), y0.data_ptr(), t0.data_ptr(),
+                           y1.data_ptr(), t1.data_ptr(), N * H * W, C, L.stream()), "dfq_add_q8")
+    for yb, (lo, hi) in zip((y0, y1), outs):
+        _q, want = oracle.fake_quant(s.astype(np.float32), 8, float(np.float32(lo)), float(np.float32(hi)), want_codes=True)
+        assert np.array_equal(from_codes_nhwc(yb.cpu(), s.shape).numpy(), want.astype(np.uint8))   # elementwise: exact
+        assert not yb.cpu().view(-1, 32)[:, C:].any()
+    # ---- spatial mean feeding another grid
+    N, C, H, W = 5, 1280, 7, 7
+    cx = rng.integers(0, 256, (N, C, H, W)).astype(np.uint8)
+    sin, scin = slot(0.0, 6.0)
+    m = deq(cx, np.float32(0.0), scin).reshape(N, C, -1).astype(np.float64).mean(-1)
+    so, _ = slot(0.1, 5.0)
+    x = to_codes_nhwc(torch.from_numpy(cx)).reshape(-1).to(DEV)
+    y = torch.full((N * C,), 9, dtype=torch.int8, device=DEV)
+    yf = torch.zeros(N, C, device=DEV)
+    L.check(lib.dfq_mean_q8(x.data_ptr(), sin.data_ptr(), y.data_ptr(), so.data_ptr(), yf.data_ptr(), N, C, H * W,
+                            L.stream()), "dfq_mean_q8")
+    assert np.abs(yf.cpu().numpy() - m).max() <= 2e-6 * np.abs(m).max()
+    _q, want = oracle.fake_quant(yf.cpu().numpy(), 8, float(np.float32(0.1)), float(np.float32(5.0)), want_codes=True)
+    assert np.array_equal(from_codes_nhwc(y.cpu(), (N, C)).numpy(), want.astype(np.uint8))
+
+
+@pytest.fixture(scope="module")
+def static_model():
+    model, graph, bottoms, targ, tr = dfq_quantised("mobilenetv2", DEV, np.load(os.path.join(GOLD, "mobilenetv2_dfq.npz")))
+    for m in model.modules():
+        if hasattr(m, "set_update_stat"):
+            m.set_update_stat(False)
+    return model, tr
+
+
+def test_static_plan_reproduces_the_reference_codes_edge_by_edge(static_model):
+    """Every producer -> consumer edge of MobileNetV2: fed the reference's input codes, a q8 kernel must emit the
+    codes the reference's consumer QuantMeasure produced (tests/golden/eval_tf_static_mobilenetv2.npz)."""
+    from data_free_quantization_b200.eval_q8 import EvalPlanQ8
+    model, tr = static_model
+    tf = np.load(os.path.join(GOLD, "eval_tf_static_mobilenetv2.npz"))
+    plan = EvalPlanQ8(model, tr, batch=1)
+
+    def gold_codes(key):
+        return tf[f"L/{key[1]}/xq"] if key[0] == "L" else tf[f"T/{key[1]}/xq{key[2]}"]
+
+    def gold_range(key):
+        return tf[f"L/{key[1]}/range"] if key[0] == "L" else tf[f"T/{key[1]}/range{key[2]}"]
+    # the plan's static ranges are the reference's
+    slots = plan.slots.cpu().numpy()
+    for idx, key in plan.slot_key.items():
+        want = gold_range(key).astype(np.float32)
+        assert np.allclose(slots[idx, :2], want, rtol=1e-6, atol=1e-7), key      # (sqrt on add branches: utils/minmax.py)
+        plan.set_range(idx, float(want[0]), float(want[1]))
+    x = torch.randn(4, 3, 224, 224, generator=torch.Generator().manual_seed(2))[:1].to(DEV)
+    worst, edges = 0.0, 0
+    for name, io in plan.step_io.items():
+        if io["kind"] == "stem":
+            res = plan.run_step(name, image=x)
+        else:
+            res = plan.run_step(name, in_codes=[gold_codes(plan.slot_key[i]) for i in io["in_slots"]])
+        for idx in io["out_slots"]:
+            worst = max(worst, check_codes(res[idx].numpy(), gold_codes(plan.slot_key[idx]), f"{name} -> {plan.slot_key[idx]}"))
+            edges += 1
+        if "fp32" in res:                                       # the classifier's logits
+            want = tf["logits"]
+            assert np.abs(res["fp32"].numpy().reshape(want.shape) - want).max() <= 1e-3 * np.abs(want).max()
+    print(f"{edges} producer->consumer edges; worst fraction of codes off by one: {worst:.2e}")
+    assert edges >= 74
+
+
+def test_static_plan_end_to_end_against_reference(static_model):
+    from data_free_quantization_b200.eval_q8 import EvalPlanQ8
+    model, tr = static_model
+    g = np.load(os.path.join(GOLD, "eval_static_mobilenetv2.npz"))
+    info = json.load(open(os.path.join(GOLD, "eval_static_mobilenetv2.json")))
+    n = info["images"]
+    plan = EvalPlanQ8(model, tr, batch=n)
+    x = torch.randn(n, 3, 224, 224, generator=torch.Generator().manual_seed(7)).to(DEV)
+    got = plan(x).cpu().numpy().reshape(g["logits"].shape)
+    shift = float(np.abs(got - g["logits"]).max() / np.abs(g["logits"]).max())
+    agree = float((got.argmax(1) == g["argmax"]).mean())
+    print(f"static plan vs reference: logits {shift:.2e} of the largest (reference vs itself under 1e-7 input noise: "
+          f"{info['reference_logit_shift_under_perturbation']:.2e}), top-1 agreement {agree:.4f}")
+    assert agree >= 0.999
+    assert shift <= 2.0 * info["reference_logit_shift_under_perturbation"]
+    # replayed as one CUDA graph: identical
+    replay = plan.capture()
+    plan.input.buf.copy_(x)
+    replay()
+    torch.cuda.synchronize()
+    assert np.array_equal(plan.output.buf.cpu().numpy().reshape(got.shape), got)
