@@ -43,6 +43,8 @@ def parse():
     ap.add_argument("--no-micro", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--micro-elems", type=int, default=MICRO_ELEMS)
+    ap.add_argument("--no-sweep", action="store_true", help="skip the 2^20..2^32 size sweep of configs[4]")
+    ap.add_argument("--sweep-max-log2", type=int, default=32)
     return ap.parse_args()
 
 
@@ -246,6 +248,90 @@ def kernel_rooflines(torch, dev, peak_gbs, n_elems, reps=10):
     return out
 
 
+def kernel_sweep(torch, dev, peak_gbs, scratch, max_log2=32):
+    """BASELINE.json configs[4] / SURVEY.md 8d config 5: single fp32 tensors of 2^20 .. 2^32 elements (randn * 0.1,
+    seed 3; plus a uniform and a heavy-tailed randn^3 tensor at 2^28 to exercise the clamp), viewed as [1024, n/1024]
+    for the bias-correction reduction.  Tensors that fit the 126 MB L2 are timed with an L2 flush between
+    repetitions.  GB/s over the algorithmic bytes (8 / 12 / 8 per element)."""
+    from data_free_quantization_b200.bias_correction import eps_dot
+    from data_free_quantization_b200.utils.quantize import fake_quant_tensors, minmax, quantize
+    import torch.nn as nn
+    out = []
+
+    def run(x, tag):
+        n = x.numel()
+        y = torch.empty_like(x)
+        lo, hi = (float(v) for v in minmax(x).tolist())
+        lin = nn.Linear(2, 2)
+        lin.weight = nn.Parameter(x.view(1024, -1), requires_grad=False)
+        v = torch.randn(n // 1024, device=dev)
+        cases = [("apply", 8, lambda: fake_quant_tensors_apply(x, y, lo, hi)),
+                 ("multi", 12, lambda: fake_quant_tensors([x], 8, 0, outs=[y])),
+                 ("bias_correct", 8, lambda: eps_dot([lin], [v], 8))]
+        rec = {"elems": n, "input": tag}
+        reps = 3 if n >= (1 << 30) else 6
+        for name, bpe, fn in cases:
+            fn()
+            torch.cuda.synchronize()
+            ts = []
+            for _ in range(reps):
+                if n * 4 < (128 << 20):
+                    flush_l2(torch, scratch)
+                a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                a.record()
+                fn()
+                b.record()
+                b.synchronize()
+                ts.append(a.elapsed_time(b))
+            ms = sorted(ts)[len(ts) // 2]
+            rec[name] = {"ms": round(ms, 4), "gbs": round(bpe * n / (ms * 1e-3) / 1e9, 1),
+                         "frac": round(bpe * n / (ms * 1e-3) / 1e9 / peak_gbs, 3)}
+        out.append(rec)
+        del y, lin, v
+
+    def fake_quant_tensors_apply(x, y, lo, hi):
+        from data_free_quantization_b200.utils.quantize import _apply, _params
+        return _apply(x, y, 8, _params(lo, hi, 8, 0))
+
+    g = torch.Generator(device=dev).manual_seed(3)
+    for lg in range(20, max_log2 + 1, 2):
+        x = torch.randn(1 << lg, device=dev, generator=g) * 0.1
+        run(x, "randn*0.1")
+        del x
+        torch.cuda.empty_cache()
+    x = torch.rand(1 << 28, device=dev, generator=g)
+    run(x, "uniform[0,1)")
+    x = torch.randn(1 << 28, device=dev, generator=g)
+    x = x * x * x
+    run(x, "randn^3 (heavy tails)")
+    del x
+    torch.cuda.empty_cache()
+    return out
+
+
+def int8_peak(torch, dev):
+    """Measured dense int8 tensor throughput of this GPU (cuBLASLt through torch._int_mm, 8192^3, best of 10): the
+    denominator for the tensor-pipe fractions of the s8 tcgen05 kernels (SURVEY.md 8d asks for a measured one)."""
+    try:
+        a = torch.randint(-128, 127, (8192, 8192), dtype=torch.int8, device=dev)
+        b = torch.randint(-128, 127, (8192, 8192), dtype=torch.int8, device=dev)
+        for _ in range(3):
+            torch._int_mm(a, b)
+        torch.cuda.synchronize()
+        best = 1e9
+        for _ in range(10):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            torch._int_mm(a, b)
+            e1.record()
+            e1.synchronize()
+            best = min(best, e0.elapsed_time(e1))
+        return {"tops": round(2 * 8192 ** 3 / (best * 1e-3) / 1e12, 1), "how": "torch._int_mm (cuBLASLt s8 x s8 -> s32) "
+                "8192^3, best of 10, CUDA events"}
+    except Exception as exc:                                   # noqa: BLE001 -- a library refusal is reported, not fatal
+        return {"tops": None, "how": f"torch._int_mm unavailable: {exc!r}"[:200]}
+
+
 def sharded_microbench(torch, dev, world, peak_gbs, elems=1 << 26, per_rank=2, reps=5):
     """BASELINE.json configs[4]: a list of world*per_rank equal fp32 tensors (256 MiB each, larger than L2 together)
     dealt to the ranks; every rank fake-quantises its share (range reduce + apply, 12 B/elt) and the quantised
@@ -304,12 +390,23 @@ def eval_images_per_s(torch, case, batch, steps, warmup):
     return batch * steps / (ms * 1e-3), ms / steps
 
 
-def eval_plan_images_per_s(torch, case, batch, steps, warmup):
+def eval_plan_images_per_s(torch, case, batch, steps, warmup, static=False):
     """The same forward through the static eval plan (eval_plan.py: every layer a libdfq_b200 kernel, one CUDA
     graph per batch).  The timed step includes the H2D copy of the batch from pinned host memory and the D2H read
-    of the top-1 indices (main_dfq.py:96-103)."""
+    of the top-1 indices (main_dfq.py:96-103).
+    static=True: every QuantMeasure in static-range mode (utils/quantize.py:125-126, ranges as set_quant_minmax
+    leaves them) on the u8 pipeline of eval_q8.py / csrc/q8.cu."""
     from data_free_quantization_b200.eval_plan import EvalPlan
-    plan = EvalPlan(case.model, case.tr, batch=batch)
+    if static:
+        from data_free_quantization_b200.eval_q8 import EvalPlanQ8
+        from data_free_quantization_b200.utils.layer_transform import set_quant_minmax
+        set_quant_minmax(case.graph, case.bottoms, verbose=False)       # undo the widening of the dynamic-range runs
+        for m in case.model.modules():
+            if hasattr(m, "set_update_stat"):
+                m.set_update_stat(False)
+        plan = EvalPlanQ8(case.model, case.tr, batch=batch)
+    else:
+        plan = EvalPlan(case.model, case.tr, batch=batch)
     x = torch.randn(batch, 3, 224, 224, generator=torch.Generator().manual_seed(2)).pin_memory()
     top1 = torch.empty(batch, dtype=torch.int64).pin_memory()
     plan.input.buf.copy_(x)
@@ -409,7 +506,10 @@ def deeplab_section(torch, dev, world):
 
 # ------------------------------------------------------------------------------------------ CPU baseline
 def oracle_pipeline_once():
-    """The reference path restated in C (oracle/, 1 host thread) on the same seeded MobileNetV2.  Returns ms."""
+    """The reference path restated in C (oracle/, 1 host thread) on the same seeded MobileNetV2: the stages of
+    main_dfq.py:188-231 the oracle restates (merge, CLE, absorb, second merge, quantise, clip; set_quant_minmax is
+    host scalar logic of ~7 ms in the Python original and has no C restatement -- leaving it out favours this arm).
+    Returns (ms, CLE iterations)."""
     import json as _json
     import torch
     from oracle import oracle as O
@@ -428,7 +528,7 @@ def oracle_pipeline_once():
     P.merge_batchnorm(st, topo)
     iters, _, _ = P.cross_layer_equalization(st, topo)
     P.bias_absorption(st, topo, 3)
-    for bn in set(topo["conv_bn"].values()):
+    for bn in set(topo["conv_bn"].values()):          # main_dfq.py:211: the second merge resets the BN stash
         st[bn + ".fake_weight"].fill(1.0)
         st[bn + ".fake_bias"].fill(0.0)
     P.quantize_targ_layer(st, topo, 8, 8)
@@ -436,22 +536,29 @@ def oracle_pipeline_once():
     return (time.perf_counter() - t) * 1e3, iters
 
 
+def bench_config(world, weights=3469760):
+    """`config` of the JSON line -- identical for both arms."""
+    return {"workload": WORKLOAD, "weights": weights, "pipelines_per_step": world,
+            "l2": "flushed between timed steps (256 MiB scratch write)",
+            "excluded": "graph tracing / switch_layers (out of scope, SURVEY.md 8d)"}
+
+
 def reference_arm(args):
-    """--impl reference: the CPU port of the reference path, timed on this box's host cores."""
+    """--impl reference: the CPU port of the reference path, timed on this box's host cores (rank 0 only)."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    for _ in range(min(args.warmup, 1)):
+    for _ in range(args.warmup):
         oracle_pipeline_once()
-    ts = [oracle_pipeline_once()[0] for _ in range(max(1, min(args.steps, 10)))]
+    ts = [oracle_pipeline_once()[0] for _ in range(max(1, args.steps))]
     ms = sum(ts) / len(ts)
-    sample = ("full pipeline (merge+CLE 44 iterations+absorb+quantize+clip) on the seeded MobileNetV2, "
-              f"{len(ts)} passes; C restatement of the reference (oracle/dfq_oracle.c), not the Python original "
-              "(that takes ~80-110 s per pass, BASELINE.md)")
+    sample = ("full pipeline (merge+CLE 44 iterations+absorb+merge+quantize+clip) on the seeded MobileNetV2, "
+              f"{len(ts)} timed passes after {args.warmup} warm-up; C restatement of the reference "
+              "(oracle/dfq_oracle.c, one host thread), not the Python original (~80-110 s per pass, BASELINE.md)")
     return {"impl": "reference", "metric": METRIC, "value": round(ms, 3), "unit": UNIT, "n_gpus": args.gpus,
-            "steps": len(ts), "warmup": min(args.warmup, 1), "ms_per_step": round(ms, 3), "higher_is_better": False,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms, 3), "higher_is_better": False,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": WORKLOAD},
+            "config": bench_config(args.gpus),
             "cpu_baseline": {"value": round(ms, 3), "unit": UNIT, "cores": 1, "kind": "port", "sample": sample},
             "e2e": {"value": round(ms, 3), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
@@ -588,6 +695,25 @@ def _main(args):
                               "ms_per_batch": round(ev_ms, 3),
                               "path": "reference-shaped nn.Module forward: QuantMeasure on libdfq_b200 kernels, "
                                       "conv/linear arithmetic through F.conv2d (cuDNN fp32, library)"}}
+    ev_static = None
+    if not args.no_eval:
+        with quiet:
+            st_dev, st_e2e, st_ops, st_bytes = eval_plan_images_per_s(torch, case, EVAL_BATCH, max(5, args.steps // 2), 3,
+                                                                      static=True)
+        if world > 1:
+            t = torch.tensor([st_dev, st_e2e], device=dev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            st_dev, st_e2e = t.tolist()
+        ev_static = {"images_per_s": round(EVAL_BATCH * world / (st_dev * 1e-3), 1),
+                     "e2e_images_per_s": round(EVAL_BATCH * world / (st_e2e * 1e-3), 1),
+                     "batch_per_gpu": EVAL_BATCH, "ms_per_batch": round(st_dev, 3), "e2e_ms_per_batch": round(st_e2e, 3),
+                     "launches_per_batch": st_ops, "activation_code_bytes_written": st_bytes,
+                     "algorithmic_bytes_per_image": 13941800,
+                     "hbm_gbs_algorithmic": round(13941800 * EVAL_BATCH / (st_dev * 1e-3) / 1e9, 1),
+                     "path": "static-range mode (set_update_stat(False), utils/quantize.py:125-126): producers "
+                             "requantise to the consumers' grids and write s8 codes NHWC; 1x1 convs / classifier by "
+                             "tensor-map TMA + tcgen05.mma.kind::i8, depthwise / stem / add / mean on CUDA cores "
+                             "(csrc/q8.cu); one CUDA graph per batch"}
     deeplab = None
     if not args.no_eval:
         with quiet:
@@ -609,6 +735,8 @@ def _main(args):
             dist.destroy_process_group()
         return
     kernels = kernel_rooflines(torch, dev, peak, args.micro_elems) if not args.no_micro else []
+    sweep = kernel_sweep(torch, dev, peak, scratch, args.sweep_max_log2) if not (args.no_micro or args.no_sweep) else None
+    i8peak = int8_peak(torch, dev) if not args.no_micro else None
     # roofline of the step's dominant kernel: the persistent CLE loop.  Algorithmic bytes: 12 B x
     # 4 252 832 pair elements per outer iteration x the iterations it ran; duration: CUDA events around its launch on
     # the launch stream (breakdown pass above).
@@ -640,14 +768,18 @@ def _main(args):
     line = {"metric": METRIC, "value": round(ms_dev / world, 4), "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": round(ms_dev, 4), "higher_is_better": False, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "weights": case.weight_elems, "pipelines_per_step": world,
-                       "l2": "flushed between timed steps (256 MiB scratch write)",
-                       "excluded": "graph tracing / switch_layers (out of scope, SURVEY.md 8d)"},
+            "config": bench_config(world, case.weight_elems),
+            "scaling_of": "value = max-over-ranks step time / N for N independent pipeline replicas (the weight-side "
+                          "pipeline of one 14 MB model does not shard: SURVEY.md 8e); the path's sharded quantities "
+                          "are eval.images_per_s / eval_static.images_per_s (batch-sharded) and kernels_sharded "
+                          "(layer-sharded, NCCL all-gather)",
             "e2e": {"value": round(ms_e2e / world, 4), "unit": UNIT, "h2d_bytes_per_step": case.h2d_bytes(),
                     "d2h_bytes_per_step": case.d2h_bytes()},
             "gpu_launches": int(launches) // max(1, args.steps),
             "stages_ms": {k: round(v, 3) for k, v in stages.items() if isinstance(v, float)},
-            "roofline": roof, "kernels": kernels, "kernels_sharded": sharded, "eval": ev, "deeplab": deeplab, "cpu_baseline": cpu, "clocks": clocks.summary()}
+            "roofline": roof, "kernels": kernels, "kernels_sweep": sweep, "int8_peak": i8peak,
+            "kernels_sharded": sharded, "eval": ev, "eval_static": ev_static,
+            "deeplab": deeplab, "cpu_baseline": cpu, "clocks": clocks.summary()}
     if world > 1:
         dist.destroy_process_group()
     return line

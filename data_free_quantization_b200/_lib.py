@@ -109,9 +109,9 @@ class DfqPwQ8Desc(ctypes.Structure):
 
 
 class DfqDwQ8Desc(ctypes.Structure):
-    _fields_ = [("x", c_void), ("w9", c_void), ("bias", c_void), ("in_slot", c_void), ("y0", c_void),
+    _fields_ = [("x", c_void), ("wrow", c_void), ("bias", c_void), ("in_slot", c_void), ("y0", c_void),
                 ("out_slot0", c_void), ("y1", c_void), ("out_slot1", c_void)] + \
-               [(k, i32) for k in ("N", "H", "W", "C", "stride", "relu")]
+               [(k, i32) for k in ("N", "H", "W", "C", "stride", "relu")] + [("s_w", f32), ("c_w", f32)]
 
 
 class DfqStemQ8Desc(ctypes.Structure):

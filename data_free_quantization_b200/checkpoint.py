@@ -94,6 +94,7 @@ def load_packed(path):
 def _dequant(codes, slot, out):
     L.check(L.lib().dfq_dequant_codes_f32(codes.data_ptr(), codes.element_size(), L.dev_f32(out, "tensor"),
                                           out.numel(), 1, slot.data_ptr(), L.stream()), "dfq_dequant_codes_f32")
+    L.bump_weights_epoch()          # raw-pointer write: packed-code caches of the eval kernels are stale now
 
 
 def unpack_into(model, packed):

@@ -109,11 +109,61 @@ __device__ __forceinline__ uint32_t code_bits(float x, const QuantConsts &c) {
     }
     return (uint32_t)__float2int_rn(fminf(fmaxf(__fdiv_rn(t, c.scale), c.qmin), c.qmax));
 }
+// The exact quantiser (IEEE division) for a value whose reciprocal estimate sits near a tie: rare, kept OUT of line so
+// that the unrolled fast paths stay small (the depthwise kernel was 94 KB of code and stalled on instruction fetch).
+__device__ __noinline__ uint32_t code_bits_exact(float x, float neg_min, float scale, float rscale, float qmin,
+                                                 float qmax, float t_lo, float t_hi) {
+    const float t = __fadd_rn(x, neg_min);
+    const float tc = fminf(fmaxf(t, t_lo), t_hi);
+    return __float_as_uint(__fadd_rn(fminf(fmaxf(div_const_rn(tc, scale, rscale), qmin), qmax), 12582912.0f));
+}
+
+// N values -> N centred s8 codes, four per word.  The reciprocal estimates of all N values are formed in straight-line
+// code (the values interleave in the pipeline); ONE branch per call goes to the exact division, taken when any of
+// them sits within a few ulp of a tie (~5e-4 per value).
+template <int N>
+__device__ __forceinline__ void pack_codes(const float (&v)[N], const QuantConsts &c, uint32_t (&w)[N / 4]) {
+    uint32_t b[N];
+    if (c.fast) {                                           // block-uniform
+        const float magic = 12582912.0f;
+        uint32_t flagged = 0;
+#pragma unroll
+        for (int i = 0; i < N; ++i) {
+            const float cl = fminf(fmaxf(__fmul_rn(__fadd_rn(v[i], c.neg_min), c.rscale), c.qmin), c.qmax);
+            const float m = __fadd_rn(cl, magic);
+            b[i] = __float_as_uint(m);
+            if (fabsf(__fsub_rn(cl, __fadd_rn(m, -magic))) > c.amb) flagged |= 1u << i;
+        }
+        while (flagged) {                                    // rare: out-of-line exact division, one value at a time
+            const int i = __ffs(flagged) - 1;
+            flagged &= flagged - 1;
+            float x = v[0];
+#pragma unroll
+            for (int j = 1; j < N; ++j) x = (j == i) ? v[j] : x;
+            const uint32_t e = code_bits_exact(x, c.neg_min, c.scale, c.rscale, c.qmin, c.qmax, c.t_lo, c.t_hi);
+#pragma unroll
+            for (int j = 0; j < N; ++j) b[j] = (j == i) ? e : b[j];
+        }
+    } else {
+#pragma unroll
+        for (int i = 0; i < N; ++i) b[i] = code_bits(v[i], c);
+    }
+#pragma unroll
+    for (int j = 0; j < N / 4; ++j) {
+        const uint32_t lo = __byte_perm(b[4 * j], b[4 * j + 1], 0x0040), hi = __byte_perm(b[4 * j + 2], b[4 * j + 3], 0x0040);
+        w[j] = __byte_perm(lo, hi, 0x5410) ^ 0x80808080u;
+    }
+}
 // four values -> four centred s8 codes in one word
 __device__ __forceinline__ uint32_t pack4(float v0, float v1, float v2, float v3, const QuantConsts &c) {
-    const uint32_t b0 = code_bits(v0, c), b1 = code_bits(v1, c), b2 = code_bits(v2, c), b3 = code_bits(v3, c);
-    const uint32_t lo = __byte_perm(b0, b1, 0x0040), hi = __byte_perm(b2, b3, 0x0040);
-    return __byte_perm(lo, hi, 0x5410) ^ 0x80808080u;
+    const float v[4] = {v0, v1, v2, v3};
+    uint32_t w[1];
+    pack_codes<4>(v, c, w);
+    return w[0];
+}
+// bytes of channels >= `left` (counted from the word's first channel) cleared: padding channels are s8 zero
+__device__ __forceinline__ uint32_t keep_left(uint32_t w, int left) {
+    return left >= 4 ? w : (left <= 0 ? 0u : (w & (0xffffffffu >> (8 * (4 - left)))));
 }
 // centred s8 code word -> the four fp32 values the reference's quantiser produced: fl(fl(code * s) + min)
 __device__ __forceinline__ void dequant4(uint32_t w, float s, float mn, float *out) {
@@ -125,7 +175,91 @@ __device__ __forceinline__ void dequant4(uint32_t w, float s, float mn, float *o
     }
 }
 
-__global__ void __launch_bounds__(kQThreads, 1)
+template <int U> struct TmemLd;
+template <> struct TmemLd<8> {
+    static __device__ __forceinline__ void ld(uint32_t (&d)[8], uint32_t addr) {
+        asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                     : "=r"(d[0]), "=r"(d[1]), "=r"(d[2]), "=r"(d[3]), "=r"(d[4]), "=r"(d[5]), "=r"(d[6]), "=r"(d[7])
+                     : "r"(addr));
+    }
+};
+template <> struct TmemLd<16> {
+    static __device__ __forceinline__ void ld(uint32_t (&d)[16], uint32_t addr) {
+        asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, "
+                     "%14, %15}, [%16];"
+                     : "=r"(d[0]), "=r"(d[1]), "=r"(d[2]), "=r"(d[3]), "=r"(d[4]), "=r"(d[5]), "=r"(d[6]), "=r"(d[7]),
+                       "=r"(d[8]), "=r"(d[9]), "=r"(d[10]), "=r"(d[11]), "=r"(d[12]), "=r"(d[13]), "=r"(d[14]), "=r"(d[15])
+                     : "r"(addr));
+    }
+};
+
+struct EpiCtx {
+    const PwQ8Args *a; const float *chan_c; uint32_t tbase; int64_t g; int o0, n_real, half; bool valid, small_acc;
+    float fa, fr, floor_v;
+};
+
+// One accumulator row (this thread's pixel) of one tile: units of U columns alternate between the two warps of the
+// lane group; SUM_k a and the first unit arrive behind ONE wait, the next unit is in flight behind the arithmetic.
+template <int U>
+__device__ __forceinline__ void epi_tile(const EpiCtx &e, const QuantConsts &q0, const QuantConsts &q1) {
+    const PwQ8Args &a = *e.a;
+    const bool has0 = a.y[0] != nullptr, has1 = a.y[1] != nullptr;
+    uint32_t rs, d[U];
+    int unit = e.half;
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];" : "=r"(rs) : "r"(e.tbase + (uint32_t)e.n_real));
+    if (unit * U < e.n_real) TmemLd<U>::ld(d, e.tbase + (uint32_t)(unit * U));
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+    const float row_c = __fmul_rn(e.fr, (float)(int)rs);                     // s_x c_w SUM_k a[p,k]
+    for (; unit * U < e.n_real; unit += 2) {
+        const int nv = min(U, e.n_real - unit * U);                          // warp-uniform
+        float yv[U];
+        if (e.small_acc) {       // |acc| <= K * 2^14 < 2^22: exact conversion on the full-rate pipes (I2F is 1/4 rate)
+#pragma unroll
+            for (int j = 0; j < U; ++j)
+                yv[j] = fmaxf(__fmaf_rn(e.fa, __fadd_rn(__int_as_float(0x4B400000 + (int)d[j]), -12582912.0f),
+                                        __fadd_rn(row_c, e.chan_c[unit * U + j])), e.floor_v);
+        } else {
+#pragma unroll
+            for (int j = 0; j < U; ++j)
+                yv[j] = fmaxf(__fmaf_rn(e.fa, (float)(int)d[j], __fadd_rn(row_c, e.chan_c[unit * U + j])), e.floor_v);
+        }
+        if ((unit + 2) * U < e.n_real) TmemLd<U>::ld(d, e.tbase + (uint32_t)((unit + 2) * U));
+        if (e.valid) {
+            if (a.yf) {
+                float *py = a.yf + e.g * a.yf_g + (int64_t)(e.o0 + unit * U) * a.yf_o;
+#pragma unroll
+                for (int j = 0; j < U; ++j)
+                    if (j < nv) py[(int64_t)j * a.yf_o] = yv[j];
+            }
+#pragma unroll
+            for (int t = 0; t < 2; ++t) {
+                if (!(t ? has1 : has0)) continue;
+                const QuantConsts &qc = t ? q1 : q0;
+                uint32_t w[U / 4];
+                pack_codes<U>(yv, qc, w);
+                if (nv < U) {
+#pragma unroll
+                    for (int j4 = 0; j4 < U / 4; ++j4) w[j4] = keep_left(w[j4], nv - 4 * j4);
+                }
+                int8_t *dst = a.y[t] + e.g * a.cp_out + e.o0 + unit * U;
+                if (U == 16) *reinterpret_cast<uint4 *>(dst) = make_uint4(w[0], w[1], w[U / 4 - 2], w[U / 4 - 1]);
+                else *reinterpret_cast<uint2 *>(dst) = make_uint2(w[0], w[1]);
+            }
+        }
+        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+    }
+    // channels between the layer's last one and the padded row end that no unit covered: s8 zero
+    if (e.valid && e.half == 0) {
+        const int done = (e.n_real + U - 1) / U * U, row_end = min(a.o_per_pass, a.cp_out - e.o0);
+        for (int cpad = done; cpad < row_end; cpad += 8) {
+#pragma unroll
+            for (int t = 0; t < 2; ++t)
+                if (t ? has1 : has0) *reinterpret_cast<uint2 *>(a.y[t] + e.g * a.cp_out + e.o0 + cpad) = make_uint2(0u, 0u);
+        }
+    }
+}
+
+__global__ void __launch_bounds__(kQThreads, 2)
 pwq8_kernel(const __grid_constant__ CUtensorMap tmA, PwQ8Args a) {
     extern __shared__ uint8_t smem_raw[];
     __shared__ __align__(8) uint64_t bars[2 * kQMaxStages + 4];   // full[stages] | empty[stages] | tfull[2] | tempty[2]
@@ -225,6 +359,7 @@ pwq8_kernel(const __grid_constant__ CUtensorMap tmA, PwQ8Args a) {
         if (has1) q1 = consts_from_slot(*a.out_slot[1], 8, 0, 0.f, 0.f);
         const float fa = __fmul_rn(sx, a.s_w), fr = __fmul_rn(sx, a.c_w);
         const float floor_v = a.relu ? 0.0f : -INFINITY;
+        const bool small_acc = a.Kp <= 255;
         int acc = 0; uint32_t aphase = 0;
         for (int64_t tile = tile0; tile < a.tiles; tile += tstep) {
             const int64_t g = tile * kQM + row;
@@ -232,49 +367,9 @@ pwq8_kernel(const __grid_constant__ CUtensorMap tmA, PwQ8Args a) {
             mbar_wait(tfull0 + 8 * acc, aphase);
             tc_fence_after();
             const uint32_t tbase = tmem + ((uint32_t)(32 * lg) << 16) + (uint32_t)(acc * a.npass);
-            uint32_t rs;
-            asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];" : "=r"(rs) : "r"(tbase + (uint32_t)n_real));
-            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-            const float row_c = __fmul_rn(fr, (float)(int)rs);               // s_x c_w SUM_k a[p,k]
-            for (int chunk = half; chunk * 16 < n_real; chunk += 2) {
-                uint32_t d[16];
-                asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, "
-                             "%12, %13, %14, %15}, [%16];"
-                             : "=r"(d[0]), "=r"(d[1]), "=r"(d[2]), "=r"(d[3]), "=r"(d[4]), "=r"(d[5]), "=r"(d[6]),
-                               "=r"(d[7]), "=r"(d[8]), "=r"(d[9]), "=r"(d[10]), "=r"(d[11]), "=r"(d[12]), "=r"(d[13]),
-                               "=r"(d[14]), "=r"(d[15])
-                             : "r"(tbase + (uint32_t)(chunk * 16)));
-                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-                const int nv = min(16, n_real - chunk * 16);                 // warp-uniform
-                float yv[16];
-#pragma unroll
-                for (int j = 0; j < 16; ++j)
-                    yv[j] = fmaxf(__fmaf_rn(fa, (float)(int)d[j], __fadd_rn(row_c, chan_c[chunk * 16 + j])), floor_v);
-                if (valid) {
-                    if (a.yf) {
-                        float *py = a.yf + g * a.yf_g + (int64_t)(o0 + chunk * 16) * a.yf_o;
-#pragma unroll
-                        for (int j = 0; j < 16; ++j)
-                            if (j < nv) py[(int64_t)j * a.yf_o] = yv[j];
-                    }
-#pragma unroll
-                    for (int t = 0; t < 2; ++t) {
-                        if (!(t ? has1 : has0)) continue;
-                        const QuantConsts &qc = t ? q1 : q0;
-                        uint32_t w4[4];
-#pragma unroll
-                        for (int j4 = 0; j4 < 4; ++j4) {
-                            uint32_t w = pack4(yv[4 * j4], yv[4 * j4 + 1], yv[4 * j4 + 2], yv[4 * j4 + 3], qc);
-                            // channels past the layer's last one (padding up to a multiple of 16): s8 zero
-                            const int left = nv - 4 * j4;
-                            if (left < 4) w = left <= 0 ? 0u : (w & (0xffffffffu >> (8 * (4 - left))));
-                            w4[j4] = w;
-                        }
-                        *reinterpret_cast<uint4 *>(a.y[t] + g * a.cp_out + o0 + chunk * 16) =
-                            make_uint4(w4[0], w4[1], w4[2], w4[3]);
-                    }
-                }
-            }
+            const EpiCtx ctx = {&a, chan_c, tbase, g, o0, n_real, half, valid, small_acc, fa, fr, floor_v};
+            if (n_real <= 16) epi_tile<8>(ctx, q0, q1);      // a 16-channel layer keeps all eight epilogue warps busy
+            else epi_tile<16>(ctx, q0, q1);
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(tempty0 + 8 * acc);
@@ -289,94 +384,147 @@ pwq8_kernel(const __grid_constant__ CUtensorMap tmA, PwQ8Args a) {
 }
 
 // ---------------------------------------------------------------------------------------------------------
-// Depthwise 3 x 3, pad 1, stride 1 or 2, NHWC codes in and out.  A thread owns 4 channels (one 32-bit code word) of a
-// strip of output pixels along a row and slides a 3 x 3 window of dequantised values through registers; consecutive
-// threads take consecutive channel words (coalesced 128-byte rows of a pixel).
+// Depthwise 3 x 3, pad 1, stride 1 or 2, NHWC codes in and out, exact integer sums on dp4a.
+//   y = s_x s_w SUM a b + s_x c_w SUM a + c_x s_w SUM_inb b + n_inb c_x c_w + bias        (a, b centred s8 codes;
+// zero padding is an exact 0.0 in the reference, i.e. the tap is absent: a = 0 there, and the two constant terms count
+// the in-bound taps only).
+// A thread owns 4 channels (one code word per pixel) of one output row and walks it in strips of 12 input columns.
+// Each 4-pixel x 4-channel block of a row is transposed in registers (8 PRMT) into one word per CHANNEL holding four
+// horizontally adjacent pixels; the three taps of a row then are a byte window of that string (1 PRMT) against the
+// row's packed weights (w0, w1, w2, 0): ONE dp4a per row for the dot product and one for SUM a, instead of three
+// code -> fp32 conversions and three FMAs.  ~30 instructions per output, about half of the fp32 formulation.
 struct DwQ8Args {
-    const int8_t *x; const float *w9; const float *bias; const RangeSlot *in_slot;
+    const int8_t *x; const uint32_t *wrow; const float *bias; const RangeSlot *in_slot;
     const RangeSlot *out_slot[2]; int8_t *y[2];
-    int N, H, W, OH, OW, C, Cp, stride, relu, strip, strips;
+    int N, H, W, OH, OW, C, Cp, stride, relu, strips;
+    float s_w, c_w;
 };
 
-template <int S>
-__global__ void __launch_bounds__(kThreads)
+template <int S> struct DwStrip { static constexpr int value = S == 1 ? 10 : 5; };   // outputs per 12 input columns
+
+__device__ __forceinline__ float small_int_to_float(int v) {      // exact for |v| < 2^22, full-rate instructions
+    return __fadd_rn(__int_as_float(0x4B400000 + v), -12582912.0f);
+}
+
+template <int S, bool DUAL>
+__global__ void __launch_bounds__(kThreads, 2)
 dwq8_kernel(DwQ8Args a) {
-    const int cw = a.Cp >> 2;                                     // channel words per pixel
-    const int64_t idx = (int64_t)blockIdx.x * kThreads + threadIdx.x;
-    const int64_t total = (int64_t)a.N * a.OH * a.strips * cw;
-    if (idx >= total) return;
-    const int cg = (int)(idx % cw);
-    int64_t rest = idx / cw;
-    const int sp = (int)(rest % a.strips); rest /= a.strips;
-    const int oy = (int)(rest % a.OH);
-    const int n = (int)(rest / a.OH);
-    const int c0 = cg * 4;
+    constexpr int P = DwStrip<S>::value;
+    const unsigned cw = (unsigned)a.Cp >> 2;                      // channel words per pixel
+    const unsigned idx = blockIdx.x * kThreads + threadIdx.x;
+    if (idx >= (unsigned)a.N * (unsigned)a.OH * cw) return;
+    const unsigned cg = idx % cw, rest = idx / cw;
+    const int oy = (int)(rest % (unsigned)a.OH);
+    const int n = (int)(rest / (unsigned)a.OH);
+    const int c0 = (int)cg * 4;
     const RangeSlot in = *a.in_slot;
-    const float sx = in.scale, mn = in.mn;
-    const bool has1 = a.y[1] != nullptr;
+    const float sx = in.scale, cx = __fmaf_rn(128.0f, sx, in.mn);
+    const float fa = __fmul_rn(sx, a.s_w), fb = __fmul_rn(sx, a.c_w);
+    const float cxsw = __fmul_rn(cx, a.s_w), cxcw = __fmul_rn(cx, a.c_w);
     const QuantConsts q0 = consts_from_slot(*a.out_slot[0], 8, 0, 0.f, 0.f);
     QuantConsts q1 = q0;
-    if (has1) q1 = consts_from_slot(*a.out_slot[1], 8, 0, 0.f, 0.f);
-    float wt[9][4], b4[4];
+    if (DUAL) q1 = consts_from_slot(*a.out_slot[1], 8, 0, 0.f, 0.f);
+    const int iy0 = oy * S - 1;
+    const bool rowok[3] = {(unsigned)iy0 < (unsigned)a.H, (unsigned)(iy0 + 1) < (unsigned)a.H,
+                           (unsigned)(iy0 + 2) < (unsigned)a.H};
+    uint32_t wr[3][4];                                            // [row][channel] = (w0, w1, w2, 0) centred s8
 #pragma unroll
-    for (int t = 0; t < 9; ++t) {
-        const float4 v = __ldg(reinterpret_cast<const float4 *>(a.w9 + (int64_t)t * a.Cp + c0));
-        wt[t][0] = v.x; wt[t][1] = v.y; wt[t][2] = v.z; wt[t][3] = v.w;
+    for (int r = 0; r < 3; ++r) {
+        const uint4 v = __ldg(reinterpret_cast<const uint4 *>(a.wrow + (int64_t)r * a.Cp + c0));
+        wr[r][0] = rowok[r] ? v.x : 0u; wr[r][1] = rowok[r] ? v.y : 0u;
+        wr[r][2] = rowok[r] ? v.z : 0u; wr[r][3] = rowok[r] ? v.w : 0u;
     }
+    float b4[4];
     {
         const float4 v = a.bias ? __ldg(reinterpret_cast<const float4 *>(a.bias + c0)) : make_float4(0.f, 0.f, 0.f, 0.f);
         b4[0] = v.x; b4[1] = v.y; b4[2] = v.z; b4[3] = v.w;
     }
-    const int ox0 = sp * a.strip, ox1 = min(a.OW, ox0 + a.strip);
-    const int iy0 = oy * S - 1;
-    const int8_t *xn = a.x + (int64_t)n * a.H * a.W * a.Cp + c0;
-    // column `ix` of the window: three rows of four dequantised channels (exact zeros outside the image)
-    auto load_col = [&](int ix, float (&col)[3][4]) {
+    // column sums of the in-bound rows' weights, per tap column j and channel: SUM_inb b for any column mask
+    int rs[3][4];
 #pragma unroll
-        for (int r = 0; r < 3; ++r) {
-            const int iy = iy0 + r;
-            if ((unsigned)iy < (unsigned)a.H && (unsigned)ix < (unsigned)a.W) {
-                const uint32_t w = __ldg(reinterpret_cast<const uint32_t *>(xn + ((int64_t)iy * a.W + ix) * a.Cp));
-                dequant4(w, sx, mn, col[r]);
-            } else {
-                col[r][0] = col[r][1] = col[r][2] = col[r][3] = 0.0f;
-            }
-        }
-    };
-    float win[3][3][4];                                           // [column][row][channel]
-    const int ixs = ox0 * S - 1;
-    load_col(ixs, win[0]);
-    load_col(ixs + 1, win[1]);
+    for (int c = 0; c < 4; ++c)
+#pragma unroll
+        for (int j = 0; j < 3; ++j)
+            rs[j][c] = (int)(int8_t)(wr[0][c] >> (8 * j)) + (int)(int8_t)(wr[1][c] >> (8 * j)) +
+                       (int)(int8_t)(wr[2][c] >> (8 * j));
+    const int nrows = (int)rowok[0] + (int)rowok[1] + (int)rowok[2];
+    const uint32_t ones[3] = {rowok[0] ? 0x00010101u : 0u, rowok[1] ? 0x00010101u : 0u, rowok[2] ? 0x00010101u : 0u};
+    // c_x s_w SUM_inb b + n_inb c_x c_w + bias for the four column cases: all three tap columns in bounds, the left one
+    // outside (first pixel of a row), the right one outside (last pixel), both (a one-pixel-wide image)
+    float cst_in[4], cst_l[4], cst_r[4], cst_lr[4];
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+        auto mk = [&](int sb, int ncols) {
+            return __fadd_rn(__fmaf_rn(cxsw, (float)sb, __fmul_rn((float)(ncols * nrows), cxcw)), b4[c]);
+        };
+        cst_in[c] = mk(rs[0][c] + rs[1][c] + rs[2][c], 3);
+        cst_l[c] = mk(rs[1][c] + rs[2][c], 2);
+        cst_r[c] = mk(rs[0][c] + rs[1][c], 2);
+        cst_lr[c] = mk(rs[1][c], 1);
+    }
+    const int8_t *xn = a.x + (int64_t)n * a.H * a.W * a.Cp + c0;
     const float floor_v = a.relu ? 0.0f : -INFINITY;
     const int64_t orow = ((int64_t)n * a.OH + oy) * a.OW;
-    for (int ox = ox0; ox < ox1; ++ox) {
-        load_col(ox * S + 1, win[2]);
-        float acc[4] = {0.f, 0.f, 0.f, 0.f};
+    const int left = a.C - c0;
+    for (int sp = 0; sp < a.strips; ++sp) {
+        const int ox0 = sp * P, ixs = ox0 * S - 1;
+        // 12 input columns x 3 rows (zero words outside the image), transposed per 4-column block
+        uint32_t t[3][3][4];                                      // [row][block][channel]: 4 adjacent pixels of a channel
 #pragma unroll
-        for (int i = 0; i < 3; ++i)                               // tap order (i, j) row-major, as the fp32 kernels
+        for (int r = 0; r < 3; ++r) {
+            const int8_t *xr = xn + (int64_t)(iy0 + r) * a.W * a.Cp;
 #pragma unroll
-            for (int j = 0; j < 3; ++j)
+            for (int blk = 0; blk < 3; ++blk) {
+                uint32_t p[4];
 #pragma unroll
-                for (int c = 0; c < 4; ++c) acc[c] = __fmaf_rn(win[j][i][c], wt[i * 3 + j][c], acc[c]);
-        float yv[4];
+                for (int q = 0; q < 4; ++q) {
+                    const int ix = ixs + 4 * blk + q;
+                    p[q] = (rowok[r] && (unsigned)ix < (unsigned)a.W)
+                               ? __ldg(reinterpret_cast<const uint32_t *>(xr + (int64_t)ix * a.Cp)) : 0u;
+                }
+                const uint32_t a0 = __byte_perm(p[0], p[1], 0x5140), a1 = __byte_perm(p[0], p[1], 0x7362);
+                const uint32_t b0 = __byte_perm(p[2], p[3], 0x5140), b1 = __byte_perm(p[2], p[3], 0x7362);
+                t[r][blk][0] = __byte_perm(a0, b0, 0x5410); t[r][blk][1] = __byte_perm(a0, b0, 0x7632);
+                t[r][blk][2] = __byte_perm(a1, b1, 0x5410); t[r][blk][3] = __byte_perm(a1, b1, 0x7632);
+            }
+        }
 #pragma unroll
-        for (int c = 0; c < 4; ++c) yv[c] = fmaxf(__fadd_rn(acc[c], b4[c]), floor_v);
-        const int left = a.C - c0;
-        const uint32_t mask = left >= 4 ? 0xffffffffu : (left <= 0 ? 0u : (0xffffffffu >> (8 * (4 - left))));
-        const int64_t off = (orow + ox) * a.Cp + c0;
-        *reinterpret_cast<uint32_t *>(a.y[0] + off) = pack4(yv[0], yv[1], yv[2], yv[3], q0) & mask;
-        if (has1) *reinterpret_cast<uint32_t *>(a.y[1] + off) = pack4(yv[0], yv[1], yv[2], yv[3], q1) & mask;
-        if (S == 1) {
+        for (int k = 0; k < P; ++k) {
+            const int ox = ox0 + k;
+            if (ox >= a.OW) break;                                // (uniform across the warp: same strip, same k)
+            constexpr int o = 0;  (void)o;
+            const int off_b = k * S;                              // byte offset of the window in the 12-byte row string
+            const int wi = off_b >> 2, sh = off_b & 3;
+            const uint32_t sel = 0x3210u + 0x1111u * (uint32_t)sh;
+            int acc[4], sa[4];
 #pragma unroll
-            for (int r = 0; r < 3; ++r)
+            for (int c = 0; c < 4; ++c) {
+                acc[c] = 0; sa[c] = 0;
 #pragma unroll
-                for (int c = 0; c < 4; ++c) { win[0][r][c] = win[1][r][c]; win[1][r][c] = win[2][r][c]; }
-        } else {
+                for (int r = 0; r < 3; ++r) {
+                    const uint32_t hiw = wi < 2 ? t[r][wi < 2 ? wi + 1 : 2][c] : 0u;
+                    const uint32_t win = __byte_perm(t[r][wi][c], hiw, sel);
+                    acc[c] = __dp4a((int)win, (int)wr[r][c], acc[c]);
+                    sa[c] = __dp4a((int)win, (int)ones[r], sa[c]);
+                }
+            }
+            const int ixl = ox * S - 1;
+            const bool lin = ixl >= 0, rin = ixl + 2 < a.W;      // left / right tap column in bounds (centre always is)
+            float yv[4];
 #pragma unroll
-            for (int r = 0; r < 3; ++r)
-#pragma unroll
-                for (int c = 0; c < 4; ++c) win[0][r][c] = win[2][r][c];
-            if (ox + 1 < ox1) load_col((ox + 1) * S, win[1]);
+            for (int c = 0; c < 4; ++c) {
+                const float cst = lin ? (rin ? cst_in[c] : cst_r[c]) : (rin ? cst_l[c] : cst_lr[c]);
+                yv[c] = fmaxf(__fmaf_rn(fa, small_int_to_float(acc[c]), __fmaf_rn(fb, small_int_to_float(sa[c]), cst)),
+                              floor_v);
+            }
+            const int64_t off = (orow + ox) * a.Cp + c0;
+            uint32_t w[1];
+            pack_codes<4>(yv, q0, w);
+            *reinterpret_cast<uint32_t *>(a.y[0] + off) = keep_left(w[0], left);
+            if (DUAL) {
+                pack_codes<4>(yv, q1, w);
+                *reinterpret_cast<uint32_t *>(a.y[1] + off) = keep_left(w[0], left);
+            }
         }
     }
 }
@@ -408,6 +556,7 @@ stemq8_kernel(StemQ8Args a) {
     const int n = (int)(p / ((int64_t)a.OW * a.OH));
     const QuantConsts qi = consts_from_slot(*a.in_slot, 8, 0, 0.f, 0.f);
     float xin[27];
+    bool ok[27];
 #pragma unroll
     for (int c = 0; c < 3; ++c)
 #pragma unroll
@@ -415,11 +564,36 @@ stemq8_kernel(StemQ8Args a) {
 #pragma unroll
             for (int j = 0; j < 3; ++j) {
                 const int iy = oy * a.stride - a.pad + i, ix = ox * a.stride - a.pad + j;
-                float v = 0.0f;
-                if ((unsigned)iy < (unsigned)a.H && (unsigned)ix < (unsigned)a.W)
-                    v = quant_dequant(__ldg(a.x + (((int64_t)n * 3 + c) * a.H + iy) * a.W + ix), qi);
-                xin[(c * 3 + i) * 3 + j] = v;
+                const int t = (c * 3 + i) * 3 + j;
+                ok[t] = (unsigned)iy < (unsigned)a.H && (unsigned)ix < (unsigned)a.W;
+                xin[t] = ok[t] ? __ldg(a.x + (((int64_t)n * 3 + c) * a.H + iy) * a.W + ix) : 0.0f;
             }
+    // utils/quantize.py:72-76 on the 27 inputs: reciprocal estimates in straight-line code, one branch to the exact
+    // division when any of them is within a few ulp of a tie; taps in the zero padding stay exact zeros
+    if (qi.fast) {
+        float t27[27], cl[27], q[27];
+        bool near_tie = false;
+#pragma unroll
+        for (int t = 0; t < 27; ++t) {
+            t27[t] = __fadd_rn(xin[t], qi.neg_min);
+            cl[t] = fminf(fmaxf(__fmul_rn(t27[t], qi.rscale), qi.qmin), qi.qmax);
+            q[t] = rint_small(cl[t]);
+            near_tie |= fabsf(__fsub_rn(cl[t], q[t])) > qi.amb;
+        }
+        if (near_tie) {
+#pragma unroll
+            for (int t = 0; t < 27; ++t)
+                if (fabsf(__fsub_rn(cl[t], q[t])) > qi.amb) {
+                    const float tc = fminf(fmaxf(t27[t], qi.t_lo), qi.t_hi);
+                    q[t] = rint_small(fminf(fmaxf(div_const_rn(tc, qi.scale, qi.rscale), qi.qmin), qi.qmax));
+                }
+        }
+#pragma unroll
+        for (int t = 0; t < 27; ++t) xin[t] = ok[t] ? __fadd_rn(__fmul_rn(q[t], qi.scale), qi.add_back) : 0.0f;
+    } else {
+#pragma unroll
+        for (int t = 0; t < 27; ++t) xin[t] = ok[t] ? quant_dequant(xin[t], qi) : 0.0f;
+    }
     const bool has1 = a.y[1] != nullptr;
     const QuantConsts q0 = consts_from_slot(*a.out_slot[0], 8, 0, 0.f, 0.f);
     QuantConsts q1 = q0;
@@ -448,13 +622,9 @@ stemq8_kernel(StemQ8Args a) {
             if (t2 && !has1) continue;
             const QuantConsts &qc = t2 ? q1 : q0;
             uint32_t w4[4];
+            pack_codes<16>(yv, qc, w4);
 #pragma unroll
-            for (int j4 = 0; j4 < 4; ++j4) {
-                uint32_t w = pack4(yv[4 * j4], yv[4 * j4 + 1], yv[4 * j4 + 2], yv[4 * j4 + 3], qc);
-                const int left = a.O - ob - 4 * j4;
-                if (left < 4) w = left <= 0 ? 0u : (w & (0xffffffffu >> (8 * (4 - left))));
-                w4[j4] = w;
-            }
+            for (int j4 = 0; j4 < 4; ++j4) w4[j4] = keep_left(w4[j4], a.O - ob - 4 * j4);
             *reinterpret_cast<uint4 *>(a.y[t2] + p * a.Cp + ob) = make_uint4(w4[0], w4[1], w4[2], w4[3]);
         }
     }
@@ -497,27 +667,36 @@ addq8_kernel(const int8_t *__restrict__ xa, const int8_t *__restrict__ xb, const
 // shuffle tree), requantised to the consumer's grid -> codes [N][Cp_out], and / or written as fp32 [N][C].
 __global__ void __launch_bounds__(kThreads)
 meanq8_kernel(const int8_t *__restrict__ x, const RangeSlot *sin, int8_t *y, const RangeSlot *sout, float *yf,
-              int C, int Cp, int HW, int Cp_out) {
-    const int groups = (C + 7) / 8;
-    const int n = blockIdx.x / groups, c0 = (blockIdx.x % groups) * 8;
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int c = c0 + warp;
-    if (c >= C) return;
+              int C, int Cp, int HW, int Cp_out, int64_t N) {
+    // one thread per 4-channel word (consecutive threads read consecutive words of a pixel), pixels in order
+    const int cw = Cp >> 2;
+    const int64_t idx = (int64_t)blockIdx.x * kThreads + threadIdx.x;
+    if (idx >= N * cw) return;
+    const int cg = (int)(idx % cw);
+    const int64_t n = idx / cw;
     const RangeSlot in = *sin;
-    const int8_t *p = x + (int64_t)n * HW * Cp + c;
-    float s = 0.0f;
-    for (int k = lane; k < HW; k += 32) {
-        const float q = (float)((int)p[(int64_t)k * Cp] + 128);
-        s = __fadd_rn(s, __fadd_rn(__fmul_rn(q, in.scale), in.mn));
+    const uint32_t *p = reinterpret_cast<const uint32_t *>(x + n * (int64_t)HW * Cp) + cg;
+    float s[4] = {0.f, 0.f, 0.f, 0.f};
+    for (int k = 0; k < HW; ++k) {
+        float v[4];
+        dequant4(__ldg(p + (int64_t)k * cw), in.scale, in.mn, v);
+#pragma unroll
+        for (int c = 0; c < 4; ++c) s[c] = __fadd_rn(s[c], v[c]);
     }
-    s = warp_sum(s);
-    const float m = __fdiv_rn(s, (float)HW);
-    if (lane == 0) {
-        if (yf) yf[(int64_t)n * C + c] = m;
-        if (y) {
-            const QuantConsts qc = consts_from_slot(*sout, 8, 0, 0.f, 0.f);
-            y[(int64_t)n * Cp_out + c] = (int8_t)((code_bits(m, qc) & 0xffu) ^ 0x80u);
-        }
+    float m[4];
+#pragma unroll
+    for (int c = 0; c < 4; ++c) m[c] = __fdiv_rn(s[c], (float)HW);
+    const int c0 = cg * 4;
+    if (yf) {
+#pragma unroll
+        for (int c = 0; c < 4; ++c)
+            if (c0 + c < C) yf[n * C + c0 + c] = m[c];
+    }
+    if (y) {
+        const QuantConsts qc = consts_from_slot(*sout, 8, 0, 0.f, 0.f);
+        uint32_t w[1];
+        pack_codes<4>(m, qc, w);
+        *reinterpret_cast<uint32_t *>(y + n * Cp_out + c0) = keep_left(w[0], C - c0);
     }
 }
 
@@ -604,19 +783,21 @@ extern "C" int dfq_pw_q8(const DfqPwQ8Desc *d, void *stream) {
     a.tmem_cols = 32;
     while (a.tmem_cols < 2 * a.npass) a.tmem_cols *= 2;
     const size_t stage_bytes = (size_t)kQASlab + (size_t)a.npass * kQSlab;
-    int stages = (int)((200 * 1024) / stage_bytes);
+    // CTAs per SM: as many as the TMEM allows (each holds tmem_cols of the 512 columns; a CTA that could not get its
+    // columns would spin in tcgen05.alloc), at most two; the shared-memory request is sized / padded to enforce it
+    const int ctas_tmem = 512 / a.tmem_cols;
+    const int want_ctas = ctas_tmem < 2 ? 1 : 2;
+    const size_t smem_cap = 227 * 1024 - 2048;                 // dynamic part: the kernel has ~1.2 KB of static shared memory
+    const size_t budget = smem_cap / (size_t)want_ctas - 1024;
+    int stages = (int)((budget - 1024) / stage_bytes);
     if (stages > kQMaxStages) stages = kQMaxStages;
-    const int64_t need = (int64_t)a.slabs * 2;                   // two tiles' worth of slabs in flight is plenty
-    if (stages > need && need >= 2) stages = (int)need;
+    const int64_t need = (int64_t)a.slabs * 2 < 6 ? 6 : (int64_t)a.slabs * 2;   // single-slab layers: A tiles of the next tiles prefetched
+    if (stages > need) stages = (int)need;
     if (stages < 2) return (int)cudaErrorInvalidValue;
     a.stages = stages;
-    // one CTA per SM when the two accumulators need all 512 TMEM columns, else as many as fit (the allocation of a
-    // second CTA would otherwise spin): the shared-memory request is padded to enforce it
     size_t smem = (size_t)stages * stage_bytes + 1024;
-    const int ctas_tmem = 512 / a.tmem_cols;
-    const size_t smem_cap = 227 * 1024;
     {
-        const size_t floor_bytes = smem_cap / (size_t)(ctas_tmem + 1) + 1024;
+        const size_t floor_bytes = smem_cap / (size_t)(want_ctas + 1) + 1024;
         if (smem < floor_bytes) smem = floor_bytes;
     }
     static size_t configured = 0;
@@ -640,7 +821,7 @@ extern "C" int dfq_pw_q8(const DfqPwQ8Desc *d, void *stream) {
     cudaError_t ce = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, pwq8_kernel, kQThreads, smem);
     if (ce != cudaSuccess) return (int)ce;
     if (occ < 1) return (int)cudaErrorLaunchOutOfResources;
-    if (occ > ctas_tmem) occ = ctas_tmem;
+    if (occ > want_ctas) occ = want_ctas;
     int64_t per_pass = ((int64_t)sm_count() * occ) / a.n_pass;
     if (per_pass < 1) per_pass = 1;
     if (per_pass > a.tiles) per_pass = a.tiles;
@@ -651,21 +832,29 @@ extern "C" int dfq_pw_q8(const DfqPwQ8Desc *d, void *stream) {
 }
 
 extern "C" int dfq_dw_q8(const DfqDwQ8Desc *d, void *stream) {
-    if (!d || !d->x || !d->w9 || !d->in_slot || !d->y0 || !d->out_slot0 || (d->y1 && !d->out_slot1) || d->N <= 0 ||
+    if (!d || !d->x || !d->wrow || !d->in_slot || !d->y0 || !d->out_slot0 || (d->y1 && !d->out_slot1) || d->N <= 0 ||
         (d->stride != 1 && d->stride != 2))
         return (int)cudaErrorInvalidValue;
     DwQ8Args a = {};
-    a.x = d->x; a.w9 = d->w9; a.bias = d->bias; a.in_slot = (const RangeSlot *)d->in_slot;
+    a.x = d->x; a.wrow = d->wrow; a.bias = d->bias; a.in_slot = (const RangeSlot *)d->in_slot;
     a.out_slot[0] = (const RangeSlot *)d->out_slot0; a.out_slot[1] = (const RangeSlot *)d->out_slot1;
     a.y[0] = d->y0; a.y[1] = d->y1;
     a.N = d->N; a.H = d->H; a.W = d->W; a.C = d->C; a.Cp = (d->C + 15) / 16 * 16; a.stride = d->stride; a.relu = d->relu;
+    a.s_w = d->s_w; a.c_w = d->c_w;
     a.OH = (d->H + 2 - 3) / d->stride + 1; a.OW = (d->W + 2 - 3) / d->stride + 1;
-    a.strip = a.OW >= 56 ? 14 : (a.OW >= 14 ? 7 : a.OW);
-    a.strips = (a.OW + a.strip - 1) / a.strip;
-    const int64_t total = (int64_t)a.N * a.OH * a.strips * (a.Cp / 4);
+    const int P = d->stride == 1 ? DwStrip<1>::value : DwStrip<2>::value;
+    a.strips = (a.OW + P - 1) / P;
+    const int64_t total = (int64_t)a.N * a.OH * (a.Cp / 4);
+    if (total >= 0x7fffffffll) return (int)cudaErrorInvalidValue;
     const unsigned grid = (unsigned)((total + kThreads - 1) / kThreads);
-    if (d->stride == 1) dwq8_kernel<1><<<grid, kThreads, 0, (cudaStream_t)stream>>>(a);
-    else dwq8_kernel<2><<<grid, kThreads, 0, (cudaStream_t)stream>>>(a);
+    const cudaStream_t st = (cudaStream_t)stream;
+    if (d->stride == 1) {
+        if (d->y1) dwq8_kernel<1, true><<<grid, kThreads, 0, st>>>(a);
+        else dwq8_kernel<1, false><<<grid, kThreads, 0, st>>>(a);
+    } else {
+        if (d->y1) dwq8_kernel<2, true><<<grid, kThreads, 0, st>>>(a);
+        else dwq8_kernel<2, false><<<grid, kThreads, 0, st>>>(a);
+    }
     g_launches += 1;
     return (int)cudaGetLastError();
 }
@@ -706,12 +895,9 @@ extern "C" int dfq_mean_q8(const int8_t *x, const float *in_slot, int8_t *y, con
     if (!x || !in_slot || (!y && !yf) || (y && !out_slot) || N <= 0 || C <= 0 || HW <= 0)
         return (int)cudaErrorInvalidValue;
     const int Cp = (C + 15) / 16 * 16;
-    if (y) {
-        cudaError_t e = cudaMemsetAsync(y, 0, (size_t)N * Cp, (cudaStream_t)stream);     // pad channels: s8 zero
-        if (e != cudaSuccess) return (int)e;
-    }
-    meanq8_kernel<<<(unsigned)(N * ((C + 7) / 8)), kThreads, 0, (cudaStream_t)stream>>>(
-        x, (const RangeSlot *)in_slot, y, (const RangeSlot *)out_slot, yf, C, Cp, HW, Cp);
+    const int64_t total = N * (Cp / 4);
+    meanq8_kernel<<<(unsigned)((total + kThreads - 1) / kThreads), kThreads, 0, (cudaStream_t)stream>>>(
+        x, (const RangeSlot *)in_slot, y, (const RangeSlot *)out_slot, yf, C, Cp, HW, Cp, N);
     g_launches += 1;
     return (int)cudaGetLastError();
 }

@@ -64,6 +64,7 @@ class CudaBackend:
         slot = slot.contiguous()
         L.check(L.lib().dfq_dequant_codes_f32(codes.data_ptr(), 1, L.dev_f32(out, "weight"), out.numel(), 1,
                                               slot.data_ptr(), L.stream()), "dfq_dequant_codes_f32")
+        L.bump_weights_epoch()      # raw-pointer write: packed-code caches of the eval kernels are stale now
 
     def minmax(self, x):
         from .utils.quantize import minmax

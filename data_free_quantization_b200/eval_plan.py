@@ -449,6 +449,8 @@ class EvalPlan:
     def _i8_launch(self, m, wq, bq, src, out, st, images, P, linear):
         """Launch closure of the tensor-core kernel for this layer, or None when its weights are not on a grid."""
         from . import pw_i8
+        if not 1 <= int(m.quant.num_bits) <= 8:
+            return None                 # the s8 kernels cover activation grids of <= 8 bits: fp32 kernel instead
         pk = pw_i8.pack_weight(wq, getattr(m, "num_bits", None),
                                o_cap=pw_i8.choose_o_cap(images * P, wq.shape[0], fill=self.narrow_passes)
                                if self.narrow_passes > 0 else 0)
@@ -464,6 +466,8 @@ class EvalPlan:
     def _conv_i8_launch(self, m, wq, bq, src, out, st, stride, pad, dil):
         """Dense k x k convolution as tcgen05 implicit GEMM (dfq_conv_i8), or None when the weights are off-grid."""
         from . import pw_i8
+        if not 1 <= int(m.quant.num_bits) <= 8:
+            return None
         pk = pw_i8.pack_weight_conv(wq, getattr(m, "num_bits", None),
                                     o_cap=pw_i8.choose_o_cap(out.numel // out.shape[1], wq.shape[0],
                                                              fill=self.narrow_passes)
@@ -529,13 +533,19 @@ class EvalPlan:
         return self.output.buf
 
     def capture(self):
-        """Capture launch() into a CUDA graph; returns a callable replaying it."""
+        """Capture launch() into a CUDA graph; returns a callable replaying it.  The warm-up launch outside the capture
+        runs on whatever self.input.buf holds; with update_stat measures it would widen the running ranges with that
+        data, so the ranges are restored afterwards."""
+        saved = [(qm, qm.running_min.clone(), qm.running_max.clone()) for qm, _i, _t in self.measures]
         g = torch.cuda.CUDAGraph()
         s = torch.cuda.Stream()
         s.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(s):
             self.launch()                       # warm-up outside capture
         torch.cuda.current_stream().wait_stream(s)
+        for qm, lo, hi in saved:
+            qm.running_min.copy_(lo)
+            qm.running_max.copy_(hi)
         with torch.cuda.graph(g):
             self.launch()
         self.graph = g

@@ -63,13 +63,34 @@ class PackedQ8:
         self.n_pass, self.o_per_pass = n_pass.value, opp.value
 
 
+def pack_depthwise(w):
+    """[C, 1, 3, 3] fake-quantised depthwise weight -> ([3][Cp] words (w(r,0), w(r,1), w(r,2), 0) of centred s8 codes,
+    s_w, c_w) for dfq_dw_q8."""
+    rec = None
+    for b in (8, 7, 6, 5, 4, 3, 2):
+        rec = pw_i8._recover_codes(w, b)
+        if rec is not None:
+            break
+    if rec is None:
+        raise RuntimeError("q8 plan: depthwise weight is not on an integer grid of <= 8 bits")
+    s32, lo, q, bits = rec
+    up = 2 ** (8 - bits)
+    C = w.shape[0]
+    codes = ((q - 2 ** (bits - 1)) * up).to(torch.int8).cpu().numpy().reshape(C, 3, 3).astype(np.uint8).astype(np.uint32)
+    rows = np.zeros((3, _cp(C)), np.uint32)
+    rows[:, :C] = (codes[:, :, 0] | (codes[:, :, 1] << 8) | (codes[:, :, 2] << 16)).T
+    return torch.from_numpy(rows.view(np.int32)).to(w.device), s32 / up, float(np.float32(lo + 2 ** (bits - 1) * s32))
+
+
 def choose_o_cap(G, O, sms=148):
-    """Output channels per pass: 240 unless that leaves most SMs without a tile (small feature maps, the classifier)."""
+    """Output channels per pass.  112 (+ the row of ones = 128 accumulator columns): two accumulators then take 256 of
+    the 512 TMEM columns, so TWO CTAs -- 16 epilogue warps -- share an SM; the A tile a second pass re-reads is small
+    next to the codes it writes.  Narrower when that still leaves most SMs without a tile (the classifier)."""
     tiles = (int(G) + 127) // 128
-    if tiles * ((O + 239) // 240) >= sms // 2:
-        return 0
-    want = max(1, sms // tiles)
-    return max(16, min(240, _cp((O + want - 1) // want)))
+    if tiles * ((O + 111) // 112) >= sms:
+        return 112
+    want = max(1, (2 * sms) // tiles)
+    return max(16, min(112, _cp((O + want - 1) // want)))
 
 
 def to_codes_nhwc(x_codes_nchw):
@@ -77,6 +98,8 @@ def to_codes_nhwc(x_codes_nchw):
     a = torch.as_tensor(x_codes_nchw)
     if a.dim() == 2:
         a = a[:, :, None, None]
+    elif a.dim() == 3:
+        a = a[..., None]
     N, C, H, W = a.shape
     out = torch.zeros(N, H, W, _cp(C), dtype=torch.int8)
     out[..., :C] = (a.permute(0, 2, 3, 1).to(torch.int16) - 128).to(torch.int8)
@@ -178,16 +201,16 @@ class EvalPlanQ8(EvalPlan):
                     kind2 = "pw"
                 elif kh == 3 and kw == 3 and g == C == m.out_channels and p == 1 and d == 1 and s in (1, 2) and oidx:
                     Cp = _cp(C)
-                    w9 = torch.zeros(9, Cp, dtype=torch.float32, device=dev)
-                    w9[:, :C] = w.reshape(C, 9).t()
+                    wrow, dsw, dcw = pack_depthwise(w)
                     bp = torch.zeros(Cp, dtype=torch.float32, device=dev)
                     if b is not None:
                         bp[:C] = b
                     desc = L.DfqDwQ8Desc()
-                    desc.x, desc.w9, desc.bias = self.codes[st["slot"]].data_ptr(), w9.data_ptr(), bp.data_ptr()
+                    desc.x, desc.wrow, desc.bias = self.codes[st["slot"]].data_ptr(), wrow.data_ptr(), bp.data_ptr()
+                    desc.s_w, desc.c_w = dsw, dcw
                     desc.in_slot, desc.y0, desc.out_slot0, desc.y1, desc.out_slot1 = slot_ptr(st["slot"]), y0, s0, y1, s1
                     desc.N, desc.H, desc.W, desc.C, desc.stride, desc.relu = Nn, H, W, C, s, st["relu"]
-                    self.keep_q8 += [w9, bp, desc]
+                    self.keep_q8 += [wrow, bp, desc]
                     fn = (lambda dd: lambda: L.check(lib.dfq_dw_q8(ctypes.byref(dd), stream()), "dfq_dw_q8"))(desc)
                     kind2 = "dw"
                 else:

@@ -229,9 +229,21 @@ FUSED_EVAL = True
 fused_calls = {"conv_i8": 0, "pw_i8": 0, "depthwise": 0, "direct": 0, "linear_i8": 0}     # launches per kind (tests, tools)
 
 
+def invalidate_packed(model=None):
+    """Forget the packed integer codes cached on the layers (or everywhere, by moving the epoch).  Needed after a
+    write to `weight.data` that neither goes through this package nor bumps `weight._version` (`.data` detaches the
+    version counter): e.g. `layer.weight.data.mul_(2)`."""
+    L.bump_weights_epoch()
+    if model is not None:
+        for m in model.modules():
+            m.__dict__.pop("_dfq_packed", None)
+
+
 def _packed(layer, conv):
     """Integer codes of the layer's weight packed for the tensor-core kernels, cached until any weight-side pass
-    runs again (L.weights_epoch() moves with every descriptor-table upload) or the tensor is replaced."""
+    runs again (L.weights_epoch() moves with every descriptor-table upload, checkpoint unpack, sharded dequantise,
+    pipeline replay) or the tensor is replaced.  In-place writes through `weight.data` from outside the package are
+    invisible to the key: call invalidate_packed()."""
     from .. import pw_i8
     w = layer.weight
     key = (w.data_ptr(), w._version, tuple(w.shape), L.weights_epoch())
@@ -266,6 +278,8 @@ def _fused_conv_forward(layer, x):
     x = x.detach().contiguous()
     bias = None if layer.bias is None else layer.bias.detach()
     bits = int(layer.quant.num_bits)
+    if not 1 <= bits <= 8 and not (depthwise or direct):
+        return None                      # the s8 tensor-core kernels cover activation grids of <= 8 bits
     if depthwise or direct:
         slot = layer.quant.measure(x)
         y = torch.empty(N, O, OH, OW, dtype=torch.float32, device=x.device)
@@ -301,6 +315,8 @@ def _fused_linear_forward(layer, x):
     if not (FUSED_EVAL and x.is_cuda and not layer.quant.training and x.dim() == 2 and x.numel() > 0
             and x.dtype == torch.float32):
         return None
+    if not 1 <= int(layer.quant.num_bits) <= 8:
+        return None                      # the s8 tensor-core kernel covers activation grids of <= 8 bits
     pk = _packed(layer, conv=False)
     if pk is None:
         return None

@@ -340,12 +340,13 @@ int dfq_pw_q8(const DfqPwQ8Desc *desc_host, void *stream);
 
 typedef struct DfqDwQ8Desc {
     const int8_t *x;         /* [N][H][W][Cp]                                                            */
-    const float *w9;         /* [9][Cp] fp32 (fake-quantised) weights, tap-major, zero padded            */
+    const uint32_t *wrow;    /* [3][Cp] words (w(r,0), w(r,1), w(r,2), 0): centred s8 weight codes of kernel row r   */
     const float *bias;       /* [Cp] or NULL                                                             */
     const float *in_slot;
     int8_t *y0; const float *out_slot0;
     int8_t *y1; const float *out_slot1;
     int32_t N, H, W, C, stride, relu;
+    float s_w, c_w;          /* w_hat = s_w * (code_w - 128) + c_w                                       */
 } DfqDwQ8Desc;
 /* depthwise 3 x 3, padding 1, stride 1 or 2 */
 int dfq_dw_q8(const DfqDwQ8Desc *desc_host, void *stream);
