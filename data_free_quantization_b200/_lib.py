@@ -76,6 +76,10 @@ class DfqMergeDesc(ctypes.Structure):
                 ("first_row", i32)]
 
 
+class DfqDequantDesc(ctypes.Structure):
+    _fields_ = [("codes", c_void), ("y", c_void), ("n", i64), ("slot", c_void), ("first_block", i64)]
+
+
 class DfqClipDesc(ctypes.Structure):
     _fields_ = [("w", c_void), ("n", i64), ("first_block", i64)]
 
@@ -121,7 +125,7 @@ class DfqStemQ8Desc(ctypes.Structure):
 
 
 Q_SYMMETRIC, Q_RANGE_F32, Q_PER_CHANNEL, Q_CLAMP_OUT = 1, 2, 4, 8
-ABI_VERSION = 14
+ABI_VERSION = 15
 
 # every symbol include/dfq_b200.h declares: (restype, argtypes)
 P = ctypes.POINTER
@@ -172,6 +176,8 @@ PROTOTYPES = {
     "dfq_quant_plan_host": (ctypes.c_int, [P(DfqQuantDesc), ctypes.c_int, P(i64), P(i64)]),
     "dfq_fake_quant_multi_f32": (ctypes.c_int, [c_void, ctypes.c_int, i64, i64, c_void, c_void]),
     "dfq_dequant_codes_f32": (ctypes.c_int, [c_void, ctypes.c_int, c_void, i64, i64, c_void, c_void]),
+    "dfq_dequant_plan_host": (ctypes.c_int, [P(DfqDequantDesc), ctypes.c_int, P(i64)]),
+    "dfq_dequant_multi_f32": (ctypes.c_int, [c_void, ctypes.c_int, i64, c_void]),
     "dfq_cle_plan_host": (ctypes.c_int, [P(DfqClePair), ctypes.c_int, P(ctypes.c_int), P(ctypes.c_int)]),
     "dfq_cle_layers_plan_host": (ctypes.c_int, [P(DfqCleLayer), ctypes.c_int, P(ctypes.c_int)]),
     "dfq_cle_result_bytes": (i64, [ctypes.c_int]),

@@ -203,9 +203,68 @@ dequant_codes_kernel(const CodeT *__restrict__ codes, float *__restrict__ y, int
     }
 }
 
+// Multi-tensor form for the receiving side of the layer-sharded pass (dist.py): one launch dequantises every layer this
+// rank does not own.  `codes` and `slot` may point into a PEER GPU's memory (NVLink P2P through a symmetric-memory
+// buffer): the codes are then read straight from their owner -- 1 byte per element over the link, no staging copy, no
+// all-gather -- and the fp32 values are written locally.  A block converts 16 K elements, 16 codes per thread-load.
+constexpr int kDeqBlock = 16384;
+
+__global__ void __launch_bounds__(kThreads)
+dequant_multi_kernel(const DfqDequantDesc *__restrict__ descs, int n_desc) {
+    int lo = 0, hi = n_desc - 1;
+    while (lo < hi) {
+        int mid = (lo + hi + 1) >> 1;
+        if (descs[mid].first_block <= (int64_t)blockIdx.x) lo = mid; else hi = mid - 1;
+    }
+    const DfqDequantDesc d = descs[lo];
+    const RangeSlot r = *reinterpret_cast<const RangeSlot *>(d.slot);
+    const int64_t begin = ((int64_t)blockIdx.x - d.first_block) * kDeqBlock, end = min(begin + (int64_t)kDeqBlock, d.n);
+    const uint8_t *c = reinterpret_cast<const uint8_t *>(d.codes);
+    if (((((uintptr_t)c) | ((uintptr_t)d.y)) & 15) == 0) {
+        for (int64_t k = begin + 16 * (int64_t)threadIdx.x; k < end; k += 16 * kThreads) {
+            if (k + 16 <= end) {
+                const uint4 w = *reinterpret_cast<const uint4 *>(c + k);
+                const uint32_t ww[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    float4 o;
+                    o.x = __fadd_rn(__fmul_rn((float)(ww[j] & 0xffu), r.scale), r.mn);
+                    o.y = __fadd_rn(__fmul_rn((float)((ww[j] >> 8) & 0xffu), r.scale), r.mn);
+                    o.z = __fadd_rn(__fmul_rn((float)((ww[j] >> 16) & 0xffu), r.scale), r.mn);
+                    o.w = __fadd_rn(__fmul_rn((float)(ww[j] >> 24), r.scale), r.mn);
+                    *reinterpret_cast<float4 *>(d.y + k + 4 * j) = o;
+                }
+            } else {
+                for (int64_t e = k; e < end; ++e) d.y[e] = __fadd_rn(__fmul_rn((float)c[e], r.scale), r.mn);
+            }
+        }
+    } else {
+        for (int64_t k = begin + threadIdx.x; k < end; k += kThreads)
+            d.y[k] = __fadd_rn(__fmul_rn((float)c[k], r.scale), r.mn);
+    }
+}
+
 }  // namespace dfq
 
 using namespace dfq;
+
+extern "C" int dfq_dequant_plan_host(DfqDequantDesc *d, int n, int64_t *total_blocks) {
+    int64_t b = 0;
+    for (int i = 0; i < n; ++i) {
+        if (d[i].n <= 0 || !d[i].codes || !d[i].y || !d[i].slot) return (int)cudaErrorInvalidValue;
+        d[i].first_block = b;
+        b += (d[i].n + kDeqBlock - 1) / kDeqBlock;
+    }
+    *total_blocks = b;
+    return b > 0x7fffffffll ? (int)cudaErrorInvalidValue : 0;
+}
+
+extern "C" int dfq_dequant_multi_f32(const DfqDequantDesc *descs_dev, int n_desc, int64_t total_blocks, void *stream) {
+    if (n_desc <= 0 || total_blocks <= 0) return 0;
+    dequant_multi_kernel<<<(unsigned)total_blocks, kThreads, 0, (cudaStream_t)stream>>>(descs_dev, n_desc);
+    g_launches += 1;
+    return (int)cudaGetLastError();
+}
 
 extern "C" int dfq_dequant_codes_f32(const void *codes, int code_bytes, float *y, int64_t n, int64_t rows,
                                      const float *slots_dev, void *stream) {

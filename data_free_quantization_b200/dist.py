@@ -80,44 +80,162 @@ def _pad16(n):
 
 
 def _layout(layers, owner, world, with_bias):
-    """Byte layout of every rank's send buffer: {layer index: (codes offset, slot offset, bias offset or None)}."""
+    """Byte layout of every rank's exchange buffer: [codes of its layers, each padded to 16 B][one 16-byte slot
+    (min, max, scale, 0) per layer][fp32 biases].  Returns ({layer: (codes offset, slot offset, bias offset | None)},
+    per-rank sizes)."""
     offs, totals = {}, [0] * world
-    for i, layer in enumerate(layers):
-        r = owner[i]
-        o = totals[r]
-        co = o
-        o += _pad16(layer.weight.numel())
-        so = o
-        o += 16
-        bo = None
-        if with_bias and layer.bias is not None:
-            bo = o
-            o += _pad16(4 * layer.bias.numel())
-        offs[i] = (co, so, bo)
+    by_rank = [[i for i in range(len(layers)) if owner[i] == r] for r in range(world)]
+    for r, idxs in enumerate(by_rank):
+        o = 0
+        co = {}
+        for i in idxs:
+            co[i] = o
+            o += _pad16(layers[i].weight.numel())
+        so = {}
+        for i in idxs:
+            so[i] = o
+            o += 16
+        for i in idxs:
+            bo = None
+            if with_bias and layers[i].bias is not None:
+                bo = o
+                o += _pad16(4 * layers[i].bias.numel())
+            offs[i] = (co[i], so[i], bo)
         totals[r] = o
     return offs, totals
+
+
+class _Exchange:
+    """The buffer the quantised state crosses GPUs through.  Preferred: a SYMMETRIC-MEMORY buffer
+    (torch.distributed._symmetric_memory: every rank maps every peer's buffer over NVLink), so that the dequantising
+    kernel reads the codes straight out of their owner's HBM -- one pass, 1 byte per element over the link, no
+    all-gather, no staging copy.  Fallback (no P2P / DFQ_DIST_P2P=0): one all_gather_into_tensor of the buffers."""
+
+    _cache = {}
+
+    def __init__(self, width, dev, group):
+        import os
+        self.width, self.dev, self.group = width, dev, group
+        self.handle, self.peers = None, None
+        self.world = dist.get_world_size(group)
+        if os.environ.get("DFQ_DIST_P2P", "1") != "0" and dev.type == "cuda":
+            try:
+                import torch.distributed._symmetric_memory as symm
+                self.buf = symm.empty(width, dtype=torch.uint8, device=dev)
+                self.handle = symm.rendezvous(self.buf, group if group is not None else dist.group.WORLD)
+                self.peers = [self.handle.get_buffer(r, (width,), torch.uint8) for r in range(self.world)]
+            except Exception as exc:                          # noqa: BLE001 -- reported, then the collective path
+                self.handle, self.peers = None, None
+                self.why = repr(exc)[:200]
+        if self.handle is None:
+            self.buf = torch.zeros(width, dtype=torch.uint8, device=dev)
+            self.recv = torch.empty(self.world * width, dtype=torch.uint8, device=dev)
+
+    @classmethod
+    def get(cls, width, dev, group):
+        key = (width, str(dev), id(group))
+        if key not in cls._cache:
+            if len(cls._cache) > 4:
+                cls._cache.clear()
+            cls._cache[key] = cls(width, dev, group)
+        return cls._cache[key]
+
+    def exchange(self):
+        """After every rank has filled its buffer: returns [rank -> uint8 view of that rank's buffer]."""
+        if self.handle is not None:
+            self.handle.barrier()                             # all buffers complete and visible to their peers
+            return self.peers
+        dist.all_gather_into_tensor(self.recv, self.buf, group=self.group)
+        return list(self.recv.view(self.world, self.width))
+
+    def release(self):
+        """Peers are done reading this rank's buffer (before it is overwritten by the next pass)."""
+        if self.handle is not None:
+            self.handle.barrier()
 
 
 def quantize_targ_layer_sharded(graph, bit_weight=8, bits_bias=16, targ_type=None, group=None, backend=None):
     """quantize_targ_layer (utils/layer_transform.py:288-305) with the layers dealt to the ranks of `group`; on
     return every rank holds the complete quantised weights and biases, identical to the single-GPU pass.
-    Returns {"owner": [...], "bytes_gathered": per-rank payload}."""
+
+    Every rank fake-quantises its layers with the codes written IN PLACE into its exchange buffer (one multi-tensor
+    launch), then ONE multi-tensor launch dequantises all foreign layers -- from the peers' buffers over NVLink when
+    symmetric memory is available, else from an all-gathered copy.
+    Returns {"owner": [...], "bytes_gathered": bytes this rank received, "path": "p2p" | "all_gather" | ...}."""
     assert targ_type is not None, "targ_type cannot be None!"
     assert 1 <= bit_weight <= 8, "the sharded pass ships 8-bit codes"
-    backend = backend or CudaBackend()
     rank, world = rank_world(group)
     layers = [graph[k] for k in graph if type(graph[k]) in targ_type]
     owner = balance([layer.weight.numel() for layer in layers], world)
     with_bias = bits_bias < 32
     mine = [i for i in range(len(layers)) if owner[i] == rank]
+    if backend is not None:
+        return _sharded_generic(layers, owner, mine, rank, world, bit_weight, bits_bias, with_bias, group, backend)
+    from . import _lib as L
+    from .utils.quantize import fake_quant_tensors
+    import ctypes
+    with torch.no_grad():
+        if world == 1:
+            CudaBackend().quantize_weights([layers[i].weight.data for i in mine], bit_weight)
+            if with_bias:
+                CudaBackend().quantize_bias([layers[i].bias.data for i in mine if layers[i].bias is not None], bits_bias)
+            return {"owner": owner, "bytes_gathered": 0, "path": "single"}
+        offs, totals = _layout(layers, owner, world, with_bias)
+        width = _pad16(max(totals))
+        dev = layers[0].weight.device
+        ex = _Exchange.get(width, dev, group)
+        send = ex.buf
+        # own layers: codes land in the exchange buffer, ranges in one copy, biases in one concatenation
+        if mine:
+            ws = [layers[i].weight.data for i in mine]
+            codes = [send[offs[i][0]:offs[i][0] + layers[i].weight.numel()].view(layers[i].weight.shape) for i in mine]
+            slots = fake_quant_tensors(ws, bit_weight, 0, codes=codes)            # [n_mine, 4] {min, max, scale, 0}
+            s0 = offs[mine[0]][1]
+            send[s0:s0 + 16 * len(mine)].view(torch.float32).view(len(mine), 4).copy_(slots)
+            if with_bias:
+                bs = [layers[i].bias.data for i in mine if layers[i].bias is not None]
+                if bs:
+                    fake_quant_tensors(bs, bits_bias, 0)
+                    for i in mine:
+                        bo = offs[i][2]
+                        if bo is not None:
+                            b = layers[i].bias.data
+                            send[bo:bo + 4 * b.numel()].view(torch.float32).copy_(b)
+        bufs = ex.exchange()
+        theirs = [i for i in range(len(layers)) if owner[i] != rank]
+        if theirs:
+            descs = (L.DfqDequantDesc * len(theirs))()
+            for d, i in zip(descs, theirs):
+                base = bufs[owner[i]].data_ptr()
+                d.codes, d.slot = base + offs[i][0], base + offs[i][1]
+                d.y, d.n = L.dev_f32(layers[i].weight.data, "weight"), layers[i].weight.numel()
+            blocks = L.i64()
+            L.check(L.lib().dfq_dequant_plan_host(descs, len(theirs), ctypes.byref(blocks)), "dfq_dequant_plan_host")
+            table = L.table_to_device(descs, dev)
+            L.check(L.lib().dfq_dequant_multi_f32(table.data_ptr(), len(theirs), blocks.value, L.stream()),
+                    "dfq_dequant_multi_f32")
+            if with_bias:
+                for i in theirs:
+                    bo = offs[i][2]
+                    if bo is not None:
+                        b = layers[i].bias.data
+                        b.copy_(bufs[owner[i]][bo:bo + 4 * b.numel()].view(torch.float32))
+        ex.release()
+        got = sum(totals[r] for r in range(world) if r != rank)
+    return {"owner": owner, "bytes_gathered": got, "path": "p2p" if ex.handle is not None else "all_gather",
+            "p2p_unavailable": getattr(ex, "why", None)}
+
+
+def _sharded_generic(layers, owner, mine, rank, world, bit_weight, bits_bias, with_bias, group, backend):
+    """The same exchange with injected compute callables (CPU tests with gloo: tests/test_dist_cpu.py)."""
     with torch.no_grad():
         got = backend.quantize_weights([layers[i].weight.data for i in mine], bit_weight)
         if with_bias:
             backend.quantize_bias([layers[i].bias.data for i in mine if layers[i].bias is not None], bits_bias)
         if world == 1:
-            return {"owner": owner, "bytes_gathered": 0}
+            return {"owner": owner, "bytes_gathered": 0, "path": "single"}
         offs, totals = _layout(layers, owner, world, with_bias)
-        width = max(totals)
+        width = _pad16(max(totals))
         dev = layers[0].weight.device
         send = torch.zeros(width, dtype=torch.uint8, device=dev)
         for i, (codes, slot) in zip(mine, got):
@@ -140,7 +258,7 @@ def quantize_targ_layer_sharded(graph, bit_weight=8, bits_bias=16, targ_type=Non
             backend.dequantize(recv[r, co:co + n], recv[r, so:so + 16].view(torch.float32), layer.weight.data)
             if bo is not None:
                 layer.bias.data.copy_(recv[r, bo:bo + 4 * layer.bias.numel()].view(torch.float32))
-    return {"owner": owner, "bytes_gathered": width}
+    return {"owner": owner, "bytes_gathered": width, "path": "all_gather"}
 
 
 def fake_quant_sliced(x_slice, bits=8, group=None, backend=None):
@@ -169,7 +287,10 @@ def inference_all_sharded(run_batch, batches, group=None, device=None):
             pred = logits.argmax(1).cpu()
             correct += int((pred == labels[a:b]).sum())
             total += b - a
-    t = torch.tensor([correct, total], dtype=torch.int64, device=device or "cpu")
+    if device is None:          # NCCL reduces CUDA tensors only
+        device = torch.device("cuda", torch.cuda.current_device()) if (
+            world > 1 and dist.get_backend(group) == "nccl") else "cpu"
+    t = torch.tensor([correct, total], dtype=torch.int64, device=device)
     if world > 1:
         dist.all_reduce(t, group=group)
     return int(t[0]), int(t[1])

@@ -48,13 +48,18 @@ class _T:
 
 class EvalPlan:
     def __init__(self, model, transformer, batch, in_shape=(3, 224, 224), pw_impl="i8", dense_impl="i8",
-                 move_impl="native"):
+                 move_impl="native", sync_group=None):
         """pw_impl: "i8" = pointwise convs / linear layers on the tcgen05 s8 kernel (csrc/pw_i8.cu) wherever the
         layer's weights sit on an integer grid of <= 8 bits, "fp32" = the CUDA-core comparator everywhere.
         move_impl: "native" = pad / pooling / interpolate / cat as one-pass libdfq_b200 kernels (csrc/move.cu) that
         quantise on load and reduce the output statistics themselves; "torch" = the comparator (our fake-quant into a
         temporary, the torch op, a separate statistics pass)."""
         self.move_impl = move_impl
+        # sync_stats mode (SURVEY.md 8e): `batch` is this rank's SHARD of a batch split across `sync_group`; before every
+        # running-range update the per-sample extrema of all shards are all-gathered (in rank order = sample order), so
+        # mean_n(max_chw x) of utils/quantize.py:110-111 is taken over the UN-SHARDED batch and every rank reproduces
+        # the single-GPU ranges bit for bit (74 tiny collectives per forward: a parity mode, not a fast one).
+        self.sync_group = sync_group
         # Narrower tensor-core passes (pw_i8.choose_o_cap) for layers whose default grid leaves SMs idle.  Measured on
         # B200: every pass re-quantises its A tile, and the producer, not the accumulator width, sets a CTA's time --
         # narrowing EVERY under-filled layer made 576 -> 160 at 256 x 7 x 7 0.050 -> 0.074 ms (4 passes of 48) and
@@ -255,9 +260,22 @@ class EvalPlan:
             """Launch closure of the measure kernel feeding slot `idx` (dynamic ranges run every forward)."""
             qm, _, t = self.measures[idx]
             upd = 1 if qm.update_stat else 0
+            self.keep.append(qm)
+            if upd and self.sync_group is not None:
+                import torch.distributed as dist
+                world = dist.get_world_size(self.sync_group)
+                full = torch.empty(world * N, 2, dtype=t.stats.dtype, device=dev)
+                self.keep.append(full)
+                sargs = (full.data_ptr(), 1 if t.stats_encoded else 0, world * N, qm.running_min.data_ptr(),
+                         qm.running_max.data_ptr(), slot_ptr(idx), int(qm.num_bits), 0, upd)
+                group, local = self.sync_group, t.stats
+
+                def synced():
+                    dist.all_gather_into_tensor(full, local.view(N, 2), group=group)
+                    L.check(lib.dfq_measure_from_stats(*sargs, stream()), "dfq_measure_from_stats")
+                return synced
             args = (stats_ptr(t) if upd else None, 1 if t.stats_encoded else 0, N, qm.running_min.data_ptr(),
                     qm.running_max.data_ptr(), slot_ptr(idx), int(qm.num_bits), 0, upd)
-            self.keep.append(qm)
             return lambda: L.check(lib.dfq_measure_from_stats(*args, stream()), "dfq_measure_from_stats")
 
         self.static_measures = []

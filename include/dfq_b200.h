@@ -23,7 +23,7 @@
 extern "C" {
 #endif
 
-#define DFQ_ABI_VERSION 14
+#define DFQ_ABI_VERSION 15
 
 #if defined(__GNUC__)
 #pragma GCC visibility push(default)   /* the library is built with -fvisibility=hidden */
@@ -171,6 +171,16 @@ typedef struct DfqClipDesc {
     int64_t n;
     int64_t first_block; /* filled by dfq_clip_plan_host */
 } DfqClipDesc;
+
+/* One tensor of the multi-tensor dequantisation (8-bit codes of an asymmetric grid -> fp32, the two roundings of
+ * utils/quantize.py:76).  codes / slot may live in a peer GPU's memory (P2P). */
+typedef struct DfqDequantDesc {
+    const void *codes;   /* uint8 [n]                                                  */
+    float *y;            /* fp32 [n]                                                   */
+    int64_t n;
+    const float *slot;   /* {min, max, scale, 0}                                       */
+    int64_t first_block; /* filled by dfq_dequant_plan_host                            */
+} DfqDequantDesc;
 
 int dfq_abi_version(void);
 const char *dfq_error_string(int err);
@@ -413,6 +423,10 @@ int64_t dfq_cle3_scratch_bytes(const DfqCle3Plan *plan);
 int dfq_cle3_run(const DfqCle3Tensor *tensors_dev, const DfqCle3Chain *chains_dev, const DfqCle3Plan *plan_host,
                  void *scratch_dev, double smin, double smax, int is_signed, float eps, double threshold, int count,
                  int max_iters, void *result_dev, void *debug_dev, void *stream);
+
+/* all tensors of a table in ONE launch (the receiving side of the layer-sharded pass, dist.py) */
+int dfq_dequant_plan_host(DfqDequantDesc *descs_host, int n_desc, int64_t *total_blocks);
+int dfq_dequant_multi_f32(const DfqDequantDesc *descs_dev, int n_desc, int64_t total_blocks, void *stream);
 
 /* ---- (c) bias absorption (+ optional weight clip): bias_absorption.py:9-80, clip_weight.py:4-33 */
 int dfq_absorb_plan_host(DfqAbsorbPair *pairs_host, int n_pairs, int *total_rows);

@@ -49,8 +49,35 @@ s0, s1 = shard_range(full.numel(), rank, world)
 mine = full[s0:s1].clone()
 lo, hi = fake_quant_sliced(mine, 8)
 assert (lo, hi) == (lo_, hi_) and torch.equal(mine, want[s0:s1])
+# batch-sharded eval in sync_stats mode: the per-sample extrema of all shards are gathered before every
+# running-range update, so each rank's shard of the logits and every QuantMeasure range equal the un-sharded run
+import numpy as np  # noqa: E402
+from helpers import dfq_quantised  # noqa: E402
+from data_free_quantization_b200.eval_plan import EvalPlan  # noqa: E402
+from data_free_quantization_b200.dist import inference_all_sharded  # noqa: E402
+gold = np.load(os.path.join(ROOT, "tests", "golden", "mobilenetv2_dfq.npz"))
+B = 4 * world
+x = torch.randn(B, 3, 224, 224, generator=torch.Generator().manual_seed(2))
+with contextlib.redirect_stdout(io.StringIO()):
+    m1, g1, _b, targ1, tr1 = dfq_quantised("mobilenetv2", dev, gold)
+    full = EvalPlan(m1, tr1, batch=B)(x.to(dev)).clone()
+    m2, g2, _b, targ2, tr2 = dfq_quantised("mobilenetv2", dev, gold)
+    s0, s1 = shard_range(B, rank, world)
+    plan = EvalPlan(m2, tr2, batch=s1 - s0, sync_group=dist.group.WORLD)
+    part = plan(x[s0:s1].to(dev)).clone()
+torch.cuda.synchronize()
+assert torch.equal(part.view(s1 - s0, -1), full.view(B, -1)[s0:s1]), (rank, float((part.view(s1 - s0, -1) - full.view(B, -1)[s0:s1]).abs().max()))
+for (k1, a1), (k2, a2) in zip(g1.items(), g2.items()):
+    if type(a1) in targ1:
+        assert float(a1.quant.running_min) == float(a2.quant.running_min) and float(a1.quant.running_max) == float(a2.quant.running_max)
+# the eval loop itself (main_dfq.py:66-113) with the counts all-reduced over NCCL (device defaults to the CUDA device)
+labels = full.view(B, -1).argmax(1).cpu()
+correct, total = inference_all_sharded(lambda xs: plan(xs.to(dev)).view(xs.shape[0], -1), [(x, labels)])
+assert (correct, total) == (B, B), (correct, total)
 dist.barrier()
 if rank == 0:
     print(f"dist_check ok: world {world}, sharded state dict bit-identical ({len(info['owner'])} layers, "
-          f"{info['bytes_gathered']} B gathered per rank), sliced tensor bit-identical")
+          f"{info['bytes_gathered']} B received per rank, path {info['path']}"
+          f"{'' if info.get('p2p_unavailable') is None else ' [' + info['p2p_unavailable'] + ']'}), sliced tensor "
+          f"bit-identical, batch-sharded eval with sync_stats equals the un-sharded forward bit for bit")
 dist.destroy_process_group()
