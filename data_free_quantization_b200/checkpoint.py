@@ -117,3 +117,48 @@ def unpack_into(model, packed):
                 else:
                     b.copy_(e["bias_fp32"])
     return model
+
+
+# ---- true integer biases (the "8-bit weights with 32-bit bias" scheme of the reference's report,
+# mla_report_latex/main.tex:157-166) ------------------------------------------------------------------------------
+# The reference quantises a bias on its OWN (min, max) grid (utils/layer_transform.py:301-303), which an integer
+# pipeline cannot add to an s32 accumulator.  With static activation ranges the accumulator of a layer counts units of
+# s_x * s_w (input scale x weight scale), so the bias that an integer engine adds is round(b / (s_x s_w)) as int32.
+# This is an optional export next to the reference-exact one: |b_int s_x s_w - b| <= s_x s_w / 2.
+def integer_biases(model, graph, targ_type):
+    """{module name: {"bias_i32": int32 [O] (CPU), "scale": s_x * s_w}} for every target layer with a bias whose weight
+    sits on an integer grid and whose QuantMeasure holds a static range (after set_quant_minmax)."""
+    import ctypes
+    import numpy as np
+    from . import pw_i8
+    names = {id(m): n for n, m in model.named_modules()}
+    out = {}
+    for k in graph:
+        m = graph[k]
+        if type(m) not in targ_type or m.bias is None or not hasattr(m, "quant"):
+            continue
+        rec = None
+        for b in (8, 7, 6, 5, 4, 3, 2):
+            rec = pw_i8._recover_codes(m.weight.data, b)
+            if rec is not None:
+                break
+        if rec is None:
+            continue
+        s_w = rec[0]
+        p = L.DfqQuantParams()
+        L.lib().dfq_quant_params_host(float(m.quant.running_min), float(m.quant.running_max), int(m.quant.num_bits), 0,
+                                      ctypes.byref(p))
+        scale = float(np.float32(p.scale)) * float(s_w)
+        bi = torch.round(m.bias.data.double().cpu() / scale).clamp_(-2 ** 31, 2 ** 31 - 1).to(torch.int32)
+        out[names[id(m)]] = {"bias_i32": bi, "scale": scale}
+    return out
+
+
+def apply_integer_biases(model, table):
+    """Replace the layers' biases by their integer form b_int * (s_x s_w) (what an integer-only engine computes)."""
+    mods = dict(model.named_modules())
+    with torch.no_grad():
+        for name, e in table.items():
+            b = mods[name].bias.data
+            b.copy_((e["bias_i32"].double() * e["scale"]).float().to(b.device))
+    L.bump_weights_epoch()

@@ -22,9 +22,23 @@ inline unsigned reduce_grid(int64_t virtual_blocks) {
     return (unsigned)(virtual_blocks < g ? virtual_blocks : g);
 }
 
-// Monotone float -> uint map (larger float => larger code); 0 is below every real value.
+// torch.min / torch.max propagate NaN (utils/quantize.py:29-37, float(W.min())); fminf / fmaxf drop it.
+__device__ __forceinline__ float fmin_nan(float a, float b) {
+    float r;
+    asm("min.NaN.f32 %0, %1, %2;" : "=f"(r) : "f"(a), "f"(b));
+    return r;
+}
+__device__ __forceinline__ float fmax_nan(float a, float b) {
+    float r;
+    asm("max.NaN.f32 %0, %1, %2;" : "=f"(r) : "f"(a), "f"(b));
+    return r;
+}
+
+// Monotone float -> uint map (larger float => larger code); 0 is below every real value.  NaN (either sign) maps to
+// the largest code, so it wins every atomicMax and decodes to NaN again: a range that saw a NaN is NaN.
 __device__ __forceinline__ unsigned enc_ordered(float f) {
     unsigned u = __float_as_uint(f);
+    if (f != f) return 0xffffffffu;
     return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
 }
 __device__ __forceinline__ float dec_ordered(unsigned e) {
@@ -34,12 +48,12 @@ __device__ __forceinline__ float dec_ordered(unsigned e) {
 
 __device__ __forceinline__ float warp_min(float v) {
 #pragma unroll
-    for (int o = 16; o; o >>= 1) v = fminf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    for (int o = 16; o; o >>= 1) v = fmin_nan(v, __shfl_xor_sync(0xffffffffu, v, o));
     return v;
 }
 __device__ __forceinline__ float warp_max(float v) {
 #pragma unroll
-    for (int o = 16; o; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    for (int o = 16; o; o >>= 1) v = fmax_nan(v, __shfl_xor_sync(0xffffffffu, v, o));
     return v;
 }
 __device__ __forceinline__ float warp_sum(float v) {
@@ -64,7 +78,7 @@ __device__ __forceinline__ void block_minmax(float &lo, float &hi, float *smem /
     lo = smem[0];
     hi = smem[kWarps];
 #pragma unroll
-    for (int i = 1; i < kWarps; ++i) { lo = fminf(lo, smem[i]); hi = fmaxf(hi, smem[kWarps + i]); }
+    for (int i = 1; i < kWarps; ++i) { lo = fmin_nan(lo, smem[i]); hi = fmax_nan(hi, smem[kWarps + i]); }
 }
 
 // min/max of [begin,end) of x; vectorised when the address allows it.
@@ -87,16 +101,16 @@ __device__ __forceinline__ void chunk_minmax(const float *__restrict__ x, int64_
         for (int u = 0; u < 4; ++u) {
             int64_t k = i + (int64_t)u * kThreads;
             if (k < n4) {
-                lo = fminf(lo, fminf(fminf(v[u].x, v[u].y), fminf(v[u].z, v[u].w)));
-                hi = fmaxf(hi, fmaxf(fmaxf(v[u].x, v[u].y), fmaxf(v[u].z, v[u].w)));
+                lo = fmin_nan(lo, fmin_nan(fmin_nan(v[u].x, v[u].y), fmin_nan(v[u].z, v[u].w)));
+                hi = fmax_nan(hi, fmax_nan(fmax_nan(v[u].x, v[u].y), fmax_nan(v[u].z, v[u].w)));
             }
         }
         for (int64_t k = (n4 << 2) + threadIdx.x; k < n; k += kThreads) {
-            float t = p[k]; lo = fminf(lo, t); hi = fmaxf(hi, t);
+            float t = p[k]; lo = fmin_nan(lo, t); hi = fmax_nan(hi, t);
         }
     } else {
         for (int64_t k = threadIdx.x; k < n; k += kThreads) {
-            float t = p[k]; lo = fminf(lo, t); hi = fmaxf(hi, t);
+            float t = p[k]; lo = fmin_nan(lo, t); hi = fmax_nan(hi, t);
         }
     }
 }
@@ -118,7 +132,7 @@ __host__ __device__ inline DfqQuantParams make_quant_params(double mn, double mx
         sc = (flags & DFQ_Q_RANGE_F32) ? (double)(((float)mx - (float)mn) / (float)(qhi - qlo))
                                        : (mx - mn) / (qhi - qlo);
     }
-    if (!(sc > 1e-8)) sc = 1e-8;
+    if (1e-8 > sc) sc = 1e-8;              // Python max(scale, 1e-8): a NaN scale stays NaN (utils/quantize.py:68)
     DfqQuantParams p;
     p.neg_min = (float)(-mn);
     p.scale = (float)sc;

@@ -77,7 +77,7 @@ __device__ __forceinline__ void warp_rows_minmax(const DfqQuantDesc &d, const Bl
     const float *p = d.x + r * w.cols;
     float lo = INFINITY, hi = -INFINITY;
     for (int64_t k = threadIdx.x & 31; k < w.cols; k += 32) {
-        float t = p[k]; lo = fminf(lo, t); hi = fmaxf(hi, t);
+        float t = p[k]; lo = fmin_nan(lo, t); hi = fmax_nan(hi, t);
     }
     lo = warp_min(lo); hi = warp_max(hi);
     if ((threadIdx.x & 31) == 0) {

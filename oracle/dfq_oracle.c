@@ -30,13 +30,15 @@
 EXPORT void dfqo_minmax_f32(const float *x, int64_t n, float *mn, float *mx)
 {
     float lo = INFINITY, hi = -INFINITY;
+    int nan = 0;
     for (int64_t i = 0; i < n; ++i) {
         float v = x[i];
+        if (v != v) nan = 1;                /* torch.min / torch.max propagate NaN */
         if (v < lo) lo = v;
         if (v > hi) hi = v;
     }
-    *mn = lo;
-    *mx = hi;
+    *mn = nan ? NAN : lo;
+    *mx = nan ? NAN : hi;
 }
 
 /* ------------------------------------------------------------- quant params */
@@ -66,7 +68,7 @@ EXPORT void dfqo_quant_params(double min_value, double max_value, int bits, int 
         else
             sc = (max_value - min_value) / (qhi - qlo);
     }
-    if (!(sc > 1e-8)) sc = 1e-8;          /* scale = max(scale, 1e-8)  :68 */
+    if (1e-8 > sc) sc = 1e-8;             /* scale = max(scale, 1e-8)  :68 -- Python max(): a NaN scale stays NaN */
     *neg_min = (float)(-mn);
     *scale = (float)sc;
     *qmin = (float)qlo;

@@ -51,3 +51,29 @@ def test_rejects_foreign_file(tmp_path):
     torch.save({"format": "something else"}, p)
     with pytest.raises(ValueError):
         C.load_packed(p)
+
+
+def test_true_integer_biases(gold_npz):
+    """int32 biases in units of s_x * s_w.  Each is within half a unit of the reference-exact bias,
+    and the static u8 plan run with them keeps every class of the reference-exact run."""
+    import numpy as np
+    from helpers import dfq_quantised
+    from data_free_quantization_b200 import checkpoint as C
+    from data_free_quantization_b200.eval_q8 import EvalPlanQ8
+    model, graph, bottoms, targ, tr = dfq_quantised("mobilenetv2", "cuda:0", gold_npz)
+    for m in model.modules():
+        if hasattr(m, "set_update_stat"):
+            m.set_update_stat(False)
+    x = torch.randn(32, 3, 224, 224, generator=torch.Generator().manual_seed(7)).to("cuda:0")
+    base = EvalPlanQ8(model, tr, batch=32)(x).clone()
+    table = C.integer_biases(model, graph, targ)
+    assert len(table) == 53
+    mods = dict(model.named_modules())
+    for name, e in table.items():
+        b = mods[name].bias.data.double().cpu()
+        assert e["bias_i32"].dtype == torch.int32
+        assert float((e["bias_i32"].double() * e["scale"] - b).abs().max()) <= 0.5 * e["scale"] * (1 + 1e-6)
+    C.apply_integer_biases(model, table)
+    got = EvalPlanQ8(model, tr, batch=32)(x)
+    assert torch.equal(got.argmax(1), base.argmax(1))
+    assert float((got - base).abs().max()) <= 5e-2 * float(base.abs().max())
