@@ -365,10 +365,13 @@ def sharded_microbench(torch, dev, world, peak_gbs, elems=1 << 26, per_rank=2, r
         ms = float(t[0])
     total = elems * world * per_rank
     gbs = 12 * total / (ms * 1e-3) / 1e9
-    return {"kernel": "layer-sharded fake-quant + all-gather of u8 codes + local dequant", "tensors": world * per_rank,
+    return {"kernel": "layer-sharded fake-quant; foreign layers dequantised from the owners' u8 codes (read over NVLink "
+                      "from symmetric memory, or all-gathered)", "tensors": world * per_rank,
             "elems_per_tensor": elems, "bytes_per_elt": 12, "ms": round(ms, 4), "achieved": round(gbs, 1),
             "per_gpu": round(gbs / world, 1), "peak_per_gpu": peak_gbs, "unit": "GB/s",
-            "gathered_bytes_per_rank": int(info["bytes_gathered"])}
+            "received_bytes_per_rank": int(info["bytes_gathered"]), "exchange": info.get("path"),
+            "nvlink_floor_note": "every rank must receive (N-1)/N of all codes (1 B/elt): at N = 8 that is 0.94 GB per "
+                                 "rank per step, >= 1.0 ms at 900 GB/s per direction"}
 
 
 # ------------------------------------------------------------------------------------------ quantised eval
@@ -777,6 +780,8 @@ def _main(args):
                     "d2h_bytes_per_step": case.d2h_bytes()},
             "gpu_launches": int(launches) // max(1, args.steps),
             "stages_ms": {k: round(v, 3) for k, v in stages.items() if isinstance(v, float)},
+            "stages_note": "stages_ms: the eager reference-shaped functions with a host synchronisation around each "
+                           "(first-call path); `value` replays the captured pipeline plan (pipeline_plan.py)",
             "roofline": roof, "kernels": kernels, "kernels_sweep": sweep, "int8_peak": i8peak,
             "kernels_sharded": sharded, "eval": ev, "eval_static": ev_static,
             "deeplab": deeplab, "cpu_baseline": cpu, "clocks": clocks.summary()}
