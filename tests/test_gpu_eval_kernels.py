@@ -1,4 +1,4 @@
-"""GPU: the CUDA kernels of the quantised eval forward (csrc/conv.cu, csrc/gemm_u8.cu) one by one against a plain
+"""GPU: the CUDA kernels of the quantised eval forward (csrc/conv.cu, csrc/pw_i8.cu) one by one against a plain
 PyTorch fp32 restatement of utils/quantize.py:225-256 (fake-quantise the input with the oracle's recipe, then
 F.conv2d in fp32 on the CPU).  Floating-point tolerance: 2e-5 of the output's largest magnitude (accumulation
 order differs); per-sample statistics exact for the values actually written."""

@@ -198,6 +198,89 @@ def test_stem_add_mean_q8(oracle):
     assert np.array_equal(from_codes_nhwc(y.cpu(), (N, C)).numpy(), want.astype(np.uint8))
 
 
+def test_q8_kernels_stay_inside_their_buffers(oracle):
+    """compute-sanitizer is closed on this GPU pool (profiles/r2_sanitizer.md): every output buffer of the u8 kernels
+    sits between two sentinel regions that must come back untouched; shapes are not multiples of the tile sizes."""
+    from data_free_quantization_b200 import _lib as L
+    from data_free_quantization_b200.eval_q8 import PackedQ8, pack_depthwise, to_codes_nhwc
+    lib = L.lib()
+    rng = np.random.default_rng(21)
+    GUARD = 4096
+
+    def guarded(nbytes, dtype=torch.int8):
+        item = torch.empty(0, dtype=dtype).element_size()
+        buf = torch.full((2 * GUARD + nbytes * item,), 0x5a, dtype=torch.uint8, device=DEV)
+        return buf, buf[GUARD:GUARD + nbytes * item].view(dtype)
+
+    def intact(buf, nbytes):
+        b = buf.cpu().numpy()
+        return bool((b[:GUARD] == 0x5a).all() and (b[GUARD + nbytes:] == 0x5a).all())
+    in_slot, _ = slot(-1.0, 3.0)
+    s0, _ = slot(-2.0, 9.0)
+    s1, _ = slot(0.0, 7.0)
+    # pointwise: ragged last tile, two passes, two consumers, fp32 output as well
+    for G, K, O, cap in ((1, 16, 16, 0), (130, 40, 250, 64), (513, 1280, 33, 0)):
+        w0 = (rng.standard_normal((O, K)) * 0.2).astype(np.float32)
+        w = oracle.fake_quant(w0, 8, float(w0.min()), float(w0.max()))
+        pk = PackedQ8(torch.from_numpy(w).to(DEV), o_cap=cap)
+        x = to_codes_nhwc(torch.from_numpy(rng.integers(0, 256, (G, K)).astype(np.uint8))).reshape(-1).to(DEV)
+        Cp = (O + 15) // 16 * 16
+        b0, y0 = guarded(G * Cp)
+        b1, y1 = guarded(G * Cp)
+        bf, yf = guarded(G * O, torch.float32)
+        d = L.DfqPwQ8Desc()
+        d.x, d.wpk, d.wr, d.in_slot = x.data_ptr(), pk.wpk.data_ptr(), pk.wr.data_ptr(), in_slot.data_ptr()
+        d.y0, d.out_slot0, d.y1, d.out_slot1 = y0.data_ptr(), s0.data_ptr(), y1.data_ptr(), s1.data_ptr()
+        d.yf, d.yf_g, d.yf_o = yf.data_ptr(), O, 1
+        d.G, d.K, d.O, d.relu, d.o_cap, d.s_w, d.c_w = G, K, O, 1, cap, pk.s_w, pk.c_w
+        L.check(lib.dfq_pw_q8(ctypes.byref(d), L.stream()), "dfq_pw_q8")
+        torch.cuda.synchronize()
+        assert intact(b0, G * Cp) and intact(b1, G * Cp) and intact(bf, 4 * G * O), (G, K, O)
+        assert not bool(torch.isnan(yf).any())
+    # depthwise, both strides, odd sizes, two consumers
+    for N, C, H, W, stride in ((1, 20, 5, 3, 1), (2, 33, 9, 11, 2), (1, 16, 1, 1, 1)):
+        w0 = (rng.standard_normal((C, 1, 3, 3)) * 0.3).astype(np.float32)
+        wrow, dsw, dcw = pack_depthwise(torch.from_numpy(oracle.fake_quant(w0, 8, float(w0.min()), float(w0.max()))).to(DEV))
+        Cp = (C + 15) // 16 * 16
+        OH, OW = (H - 1) // stride + 1, (W - 1) // stride + 1
+        x = to_codes_nhwc(torch.from_numpy(rng.integers(0, 256, (N, C, H, W)).astype(np.uint8))).reshape(-1).to(DEV)
+        b0, y0 = guarded(N * OH * OW * Cp)
+        b1, y1 = guarded(N * OH * OW * Cp)
+        bp = torch.zeros(Cp, device=DEV)
+        d = L.DfqDwQ8Desc()
+        d.x, d.wrow, d.bias, d.in_slot = x.data_ptr(), wrow.data_ptr(), bp.data_ptr(), in_slot.data_ptr()
+        d.y0, d.out_slot0, d.y1, d.out_slot1 = y0.data_ptr(), s0.data_ptr(), y1.data_ptr(), s1.data_ptr()
+        d.N, d.H, d.W, d.C, d.stride, d.relu, d.s_w, d.c_w = N, H, W, C, stride, 1, dsw, dcw
+        L.check(lib.dfq_dw_q8(ctypes.byref(d), L.stream()), "dfq_dw_q8")
+        torch.cuda.synchronize()
+        assert intact(b0, N * OH * OW * Cp) and intact(b1, N * OH * OW * Cp), (N, C, H, W, stride)
+    # stem, add, mean
+    N, H, W, O = 2, 9, 7, 24
+    img = torch.randn(N, 3, H, W, device=DEV)
+    wst, bst = torch.randn(O, 3, 3, 3, device=DEV) * 0.2, torch.zeros(O, device=DEV)
+    OH, OW = (H + 2 - 3) // 2 + 1, (W + 2 - 3) // 2 + 1
+    b0, y0 = guarded(N * OH * OW * 32)
+    d = L.DfqStemQ8Desc()
+    d.x, d.w, d.bias, d.in_slot, d.y0, d.out_slot0 = img.data_ptr(), wst.data_ptr(), bst.data_ptr(), in_slot.data_ptr(), y0.data_ptr(), s0.data_ptr()
+    d.N, d.H, d.W, d.O, d.stride, d.pad, d.relu = N, H, W, O, 2, 1, 1
+    L.check(lib.dfq_stem_q8(ctypes.byref(d), L.stream()), "dfq_stem_q8")
+    px, C = 77, 40
+    xa = to_codes_nhwc(torch.from_numpy(rng.integers(0, 256, (px, C)).astype(np.uint8))).reshape(-1).to(DEV)
+    ba, ya = guarded(px * 48)
+    bb, yb = guarded(px * 48)
+    L.check(lib.dfq_add_q8(xa.data_ptr(), xa.data_ptr(), in_slot.data_ptr(), s1.data_ptr(), ya.data_ptr(), s0.data_ptr(),
+                           yb.data_ptr(), s1.data_ptr(), px, C, L.stream()), "dfq_add_q8")
+    Nn, Cm, HW = 3, 100, 13
+    xm = to_codes_nhwc(torch.from_numpy(rng.integers(0, 256, (Nn, Cm, HW, 1)).astype(np.uint8))).reshape(-1).to(DEV)
+    bm, ym = guarded(Nn * 112)
+    bmf, ymf = guarded(Nn * Cm, torch.float32)
+    L.check(lib.dfq_mean_q8(xm.data_ptr(), in_slot.data_ptr(), ym.data_ptr(), s0.data_ptr(), ymf.data_ptr(), Nn, Cm, HW,
+                            L.stream()), "dfq_mean_q8")
+    torch.cuda.synchronize()
+    assert intact(b0, N * OH * OW * 32) and intact(ba, px * 48) and intact(bb, px * 48)
+    assert intact(bm, Nn * 112) and intact(bmf, 4 * Nn * Cm)
+
+
 @pytest.fixture(scope="module")
 def static_model():
     model, graph, bottoms, targ, tr = dfq_quantised("mobilenetv2", DEV, np.load(os.path.join(GOLD, "mobilenetv2_dfq.npz")))
