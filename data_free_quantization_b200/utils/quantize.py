@@ -56,24 +56,44 @@ def fake_quant_tensors(tensors, bits, flags=0, outs=None, codes=None, clip=None,
         return None
     as_list = lambda v: list(v) if isinstance(v, (list, tuple)) else [v] * T
     bits, flags, rows = as_list(bits), as_list(flags), as_list(rows if rows is not None else 1)
-    descs = (L.DfqQuantDesc * T)()
     dev = tensors[0].device
-    for i, t in enumerate(tensors):
-        d = descs[i]
-        d.x = L.dev_f32(t, f"tensor[{i}]")
-        d.y = L.dev_f32(outs[i] if outs is not None else t, f"out[{i}]")
-        d.codes = codes[i].data_ptr() if codes is not None and codes[i] is not None else None
-        d.n, d.rows, d.bits = t.numel(), int(rows[i]), int(bits[i])
-        d.flags = int(flags[i]) | (L.Q_CLAMP_OUT if clip is not None else 0)
-        if clip is not None:
-            d.clip_lo, d.clip_hi = float(clip[0]), float(clip[1])
-    tb, ts = L.i64(), L.i64()
-    L.check(L.lib().dfq_quant_plan_host(descs, T, ctypes.byref(tb), ctypes.byref(ts)), "dfq_quant_plan_host")
-    table = L.table_to_device(descs, dev)
-    ranges = torch.empty(ts.value, 4, dtype=torch.float32, device=dev)   # {min, max, scale, 0} per slot
-    L.check(L.lib().dfq_fake_quant_multi_f32(table.data_ptr(), T, tb.value, ts.value, ranges.data_ptr(), L.stream()),
+    # The descriptor table only holds addresses, sizes and flags: it is planned and uploaded once per distinct call
+    # signature and reused (a 1 GiB tensor spent 0.1 of its 0.6 ms waiting for the host to rebuild and upload it).
+    key = (dev.index, tuple(int(b) for b in bits), tuple(int(f) for f in flags), tuple(int(r) for r in rows),
+           None if clip is None else (float(clip[0]), float(clip[1])),
+           tuple(t.data_ptr() for t in tensors), tuple(t.numel() for t in tensors),
+           None if outs is None else tuple(o.data_ptr() for o in outs),
+           None if codes is None else tuple(0 if c is None else c.data_ptr() for c in codes))
+    hit = None if L._capture is not None else _table_cache.get(key)   # a captured graph keeps its own tables alive
+    if hit is None:
+        descs = (L.DfqQuantDesc * T)()
+        for i, t in enumerate(tensors):
+            d = descs[i]
+            d.x = L.dev_f32(t, f"tensor[{i}]")
+            d.y = L.dev_f32(outs[i] if outs is not None else t, f"out[{i}]")
+            d.codes = codes[i].data_ptr() if codes is not None and codes[i] is not None else None
+            d.n, d.rows, d.bits = t.numel(), int(rows[i]), int(bits[i])
+            d.flags = int(flags[i]) | (L.Q_CLAMP_OUT if clip is not None else 0)
+            if clip is not None:
+                d.clip_lo, d.clip_hi = float(clip[0]), float(clip[1])
+        tb, ts = L.i64(), L.i64()
+        L.check(L.lib().dfq_quant_plan_host(descs, T, ctypes.byref(tb), ctypes.byref(ts)), "dfq_quant_plan_host")
+        table = L.table_to_device(descs, dev)
+        if L._capture is None:                      # (tables uploaded during a graph capture live in the plan's arena)
+            if len(_table_cache) >= 64:
+                _table_cache.clear()
+            _table_cache[key] = (table, tb.value, ts.value)
+        hit = (table, tb.value, ts.value)
+    else:
+        L.bump_weights_epoch()                      # a weight-side pass is about to run (see L.weights_epoch)
+    table, tbv, tsv = hit
+    ranges = torch.empty(tsv, 4, dtype=torch.float32, device=dev)   # {min, max, scale, 0} per slot
+    L.check(L.lib().dfq_fake_quant_multi_f32(table.data_ptr(), T, tbv, tsv, ranges.data_ptr(), L.stream()),
             "dfq_fake_quant_multi_f32")
     return ranges
+
+
+_table_cache = {}
 
 
 class UniformQuantize(InplaceFunction):
