@@ -733,6 +733,14 @@ def _main(args):
     if not args.no_micro:
         with quiet:
             sharded = sharded_microbench(torch, dev, world, peak)
+            if world > 1:                       # the same exchange through one NCCL all-gather, for comparison
+                from data_free_quantization_b200 import dist as D
+                os.environ["DFQ_DIST_P2P"] = "0"
+                D._Exchange._cache.clear()
+                alt = sharded_microbench(torch, dev, world, peak)
+                os.environ.pop("DFQ_DIST_P2P")
+                D._Exchange._cache.clear()
+                sharded["all_gather_variant"] = {k: alt[k] for k in ("ms", "achieved", "per_gpu", "exchange")}
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()

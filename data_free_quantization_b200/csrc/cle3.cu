@@ -30,7 +30,7 @@ constexpr int kC3StaticSmem = 4096;    // static __shared__ of the kernel (upper
 struct Cle3Args {
     const DfqCle3Tensor *tensors; const DfqCle3Chain *chains; int n_chains, n_tensors;
     unsigned *bars;                  // [n_chains + 1] counters, kC3BarStride apart; the last one is grid-wide
-    float *s_tab;                    // [2][total_C]: s | 1/s of every pair's channels
+    unsigned long long *s_tab;       // [total_C]: {iteration tag, 1/s} of every pair's channels, one 64-bit word each
     unsigned *cp;                    // column-range partials, encoded max(-v) | max(v)
     double *dp;                      // [2 parities][dp_doubles] metric partials
     int total_C, dp_doubles;
@@ -74,6 +74,24 @@ __device__ __forceinline__ void c3_wait(const unsigned *bar, unsigned target) { 
         if (clock64() - t0 > (1ll << 33)) __trap();            // ~4 s: a lost peer must not hang the GPU
     }
     asm volatile("fence.acq_rel.gpu;" ::: "memory");
+}
+
+// Flag-in-data hand-off of the column factors: the owner of a channel publishes {iteration tag, 1/s} as ONE 64-bit
+// word (a single-copy-atomic store), a consumer polls exactly the words it needs until the tag is this iteration's.
+// No counter, no fence, no separate vector load: the barrier wait and the data fetch are the same L2 round trip.
+// A producer cannot run a whole iteration ahead of a consumer (one grid barrier per iteration), so tags never skip.
+__device__ __forceinline__ void c3_publish(unsigned long long *slot, unsigned tag, float v) {
+    const unsigned long long w = ((unsigned long long)tag << 32) | (unsigned long long)__float_as_uint(v);
+    asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(slot), "l"(w) : "memory");
+}
+__device__ __forceinline__ float c3_consume(const unsigned long long *slot, unsigned tag) {
+    const long long t0 = clock64();
+    for (;;) {
+        unsigned long long w;
+        asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(w) : "l"(slot) : "memory");
+        if ((unsigned)(w >> 32) == tag) return __uint_as_float((unsigned)w);
+        if (clock64() - t0 > (1ll << 33)) __trap();            // ~4 s: a lost peer must not hang the GPU
+    }
 }
 
 // Rescale pass over this CTA's rows of one tensor (in shared memory): optional column factors (fvec), optional row
@@ -183,7 +201,6 @@ cle3_kernel(Cle3Args a) {
     const int g = blockIdx.x - ch.cta0, G = ch.ncta;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const bool sgn = a.is_signed;
-    unsigned *gbar = a.bars + (size_t)c * kC3BarStride;
     unsigned *allbar = a.bars + (size_t)a.n_chains * kC3BarStride;
 
     for (int i = tid; i < ch.len; i += kC3Threads) s_T[i] = a.tensors[ch.t0 + i];
@@ -267,7 +284,7 @@ cle3_kernel(Cle3Args a) {
             flush_cp(T, i);
         }
     }
-    unsigned all_epoch = 1, grp_epoch = 0;
+    unsigned all_epoch = 1;
     __syncthreads();
     if (tid == 0) { c3_arrive(allbar); c3_wait(allbar, all_epoch * gridDim.x); }
     __syncthreads();
@@ -285,35 +302,52 @@ cle3_kernel(Cle3Args a) {
             const int nrows = s_nrows[i], row0 = s_row0[i], L = T.L;
             const bool up = T.up >= 0, down = T.down >= 0;
             const bool vec4 = (L & 3) == 0 && !T.dw && T.KK == 1 && L >= 16;     // 128-bit shared accesses
-            // column ranges of T(i+1) for my rows: left by the previous iteration, so they are fetched BEFORE waiting
-            // for this phase's barrier (r2_sm / rr_sm were cleared behind the previous phase's use)
+            // column ranges of T(i+1) for my rows: left by the previous iteration, so their loads are ISSUED before the
+            // factors of this phase are polled (up to four per thread ride in registers behind the polling loop; r2_sm /
+            // rr_sm were cleared behind the previous phase's use)
+            unsigned pre_lo[4], pre_hi[4];
+            int n_items = 0;
+            const unsigned *cpn = nullptr;
+            bool next_dw = false;
+            int next_C = 0;
             if (down) {
                 const DfqCle3Tensor &Tn = s_T[i + 1];
-                const unsigned *cpn = a.cp + Tn.cp_off;
-                if (Tn.dw) {
-                    for (int r = tid; r < nrows; r += kC3Threads) {
-                        r2_sm[r] = __ldcg(cpn + row0 + r); r2_sm[a.max_rows + r] = __ldcg(cpn + Tn.C + row0 + r);
-                    }
-                } else {
-                    for (int it = tid; it < nrows * G; it += kC3Threads) {
-                        const int gg = it / nrows, r = it - gg * nrows;
-                        const unsigned *p = cpn + (size_t)gg * 2 * Tn.C + row0 + r;
-                        atomicMax(r2_sm + r, __ldcg(p)); atomicMax(r2_sm + a.max_rows + r, __ldcg(p + Tn.C));
+                cpn = a.cp + Tn.cp_off; next_dw = Tn.dw != 0; next_C = Tn.C;
+                n_items = next_dw ? nrows : nrows * G;
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const int it = tid + u * kC3Threads;
+                    pre_lo[u] = pre_hi[u] = 0u;
+                    if (it < n_items) {
+                        const int gg = next_dw ? 0 : it / nrows, r = next_dw ? it : it - gg * nrows;
+                        const unsigned *p = cpn + (size_t)gg * 2 * next_C + row0 + r;
+                        pre_lo[u] = __ldcg(p); pre_hi[u] = __ldcg(p + next_C);
                     }
                 }
             }
-            if (i > 0 && G > 1) {                     // s of pair i-1 published by every CTA of the group
-                ++grp_epoch;
-                if (tid == 0) c3_wait(gbar, grp_epoch * G);
-                __syncthreads();
-            }
             C3_STAMP(1);
-            // the column factors 1/s_{i-1}
+            // the column factors 1/s_{i-1}, each polled from the word its owner publishes (tag = this iteration)
             if (up) {
-                const float *sinv = a.s_tab + a.total_C + T.up_off;
-                if (T.dw) { for (int r = tid; r < nrows; r += kC3Threads) fvec[r] = __ldcg(sinv + row0 + r); }
-                else if (T.KK == 1) { for (int j = tid; j < L; j += kC3Threads) fvec[j] = __ldcg(sinv + j); }
-                else { for (int j = tid; j < L; j += kC3Threads) fvec[j] = __ldcg(sinv + j / T.KK); }
+                const unsigned long long *sinv = a.s_tab + T.up_off;
+                const unsigned tag = (unsigned)iters + 1u;
+                if (T.dw) { for (int r = tid; r < nrows; r += kC3Threads) fvec[r] = c3_consume(sinv + row0 + r, tag); }
+                else if (T.KK == 1) { for (int j = tid; j < L; j += kC3Threads) fvec[j] = c3_consume(sinv + j, tag); }
+                else { for (int j = tid; j < L; j += kC3Threads) fvec[j] = c3_consume(sinv + j / T.KK, tag); }
+            }
+            if (down) {
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const int it = tid + u * kC3Threads;
+                    if (it < n_items) {
+                        const int r = next_dw ? it : it % nrows;
+                        atomicMax(r2_sm + r, pre_lo[u]); atomicMax(r2_sm + a.max_rows + r, pre_hi[u]);
+                    }
+                }
+                for (int it = tid + 4 * kC3Threads; it < n_items; it += kC3Threads) {       // (groups wider than 4 x 512 items)
+                    const int gg = next_dw ? 0 : it / nrows, r = next_dw ? it : it - gg * nrows;
+                    const unsigned *p = cpn + (size_t)gg * 2 * next_C + row0 + r;
+                    atomicMax(r2_sm + r, __ldcg(p)); atomicMax(r2_sm + a.max_rows + r, __ldcg(p + next_C));
+                }
             }
             __syncthreads();
             C3_STAMP(2);
@@ -326,8 +360,7 @@ cle3_kernel(Cle3Args a) {
                     float s, sinv;
                     c3_scale(a, r1, r2v, s, sinv);
                     s_sm[r] = s;
-                    a.s_tab[T.s_off + row0 + r] = s;
-                    a.s_tab[a.total_C + T.s_off + row0 + r] = sinv;
+                    c3_publish(a.s_tab + T.s_off + row0 + r, (unsigned)iters + 1u, sinv);
                     vec[r] = __fmul_rn(vec[r], s);
                     vec[nrows + r] = __fmul_rn(vec[nrows + r], s);
                     vec[2 * nrows + r] = __fmul_rn(vec[2 * nrows + r], s);
@@ -407,7 +440,6 @@ cle3_kernel(Cle3Args a) {
                 }
                 __syncthreads();
                 C3_STAMP(3);
-                if (tid == kC3Threads - 1 && G > 1) c3_arrive(gbar);   // s_i is out: the next phase may start everywhere
             }
             C3_STAMP(4);
             // rescale pass behind the barrier signal
@@ -683,7 +715,7 @@ extern "C" int dfq_cle3_run(const DfqCle3Tensor *tensors_dev, const DfqCle3Chain
     a.tensors = tensors_dev; a.chains = chains_dev; a.n_chains = p->n_chains; a.n_tensors = p->n_tensors;
     char *s = (char *)scratch_dev;
     a.bars = (unsigned *)s; s += c3_align((int64_t)(p->n_chains + 1) * kC3BarStride * 4);
-    a.s_tab = (float *)s; s += c3_align((int64_t)2 * p->total_C * 4);
+    a.s_tab = (unsigned long long *)s; s += c3_align((int64_t)2 * p->total_C * 4);
     a.cp = (unsigned *)s; s += c3_align((int64_t)p->cp_words * 4);
     a.dp = (double *)s;
     a.total_C = p->total_C; a.dp_doubles = p->dp_doubles;

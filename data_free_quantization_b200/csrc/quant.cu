@@ -221,10 +221,21 @@ dequant_multi_kernel(const DfqDequantDesc *__restrict__ descs, int n_desc) {
     const int64_t begin = ((int64_t)blockIdx.x - d.first_block) * kDeqBlock, end = min(begin + (int64_t)kDeqBlock, d.n);
     const uint8_t *c = reinterpret_cast<const uint8_t *>(d.codes);
     if (((((uintptr_t)c) | ((uintptr_t)d.y)) & 15) == 0) {
-        for (int64_t k = begin + 16 * (int64_t)threadIdx.x; k < end; k += 16 * kThreads) {
+        // all four 16-byte code words of this thread are requested before the first conversion: over NVLink a load
+        // takes microseconds, and one load in flight per thread left the link at a quarter of its bandwidth
+        constexpr int U = kDeqBlock / (16 * kThreads);
+        uint4 w[U];
+        int64_t ks[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            ks[u] = begin + 16 * ((int64_t)threadIdx.x + (int64_t)u * kThreads);
+            w[u] = (ks[u] + 16 <= end) ? __ldcs(reinterpret_cast<const uint4 *>(c + ks[u])) : make_uint4(0u, 0u, 0u, 0u);
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int64_t k = ks[u];
             if (k + 16 <= end) {
-                const uint4 w = *reinterpret_cast<const uint4 *>(c + k);
-                const uint32_t ww[4] = {w.x, w.y, w.z, w.w};
+                const uint32_t ww[4] = {w[u].x, w[u].y, w[u].z, w[u].w};
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
                     float4 o;
@@ -232,9 +243,9 @@ dequant_multi_kernel(const DfqDequantDesc *__restrict__ descs, int n_desc) {
                     o.y = __fadd_rn(__fmul_rn((float)((ww[j] >> 8) & 0xffu), r.scale), r.mn);
                     o.z = __fadd_rn(__fmul_rn((float)((ww[j] >> 16) & 0xffu), r.scale), r.mn);
                     o.w = __fadd_rn(__fmul_rn((float)(ww[j] >> 24), r.scale), r.mn);
-                    *reinterpret_cast<float4 *>(d.y + k + 4 * j) = o;
+                    __stcs(reinterpret_cast<float4 *>(d.y + k + 4 * j), o);
                 }
-            } else {
+            } else if (k < end) {
                 for (int64_t e = k; e < end; ++e) d.y[e] = __fadd_rn(__fmul_rn((float)c[e], r.scale), r.mn);
             }
         }
