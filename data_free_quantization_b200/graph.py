@@ -249,6 +249,21 @@ def _load_arg(a, env):
     return a
 
 
+def _load_arg_quantised(a, env, operands, values, k):
+    """_load_arg with the recorded operands replaced, occurrence by occurrence and in order, by their quantised values:
+    `x + x` consumes TWO measures of the CustomTensorOP, one per occurrence (utils/layer_transform.py:18-32)."""
+    if isinstance(a, torch.fx.Node):
+        if k[0] < len(operands) and a is operands[k[0]]:
+            k[0] += 1
+            return values[k[0] - 1]
+        return env[a]
+    if isinstance(a, (list, tuple)):
+        return type(a)(_load_arg_quantised(b, env, operands, values, k) for b in a)
+    if isinstance(a, dict):
+        return {key: _load_arg_quantised(v, env, operands, values, k) for key, v in a.items()}
+    return _load_arg(a, env)
+
+
 def run_graph(fxg, model, *inputs):
     """Execute the traced graph node by node; recorded tensor ops quantise their operands first."""
     env = {}
@@ -268,10 +283,12 @@ def run_graph(fxg, model, *inputs):
             return _load_arg(node.args[0], env)
         else:
             if quant and "dfq_key" in node.meta and top.num_op and top.get_graph_name() == node.meta["dfq_key"]:
-                sub = {a: top(env[a]) for a in node.meta["dfq_operands"]}
+                operands = node.meta["dfq_operands"]
+                values = [top(env[a]) for a in operands]          # one measure per occurrence, in operand order
                 top.add_idx_name_tensor_op()
-                args = _load_arg(node.args, {**env, **sub})
-                kwargs = _load_arg(node.kwargs, {**env, **sub})
+                k = [0]
+                args = _load_arg_quantised(node.args, env, operands, values, k)
+                kwargs = _load_arg_quantised(node.kwargs, env, operands, values, k)
             else:
                 args, kwargs = _load_arg(node.args, env), _load_arg(node.kwargs, env)
             if node.op == "call_module":

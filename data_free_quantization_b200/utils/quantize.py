@@ -232,7 +232,12 @@ def _conv2d_fp32(input, weight, bias, stride, padding, dilation, groups):
 
 
 def _quant_weight(weight, num_bits):
-    """quantize(W, bits, float(W.min()), float(W.max())) without the two host round trips."""
+    """quantize(W, bits, float(W.min()), float(W.max())) without the two host round trips.  When a gradient is being
+    recorded for the weight the call goes through UniformQuantize (straight-through estimator, utils/quantize.py:81-85)
+    with the range read back to the host as the reference does."""
+    if torch.is_grad_enabled() and weight.requires_grad:
+        lo, hi = (float(v) for v in minmax(weight.detach()).tolist())
+        return quantize(weight, num_bits, lo, hi)
     out = torch.empty_like(weight)
     fake_quant_tensors([weight.detach()], num_bits, 0, outs=[out])
     return out

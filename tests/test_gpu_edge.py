@@ -93,3 +93,49 @@ def test_cle_dead_channel_replicates_the_reference(oracle, impl, monkeypatch):
                       (rels[0].S, S)):
         assert got.detach().cpu().numpy().tobytes() == want.tobytes()
     assert S[5] == np.float32(1e8) ** 2 or not np.isfinite(S[5]) or S[5] >= 1e8       # s_max kept for the dead channel
+
+
+def test_straight_through_gradient_reaches_the_weights():
+    """utils/quantize.py:81-85: UniformQuantize.backward passes the gradient straight through, so a QuantConv2d /
+    QuantLinear whose weight requires grad must receive one (the weight goes through UniformQuantize, not a detach)."""
+    from data_free_quantization_b200.utils.quantize import QuantLinear
+    lin = QuantLinear(16, 8).to(DEV)
+    lin.quant.eval()
+    x = torch.randn(4, 16, device=DEV)
+    y = lin(x)
+    y.sum().backward()
+    assert lin.weight.grad is not None and lin.weight.grad.shape == lin.weight.shape
+    assert float(lin.weight.grad.abs().sum()) > 0
+
+
+def test_same_tensor_twice_in_an_add_consumes_two_measures():
+    """`x + x` records two operands; each occurrence goes through its own CustomTensorOP measure."""
+    from data_free_quantization_b200 import graph as G
+    from data_free_quantization_b200.utils import quantize as Q
+
+    class M(nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.c = nn.Conv2d(3, 4, 1)
+
+        def forward(self, x):
+            y = self.c(x)
+            return y + y
+
+    m = M().to(DEV).eval()
+    md = {1: [(nn.Conv2d, Q.QuantNConv2d), (nn.Linear, Q.QuantNLinear)]}
+    m, tr = G.switch_layers(m, G.TorchTransformer(), torch.ones(1, 3, 8, 8, device=DEV), md,
+                            ignore_layer=[Q.QuantMeasure], quant_op=True)
+    top = m.custom_tensor_op
+    qms = list(top.children())
+    assert len(qms) == 2
+    for q in qms:
+        q.update_stat = True
+        q.eval()
+    G.replace_op()
+    try:
+        with torch.no_grad():
+            m(torch.randn(2, 3, 8, 8, device=DEV))
+    finally:
+        G.restore_op()
+    assert all(float(q.running_max) != 0.0 or float(q.running_min) != 0.0 for q in qms), "second measure never ran"
