@@ -161,7 +161,9 @@ __global__ void decode_slots_kernel(const DfqQuantDesc *__restrict__ descs, int 
 
 __global__ void __launch_bounds__(kThreads)
 fake_quant_multi_kernel(const DfqQuantDesc *__restrict__ descs, int n_desc, const RangeSlot *__restrict__ ranges) {
-    BlockWork w = decode_work(descs, n_desc, blockIdx.x);
+    // blocks walk the virtual chunks BACKWARDS: the range pass just streamed the tensors front to back, so the last
+    // ~100 MB it read are still in the 126 MB L2 and the first blocks of this pass find them there
+    BlockWork w = decode_work(descs, n_desc, (int64_t)gridDim.x - 1 - blockIdx.x);
     const DfqQuantDesc &d = descs[w.desc];
     bool clamp_out = d.flags & DFQ_Q_CLAMP_OUT;
     if (w.begin >= 0) {
