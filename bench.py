@@ -539,6 +539,19 @@ def oracle_pipeline_once():
     return (time.perf_counter() - t) * 1e3, iters
 
 
+CLE_NOTES = {
+    "resident": "cle3_kernel keeps every chain's weights in the shared memory of its CTA group for all iterations "
+                "(33.6 MB of shared memory on the chip): DRAM sees the 14 MB once, the 2.2 GB of algorithmic "
+                "re-reads are shared-memory reads, and an iteration (~20 us) is bound by the flag-in-data hand-off "
+                "of the per-channel factors down each chain plus one grid barrier for the stop decision, not by "
+                "HBM; the HBM-bound kernels are measured on a 1 GiB tensor in `kernels`.",
+    "stream": "the 14 MB of weights live in the 126 MB L2 for all iterations, so DRAM traffic is ~2 x 14 MB per "
+              "launch (profiles/) and the loop is bound by one grid barrier + one dependent L2 round trip per chain "
+              "position (6 per iteration), not by HBM; the HBM-bound kernels are measured on a 1 GiB tensor in "
+              "`kernels`.",
+}
+
+
 def bench_config(world, weights=3469760):
     """`config` of the JSON line -- identical for both arms."""
     return {"workload": WORKLOAD, "weights": weights, "pipelines_per_step": world,
@@ -760,15 +773,13 @@ def _main(args):
                       f" ({cle_iters} iterations in one cooperative launch)", "bound": "hbm",
             "achieved": round(ach, 1) if ach else None, "peak": peak, "unit": "GB/s",
             "frac": round(ach / peak, 4) if ach else None,
-            # dram__bytes_read.sum + dram__bytes_write.sum of one launch, ncu --set full (profiles/r1j_ncu_cle2.md:
-            # 14.8928 MB + 1.0980 MB); the kernel has not changed since that capture
-            "traffic": 15990784 if cle_impl == "stream" else None, "peak_source": peak_src,
+            # dram__bytes_read.sum + dram__bytes_write.sum of one launch, ncu --set full: cle3_kernel 14.2272 MB +
+            # 0.1684 MB (profiles/r2_cle3_ncu.md; the rescaled weights are still dirty in L2 when the kernel ends),
+            # cle2_kernel 14.8928 MB + 1.0980 MB (profiles/r1j_ncu_cle2.md)
+            "traffic": {"resident": 14395648, "stream": 15990784}.get(cle_impl), "peak_source": peak_src,
             "kernel_ms": round(cle_kernel_ms, 4) if cle_kernel_ms else None,
             "algorithmic_bytes": cle_bytes,
-            "note": "the 14 MB of weights live in the 126 MB L2 for all iterations, so DRAM traffic is ~2 x 14 MB "
-                    "per launch (profiles/) and the loop is bound by one grid barrier + one dependent L2 round "
-                    "trip per chain position (6 per iteration), not by HBM; the HBM-bound kernels are measured on "
-                    "a 1 GiB tensor in `kernels`."}
+            "note": CLE_NOTES.get(cle_impl, CLE_NOTES["stream"])}
     cpu = None
     if not args.no_cpu_baseline:
         ms_cpu, iters = oracle_pipeline_once()

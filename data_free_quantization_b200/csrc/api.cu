@@ -14,6 +14,17 @@ int sm_count() {
     }
     return cached[dev];
 }
+int resident_blocks_per_sm(const void *kernel, int threads, size_t smem) {
+    struct Entry { const void *k; int threads; size_t smem; int occ; };
+    static Entry cache[64];
+    static int n = 0;
+    for (int i = 0; i < n; ++i)
+        if (cache[i].k == kernel && cache[i].threads == threads && cache[i].smem == smem) return cache[i].occ;
+    int occ = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, threads, smem) != cudaSuccess || occ < 1) occ = 1;
+    if (n < 64) cache[n++] = {kernel, threads, smem, occ};
+    return occ;
+}
 }  // namespace dfq
 
 extern "C" int dfq_abi_version(void) { return DFQ_ABI_VERSION; }

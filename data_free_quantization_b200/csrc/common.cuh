@@ -16,9 +16,13 @@ constexpr int kChunk = 4096;            // fp32 elements per block of the stream
 
 extern long long g_launches;            // host-side launch counter (api.cu)
 int sm_count();                         // SMs of the current device, cached (api.cu)
-// grid of a grid-stride reduction pass: 8 resident 256-thread blocks per SM (148 x 8 on B200)
-inline unsigned reduce_grid(int64_t virtual_blocks) {
-    int64_t g = (int64_t)sm_count() * 8;
+// grid of a grid-stride pass: exactly the blocks that are resident at once (occupancy of THAT kernel x SMs), never
+// more than there are chunks.  A fixed "8 per SM" over-subscribed kernels that fit 5 or 6: the extra blocks only
+// started when a first-wave block had finished its whole share, and ran the last quarter of the data at 1/3 occupancy.
+int resident_blocks_per_sm(const void *kernel, int threads, size_t smem);   // cached per kernel (api.cu)
+template <typename K>
+inline unsigned reduce_grid(K kernel, int64_t virtual_blocks, int threads = kThreads, size_t smem = 0) {
+    int64_t g = (int64_t)sm_count() * resident_blocks_per_sm((const void *)kernel, threads, smem);
     return (unsigned)(virtual_blocks < g ? virtual_blocks : g);
 }
 
@@ -82,6 +86,20 @@ __device__ __forceinline__ void block_minmax(float &lo, float &hi, float *smem /
 }
 
 // min/max of [begin,end) of x; vectorised when the address allows it.
+__device__ __forceinline__ float4 ld_coherent4(const float4 *p) {      // never the non-coherent (LDG.NC) path
+    float4 v;
+    asm volatile("ld.global.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+    return v;
+}
+
+__device__ __forceinline__ float ld_coherent1(const float *p) {
+    float v;
+    asm volatile("ld.global.f32 %0, [%1];" : "=f"(v) : "l"(p));
+    return v;
+}
+
+// kNc = false: plain loads, for kernels that write the same memory later in the same launch (fused range + apply).
+template <bool kNc = true>
 __device__ __forceinline__ void chunk_minmax(const float *__restrict__ x, int64_t begin, int64_t end,
                                              float &lo, float &hi) {
     const float *p = x + begin;
@@ -95,7 +113,7 @@ __device__ __forceinline__ void chunk_minmax(const float *__restrict__ x, int64_
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
             int64_t k = i + (int64_t)u * kThreads;
-            v[u] = (k < n4) ? __ldg(p4 + k) : make_float4(INFINITY, INFINITY, INFINITY, INFINITY);
+            v[u] = (k < n4) ? (kNc ? __ldg(p4 + k) : ld_coherent4(p4 + k)) : make_float4(INFINITY, INFINITY, INFINITY, INFINITY);
         }
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
@@ -106,11 +124,11 @@ __device__ __forceinline__ void chunk_minmax(const float *__restrict__ x, int64_
             }
         }
         for (int64_t k = (n4 << 2) + threadIdx.x; k < n; k += kThreads) {
-            float t = p[k]; lo = fmin_nan(lo, t); hi = fmax_nan(hi, t);
+            float t = kNc ? p[k] : ld_coherent1(p + k); lo = fmin_nan(lo, t); hi = fmax_nan(hi, t);
         }
     } else {
         for (int64_t k = threadIdx.x; k < n; k += kThreads) {
-            float t = p[k]; lo = fmin_nan(lo, t); hi = fmax_nan(hi, t);
+            float t = kNc ? p[k] : ld_coherent1(p + k); lo = fmin_nan(lo, t); hi = fmax_nan(hi, t);
         }
     }
 }

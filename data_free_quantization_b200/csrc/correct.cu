@@ -307,7 +307,7 @@ extern "C" int dfq_bias_correct(const DfqCorrDesc *descs_dev, int n_desc, int64_
     if (!range_given) {
         cudaError_t e = cudaMemsetAsync(ranges_dev, 0, sizeof(float) * 4 * n_desc, st);
         if (e != cudaSuccess) return (int)e;
-        corr_minmax_kernel<<<reduce_grid(total_blocks), kThreads, 0, st>>>(descs_dev, n_desc, total_blocks,
+        corr_minmax_kernel<<<reduce_grid(corr_minmax_kernel, total_blocks), kThreads, 0, st>>>(descs_dev, n_desc, total_blocks,
                                                                            (unsigned *)ranges_dev);
         g_launches += 1;
     }
