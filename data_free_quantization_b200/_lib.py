@@ -125,7 +125,7 @@ class DfqStemQ8Desc(ctypes.Structure):
 
 
 Q_SYMMETRIC, Q_RANGE_F32, Q_PER_CHANNEL, Q_CLAMP_OUT = 1, 2, 4, 8
-ABI_VERSION = 15
+ABI_VERSION = 16
 
 # every symbol include/dfq_b200.h declares: (restype, argtypes)
 P = ctypes.POINTER
@@ -139,6 +139,8 @@ PROTOTYPES = {
     "dfq_fake_quant_apply_f32": (ctypes.c_int, [c_void, c_void, c_void, i64, ctypes.c_int, P(DfqQuantParams), c_void]),
     "dfq_measure_update": (ctypes.c_int, [c_void, i64, i64, c_void, c_void, c_void, ctypes.c_int, ctypes.c_int,
                                           ctypes.c_int, c_void, c_void]),
+    "dfq_measure_update_noalloc": (ctypes.c_int, [c_void, i64, i64, c_void, c_void, c_void, ctypes.c_int, ctypes.c_int,
+                                                  ctypes.c_int, c_void]),
     "dfq_fake_quant_apply_slot_f32": (ctypes.c_int, [c_void, c_void, c_void, i64, ctypes.c_int, ctypes.c_int, c_void,
                                                      c_void]),
     "dfq_measure_from_stats": (ctypes.c_int, [c_void, ctypes.c_int, i64, c_void, c_void, c_void, ctypes.c_int,

@@ -2,6 +2,7 @@
 // the device -- utils/quantize.py:94-126.  No host round trip per layer: the per-sample extrema, their mean over
 // the batch, the running-range update (Python max()/min() semantics, :110-111) and the scale all stay in HBM, so
 // a whole forward can be captured in a CUDA graph.
+#include <cstdio>
 #include "common.cuh"
 #include "apply.cuh"
 
@@ -80,6 +81,49 @@ extern "C" int dfq_measure_update(const float *x, int64_t n_samples, int64_t chw
                                              (RangeSlot *)slot_dev, bits, flags, update_stat, 0);
     g_launches += 1;
     return (int)cudaGetLastError();
+}
+
+// ---- allocation-free variant (no counterpart in the reference) ------
+// Same work as dfq_measure_update, but the per-sample extrema live in a file-scope device array instead of a
+// caller-provided scratch buffer, so a caller that may not allocate (CUDA graph capture, a tight serving loop) needs
+// nothing but its inputs and outputs.  Every GPU that loads the library holds the 32 KB until exit.  All calls share
+// the array: calls that overlap on the GPU (different streams) race on it; calls on one stream are ordered.
+static __device__ __align__(256) float g_measure_scratch[2 * DFQ_MEASURE_NOALLOC_MAX_SAMPLES];
+
+// The symbol's name is only a host-side handle; its device address is looked up once per device, with that device
+// current (cudaGetSymbolAddress allocates nothing: the array is part of the loaded module).
+static int measure_scratch_ptr(float **out) {
+    static float *cached[64] = {nullptr};
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return (int)e;
+    if (dev < 0 || dev >= 64) return (int)cudaErrorInvalidDevice;
+    if (!cached[dev]) {
+        float *p = nullptr;
+        e = cudaGetSymbolAddress((void **)&p, g_measure_scratch);
+        if (e != cudaSuccess) return (int)e;
+        cached[dev] = p;
+    }
+    *out = cached[dev];
+    return 0;
+}
+
+extern "C" int dfq_measure_update_noalloc(const float *x, int64_t n_samples, int64_t chw, float *running_min,
+                                          float *running_max, float *slot_dev, int bits, int flags, int update_stat,
+                                          void *stream) {
+    if (update_stat && n_samples > DFQ_MEASURE_NOALLOC_MAX_SAMPLES) {
+        fprintf(stderr, "dfq_measure_update_noalloc: n_samples = %lld exceeds the built-in scratch of %d samples; "
+                        "use dfq_measure_update with a caller-provided stats_scratch\n",
+                (long long)n_samples, DFQ_MEASURE_NOALLOC_MAX_SAMPLES);
+        return (int)cudaErrorInvalidValue;
+    }
+    float *scratch = nullptr;
+    int e = measure_scratch_ptr(&scratch);
+    if (e) return e;
+    // dfq_minmax_rows_f32 clears the 2*n_samples words it accumulates into (cudaMemsetAsync on `stream`) before its
+    // atomics run, so what the previous call left in the array is never read
+    return dfq_measure_update(x, n_samples, chw, running_min, running_max, slot_dev, bits, flags, update_stat, scratch,
+                              stream);
 }
 
 extern "C" int dfq_measure_from_stats(const void *stats, int encoded, int64_t n_samples, float *running_min,

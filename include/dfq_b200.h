@@ -23,7 +23,7 @@
 extern "C" {
 #endif
 
-#define DFQ_ABI_VERSION 15
+#define DFQ_ABI_VERSION 16
 
 #if defined(__GNUC__)
 #pragma GCC visibility push(default)   /* the library is built with -fvisibility=hidden */
@@ -220,6 +220,18 @@ int dfq_measure_update(const float *x, int64_t n_samples, int64_t chw, float *ru
                        float *slot_dev, int bits, int flags, int update_stat, float *stats_scratch, void *stream);
 int dfq_fake_quant_apply_slot_f32(const float *x, float *y, void *codes, int64_t n, int bits, int flags,
                                   const float *slot_dev, void *stream);
+
+/* dfq_measure_update without the stats_scratch argument and without any allocation.  No counterpart in the reference:
+ * added for callers that cannot call cudaMalloc (code under CUDA graph capture,
+ * tight serving loops).  The per-sample extrema go to a file-scope device array of the library
+ * (2 * DFQ_MEASURE_NOALLOC_MAX_SAMPLES floats = 32 KB, held by every GPU that loads the library until exit); the call
+ * makes no cudaMalloc / cudaFree and calls no allocating routine.  n_samples > DFQ_MEASURE_NOALLOC_MAX_SAMPLES (with
+ * update_stat != 0) is rejected with cudaErrorInvalidValue and a message on stderr.  Results are those of
+ * dfq_measure_update bit for bit.  All calls share the array: calls that overlap on the GPU (different streams) race;
+ * calls on one stream are ordered.  The array keeps the last call's contents; each call clears what it uses. */
+#define DFQ_MEASURE_NOALLOC_MAX_SAMPLES 4096
+int dfq_measure_update_noalloc(const float *x, int64_t n_samples, int64_t chw, float *running_min, float *running_max,
+                               float *slot_dev, int bits, int flags, int update_stat, void *stream);
 
 /* the same from already reduced per-sample statistics: stats = [n_samples, 2] floats (encoded == 0), or the
  * order-preserving integer encoding {enc(max(-y)), enc(max(y))} a producing dfq_q* kernel accumulated in its
