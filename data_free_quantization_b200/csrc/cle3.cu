@@ -5,15 +5,20 @@
 // memory.  The streaming form (cle2.cu) re-reads every tensor from L2 twice per iteration behind one GRID barrier
 // per chain position (264 barriers of ~10 us for MobileNetV2: latency-bound at 0.12 of the HBM roofline).  Here
 //   * the 16 chains are independent (a chain = T0 -> T1 -> ... -> Tm, pair k = (Tk, Tk+1)), so each chain gets its
-//     own group of CTAs (sized by its element count) and synchronises only inside the group;
+//     own group of CTAs (sized by its element count);
 //   * a CTA owns whole ROWS of every tensor of its chain, loaded once; per iteration each tensor is visited in ONE
 //     phase: columns *= 1/s_{k-1} (published by the owners of Tk-1's rows), row ranges, s_k = f(r1, r2) with r2 the
 //     column ranges of Tk+1 left by the previous iteration, rows *= s_k, |W - W_old| summed on the fly (W_old is the
 //     value just read: no second copy), column-range partials of the result for the next iteration;
-//   * only the per-channel vectors cross SMs (s, 1/s, column-range partials, metric partials: a few KB through L2);
-//     the group barrier of phase k is signalled as soon as s_k is published, the rescale pass runs behind it;
-//   * one grid-wide barrier per ITERATION carries the convergence metric; every CTA evaluates
-//     Cross_layer_equal.py:107-115 identically, so the loop stops exactly where the reference stops.
+//   * only the per-channel vectors cross SMs (1/s, column-range partials, metric partials: a few KB through L2).
+//     There is NO barrier between the phases of an iteration: the owner of a channel publishes {iteration, 1/s_k} as
+//     one 64-bit word as soon as it has it (c3_publish), and a consumer polls exactly the words its columns need
+//     (c3_consume) -- the wait and the data fetch are the same L2 round trip, and a CTA whose producers are done never
+//     waits for the slowest CTA of the group; the column partials it needs next are prefetched before it polls;
+//   * one grid-wide barrier per ITERATION carries the convergence metric (it also bounds how far a producer can run
+//     ahead, so the iteration tags never skip); every CTA evaluates Cross_layer_equal.py:107-115 identically from the
+//     same partials in the same order, so the loop stops exactly where the reference stops.
+// MobileNetV2 on B200: 44 iterations in 0.93 ms (19.7 us per iteration; cle2.cu 2.78 ms), 14.4 MB of DRAM traffic.
 // Same arithmetic and the same order of roundings per element as cle.cu / cle2.cu (bit-identical results).
 #include <algorithm>
 #include <vector>
@@ -29,7 +34,7 @@ constexpr int kC3StaticSmem = 4096;    // static __shared__ of the kernel (upper
 
 struct Cle3Args {
     const DfqCle3Tensor *tensors; const DfqCle3Chain *chains; int n_chains, n_tensors;
-    unsigned *bars;                  // [n_chains + 1] counters, kC3BarStride apart; the last one is grid-wide
+    unsigned *bars;                  // [n_chains + 1] counters, kC3BarStride apart; only the last (grid-wide) is used
     unsigned long long *s_tab;       // [total_C]: {iteration tag, 1/s} of every pair's channels, one 64-bit word each
     unsigned *cp;                    // column-range partials, encoded max(-v) | max(v)
     double *dp;                      // [2 parities][dp_doubles] metric partials
