@@ -154,6 +154,48 @@ class _Exchange:
             self.handle.barrier()
 
 
+_PIECE = 1 << 20          # elements per piece of a foreign layer (a multiple of the kernel's 16 K-element block)
+_foreign_cache = {}
+
+
+def _foreign_table(layers, owner, offs, theirs, bufs, rank, world, dev):
+    """Descriptor table of the one launch that dequantises every foreign layer, cached per (buffers, weights).
+
+    Order matters over NVLink: blocks run roughly in table order, and with the layers listed owner by owner all ranks
+    read from the SAME peer at the same time -- its egress (900 GB/s) shared by N - 1 readers while the other peers sit
+    idle (measured at N = 8: 5.1 ms for 0.94 GB per rank, slower than the all-gather).  So every layer is cut into
+    1 Mi-element pieces and the pieces are dealt round-robin over the owners, starting with the next rank: at any time a
+    rank has loads in flight to all N - 1 peers, and no two ranks start on the same one."""
+    from . import _lib as L
+    import ctypes
+    key = (rank, world, tuple(b.data_ptr() for b in bufs), tuple(layers[i].weight.data_ptr() for i in theirs),
+           tuple(layers[i].weight.numel() for i in theirs))
+    hit = _foreign_cache.get(key)
+    if hit is not None:
+        return hit
+    per_owner = {}
+    for i in theirs:
+        base = bufs[owner[i]].data_ptr()
+        y, n = L.dev_f32(layers[i].weight.data, "weight"), layers[i].weight.numel()
+        for o in range(0, n, _PIECE):
+            per_owner.setdefault(owner[i], []).append((base + offs[i][0] + o, base + offs[i][1], y + 4 * o,
+                                                       min(_PIECE, n - o)))
+    order = [(rank + j) % world for j in range(1, world) if (rank + j) % world in per_owner]
+    pieces = []
+    for k in range(max(len(v) for v in per_owner.values())):
+        pieces += [per_owner[r][k] for r in order if k < len(per_owner[r])]
+    descs = (L.DfqDequantDesc * len(pieces))()
+    for d, (codes, slot, y, n) in zip(descs, pieces):
+        d.codes, d.slot, d.y, d.n = codes, slot, y, n
+    blocks = L.i64()
+    L.check(L.lib().dfq_dequant_plan_host(descs, len(pieces), ctypes.byref(blocks)), "dfq_dequant_plan_host")
+    if len(_foreign_cache) > 8:
+        _foreign_cache.clear()
+    hit = (L.table_to_device(descs, dev), len(pieces), blocks.value)
+    _foreign_cache[key] = hit
+    return hit
+
+
 def quantize_targ_layer_sharded(graph, bit_weight=8, bits_bias=16, targ_type=None, group=None, backend=None):
     """quantize_targ_layer (utils/layer_transform.py:288-305) with the layers dealt to the ranks of `group`; on
     return every rank holds the complete quantised weights and biases, identical to the single-GPU pass.
@@ -204,15 +246,8 @@ def quantize_targ_layer_sharded(graph, bit_weight=8, bits_bias=16, targ_type=Non
         bufs = ex.exchange()
         theirs = [i for i in range(len(layers)) if owner[i] != rank]
         if theirs:
-            descs = (L.DfqDequantDesc * len(theirs))()
-            for d, i in zip(descs, theirs):
-                base = bufs[owner[i]].data_ptr()
-                d.codes, d.slot = base + offs[i][0], base + offs[i][1]
-                d.y, d.n = L.dev_f32(layers[i].weight.data, "weight"), layers[i].weight.numel()
-            blocks = L.i64()
-            L.check(L.lib().dfq_dequant_plan_host(descs, len(theirs), ctypes.byref(blocks)), "dfq_dequant_plan_host")
-            table = L.table_to_device(descs, dev)
-            L.check(L.lib().dfq_dequant_multi_f32(table.data_ptr(), len(theirs), blocks.value, L.stream()),
+            table, n_desc, blocks = _foreign_table(layers, owner, offs, theirs, bufs, rank, world, dev)
+            L.check(L.lib().dfq_dequant_multi_f32(table.data_ptr(), n_desc, blocks, L.stream()),
                     "dfq_dequant_multi_f32")
             if with_bias:
                 for i in theirs:
