@@ -115,7 +115,15 @@ class DfqPwQ8Desc(ctypes.Structure):
 class DfqDwQ8Desc(ctypes.Structure):
     _fields_ = [("x", c_void), ("wrow", c_void), ("bias", c_void), ("in_slot", c_void), ("y0", c_void),
                 ("out_slot0", c_void), ("y1", c_void), ("out_slot1", c_void)] + \
-               [(k, i32) for k in ("N", "H", "W", "C", "stride", "relu")] + [("s_w", f32), ("c_w", f32)]
+               [(k, i32) for k in ("N", "H", "W", "C", "stride", "relu")] + [("s_w", f32), ("c_w", f32)] + \
+               [(k, i32) for k in ("pad", "dil", "pad_code")]
+
+
+class DfqConvQ8Desc(ctypes.Structure):
+    _fields_ = [("x", c_void), ("wpk", c_void), ("wr", c_void), ("wrt", c_void), ("bias", c_void), ("in_slot", c_void),
+                ("y0", c_void), ("out_slot0", c_void), ("y1", c_void), ("out_slot1", c_void)] + \
+               [(k, i32) for k in ("N", "C", "H", "W", "O", "OH", "OW", "kh", "kw", "stride", "pad", "dil", "relu")] + \
+               [("s_w", f32), ("c_w", f32), ("o_cap", i32)]
 
 
 class DfqStemQ8Desc(ctypes.Structure):
@@ -125,7 +133,7 @@ class DfqStemQ8Desc(ctypes.Structure):
 
 
 Q_SYMMETRIC, Q_RANGE_F32, Q_PER_CHANNEL, Q_CLAMP_OUT = 1, 2, 4, 8
-ABI_VERSION = 16
+ABI_VERSION = 17
 
 # every symbol include/dfq_b200.h declares: (restype, argtypes)
 P = ctypes.POINTER
@@ -175,6 +183,12 @@ PROTOTYPES = {
     "dfq_add_q8": (ctypes.c_int, [c_void, c_void, c_void, c_void, c_void, c_void, c_void, c_void, i64, ctypes.c_int,
                                   c_void]),
     "dfq_mean_q8": (ctypes.c_int, [c_void, c_void, c_void, c_void, c_void, i64, ctypes.c_int, ctypes.c_int, c_void]),
+    "dfq_conv_q8": (ctypes.c_int, [P(DfqConvQ8Desc), c_void]),
+    "dfq_interp_q8": (ctypes.c_int, [c_void, c_void] + [ctypes.c_int] * 7 + [c_void] * 6),
+    "dfq_regrid_q8": (ctypes.c_int, [c_void, c_void, i64, ctypes.c_int, c_void, c_void, c_void, c_void, ctypes.c_int,
+                                     ctypes.c_int, ctypes.c_int, c_void]),
+    "dfq_pool_q8": (ctypes.c_int, [c_void, i64, ctypes.c_int, ctypes.c_int, ctypes.c_int, c_void, c_void, c_void, c_void,
+                                   c_void]),
     "dfq_quant_plan_host": (ctypes.c_int, [P(DfqQuantDesc), ctypes.c_int, P(i64), P(i64)]),
     "dfq_fake_quant_multi_f32": (ctypes.c_int, [c_void, ctypes.c_int, i64, i64, c_void, c_void]),
     "dfq_dequant_codes_f32": (ctypes.c_int, [c_void, ctypes.c_int, c_void, i64, i64, c_void, c_void]),

@@ -18,6 +18,7 @@
 // for the next QuantMeasure (utils/quantize.py:110-111), coalesced fp32 stores.
 #include <cstdlib>
 #include "common.cuh"
+#include "q8_pack.cuh"
 
 namespace dfq {
 
@@ -39,6 +40,9 @@ struct PwI8Args {
     const int8_t *xq;                 // kQ: centred s8 codes [N][H][W][cchunks * 16]
     int C, H, W, OW, kh, kw, stride, pad, dil, taps, cchunks, Kreal;
     int64_t tiles;                    // warp-specialised form: 128-pixel tiles (work items = tiles * n_pass)
+    // kOutQ (static-range plan, eval_q8.py): the output leaves as centred s8 codes, NHWC with cp_out channels per
+    // pixel, on the grid(s) of the consumer(s) instead of fp32 NCHW
+    int8_t *yq[2]; const RangeSlot *oslot[2]; int cp_out;
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -165,8 +169,8 @@ __device__ __forceinline__ float tap_corr(const float *tap_c, uint32_t oob, int 
 // kLin: the activation is row-major [G][K] with K contiguous (a linear layer): a thread's 16-float chunk is four
 // 128-bit loads.  As 16 scalar loads the 32 lanes of every load instruction hit 32 different lines -- the LSU, not
 // the latency, set the classifier's 7.5 us per slab (256 x 1280 -> 1000: 0.153 ms for 20 slabs).
-template <bool kPre, bool kConv, bool kQ, bool kLin = false>
-__global__ void __launch_bounds__(kThreads, kPre ? 3 : 4)
+template <bool kPre, bool kConv, bool kQ, bool kLin = false, bool kOutQ = false>
+__global__ void __launch_bounds__(kThreads, kOutQ ? 2 : (kPre ? 3 : 4))
 pw_i8_kernel(PwI8Args a) {
     extern __shared__ __align__(128) uint8_t smem[];
     // Weight ring: kBS stages, the bulk copy of slab s + kAhead is issued at step s.  With the two-stage ring the copy
@@ -402,6 +406,11 @@ pw_i8_kernel(PwI8Args a) {
             if (!((unsigned)ih < (unsigned)a.H && (unsigned)iw < (unsigned)a.W)) oob |= 1u << t;
         }
     }
+    QuantConsts oq0 = qc, oq1 = qc;
+    if (kOutQ) {
+        oq0 = consts_from_slot(*a.oslot[0], 8, 0, 0.f, 0.f);
+        if (a.yq[1]) oq1 = consts_from_slot(*a.oslot[1], 8, 0, 0.f, 0.f);
+    }
     for (int chunk = warp >> 2; chunk * 16 < a.npass; chunk += 2) {
         const int oc = o0 + chunk * 16;
         if (oc >= o_end) break;                                   // warp-uniform
@@ -435,6 +444,7 @@ pw_i8_kernel(PwI8Args a) {
                     }
                 }
             }
+            float y16[16];
 #pragma unroll
             for (int j4 = 0; j4 < 4; ++j4) {
                 const float4 c4 = cc[j4];
@@ -444,10 +454,44 @@ pw_i8_kernel(PwI8Args a) {
                     float cst = __fadd_rn(row_c, cj[t]);
                     if (kConv && oob) cst = __fsub_rn(cst, corr[4 * j4 + t]);
                     const float yv = fmaxf(__fmaf_rn(fa, (float)(int)d[4 * j4 + t], cst), floor_v);
-                    *py = yv;
-                    py += ys_o;
-                    lo = fminf(lo, yv); hi = fmaxf(hi, yv);
+                    if constexpr (kOutQ) {
+                        y16[4 * j4 + t] = yv;
+                    } else {
+                        *py = yv;
+                        py += ys_o;
+                        lo = fminf(lo, yv); hi = fmaxf(hi, yv);
+                    }
                 }
+            }
+            if constexpr (kOutQ) {                                 // 16 channels of one pixel = one 128-bit store per grid
+                const int64_t off = (en * a.P + ep) * a.cp_out + oc;
+                uint32_t w[4];
+                pack_codes<16>(y16, oq0, w);
+                *reinterpret_cast<uint4 *>(a.yq[0] + off) = make_uint4(w[0], w[1], w[2], w[3]);
+                if (a.yq[1]) {
+                    pack_codes<16>(y16, oq1, w);
+                    *reinterpret_cast<uint4 *>(a.yq[1] + off) = make_uint4(w[0], w[1], w[2], w[3]);
+                }
+            }
+        } else if (kOutQ) {                                        // ragged last chunk: channels >= nvalid are s8 zeros
+            float y16[16];
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+                float cst = __fadd_rn(row_c, chan_c[chunk * 16 + j]);
+                if (kConv && oob) cst = __fsub_rn(cst, tap_corr(tap_c, oob, a.taps, a.npass, chunk * 16 + j));
+                y16[j] = j < nvalid ? fmaxf(__fmaf_rn(fa, (float)(int)d[j], cst), floor_v) : 0.0f;
+            }
+            const int64_t off = (en * a.P + ep) * a.cp_out + oc;
+            for (int gi = 0; gi < 2; ++gi) {
+                if (!a.yq[gi]) break;
+                uint32_t w[4];
+                pack_codes<16>(y16, gi ? oq1 : oq0, w);
+#pragma unroll
+                for (int q4 = 0; q4 < 4; ++q4) w[q4] = keep_left(w[q4], nvalid - 4 * q4);
+                if (oc + 16 <= a.cp_out) *reinterpret_cast<uint4 *>(a.yq[gi] + off) = make_uint4(w[0], w[1], w[2], w[3]);
+                else
+                    for (int q4 = 0; q4 < 4 && oc + 4 * q4 < a.cp_out; ++q4)
+                        *reinterpret_cast<uint32_t *>(a.yq[gi] + off + 4 * q4) = w[q4];
             }
         } else {
 #pragma unroll
@@ -787,7 +831,9 @@ static int pw_i8_launch(PwI8Args &a, bool conv, int64_t G, cudaStream_t stream) 
                              (const void *)pw_i8_kernel<false, true, false>, (const void *)pw_i8_kernel<true, true, false>,
                              (const void *)pw_i8_kernel<false, true, true>, (const void *)pw_i8_kernel<true, true, true>,
                              (const void *)pw_i8_kernel<false, false, false, true>,
-                             (const void *)pw_i8_kernel<true, false, false, true>};
+                             (const void *)pw_i8_kernel<true, false, false, true>,
+                             (const void *)pw_i8_kernel<false, true, true, false, true>,
+                             (const void *)pw_i8_kernel<true, true, true, false, true>};
         for (const void *fn : fns) {
             cudaError_t ce = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
             if (ce != cudaSuccess) return (int)ce;
@@ -836,7 +882,10 @@ static int pw_i8_launch(PwI8Args &a, bool conv, int64_t G, cudaStream_t stream) 
         static int conv_pre = -2;
         if (conv_pre == -2) { const char *e = getenv("DFQ_CONV_PRE"); conv_pre = e ? atoi(e) : -1; }
         const bool pre_q = conv_pre >= 0 ? (conv_pre != 0 && a.slabs >= 2) : (pre || (a.slabs >= 2 && a.tmem_cols >= 256));
-        if (pre_q) pw_i8_kernel<true, true, true><<<grid, kThreads, smem, stream>>>(a);
+        if (a.yq[0]) {
+            if (pre_q) pw_i8_kernel<true, true, true, false, true><<<grid, kThreads, smem, stream>>>(a);
+            else pw_i8_kernel<false, true, true, false, true><<<grid, kThreads, smem, stream>>>(a);
+        } else if (pre_q) pw_i8_kernel<true, true, true><<<grid, kThreads, smem, stream>>>(a);
         else pw_i8_kernel<false, true, true><<<grid, kThreads, smem, stream>>>(a);
     } else if (false) {
         if (pre) pw_i8_kernel<true, true, true><<<grid, kThreads, smem, stream>>>(a);
@@ -908,5 +957,35 @@ extern "C" int dfq_conv_i8(const DfqConvI8Desc *d, void *stream) {
         g_launches += 1;
         a.xq = d->scratch;
     }
+    return pw_i8_launch(a, true, a.G, (cudaStream_t)stream);
+}
+
+// Static-range form (eval_q8.py): the input already IS centred s8 codes, NHWC with the channels padded to 16 (what every
+// producer of the u8 plan writes), so there is no quantising pre-pass, and the output leaves as codes on the grid(s) of
+// its consumer(s).  Same pipeline, same packed weights, same padding correction as dfq_conv_i8.
+extern "C" int dfq_conv_q8(const DfqConvQ8Desc *d, void *stream) {
+    if (!d || !d->x || !d->y0 || !d->out_slot0 || !d->wpk || !d->wr || !d->wrt || !d->in_slot || d->N <= 0 ||
+        d->kh <= 0 || d->kw <= 0 || d->kh * d->kw > 32 || d->stride <= 0 || d->dil <= 0 || d->pad < 0 ||
+        (d->y1 && !d->out_slot1))
+        return (int)cudaErrorInvalidValue;
+    const int OH = (d->H + 2 * d->pad - d->dil * (d->kh - 1) - 1) / d->stride + 1;
+    const int OW = (d->W + 2 * d->pad - d->dil * (d->kw - 1) - 1) / d->stride + 1;
+    if (OH != d->OH || OW != d->OW || OH <= 0 || OW <= 0) return (int)cudaErrorInvalidValue;
+    if ((int64_t)d->C * d->H * d->W > 0x7fffffffll) return (int)cudaErrorInvalidValue;
+    PwI8Args a = {};
+    int64_t bytes;
+    a.taps = d->kh * d->kw; a.cchunks = (d->C + 15) / 16; a.K = a.taps * a.cchunks * 16; a.Kreal = a.taps * d->C;
+    int e = plan_cap(d->O, a.K, d->o_cap, &a.n_pass, &a.o_per_pass, &a.npass, &a.slabs, &bytes);
+    if (e) return e;
+    a.wpk = d->wpk; a.wr = d->wr; a.wrt = d->wrt; a.bias = d->bias;
+    a.slot = (const RangeSlot *)d->in_slot;
+    a.P = OH * OW; a.G = (int64_t)d->N * a.P;
+    a.O = d->O; a.bits = 8; a.relu = d->relu; a.s_w = d->s_w; a.c_w = d->c_w;
+    a.C = d->C; a.H = d->H; a.W = d->W; a.OW = OW; a.kh = d->kh; a.kw = d->kw; a.stride = d->stride; a.pad = d->pad;
+    a.dil = d->dil;
+    a.xq = d->x;
+    a.yq[0] = d->y0; a.yq[1] = d->y1;
+    a.oslot[0] = (const RangeSlot *)d->out_slot0; a.oslot[1] = (const RangeSlot *)d->out_slot1;
+    a.cp_out = (d->O + 15) / 16 * 16;
     return pw_i8_launch(a, true, a.G, (cudaStream_t)stream);
 }

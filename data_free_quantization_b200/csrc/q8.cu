@@ -22,6 +22,7 @@
 //   meanq8_kernel spatial mean (utils/layer_transform.py:79-95) feeding the classifier's grid.
 #include <cuda.h>
 #include "common.cuh"
+#include "q8_pack.cuh"
 
 namespace dfq {
 namespace {
@@ -93,87 +94,6 @@ __device__ __forceinline__ void umma_commit(uint32_t bar) {
 }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-
-// The integer code of utils/quantize.py:72-74 in the low byte of the result (see quant_code, common.cuh)
-__device__ __forceinline__ uint32_t code_bits(float x, const QuantConsts &c) {
-    const float t = __fadd_rn(x, c.neg_min);
-    if (c.fast) {                                           // block-uniform
-        const float magic = 12582912.0f;
-        const float cl = fminf(fmaxf(__fmul_rn(t, c.rscale), c.qmin), c.qmax);
-        float m = __fadd_rn(cl, magic);
-        if (fabsf(__fsub_rn(cl, __fadd_rn(m, -magic))) > c.amb) {          // within a few ulp of a tie: exact division
-            const float tc = fminf(fmaxf(t, c.t_lo), c.t_hi);
-            m = __fadd_rn(fminf(fmaxf(div_const_rn(tc, c.scale, c.rscale), c.qmin), c.qmax), magic);
-        }
-        return __float_as_uint(m);
-    }
-    return (uint32_t)__float2int_rn(fminf(fmaxf(__fdiv_rn(t, c.scale), c.qmin), c.qmax));
-}
-// The exact quantiser (IEEE division) for a value whose reciprocal estimate sits near a tie: rare, kept OUT of line so
-// that the unrolled fast paths stay small (the depthwise kernel was 94 KB of code and stalled on instruction fetch).
-__device__ __noinline__ uint32_t code_bits_exact(float x, float neg_min, float scale, float rscale, float qmin,
-                                                 float qmax, float t_lo, float t_hi) {
-    const float t = __fadd_rn(x, neg_min);
-    const float tc = fminf(fmaxf(t, t_lo), t_hi);
-    return __float_as_uint(__fadd_rn(fminf(fmaxf(div_const_rn(tc, scale, rscale), qmin), qmax), 12582912.0f));
-}
-
-// N values -> N centred s8 codes, four per word.  The reciprocal estimates of all N values are formed in straight-line
-// code (the values interleave in the pipeline); ONE branch per call goes to the exact division, taken when any of
-// them sits within a few ulp of a tie (~5e-4 per value).
-template <int N>
-__device__ __forceinline__ void pack_codes(const float (&v)[N], const QuantConsts &c, uint32_t (&w)[N / 4]) {
-    uint32_t b[N];
-    if (c.fast) {                                           // block-uniform
-        const float magic = 12582912.0f;
-        uint32_t flagged = 0;
-#pragma unroll
-        for (int i = 0; i < N; ++i) {
-            const float cl = fminf(fmaxf(__fmul_rn(__fadd_rn(v[i], c.neg_min), c.rscale), c.qmin), c.qmax);
-            const float m = __fadd_rn(cl, magic);
-            b[i] = __float_as_uint(m);
-            if (fabsf(__fsub_rn(cl, __fadd_rn(m, -magic))) > c.amb) flagged |= 1u << i;
-        }
-        while (flagged) {                                    // rare: out-of-line exact division, one value at a time
-            const int i = __ffs(flagged) - 1;
-            flagged &= flagged - 1;
-            float x = v[0];
-#pragma unroll
-            for (int j = 1; j < N; ++j) x = (j == i) ? v[j] : x;
-            const uint32_t e = code_bits_exact(x, c.neg_min, c.scale, c.rscale, c.qmin, c.qmax, c.t_lo, c.t_hi);
-#pragma unroll
-            for (int j = 0; j < N; ++j) b[j] = (j == i) ? e : b[j];
-        }
-    } else {
-#pragma unroll
-        for (int i = 0; i < N; ++i) b[i] = code_bits(v[i], c);
-    }
-#pragma unroll
-    for (int j = 0; j < N / 4; ++j) {
-        const uint32_t lo = __byte_perm(b[4 * j], b[4 * j + 1], 0x0040), hi = __byte_perm(b[4 * j + 2], b[4 * j + 3], 0x0040);
-        w[j] = __byte_perm(lo, hi, 0x5410) ^ 0x80808080u;
-    }
-}
-// four values -> four centred s8 codes in one word
-__device__ __forceinline__ uint32_t pack4(float v0, float v1, float v2, float v3, const QuantConsts &c) {
-    const float v[4] = {v0, v1, v2, v3};
-    uint32_t w[1];
-    pack_codes<4>(v, c, w);
-    return w[0];
-}
-// bytes of channels >= `left` (counted from the word's first channel) cleared: padding channels are s8 zero
-__device__ __forceinline__ uint32_t keep_left(uint32_t w, int left) {
-    return left >= 4 ? w : (left <= 0 ? 0u : (w & (0xffffffffu >> (8 * (4 - left)))));
-}
-// centred s8 code word -> the four fp32 values the reference's quantiser produced: fl(fl(code * s) + min)
-__device__ __forceinline__ void dequant4(uint32_t w, float s, float mn, float *out) {
-    const uint32_t u = w ^ 0x80808080u;                                     // codes 0..255
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        const float q = __fadd_rn(__uint_as_float(__byte_perm(u, 0x4B000000u, 0x7650 + i)), -8388608.0f);
-        out[i] = __fadd_rn(__fmul_rn(q, s), mn);
-    }
-}
 
 template <int U> struct TmemLd;
 template <> struct TmemLd<8> {
@@ -398,6 +318,7 @@ struct DwQ8Args {
     const RangeSlot *out_slot[2]; int8_t *y[2];
     int N, H, W, OH, OW, C, Cp, stride, relu, strips;
     float s_w, c_w;
+    int pad, dil;                // generic kernel only (the dp4a kernel is pad 1, dilation 1)
 };
 
 template <int S> struct DwStrip { static constexpr int value = S == 1 ? 10 : 5; };   // outputs per 12 input columns
@@ -406,7 +327,10 @@ __device__ __forceinline__ float small_int_to_float(int v) {      // exact for |
     return __fadd_rn(__int_as_float(0x4B400000 + v), -12582912.0f);
 }
 
-template <int S, bool DUAL>
+// PADC: the border is not conv zero padding but F.pad(x) AHEAD of the QuantMeasure (DeepLab's fixed_padding,
+// modeling/segmentation/backbone/mobilenet.py): the padded zeros are quantised with the tensor, so a border tap carries
+// the code of 0.0 on the input grid (dequantised: not exactly 0 unless the grid contains it) and counts as in-bound.
+template <int S, bool DUAL, bool PADC = false>
 __global__ void __launch_bounds__(kThreads, 2)
 dwq8_kernel(DwQ8Args a) {
     constexpr int P = DwStrip<S>::value;
@@ -425,8 +349,11 @@ dwq8_kernel(DwQ8Args a) {
     QuantConsts q1 = q0;
     if (DUAL) q1 = consts_from_slot(*a.out_slot[1], 8, 0, 0.f, 0.f);
     const int iy0 = oy * S - 1;
-    const bool rowok[3] = {(unsigned)iy0 < (unsigned)a.H, (unsigned)(iy0 + 1) < (unsigned)a.H,
-                           (unsigned)(iy0 + 2) < (unsigned)a.H};
+    const bool rowin[3] = {(unsigned)iy0 < (unsigned)a.H, (unsigned)(iy0 + 1) < (unsigned)a.H,
+                           (unsigned)(iy0 + 2) < (unsigned)a.H};          // the row exists in memory
+    const bool rowok[3] = {PADC || rowin[0], PADC || rowin[1], PADC || rowin[2]};   // the row's taps count
+    uint32_t padw = 0u;
+    if (PADC) padw = pack4(0.0f, 0.0f, 0.0f, 0.0f, consts_from_slot(in, 8, 0, 0.f, 0.f));
     uint32_t wr[3][4];                                            // [row][channel] = (w0, w1, w2, 0) centred s8
 #pragma unroll
     for (int r = 0; r < 3; ++r) {
@@ -479,8 +406,8 @@ dwq8_kernel(DwQ8Args a) {
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
                     const int ix = ixs + 4 * blk + q;
-                    p[q] = (rowok[r] && (unsigned)ix < (unsigned)a.W)
-                               ? __ldg(reinterpret_cast<const uint32_t *>(xr + (int64_t)ix * a.Cp)) : 0u;
+                    p[q] = (rowin[r] && (unsigned)ix < (unsigned)a.W)
+                               ? __ldg(reinterpret_cast<const uint32_t *>(xr + (int64_t)ix * a.Cp)) : padw;
                 }
                 const uint32_t a0 = __byte_perm(p[0], p[1], 0x5140), a1 = __byte_perm(p[0], p[1], 0x7362);
                 const uint32_t b0 = __byte_perm(p[2], p[3], 0x5140), b1 = __byte_perm(p[2], p[3], 0x7362);
@@ -509,7 +436,7 @@ dwq8_kernel(DwQ8Args a) {
                 }
             }
             const int ixl = ox * S - 1;
-            const bool lin = ixl >= 0, rin = ixl + 2 < a.W;      // left / right tap column in bounds (centre always is)
+            const bool lin = PADC || ixl >= 0, rin = PADC || ixl + 2 < a.W;   // left / right tap column counts (centre always does)
             float yv[4];
 #pragma unroll
             for (int c = 0; c < 4; ++c) {
@@ -526,6 +453,68 @@ dwq8_kernel(DwQ8Args a) {
                 *reinterpret_cast<uint32_t *>(a.y[1] + off) = keep_left(w[0], left);
             }
         }
+    }
+}
+
+// Depthwise 3 x 3 with any padding / dilation (DeepLab's dilated blocks: one layer of 960 channels at 33 x 33): one
+// thread per output pixel and 4-channel word, nine word loads, the same integer sums and the same fp32 expression
+// as dwq8_kernel (bit-identical where both apply), without its strip transposes.
+template <bool PADC>
+__global__ void __launch_bounds__(kThreads)
+dwq8_generic_kernel(DwQ8Args a) {
+    const unsigned cw = (unsigned)a.Cp >> 2;
+    const int64_t idx = (int64_t)blockIdx.x * kThreads + threadIdx.x;
+    if (idx >= (int64_t)a.N * a.OH * a.OW * cw) return;
+    const int cg = (int)(idx % cw);
+    int64_t rest = idx / cw;
+    const int ox = (int)(rest % a.OW); rest /= a.OW;
+    const int oy = (int)(rest % a.OH);
+    const int n = (int)(rest / a.OH);
+    const int c0 = cg * 4;
+    const RangeSlot in = *a.in_slot;
+    const float sx = in.scale, cx = __fmaf_rn(128.0f, sx, in.mn);
+    const float fa = __fmul_rn(sx, a.s_w), fb = __fmul_rn(sx, a.c_w);
+    const float cxsw = __fmul_rn(cx, a.s_w), cxcw = __fmul_rn(cx, a.c_w);
+    uint32_t padw = 0u;
+    if (PADC) padw = pack4(0.0f, 0.0f, 0.0f, 0.0f, consts_from_slot(in, 8, 0, 0.f, 0.f));
+    int acc[4] = {0, 0, 0, 0}, sa[4] = {0, 0, 0, 0}, sb[4] = {0, 0, 0, 0}, ninb = 0;
+    const int8_t *xn = a.x + (int64_t)n * a.H * a.W * a.Cp + c0;
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+        const uint4 wv = __ldg(reinterpret_cast<const uint4 *>(a.wrow + (int64_t)r * a.Cp + c0));
+        const uint32_t wr[4] = {wv.x, wv.y, wv.z, wv.w};
+        const int iy = oy * a.stride - a.pad + r * a.dil;
+#pragma unroll
+        for (int j = 0; j < 3; ++j) {
+            const int ix = ox * a.stride - a.pad + j * a.dil;
+            const bool mem = (unsigned)iy < (unsigned)a.H && (unsigned)ix < (unsigned)a.W;
+            if (!mem && !PADC) continue;
+            const uint32_t w = mem ? __ldg(reinterpret_cast<const uint32_t *>(xn + ((int64_t)iy * a.W + ix) * a.Cp)) : padw;
+            ++ninb;
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                const int av = (int)(int8_t)(w >> (8 * c)), bv = (int)(int8_t)(wr[c] >> (8 * j));
+                acc[c] += av * bv; sa[c] += av; sb[c] += bv;
+            }
+        }
+    }
+    const float4 bq = a.bias ? __ldg(reinterpret_cast<const float4 *>(a.bias + c0)) : make_float4(0.f, 0.f, 0.f, 0.f);
+    const float b4[4] = {bq.x, bq.y, bq.z, bq.w};
+    const float floor_v = a.relu ? 0.0f : -INFINITY;
+    float yv[4];
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+        const float cst = __fadd_rn(__fmaf_rn(cxsw, (float)sb[c], __fmul_rn((float)ninb, cxcw)), b4[c]);
+        yv[c] = fmaxf(__fmaf_rn(fa, small_int_to_float(acc[c]), __fmaf_rn(fb, small_int_to_float(sa[c]), cst)), floor_v);
+    }
+    const int64_t off = (((int64_t)n * a.OH + oy) * a.OW + ox) * a.Cp + c0;
+    const int left = a.C - c0;
+    uint32_t w[1];
+    pack_codes<4>(yv, consts_from_slot(*a.out_slot[0], 8, 0, 0.f, 0.f), w);
+    *reinterpret_cast<uint32_t *>(a.y[0] + off) = keep_left(w[0], left);
+    if (a.y[1]) {
+        pack_codes<4>(yv, consts_from_slot(*a.out_slot[1], 8, 0, 0.f, 0.f), w);
+        *reinterpret_cast<uint32_t *>(a.y[1] + off) = keep_left(w[0], left);
     }
 }
 
@@ -833,7 +822,7 @@ extern "C" int dfq_pw_q8(const DfqPwQ8Desc *d, void *stream) {
 
 extern "C" int dfq_dw_q8(const DfqDwQ8Desc *d, void *stream) {
     if (!d || !d->x || !d->wrow || !d->in_slot || !d->y0 || !d->out_slot0 || (d->y1 && !d->out_slot1) || d->N <= 0 ||
-        (d->stride != 1 && d->stride != 2))
+        (d->stride != 1 && d->stride != 2) || d->pad < 0 || d->dil < 0)
         return (int)cudaErrorInvalidValue;
     DwQ8Args a = {};
     a.x = d->x; a.wrow = d->wrow; a.bias = d->bias; a.in_slot = (const RangeSlot *)d->in_slot;
@@ -841,19 +830,36 @@ extern "C" int dfq_dw_q8(const DfqDwQ8Desc *d, void *stream) {
     a.y[0] = d->y0; a.y[1] = d->y1;
     a.N = d->N; a.H = d->H; a.W = d->W; a.C = d->C; a.Cp = (d->C + 15) / 16 * 16; a.stride = d->stride; a.relu = d->relu;
     a.s_w = d->s_w; a.c_w = d->c_w;
-    a.OH = (d->H + 2 - 3) / d->stride + 1; a.OW = (d->W + 2 - 3) / d->stride + 1;
+    a.dil = d->dil ? d->dil : 1;                       // 0 = the defaults of the first ABI: padding 1, dilation 1
+    a.pad = (d->pad || d->dil) ? d->pad : 1;
+    a.OH = (d->H + 2 * a.pad - 2 * a.dil - 1) / d->stride + 1; a.OW = (d->W + 2 * a.pad - 2 * a.dil - 1) / d->stride + 1;
+    if (a.OH <= 0 || a.OW <= 0) return (int)cudaErrorInvalidValue;
+    const cudaStream_t st = (cudaStream_t)stream;
+    const bool padc = d->pad_code != 0;
+    if (a.pad != 1 || a.dil != 1) {
+        const int64_t total = (int64_t)a.N * a.OH * a.OW * (a.Cp / 4);
+        const int64_t blocks = (total + kThreads - 1) / kThreads;
+        if (blocks >= 0x7fffffffll) return (int)cudaErrorInvalidValue;
+        if (padc) dwq8_generic_kernel<true><<<(unsigned)blocks, kThreads, 0, st>>>(a);
+        else dwq8_generic_kernel<false><<<(unsigned)blocks, kThreads, 0, st>>>(a);
+        g_launches += 1;
+        return (int)cudaGetLastError();
+    }
     const int P = d->stride == 1 ? DwStrip<1>::value : DwStrip<2>::value;
     a.strips = (a.OW + P - 1) / P;
     const int64_t total = (int64_t)a.N * a.OH * (a.Cp / 4);
     if (total >= 0x7fffffffll) return (int)cudaErrorInvalidValue;
     const unsigned grid = (unsigned)((total + kThreads - 1) / kThreads);
-    const cudaStream_t st = (cudaStream_t)stream;
-    if (d->stride == 1) {
-        if (d->y1) dwq8_kernel<1, true><<<grid, kThreads, 0, st>>>(a);
-        else dwq8_kernel<1, false><<<grid, kThreads, 0, st>>>(a);
-    } else {
-        if (d->y1) dwq8_kernel<2, true><<<grid, kThreads, 0, st>>>(a);
-        else dwq8_kernel<2, false><<<grid, kThreads, 0, st>>>(a);
+    const int variant = (d->stride == 2 ? 4 : 0) | (d->y1 ? 2 : 0) | (padc ? 1 : 0);
+    switch (variant) {
+    case 0: dwq8_kernel<1, false, false><<<grid, kThreads, 0, st>>>(a); break;
+    case 1: dwq8_kernel<1, false, true><<<grid, kThreads, 0, st>>>(a); break;
+    case 2: dwq8_kernel<1, true, false><<<grid, kThreads, 0, st>>>(a); break;
+    case 3: dwq8_kernel<1, true, true><<<grid, kThreads, 0, st>>>(a); break;
+    case 4: dwq8_kernel<2, false, false><<<grid, kThreads, 0, st>>>(a); break;
+    case 5: dwq8_kernel<2, false, true><<<grid, kThreads, 0, st>>>(a); break;
+    case 6: dwq8_kernel<2, true, false><<<grid, kThreads, 0, st>>>(a); break;
+    default: dwq8_kernel<2, true, true><<<grid, kThreads, 0, st>>>(a); break;
     }
     g_launches += 1;
     return (int)cudaGetLastError();

@@ -1,0 +1,221 @@
+// Kernel (e), static-range form, data-movement ops on code tensors (what DeepLabV3+ adds to MobileNetV2's graph):
+//   interpq8_kernel  F.interpolate(Q(x), size, 'bilinear', align_corners) as patched by utils/layer_transform.py:98-110:
+//                    the operand's codes are dequantised (they ARE Q(x)), blended with ATen's index / weight arithmetic,
+//                    and leave on the consumer's grid -- or as fp32 NCHW (the network's logits);
+//   regridq8_kernel  one operand of torch.cat (utils/layer_transform.py:112-125): every operand has its own QuantMeasure,
+//                    the concatenation is quantised again by the consuming convolution's: codes on grid A -> values ->
+//                    codes on grid B, written at the operand's channel offset of the wider NHWC tensor;
+//   poolq8_kernel    nn.AdaptiveAvgPool2d(1) (not a patched op: it sees the RAW fp32 tensor, which the producing 1 x 1
+//                    convolution writes next to its codes) -> codes on the grid of the following convolution.
+// Activation format: centred s8 codes, NHWC, channels padded to 16 with zero bytes (see q8.cu).
+#include "common.cuh"
+#include "q8_pack.cuh"
+
+namespace dfq {
+namespace {
+
+// ATen UpSample.h area_pixel_compute_source_index + the two-tap weights (same as move.cu)
+__device__ __forceinline__ void q8_interp_index(int o, float scale, int size, int align, int &i0, int &i1, float &l1) {
+    const float s = align ? __fmul_rn(scale, (float)o)
+                          : fmaxf(__fsub_rn(__fmul_rn(scale, __fadd_rn((float)o, 0.5f)), 0.5f), 0.0f);
+    i0 = min((int)s, size - 1);
+    i1 = i0 + (i0 < size - 1 ? 1 : 0);
+    l1 = fminf(fmaxf(__fsub_rn(s, (float)i0), 0.0f), 1.0f);
+}
+
+struct InterpQ8Args {
+    const int8_t *x; const RangeSlot *in_slot;
+    int8_t *y[2]; const RangeSlot *out_slot[2]; float *yf;
+    int N, C, Cp, H, W, OH, OW, align;
+    float sy, sx;
+};
+
+// the four values of one channel word at output pixel (oy, ox) of image n
+__device__ __forceinline__ void interp_word(const InterpQ8Args &a, const int8_t *xn, int cwi, int y0, int y1, float l1y,
+                                            int x0, int x1, float l1x, float s, float mn, float *v) {
+    const int64_t rs = (int64_t)a.W * a.Cp;
+    const uint32_t w00 = __ldg(reinterpret_cast<const uint32_t *>(xn + y0 * rs + (int64_t)x0 * a.Cp) + cwi);
+    const uint32_t w01 = __ldg(reinterpret_cast<const uint32_t *>(xn + y0 * rs + (int64_t)x1 * a.Cp) + cwi);
+    const uint32_t w10 = __ldg(reinterpret_cast<const uint32_t *>(xn + y1 * rs + (int64_t)x0 * a.Cp) + cwi);
+    const uint32_t w11 = __ldg(reinterpret_cast<const uint32_t *>(xn + y1 * rs + (int64_t)x1 * a.Cp) + cwi);
+    float a00[4], a01[4], a10[4], a11[4];
+    dequant4(w00, s, mn, a00); dequant4(w01, s, mn, a01); dequant4(w10, s, mn, a10); dequant4(w11, s, mn, a11);
+    const float l0x = __fsub_rn(1.0f, l1x), l0y = __fsub_rn(1.0f, l1y);
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+        const float top = __fadd_rn(__fmul_rn(l0x, a00[c]), __fmul_rn(l1x, a01[c]));
+        const float bot = __fadd_rn(__fmul_rn(l0x, a10[c]), __fmul_rn(l1x, a11[c]));
+        v[c] = __fadd_rn(__fmul_rn(l0y, top), __fmul_rn(l1y, bot));
+    }
+}
+
+// codes out: one thread per (pixel, channel word), channel words fastest (coalesced code loads and stores)
+__global__ void __launch_bounds__(kThreads)
+interpq8_codes_kernel(InterpQ8Args a) {
+    const int cw = a.Cp >> 2;
+    const int64_t idx = (int64_t)blockIdx.x * kThreads + threadIdx.x;
+    if (idx >= (int64_t)a.N * a.OH * a.OW * cw) return;
+    const int cwi = (int)(idx % cw);
+    int64_t rest = idx / cw;
+    const int ox = (int)(rest % a.OW); rest /= a.OW;
+    const int oy = (int)(rest % a.OH);
+    const int n = (int)(rest / a.OH);
+    int y0, y1, x0, x1; float l1y, l1x;
+    q8_interp_index(oy, a.sy, a.H, a.align, y0, y1, l1y);
+    q8_interp_index(ox, a.sx, a.W, a.align, x0, x1, l1x);
+    const RangeSlot in = *a.in_slot;
+    float v[4];
+    interp_word(a, a.x + (int64_t)n * a.H * a.W * a.Cp, cwi, y0, y1, l1y, x0, x1, l1x, in.scale, in.mn, v);
+    const int64_t off = (((int64_t)n * a.OH + oy) * a.OW + ox) * a.Cp + 4 * cwi;
+    const int left = a.C - 4 * cwi;
+    uint32_t w[1];
+    pack_codes<4>(v, consts_from_slot(*a.out_slot[0], 8, 0, 0.f, 0.f), w);
+    *reinterpret_cast<uint32_t *>(a.y[0] + off) = keep_left(w[0], left);
+    if (a.y[1]) {
+        pack_codes<4>(v, consts_from_slot(*a.out_slot[1], 8, 0, 0.f, 0.f), w);
+        *reinterpret_cast<uint32_t *>(a.y[1] + off) = keep_left(w[0], left);
+    }
+}
+
+// fp32 NCHW out (the logits): one thread per output pixel, pixels fastest (coalesced fp32 stores per channel plane; the
+// source image is a few hundred KB of codes and stays in L1 / L2)
+__global__ void __launch_bounds__(kThreads)
+interpq8_f32_kernel(InterpQ8Args a) {
+    const int64_t idx = (int64_t)blockIdx.x * kThreads + threadIdx.x;
+    if (idx >= (int64_t)a.N * a.OH * a.OW) return;
+    const int ox = (int)(idx % a.OW);
+    const int oy = (int)((idx / a.OW) % a.OH);
+    const int n = (int)(idx / ((int64_t)a.OW * a.OH));
+    int y0, y1, x0, x1; float l1y, l1x;
+    q8_interp_index(oy, a.sy, a.H, a.align, y0, y1, l1y);
+    q8_interp_index(ox, a.sx, a.W, a.align, x0, x1, l1x);
+    const RangeSlot in = *a.in_slot;
+    const int8_t *xn = a.x + (int64_t)n * a.H * a.W * a.Cp;
+    const int64_t plane = (int64_t)a.OH * a.OW;
+    float *yp = a.yf + (int64_t)n * a.C * plane + (int64_t)oy * a.OW + ox;
+    for (int cwi = 0; 4 * cwi < a.C; ++cwi) {
+        float v[4];
+        interp_word(a, xn, cwi, y0, y1, l1y, x0, x1, l1x, in.scale, in.mn, v);
+#pragma unroll
+        for (int c = 0; c < 4; ++c)
+            if (4 * cwi + c < a.C) yp[(int64_t)(4 * cwi + c) * plane] = v[c];
+    }
+}
+
+struct RegridQ8Args {
+    const int8_t *x; const RangeSlot *in_slot;
+    int8_t *y[2]; const RangeSlot *out_slot[2];
+    int64_t G; int C, cp_in, cp_out, c_off, words_out;    // words_out: 4-channel words this launch writes per pixel
+};
+
+__global__ void __launch_bounds__(kThreads)
+regridq8_kernel(RegridQ8Args a) {
+    const int64_t idx = (int64_t)blockIdx.x * kThreads + threadIdx.x;
+    if (idx >= a.G * a.words_out) return;
+    const int wi = (int)(idx % a.words_out);
+    const int64_t g = idx / a.words_out;
+    const int left = a.C - 4 * wi;                               // real channels in this word (<= 0: the padded tail)
+    uint32_t w0 = 0u, w1 = 0u;
+    if (left > 0) {
+        const RangeSlot in = *a.in_slot;
+        float v[4];
+        dequant4(__ldg(reinterpret_cast<const uint32_t *>(a.x + g * a.cp_in) + wi), in.scale, in.mn, v);
+        uint32_t w[1];
+        pack_codes<4>(v, consts_from_slot(*a.out_slot[0], 8, 0, 0.f, 0.f), w);
+        w0 = keep_left(w[0], left);
+        if (a.y[1]) {
+            pack_codes<4>(v, consts_from_slot(*a.out_slot[1], 8, 0, 0.f, 0.f), w);
+            w1 = keep_left(w[0], left);
+        }
+    }
+    const int64_t off = g * a.cp_out + a.c_off + 4 * wi;
+    *reinterpret_cast<uint32_t *>(a.y[0] + off) = w0;
+    if (a.y[1]) *reinterpret_cast<uint32_t *>(a.y[1] + off) = w1;
+}
+
+// mean over the HW rows of x[n] ([HW][C] fp32, rows `ld` floats apart): thread per (n, channel), fp64 accumulation
+__global__ void __launch_bounds__(kThreads)
+poolq8_kernel(const float *__restrict__ x, int64_t ld, int N, int HW, int C, int Cp, int8_t *y0, const RangeSlot *s0,
+              int8_t *y1, const RangeSlot *s1) {
+    const int idx = blockIdx.x * kThreads + threadIdx.x;
+    if (idx >= N * Cp) return;
+    const int c = idx % Cp, n = idx / Cp;
+    int8_t code0 = 0, code1 = 0;
+    if (c < C) {
+        const float *p = x + (int64_t)n * HW * ld + c;
+        double acc = 0.0;
+        for (int i = 0; i < HW; ++i) acc += (double)__ldg(p + (int64_t)i * ld);
+        const float m = (float)(acc / (double)HW);
+        code0 = (int8_t)(pack4(m, m, m, m, consts_from_slot(*s0, 8, 0, 0.f, 0.f)) & 0xffu);
+        if (y1) code1 = (int8_t)(pack4(m, m, m, m, consts_from_slot(*s1, 8, 0, 0.f, 0.f)) & 0xffu);
+    }
+    y0[idx] = code0;
+    if (y1) y1[idx] = code1;
+}
+
+inline float q8_interp_scale(int in, int out, int align) {
+    if (align) return out > 1 ? (float)(in - 1) / (float)(out - 1) : 0.0f;
+    return out > 0 ? (float)in / (float)out : 0.0f;
+}
+
+}  // namespace
+}  // namespace dfq
+
+using namespace dfq;
+
+extern "C" int dfq_interp_q8(const int8_t *x, const float *in_slot, int N, int C, int H, int W, int OH, int OW,
+                             int align_corners, int8_t *y0, const float *out_slot0, int8_t *y1, const float *out_slot1,
+                             float *yf, void *stream) {
+    if (!x || !in_slot || N <= 0 || C <= 0 || H <= 0 || W <= 0 || OH <= 0 || OW <= 0 || (!y0 && !yf) || (y0 && !out_slot0) ||
+        (y1 && (!y0 || !out_slot1)))
+        return (int)cudaErrorInvalidValue;
+    InterpQ8Args a = {};
+    a.x = x; a.in_slot = (const RangeSlot *)in_slot;
+    a.y[0] = y0; a.y[1] = y1; a.out_slot[0] = (const RangeSlot *)out_slot0; a.out_slot[1] = (const RangeSlot *)out_slot1;
+    a.yf = yf;
+    a.N = N; a.C = C; a.Cp = (C + 15) / 16 * 16; a.H = H; a.W = W; a.OH = OH; a.OW = OW; a.align = align_corners ? 1 : 0;
+    a.sy = q8_interp_scale(H, OH, a.align); a.sx = q8_interp_scale(W, OW, a.align);
+    const cudaStream_t st = (cudaStream_t)stream;
+    if (y0) {
+        const int64_t blocks = ((int64_t)N * OH * OW * (a.Cp / 4) + kThreads - 1) / kThreads;
+        if (blocks >= 0x7fffffffll) return (int)cudaErrorInvalidValue;
+        interpq8_codes_kernel<<<(unsigned)blocks, kThreads, 0, st>>>(a);
+        g_launches += 1;
+    }
+    if (yf) {
+        const int64_t blocks = ((int64_t)N * OH * OW + kThreads - 1) / kThreads;
+        if (blocks >= 0x7fffffffll) return (int)cudaErrorInvalidValue;
+        interpq8_f32_kernel<<<(unsigned)blocks, kThreads, 0, st>>>(a);
+        g_launches += 1;
+    }
+    return (int)cudaGetLastError();
+}
+
+extern "C" int dfq_regrid_q8(const int8_t *x, const float *in_slot, int64_t G, int C, int8_t *y0, const float *out_slot0,
+                             int8_t *y1, const float *out_slot1, int cp_out, int c_off, int fill_tail, void *stream) {
+    if (!x || !in_slot || !y0 || !out_slot0 || (y1 && !out_slot1) || G <= 0 || C <= 0 || (c_off & 3) || cp_out <= 0 ||
+        (cp_out & 15) || c_off + C > cp_out)
+        return (int)cudaErrorInvalidValue;
+    RegridQ8Args a = {};
+    a.x = x; a.in_slot = (const RangeSlot *)in_slot;
+    a.y[0] = y0; a.y[1] = y1; a.out_slot[0] = (const RangeSlot *)out_slot0; a.out_slot[1] = (const RangeSlot *)out_slot1;
+    a.G = G; a.C = C; a.cp_in = (C + 15) / 16 * 16; a.cp_out = cp_out; a.c_off = c_off;
+    // the last operand also clears the row's padding channels (buffers are recycled between tensors)
+    a.words_out = fill_tail ? (cp_out - c_off) / 4 : (C + 3) / 4;
+    const int64_t blocks = (G * a.words_out + kThreads - 1) / kThreads;
+    if (blocks >= 0x7fffffffll) return (int)cudaErrorInvalidValue;
+    regridq8_kernel<<<(unsigned)blocks, kThreads, 0, (cudaStream_t)stream>>>(a);
+    g_launches += 1;
+    return (int)cudaGetLastError();
+}
+
+extern "C" int dfq_pool_q8(const float *x, int64_t ld, int N, int HW, int C, int8_t *y0, const float *out_slot0,
+                           int8_t *y1, const float *out_slot1, void *stream) {
+    if (!x || !y0 || !out_slot0 || (y1 && !out_slot1) || N <= 0 || HW <= 0 || C <= 0 || ld < C)
+        return (int)cudaErrorInvalidValue;
+    const int Cp = (C + 15) / 16 * 16;
+    poolq8_kernel<<<(unsigned)((N * Cp + kThreads - 1) / kThreads), kThreads, 0, (cudaStream_t)stream>>>(
+        x, ld, N, HW, C, Cp, y0, (const RangeSlot *)out_slot0, y1, (const RangeSlot *)out_slot1);
+    g_launches += 1;
+    return (int)cudaGetLastError();
+}

@@ -23,7 +23,7 @@
 extern "C" {
 #endif
 
-#define DFQ_ABI_VERSION 16
+#define DFQ_ABI_VERSION 17
 
 #if defined(__GNUC__)
 #pragma GCC visibility push(default)   /* the library is built with -fvisibility=hidden */
@@ -336,6 +336,27 @@ int dfq_conv_i8_k_host(int C, int kh, int kw);
 int64_t dfq_conv_i8_scratch_bytes(int N, int C, int H, int W);
 int dfq_conv_i8(const DfqConvI8Desc *desc_host, void *stream);
 
+/* The dense k x k convolution of the STATIC-range plan (set_update_stat(False), utils/quantize.py:119-126; the
+ * activation format of dfq_pw_q8 below): x is centred s8 codes [N, H, W, C padded to 16] on the grid in_slot, the output
+ * is written as codes [N, OH, OW, O padded to 16] on the grid(s) of its consumer(s) -- no quantising pre-pass, no fp32
+ * activation in HBM.  wpk / wr / wrt as for dfq_conv_i8 (same packing). */
+typedef struct DfqConvQ8Desc {
+    const int8_t *x;
+    const int8_t *wpk;
+    const float *wr;         /* [O]                                                             */
+    const float *wrt;        /* [kh*kw][O]                                                      */
+    const float *bias;       /* [O] or NULL                                                     */
+    const float *in_slot;    /* {min, max, scale, 0} of the input's grid                        */
+    int8_t *y0;              /* codes on out_slot0's grid                                       */
+    const float *out_slot0;
+    int8_t *y1;              /* NULL, or the same values on a second consumer's grid            */
+    const float *out_slot1;
+    int32_t N, C, H, W, O, OH, OW, kh, kw, stride, pad, dil, relu;
+    float s_w, c_w;
+    int32_t o_cap;
+} DfqConvQ8Desc;
+int dfq_conv_q8(const DfqConvQ8Desc *desc_host, void *stream);
+
 /* ---- (e) static-range W8A8 eval (csrc/q8.cu): QuantMeasure with update_stat == False, utils/quantize.py:119-126 ----
  * Activations are CENTRED s8 CODES (code - 128 of utils/quantize.py:72-74 on the CONSUMER's grid), NHWC, channels
  * padded to a multiple of 16 with zero bytes; a range slot is {min, max, scale, 0} as fp32.  Every producer writes
@@ -369,9 +390,28 @@ typedef struct DfqDwQ8Desc {
     int8_t *y1; const float *out_slot1;
     int32_t N, H, W, C, stride, relu;
     float s_w, c_w;          /* w_hat = s_w * (code_w - 128) + c_w                                       */
+    int32_t pad, dil;        /* padding per side and dilation; both 0 = padding 1, dilation 1            */
+    int32_t pad_code;        /* 0: conv zero padding (a border tap is absent); 1: the padding was F.pad(x) ahead of
+                              * the QuantMeasure (DeepLab's fixed_padding, mobilenet.py of the reference's
+                              * modeling/segmentation/backbone): a border tap is the code of 0.0 on the input grid */
 } DfqDwQ8Desc;
-/* depthwise 3 x 3, padding 1, stride 1 or 2 */
+/* depthwise 3 x 3, stride 1 or 2; the dp4a kernel for padding 1 / dilation 1, a generic one otherwise */
 int dfq_dw_q8(const DfqDwQ8Desc *desc_host, void *stream);
+
+/* ---- data-movement ops of the static-range plan on code tensors (DeepLabV3+: utils/layer_transform.py:98-125) ----
+ * F.interpolate(Q(x), (OH, OW), 'bilinear', align_corners): x codes [N,H,W,Cp] on in_slot's grid; the result leaves as
+ * codes on the consumer grids (y0 / y1) and / or as fp32 NCHW (yf: the network's logits). */
+int dfq_interp_q8(const int8_t *x, const float *in_slot, int N, int C, int H, int W, int OH, int OW, int align_corners,
+                  int8_t *y0, const float *out_slot0, int8_t *y1, const float *out_slot1, float *yf, void *stream);
+/* One operand of torch.cat(dim=1): G pixels x C channels of codes on in_slot's grid (its own QuantMeasure) -> the values
+ * -> codes on the grid(s) of the concatenation's consumer, at channel offset c_off (multiple of 4) of rows cp_out
+ * channels wide.  fill_tail != 0 (last operand): the row's remaining padding channels are cleared too. */
+int dfq_regrid_q8(const int8_t *x, const float *in_slot, int64_t G, int C, int8_t *y0, const float *out_slot0,
+                  int8_t *y1, const float *out_slot1, int cp_out, int c_off, int fill_tail, void *stream);
+/* nn.AdaptiveAvgPool2d(1) of the RAW fp32 tensor (not a patched op: modeling/segmentation/aspp.py:61-64), x [N][HW] rows
+ * of C floats `ld` floats apart (the fp32 side output of dfq_pw_q8) -> codes [N][Cp] on the consumer grids. */
+int dfq_pool_q8(const float *x, int64_t ld, int N, int HW, int C, int8_t *y0, const float *out_slot0, int8_t *y1,
+                const float *out_slot1, void *stream);
 
 typedef struct DfqStemQ8Desc {
     const float *x;          /* [N][3][H][W] fp32 image                                                  */
