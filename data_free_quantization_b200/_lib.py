@@ -116,7 +116,7 @@ class DfqDwQ8Desc(ctypes.Structure):
     _fields_ = [("x", c_void), ("wrow", c_void), ("bias", c_void), ("in_slot", c_void), ("y0", c_void),
                 ("out_slot0", c_void), ("y1", c_void), ("out_slot1", c_void)] + \
                [(k, i32) for k in ("N", "H", "W", "C", "stride", "relu")] + [("s_w", f32), ("c_w", f32)] + \
-               [(k, i32) for k in ("pad", "dil", "pad_code")]
+               [(k, i32) for k in ("pad", "dil")]
 
 
 class DfqConvQ8Desc(ctypes.Structure):
@@ -187,6 +187,7 @@ PROTOTYPES = {
     "dfq_interp_q8": (ctypes.c_int, [c_void, c_void] + [ctypes.c_int] * 7 + [c_void] * 6),
     "dfq_regrid_q8": (ctypes.c_int, [c_void, c_void, i64, ctypes.c_int, c_void, c_void, c_void, c_void, ctypes.c_int,
                                      ctypes.c_int, ctypes.c_int, c_void]),
+    "dfq_pad_q8": (ctypes.c_int, [c_void, c_void] + [ctypes.c_int] * 8 + [c_void, c_void]),
     "dfq_pool_q8": (ctypes.c_int, [c_void, i64, ctypes.c_int, ctypes.c_int, ctypes.c_int, c_void, c_void, c_void, c_void,
                                    c_void]),
     "dfq_quant_plan_host": (ctypes.c_int, [P(DfqQuantDesc), ctypes.c_int, P(i64), P(i64)]),

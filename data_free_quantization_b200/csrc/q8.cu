@@ -327,10 +327,9 @@ __device__ __forceinline__ float small_int_to_float(int v) {      // exact for |
     return __fadd_rn(__int_as_float(0x4B400000 + v), -12582912.0f);
 }
 
-// PADC: the border is not conv zero padding but F.pad(x) AHEAD of the QuantMeasure (DeepLab's fixed_padding,
-// modeling/segmentation/backbone/mobilenet.py): the padded zeros are quantised with the tensor, so a border tap carries
-// the code of 0.0 on the input grid (dequantised: not exactly 0 unless the grid contains it) and counts as in-bound.
-template <int S, bool DUAL, bool PADC = false>
+// a.pad is 1 (the convolution pads with zeros) or 0 (DeepLab: F.pad ran ahead of the QuantMeasure, the padded tensor exists
+// as codes -- dfq_pad_q8 -- and every tap is in bounds).
+template <int S, bool DUAL>
 __global__ void __launch_bounds__(kThreads, 2)
 dwq8_kernel(DwQ8Args a) {
     constexpr int P = DwStrip<S>::value;
@@ -348,12 +347,9 @@ dwq8_kernel(DwQ8Args a) {
     const QuantConsts q0 = consts_from_slot(*a.out_slot[0], 8, 0, 0.f, 0.f);
     QuantConsts q1 = q0;
     if (DUAL) q1 = consts_from_slot(*a.out_slot[1], 8, 0, 0.f, 0.f);
-    const int iy0 = oy * S - 1;
-    const bool rowin[3] = {(unsigned)iy0 < (unsigned)a.H, (unsigned)(iy0 + 1) < (unsigned)a.H,
-                           (unsigned)(iy0 + 2) < (unsigned)a.H};          // the row exists in memory
-    const bool rowok[3] = {PADC || rowin[0], PADC || rowin[1], PADC || rowin[2]};   // the row's taps count
-    uint32_t padw = 0u;
-    if (PADC) padw = pack4(0.0f, 0.0f, 0.0f, 0.0f, consts_from_slot(in, 8, 0, 0.f, 0.f));
+    const int iy0 = oy * S - a.pad;
+    const bool rowok[3] = {(unsigned)iy0 < (unsigned)a.H, (unsigned)(iy0 + 1) < (unsigned)a.H,
+                           (unsigned)(iy0 + 2) < (unsigned)a.H};
     uint32_t wr[3][4];                                            // [row][channel] = (w0, w1, w2, 0) centred s8
 #pragma unroll
     for (int r = 0; r < 3; ++r) {
@@ -394,7 +390,7 @@ dwq8_kernel(DwQ8Args a) {
     const int64_t orow = ((int64_t)n * a.OH + oy) * a.OW;
     const int left = a.C - c0;
     for (int sp = 0; sp < a.strips; ++sp) {
-        const int ox0 = sp * P, ixs = ox0 * S - 1;
+        const int ox0 = sp * P, ixs = ox0 * S - a.pad;
         // 12 input columns x 3 rows (zero words outside the image), transposed per 4-column block
         uint32_t t[3][3][4];                                      // [row][block][channel]: 4 adjacent pixels of a channel
 #pragma unroll
@@ -406,8 +402,8 @@ dwq8_kernel(DwQ8Args a) {
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
                     const int ix = ixs + 4 * blk + q;
-                    p[q] = (rowin[r] && (unsigned)ix < (unsigned)a.W)
-                               ? __ldg(reinterpret_cast<const uint32_t *>(xr + (int64_t)ix * a.Cp)) : padw;
+                    p[q] = (rowok[r] && (unsigned)ix < (unsigned)a.W)
+                               ? __ldg(reinterpret_cast<const uint32_t *>(xr + (int64_t)ix * a.Cp)) : 0u;
                 }
                 const uint32_t a0 = __byte_perm(p[0], p[1], 0x5140), a1 = __byte_perm(p[0], p[1], 0x7362);
                 const uint32_t b0 = __byte_perm(p[2], p[3], 0x5140), b1 = __byte_perm(p[2], p[3], 0x7362);
@@ -435,8 +431,8 @@ dwq8_kernel(DwQ8Args a) {
                     sa[c] = __dp4a((int)win, (int)ones[r], sa[c]);
                 }
             }
-            const int ixl = ox * S - 1;
-            const bool lin = PADC || ixl >= 0, rin = PADC || ixl + 2 < a.W;   // left / right tap column counts (centre always does)
+            const int ixl = ox * S - a.pad;
+            const bool lin = ixl >= 0, rin = ixl + 2 < a.W;      // left / right tap column in bounds (centre always is)
             float yv[4];
 #pragma unroll
             for (int c = 0; c < 4; ++c) {
@@ -456,10 +452,9 @@ dwq8_kernel(DwQ8Args a) {
     }
 }
 
-// Depthwise 3 x 3 with any padding / dilation (DeepLab's dilated blocks: one layer of 960 channels at 33 x 33): one
+// Depthwise 3 x 3 with any zero padding / dilation (DeepLab's dilated block: one layer of 960 channels at 33 x 33): one
 // thread per output pixel and 4-channel word, nine word loads, the same integer sums and the same fp32 expression
 // as dwq8_kernel (bit-identical where both apply), without its strip transposes.
-template <bool PADC>
 __global__ void __launch_bounds__(kThreads)
 dwq8_generic_kernel(DwQ8Args a) {
     const unsigned cw = (unsigned)a.Cp >> 2;
@@ -475,8 +470,6 @@ dwq8_generic_kernel(DwQ8Args a) {
     const float sx = in.scale, cx = __fmaf_rn(128.0f, sx, in.mn);
     const float fa = __fmul_rn(sx, a.s_w), fb = __fmul_rn(sx, a.c_w);
     const float cxsw = __fmul_rn(cx, a.s_w), cxcw = __fmul_rn(cx, a.c_w);
-    uint32_t padw = 0u;
-    if (PADC) padw = pack4(0.0f, 0.0f, 0.0f, 0.0f, consts_from_slot(in, 8, 0, 0.f, 0.f));
     int acc[4] = {0, 0, 0, 0}, sa[4] = {0, 0, 0, 0}, sb[4] = {0, 0, 0, 0}, ninb = 0;
     const int8_t *xn = a.x + (int64_t)n * a.H * a.W * a.Cp + c0;
 #pragma unroll
@@ -487,9 +480,8 @@ dwq8_generic_kernel(DwQ8Args a) {
 #pragma unroll
         for (int j = 0; j < 3; ++j) {
             const int ix = ox * a.stride - a.pad + j * a.dil;
-            const bool mem = (unsigned)iy < (unsigned)a.H && (unsigned)ix < (unsigned)a.W;
-            if (!mem && !PADC) continue;
-            const uint32_t w = mem ? __ldg(reinterpret_cast<const uint32_t *>(xn + ((int64_t)iy * a.W + ix) * a.Cp)) : padw;
+            if (!((unsigned)iy < (unsigned)a.H && (unsigned)ix < (unsigned)a.W)) continue;   // zero padding: tap absent
+            const uint32_t w = __ldg(reinterpret_cast<const uint32_t *>(xn + ((int64_t)iy * a.W + ix) * a.Cp));
             ++ninb;
 #pragma unroll
             for (int c = 0; c < 4; ++c) {
@@ -830,18 +822,16 @@ extern "C" int dfq_dw_q8(const DfqDwQ8Desc *d, void *stream) {
     a.y[0] = d->y0; a.y[1] = d->y1;
     a.N = d->N; a.H = d->H; a.W = d->W; a.C = d->C; a.Cp = (d->C + 15) / 16 * 16; a.stride = d->stride; a.relu = d->relu;
     a.s_w = d->s_w; a.c_w = d->c_w;
-    a.dil = d->dil ? d->dil : 1;                       // 0 = the defaults of the first ABI: padding 1, dilation 1
-    a.pad = (d->pad || d->dil) ? d->pad : 1;
+    a.dil = d->dil > 0 ? d->dil : 1;
+    a.pad = d->pad;
     a.OH = (d->H + 2 * a.pad - 2 * a.dil - 1) / d->stride + 1; a.OW = (d->W + 2 * a.pad - 2 * a.dil - 1) / d->stride + 1;
     if (a.OH <= 0 || a.OW <= 0) return (int)cudaErrorInvalidValue;
     const cudaStream_t st = (cudaStream_t)stream;
-    const bool padc = d->pad_code != 0;
-    if (a.pad != 1 || a.dil != 1) {
+    if (a.pad > 1 || a.dil != 1) {
         const int64_t total = (int64_t)a.N * a.OH * a.OW * (a.Cp / 4);
         const int64_t blocks = (total + kThreads - 1) / kThreads;
         if (blocks >= 0x7fffffffll) return (int)cudaErrorInvalidValue;
-        if (padc) dwq8_generic_kernel<true><<<(unsigned)blocks, kThreads, 0, st>>>(a);
-        else dwq8_generic_kernel<false><<<(unsigned)blocks, kThreads, 0, st>>>(a);
+        dwq8_generic_kernel<<<(unsigned)blocks, kThreads, 0, st>>>(a);
         g_launches += 1;
         return (int)cudaGetLastError();
     }
@@ -850,16 +840,12 @@ extern "C" int dfq_dw_q8(const DfqDwQ8Desc *d, void *stream) {
     const int64_t total = (int64_t)a.N * a.OH * (a.Cp / 4);
     if (total >= 0x7fffffffll) return (int)cudaErrorInvalidValue;
     const unsigned grid = (unsigned)((total + kThreads - 1) / kThreads);
-    const int variant = (d->stride == 2 ? 4 : 0) | (d->y1 ? 2 : 0) | (padc ? 1 : 0);
-    switch (variant) {
-    case 0: dwq8_kernel<1, false, false><<<grid, kThreads, 0, st>>>(a); break;
-    case 1: dwq8_kernel<1, false, true><<<grid, kThreads, 0, st>>>(a); break;
-    case 2: dwq8_kernel<1, true, false><<<grid, kThreads, 0, st>>>(a); break;
-    case 3: dwq8_kernel<1, true, true><<<grid, kThreads, 0, st>>>(a); break;
-    case 4: dwq8_kernel<2, false, false><<<grid, kThreads, 0, st>>>(a); break;
-    case 5: dwq8_kernel<2, false, true><<<grid, kThreads, 0, st>>>(a); break;
-    case 6: dwq8_kernel<2, true, false><<<grid, kThreads, 0, st>>>(a); break;
-    default: dwq8_kernel<2, true, true><<<grid, kThreads, 0, st>>>(a); break;
+    if (d->stride == 1) {
+        if (d->y1) dwq8_kernel<1, true><<<grid, kThreads, 0, st>>>(a);
+        else dwq8_kernel<1, false><<<grid, kThreads, 0, st>>>(a);
+    } else {
+        if (d->y1) dwq8_kernel<2, true><<<grid, kThreads, 0, st>>>(a);
+        else dwq8_kernel<2, false><<<grid, kThreads, 0, st>>>(a);
     }
     g_launches += 1;
     return (int)cudaGetLastError();

@@ -5,6 +5,8 @@
 //   regridq8_kernel  one operand of torch.cat (utils/layer_transform.py:112-125): every operand has its own QuantMeasure,
 //                    the concatenation is quantised again by the consuming convolution's: codes on grid A -> values ->
 //                    codes on grid B, written at the operand's channel offset of the wider NHWC tensor;
+//   padq8_kernel     F.pad ahead of a QuantMeasure (never quantised itself: utils/layer_transform.py ignore_op=['pad']; the
+//                    padded zeros are quantised by the consumer's measure, so the border is code(0.0) on its grid);
 //   poolq8_kernel    nn.AdaptiveAvgPool2d(1) (not a patched op: it sees the RAW fp32 tensor, which the producing 1 x 1
 //                    convolution writes next to its codes) -> codes on the grid of the following convolution.
 // Activation format: centred s8 codes, NHWC, channels padded to 16 with zero bytes (see q8.cu).
@@ -153,6 +155,31 @@ poolq8_kernel(const float *__restrict__ x, int64_t ld, int N, int HW, int C, int
     if (y1) y1[idx] = code1;
 }
 
+// F.pad(x, (l, r, t, b)) AHEAD of a QuantMeasure (DeepLab's fixed_padding): the measure quantises the padded zeros with
+// the tensor, so the border holds the code of 0.0 on that grid.  One thread per output pixel and 16-byte channel chunk.
+__global__ void __launch_bounds__(kThreads)
+padq8_kernel(const int8_t *__restrict__ x, const RangeSlot *slot, int8_t *__restrict__ y, int N, int H, int W, int Cp,
+             int C, int pl, int pt, int OH, int OW) {
+    const int chunks = Cp >> 4;
+    const int64_t idx = (int64_t)blockIdx.x * kThreads + threadIdx.x;
+    if (idx >= (int64_t)N * OH * OW * chunks) return;
+    const int ch = (int)(idx % chunks);
+    int64_t rest = idx / chunks;
+    const int ox = (int)(rest % OW); rest /= OW;
+    const int oy = (int)(rest % OH);
+    const int n = (int)(rest / OH);
+    const int iy = oy - pt, ix = ox - pl;
+    uint4 v;
+    if ((unsigned)iy < (unsigned)H && (unsigned)ix < (unsigned)W) {
+        v = __ldg(reinterpret_cast<const uint4 *>(x + (((int64_t)n * H + iy) * W + ix) * Cp) + ch);
+    } else {
+        const uint32_t w = pack4(0.0f, 0.0f, 0.0f, 0.0f, consts_from_slot(*slot, 8, 0, 0.f, 0.f));
+        const int left = C - 16 * ch;                             // the tensor's padding CHANNELS stay s8 zero
+        v = make_uint4(keep_left(w, left), keep_left(w, left - 4), keep_left(w, left - 8), keep_left(w, left - 12));
+    }
+    reinterpret_cast<uint4 *>(y + (((int64_t)n * OH + oy) * OW + ox) * Cp)[ch] = v;
+}
+
 inline float q8_interp_scale(int in, int out, int align) {
     if (align) return out > 1 ? (float)(in - 1) / (float)(out - 1) : 0.0f;
     return out > 0 ? (float)in / (float)out : 0.0f;
@@ -216,6 +243,19 @@ extern "C" int dfq_pool_q8(const float *x, int64_t ld, int N, int HW, int C, int
     const int Cp = (C + 15) / 16 * 16;
     poolq8_kernel<<<(unsigned)((N * Cp + kThreads - 1) / kThreads), kThreads, 0, (cudaStream_t)stream>>>(
         x, ld, N, HW, C, Cp, y0, (const RangeSlot *)out_slot0, y1, (const RangeSlot *)out_slot1);
+    g_launches += 1;
+    return (int)cudaGetLastError();
+}
+
+extern "C" int dfq_pad_q8(const int8_t *x, const float *slot, int N, int C, int H, int W, int pl, int pr, int pt, int pb,
+                          int8_t *y, void *stream) {
+    if (!x || !slot || !y || N <= 0 || C <= 0 || H <= 0 || W <= 0 || pl < 0 || pr < 0 || pt < 0 || pb < 0)
+        return (int)cudaErrorInvalidValue;
+    const int Cp = (C + 15) / 16 * 16, OH = H + pt + pb, OW = W + pl + pr;
+    const int64_t blocks = ((int64_t)N * OH * OW * (Cp / 16) + kThreads - 1) / kThreads;
+    if (blocks >= 0x7fffffffll) return (int)cudaErrorInvalidValue;
+    padq8_kernel<<<(unsigned)blocks, kThreads, 0, (cudaStream_t)stream>>>(x, (const RangeSlot *)slot, y, N, H, W, Cp, C, pl,
+                                                                         pt, OH, OW);
     g_launches += 1;
     return (int)cudaGetLastError();
 }

@@ -8,10 +8,12 @@ measures' ranges) and stores centred s8 codes, NHWC, channels padded to 16.  The
 classifier read those codes by tensor-map TMA straight into the tcgen05 operand layout.  13.9 MB per image of
 activation traffic for MobileNetV2 instead of 55.8 MB with fp32 activations (eval_plan.py).
 
-Supported graph: what MobileNetV2 traces to -- a dense 3 x 3 stem on the fp32 image, 1 x 1 convolutions, depthwise
-3 x 3 (pad 1, stride 1 / 2), residual adds, the spatial mean, the linear classifier; ReLU fused, BatchNorm already
-merged.  Anything else (DeepLab's pad / interpolate / cat / atrous convolutions) raises NotImplementedError: those run
-on the dynamic-range plan.
+Supported graph: what MobileNetV2 and DeepLabV3+ (MobileNetV2 backbone) trace to -- a dense 3 x 3 stem on the fp32
+image, 1 x 1 convolutions, depthwise 3 x 3 (stride 1 / 2, any dilation; conv zero padding or F.pad ahead of the
+measure, which is folded into the convolution), dense k x k convolutions (atrous ASPP branches, decoder) on tcgen05,
+residual adds, the spatial mean, the global average pool, bilinear interpolation, channel concatenation, the linear
+classifier; ReLU fused, BatchNorm already merged.  A tensor read by several QuantMeasures with bit-identical ranges is
+written once.  Anything else raises NotImplementedError: it runs on the dynamic-range plan (eval_plan.EvalPlan).
 
 Semantics per op are those of the reference with replace_op() in force (utils/layer_transform.py:18-125,
 utils/quantize.py:250-256, 358-363); bits_activation is 8 (the reference's set_layer_bits never changes it).
@@ -121,8 +123,7 @@ class EvalPlanQ8(EvalPlan):
 
     # ------------------------------------------------------------------------------------- buffers + launches
     def _assign(self, steps):
-        dev, N = self.dev, self.N
-        lib, stream = L.lib(), L.stream
+        dev = self.dev
         for qm, _idx, _t in self.measures:
             if qm.update_stat:
                 raise RuntimeError("q8 plan: every QuantMeasure must be in static mode (set_update_stat(False), "
@@ -130,51 +131,130 @@ class EvalPlanQ8(EvalPlan):
             if int(qm.num_bits) != 8:
                 raise NotImplementedError("q8 plan: 8-bit activations only")
         self.refresh_static()
-        cons = {}
+        # F.pad is never quantised itself (utils/layer_transform.py ignore_op): the QuantMeasure of the convolution that
+        # reads the padded tensor quantises the padded zeros with it.  So the producer of x writes x on that measure's
+        # grid, and the pad op copies it into a padded code tensor whose border is code(0.0) on that grid.
+        live = steps
+        slots_in = lambda st: [st[k] for k in ("slot", "slot_a", "slot_b") if st.get(k) is not None] + \
+            list(st.get("slots", ()))
+        ins_of = lambda st: [st[k] for k in ("src", "a", "b") if k in st] + list(st.get("srcs", ()))
+        direct, raw, via_pad = {}, set(), {}
         for _qm, idx, t in self.measures:
-            cons.setdefault(id(t), []).append(idx)
+            direct.setdefault(id(t), []).append(idx)
+        padded = {id(st["out"]) for st in live if st["kind"] == "pad"}
+        for st in live:
+            if st["kind"] == "pad":
+                if id(st["src"]) in padded:
+                    raise NotImplementedError(f"{st['name']}: F.pad of a padded tensor")
+                via_pad.setdefault(id(st["src"]), []).extend(direct.get(id(st["out"]), []))
+            elif st["kind"] == "pool":
+                raw.add(id(st["src"]))
+        # consumers with bit-identical ranges share one code buffer (ASPP: five branches read one tensor on one grid)
+        host = self.slots_host
+        same = lambda i, j: host[i, :2].tobytes() == host[j, :2].tobytes()
+
+        def group(idxs):
+            reps = []
+            for idx in idxs:
+                if not any(same(r, idx) for r in reps):
+                    reps.append(idx)
+            return reps
+        rep_in = lambda reps, idx: next(k for k, r in enumerate(reps) if same(r, idx))
+        step_of_slot = {}
+        for i, st in enumerate(live):
+            for idx in slots_in(st):
+                step_of_slot[idx] = i
+        pad_step = {id(st["out"]): i for i, st in enumerate(live) if st["kind"] == "pad"}
         slot_ptr = lambda i: self.slots[i].data_ptr()
-        # code buffers, one per (tensor, consumer grid); reused once their single reader has run
-        ins_of = lambda st: [st[k] for k in ("src", "a", "b") if k in st]
-        slot_of_in = lambda st: [st[k] for k in ("slot", "slot_a", "slot_b") if st.get(k) is not None]
-        last_read = {}
-        for i, st in enumerate(steps):
-            for idx in slot_of_in(st):
-                last_read[idx] = i
-        pool, self.codes, self.slot_key = {}, {}, {}
+        pool, self.codes, self.pre, self.slot_key = {}, {}, {}, {}
         self.act_bytes = 0
+        self.f32_of = {}
 
         def code_shape(t):
             return (t.shape[0], t.shape[2], t.shape[3], _cp(t.shape[1])) if len(t.shape) == 4 else (t.shape[0], _cp(t.shape[1]))
 
-        def alloc(t, idx):
-            shp = code_shape(t)
-            n = int(np.prod(shp))
+        alive = []                       # [buffer, steps that still have to read it]
+
+        def take(n):
             free = pool.get(n)
             buf = free.pop() if free else torch.zeros(n, dtype=torch.int8, device=dev)
-            self.codes[idx] = buf
             self.act_bytes += n
             return buf
 
+        def retire(i):
+            for ent in alive:
+                ent[1].discard(i)
+            for ent in alive:
+                if not ent[1]:
+                    pool.setdefault(ent[0].numel(), []).append(ent[0])
+            alive[:] = [e for e in alive if e[1]]
+
         def outs_of(t, name):
-            idxs = cons.get(id(t), [])
-            if len(idxs) > 2:
-                raise NotImplementedError(f"{name}: {len(idxs)} quantised consumers (the q8 kernels write two grids)")
-            return idxs
+            """Code buffers for the distinct consumer grids of tensor t: (y0, s0, y1, s1, slots measured on t itself)."""
+            mine, through = direct.get(id(t), []), via_pad.get(id(t), [])
+            reps = group(mine + through)
+            if len(reps) > 2:
+                raise NotImplementedError(f"{name}: {len(reps)} distinct consumer grids (the q8 kernels write two)")
+            n = int(np.prod(code_shape(t)))
+            ents = [[take(n), set()] for _ in reps]
+            for idx in mine:
+                k = rep_in(reps, idx)
+                self.codes[idx] = ents[k][0]
+                ents[k][1].add(step_of_slot[idx])
+            for idx in through:                       # read by the pad op, which writes what the measure's layer reads
+                k = rep_in(reps, idx)
+                self.pre[idx] = ents[k][0]
+                ents[k][1].add(next(i for i, st in enumerate(live) if st["kind"] == "pad" and st["src"] is t
+                                    and idx in direct.get(id(st["out"]), [])))
+            alive.extend(ents)
+            y0 = ents[0][0].data_ptr() if ents else None
+            y1 = ents[1][0].data_ptr() if len(ents) > 1 else None
+            return (y0, slot_ptr(reps[0]) if reps else None, y1, slot_ptr(reps[1]) if len(reps) > 1 else None, list(mine))
+
+        def f32_out(t, shape):
+            buf = torch.empty(*shape, dtype=torch.float32, device=dev)
+            self.f32_of[id(t)] = buf
+            return buf
 
         self.input.buf = torch.empty(*self.input.shape, dtype=torch.float32, device=dev)
         self.keep_q8 = []
         self.step_io = {}
         self.out_of = {}
+        lib, stream = L.lib(), L.stream
         top_i = 0
-        for i, st in enumerate(steps):
+        for i, st in enumerate(live):
             kind, name, out = st["kind"], st["name"], st["out"]
-            oidx = outs_of(out, name)
-            obufs = [alloc(out, idx) for idx in oidx]
-            y0 = obufs[0].data_ptr() if obufs else None
-            y1 = obufs[1].data_ptr() if len(obufs) > 1 else None
-            s0 = slot_ptr(oidx[0]) if oidx else None
-            s1 = slot_ptr(oidx[1]) if len(oidx) > 1 else None
+            is_final = out is self.output
+            io_extra = {}
+            if kind == "pad":
+                src = st["src"]
+                pl, pr, pt, pb = st["pad"]
+                Nn, C, H, W = src.shape
+                oidx = list(direct.get(id(out), []))
+                reps = group(oidx)
+                n = int(np.prod(code_shape(out)))
+                calls = []
+                for r in reps:
+                    ent = [take(n), set()]
+                    for idx in oidx:
+                        if same(r, idx):
+                            self.codes[idx] = ent[0]
+                            ent[1].add(step_of_slot[idx])
+                    alive.append(ent)
+                    calls.append((self.pre[r].data_ptr(), slot_ptr(r), Nn, C, H, W, pl, pr, pt, pb, ent[0].data_ptr()))
+
+                def fn(calls=calls):
+                    for a2 in calls:
+                        L.check(lib.dfq_pad_q8(*a2, stream()), "dfq_pad_q8")
+                kind2 = "pad"
+                io_extra = {"pre_slots": reps, "pad": (pl, pr, pt, pb)}
+                self.ops.append((name, fn))
+                self.out_of[name] = out
+                self.step_io[name] = {"kind": kind2, "in_slots": [], "srcs": [src], "out": out, "out_slots": oidx,
+                                      "relu": 0, "fn": fn, **io_extra}
+                retire(i)
+                continue
+            y0, s0, y1, s1, oidx = outs_of(out, name)
             if kind == "conv":
                 m, src = st["m"], st["src"]
                 kh, kw, s, p, d, g = st["geom"]
@@ -183,36 +263,65 @@ class EvalPlanQ8(EvalPlan):
                 self.slot_key[st["slot"]] = ("L", name)
                 w = m.weight.data
                 b = None if m.bias is None else m.bias.data
-                Nn, C, H, W = src.shape
-                if src is self.input:
-                    if not (kh == 3 and kw == 3 and g == 1 and C == 3 and d == 1 and m.out_channels <= 32 and oidx):
+                padinfo = None
+                rsrc = src
+                Nn, C, H, W = rsrc.shape
+                xcodes = self.codes.get(st["slot"])
+                if rsrc is self.input:
+                    if not (kh == 3 and kw == 3 and g == 1 and C == 3 and d == 1 and m.out_channels <= 32 and y0 is not None
+                            and padinfo is None):
                         raise NotImplementedError(f"{name}: only a dense 3 x 3 stem on 3 channels reads the image")
                     desc = L.DfqStemQ8Desc()
-                    desc.x, desc.w = src.buf.data_ptr(), L.dev_f32(w.contiguous(), "weight")
+                    desc.x, desc.w = rsrc.buf.data_ptr(), L.dev_f32(w.contiguous(), "weight")
                     desc.bias = None if b is None else L.dev_f32(b, "bias")
                     desc.in_slot, desc.y0, desc.out_slot0, desc.y1, desc.out_slot1 = slot_ptr(st["slot"]), y0, s0, y1, s1
                     desc.N, desc.H, desc.W, desc.O, desc.stride, desc.pad, desc.relu = Nn, H, W, m.out_channels, s, p, st["relu"]
                     self.keep_q8.append(desc)
                     fn = (lambda dd: lambda: L.check(lib.dfq_stem_q8(ctypes.byref(dd), stream()), "dfq_stem_q8"))(desc)
                     kind2 = "stem"
-                elif kh == 1 and kw == 1 and g == 1 and s == 1 and p == 0:
-                    fn = self._pw(name, w.reshape(w.shape[0], -1), b, self.codes[st["slot"]], slot_ptr(st["slot"]),
-                                  Nn * H * W, y0, s0, y1, s1, st["relu"], None)
+                elif kh == 1 and kw == 1 and g == 1 and s == 1 and p == 0 and padinfo is None:
+                    yf = None
+                    if is_final or y0 is None:
+                        raise NotImplementedError(f"{name}: a 1 x 1 convolution as the network's output")
+                    if id(out) in raw:
+                        yf = f32_out(out, (Nn * H * W, m.out_channels))      # fp32 NHWC rows next to the codes
+                    fn = self._pw(name, w.reshape(w.shape[0], -1), b, xcodes, slot_ptr(st["slot"]),
+                                  Nn * H * W, y0, s0, y1, s1, st["relu"], yf)
                     kind2 = "pw"
-                elif kh == 3 and kw == 3 and g == C == m.out_channels and p == 1 and d == 1 and s in (1, 2) and oidx:
+                elif kh == 3 and kw == 3 and g == C == m.out_channels and s in (1, 2) and y0 is not None:
+                    if p > d:
+                        raise NotImplementedError(f"{name}: depthwise padding {p} with dilation {d}")
+                    pad_each = p
                     Cp = _cp(C)
                     wrow, dsw, dcw = pack_depthwise(w)
                     bp = torch.zeros(Cp, dtype=torch.float32, device=dev)
                     if b is not None:
                         bp[:C] = b
                     desc = L.DfqDwQ8Desc()
-                    desc.x, desc.wrow, desc.bias = self.codes[st["slot"]].data_ptr(), wrow.data_ptr(), bp.data_ptr()
+                    desc.x, desc.wrow, desc.bias = xcodes.data_ptr(), wrow.data_ptr(), bp.data_ptr()
                     desc.s_w, desc.c_w = dsw, dcw
                     desc.in_slot, desc.y0, desc.out_slot0, desc.y1, desc.out_slot1 = slot_ptr(st["slot"]), y0, s0, y1, s1
                     desc.N, desc.H, desc.W, desc.C, desc.stride, desc.relu = Nn, H, W, C, s, st["relu"]
+                    desc.pad, desc.dil = pad_each, d
                     self.keep_q8 += [wrow, bp, desc]
                     fn = (lambda dd: lambda: L.check(lib.dfq_dw_q8(ctypes.byref(dd), stream()), "dfq_dw_q8"))(desc)
                     kind2 = "dw"
+                elif g == 1 and padinfo is None and y0 is not None:        # dense k x k (ASPP's atrous 3 x 3, the decoder's 3 x 3)
+                    G_out = out.shape[0] * out.shape[2] * out.shape[3]
+                    pk = pw_i8.pack_weight_conv(w, None, o_cap=pw_i8.choose_o_cap(G_out, w.shape[0]))
+                    if pk is None:
+                        raise RuntimeError(f"{name}: weight is not on an integer grid of <= 8 bits")
+                    desc = L.DfqConvQ8Desc()
+                    desc.x, desc.wpk, desc.wr, desc.wrt = xcodes.data_ptr(), pk.wpk.data_ptr(), pk.wr.data_ptr(), pk.wrt.data_ptr()
+                    desc.bias = None if b is None else L.dev_f32(b, "bias")
+                    desc.in_slot, desc.y0, desc.out_slot0, desc.y1, desc.out_slot1 = slot_ptr(st["slot"]), y0, s0, y1, s1
+                    desc.N, desc.C, desc.H, desc.W = Nn, C, H, W
+                    desc.O, desc.OH, desc.OW = out.shape[1], out.shape[2], out.shape[3]
+                    desc.kh, desc.kw, desc.stride, desc.pad, desc.dil, desc.relu = kh, kw, s, p, d, st["relu"]
+                    desc.s_w, desc.c_w, desc.o_cap = pk.s_w, pk.c_w, pk.o_cap
+                    self.keep_q8 += [pk, desc, b]
+                    fn = (lambda dd: lambda: L.check(lib.dfq_conv_q8(ctypes.byref(dd), stream()), "dfq_conv_q8"))(desc)
+                    kind2 = "dense"
                 else:
                     raise NotImplementedError(f"{name}: convolution geometry {st['geom']} is not covered by the q8 plan")
             elif kind == "linear":
@@ -221,18 +330,17 @@ class EvalPlanQ8(EvalPlan):
                     raise NotImplementedError(f"{name}: linear layer without a QuantMeasure")
                 self.slot_key[st["slot"]] = ("L", name)
                 yf = None
-                if out is self.output or not oidx:
-                    out.buf = torch.empty(*out.shape, dtype=torch.float32, device=dev)
-                    yf = out.buf
+                if is_final or y0 is None:
+                    yf = f32_out(out, out.shape)
+                    out.buf = yf
                 fn = self._pw(name, m.weight.data, None if m.bias is None else m.bias.data, self.codes[st["slot"]],
                               slot_ptr(st["slot"]), src.shape[0], y0, s0, y1, s1, st["relu"], yf)
                 kind2 = "linear"
             elif kind == "add":
-                a_, b_ = st["a"], st["b"]
                 self.slot_key[st["slot_a"]] = ("T", top_i, 0)
                 self.slot_key[st["slot_b"]] = ("T", top_i, 1)
                 top_i += 1
-                if not oidx:
+                if y0 is None:
                     raise NotImplementedError(f"{name}: residual add without a quantised consumer")
                 Nn, C, H, W = out.shape
                 args = (self.codes[st["slot_a"]].data_ptr(), self.codes[st["slot_b"]].data_ptr(), slot_ptr(st["slot_a"]),
@@ -245,22 +353,64 @@ class EvalPlanQ8(EvalPlan):
                 top_i += 1
                 Nn, C, H, W = src.shape
                 yf = None
-                if not oidx:
-                    out.buf = torch.empty(*out.shape, dtype=torch.float32, device=dev)
+                if y0 is None:
+                    out.buf = f32_out(out, out.shape)
                     yf = out.buf.data_ptr()
                 args = (self.codes[st["slot"]].data_ptr(), slot_ptr(st["slot"]), y0, s0, yf, Nn, C, H * W)
                 fn = (lambda a2: lambda: L.check(lib.dfq_mean_q8(*a2, stream()), "dfq_mean_q8"))(args)
                 kind2 = "mean"
+            elif kind == "pool":
+                src = st["src"]
+                x32 = self.f32_of.get(id(src))
+                if x32 is None:
+                    raise NotImplementedError(f"{name}: the pooled tensor must come from a 1 x 1 convolution of the plan")
+                if y0 is None:
+                    raise NotImplementedError(f"{name}: global pool without a quantised consumer")
+                Nn, C, H, W = src.shape
+                args = (x32.data_ptr(), C, Nn, H * W, C, y0, s0, y1, s1)
+                fn = (lambda a2: lambda: L.check(lib.dfq_pool_q8(*a2, stream()), "dfq_pool_q8"))(args)
+                kind2 = "pool"
+            elif kind == "interp":
+                src = st["src"]
+                self.slot_key[st["slots"][0]] = ("T", top_i, 0)
+                top_i += 1
+                Nn, C, H, W = src.shape
+                OH, OW = st["size"]
+                yf = None
+                if is_final or y0 is None:
+                    out.buf = f32_out(out, out.shape)               # fp32 NCHW: the network's output
+                    yf = out.buf.data_ptr()
+                args = (self.codes[st["slots"][0]].data_ptr(), slot_ptr(st["slots"][0]), Nn, C, H, W, OH, OW,
+                        1 if st["align"] else 0, y0, s0, y1, s1, yf)
+                fn = (lambda a2: lambda: L.check(lib.dfq_interp_q8(*a2, stream()), "dfq_interp_q8"))(args)
+                kind2 = "interp"
+            elif kind == "cat":
+                if y0 is None:
+                    raise NotImplementedError(f"{name}: concatenation without a quantised consumer")
+                Nn, Ct, H, W = out.shape
+                calls, c_off = [], 0
+                for j, (t, sl) in enumerate(zip(st["srcs"], st["slots"])):
+                    self.slot_key[sl] = ("T", top_i, j)
+                    if c_off % 4:
+                        raise NotImplementedError(f"{name}: operand {j} starts at channel {c_off} (not a multiple of 4)")
+                    calls.append((self.codes[sl].data_ptr(), slot_ptr(sl), Nn * H * W, t.shape[1], y0, s0, y1, s1,
+                                  _cp(Ct), c_off, 1 if j == len(st["srcs"]) - 1 else 0))
+                    c_off += t.shape[1]
+                top_i += 1
+
+                def fn(calls=calls):
+                    for a2 in calls:
+                        L.check(lib.dfq_regrid_q8(*a2, stream()), "dfq_regrid_q8")
+                kind2 = "cat"
             else:
                 raise NotImplementedError(f"{name}: `{kind}` is not covered by the q8 plan (use eval_plan.EvalPlan)")
             self.ops.append((name, fn))
             self.out_of[name] = out
-            self.step_io[name] = {"kind": kind2, "in_slots": slot_of_in(st), "srcs": ins_of(st), "out": out,
+            self.step_io[name] = {"kind": kind2, "in_slots": slots_in(st), "srcs": ins_of(st), "out": out,
                                   "out_slots": oidx, "relu": st.get("relu", 0), "fn": fn}
-            for idx in slot_of_in(st):                      # the codes this step read are dead now
-                if last_read[idx] == i and idx in self.codes:
-                    buf = self.codes[idx]
-                    pool.setdefault(buf.numel(), []).append(buf)
+            retire(i)                                       # code buffers whose last reader this step was
+        if self.output.buf is None:
+            raise NotImplementedError("q8 plan: the network's output is not produced as fp32")
         self.op_info = {n: {"kind": io["kind"]} for n, io in self.step_io.items()}
         self.hbm_bytes = self.act_bytes
 
@@ -282,6 +432,7 @@ class EvalPlanQ8(EvalPlan):
         """(min, max, scale) of every measure from its running range (one device->host copy)."""
         if not self.measures:
             self.slots = torch.zeros(1, 4, dtype=torch.float32, device=self.dev)
+            self.slots_host = np.zeros((1, 4), np.float32)
             return
         rng = torch.stack([torch.cat([qm.running_min.detach().reshape(1), qm.running_max.detach().reshape(1)])
                            for qm, _i, _t in self.measures]).cpu().numpy()
@@ -290,6 +441,7 @@ class EvalPlanQ8(EvalPlan):
         for i, (lo, hi) in enumerate(rng):
             L.lib().dfq_quant_params_host(float(lo), float(hi), 8, 0, ctypes.byref(p))
             host[i] = (lo, hi, p.scale, 0.0)
+        self.slots_host = host
         if getattr(self, "slots", None) is not None and self.slots.shape[0] == host.shape[0]:
             self.slots.copy_(torch.from_numpy(host))
         else:
@@ -312,8 +464,11 @@ class EvalPlanQ8(EvalPlan):
         if image is not None:
             self.input.buf.copy_(image)
         if in_codes is not None:
-            for idx, c in zip(io["in_slots"], in_codes):
-                self.codes[idx].copy_(to_codes_nhwc(c).reshape(-1))
+            # a pad op reads what its producer wrote for the padded tensor's consumers (self.pre), any other op its
+            # measures' code buffers
+            bufs = [self.pre[i] for i in io["pre_slots"]] if io["kind"] == "pad" else [self.codes[i] for i in io["in_slots"]]
+            for buf, c in zip(bufs, in_codes):
+                buf.copy_(to_codes_nhwc(c).reshape(-1))
         io["fn"]()
         res = {idx: from_codes_nhwc(self.codes[idx], io["out"].shape).cpu() for idx in io["out_slots"]}
         if io["out"].buf is not None and io["out"].buf.dtype == torch.float32 and io["out"] is not self.input:

@@ -390,12 +390,9 @@ typedef struct DfqDwQ8Desc {
     int8_t *y1; const float *out_slot1;
     int32_t N, H, W, C, stride, relu;
     float s_w, c_w;          /* w_hat = s_w * (code_w - 128) + c_w                                       */
-    int32_t pad, dil;        /* padding per side and dilation; both 0 = padding 1, dilation 1            */
-    int32_t pad_code;        /* 0: conv zero padding (a border tap is absent); 1: the padding was F.pad(x) ahead of
-                              * the QuantMeasure (DeepLab's fixed_padding, mobilenet.py of the reference's
-                              * modeling/segmentation/backbone): a border tap is the code of 0.0 on the input grid */
+    int32_t pad, dil;        /* zero padding per side (0, 1, ...) and dilation (0 is read as 1)           */
 } DfqDwQ8Desc;
-/* depthwise 3 x 3, stride 1 or 2; the dp4a kernel for padding 1 / dilation 1, a generic one otherwise */
+/* depthwise 3 x 3, stride 1 or 2; the dp4a kernel for padding 0 / 1 with dilation 1, a generic one otherwise */
 int dfq_dw_q8(const DfqDwQ8Desc *desc_host, void *stream);
 
 /* ---- data-movement ops of the static-range plan on code tensors (DeepLabV3+: utils/layer_transform.py:98-125) ----
@@ -408,6 +405,11 @@ int dfq_interp_q8(const int8_t *x, const float *in_slot, int N, int C, int H, in
  * channels wide.  fill_tail != 0 (last operand): the row's remaining padding channels are cleared too. */
 int dfq_regrid_q8(const int8_t *x, const float *in_slot, int64_t G, int C, int8_t *y0, const float *out_slot0,
                   int8_t *y1, const float *out_slot1, int cp_out, int c_off, int fill_tail, void *stream);
+/* F.pad(x, (pl, pr, pt, pb)) ahead of a QuantMeasure (DeepLab's fixed_padding; utils/layer_transform.py ignore_op=['pad']:
+ * the pad itself is not quantised, the consumer's measure quantises the padded tensor): x codes [N,H,W,Cp] on the
+ * consumer's grid `slot` -> y [N,H+pt+pb,W+pl+pr,Cp], border = the code of 0.0 on that grid. */
+int dfq_pad_q8(const int8_t *x, const float *slot, int N, int C, int H, int W, int pl, int pr, int pt, int pb, int8_t *y,
+               void *stream);
 /* nn.AdaptiveAvgPool2d(1) of the RAW fp32 tensor (not a patched op: modeling/segmentation/aspp.py:61-64), x [N][HW] rows
  * of C floats `ld` floats apart (the fp32 side output of dfq_pw_q8) -> codes [N][Cp] on the consumer grids. */
 int dfq_pool_q8(const float *x, int64_t ld, int N, int HW, int C, int8_t *y0, const float *out_slot0, int8_t *y1,

@@ -130,6 +130,7 @@ def test_depthwise_q8(oracle, N, C, H, W, stride, relu, dual):
     if dual:
         d.y1, d.out_slot1 = y1.data_ptr(), s1.data_ptr()
     d.N, d.H, d.W, d.C, d.stride, d.relu = N, H, W, C, stride, relu
+    d.pad, d.dil = 1, 1
     L.check(L.lib().dfq_dw_q8(ctypes.byref(d), L.stream()), "dfq_dw_q8")
     torch.cuda.synchronize()
     for t, (yb, (lo, hi)) in enumerate(zip((y0, y1), ranges)):
@@ -251,6 +252,7 @@ def test_q8_kernels_stay_inside_their_buffers(oracle):
         d.x, d.wrow, d.bias, d.in_slot = x.data_ptr(), wrow.data_ptr(), bp.data_ptr(), in_slot.data_ptr()
         d.y0, d.out_slot0, d.y1, d.out_slot1 = y0.data_ptr(), s0.data_ptr(), y1.data_ptr(), s1.data_ptr()
         d.N, d.H, d.W, d.C, d.stride, d.relu, d.s_w, d.c_w = N, H, W, C, stride, 1, dsw, dcw
+        d.pad, d.dil = 1, 1
         L.check(lib.dfq_dw_q8(ctypes.byref(d), L.stream()), "dfq_dw_q8")
         torch.cuda.synchronize()
         assert intact(b0, N * OH * OW * Cp) and intact(b1, N * OH * OW * Cp), (N, C, H, W, stride)
