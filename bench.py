@@ -500,7 +500,27 @@ def deeplab_section(torch, dev, world):
         replay()
     torch.cuda.synchronize()
     ms = time_steps(torch, replay, 5) / 5
+    # static-range mode (set_update_stat(False), utils/quantize.py:125-126) on the u8 plan: ranges as set_quant_minmax
+    # leaves them (the dynamic forwards above widened the running ranges)
+    from data_free_quantization_b200.eval_q8 import EvalPlanQ8
+    del plan, replay
+    set_quant_minmax(graph, bottoms, verbose=False)
+    for m in model.modules():
+        if hasattr(m, "set_update_stat"):
+            m.set_update_stat(False)
+    plan8 = EvalPlanQ8(model, tr, batch=batch, in_shape=(3, 513, 513))
+    plan8(x)
+    replay8 = plan8.capture()
+    for _ in range(2):
+        replay8()
+    torch.cuda.synchronize()
+    ms8 = time_steps(torch, replay8, 5) / 5
     return {"model": "DeepLabV3+ MobileNetV2, 513x513, W8A8, random-init", "pipeline_ms": round(pipe_ms, 3),
+            "eval_static_ms_per_batch": ms8, "static_plan_ops": len(plan8.ops),
+            "static_activation_code_bytes": int(plan8.act_bytes),
+            "static_path": "static-range mode on u8 codes (eval_q8.py): F.pad / interpolate / cat / global pool on code "
+                           "tensors, dense atrous and decoder 3x3 on tcgen05 with requantising epilogue (dfq_conv_q8), "
+                           "depthwise on dp4a; one CUDA graph",
             "pipeline_scope": "merge_batchnorm .. clip_weight incl. create_relation (43 CLE iterations)",
             "eval_batch_per_gpu": batch, "eval_ms_per_batch": ms, "plan_ops": len(plan.ops),
             "path": "static eval plan as one CUDA graph: dense 3x3 (atrous / decoder) and pointwise on tcgen05, "
@@ -742,6 +762,13 @@ def _main(args):
         deeplab["eval_ms_per_batch"] = round(ms_dl, 3)
         deeplab["eval_images_per_s"] = round(deeplab["eval_batch_per_gpu"] * world / (ms_dl * 1e-3), 1)
         deeplab["eval_scaling"] = "strong (16 images split across the ranks)"
+        ms_s = deeplab.pop("eval_static_ms_per_batch")
+        if world > 1:
+            t = torch.tensor([ms_s], device=dev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms_s = float(t[0])
+        deeplab["eval_static_ms_per_batch"] = round(ms_s, 3)
+        deeplab["eval_static_images_per_s"] = round(deeplab["eval_batch_per_gpu"] * world / (ms_s * 1e-3), 1)
     sharded = None
     if not args.no_micro:
         with quiet:

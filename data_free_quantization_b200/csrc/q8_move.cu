@@ -51,14 +51,15 @@ __device__ __forceinline__ void interp_word(const InterpQ8Args &a, const int8_t 
     }
 }
 
-// codes out: one thread per (pixel, channel word), channel words fastest (coalesced code loads and stores)
+// codes out: one thread per (pixel, 16-channel chunk), chunks fastest: four 128-bit corner loads, one 128-bit store per
+// grid, the indices and weights computed once per 16 channels
 __global__ void __launch_bounds__(kThreads)
 interpq8_codes_kernel(InterpQ8Args a) {
-    const int cw = a.Cp >> 2;
+    const int chunks = a.Cp >> 4;
     const int64_t idx = (int64_t)blockIdx.x * kThreads + threadIdx.x;
-    if (idx >= (int64_t)a.N * a.OH * a.OW * cw) return;
-    const int cwi = (int)(idx % cw);
-    int64_t rest = idx / cw;
+    if (idx >= (int64_t)a.N * a.OH * a.OW * chunks) return;
+    const int ch = (int)(idx % chunks);
+    int64_t rest = idx / chunks;
     const int ox = (int)(rest % a.OW); rest /= a.OW;
     const int oy = (int)(rest % a.OH);
     const int n = (int)(rest / a.OH);
@@ -66,16 +67,36 @@ interpq8_codes_kernel(InterpQ8Args a) {
     q8_interp_index(oy, a.sy, a.H, a.align, y0, y1, l1y);
     q8_interp_index(ox, a.sx, a.W, a.align, x0, x1, l1x);
     const RangeSlot in = *a.in_slot;
-    float v[4];
-    interp_word(a, a.x + (int64_t)n * a.H * a.W * a.Cp, cwi, y0, y1, l1y, x0, x1, l1x, in.scale, in.mn, v);
-    const int64_t off = (((int64_t)n * a.OH + oy) * a.OW + ox) * a.Cp + 4 * cwi;
-    const int left = a.C - 4 * cwi;
-    uint32_t w[1];
-    pack_codes<4>(v, consts_from_slot(*a.out_slot[0], 8, 0, 0.f, 0.f), w);
-    *reinterpret_cast<uint32_t *>(a.y[0] + off) = keep_left(w[0], left);
-    if (a.y[1]) {
-        pack_codes<4>(v, consts_from_slot(*a.out_slot[1], 8, 0, 0.f, 0.f), w);
-        *reinterpret_cast<uint32_t *>(a.y[1] + off) = keep_left(w[0], left);
+    const int8_t *xn = a.x + (int64_t)n * a.H * a.W * a.Cp;
+    const int64_t rs = (int64_t)a.W * a.Cp;
+    const uint4 q00 = __ldg(reinterpret_cast<const uint4 *>(xn + y0 * rs + (int64_t)x0 * a.Cp) + ch);
+    const uint4 q01 = __ldg(reinterpret_cast<const uint4 *>(xn + y0 * rs + (int64_t)x1 * a.Cp) + ch);
+    const uint4 q10 = __ldg(reinterpret_cast<const uint4 *>(xn + y1 * rs + (int64_t)x0 * a.Cp) + ch);
+    const uint4 q11 = __ldg(reinterpret_cast<const uint4 *>(xn + y1 * rs + (int64_t)x1 * a.Cp) + ch);
+    const uint32_t w00[4] = {q00.x, q00.y, q00.z, q00.w}, w01[4] = {q01.x, q01.y, q01.z, q01.w};
+    const uint32_t w10[4] = {q10.x, q10.y, q10.z, q10.w}, w11[4] = {q11.x, q11.y, q11.z, q11.w};
+    const float l0x = __fsub_rn(1.0f, l1x), l0y = __fsub_rn(1.0f, l1y);
+    float v[16];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        float a00[4], a01[4], a10[4], a11[4];
+        dequant4(w00[k], in.scale, in.mn, a00); dequant4(w01[k], in.scale, in.mn, a01);
+        dequant4(w10[k], in.scale, in.mn, a10); dequant4(w11[k], in.scale, in.mn, a11);
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            const float top = __fadd_rn(__fmul_rn(l0x, a00[c]), __fmul_rn(l1x, a01[c]));
+            const float bot = __fadd_rn(__fmul_rn(l0x, a10[c]), __fmul_rn(l1x, a11[c]));
+            v[4 * k + c] = __fadd_rn(__fmul_rn(l0y, top), __fmul_rn(l1y, bot));
+        }
+    }
+    const int64_t off = (((int64_t)n * a.OH + oy) * a.OW + ox) * a.Cp + 16 * ch;
+    const int left = a.C - 16 * ch;
+    for (int gi = 0; gi < 2; ++gi) {
+        if (!a.y[gi]) break;
+        uint32_t w[4];
+        pack_codes<16>(v, consts_from_slot(*a.out_slot[gi], 8, 0, 0.f, 0.f), w);
+        *reinterpret_cast<uint4 *>(a.y[gi] + off) = make_uint4(keep_left(w[0], left), keep_left(w[1], left - 4),
+                                                               keep_left(w[2], left - 8), keep_left(w[3], left - 12));
     }
 }
 
@@ -135,24 +156,35 @@ regridq8_kernel(RegridQ8Args a) {
     if (a.y[1]) *reinterpret_cast<uint32_t *>(a.y[1] + off) = w1;
 }
 
-// mean over the HW rows of x[n] ([HW][C] fp32, rows `ld` floats apart): thread per (n, channel), fp64 accumulation
+// mean over the HW rows of x[n] ([HW][C] fp32, rows `ld` floats apart): a block per (n, 32 channels), lanes on channels
+// (coalesced 128-byte row segments), warps striding the rows; fp64 accumulation, fixed combination order
 __global__ void __launch_bounds__(kThreads)
 poolq8_kernel(const float *__restrict__ x, int64_t ld, int N, int HW, int C, int Cp, int8_t *y0, const RangeSlot *s0,
               int8_t *y1, const RangeSlot *s1) {
-    const int idx = blockIdx.x * kThreads + threadIdx.x;
-    if (idx >= N * Cp) return;
-    const int c = idx % Cp, n = idx / Cp;
-    int8_t code0 = 0, code1 = 0;
+    __shared__ double part[kWarps][32];
+    const int groups = (Cp + 31) >> 5;
+    const int n = blockIdx.x / groups, c = (blockIdx.x % groups) * 32 + (threadIdx.x & 31);
+    const int warp = threadIdx.x >> 5;
+    double acc = 0.0;
     if (c < C) {
         const float *p = x + (int64_t)n * HW * ld + c;
-        double acc = 0.0;
-        for (int i = 0; i < HW; ++i) acc += (double)__ldg(p + (int64_t)i * ld);
-        const float m = (float)(acc / (double)HW);
-        code0 = (int8_t)(pack4(m, m, m, m, consts_from_slot(*s0, 8, 0, 0.f, 0.f)) & 0xffu);
-        if (y1) code1 = (int8_t)(pack4(m, m, m, m, consts_from_slot(*s1, 8, 0, 0.f, 0.f)) & 0xffu);
+        for (int i = warp; i < HW; i += kWarps) acc += (double)__ldg(p + (int64_t)i * ld);
     }
-    y0[idx] = code0;
-    if (y1) y1[idx] = code1;
+    part[warp][threadIdx.x & 31] = acc;
+    __syncthreads();
+    if (warp == 0 && c < Cp) {
+        int8_t code0 = 0, code1 = 0;
+        if (c < C) {
+            double t = 0.0;
+#pragma unroll
+            for (int w = 0; w < kWarps; ++w) t += part[w][threadIdx.x];
+            const float m = (float)(t / (double)HW);
+            code0 = (int8_t)(pack4(m, m, m, m, consts_from_slot(*s0, 8, 0, 0.f, 0.f)) & 0xffu);
+            if (y1) code1 = (int8_t)(pack4(m, m, m, m, consts_from_slot(*s1, 8, 0, 0.f, 0.f)) & 0xffu);
+        }
+        y0[n * Cp + c] = code0;
+        if (y1) y1[n * Cp + c] = code1;
+    }
 }
 
 // F.pad(x, (l, r, t, b)) AHEAD of a QuantMeasure (DeepLab's fixed_padding): the measure quantises the padded zeros with
@@ -204,7 +236,7 @@ extern "C" int dfq_interp_q8(const int8_t *x, const float *in_slot, int N, int C
     a.sy = q8_interp_scale(H, OH, a.align); a.sx = q8_interp_scale(W, OW, a.align);
     const cudaStream_t st = (cudaStream_t)stream;
     if (y0) {
-        const int64_t blocks = ((int64_t)N * OH * OW * (a.Cp / 4) + kThreads - 1) / kThreads;
+        const int64_t blocks = ((int64_t)N * OH * OW * (a.Cp / 16) + kThreads - 1) / kThreads;
         if (blocks >= 0x7fffffffll) return (int)cudaErrorInvalidValue;
         interpq8_codes_kernel<<<(unsigned)blocks, kThreads, 0, st>>>(a);
         g_launches += 1;
@@ -241,7 +273,7 @@ extern "C" int dfq_pool_q8(const float *x, int64_t ld, int N, int HW, int C, int
     if (!x || !y0 || !out_slot0 || (y1 && !out_slot1) || N <= 0 || HW <= 0 || C <= 0 || ld < C)
         return (int)cudaErrorInvalidValue;
     const int Cp = (C + 15) / 16 * 16;
-    poolq8_kernel<<<(unsigned)((N * Cp + kThreads - 1) / kThreads), kThreads, 0, (cudaStream_t)stream>>>(
+    poolq8_kernel<<<(unsigned)(N * ((Cp + 31) / 32)), kThreads, 0, (cudaStream_t)stream>>>(
         x, ld, N, HW, C, Cp, y0, (const RangeSlot *)out_slot0, y1, (const RangeSlot *)out_slot1);
     g_launches += 1;
     return (int)cudaGetLastError();
