@@ -503,6 +503,7 @@ def deeplab_section(torch, dev, world):
     # static-range mode (set_update_stat(False), utils/quantize.py:125-126) on the u8 plan: ranges as set_quant_minmax
     # leaves them (the dynamic forwards above widened the running ranges)
     from data_free_quantization_b200.eval_q8 import EvalPlanQ8
+    n_ops = len(plan.ops)
     del plan, replay
     set_quant_minmax(graph, bottoms, verbose=False)
     for m in model.modules():
@@ -522,7 +523,7 @@ def deeplab_section(torch, dev, world):
                            "tensors, dense atrous and decoder 3x3 on tcgen05 with requantising epilogue (dfq_conv_q8), "
                            "depthwise on dp4a; one CUDA graph",
             "pipeline_scope": "merge_batchnorm .. clip_weight incl. create_relation (43 CLE iterations)",
-            "eval_batch_per_gpu": batch, "eval_ms_per_batch": ms, "plan_ops": len(plan.ops),
+            "eval_batch_per_gpu": batch, "eval_ms_per_batch": ms, "plan_ops": n_ops,
             "path": "static eval plan as one CUDA graph: dense 3x3 (atrous / decoder) and pointwise on tcgen05, "
                     "depthwise on CUDA cores, pad / pool / interpolate / cat as plan ops"}
 
