@@ -265,8 +265,8 @@ def main(argv=None):
     print(f"DFQ pipeline total: {sum(v for v in timings.values() if isinstance(v, float)):.3f} ms")
     model.eval()
     if args.static:
-        if not args.quantize or args.task != 'cls':
-            raise SystemExit("--static needs --quantize and --task cls (the u8 pipeline covers MobileNetV2's graph)")
+        if not args.quantize:
+            raise SystemExit("--static needs --quantize (the u8 pipeline runs the quantised eval forward)")
         for m in model.modules():
             if hasattr(m, "set_update_stat"):
                 m.set_update_stat(False)
