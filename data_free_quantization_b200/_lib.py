@@ -123,7 +123,7 @@ class DfqConvQ8Desc(ctypes.Structure):
     _fields_ = [("x", c_void), ("wpk", c_void), ("wr", c_void), ("wrt", c_void), ("bias", c_void), ("in_slot", c_void),
                 ("y0", c_void), ("out_slot0", c_void), ("y1", c_void), ("out_slot1", c_void)] + \
                [(k, i32) for k in ("N", "C", "H", "W", "O", "OH", "OW", "kh", "kw", "stride", "pad", "dil", "relu")] + \
-               [("s_w", f32), ("c_w", f32), ("o_cap", i32)]
+               [("s_w", f32), ("c_w", f32), ("o_cap", i32), ("tma", i32)]
 
 
 class DfqStemQ8Desc(ctypes.Structure):
@@ -133,7 +133,7 @@ class DfqStemQ8Desc(ctypes.Structure):
 
 
 Q_SYMMETRIC, Q_RANGE_F32, Q_PER_CHANNEL, Q_CLAMP_OUT = 1, 2, 4, 8
-ABI_VERSION = 17
+ABI_VERSION = 18
 
 # every symbol include/dfq_b200.h declares: (restype, argtypes)
 P = ctypes.POINTER
@@ -184,6 +184,8 @@ PROTOTYPES = {
                                   c_void]),
     "dfq_mean_q8": (ctypes.c_int, [c_void, c_void, c_void, c_void, c_void, i64, ctypes.c_int, ctypes.c_int, c_void]),
     "dfq_conv_q8": (ctypes.c_int, [P(DfqConvQ8Desc), c_void]),
+    "dfq_conv_q8_plan_host": (ctypes.c_int, [ctypes.c_int] * 4 + [P(ctypes.c_int), P(i64)]),
+    "dfq_conv_q8_pack_host": (ctypes.c_int, [c_void] + [ctypes.c_int] * 4 + [c_void]),
     "dfq_interp_q8": (ctypes.c_int, [c_void, c_void] + [ctypes.c_int] * 7 + [c_void] * 6),
     "dfq_regrid_q8": (ctypes.c_int, [c_void, c_void, i64, ctypes.c_int, c_void, c_void, c_void, c_void, ctypes.c_int,
                                      ctypes.c_int, ctypes.c_int, c_void]),

@@ -21,6 +21,7 @@
 //   addq8_kernel  residual add of two code tensors on different grids (utils/layer_transform.py:18-32).
 //   meanq8_kernel spatial mean (utils/layer_transform.py:79-95) feeding the classifier's grid.
 #include <cuda.h>
+#include <vector>
 #include "common.cuh"
 #include "q8_pack.cuh"
 
@@ -41,6 +42,11 @@ struct PwQ8Args {
     int64_t G, tiles;
     int K, Kp, O, relu, n_pass, o_per_pass, npass, slabs, tmem_cols, stages;
     float s_w, c_w;
+    // dense k x k form (CONV): a tile is a BH x BW patch (= 128 pixels) of one image's output; the K loop runs tap-major
+    // over `taps` x `cslabs` 128-byte channel slabs, each one 4-D TMA box of the code tensor shifted by the tap's offset
+    // (out-of-image pixels arrive as zero bytes).  K above = taps * C (real reduction length).
+    const float *wrt;                 // [taps][O] s_w * (sum over channels of the centred weight codes of one tap)
+    int N, C, Cp, H, W, OH, OW, kh, kw, pad, dil, taps, cslabs, BW, BH, tiles_x, tiles_y;
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -71,6 +77,11 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void *src, uint32_t
 __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap *map, int c0, int c1, uint32_t bar) {
     asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
                  ::"r"(dst), "l"(map), "r"(c0), "r"(c1), "r"(bar) : "memory");
+}
+__device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap *map, int c0, int c1, int c2, int c3,
+                                            uint32_t bar) {
+    asm volatile("cp.async.bulk.tensor.4d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4, %5}], [%6];"
+                 ::"r"(dst), "l"(map), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(bar) : "memory");
 }
 // K-major operand, SWIZZLE_128B: rows of 128 bytes, 8-row groups 1024 bytes apart (SBO), 16-byte chunks XOR-swizzled
 // by the row -- what the TMA writes for a {128 B, 128 rows} box.  The K offset of an MMA goes into the start address.
@@ -116,6 +127,7 @@ template <> struct TmemLd<16> {
 struct EpiCtx {
     const PwQ8Args *a; const float *chan_c; uint32_t tbase; int64_t g; int o0, n_real, half; bool valid, small_acc;
     float fa, fr, floor_v;
+    uint32_t oob; const float *tap_c;      // CONV: taps of this pixel that fell in the zero padding, and what each stands for
 };
 
 // One accumulator row (this thread's pixel) of one tile: units of U columns alternate between the two warps of the
@@ -133,7 +145,21 @@ __device__ __forceinline__ void epi_tile(const EpiCtx &e, const QuantConsts &q0,
     for (; unit * U < e.n_real; unit += 2) {
         const int nv = min(U, e.n_real - unit * U);                          // warp-uniform
         float yv[U];
-        if (e.small_acc) {       // |acc| <= K * 2^14 < 2^22: exact conversion on the full-rate pipes (I2F is 1/4 rate)
+        if (e.oob) {             // CONV, border pixel: zero padding is an exact 0.0 in the reference (the tap is absent),
+                                 // while the s8 zero the TMA filled in stands for c_x: take that back out, tap by tap
+            float corr[U];
+#pragma unroll
+            for (int j = 0; j < U; ++j) corr[j] = 0.0f;
+            for (uint32_t mm = e.oob; mm; mm &= mm - 1) {
+                const float *tc = e.tap_c + (__ffs(mm) - 1) * a.npass + unit * U;
+#pragma unroll
+                for (int j = 0; j < U; ++j) corr[j] = __fadd_rn(corr[j], tc[j]);
+            }
+#pragma unroll
+            for (int j = 0; j < U; ++j)
+                yv[j] = fmaxf(__fmaf_rn(e.fa, (float)(int)d[j],
+                                        __fsub_rn(__fadd_rn(row_c, e.chan_c[unit * U + j]), corr[j])), e.floor_v);
+        } else if (e.small_acc) {       // |acc| <= K * 2^14 < 2^22: exact conversion on the full-rate pipes (I2F is 1/4 rate)
 #pragma unroll
             for (int j = 0; j < U; ++j)
                 yv[j] = fmaxf(__fmaf_rn(e.fa, __fadd_rn(__int_as_float(0x4B400000 + (int)d[j]), -12582912.0f),
@@ -179,6 +205,7 @@ __device__ __forceinline__ void epi_tile(const EpiCtx &e, const QuantConsts &q0,
     }
 }
 
+template <bool CONV>
 __global__ void __launch_bounds__(kQThreads, 2)
 pwq8_kernel(const __grid_constant__ CUtensorMap tmA, PwQ8Args a) {
     extern __shared__ uint8_t smem_raw[];
@@ -220,6 +247,15 @@ pwq8_kernel(const __grid_constant__ CUtensorMap tmA, PwQ8Args a) {
         }
         chan_c[tid] = c;
     }
+    // CONV: what one out-of-bounds tap contributed through c_x, per output channel of this pass
+    float *tap_c = reinterpret_cast<float *>(smem + (size_t)a.stages * (kQASlab + bslab));
+    if (CONV) {
+        const float ccw = __fmul_rn(__fmul_rn((float)a.C, a.c_w), cx);
+        for (int i = tid; i < a.taps * a.npass; i += kQThreads) {
+            const int t = i / a.npass, ol = i - t * a.npass;
+            tap_c[i] = ol < n_real ? __fmaf_rn(cx, __ldg(a.wrt + (int64_t)t * a.O + o0 + ol), ccw) : 0.0f;
+        }
+    }
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
@@ -231,9 +267,23 @@ pwq8_kernel(const __grid_constant__ CUtensorMap tmA, PwQ8Args a) {
             const int8_t *wsrc = a.wpk + (int64_t)pass * a.slabs * bslab;
             int stage = 0; uint32_t phase = 0;
             for (int64_t tile = tile0; tile < a.tiles; tile += tstep) {
+                int tn = 0, oh0 = 0, ow0 = 0;
+                if (CONV) {
+                    const int per = a.tiles_x * a.tiles_y;
+                    tn = (int)(tile / per);
+                    const int r = (int)(tile - (int64_t)tn * per);
+                    oh0 = (r / a.tiles_x) * a.BH; ow0 = (r % a.tiles_x) * a.BW;
+                }
+                int tap = 0, cs = 0;
                 for (int s = 0; s < a.slabs; ++s) {
                     mbar_wait(empty0 + 8 * stage, phase ^ 1);
                     mbar_expect_tx(full0 + 8 * stage, kQASlab + bslab);
+                    if (CONV) {
+                        const int ti = tap / a.kw, tj = tap - ti * a.kw;
+                        tma_load_4d(sA_u + stage * kQASlab, &tmA, cs * kQSlab, ow0 + tj * a.dil - a.pad,
+                                    oh0 + ti * a.dil - a.pad, tn, full0 + 8 * stage);
+                        if (++cs == a.cslabs) { cs = 0; ++tap; }
+                    } else
                     tma_load_2d(sA_u + stage * kQASlab, &tmA, s * kQSlab, (int)(tile * kQM), full0 + 8 * stage);
                     bulk_g2s(sB_u + stage * bslab, wsrc + (int64_t)s * bslab, bslab, full0 + 8 * stage);
                     if (++stage == a.stages) { stage = 0; phase ^= 1; }
@@ -255,7 +305,7 @@ pwq8_kernel(const __grid_constant__ CUtensorMap tmA, PwQ8Args a) {
                 for (int s = 0; s < a.slabs; ++s) {
                     mbar_wait(full0 + 8 * stage, phase);
                     tc_fence_after();
-                    const int kb = min(kQSlab, a.Kp - s * kQSlab);
+                    const int kb = CONV ? min(kQSlab, a.Cp - (s % a.cslabs) * kQSlab) : min(kQSlab, a.Kp - s * kQSlab);
                     const int nk = (kb + 31) >> 5;
                     for (int kk = 0; kk < nk; ++kk) {
                         const uint64_t ad = desc_sw128(sA_u + stage * kQASlab + kk * 32);
@@ -279,15 +329,29 @@ pwq8_kernel(const __grid_constant__ CUtensorMap tmA, PwQ8Args a) {
         if (has1) q1 = consts_from_slot(*a.out_slot[1], 8, 0, 0.f, 0.f);
         const float fa = __fmul_rn(sx, a.s_w), fr = __fmul_rn(sx, a.c_w);
         const float floor_v = a.relu ? 0.0f : -INFINITY;
-        const bool small_acc = a.Kp <= 255;
+        const bool small_acc = !CONV && a.Kp <= 255;
         int acc = 0; uint32_t aphase = 0;
         for (int64_t tile = tile0; tile < a.tiles; tile += tstep) {
-            const int64_t g = tile * kQM + row;
-            const bool valid = g < a.G;
+            int64_t g = tile * kQM + row;
+            bool valid = g < a.G;
+            uint32_t oob = 0;
+            if (CONV) {
+                const int per = a.tiles_x * a.tiles_y;
+                const int tn = (int)(tile / per);
+                const int r = (int)(tile - (int64_t)tn * per);
+                const int oh = (r / a.tiles_x) * a.BH + row / a.BW, ow = (r % a.tiles_x) * a.BW + row % a.BW;
+                valid = oh < a.OH && ow < a.OW;
+                g = ((int64_t)tn * a.OH + oh) * a.OW + ow;
+                for (int t = 0; t < a.taps; ++t) {
+                    const int ih = oh + (t / a.kw) * a.dil - a.pad, iw = ow + (t % a.kw) * a.dil - a.pad;
+                    if (!((unsigned)ih < (unsigned)a.H && (unsigned)iw < (unsigned)a.W)) oob |= 1u << t;
+                }
+                if (!valid) oob = 0;
+            }
             mbar_wait(tfull0 + 8 * acc, aphase);
             tc_fence_after();
             const uint32_t tbase = tmem + ((uint32_t)(32 * lg) << 16) + (uint32_t)(acc * a.npass);
-            const EpiCtx ctx = {&a, chan_c, tbase, g, o0, n_real, half, valid, small_acc, fa, fr, floor_v};
+            const EpiCtx ctx = {&a, chan_c, tbase, g, o0, n_real, half, valid, small_acc, fa, fr, floor_v, oob, tap_c};
             if (n_real <= 16) epi_tile<8>(ctx, q0, q1);      // a 16-channel layer keeps all eight epilogue warps busy
             else epi_tile<16>(ctx, q0, q1);
             tc_fence_before();
@@ -783,7 +847,7 @@ extern "C" int dfq_pw_q8(const DfqPwQ8Desc *d, void *stream) {
     }
     static size_t configured = 0;
     if (configured < smem) {
-        cudaError_t ce = cudaFuncSetAttribute(pwq8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_cap);
+        cudaError_t ce = cudaFuncSetAttribute(pwq8_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_cap);
         if (ce != cudaSuccess) return (int)ce;
         configured = smem_cap;
     }
@@ -799,7 +863,7 @@ extern "C" int dfq_pw_q8(const DfqPwQ8Desc *d, void *stream) {
                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return (int)cudaErrorInvalidValue;
     int occ = 0;
-    cudaError_t ce = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, pwq8_kernel, kQThreads, smem);
+    cudaError_t ce = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, pwq8_kernel<false>, kQThreads, smem);
     if (ce != cudaSuccess) return (int)ce;
     if (occ < 1) return (int)cudaErrorLaunchOutOfResources;
     if (occ > want_ctas) occ = want_ctas;
@@ -807,10 +871,109 @@ extern "C" int dfq_pw_q8(const DfqPwQ8Desc *d, void *stream) {
     if (per_pass < 1) per_pass = 1;
     if (per_pass > a.tiles) per_pass = a.tiles;
     const unsigned grid = (unsigned)(per_pass * a.n_pass);
-    pwq8_kernel<<<grid, kQThreads, smem, (cudaStream_t)stream>>>(tm, a);
+    pwq8_kernel<false><<<grid, kQThreads, smem, (cudaStream_t)stream>>>(tm, a);
     g_launches += 1;
     return (int)cudaGetLastError();
 }
+
+// ---- dense k x k on the same pipeline (stride 1) ------------------------------------------------------------------
+// Packed reduction order: tap-major, then 128-byte channel slabs (channels zero-padded to a multiple of 128 per tap), so
+// that one ring stage = one TMA box of one tap.
+extern "C" int dfq_conv_q8_plan_host(int O, int C, int taps, int o_cap, int *kq, int64_t *packed_bytes) {
+    if (O <= 0 || C <= 0 || taps <= 0 || taps > 25) return (int)cudaErrorInvalidValue;
+    const int Cp = (C + 15) / 16 * 16, cslabs = (Cp + kQSlab - 1) / kQSlab;
+    *kq = taps * cslabs * kQSlab;
+    int np, opp, npass, slabs;
+    return q8_plan(O, *kq, o_cap, &np, &opp, &npass, &slabs, packed_bytes);
+}
+
+// codes: [O][taps][C padded to 16] centred weight codes
+extern "C" int dfq_conv_q8_pack_host(const int8_t *codes, int O, int C, int taps, int o_cap, int8_t *packed) {
+    int kq; int64_t bytes;
+    int e = dfq_conv_q8_plan_host(O, C, taps, o_cap, &kq, &bytes);
+    if (e) return e;
+    const int Cp = (C + 15) / 16 * 16, per_tap = kq / taps;
+    std::vector<int8_t> lay((size_t)O * kq, 0);
+    for (int o = 0; o < O; ++o)
+        for (int t = 0; t < taps; ++t)
+            for (int c = 0; c < Cp; ++c)
+                lay[((size_t)o * taps + t) * per_tap + c] = codes[((size_t)o * taps + t) * Cp + c];
+    return dfq_pw_q8_pack_host(lay.data(), O, kq, o_cap, packed);
+}
+
+namespace dfq {
+int conv_q8_tma(const DfqConvQ8Desc *d, void *stream) {
+    PwQ8Args a = {};
+    a.taps = d->kh * d->kw;
+    a.C = d->C; a.Cp = (d->C + 15) / 16 * 16; a.cslabs = (a.Cp + kQSlab - 1) / kQSlab;
+    const int kq = a.taps * a.cslabs * kQSlab;
+    int64_t bytes;
+    int e = q8_plan(d->O, kq, d->o_cap, &a.n_pass, &a.o_per_pass, &a.npass, &a.slabs, &bytes);
+    if (e) return e;
+    if (a.slabs != a.taps * a.cslabs || a.taps > 25) return (int)cudaErrorInvalidValue;
+    a.wpk = d->wpk; a.wr = d->wr; a.wrt = d->wrt; a.bias = d->bias; a.in_slot = (const RangeSlot *)d->in_slot;
+    a.out_slot[0] = (const RangeSlot *)d->out_slot0; a.out_slot[1] = (const RangeSlot *)d->out_slot1;
+    a.y[0] = d->y0; a.y[1] = d->y1; a.cp_out = (d->O + 15) / 16 * 16;
+    a.K = a.taps * d->C; a.Kp = kq; a.O = d->O; a.relu = d->relu; a.s_w = d->s_w; a.c_w = d->c_w;
+    a.N = d->N; a.H = d->H; a.W = d->W; a.OH = d->OH; a.OW = d->OW; a.kh = d->kh; a.kw = d->kw; a.pad = d->pad; a.dil = d->dil;
+    // the 128-pixel tile as a BH x BW patch: the shape that wastes the fewest pixels past the image's edges
+    int64_t best = -1;
+    for (int bw = 128; bw >= 8; bw >>= 1) {
+        const int bh = 128 / bw;
+        const int64_t t = (int64_t)((d->OW + bw - 1) / bw) * ((d->OH + bh - 1) / bh);
+        if (best < 0 || t < best) { best = t; a.BW = bw; a.BH = bh; }
+    }
+    a.tiles_x = (d->OW + a.BW - 1) / a.BW; a.tiles_y = (d->OH + a.BH - 1) / a.BH;
+    a.tiles = (int64_t)d->N * a.tiles_x * a.tiles_y;
+    a.G = (int64_t)d->N * d->OH * d->OW;
+    if (a.tiles > 0x7fffffffll) return (int)cudaErrorInvalidValue;
+    a.tmem_cols = 32;
+    while (a.tmem_cols < 2 * a.npass) a.tmem_cols *= 2;
+    if (a.tmem_cols > 512) return (int)cudaErrorInvalidValue;
+    const size_t stage_bytes = (size_t)kQASlab + (size_t)a.npass * kQSlab;
+    const size_t tap_bytes = (size_t)a.taps * a.npass * sizeof(float);
+    const int want_ctas = 512 / a.tmem_cols < 2 ? 1 : 2;
+    const size_t smem_cap = 227 * 1024 - 2048;
+    const size_t budget = smem_cap / (size_t)want_ctas - 1024 - tap_bytes;
+    int stages = (int)((budget - 1024) / stage_bytes);
+    if (stages > kQMaxStages) stages = kQMaxStages;
+    if (stages < 2) return (int)cudaErrorInvalidValue;
+    a.stages = stages;
+    size_t smem = (size_t)stages * stage_bytes + tap_bytes + 1024;
+    {
+        const size_t floor_bytes = smem_cap / (size_t)(want_ctas + 1) + 1024;
+        if (smem < floor_bytes) smem = floor_bytes;
+    }
+    static bool configured = false;
+    if (!configured) {
+        cudaError_t ce = cudaFuncSetAttribute(pwq8_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_cap);
+        if (ce != cudaSuccess) return (int)ce;
+        configured = true;
+    }
+    EncodeTiledFn enc = encode_tiled();
+    if (!enc) return (int)cudaErrorNotSupported;
+    CUtensorMap tm;
+    const cuuint64_t gdim[4] = {(cuuint64_t)a.Cp, (cuuint64_t)d->W, (cuuint64_t)d->H, (cuuint64_t)d->N};
+    const cuuint64_t gstr[3] = {(cuuint64_t)a.Cp, (cuuint64_t)a.Cp * d->W, (cuuint64_t)a.Cp * d->W * d->H};
+    const cuuint32_t box[4] = {(cuuint32_t)kQSlab, (cuuint32_t)a.BW, (cuuint32_t)a.BH, 1};
+    const cuuint32_t estr[4] = {1, 1, 1, 1};
+    CUresult r = enc(&tm, CU_TENSOR_MAP_DATA_TYPE_UINT8, 4, (void *)d->x, gdim, gstr, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return (int)cudaErrorInvalidValue;
+    int occ = 0;
+    cudaError_t ce = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, pwq8_kernel<true>, kQThreads, smem);
+    if (ce != cudaSuccess) return (int)ce;
+    if (occ < 1) return (int)cudaErrorLaunchOutOfResources;
+    if (occ > want_ctas) occ = want_ctas;
+    int64_t per_pass = ((int64_t)sm_count() * occ) / a.n_pass;
+    if (per_pass < 1) per_pass = 1;
+    if (per_pass > a.tiles) per_pass = a.tiles;
+    pwq8_kernel<true><<<(unsigned)(per_pass * a.n_pass), kQThreads, smem, (cudaStream_t)stream>>>(tm, a);
+    g_launches += 1;
+    return (int)cudaGetLastError();
+}
+}  // namespace dfq
 
 extern "C" int dfq_dw_q8(const DfqDwQ8Desc *d, void *stream) {
     if (!d || !d->x || !d->wrow || !d->in_slot || !d->y0 || !d->out_slot0 || (d->y1 && !d->out_slot1) || d->N <= 0 ||

@@ -19,6 +19,7 @@ Semantics per op are those of the reference with replace_op() in force (utils/la
 utils/quantize.py:250-256, 358-363); bits_activation is 8 (the reference's set_layer_bits never changes it).
 """
 import ctypes
+import os
 
 import numpy as np
 import torch
@@ -63,6 +64,45 @@ class PackedQ8:
         self.wpk, self.wr = torch.from_numpy(packed).to(dev), torch.from_numpy(wr).to(dev)
         self.codes = codes
         self.n_pass, self.o_per_pass = n_pass.value, opp.value
+
+
+class PackedConvQ8:
+    """Weight codes of a dense k x k convolution in the layout of the TMA-fed kernel (dfq_conv_q8 with tma = 1):
+    reduction tap-major, then 128-byte channel slabs; plus the per-tap code sums the zero-padding correction needs."""
+
+    def __init__(self, w, o_cap=0):
+        rec = None
+        for b in (8, 7, 6, 5, 4, 3, 2):
+            rec = pw_i8._recover_codes(w, b)
+            if rec is not None:
+                break
+        if rec is None:
+            raise RuntimeError("q8 plan: weight is not on an integer grid of <= 8 bits (run quantize_targ_layer first)")
+        s32, lo, q, bits = rec
+        up = 2 ** (8 - bits)
+        O, C, kh, kw = w.shape
+        taps, Cp = kh * kw, _cp(C)
+        codes = ((q - 2 ** (bits - 1)) * up).to(torch.int8).cpu().numpy().reshape(O, C, taps)
+        lay = np.zeros((O, taps, Cp), dtype=np.int8)
+        lay[:, :, :C] = codes.transpose(0, 2, 1)
+        lib = L.lib()
+        kq, nbytes = ctypes.c_int(), L.i64()
+        self.o_cap = int(o_cap)
+        L.check(lib.dfq_conv_q8_plan_host(O, C, taps, self.o_cap, ctypes.byref(kq), ctypes.byref(nbytes)),
+                "dfq_conv_q8_plan_host")
+        packed = np.empty(nbytes.value, dtype=np.int8)
+        lay = np.ascontiguousarray(lay)
+        L.check(lib.dfq_conv_q8_pack_host(lay.ctypes.data, O, C, taps, self.o_cap, packed.ctypes.data),
+                "dfq_conv_q8_pack_host")
+        self.s_w = s32 / up
+        self.c_w = float(np.float32(lo + 2 ** (bits - 1) * s32))
+        tap_sums = codes.astype(np.int64).sum(1)                                   # [O, taps]
+        wr = (tap_sums.sum(1).astype(np.float64) * self.s_w).astype(np.float32)
+        wrt = np.ascontiguousarray((tap_sums.T.astype(np.float64) * self.s_w).astype(np.float32))   # [taps, O]
+        dev = w.device
+        self.wpk, self.wr, self.wrt = (torch.from_numpy(packed).to(dev), torch.from_numpy(wr).to(dev),
+                                       torch.from_numpy(wrt).to(dev))
+        self.O = O
 
 
 def pack_depthwise(w):
@@ -308,7 +348,17 @@ class EvalPlanQ8(EvalPlan):
                     kind2 = "dw"
                 elif g == 1 and padinfo is None and y0 is not None:        # dense k x k (ASPP's atrous 3 x 3, the decoder's 3 x 3)
                     G_out = out.shape[0] * out.shape[2] * out.shape[3]
-                    pk = pw_i8.pack_weight_conv(w, None, o_cap=pw_i8.choose_o_cap(G_out, w.shape[0]))
+                    # DFQ_CONV_Q8_TMA=1 selects the TMA-fed, warp-specialised form (stride 1).  Same codes out; measured
+                    # SLOWER on the decoder's 304 / 256 -> 256 layers at 129 x 129 (0.71 / 0.53 ms against 0.35 / 0.33 ms):
+                    # a 128-pixel tile re-streams the whole weight tensor through L2 -> shared memory (~8.9 TB/s
+                    # measured), and the row-of-ones trick that feeds SUM_k a costs a third pass at 256 output
+                    # channels, while the register-gather kernel forms the code sums with dp4a and runs ONE pass of
+                    # N = 256.  Kept selectable (and tested) as the base for a cluster / multicast version.
+                    tma = 1 if s == 1 and os.environ.get("DFQ_CONV_Q8_TMA", "0") == "1" else 0
+                    if tma:
+                        pk = PackedConvQ8(w, o_cap=choose_o_cap(G_out, w.shape[0]))
+                    else:
+                        pk = pw_i8.pack_weight_conv(w, None, o_cap=pw_i8.choose_o_cap(G_out, w.shape[0]))
                     if pk is None:
                         raise RuntimeError(f"{name}: weight is not on an integer grid of <= 8 bits")
                     desc = L.DfqConvQ8Desc()
@@ -318,7 +368,7 @@ class EvalPlanQ8(EvalPlan):
                     desc.N, desc.C, desc.H, desc.W = Nn, C, H, W
                     desc.O, desc.OH, desc.OW = out.shape[1], out.shape[2], out.shape[3]
                     desc.kh, desc.kw, desc.stride, desc.pad, desc.dil, desc.relu = kh, kw, s, p, d, st["relu"]
-                    desc.s_w, desc.c_w, desc.o_cap = pk.s_w, pk.c_w, pk.o_cap
+                    desc.s_w, desc.c_w, desc.o_cap, desc.tma = pk.s_w, pk.c_w, pk.o_cap, tma
                     self.keep_q8 += [pk, desc, b]
                     fn = (lambda dd: lambda: L.check(lib.dfq_conv_q8(ctypes.byref(dd), stream()), "dfq_conv_q8"))(desc)
                     kind2 = "dense"

@@ -23,7 +23,7 @@
 extern "C" {
 #endif
 
-#define DFQ_ABI_VERSION 17
+#define DFQ_ABI_VERSION 18
 
 #if defined(__GNUC__)
 #pragma GCC visibility push(default)   /* the library is built with -fvisibility=hidden */
@@ -354,8 +354,15 @@ typedef struct DfqConvQ8Desc {
     int32_t N, C, H, W, O, OH, OW, kh, kw, stride, pad, dil, relu;
     float s_w, c_w;
     int32_t o_cap;
+    int32_t tma;             /* 0: wpk packed by dfq_pw_i8_pack_cap_host (register-gather kernel, any stride);
+                              * 1: wpk packed by dfq_conv_q8_pack_host (stride 1): the activation tile of every tap arrives
+                              *    by a 4-D tensor-map TMA box of the code tensor, warp-specialised tcgen05 pipeline     */
 } DfqConvQ8Desc;
 int dfq_conv_q8(const DfqConvQ8Desc *desc_host, void *stream);
+/* weight layout of the tma form: reduction tap-major, then 128-byte channel slabs (zero padded); codes_host is
+ * [O][kh*kw][C padded to 16] centred codes; *kq = padded reduction length, o_cap as for dfq_pw_q8 (0 = 240 per pass) */
+int dfq_conv_q8_plan_host(int O, int C, int taps, int o_cap, int *kq, int64_t *packed_bytes);
+int dfq_conv_q8_pack_host(const int8_t *codes_host, int O, int C, int taps, int o_cap, int8_t *packed_host);
 
 /* ---- (e) static-range W8A8 eval (csrc/q8.cu): QuantMeasure with update_stat == False, utils/quantize.py:119-126 ----
  * Activations are CENTRED s8 CODES (code - 128 of utils/quantize.py:72-74 on the CONSUMER's grid), NHWC, channels

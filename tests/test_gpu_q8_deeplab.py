@@ -91,6 +91,29 @@ def test_deeplab_static_plan_edge_by_edge(static_deeplab):
     assert edges >= 85
 
 
+def test_deeplab_dense_layers_tma_form(static_deeplab, monkeypatch):
+    """The TMA-fed form of the dense k x k kernel (DFQ_CONV_Q8_TMA=1: 4-D tensor-map boxes of the code tensor per tap,
+    zero padding by the TMA's out-of-bounds fill, warp-specialised tcgen05 pipeline) against the same goldens."""
+    from data_free_quantization_b200.eval_q8 import EvalPlanQ8
+    model, tr = static_deeplab
+    monkeypatch.setenv("DFQ_CONV_Q8_TMA", "1")
+    tf = np.load(os.path.join(GOLD, "eval_tf_static_deeplab.npz"))
+    plan = EvalPlanQ8(model, tr, batch=1, in_shape=(3, 129, 129))
+    gold = lambda key: tf[f"L/{key[1]}/xq"] if key[0] == "L" else tf[f"T/{key[1]}/xq{key[2]}"]
+    rng = lambda key: tf[f"L/{key[1]}/range"] if key[0] == "L" else tf[f"T/{key[1]}/range{key[2]}"]
+    for idx, key in plan.slot_key.items():
+        plan.set_range(idx, float(np.float32(rng(key)[0])), float(np.float32(rng(key)[1])))
+    done = 0
+    for name, io in plan.step_io.items():
+        if io["kind"] != "dense":
+            continue
+        res = plan.run_step(name, in_codes=[gold(plan.slot_key[i]) for i in io["in_slots"]])
+        for idx in io["out_slots"]:
+            check_codes(res[idx].numpy(), gold(plan.slot_key[idx]), f"{name} (tma) -> {plan.slot_key[idx]}")
+            done += 1
+    assert done == 5
+
+
 def test_deeplab_static_plan_end_to_end(static_deeplab):
     from data_free_quantization_b200.eval_q8 import EvalPlanQ8
     model, tr = static_deeplab
