@@ -27,16 +27,40 @@ absorb_wc_kernel(const DfqAbsorbPair *__restrict__ pairs, int n_pairs, int total
     const int G = p.C1 / p.I2, Og = p.O2 / G, g = o / Og, KK = p.KK;
     float *w = p.W2 + (int64_t)o * p.I2 * KK;
     double acc = 0.0;
-    for (int it = lane; it < p.I2; it += 32) {
-        int ci = g * p.I2 + it;
-        float c = absorb_c(p.bn_b[ci], p.bn_w[ci], N);
-        float rs = 0.0f;
-        for (int k = 0; k < KK; ++k) {                     // torch.sum(W2.view(O, I, -1), -1), :52,:65
-            float v = w[it * KK + k];
-            rs = __fadd_rn(rs, v);
-            if (do_clip) w[it * KK + k] = fminf(fmaxf(v, lo_c), hi_c);
+    if (KK == 1) {
+        // pointwise / linear rows: eight independent loads of W, beta and gamma in flight, then the SAME accumulation
+        // order as the plain loop (a 1280-long row was 40 dependent L2 round trips per lane: 41 us for the model)
+        constexpr int U = 8;
+        for (int base = lane; base < p.I2; base += 32 * U) {
+            float v[U], bb[U], bw[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int it = base + 32 * u;
+                if (it < p.I2) { v[u] = w[it]; bb[u] = p.bn_b[g * p.I2 + it]; bw[u] = p.bn_w[g * p.I2 + it]; }
+            }
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int it = base + 32 * u;
+                if (it < p.I2) {
+                    const float c = absorb_c(bb[u], bw[u], N);
+                    const float rs = __fadd_rn(0.0f, v[u]);
+                    if (do_clip) w[it] = fminf(fmaxf(v[u], lo_c), hi_c);
+                    acc += (double)rs * (double)c;
+                }
+            }
         }
-        acc += (double)rs * (double)c;                     // matmul(., c), :64-67
+    } else {
+        for (int it = lane; it < p.I2; it += 32) {
+            int ci = g * p.I2 + it;
+            float c = absorb_c(p.bn_b[ci], p.bn_w[ci], N);
+            float rs = 0.0f;
+            for (int k = 0; k < KK; ++k) {                     // torch.sum(W2.view(O, I, -1), -1), :52,:65
+                float v = w[it * KK + k];
+                rs = __fadd_rn(rs, v);
+                if (do_clip) w[it * KK + k] = fminf(fmaxf(v, lo_c), hi_c);
+            }
+            acc += (double)rs * (double)c;                     // matmul(., c), :64-67
+        }
     }
     acc = warp_sum(acc);
     if (lane == 0) p.wc[o] = (float)acc;
@@ -45,12 +69,23 @@ absorb_wc_kernel(const DfqAbsorbPair *__restrict__ pairs, int n_pairs, int total
 // b1 -= c ; fake_bias -= c ; b2 += wc  (:78-80), relations in list order for every element.
 __global__ void absorb_bias_kernel(const DfqAbsorbPair *__restrict__ pairs, int n_pairs, float N) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
+    // The c of a pair depends only on ITS BatchNorm, which no other pair's update touches: the two loads of pair r + 1
+    // are issued before pair r's read-modify-writes (those stay in list order).  37 dependent round trips became ~19.
+    float nb = 0.0f, nw = 0.0f;
+    bool have = false;
     for (int r = 0; r < n_pairs; ++r) {
         const DfqAbsorbPair &p = pairs[r];
+        float bb = nb, bw = nw;
+        if (!have && i < p.C1) { bb = p.bn_b[i]; bw = p.bn_w[i]; }
+        have = false;
+        if (r + 1 < n_pairs && pairs[r + 1].bn_b != p.bn_b && i < pairs[r + 1].C1) {
+            nb = pairs[r + 1].bn_b[i]; nw = pairs[r + 1].bn_w[i];
+            have = true;
+        }
         if (i < p.C1) {
-            float c = absorb_c(p.bn_b[i], p.bn_w[i], N);
+            float c = absorb_c(bb, bw, N);
             p.b1[i] = __fadd_rn(p.b1[i], -c);
-            p.bn_b[i] = __fadd_rn(p.bn_b[i], -c);
+            p.bn_b[i] = __fadd_rn(bb, -c);
             if (p.c) p.c[i] = c;
         }
         if (i < p.O2) p.b2[i] = __fadd_rn(p.b2[i], p.wc[i]);

@@ -423,10 +423,94 @@ class QuantNLinear(nn.Linear):
         return F.linear(input, self.weight, self.bias)
 
 
-# The reference's QConv2d / QLinear (:129-210, :260-323) add per-channel `scale`/`scale_prev` merging on top of
-# QuantConv2d / QuantLinear; no script of the hot path instantiates them with scales, so they alias the plain forms.
-QConv2d = QuantConv2d
-QLinear = QuantLinear
+class _ScaleMixin:
+    """set_scale / merge_scale_to_weight of the reference's QConv2d / QLinear (utils/quantize.py:142-166, 270-291): an
+    output-channel `scale` (a Parameter) and the previous layer's `scale_prev`, applied to the weight (and bias) ahead of
+    the per-forward weight quantisation, or folded into the stored weight once."""
+
+    def set_scale(self, scale=None, scale_prev=None):
+        if scale is not None:
+            self.register_parameter("scale", nn.Parameter(scale.view(*self._scale_shape)))
+        if scale_prev is not None:
+            self.scale_prev = scale_prev
+
+    def merge_scale_to_weight(self):
+        if getattr(self, "scale_prev", None) is not None:
+            self.weight.data.copy_(self.merge_scale_prev(self.weight.detach(), self.scale_prev))
+            self.scale_prev = None
+        if getattr(self, "scale", None) is not None:
+            weight, bias = self.merge_scale(self.weight.detach(), self.bias.detach() if self.bias is not None else None,
+                                            self.scale)
+            self.weight.data.copy_(weight)
+            if self.bias is not None:
+                self.bias.data.copy_(bias)
+            self.scale = None
+
+    def merge_scale(self, weight, bias, scale):
+        weight = weight * scale
+        if bias is not None:
+            bias = bias * scale.view(-1)
+        return weight, bias
+
+    def _scaled(self):
+        """(weight, bias) with the pending scales applied -- utils/quantize.py:183-198, 300-311."""
+        sweight, sbias = self.weight, self.bias
+        if getattr(self, "scale_prev", None) is not None:
+            sweight = self.merge_scale_prev(sweight, self.scale_prev)
+        if getattr(self, "scale", None) is not None:
+            sweight, sbias = self.merge_scale(sweight, sbias, self.scale)
+        return sweight, sbias
+
+
+class QConv2d(_ScaleMixin, nn.Conv2d):
+    """utils/quantize.py:129-210.  The weight range is reduced and the weight fake-quantised per forward by the
+    library's kernels (quantize with the range from dfq_minmax_f32); the convolution arithmetic itself is F.conv2d,
+    as in QuantConv2d."""
+    _scale_shape = (-1, 1, 1, 1)
+
+    def __init__(self, in_channels, out_channels, kernel_size, stride=1, padding=0, dilation=1, groups=1, bias=True,
+                 num_bits=8, num_bits_act=8, num_bits_bias=16, momentum=0.1):
+        super(QConv2d, self).__init__(in_channels, out_channels, kernel_size, stride, padding, dilation, groups, bias)
+        self.num_bits = num_bits
+        self.num_bits_bias = num_bits_bias
+        self.quant = QuantMeasure(num_bits=num_bits_act, momentum=momentum)
+
+    def merge_scale_prev(self, weight, scale_prev):
+        # :168-177: the input channels of every group are divided by that group's slice of the previous layer's scale
+        step_s = weight.shape[1]
+        sp = scale_prev[:, 0, 0, 0].view(1, -1, 1, 1)
+        step = weight.shape[0] // self.groups
+        parts = [weight[g * step:(g + 1) * step] / sp[:, g * step_s:(g + 1) * step_s] for g in range(self.groups)]
+        return torch.cat(parts, 0)
+
+    def forward(self, input):
+        input = self.quant(input)
+        sweight, sbias = self._scaled()
+        qweight = _quant_weight(sweight.contiguous(), self.num_bits)
+        qbias = quantize(sbias.contiguous(), num_bits=self.num_bits_bias) if sbias is not None else None
+        return _conv2d_fp32(input, qweight, qbias, self.stride, self.padding, self.dilation, self.groups)
+
+
+class QLinear(_ScaleMixin, nn.Linear):
+    """utils/quantize.py:260-323."""
+    _scale_shape = (-1, 1)
+
+    def __init__(self, in_features, out_features, bias=True, num_bits=8, num_bits_act=8, num_bits_bias=16,
+                 momentum=0.1):
+        super(QLinear, self).__init__(in_features, out_features, bias)
+        self.num_bits = num_bits
+        self.num_bits_bias = num_bits_bias
+        self.quant = QuantMeasure(num_bits=num_bits_act, momentum=momentum)
+
+    def merge_scale_prev(self, weight, scale_prev):
+        return weight * scale_prev.view(1, -1)                     # :293-294
+
+    def forward(self, input):
+        input = self.quant(input)
+        sweight, sbias = self._scaled()
+        qweight = _quant_weight(sweight.contiguous(), self.num_bits)
+        qbias = quantize(sbias.contiguous(), num_bits=self.num_bits_bias) if sbias is not None else None
+        return F.linear(input, qweight, qbias)
 
 
 def set_layer_bits(graph, bits_weight=8, bits_activation=8, bits_bias=16, targ_type=None):
