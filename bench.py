@@ -332,6 +332,42 @@ def int8_peak(torch, dev):
         return {"tops": None, "how": f"torch._int_mm unavailable: {exc!r}"[:200]}
 
 
+def sliced_microbench(torch, dev, world, peak_gbs, total_log2=32, reps=3):
+    """BASELINE.json configs[4], the single huge tensor: 2^total_log2 fp32 elements split into contiguous slices across
+    the ranks (dist.fake_quant_sliced): local min/max, ONE all-reduce of two floats, local in-place apply.  Strong
+    scaling; aggregate GB/s over the algorithmic 12 B/elt, max-over-ranks device time."""
+    import torch.distributed as dist
+    from data_free_quantization_b200.dist import fake_quant_sliced
+    n = (1 << total_log2) // world
+    g = torch.Generator(device=dev).manual_seed(5 + (dist.get_rank() if world > 1 else 0))
+    x = torch.randn(n, device=dev, generator=g) * 0.1
+    ts = []
+    for it in range(reps + 1):
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        fake_quant_sliced(x, 8)
+        b.record()
+        b.synchronize()
+        t = torch.tensor([a.elapsed_time(b)], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        if it:
+            ts.append(float(t[0]))
+    del x
+    torch.cuda.empty_cache()
+    ms = sorted(ts)[len(ts) // 2]
+    gbs = 12.0 * (n * world) / (ms * 1e-3) / 1e9
+    return {"kernel": "fake_quant_sliced: one tensor in contiguous slices, all-reduce of (min, max), in-place apply",
+            "elems_total": n * world, "elems_per_gpu": n, "bytes_per_elt": 12, "ms": round(ms, 4),
+            "achieved": round(gbs, 1), "per_gpu": round(gbs / world, 1), "peak_per_gpu": peak_gbs, "unit": "GB/s",
+            "frac_per_gpu": round(gbs / world / peak_gbs, 4), "scaling": "strong",
+            "note": "includes the host read of the reduced range (the elementwise pass takes host constants, as "
+                    "utils/quantize.py:51-68 forms the scale in Python floats)"}
+
+
 def sharded_microbench(torch, dev, world, peak_gbs, elems=1 << 26, per_rank=2, reps=5):
     """BASELINE.json configs[4]: a list of world*per_rank equal fp32 tensors (256 MiB each, larger than L2 together)
     dealt to the ranks; every rank fake-quantises its share (range reduce + apply, 12 B/elt) and the quantised
@@ -770,9 +806,10 @@ def _main(args):
             ms_s = float(t[0])
         deeplab["eval_static_ms_per_batch"] = round(ms_s, 3)
         deeplab["eval_static_images_per_s"] = round(deeplab["eval_batch_per_gpu"] * world / (ms_s * 1e-3), 1)
-    sharded = None
+    sharded, sliced = None, None
     if not args.no_micro:
         with quiet:
+            sliced = sliced_microbench(torch, dev, world, peak, total_log2=min(32, max(28, args.sweep_max_log2)))
             sharded = sharded_microbench(torch, dev, world, peak)
             if world > 1:                       # the same exchange through one NCCL all-gather, for comparison
                 from data_free_quantization_b200 import dist as D
@@ -830,7 +867,7 @@ def _main(args):
             "stages_note": "stages_ms: the eager reference-shaped functions with a host synchronisation around each "
                            "(first-call path); `value` replays the captured pipeline plan (pipeline_plan.py)",
             "roofline": roof, "kernels": kernels, "kernels_sweep": sweep, "int8_peak": i8peak,
-            "kernels_sharded": sharded, "eval": ev, "eval_static": ev_static,
+            "kernels_sharded": sharded, "kernels_sliced": sliced, "eval": ev, "eval_static": ev_static,
             "deeplab": deeplab, "cpu_baseline": cpu, "clocks": clocks.summary()}
     if world > 1:
         dist.destroy_process_group()
