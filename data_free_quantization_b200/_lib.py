@@ -105,11 +105,15 @@ class DfqConvI8Desc(ctypes.Structure):
                                    "relu")] + [("s_w", f32), ("c_w", f32), ("scratch", c_void), ("o_cap", i32), ("reserved", i32)]
 
 
+class DfqQ8OutMap(ctypes.Structure):
+    _fields_ = [(k, i32) for k in ("OH", "OW", "pl", "pr", "pt", "pb")]
+
+
 class DfqPwQ8Desc(ctypes.Structure):
     _fields_ = [("x", c_void), ("wpk", c_void), ("wr", c_void), ("bias", c_void), ("in_slot", c_void),
                 ("y0", c_void), ("out_slot0", c_void), ("y1", c_void), ("out_slot1", c_void), ("yf", c_void),
                 ("yf_g", i64), ("yf_o", i64), ("G", i64), ("K", i32), ("O", i32), ("relu", i32), ("o_cap", i32),
-                ("s_w", f32), ("c_w", f32)]
+                ("s_w", f32), ("c_w", f32), ("map0", DfqQ8OutMap), ("map1", DfqQ8OutMap)]
 
 
 class DfqDwQ8Desc(ctypes.Structure):
@@ -129,11 +133,12 @@ class DfqConvQ8Desc(ctypes.Structure):
 class DfqStemQ8Desc(ctypes.Structure):
     _fields_ = [("x", c_void), ("w", c_void), ("bias", c_void), ("in_slot", c_void), ("y0", c_void),
                 ("out_slot0", c_void), ("y1", c_void), ("out_slot1", c_void)] + \
-               [(k, i32) for k in ("N", "H", "W", "O", "stride", "pad", "relu", "reserved")]
+               [(k, i32) for k in ("N", "H", "W", "O", "stride", "pad", "relu", "reserved")] + \
+               [("map0", DfqQ8OutMap), ("map1", DfqQ8OutMap)]
 
 
 Q_SYMMETRIC, Q_RANGE_F32, Q_PER_CHANNEL, Q_CLAMP_OUT = 1, 2, 4, 8
-ABI_VERSION = 18
+ABI_VERSION = 19
 
 # every symbol include/dfq_b200.h declares: (restype, argtypes)
 P = ctypes.POINTER
@@ -181,7 +186,7 @@ PROTOTYPES = {
     "dfq_dw_q8": (ctypes.c_int, [P(DfqDwQ8Desc), c_void]),
     "dfq_stem_q8": (ctypes.c_int, [P(DfqStemQ8Desc), c_void]),
     "dfq_add_q8": (ctypes.c_int, [c_void, c_void, c_void, c_void, c_void, c_void, c_void, c_void, i64, ctypes.c_int,
-                                  c_void]),
+                                  P(DfqQ8OutMap), P(DfqQ8OutMap), c_void]),
     "dfq_mean_q8": (ctypes.c_int, [c_void, c_void, c_void, c_void, c_void, i64, ctypes.c_int, ctypes.c_int, c_void]),
     "dfq_conv_q8": (ctypes.c_int, [P(DfqConvQ8Desc), c_void]),
     "dfq_conv_q8_plan_host": (ctypes.c_int, [ctypes.c_int] * 4 + [P(ctypes.c_int), P(i64)]),

@@ -38,6 +38,7 @@ constexpr int kQSpin = 1 << 26;          // bounded mbarrier spin: a protocol bu
 struct PwQ8Args {
     const int8_t *wpk; const float *wr; const float *bias; const RangeSlot *in_slot;
     const RangeSlot *out_slot[2]; int8_t *y[2]; int cp_out;
+    Q8OutMap omap[2];
     float *yf; int64_t yf_g, yf_o;
     int64_t G, tiles;
     int K, Kp, O, relu, n_pass, o_per_pass, npass, slabs, tmem_cols, stages;
@@ -128,11 +129,12 @@ struct EpiCtx {
     const PwQ8Args *a; const float *chan_c; uint32_t tbase; int64_t g; int o0, n_real, half; bool valid, small_acc;
     float fa, fr, floor_v;
     uint32_t oob; const float *tap_c;      // CONV: taps of this pixel that fell in the zero padding, and what each stands for
+    int gp[2];                             // row of this pixel in output 0 / 1 (plain: g; padded consumer: its interior)
 };
 
 // One accumulator row (this thread's pixel) of one tile: units of U columns alternate between the two warps of the
 // lane group; SUM_k a and the first unit arrive behind ONE wait, the next unit is in flight behind the arithmetic.
-template <int U>
+template <int U, bool CONV>
 __device__ __forceinline__ void epi_tile(const EpiCtx &e, const QuantConsts &q0, const QuantConsts &q1) {
     const PwQ8Args &a = *e.a;
     const bool has0 = a.y[0] != nullptr, has1 = a.y[1] != nullptr;
@@ -145,7 +147,7 @@ __device__ __forceinline__ void epi_tile(const EpiCtx &e, const QuantConsts &q0,
     for (; unit * U < e.n_real; unit += 2) {
         const int nv = min(U, e.n_real - unit * U);                          // warp-uniform
         float yv[U];
-        if (e.oob) {             // CONV, border pixel: zero padding is an exact 0.0 in the reference (the tap is absent),
+        if (CONV && e.oob) {     // border pixel: zero padding is an exact 0.0 in the reference (the tap is absent),
                                  // while the s8 zero the TMA filled in stands for c_x: take that back out, tap by tap
             float corr[U];
 #pragma unroll
@@ -187,7 +189,7 @@ __device__ __forceinline__ void epi_tile(const EpiCtx &e, const QuantConsts &q0,
 #pragma unroll
                     for (int j4 = 0; j4 < U / 4; ++j4) w[j4] = keep_left(w[j4], nv - 4 * j4);
                 }
-                int8_t *dst = a.y[t] + e.g * a.cp_out + e.o0 + unit * U;
+                int8_t *dst = a.y[t] + (int64_t)e.gp[t] * a.cp_out + e.o0 + unit * U;
                 if (U == 16) *reinterpret_cast<uint4 *>(dst) = make_uint4(w[0], w[1], w[U / 4 - 2], w[U / 4 - 1]);
                 else *reinterpret_cast<uint2 *>(dst) = make_uint2(w[0], w[1]);
             }
@@ -200,7 +202,7 @@ __device__ __forceinline__ void epi_tile(const EpiCtx &e, const QuantConsts &q0,
         for (int cpad = done; cpad < row_end; cpad += 8) {
 #pragma unroll
             for (int t = 0; t < 2; ++t)
-                if (t ? has1 : has0) *reinterpret_cast<uint2 *>(a.y[t] + e.g * a.cp_out + e.o0 + cpad) = make_uint2(0u, 0u);
+                if (t ? has1 : has0) *reinterpret_cast<uint2 *>(a.y[t] + (int64_t)e.gp[t] * a.cp_out + e.o0 + cpad) = make_uint2(0u, 0u);
         }
     }
 }
@@ -351,9 +353,10 @@ pwq8_kernel(const __grid_constant__ CUtensorMap tmA, PwQ8Args a) {
             mbar_wait(tfull0 + 8 * acc, aphase);
             tc_fence_after();
             const uint32_t tbase = tmem + ((uint32_t)(32 * lg) << 16) + (uint32_t)(acc * a.npass);
-            const EpiCtx ctx = {&a, chan_c, tbase, g, o0, n_real, half, valid, small_acc, fa, fr, floor_v, oob, tap_c};
-            if (n_real <= 16) epi_tile<8>(ctx, q0, q1);      // a 16-channel layer keeps all eight epilogue warps busy
-            else epi_tile<16>(ctx, q0, q1);
+            const EpiCtx ctx = {&a, chan_c, tbase, g, o0, n_real, half, valid, small_acc, fa, fr, floor_v, oob, tap_c,
+                                {valid ? (int)q8_out_pixel(a.omap[0], g) : 0, valid ? (int)q8_out_pixel(a.omap[1], g) : 0}};
+            if (n_real <= 16) epi_tile<8, CONV>(ctx, q0, q1);      // a 16-channel layer keeps all eight epilogue warps busy
+            else epi_tile<16, CONV>(ctx, q0, q1);
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(tempty0 + 8 * acc);
@@ -581,6 +584,7 @@ struct StemQ8Args {
     const float *x; const float *w; const float *bias; const RangeSlot *in_slot;
     const RangeSlot *out_slot[2]; int8_t *y[2];
     int N, H, W, OH, OW, O, Cp, stride, pad, relu;
+    Q8OutMap omap[2];
 };
 
 __global__ void __launch_bounds__(kThreads)
@@ -670,7 +674,7 @@ stemq8_kernel(StemQ8Args a) {
             pack_codes<16>(yv, qc, w4);
 #pragma unroll
             for (int j4 = 0; j4 < 4; ++j4) w4[j4] = keep_left(w4[j4], a.O - ob - 4 * j4);
-            *reinterpret_cast<uint4 *>(a.y[t2] + p * a.Cp + ob) = make_uint4(w4[0], w4[1], w4[2], w4[3]);
+            *reinterpret_cast<uint4 *>(a.y[t2] + q8_out_pixel(a.omap[t2], p) * a.Cp + ob) = make_uint4(w4[0], w4[1], w4[2], w4[3]);
         }
     }
 }
@@ -680,7 +684,8 @@ stemq8_kernel(StemQ8Args a) {
 // requantised to the grid(s) of the consumer(s).  16 elements per thread.
 __global__ void __launch_bounds__(kThreads)
 addq8_kernel(const int8_t *__restrict__ xa, const int8_t *__restrict__ xb, const RangeSlot *sa, const RangeSlot *sb,
-             int8_t *y0, const RangeSlot *s0, int8_t *y1, const RangeSlot *s1, int64_t n16, int C, int Cp) {
+             int8_t *y0, const RangeSlot *s0, int8_t *y1, const RangeSlot *s1, int64_t n16, int C, int Cp, Q8OutMap m0,
+             Q8OutMap m1) {
     const int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x;
     if (i >= n16) return;
     const RangeSlot ra = *sa, rb = *sb;
@@ -703,8 +708,9 @@ addq8_kernel(const int8_t *__restrict__ xa, const int8_t *__restrict__ xb, const
         o0[j] = pack4(s[0], s[1], s[2], s[3], q0) & mask;
         o1[j] = y1 ? (pack4(s[0], s[1], s[2], s[3], q1) & mask) : 0u;
     }
-    reinterpret_cast<uint4 *>(y0)[i] = make_uint4(o0[0], o0[1], o0[2], o0[3]);
-    if (y1) reinterpret_cast<uint4 *>(y1)[i] = make_uint4(o1[0], o1[1], o1[2], o1[3]);
+    const int64_t pix = (i * 16) / Cp;
+    *reinterpret_cast<uint4 *>(y0 + q8_out_pixel(m0, pix) * Cp + cbase) = make_uint4(o0[0], o0[1], o0[2], o0[3]);
+    if (y1) *reinterpret_cast<uint4 *>(y1 + q8_out_pixel(m1, pix) * Cp + cbase) = make_uint4(o1[0], o1[1], o1[2], o1[3]);
 }
 
 // Spatial mean of Q(x) (utils/layer_transform.py:79-95 around x.mean(3).mean(2) / torch.mean): codes [N][HW][Cp] ->
@@ -821,6 +827,7 @@ extern "C" int dfq_pw_q8(const DfqPwQ8Desc *d, void *stream) {
     a.wpk = d->wpk; a.wr = d->wr; a.bias = d->bias; a.in_slot = (const RangeSlot *)d->in_slot;
     a.out_slot[0] = (const RangeSlot *)d->out_slot0; a.out_slot[1] = (const RangeSlot *)d->out_slot1;
     a.y[0] = d->y0; a.y[1] = d->y1; a.cp_out = (d->O + 15) / 16 * 16;
+    a.omap[0] = q8_make_map(&d->map0); a.omap[1] = q8_make_map(&d->map1);
     a.yf = d->yf; a.yf_g = d->yf_g; a.yf_o = d->yf_o;
     a.G = d->G; a.tiles = (d->G + kQM - 1) / kQM;
     a.K = d->K; a.Kp = (d->K + 15) / 16 * 16; a.O = d->O; a.relu = d->relu; a.s_w = d->s_w; a.c_w = d->c_w;
@@ -1025,6 +1032,7 @@ extern "C" int dfq_stem_q8(const DfqStemQ8Desc *d, void *stream) {
     a.N = d->N; a.H = d->H; a.W = d->W; a.O = d->O; a.Cp = (d->O + 15) / 16 * 16; a.stride = d->stride; a.pad = d->pad;
     a.relu = d->relu;
     a.OH = (d->H + 2 * d->pad - 3) / d->stride + 1; a.OW = (d->W + 2 * d->pad - 3) / d->stride + 1;
+    a.omap[0] = q8_make_map(&d->map0); a.omap[1] = q8_make_map(&d->map1);
     const int64_t total = (int64_t)a.N * a.OH * a.OW;
     stemq8_kernel<<<(unsigned)((total + kThreads - 1) / kThreads), kThreads, 0, (cudaStream_t)stream>>>(a);
     g_launches += 1;
@@ -1033,14 +1041,14 @@ extern "C" int dfq_stem_q8(const DfqStemQ8Desc *d, void *stream) {
 
 extern "C" int dfq_add_q8(const int8_t *xa, const int8_t *xb, const float *slot_a, const float *slot_b, int8_t *y0,
                           const float *out_slot0, int8_t *y1, const float *out_slot1, int64_t pixels, int C,
-                          void *stream) {
+                          const DfqQ8OutMap *map0, const DfqQ8OutMap *map1, void *stream) {
     if (!xa || !xb || !slot_a || !slot_b || !y0 || !out_slot0 || (y1 && !out_slot1) || pixels <= 0 || C <= 0)
         return (int)cudaErrorInvalidValue;
     const int Cp = (C + 15) / 16 * 16;
     const int64_t n16 = pixels * (Cp / 16);
     addq8_kernel<<<(unsigned)((n16 + kThreads - 1) / kThreads), kThreads, 0, (cudaStream_t)stream>>>(
         xa, xb, (const RangeSlot *)slot_a, (const RangeSlot *)slot_b, y0, (const RangeSlot *)out_slot0, y1,
-        (const RangeSlot *)out_slot1, n16, C, Cp);
+        (const RangeSlot *)out_slot1, n16, C, Cp, q8_make_map(map0), q8_make_map(map1));
     g_launches += 1;
     return (int)cudaGetLastError();
 }

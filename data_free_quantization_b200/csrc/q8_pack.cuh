@@ -87,5 +87,24 @@ __device__ __forceinline__ void dequant4(uint32_t w, float s, float mn, float *o
     }
 }
 
+// device form of DfqQ8OutMap: Wp == 0 -> row g; else the interior of a padded tensor
+struct Q8OutMap { int OW, OHW, pl, pt, Wp, HpWp; };
+__device__ __forceinline__ int64_t q8_out_pixel(const Q8OutMap &m, int64_t g) {
+    if (m.Wp == 0) return g;
+    const uint32_t g32 = (uint32_t)g;                           // pixel counts are < 2^31 (checked by the launchers)
+    const uint32_t n = g32 / (uint32_t)m.OHW;
+    const uint32_t r = g32 - n * (uint32_t)m.OHW;
+    const uint32_t oh = r / (uint32_t)m.OW, ow = r - oh * (uint32_t)m.OW;
+    return (int64_t)n * m.HpWp + (int64_t)((oh + m.pt) * (uint32_t)m.Wp + ow + m.pl);
+}
+inline Q8OutMap q8_make_map(const DfqQ8OutMap *h) {
+    Q8OutMap m = {0, 0, 0, 0, 0, 0};
+    if (h && (h->pl | h->pr | h->pt | h->pb)) {
+        m.OW = h->OW; m.OHW = h->OH * h->OW; m.pl = h->pl; m.pt = h->pt;
+        m.Wp = h->OW + h->pl + h->pr; m.HpWp = (h->OH + h->pt + h->pb) * m.Wp;
+    }
+    return m;
+}
+
 }  // namespace
 }  // namespace dfq

@@ -229,27 +229,65 @@ class EvalPlanQ8(EvalPlan):
                     pool.setdefault(ent[0].numel(), []).append(ent[0])
             alive[:] = [e for e in alive if e[1]]
 
-        def outs_of(t, name):
-            """Code buffers for the distinct consumer grids of tensor t: (y0, s0, y1, s1, slots measured on t itself)."""
+        self.shape_of, self.padded_bufs = {}, []
+        pads_of = {}                      # id(x) -> pad steps reading x
+        for st in live:
+            if st["kind"] == "pad":
+                pads_of.setdefault(id(st["src"]), []).append(st)
+
+        def outs_of(t, name, can_map=False):
+            """Code buffers for the consumers of tensor t -> (y0, s0, y1, s1, slots served, map0, map1).
+            One plain buffer per distinct grid of the measures on t itself.  Measures that see F.pad(t): when the
+            producer can place pixels (can_map: stem, 1 x 1 convolution, residual add) it writes the INTERIOR of a
+            dedicated padded tensor whose border was filled once with code(0.0) on that grid -- no pad launch; otherwise
+            t is written plain on that grid (self.pre) and the pad op copies it."""
             mine, through = direct.get(id(t), []), via_pad.get(id(t), [])
-            reps = group(mine + through)
-            if len(reps) > 2:
-                raise NotImplementedError(f"{name}: {len(reps)} distinct consumer grids (the q8 kernels write two)")
             n = int(np.prod(code_shape(t)))
-            ents = [[take(n), set()] for _ in reps]
-            for idx in mine:
-                k = rep_in(reps, idx)
-                self.codes[idx] = ents[k][0]
-                ents[k][1].add(step_of_slot[idx])
-            for idx in through:                       # read by the pad op, which writes what the measure's layer reads
-                k = rep_in(reps, idx)
-                self.pre[idx] = ents[k][0]
-                ents[k][1].add(next(i for i, st in enumerate(live) if st["kind"] == "pad" and st["src"] is t
-                                    and idx in direct.get(id(st["out"]), [])))
-            alive.extend(ents)
-            y0 = ents[0][0].data_ptr() if ents else None
-            y1 = ents[1][0].data_ptr() if len(ents) > 1 else None
-            return (y0, slot_ptr(reps[0]) if reps else None, y1, slot_ptr(reps[1]) if len(reps) > 1 else None, list(mine))
+            outs = []                     # [buffer, slot idx, map]
+            if can_map:
+                reps = group(mine)
+                ents = [[take(n), set()] for _ in reps]
+                for idx in mine:
+                    k = rep_in(reps, idx)
+                    self.codes[idx], self.shape_of[idx] = ents[k][0], tuple(t.shape)
+                    ents[k][1].add(step_of_slot[idx])
+                alive.extend(ents)
+                outs += [[e[0], r, None] for e, r in zip(ents, reps)]
+                for pst in pads_of.get(id(t), []):
+                    pt_, (pl, pr, ptop, pb) = pst["out"], pst["pad"]
+                    idxs = direct.get(id(pt_), [])
+                    for r in group(idxs):
+                        buf = torch.zeros(int(np.prod(code_shape(pt_))), dtype=torch.int8, device=dev)   # never recycled
+                        self.act_bytes += buf.numel()
+                        m = L.DfqQ8OutMap()
+                        m.OH, m.OW, m.pl, m.pr, m.pt, m.pb = t.shape[2], t.shape[3], pl, pr, ptop, pb
+                        for idx in idxs:
+                            if same(r, idx):
+                                self.codes[idx], self.shape_of[idx] = buf, tuple(pt_.shape)
+                        self.padded_bufs.append((buf, code_shape(pt_), pt_.shape[1], (pl, pr, ptop, pb), r))
+                        outs.append([buf, r, m])
+                served = list(mine) + list(through)
+            else:
+                reps = group(mine + through)
+                ents = [[take(n), set()] for _ in reps]
+                for idx in mine:
+                    k = rep_in(reps, idx)
+                    self.codes[idx], self.shape_of[idx] = ents[k][0], tuple(t.shape)
+                    ents[k][1].add(step_of_slot[idx])
+                for idx in through:                   # read by the pad op, which writes what the measure's layer reads
+                    k = rep_in(reps, idx)
+                    self.pre[idx] = ents[k][0]
+                    ents[k][1].add(next(i for i, st in enumerate(live) if st["kind"] == "pad" and st["src"] is t
+                                        and idx in direct.get(id(st["out"]), [])))
+                alive.extend(ents)
+                outs += [[e[0], r, None] for e, r in zip(ents, reps)]
+                served = list(mine)
+            if len(outs) > 2:
+                raise NotImplementedError(f"{name}: {len(outs)} distinct consumer tensors (the q8 kernels write two)")
+            y0 = outs[0][0].data_ptr() if outs else None
+            y1 = outs[1][0].data_ptr() if len(outs) > 1 else None
+            return (y0, slot_ptr(outs[0][1]) if outs else None, y1, slot_ptr(outs[1][1]) if len(outs) > 1 else None,
+                    served, outs[0][2] if outs else None, outs[1][2] if len(outs) > 1 else None)
 
         def f32_out(t, shape):
             buf = torch.empty(*shape, dtype=torch.float32, device=dev)
@@ -270,7 +308,9 @@ class EvalPlanQ8(EvalPlan):
                 src = st["src"]
                 pl, pr, pt, pb = st["pad"]
                 Nn, C, H, W = src.shape
-                oidx = list(direct.get(id(out), []))
+                oidx = [idx for idx in direct.get(id(out), []) if idx not in self.codes]
+                if not oidx:                 # the producer wrote the interior of the padded tensor itself
+                    continue
                 reps = group(oidx)
                 n = int(np.prod(code_shape(out)))
                 calls = []
@@ -278,7 +318,7 @@ class EvalPlanQ8(EvalPlan):
                     ent = [take(n), set()]
                     for idx in oidx:
                         if same(r, idx):
-                            self.codes[idx] = ent[0]
+                            self.codes[idx], self.shape_of[idx] = ent[0], tuple(out.shape)
                             ent[1].add(step_of_slot[idx])
                     alive.append(ent)
                     calls.append((self.pre[r].data_ptr(), slot_ptr(r), Nn, C, H, W, pl, pr, pt, pb, ent[0].data_ptr()))
@@ -294,7 +334,13 @@ class EvalPlanQ8(EvalPlan):
                                       "relu": 0, "fn": fn, **io_extra}
                 retire(i)
                 continue
-            y0, s0, y1, s1, oidx = outs_of(out, name)
+            can_map = kind == "add"
+            if kind == "conv":
+                kh_, kw_, s_, p_, d_, g_ = st["geom"]
+                can_map = (st["src"] is self.input) or (kh_ == 1 and kw_ == 1 and g_ == 1 and s_ == 1 and p_ == 0)
+            if os.environ.get("DFQ_Q8_PAD_OP", "0") == "1":      # A/B switch: F.pad as its own launch (dfq_pad_q8)
+                can_map = False
+            y0, s0, y1, s1, oidx, m0, m1 = outs_of(out, name, can_map)
             if kind == "conv":
                 m, src = st["m"], st["src"]
                 kh, kw, s, p, d, g = st["geom"]
@@ -316,6 +362,10 @@ class EvalPlanQ8(EvalPlan):
                     desc.bias = None if b is None else L.dev_f32(b, "bias")
                     desc.in_slot, desc.y0, desc.out_slot0, desc.y1, desc.out_slot1 = slot_ptr(st["slot"]), y0, s0, y1, s1
                     desc.N, desc.H, desc.W, desc.O, desc.stride, desc.pad, desc.relu = Nn, H, W, m.out_channels, s, p, st["relu"]
+                    if m0 is not None:
+                        desc.map0 = m0
+                    if m1 is not None:
+                        desc.map1 = m1
                     self.keep_q8.append(desc)
                     fn = (lambda dd: lambda: L.check(lib.dfq_stem_q8(ctypes.byref(dd), stream()), "dfq_stem_q8"))(desc)
                     kind2 = "stem"
@@ -326,7 +376,7 @@ class EvalPlanQ8(EvalPlan):
                     if id(out) in raw:
                         yf = f32_out(out, (Nn * H * W, m.out_channels))      # fp32 NHWC rows next to the codes
                     fn = self._pw(name, w.reshape(w.shape[0], -1), b, xcodes, slot_ptr(st["slot"]),
-                                  Nn * H * W, y0, s0, y1, s1, st["relu"], yf)
+                                  Nn * H * W, y0, s0, y1, s1, st["relu"], yf, m0, m1)
                     kind2 = "pw"
                 elif kh == 3 and kw == 3 and g == C == m.out_channels and s in (1, 2) and y0 is not None:
                     if p > d:
@@ -394,7 +444,9 @@ class EvalPlanQ8(EvalPlan):
                     raise NotImplementedError(f"{name}: residual add without a quantised consumer")
                 Nn, C, H, W = out.shape
                 args = (self.codes[st["slot_a"]].data_ptr(), self.codes[st["slot_b"]].data_ptr(), slot_ptr(st["slot_a"]),
-                        slot_ptr(st["slot_b"]), y0, s0, y1, s1, Nn * H * W, C)
+                        slot_ptr(st["slot_b"]), y0, s0, y1, s1, Nn * H * W, C,
+                        None if m0 is None else ctypes.pointer(m0), None if m1 is None else ctypes.pointer(m1))
+                self.keep_q8 += [m0, m1]
                 fn = (lambda a2: lambda: L.check(lib.dfq_add_q8(*a2, stream()), "dfq_add_q8"))(args)
                 kind2 = "add"
             elif kind == "mean":
@@ -463,8 +515,22 @@ class EvalPlanQ8(EvalPlan):
             raise NotImplementedError("q8 plan: the network's output is not produced as fp32")
         self.op_info = {n: {"kind": io["kind"]} for n, io in self.step_io.items()}
         self.hbm_bytes = self.act_bytes
+        self._fill_borders()
 
-    def _pw(self, name, w2d, bias, xbuf, in_slot, G, y0, s0, y1, s1, relu, yf):
+    def _fill_borders(self):
+        """Border of every producer-placed padded tensor: code(0.0) on its consumer's grid, i.e. what the reference's
+        QuantMeasure makes of the zeros F.pad put there (utils/quantize.py:72-74 with x = 0), as centred s8; the tensor's
+        padding channels stay s8 zero.  The interior is rewritten by the producer on every forward."""
+        for buf, (N, Hp, Wp, Cp), C, (pl, pr, pt, pb), idx in getattr(self, "padded_bufs", ()):
+            lo, _hi, scale = (np.float32(v) for v in self.slots_host[idx, :3])
+            q = np.rint(np.float32(np.float32(0.0) + np.float32(-lo)) / scale)
+            code = int(min(max(q, 0.0), 255.0)) - 128
+            v = buf.view(N, Hp, Wp, Cp)
+            for sl in ((slice(None), slice(0, pt)), (slice(None), slice(Hp - pb, Hp)),
+                       (slice(None), slice(None), slice(0, pl)), (slice(None), slice(None), slice(Wp - pr, Wp))):
+                v[sl][..., :C] = code
+
+    def _pw(self, name, w2d, bias, xbuf, in_slot, G, y0, s0, y1, s1, relu, yf, m0=None, m1=None):
         pk = PackedQ8(w2d, o_cap=choose_o_cap(G, w2d.shape[0]))
         d = L.DfqPwQ8Desc()
         d.x, d.wpk, d.wr = xbuf.data_ptr(), pk.wpk.data_ptr(), pk.wr.data_ptr()
@@ -473,6 +539,10 @@ class EvalPlanQ8(EvalPlan):
         if yf is not None:
             d.yf, d.yf_g, d.yf_o = yf.data_ptr(), pk.O, 1
         d.G, d.K, d.O, d.relu, d.o_cap, d.s_w, d.c_w = int(G), pk.K, pk.O, int(relu), pk.o_cap, pk.s_w, pk.c_w
+        if m0 is not None:
+            d.map0 = m0
+        if m1 is not None:
+            d.map1 = m1
         self.keep_q8 += [pk, d, bias]
         lib, stream = L.lib(), L.stream
         return lambda: L.check(lib.dfq_pw_q8(ctypes.byref(d), stream()), "dfq_pw_q8")
@@ -496,6 +566,7 @@ class EvalPlanQ8(EvalPlan):
             self.slots.copy_(torch.from_numpy(host))
         else:
             self.slots = torch.from_numpy(host).to(self.dev)
+        self._fill_borders()
 
     def launch(self):
         for _name, fn in self.ops:
@@ -505,6 +576,9 @@ class EvalPlanQ8(EvalPlan):
         p = L.DfqQuantParams()
         L.lib().dfq_quant_params_host(float(lo), float(hi), 8, 0, ctypes.byref(p))
         self.slots[idx].copy_(torch.tensor([float(lo), float(hi), p.scale, 0.0], dtype=torch.float32))
+        self.slots_host[idx] = (np.float32(lo), np.float32(hi), np.float32(p.scale), 0.0)
+        if any(r == idx for *_rest, r in self.padded_bufs):
+            self._fill_borders()
 
     def run_step(self, name, in_codes=None, image=None):
         """Run ONE op on given operand codes (uint8, logical NCHW / NC shape, one per operand) -- or the fp32 image for
@@ -520,7 +594,8 @@ class EvalPlanQ8(EvalPlan):
             for buf, c in zip(bufs, in_codes):
                 buf.copy_(to_codes_nhwc(c).reshape(-1))
         io["fn"]()
-        res = {idx: from_codes_nhwc(self.codes[idx], io["out"].shape).cpu() for idx in io["out_slots"]}
+        res = {idx: from_codes_nhwc(self.codes[idx], self.shape_of.get(idx, io["out"].shape)).cpu()
+               for idx in io["out_slots"]}
         if io["out"].buf is not None and io["out"].buf.dtype == torch.float32 and io["out"] is not self.input:
             res["fp32"] = io["out"].buf.clone().cpu()
         return res

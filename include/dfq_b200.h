@@ -23,7 +23,7 @@
 extern "C" {
 #endif
 
-#define DFQ_ABI_VERSION 18
+#define DFQ_ABI_VERSION 19
 
 #if defined(__GNUC__)
 #pragma GCC visibility push(default)   /* the library is built with -fvisibility=hidden */
@@ -368,6 +368,12 @@ int dfq_conv_q8_pack_host(const int8_t *codes_host, int O, int C, int taps, int 
  * Activations are CENTRED s8 CODES (code - 128 of utils/quantize.py:72-74 on the CONSUMER's grid), NHWC, channels
  * padded to a multiple of 16 with zero bytes; a range slot is {min, max, scale, 0} as fp32.  Every producer writes
  * the codes for up to two consumers (y0 / y1 with their slots; y1 may be NULL). */
+/* Where a producer of the static-range plan puts the pixels of one of its outputs.  All zero: row g of the [pixels][Cp]
+ * code tensor.  Otherwise the output is the INTERIOR of a tensor padded by F.pad(x, (pl, pr, pt, pb)) ahead of a
+ * QuantMeasure (DeepLab's fixed_padding): pixel (n, oh, ow) of the OH x OW image goes to row
+ * (n (OH+pt+pb) + oh + pt) (OW+pl+pr) + ow + pl; the border holds code(0.0) on that grid, written once by the plan. */
+typedef struct DfqQ8OutMap { int32_t OH, OW, pl, pr, pt, pb; } DfqQ8OutMap;
+
 typedef struct DfqPwQ8Desc {
     const int8_t *x;         /* [G][Kp] codes on this layer's grid (Kp = K rounded up to 16)            */
     const int8_t *wpk;       /* dfq_pw_q8_pack_host                                                      */
@@ -381,6 +387,7 @@ typedef struct DfqPwQ8Desc {
     int64_t G;               /* pixels (images x H x W) or rows of a linear layer                        */
     int32_t K, O, relu, o_cap;
     float s_w, c_w;          /* w_hat = s_w * (code_w - 128) + c_w                                       */
+    DfqQ8OutMap map0, map1;  /* pixel placement of y0 / y1 (all zero = plain)                            */
 } DfqPwQ8Desc;
 int dfq_pw_q8_plan_host(int O, int K, int o_cap, int *n_pass, int *o_per_pass, int *npass, int *slabs,
                         int64_t *packed_bytes);
@@ -430,12 +437,14 @@ typedef struct DfqStemQ8Desc {
     int8_t *y0; const float *out_slot0;
     int8_t *y1; const float *out_slot1;
     int32_t N, H, W, O, stride, pad, relu, reserved;
+    DfqQ8OutMap map0, map1;
 } DfqStemQ8Desc;
 /* dense 3 x 3 stem on 3 input channels, O <= 32 */
 int dfq_stem_q8(const DfqStemQ8Desc *desc_host, void *stream);
 /* residual add of two code tensors [pixels][Cp] on their own grids (utils/layer_transform.py:18-32) */
 int dfq_add_q8(const int8_t *xa, const int8_t *xb, const float *slot_a, const float *slot_b, int8_t *y0,
-               const float *out_slot0, int8_t *y1, const float *out_slot1, int64_t pixels, int C, void *stream);
+               const float *out_slot0, int8_t *y1, const float *out_slot1, int64_t pixels, int C,
+               const DfqQ8OutMap *map0, const DfqQ8OutMap *map1 /* host pointers, NULL = plain */, void *stream);
 /* spatial mean of Q(x): codes [N][HW][Cp] -> codes [N][Cp] on out_slot's grid (y) and / or fp32 [N][C] (yf) */
 int dfq_mean_q8(const int8_t *x, const float *in_slot, int8_t *y, const float *out_slot, float *yf, int64_t N, int C,
                 int HW, void *stream);

@@ -178,7 +178,7 @@ def test_stem_add_mean_q8(oracle):
     xa, xb = to_codes_nhwc(torch.from_numpy(ca)).reshape(-1).to(DEV), to_codes_nhwc(torch.from_numpy(cb)).reshape(-1).to(DEV)
     y0, y1 = torch.zeros_like(xa), torch.zeros_like(xa)
     L.check(lib.dfq_add_q8(xa.data_ptr(), xb.data_ptr(), sa.data_ptr(), sb.data_ptr(), y0.data_ptr(), t0.data_ptr(),
-                           y1.data_ptr(), t1.data_ptr(), N * H * W, C, L.stream()), "dfq_add_q8")
+                           y1.data_ptr(), t1.data_ptr(), N * H * W, C, None, None, L.stream()), "dfq_add_q8")
     for yb, (lo, hi) in zip((y0, y1), outs):
         _q, want = oracle.fake_quant(s.astype(np.float32), 8, float(np.float32(lo)), float(np.float32(hi)), want_codes=True)
         assert np.array_equal(from_codes_nhwc(yb.cpu(), s.shape).numpy(), want.astype(np.uint8))   # elementwise: exact
@@ -271,7 +271,7 @@ def test_q8_kernels_stay_inside_their_buffers(oracle):
     ba, ya = guarded(px * 48)
     bb, yb = guarded(px * 48)
     L.check(lib.dfq_add_q8(xa.data_ptr(), xa.data_ptr(), in_slot.data_ptr(), s1.data_ptr(), ya.data_ptr(), s0.data_ptr(),
-                           yb.data_ptr(), s1.data_ptr(), px, C, L.stream()), "dfq_add_q8")
+                           yb.data_ptr(), s1.data_ptr(), px, C, None, None, L.stream()), "dfq_add_q8")
     Nn, Cm, HW = 3, 100, 13
     xm = to_codes_nhwc(torch.from_numpy(rng.integers(0, 256, (Nn, Cm, HW, 1)).astype(np.uint8))).reshape(-1).to(DEV)
     bm, ym = guarded(Nn * 112)
