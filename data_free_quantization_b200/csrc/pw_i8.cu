@@ -263,12 +263,17 @@ pw_i8_kernel(PwI8Args a) {
     };
     // activations of one ring stage: two 16-wide K chunks per thread, all loads in flight before any use
     float v[kQ ? 1 : 2][kQ ? 1 : 16];
-    uint4 vq[2];
-    auto load_stage = [&](int s) {
+    // kQ + kPre: the code words of kD stages ahead are in flight.  With one stage ahead the slab loop was ONE L2 round
+    // trip per iteration (the loads of stage s + 1 leave after the stores of stage s and are needed by the stores of
+    // stage s + 1): ~950 cycles per 256 cycles of MMA, whatever was done about the barrier or the weight stream
+    // (profiles/r2_conv_q8_ncu.md).  The slab loop is unrolled by kD so that the ring index is a compile-time constant.
+    constexpr int kD = (kQ && kPre) ? 4 : 1;
+    uint4 vq[kD][2];
+    auto load_stage = [&](int s, int u) {
 #pragma unroll
         for (int c = 0; c < 2; ++c) {
             if (kQ) {
-                vq[c] = chunk_q(s * 4 + h + 2 * c);
+                vq[kQ ? u : 0][c] = chunk_q(s * 4 + h + 2 * c);
             } else {
                 bool live, inb; const float *px; int nch;
                 chunk_src(s * 4 + h + 2 * c, live, inb, px, nch);
@@ -287,7 +292,11 @@ pw_i8_kernel(PwI8Args a) {
             }
         }
     };
-    if (kPre) load_stage(0);                            // in flight during the TMEM allocation and the barrier
+    if (kPre) {                                         // in flight during the TMEM allocation and the barrier
+#pragma unroll
+        for (int u = 0; u < kD; ++u)
+            if (u == 0 || u < a.slabs) load_stage(u, u);
+    }
     const QuantConsts qc = consts_from_slot(*a.slot, a.bits, 0, 0.f, 0.f);
     const int sh = 8 - a.bits;                          // < 8-bit grids: a = (code - 2^(bits-1)) << sh, s_x >> sh
     const float sx = __fmul_rn(qc.scale, 1.0f / (float)(1 << sh));
@@ -325,9 +334,13 @@ pw_i8_kernel(PwI8Args a) {
                            ((uint32_t)(kI8M >> 4) << 24);
     int csum = 0;
 
-    for (int s = 0; s < a.slabs; ++s) {
+    for (int sb = 0; sb < a.slabs; sb += kD) {
+#pragma unroll
+    for (int u = 0; u < kD; ++u) {
+        const int s = sb + u;
+        if (s >= a.slabs) break;                         // (uniform)
         const int buf = s & 1;
-        if (!kPre) load_stage(s);                        // 1. this stage's activations
+        if (!kPre) load_stage(s, 0);                     // 1. this stage's activations
         // 2. the ring stage is free once the MMAs issued two slabs ago have retired
         if (s >= 2) mbar_wait(done0 + 8 * buf, ((s >> 1) - 1) & 1);
         const int bbuf = s & (kBS - 1);
@@ -341,7 +354,7 @@ pw_i8_kernel(PwI8Args a) {
         for (int c = 0; c < 2; ++c) {
             uint32_t w4[4] = {0u, 0u, 0u, 0u};
             if (kQ) {
-                w4[0] = vq[c].x; w4[1] = vq[c].y; w4[2] = vq[c].z; w4[3] = vq[c].w;
+                w4[0] = vq[kQ ? u : 0][c].x; w4[1] = vq[kQ ? u : 0][c].y; w4[2] = vq[kQ ? u : 0][c].z; w4[3] = vq[kQ ? u : 0][c].w;
 #pragma unroll
                 for (int q4 = 0; q4 < 4; ++q4) csum = __dp4a((int)w4[q4], 0x01010101, csum);
             } else {
@@ -363,7 +376,7 @@ pw_i8_kernel(PwI8Args a) {
             *reinterpret_cast<uint4 *>(sA + buf * kI8ASlab + (h + 2 * c) * (kI8M * 16) + r * 16) =
                 make_uint4(w4[0], w4[1], w4[2], w4[3]);
         }
-        if (kPre && s + 1 < a.slabs) load_stage(s + 1);
+        if (kPre && s + kD < a.slabs) load_stage(s + kD, u);
         // 4. generic-proxy stores -> visible to the tensor core's async proxy, then one thread issues
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         __syncthreads();
@@ -378,6 +391,7 @@ pw_i8_kernel(PwI8Args a) {
             }
             umma_commit(done0 + 8 * buf);
         }
+    }
     }
     colsum_s[h][r] = csum;
     {   // MMAs retire in order: the last stage's barrier covers the whole accumulation
