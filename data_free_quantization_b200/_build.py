@@ -11,7 +11,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 SO = os.path.join(HERE, "libdfq_b200.so")
-SOURCES = ["api.cu", "quant.cu", "cle.cu", "cle2.cu", "cle3.cu", "absorb.cu", "correct.cu", "act.cu", "conv.cu", "move.cu", "pw_i8.cu", "q8.cu", "q8_move.cu"]
+SOURCES = ["api.cu", "quant.cu", "cle.cu", "cle2.cu", "cle3.cu", "absorb.cu", "correct.cu", "act.cu", "conv.cu", "move.cu", "pw_i8.cu", "q8.cu", "q8_move.cu", "conv_halo.cu"]
 # -fmad=false: the reference's elementwise chains round after every operation;
 # kernels that want an FMA ask for it explicitly with __fmaf_rn.
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-fmad=false", "-std=c++17",

@@ -138,7 +138,7 @@ class DfqStemQ8Desc(ctypes.Structure):
 
 
 Q_SYMMETRIC, Q_RANGE_F32, Q_PER_CHANNEL, Q_CLAMP_OUT = 1, 2, 4, 8
-ABI_VERSION = 19
+ABI_VERSION = 20
 
 # every symbol include/dfq_b200.h declares: (restype, argtypes)
 P = ctypes.POINTER
@@ -189,6 +189,7 @@ PROTOTYPES = {
                                   P(DfqQ8OutMap), P(DfqQ8OutMap), c_void]),
     "dfq_mean_q8": (ctypes.c_int, [c_void, c_void, c_void, c_void, c_void, i64, ctypes.c_int, ctypes.c_int, c_void]),
     "dfq_conv_q8": (ctypes.c_int, [P(DfqConvQ8Desc), c_void]),
+    "dfq_conv_q8_halo_k_host": (ctypes.c_int, [ctypes.c_int]),
     "dfq_conv_q8_plan_host": (ctypes.c_int, [ctypes.c_int] * 4 + [P(ctypes.c_int), P(i64)]),
     "dfq_conv_q8_pack_host": (ctypes.c_int, [c_void] + [ctypes.c_int] * 4 + [c_void]),
     "dfq_interp_q8": (ctypes.c_int, [c_void, c_void] + [ctypes.c_int] * 7 + [c_void] * 6),

@@ -977,7 +977,10 @@ extern "C" int dfq_conv_i8(const DfqConvI8Desc *d, void *stream) {
 // Static-range form (eval_q8.py): the input already IS centred s8 codes, NHWC with the channels padded to 16 (what every
 // producer of the u8 plan writes), so there is no quantising pre-pass, and the output leaves as codes on the grid(s) of
 // its consumer(s).  Same pipeline, same packed weights, same padding correction as dfq_conv_i8.
-namespace dfq { int conv_q8_tma(const DfqConvQ8Desc *d, void *stream); }      // q8.cu
+namespace dfq {
+int conv_q8_tma(const DfqConvQ8Desc *d, void *stream);       // q8.cu
+int conv_q8_halo(const DfqConvQ8Desc *d, void *stream);      // conv_halo.cu
+}
 
 extern "C" int dfq_conv_q8(const DfqConvQ8Desc *d, void *stream) {
     if (!d || !d->x || !d->y0 || !d->out_slot0 || !d->wpk || !d->wr || !d->wrt || !d->in_slot || d->N <= 0 ||
@@ -988,6 +991,7 @@ extern "C" int dfq_conv_q8(const DfqConvQ8Desc *d, void *stream) {
     const int OW = (d->W + 2 * d->pad - d->dil * (d->kw - 1) - 1) / d->stride + 1;
     if (OH != d->OH || OW != d->OW || OH <= 0 || OW <= 0) return (int)cudaErrorInvalidValue;
     if ((int64_t)d->C * d->H * d->W > 0x7fffffffll) return (int)cudaErrorInvalidValue;
+    if (d->tma == 2) return conv_q8_halo(d, stream);   // 3 x 3, stride 1, pad 1: halo tile in shared memory, no gather
     if (d->tma) {                           // wpk in the dfq_conv_q8_pack_host layout: TMA-fed, warp-specialised kernel
         if (d->stride != 1) return (int)cudaErrorInvalidValue;
         return conv_q8_tma(d, stream);

@@ -105,6 +105,29 @@ class PackedConvQ8:
         self.O = O
 
 
+def pack_conv_halo(w):
+    """Weights of a 3 x 3 convolution for the halo kernel (dfq_conv_q8 with tma = 2): pw_i8 packing over a reduction
+    ordered [tap][16-byte channel chunk], the chunks of a tap zero-padded to a multiple of 4."""
+    base = pw_i8.pack_weight_conv(w, None, o_cap=0)          # recovers the codes; wr / wrt / scale as for dfq_conv_i8
+    if base is None:
+        return None
+    O, C, kh, kw = w.shape
+    kq = L.lib().dfq_conv_q8_halo_k_host(C)
+    per_tap = kq // 9
+    lay = np.zeros((O, 9, per_tap), dtype=np.int8)
+    lay[:, :, :C] = base.codes.transpose(0, 2, 1)            # codes: [O, C, taps] centred s8
+    lay = np.ascontiguousarray(lay.reshape(O, kq))
+    lib = L.lib()
+    n_pass, opp, npass, slabs, nbytes = (ctypes.c_int(), ctypes.c_int(), ctypes.c_int(), ctypes.c_int(), L.i64())
+    L.check(lib.dfq_pw_i8_plan_cap_host(O, kq, 0, ctypes.byref(n_pass), ctypes.byref(opp), ctypes.byref(npass),
+                                        ctypes.byref(slabs), ctypes.byref(nbytes)), "dfq_pw_i8_plan_cap_host")
+    packed = np.empty(nbytes.value, dtype=np.int8)
+    L.check(lib.dfq_pw_i8_pack_cap_host(lay.ctypes.data, O, kq, 0, packed.ctypes.data), "dfq_pw_i8_pack_cap_host")
+    base.wpk = torch.from_numpy(packed).to(w.device)
+    base.o_cap = 0
+    return base
+
+
 def pack_depthwise(w):
     """[C, 1, 3, 3] fake-quantised depthwise weight -> ([3][Cp] words (w(r,0), w(r,1), w(r,2), 0) of centred s8 codes,
     s_w, c_w) for dfq_dw_q8."""
@@ -405,7 +428,12 @@ class EvalPlanQ8(EvalPlan):
                     # channels, while the register-gather kernel forms the code sums with dp4a and runs ONE pass of
                     # N = 256.  Kept selectable (and tested) as the base for a cluster / multicast version.
                     tma = 1 if s == 1 and os.environ.get("DFQ_CONV_Q8_TMA", "0") == "1" else 0
-                    if tma:
+                    # 3 x 3, stride 1, pad 1, dilation 1 (the decoder): halo tile in shared memory, no gather
+                    if (kh, kw, s, p, d) == (3, 3, 1, 1, 1) and os.environ.get("DFQ_CONV_Q8_HALO", "1") != "0" and not tma:
+                        tma = 2
+                    if tma == 2:
+                        pk = pack_conv_halo(w)
+                    elif tma:
                         pk = PackedConvQ8(w, o_cap=choose_o_cap(G_out, w.shape[0]))
                     else:
                         pk = pw_i8.pack_weight_conv(w, None, o_cap=pw_i8.choose_o_cap(G_out, w.shape[0]))

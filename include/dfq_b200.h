@@ -23,7 +23,7 @@
 extern "C" {
 #endif
 
-#define DFQ_ABI_VERSION 19
+#define DFQ_ABI_VERSION 20
 
 #if defined(__GNUC__)
 #pragma GCC visibility push(default)   /* the library is built with -fvisibility=hidden */
@@ -356,11 +356,17 @@ typedef struct DfqConvQ8Desc {
     int32_t o_cap;
     int32_t tma;             /* 0: wpk packed by dfq_pw_i8_pack_cap_host (register-gather kernel, any stride);
                               * 1: wpk packed by dfq_conv_q8_pack_host (stride 1): the activation tile of every tap arrives
-                              *    by a 4-D tensor-map TMA box of the code tensor, warp-specialised tcgen05 pipeline     */
+                              *    by a 4-D tensor-map TMA box of the code tensor, warp-specialised tcgen05 pipeline;
+                              * 2: 3 x 3, stride 1, dilation 1, padding 1 only: the 18 x 10 input halo of a 16 x 8 pixel
+                              *    tile is loaded once by TMA and all nine taps read it through shifted UMMA descriptors
+                              *    (no im2col gather).  wpk packed by dfq_pw_i8_pack_cap_host over a reduction ordered
+                              *    [tap][16-byte channel chunk] with the chunks of a tap zero-padded to a multiple of 4
+                              *    (dfq_conv_q8_halo_k_host(C) = its length)                                             */
 } DfqConvQ8Desc;
 int dfq_conv_q8(const DfqConvQ8Desc *desc_host, void *stream);
 /* weight layout of the tma form: reduction tap-major, then 128-byte channel slabs (zero padded); codes_host is
  * [O][kh*kw][C padded to 16] centred codes; *kq = padded reduction length, o_cap as for dfq_pw_q8 (0 = 240 per pass) */
+int dfq_conv_q8_halo_k_host(int C);
 int dfq_conv_q8_plan_host(int O, int C, int taps, int o_cap, int *kq, int64_t *packed_bytes);
 int dfq_conv_q8_pack_host(const int8_t *codes_host, int O, int C, int taps, int o_cap, int8_t *packed_host);
 
