@@ -102,7 +102,7 @@ class DfqConvI8Desc(ctypes.Structure):
     _fields_ = [("x", c_void), ("y", c_void), ("wpk", c_void), ("wr", c_void), ("wrt", c_void), ("bias", c_void),
                 ("in_slot", c_void), ("out_stats", c_void)] + \
                [(k, i32) for k in ("N", "C", "H", "W", "O", "OH", "OW", "kh", "kw", "stride", "pad", "dil", "bits",
-                                   "relu")] + [("s_w", f32), ("c_w", f32), ("scratch", c_void), ("o_cap", i32), ("reserved", i32)]
+                                   "relu")] + [("s_w", f32), ("c_w", f32), ("scratch", c_void), ("o_cap", i32), ("halo", i32)]
 
 
 class DfqQ8OutMap(ctypes.Structure):
@@ -138,7 +138,7 @@ class DfqStemQ8Desc(ctypes.Structure):
 
 
 Q_SYMMETRIC, Q_RANGE_F32, Q_PER_CHANNEL, Q_CLAMP_OUT = 1, 2, 4, 8
-ABI_VERSION = 20
+ABI_VERSION = 21
 
 # every symbol include/dfq_b200.h declares: (restype, argtypes)
 P = ctypes.POINTER

@@ -41,6 +41,7 @@ constexpr int kHMaxStages = 8;
 struct HaloArgs {
     const int8_t *x; const int8_t *wpk; const float *wr; const float *wrt; const float *bias; const RangeSlot *in_slot;
     const RangeSlot *out_slot[2]; int8_t *y[2]; int cp_out;
+    float *yf; unsigned *stats;         // kF32 (dynamic-range plan): fp32 NCHW output + encoded per-sample extrema
     int N, C, H, W, O, relu, n_pass, o_per_pass, npass, slabs, cpt, tiles_x, tiles_y, tmem_cols, stages;
     int64_t tiles;
     float s_w, c_w;
@@ -52,6 +53,7 @@ __device__ __forceinline__ bool elect_one() {
     return p != 0;
 }
 
+template <bool kF32>
 __global__ void __launch_bounds__(kHThreads, 1)
 conv3x3_halo_kernel(HaloArgs a) {
     extern __shared__ uint8_t smem_raw[];
@@ -180,9 +182,12 @@ conv3x3_halo_kernel(HaloArgs a) {
         const int lg = warp & 3, quarter = (warp - 2) >> 2;
         const int row = 32 * lg + lane;
         const int ty = row >> 3, tx = row & 7;
-        const QuantConsts q0 = consts_from_slot(*a.out_slot[0], 8, 0, 0.f, 0.f);
-        QuantConsts q1 = q0;
-        if (a.y[1]) q1 = consts_from_slot(*a.out_slot[1], 8, 0, 0.f, 0.f);
+        QuantConsts q0 = {}, q1 = {};
+        if (!kF32) {
+            q0 = consts_from_slot(*a.out_slot[0], 8, 0, 0.f, 0.f);
+            q1 = q0;
+            if (a.y[1]) q1 = consts_from_slot(*a.out_slot[1], 8, 0, 0.f, 0.f);
+        }
         const float fa = __fmul_rn(sx, a.s_w), fr = __fmul_rn(sx, a.c_w);
         const float floor_v = a.relu ? 0.0f : -INFINITY;
         int acc = 0; uint32_t aphase = 0;
@@ -208,6 +213,7 @@ conv3x3_halo_kernel(HaloArgs a) {
             mbar_wait(tfull0 + 8 * acc, aphase);
             tc_fence_after();
             const uint32_t tbase = tmem + ((uint32_t)(32 * lg) << 16) + (uint32_t)(acc * a.npass);
+            float lo = INFINITY, hi = -INFINITY;
             for (int chunk = quarter; chunk * 16 < n_real; chunk += kHEpiWarps / 4) {
                 uint32_t d[16];
                 asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, "
@@ -246,17 +252,36 @@ conv3x3_halo_kernel(HaloArgs a) {
 #pragma unroll
                         for (int j = 0; j < 16; ++j) yv[j] = j < nv ? yv[j] : 0.0f;
                     }
-                    const int64_t off = g * a.cp_out + o0 + chunk * 16;
-                    for (int gi = 0; gi < 2; ++gi) {
-                        if (!a.y[gi]) break;
-                        uint32_t w[4];
-                        pack_codes<16>(yv, gi ? q1 : q0, w);
-                        if (nv < 16) {
+                    if (kF32) {
+                        float *py = a.yf + (((int64_t)n * a.O + o0 + chunk * 16) * a.H + oh) * a.W + ow;
+                        const int64_t plane = (int64_t)a.H * a.W;
 #pragma unroll
-                            for (int q4 = 0; q4 < 4; ++q4) w[q4] = keep_left(w[q4], nv - 4 * q4);
+                        for (int j = 0; j < 16; ++j) {
+                            if (j < nv) {
+                                py[j * plane] = yv[j];
+                                lo = fminf(lo, yv[j]); hi = fmaxf(hi, yv[j]);
+                            }
                         }
-                        *reinterpret_cast<uint4 *>(a.y[gi] + off) = make_uint4(w[0], w[1], w[2], w[3]);
+                    } else {
+                        const int64_t off = g * a.cp_out + o0 + chunk * 16;
+                        for (int gi = 0; gi < 2; ++gi) {
+                            if (!a.y[gi]) break;
+                            uint32_t w[4];
+                            pack_codes<16>(yv, gi ? q1 : q0, w);
+                            if (nv < 16) {
+#pragma unroll
+                                for (int q4 = 0; q4 < 4; ++q4) w[q4] = keep_left(w[q4], nv - 4 * q4);
+                            }
+                            *reinterpret_cast<uint4 *>(a.y[gi] + off) = make_uint4(w[0], w[1], w[2], w[3]);
+                        }
                     }
+                }
+            }
+            if (kF32 && a.stats) {                                  // per-sample extrema, encoded (a tile is one image)
+                lo = warp_min(lo); hi = warp_max(hi);
+                if (lane == 0 && hi >= lo) {
+                    atomicMax(a.stats + 2 * n, enc_ordered(-lo));
+                    atomicMax(a.stats + 2 * n + 1, enc_ordered(hi));
                 }
             }
             tc_fence_before();
@@ -318,24 +343,18 @@ using namespace dfq;
 extern "C" int dfq_conv_q8_halo_k_host(int C) { return 9 * (((C + 15) / 16 + 3) / 4 * 4) * 16; }
 
 namespace dfq {
-int conv_q8_halo(const DfqConvQ8Desc *d, void *stream) {
-    if (d->kh != 3 || d->kw != 3 || d->stride != 1 || d->dil != 1 || d->pad != 1 || d->OH != d->H || d->OW != d->W)
-        return (int)cudaErrorInvalidValue;
-    HaloArgs a = {};
-    const int Cp = (d->C + 15) / 16 * 16;
+static int halo_launch(HaloArgs &a, int o_cap, bool f32, void *stream) {
+    const int Cp = (a.C + 15) / 16 * 16;
     a.cpt = ((Cp / 16) + 3) / 4 * 4;
     const int kq = 9 * a.cpt * 16;
     int64_t bytes;
-    int e = dfq_pw_i8_plan_cap_host(d->O, kq, d->o_cap, &a.n_pass, &a.o_per_pass, &a.npass, &a.slabs, &bytes);
+    int e = dfq_pw_i8_plan_cap_host(a.O, kq, o_cap, &a.n_pass, &a.o_per_pass, &a.npass, &a.slabs, &bytes);
     if (e) return e;
     if (a.slabs != 9 * a.cpt / 4) return (int)cudaErrorInvalidValue;
-    a.x = d->x; a.wpk = d->wpk; a.wr = d->wr; a.wrt = d->wrt; a.bias = d->bias; a.in_slot = (const RangeSlot *)d->in_slot;
-    a.out_slot[0] = (const RangeSlot *)d->out_slot0; a.out_slot[1] = (const RangeSlot *)d->out_slot1;
-    a.y[0] = d->y0; a.y[1] = d->y1; a.cp_out = (d->O + 15) / 16 * 16;
-    a.N = d->N; a.C = d->C; a.H = d->H; a.W = d->W; a.O = d->O; a.relu = d->relu; a.s_w = d->s_w; a.c_w = d->c_w;
-    a.tiles_x = (d->W + kHTX - 1) / kHTX; a.tiles_y = (d->H + kHTY - 1) / kHTY;
-    a.tiles = (int64_t)d->N * a.tiles_x * a.tiles_y;
-    if (a.tiles > 0x7fffffffll || (int64_t)d->N * d->H * d->W > 0x7fffffffll) return (int)cudaErrorInvalidValue;
+    a.cp_out = (a.O + 15) / 16 * 16;
+    a.tiles_x = (a.W + kHTX - 1) / kHTX; a.tiles_y = (a.H + kHTY - 1) / kHTY;
+    a.tiles = (int64_t)a.N * a.tiles_x * a.tiles_y;
+    if (a.tiles > 0x7fffffffll || (int64_t)a.N * a.H * a.W > 0x7fffffffll) return (int)cudaErrorInvalidValue;
     a.tmem_cols = 32;
     while (a.tmem_cols < 2 * a.npass) a.tmem_cols *= 2;
     if (a.tmem_cols > 512) return (int)cudaErrorInvalidValue;
@@ -345,20 +364,54 @@ int conv_q8_halo(const DfqConvQ8Desc *d, void *stream) {
     if (2 * halo_bytes + 2 * bslab + tap_bytes + 128 > smem_cap) return (int)cudaErrorInvalidValue;
     int stages = (int)((smem_cap - 2 * halo_bytes - tap_bytes - 128) / bslab);
     if (stages > kHMaxStages) stages = kHMaxStages;
-    { const char *e = getenv("DFQ_HALO_STAGES"); if (e && atoi(e) >= 2 && atoi(e) < stages) stages = atoi(e); }
     a.stages = stages;
     const size_t smem = 2 * halo_bytes + (size_t)stages * bslab + tap_bytes + 128;
     static bool configured = false;
     if (!configured) {
-        cudaError_t ce = cudaFuncSetAttribute(conv3x3_halo_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_cap);
+        cudaError_t ce = cudaFuncSetAttribute(conv3x3_halo_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_cap);
+        if (ce == cudaSuccess)
+            ce = cudaFuncSetAttribute(conv3x3_halo_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_cap);
         if (ce != cudaSuccess) return (int)ce;
         configured = true;
     }
     int64_t per_pass = (int64_t)sm_count() / a.n_pass;          // one CTA per SM (two accumulators = all TMEM columns at N = 256)
     if (per_pass < 1) per_pass = 1;
     if (per_pass > a.tiles) per_pass = a.tiles;
-    conv3x3_halo_kernel<<<(unsigned)(per_pass * a.n_pass), kHThreads, smem, (cudaStream_t)stream>>>(a);
+    const unsigned grid = (unsigned)(per_pass * a.n_pass);
+    if (f32) conv3x3_halo_kernel<true><<<grid, kHThreads, smem, (cudaStream_t)stream>>>(a);
+    else conv3x3_halo_kernel<false><<<grid, kHThreads, smem, (cudaStream_t)stream>>>(a);
     g_launches += 1;
     return (int)cudaGetLastError();
+}
+
+// the shape both forms cover; `smem_ok`: two halo buffers + at least two weight slabs fit
+bool conv_halo_covers(int C, int O, int kh, int kw, int stride, int pad, int dil) {
+    if (kh != 3 || kw != 3 || stride != 1 || dil != 1 || pad != 1) return false;
+    const int cpt = (((C + 15) / 16) + 3) / 4 * 4;
+    const int npass = O >= 256 ? 256 : (O + 15) / 16 * 16;
+    return 2 * (size_t)cpt * kHChunk + 2 * (size_t)npass * kHSlab + 9 * (size_t)npass * 4 + 128 <= 227 * 1024 - 4096;
+}
+
+int conv_q8_halo(const DfqConvQ8Desc *d, void *stream) {
+    if (!conv_halo_covers(d->C, d->O, d->kh, d->kw, d->stride, d->pad, d->dil) || d->OH != d->H || d->OW != d->W)
+        return (int)cudaErrorInvalidValue;
+    HaloArgs a = {};
+    a.x = d->x; a.wpk = d->wpk; a.wr = d->wr; a.wrt = d->wrt; a.bias = d->bias; a.in_slot = (const RangeSlot *)d->in_slot;
+    a.out_slot[0] = (const RangeSlot *)d->out_slot0; a.out_slot[1] = (const RangeSlot *)d->out_slot1;
+    a.y[0] = d->y0; a.y[1] = d->y1;
+    a.N = d->N; a.C = d->C; a.H = d->H; a.W = d->W; a.O = d->O; a.relu = d->relu; a.s_w = d->s_w; a.c_w = d->c_w;
+    return halo_launch(a, d->o_cap, false, stream);
+}
+
+// dynamic-range plan (dfq_conv_i8 with halo != 0): the input already quantised into `codes` by the pre-pass
+int conv_i8_halo(const DfqConvI8Desc *d, const int8_t *codes, void *stream) {
+    if (!conv_halo_covers(d->C, d->O, d->kh, d->kw, d->stride, d->pad, d->dil) || d->OH != d->H || d->OW != d->W ||
+        d->bits != 8 || !codes)
+        return (int)cudaErrorInvalidValue;
+    HaloArgs a = {};
+    a.x = codes; a.wpk = d->wpk; a.wr = d->wr; a.wrt = d->wrt; a.bias = d->bias; a.in_slot = (const RangeSlot *)d->in_slot;
+    a.yf = d->y; a.stats = d->out_stats;
+    a.N = d->N; a.C = d->C; a.H = d->H; a.W = d->W; a.O = d->O; a.relu = d->relu; a.s_w = d->s_w; a.c_w = d->c_w;
+    return halo_launch(a, d->o_cap, true, stream);
 }
 }  // namespace dfq

@@ -942,6 +942,12 @@ extern "C" int64_t dfq_conv_i8_scratch_bytes(int N, int C, int H, int W) {
     return (int64_t)N * H * W * ((C + 15) / 16 * 16);
 }
 
+namespace dfq {
+int conv_q8_tma(const DfqConvQ8Desc *d, void *stream);       // q8.cu
+int conv_q8_halo(const DfqConvQ8Desc *d, void *stream);      // conv_halo.cu
+int conv_i8_halo(const DfqConvI8Desc *d, const int8_t *codes, void *stream);
+}
+
 extern "C" int dfq_conv_i8(const DfqConvI8Desc *d, void *stream) {
     if (!d || !d->x || !d->y || !d->wpk || !d->wr || !d->wrt || !d->in_slot || d->N <= 0 || d->bits < 1 || d->bits > 8 ||
         d->kh <= 0 || d->kw <= 0 || d->kh * d->kw > 32 || d->stride <= 0 || d->dil <= 0 || d->pad < 0)
@@ -970,6 +976,9 @@ extern "C" int dfq_conv_i8(const DfqConvI8Desc *d, void *stream) {
         quant_nhwc_s8_kernel<<<grid, kThreads, 0, (cudaStream_t)stream>>>(d->x, d->scratch, a.slot, d->bits, d->C, HW, Cp);
         g_launches += 1;
         a.xq = d->scratch;
+        if (d->halo) return conv_i8_halo(d, d->scratch, stream);     // wpk in the halo layout (3 x 3, stride 1, pad 1)
+    } else if (d->halo) {
+        return (int)cudaErrorInvalidValue;
     }
     return pw_i8_launch(a, true, a.G, (cudaStream_t)stream);
 }
@@ -977,11 +986,6 @@ extern "C" int dfq_conv_i8(const DfqConvI8Desc *d, void *stream) {
 // Static-range form (eval_q8.py): the input already IS centred s8 codes, NHWC with the channels padded to 16 (what every
 // producer of the u8 plan writes), so there is no quantising pre-pass, and the output leaves as codes on the grid(s) of
 // its consumer(s).  Same pipeline, same packed weights, same padding correction as dfq_conv_i8.
-namespace dfq {
-int conv_q8_tma(const DfqConvQ8Desc *d, void *stream);       // q8.cu
-int conv_q8_halo(const DfqConvQ8Desc *d, void *stream);      // conv_halo.cu
-}
-
 extern "C" int dfq_conv_q8(const DfqConvQ8Desc *d, void *stream) {
     if (!d || !d->x || !d->y0 || !d->out_slot0 || !d->wpk || !d->wr || !d->wrt || !d->in_slot || d->N <= 0 ||
         d->kh <= 0 || d->kw <= 0 || d->kh * d->kw > 32 || d->stride <= 0 || d->dil <= 0 || d->pad < 0 ||

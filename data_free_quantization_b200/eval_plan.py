@@ -486,17 +486,24 @@ class EvalPlan:
         from . import pw_i8
         if not 1 <= int(m.quant.num_bits) <= 8:
             return None
-        pk = pw_i8.pack_weight_conv(wq, getattr(m, "num_bits", None),
-                                    o_cap=pw_i8.choose_o_cap(out.numel // out.shape[1], wq.shape[0],
-                                                             fill=self.narrow_passes)
-                                    if self.narrow_passes > 0 else 0)
+        # 3 x 3, stride 1, pad 1 on 8-bit activations (DeepLab's decoder): the halo kernel (csrc/conv_halo.cu)
+        halo = (tuple(wq.shape[2:]) == (3, 3) and (stride, pad, dil) == (1, 1, 1) and int(m.quant.num_bits) == 8
+                and os.environ.get("DFQ_CONV_HALO", "1") != "0")
+        if halo:
+            from .eval_q8 import pack_conv_halo
+            pk = pack_conv_halo(wq)
+        else:
+            pk = pw_i8.pack_weight_conv(wq, getattr(m, "num_bits", None),
+                                        o_cap=pw_i8.choose_o_cap(out.numel // out.shape[1], wq.shape[0],
+                                                                 fill=self.narrow_passes)
+                                        if self.narrow_passes > 0 else 0)
         if pk is None:
             return None
         stats = None if out.stats is None else out.stats.data_ptr()
         scratch = pw_i8.conv_scratch(src.shape, self.dev)        # the input quantised once, s8 NHWC
         desc = pw_i8.make_conv_desc(src.buf.view(src.shape), out.buf.view(out.shape), pk, bq,
                                     self.slots[st["slot"]].data_ptr(), stats, stride, pad, dil, st["relu"],
-                                    int(m.quant.num_bits), scratch=scratch)
+                                    int(m.quant.num_bits), scratch=scratch, halo=halo)
         self.keep += [pk, desc, scratch]
         self.i8_layers.append(st["name"])
         return lambda: pw_i8.launch_conv(desc)

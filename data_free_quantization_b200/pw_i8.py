@@ -163,7 +163,7 @@ def conv_scratch(x_shape, device):
     return torch.empty(int(L.lib().dfq_conv_i8_scratch_bytes(N, C, H, W)), dtype=torch.int8, device=device)
 
 
-def make_conv_desc(x, y, pk, bias, slot_ptr, stats_ptr, stride, pad, dil, relu, bits, scratch=None):
+def make_conv_desc(x, y, pk, bias, slot_ptr, stats_ptr, stride, pad, dil, relu, bits, scratch=None, halo=False):
     """DfqConvI8Desc for x [N, C, H, W] -> y [N, O, OH, OW] (both contiguous fp32 CUDA tensors).  With `scratch`
     (conv_scratch) the input is quantised once and the taps read 16-byte code words -- the form for k x k > 1."""
     C, kh, kw = pk.geom
@@ -179,6 +179,7 @@ def make_conv_desc(x, y, pk, bias, slot_ptr, stats_ptr, stride, pad, dil, relu, 
     d.s_w, d.c_w = pk.s_w, pk.c_w
     d.scratch = None if scratch is None else scratch.data_ptr()
     d.o_cap = pk.o_cap
+    d.halo = 1 if halo else 0      # pk packed by eval_q8.pack_conv_halo
     return d
 
 

@@ -23,7 +23,7 @@
 extern "C" {
 #endif
 
-#define DFQ_ABI_VERSION 20
+#define DFQ_ABI_VERSION 21
 
 #if defined(__GNUC__)
 #pragma GCC visibility push(default)   /* the library is built with -fvisibility=hidden */
@@ -330,7 +330,9 @@ typedef struct DfqConvI8Desc {
     int8_t *scratch;         /* NULL, or dfq_conv_i8_scratch_bytes(N, C, H, W) device bytes: the input is then
                               * quantised ONCE into s8 NHWC codes and every tap reads 16-byte words (k x k > 1) */
     int32_t o_cap;           /* the o_cap wpk was packed with (0 = 256 channels per pass)       */
-    int32_t reserved;
+    int32_t halo;            /* 1 (3 x 3, stride 1, pad 1, dilation 1, 8-bit activations, scratch given): wpk is packed
+                              * over the [tap][chunk] reduction of dfq_conv_q8_halo_k_host and the halo kernel runs (the
+                              * tile's input halo in shared memory, taps by shifted descriptors: see DfqConvQ8Desc.tma) */
 } DfqConvI8Desc;
 int dfq_conv_i8_k_host(int C, int kh, int kw);
 int64_t dfq_conv_i8_scratch_bytes(int N, int C, int H, int W);
