@@ -77,7 +77,7 @@ struct EpiCtx {
 
 // One accumulator row (this thread's pixel) of one tile: units of U columns alternate between the two warps of the
 // lane group; SUM_k a and the first unit arrive behind ONE wait, the next unit is in flight behind the arithmetic.
-template <int U, bool CONV>
+template <int U, bool CONV, bool MAPPED>
 __device__ __forceinline__ void epi_tile(const EpiCtx &e, const QuantConsts &q0, const QuantConsts &q1) {
     const PwQ8Args &a = *e.a;
     const bool has0 = a.y[0] != nullptr, has1 = a.y[1] != nullptr;
@@ -132,7 +132,7 @@ __device__ __forceinline__ void epi_tile(const EpiCtx &e, const QuantConsts &q0,
 #pragma unroll
                     for (int j4 = 0; j4 < U / 4; ++j4) w[j4] = keep_left(w[j4], nv - 4 * j4);
                 }
-                int8_t *dst = a.y[t] + (int64_t)e.gp[t] * a.cp_out + e.o0 + unit * U;
+                int8_t *dst = a.y[t] + (MAPPED ? (int64_t)e.gp[t] : e.g) * a.cp_out + e.o0 + unit * U;
                 if (U == 16) *reinterpret_cast<uint4 *>(dst) = make_uint4(w[0], w[1], w[U / 4 - 2], w[U / 4 - 1]);
                 else *reinterpret_cast<uint2 *>(dst) = make_uint2(w[0], w[1]);
             }
@@ -145,12 +145,12 @@ __device__ __forceinline__ void epi_tile(const EpiCtx &e, const QuantConsts &q0,
         for (int cpad = done; cpad < row_end; cpad += 8) {
 #pragma unroll
             for (int t = 0; t < 2; ++t)
-                if (t ? has1 : has0) *reinterpret_cast<uint2 *>(a.y[t] + (int64_t)e.gp[t] * a.cp_out + e.o0 + cpad) = make_uint2(0u, 0u);
+                if (t ? has1 : has0) *reinterpret_cast<uint2 *>(a.y[t] + (MAPPED ? (int64_t)e.gp[t] : e.g) * a.cp_out + e.o0 + cpad) = make_uint2(0u, 0u);
         }
     }
 }
 
-template <bool CONV>
+template <bool CONV, bool MAPPED>
 __global__ void __launch_bounds__(kQThreads, 2)
 pwq8_kernel(const __grid_constant__ CUtensorMap tmA, PwQ8Args a) {
     extern __shared__ uint8_t smem_raw[];
@@ -297,9 +297,10 @@ pwq8_kernel(const __grid_constant__ CUtensorMap tmA, PwQ8Args a) {
             tc_fence_after();
             const uint32_t tbase = tmem + ((uint32_t)(32 * lg) << 16) + (uint32_t)(acc * a.npass);
             const EpiCtx ctx = {&a, chan_c, tbase, g, o0, n_real, half, valid, small_acc, fa, fr, floor_v, oob, tap_c,
-                                {valid ? (int)q8_out_pixel(a.omap[0], g) : 0, valid ? (int)q8_out_pixel(a.omap[1], g) : 0}};
-            if (n_real <= 16) epi_tile<8, CONV>(ctx, q0, q1);      // a 16-channel layer keeps all eight epilogue warps busy
-            else epi_tile<16, CONV>(ctx, q0, q1);
+                                {MAPPED && valid ? (int)q8_out_pixel(a.omap[0], g) : 0,
+                                 MAPPED && valid ? (int)q8_out_pixel(a.omap[1], g) : 0}};
+            if (n_real <= 16) epi_tile<8, CONV, MAPPED>(ctx, q0, q1);      // a 16-channel layer keeps all eight epilogue warps busy
+            else epi_tile<16, CONV, MAPPED>(ctx, q0, q1);
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(tempty0 + 8 * acc);
@@ -339,7 +340,7 @@ __device__ __forceinline__ float small_int_to_float(int v) {      // exact for |
 
 // a.pad is 1 (the convolution pads with zeros) or 0 (DeepLab: F.pad ran ahead of the QuantMeasure, the padded tensor exists
 // as codes -- dfq_pad_q8 -- and every tap is in bounds).
-template <int S, bool DUAL>
+template <int S, bool DUAL, int PAD>
 __global__ void __launch_bounds__(kThreads, 2)
 dwq8_kernel(DwQ8Args a) {
     constexpr int P = DwStrip<S>::value;
@@ -357,7 +358,7 @@ dwq8_kernel(DwQ8Args a) {
     const QuantConsts q0 = consts_from_slot(*a.out_slot[0], 8, 0, 0.f, 0.f);
     QuantConsts q1 = q0;
     if (DUAL) q1 = consts_from_slot(*a.out_slot[1], 8, 0, 0.f, 0.f);
-    const int iy0 = oy * S - a.pad;
+    const int iy0 = oy * S - PAD;
     const bool rowok[3] = {(unsigned)iy0 < (unsigned)a.H, (unsigned)(iy0 + 1) < (unsigned)a.H,
                            (unsigned)(iy0 + 2) < (unsigned)a.H};
     uint32_t wr[3][4];                                            // [row][channel] = (w0, w1, w2, 0) centred s8
@@ -400,7 +401,7 @@ dwq8_kernel(DwQ8Args a) {
     const int64_t orow = ((int64_t)n * a.OH + oy) * a.OW;
     const int left = a.C - c0;
     for (int sp = 0; sp < a.strips; ++sp) {
-        const int ox0 = sp * P, ixs = ox0 * S - a.pad;
+        const int ox0 = sp * P, ixs = ox0 * S - PAD;
         // 12 input columns x 3 rows (zero words outside the image), transposed per 4-column block
         uint32_t t[3][3][4];                                      // [row][block][channel]: 4 adjacent pixels of a channel
 #pragma unroll
@@ -441,7 +442,7 @@ dwq8_kernel(DwQ8Args a) {
                     sa[c] = __dp4a((int)win, (int)ones[r], sa[c]);
                 }
             }
-            const int ixl = ox * S - a.pad;
+            const int ixl = ox * S - PAD;
             const bool lin = ixl >= 0, rin = ixl + 2 < a.W;      // left / right tap column in bounds (centre always is)
             float yv[4];
 #pragma unroll
@@ -797,7 +798,9 @@ extern "C" int dfq_pw_q8(const DfqPwQ8Desc *d, void *stream) {
     }
     static size_t configured = 0;
     if (configured < smem) {
-        cudaError_t ce = cudaFuncSetAttribute(pwq8_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_cap);
+        cudaError_t ce = cudaFuncSetAttribute(pwq8_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_cap);
+        if (ce == cudaSuccess)
+            ce = cudaFuncSetAttribute(pwq8_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_cap);
         if (ce != cudaSuccess) return (int)ce;
         configured = smem_cap;
     }
@@ -813,7 +816,7 @@ extern "C" int dfq_pw_q8(const DfqPwQ8Desc *d, void *stream) {
                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return (int)cudaErrorInvalidValue;
     int occ = 0;
-    cudaError_t ce = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, pwq8_kernel<false>, kQThreads, smem);
+    cudaError_t ce = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, pwq8_kernel<false, false>, kQThreads, smem);
     if (ce != cudaSuccess) return (int)ce;
     if (occ < 1) return (int)cudaErrorLaunchOutOfResources;
     if (occ > want_ctas) occ = want_ctas;
@@ -821,7 +824,8 @@ extern "C" int dfq_pw_q8(const DfqPwQ8Desc *d, void *stream) {
     if (per_pass < 1) per_pass = 1;
     if (per_pass > a.tiles) per_pass = a.tiles;
     const unsigned grid = (unsigned)(per_pass * a.n_pass);
-    pwq8_kernel<false><<<grid, kQThreads, smem, (cudaStream_t)stream>>>(tm, a);
+    if (a.omap[0].Wp || a.omap[1].Wp) pwq8_kernel<false, true><<<grid, kQThreads, smem, (cudaStream_t)stream>>>(tm, a);
+    else pwq8_kernel<false, false><<<grid, kQThreads, smem, (cudaStream_t)stream>>>(tm, a);
     g_launches += 1;
     return (int)cudaGetLastError();
 }
@@ -896,7 +900,7 @@ int conv_q8_tma(const DfqConvQ8Desc *d, void *stream) {
     }
     static bool configured = false;
     if (!configured) {
-        cudaError_t ce = cudaFuncSetAttribute(pwq8_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_cap);
+        cudaError_t ce = cudaFuncSetAttribute(pwq8_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_cap);
         if (ce != cudaSuccess) return (int)ce;
         configured = true;
     }
@@ -912,14 +916,14 @@ int conv_q8_tma(const DfqConvQ8Desc *d, void *stream) {
                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return (int)cudaErrorInvalidValue;
     int occ = 0;
-    cudaError_t ce = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, pwq8_kernel<true>, kQThreads, smem);
+    cudaError_t ce = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, pwq8_kernel<true, false>, kQThreads, smem);
     if (ce != cudaSuccess) return (int)ce;
     if (occ < 1) return (int)cudaErrorLaunchOutOfResources;
     if (occ > want_ctas) occ = want_ctas;
     int64_t per_pass = ((int64_t)sm_count() * occ) / a.n_pass;
     if (per_pass < 1) per_pass = 1;
     if (per_pass > a.tiles) per_pass = a.tiles;
-    pwq8_kernel<true><<<(unsigned)(per_pass * a.n_pass), kQThreads, smem, (cudaStream_t)stream>>>(tm, a);
+    pwq8_kernel<true, false><<<(unsigned)(per_pass * a.n_pass), kQThreads, smem, (cudaStream_t)stream>>>(tm, a);
     g_launches += 1;
     return (int)cudaGetLastError();
 }
@@ -953,12 +957,16 @@ extern "C" int dfq_dw_q8(const DfqDwQ8Desc *d, void *stream) {
     const int64_t total = (int64_t)a.N * a.OH * (a.Cp / 4);
     if (total >= 0x7fffffffll) return (int)cudaErrorInvalidValue;
     const unsigned grid = (unsigned)((total + kThreads - 1) / kThreads);
-    if (d->stride == 1) {
-        if (d->y1) dwq8_kernel<1, true><<<grid, kThreads, 0, st>>>(a);
-        else dwq8_kernel<1, false><<<grid, kThreads, 0, st>>>(a);
-    } else {
-        if (d->y1) dwq8_kernel<2, true><<<grid, kThreads, 0, st>>>(a);
-        else dwq8_kernel<2, false><<<grid, kThreads, 0, st>>>(a);
+    const int variant = (d->stride == 2 ? 4 : 0) | (d->y1 ? 2 : 0) | (a.pad ? 1 : 0);
+    switch (variant) {
+    case 0: dwq8_kernel<1, false, 0><<<grid, kThreads, 0, st>>>(a); break;
+    case 1: dwq8_kernel<1, false, 1><<<grid, kThreads, 0, st>>>(a); break;
+    case 2: dwq8_kernel<1, true, 0><<<grid, kThreads, 0, st>>>(a); break;
+    case 3: dwq8_kernel<1, true, 1><<<grid, kThreads, 0, st>>>(a); break;
+    case 4: dwq8_kernel<2, false, 0><<<grid, kThreads, 0, st>>>(a); break;
+    case 5: dwq8_kernel<2, false, 1><<<grid, kThreads, 0, st>>>(a); break;
+    case 6: dwq8_kernel<2, true, 0><<<grid, kThreads, 0, st>>>(a); break;
+    default: dwq8_kernel<2, true, 1><<<grid, kThreads, 0, st>>>(a); break;
     }
     g_launches += 1;
     return (int)cudaGetLastError();
