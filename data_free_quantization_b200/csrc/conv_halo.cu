@@ -53,30 +53,42 @@ __device__ __forceinline__ bool elect_one() {
     return p != 0;
 }
 
+// Launched as clusters of TWO CTAs (neighbouring SMs) that work on different tiles of the same pass and SHARE the weight
+// stream: each CTA copies half of every slab and multicasts it into both shared memories, and a ring stage is refilled
+// only when the MMAs of both CTAs have retired it (tcgen05.commit multicast onto both `bempty` barriers).  At one CTA per
+// SM the weights were 720 KB per tile against 58 KB of activations and the kernel sat on the L2 -> SM bandwidth this
+// GPU delivered (8.9 TB/s, tensor pipe 51 %).  Both CTAs of a pair run the same number of tile iterations (a tile index
+// past the end is a ghost: loads and stores are skipped, the barriers are still walked).
 template <bool kF32>
-__global__ void __launch_bounds__(kHThreads, 1)
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kHThreads, 1)
 conv3x3_halo_kernel(HaloArgs a) {
     extern __shared__ uint8_t smem_raw[];
     __shared__ __align__(8) uint64_t bars[2 * kHMaxStages + 8];   // bfull | bempty | hfull[2] hempty[2] tfull[2] tempty[2]
     __shared__ uint32_t tmem_base_s;
     __shared__ __align__(16) float chan_c[256];
     __shared__ int S_s[2][kHY * kHX];                             // per halo pixel: sum over channels of the codes
+    __shared__ uint32_t a_off[128];                               // per weight slab: where its first chunk's A operand starts
+                                                                  // inside a halo buffer, in 16-byte units (tap shift + chunk)
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~(uintptr_t)127);
     const uint32_t halo_bytes = (uint32_t)a.cpt * kHChunk;
     const uint32_t bslab = (uint32_t)a.npass * kHSlab;
     const uint32_t sH_u = smem_u32(smem), sB_u = sH_u + 2 * halo_bytes;
-    float *tap_c = reinterpret_cast<float *>(smem + 2 * halo_bytes + (size_t)a.stages * bslab);
+    float *tap_c = reinterpret_cast<float *>(smem + 2 * halo_bytes + (size_t)a.stages * 2 * bslab);
     const uint32_t bfull0 = smem_u32(&bars[0]), bempty0 = bfull0 + 8 * kHMaxStages, hfull0 = bempty0 + 8 * kHMaxStages,
                    hempty0 = hfull0 + 16, tfull0 = hempty0 + 16, tempty0 = tfull0 + 16;
-    const int pass = blockIdx.x % a.n_pass;
-    const int64_t tile0 = blockIdx.x / a.n_pass, tstep = gridDim.x / a.n_pass;
+    const uint32_t crank = cluster_ctarank();                    // 0 / 1 inside the pair
+    const int pair = blockIdx.x >> 1, pairs = gridDim.x >> 1;
+    const int pass = pair % a.n_pass;
+    const int64_t tstep = (int64_t)(pairs / a.n_pass) * 2;
+    const int64_t tile0 = (int64_t)(pair / a.n_pass) * 2 + crank;
+    const int64_t tile_end = (a.tiles + tstep - 1) / tstep * tstep;   // every CTA walks the same number of iterations
     const int o0 = pass * a.o_per_pass, n_real = min(a.o_per_pass, a.O - o0);
     const int per_img = a.tiles_x * a.tiles_y;
 
     if (tid == 0) {
-        for (int i = 0; i < a.stages; ++i) { mbar_init(bfull0 + 8 * i, 1); mbar_init(bempty0 + 8 * i, 1); }
+        for (int i = 0; i < a.stages; ++i) { mbar_init(bfull0 + 8 * i, 1); mbar_init(bempty0 + 8 * i, 2); }   // bempty: both CTAs' commits
         for (int i = 0; i < 2; ++i) {
             mbar_init(hfull0 + 8 * i, kHLoaders); mbar_init(hempty0 + 8 * i, 1 + kHEpiWarps);   // hempty: one commit + the epilogue warps
             mbar_init(tfull0 + 8 * i, 1); mbar_init(tempty0 + 8 * i, kHEpiWarps);
@@ -100,6 +112,10 @@ conv3x3_halo_kernel(HaloArgs a) {
         }
         chan_c[tid] = c;
     }
+    for (int i = tid; i < a.slabs; i += kHThreads) {
+        const int q = 4 * i, tap = q / a.cpt, cc = q - tap * a.cpt;
+        a_off[i] = (uint32_t)(cc * (kHChunk >> 4) + (tap / 3) * kHX + tap % 3);
+    }
     {   // what one out-of-image tap contributed through c_x, per output channel of this pass
         const float ccw = __fmul_rn(__fmul_rn((float)a.C, a.c_w), cx);
         for (int i = tid; i < 9 * a.npass; i += kHThreads) {
@@ -110,6 +126,7 @@ conv3x3_halo_kernel(HaloArgs a) {
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
+    cluster_sync();                                              // the peer's barriers exist before anything is sent to them
     const uint32_t tmem = tmem_base_s;
 
     auto tile_origin = [&](int64_t tile, int &n, int &oh0, int &ow0) {
@@ -123,11 +140,13 @@ conv3x3_halo_kernel(HaloArgs a) {
         if (lane == 0) {
             const int8_t *wsrc = a.wpk + (int64_t)pass * a.slabs * bslab;
             int stage = 0; uint32_t phase = 0;
-            for (int64_t tile = tile0; tile < a.tiles; tile += tstep) {
-                for (int s = 0; s < a.slabs; ++s) {
+            for (int64_t tile = tile0; tile < tile_end; tile += tstep) {
+                for (int s = 0; s < a.slabs; s += 2) {               // a ring stage = two consecutive 64-byte slabs
+                    const uint32_t bytes = (uint32_t)min(2, a.slabs - s) * bslab;
                     mbar_wait(bempty0 + 8 * stage, phase ^ 1);
-                    mbar_expect_tx(bfull0 + 8 * stage, bslab);
-                    bulk_g2s(sB_u + stage * bslab, wsrc + (int64_t)s * bslab, bslab, bfull0 + 8 * stage);
+                    mbar_expect_tx(bfull0 + 8 * stage, bytes);                  // this CTA's half + the peer's half
+                    bulk_g2s_mc(sB_u + stage * 2 * bslab + crank * (bytes / 2),
+                                wsrc + (int64_t)s * bslab + crank * (bytes / 2), bytes / 2, bfull0 + 8 * stage, (uint16_t)3);
                     if (++stage == a.stages) { stage = 0; phase ^= 1; }
                 }
             }
@@ -142,32 +161,30 @@ conv3x3_halo_kernel(HaloArgs a) {
         int acc = 0; uint32_t aphase = 0;
         int hb = 0; uint32_t hphase = 0;
         const uint64_t bd0 = desc_plain(sB_u, a.npass * 16, 128);
-        for (int64_t tile = tile0; tile < a.tiles; tile += tstep) {
+        for (int64_t tile = tile0; tile < tile_end; tile += tstep) {
             mbar_wait(tempty0 + 8 * acc, aphase ^ 1);
             mbar_wait(hfull0 + 8 * hb, hphase);
             tc_fence_after();
             const uint32_t d = tmem + (uint32_t)(acc * a.npass);
-            uint64_t ad = desc_plain(sH_u + hb * halo_bytes, kHChunk, kHX * 16);
-            int cc = 0, tx = 0;
-            for (int s = 0; s < a.slabs; ++s) {
+            const uint64_t ad0 = desc_plain(sH_u + hb * halo_bytes, kHChunk, kHX * 16);
+            for (int s = 0; s < a.slabs; s += 2) {
                 mbar_wait(bfull0 + 8 * stage, phase);
                 tc_fence_after();
-                const uint64_t bd = bd0 + (uint64_t)(stage * (bslab >> 4));
+                const uint64_t bd = bd0 + (uint64_t)(stage * (2 * bslab >> 4));
+                const uint64_t ada = ad0 + a_off[s];
+                const bool two = s + 1 < a.slabs;
+                const uint64_t adb = ad0 + a_off[two ? s + 1 : s];
                 if (elect_one()) {
-                    umma_i8(d, ad, bd, idesc, s != 0);
-                    umma_i8(d, ad + 2 * (kHChunk >> 4), bd + (uint64_t)(2 * a.npass), idesc, 1);
-                    umma_commit(bempty0 + 8 * stage);
+                    umma_i8(d, ada, bd, idesc, s != 0);
+                    umma_i8(d, ada + 2 * (kHChunk >> 4), bd + (uint64_t)(2 * a.npass), idesc, 1);
+                    if (two) {
+                        umma_i8(d, adb, bd + (uint64_t)(bslab >> 4), idesc, 1);
+                        umma_i8(d, adb + 2 * (kHChunk >> 4), bd + (uint64_t)((bslab >> 4) + 2 * a.npass), idesc, 1);
+                    }
+                    umma_commit_mc(bempty0 + 8 * stage, (uint16_t)3);
                 }
                 __syncwarp();
                 if (++stage == a.stages) { stage = 0; phase ^= 1; }
-                cc += 4;
-                ad += 4 * (kHChunk >> 4);
-                if (cc == a.cpt) {                             // next tap: one column on, or to the next halo row
-                    cc = 0;
-                    ad -= (uint64_t)(a.cpt * (kHChunk >> 4));
-                    ad += 1;
-                    if (++tx == 3) { tx = 0; ad += kHX - 3; }
-                }
             }
             if (elect_one()) {
                 umma_commit(tfull0 + 8 * acc);
@@ -192,12 +209,12 @@ conv3x3_halo_kernel(HaloArgs a) {
         const float floor_v = a.relu ? 0.0f : -INFINITY;
         int acc = 0; uint32_t aphase = 0;
         int hb = 0; uint32_t hphase = 0;
-        for (int64_t tile = tile0; tile < a.tiles; tile += tstep) {
+        for (int64_t tile = tile0; tile < tile_end; tile += tstep) {
             int n, oh0, ow0;
             tile_origin(tile, n, oh0, ow0);
             mbar_wait(hfull0 + 8 * hb, hphase);                   // the loaders' code sums of this halo are in S_s
             const int oh = oh0 + ty, ow = ow0 + tx;
-            const bool valid = oh < a.H && ow < a.W;
+            const bool valid = tile < a.tiles && oh < a.H && ow < a.W;      // (tile >= tiles: a ghost iteration)
             int suma = 0;
             uint32_t oob = 0;
 #pragma unroll
@@ -297,13 +314,13 @@ conv3x3_halo_kernel(HaloArgs a) {
         const int hy = p / kHX, hx = p - hy * kHX;
         const int Cp16 = (a.C + 15) / 16;                          // real 16-byte chunks of a pixel
         int hb = 0; uint32_t hphase = 0;
-        for (int64_t tile = tile0; tile < a.tiles; tile += tstep) {
+        for (int64_t tile = tile0; tile < tile_end; tile += tstep) {
             int n, oh0, ow0;
             tile_origin(tile, n, oh0, ow0);
             mbar_wait(hempty0 + 8 * hb, hphase ^ 1);
             if (p < kHY * kHX) {
                 const int ih = oh0 - 1 + hy, iw = ow0 - 1 + hx;
-                const bool inb = (unsigned)ih < (unsigned)a.H && (unsigned)iw < (unsigned)a.W;
+                const bool inb = tile < a.tiles && (unsigned)ih < (unsigned)a.H && (unsigned)iw < (unsigned)a.W;
                 const uint4 *src = reinterpret_cast<const uint4 *>(a.x + (((int64_t)n * a.H + ih) * a.W + iw) * (Cp16 * 16));
                 uint8_t *dst = smem + hb * halo_bytes + p * 16;
                 int sacc = 0;
@@ -329,6 +346,7 @@ conv3x3_halo_kernel(HaloArgs a) {
     }
     tc_fence_before();
     __syncthreads();
+    cluster_sync();                                              // the peer may still multicast into / arrive on this CTA
     if (warp == 1)
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"((uint32_t)a.tmem_cols)
                      : "memory");
@@ -361,11 +379,12 @@ static int halo_launch(HaloArgs &a, int o_cap, bool f32, void *stream) {
     const size_t halo_bytes = (size_t)a.cpt * kHChunk, bslab = (size_t)a.npass * kHSlab;
     const size_t tap_bytes = 9 * (size_t)a.npass * sizeof(float);
     const size_t smem_cap = 227 * 1024 - 4096;                 // the kernel has ~2.7 KB of static shared memory
-    if (2 * halo_bytes + 2 * bslab + tap_bytes + 128 > smem_cap) return (int)cudaErrorInvalidValue;
-    int stages = (int)((smem_cap - 2 * halo_bytes - tap_bytes - 128) / bslab);
+    if (2 * halo_bytes + 4 * bslab + tap_bytes + 128 > smem_cap) return (int)cudaErrorInvalidValue;
+    int stages = (int)((smem_cap - 2 * halo_bytes - tap_bytes - 128) / (2 * bslab));   // a stage = two slabs
     if (stages > kHMaxStages) stages = kHMaxStages;
+    if (stages < 2 || a.slabs > 128) return (int)cudaErrorInvalidValue;
     a.stages = stages;
-    const size_t smem = 2 * halo_bytes + (size_t)stages * bslab + tap_bytes + 128;
+    const size_t smem = 2 * halo_bytes + (size_t)stages * 2 * bslab + tap_bytes + 128;
     static bool configured = false;
     if (!configured) {
         cudaError_t ce = cudaFuncSetAttribute(conv3x3_halo_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_cap);
@@ -374,10 +393,11 @@ static int halo_launch(HaloArgs &a, int o_cap, bool f32, void *stream) {
         if (ce != cudaSuccess) return (int)ce;
         configured = true;
     }
-    int64_t per_pass = (int64_t)sm_count() / a.n_pass;          // one CTA per SM (two accumulators = all TMEM columns at N = 256)
-    if (per_pass < 1) per_pass = 1;
-    if (per_pass > a.tiles) per_pass = a.tiles;
-    const unsigned grid = (unsigned)(per_pass * a.n_pass);
+    // clusters of two CTAs, one CTA per SM (two accumulators = all TMEM columns at N = 256); pairs share a pass
+    int64_t pairs_per_pass = (int64_t)(sm_count() / 2) / a.n_pass;
+    if (pairs_per_pass < 1) pairs_per_pass = 1;
+    if (pairs_per_pass > (a.tiles + 1) / 2) pairs_per_pass = (a.tiles + 1) / 2;
+    const unsigned grid = (unsigned)(2 * pairs_per_pass * a.n_pass);
     if (f32) conv3x3_halo_kernel<true><<<grid, kHThreads, smem, (cudaStream_t)stream>>>(a);
     else conv3x3_halo_kernel<false><<<grid, kHThreads, smem, (cudaStream_t)stream>>>(a);
     g_launches += 1;
@@ -389,7 +409,7 @@ bool conv_halo_covers(int C, int O, int kh, int kw, int stride, int pad, int dil
     if (kh != 3 || kw != 3 || stride != 1 || dil != 1 || pad != 1) return false;
     const int cpt = (((C + 15) / 16) + 3) / 4 * 4;
     const int npass = O >= 256 ? 256 : (O + 15) / 16 * 16;
-    return 2 * (size_t)cpt * kHChunk + 2 * (size_t)npass * kHSlab + 9 * (size_t)npass * 4 + 128 <= 227 * 1024 - 4096;
+    return 2 * (size_t)cpt * kHChunk + 4 * (size_t)npass * kHSlab + 9 * (size_t)npass * 4 + 128 <= 227 * 1024 - 4096;
 }
 
 int conv_q8_halo(const DfqConvQ8Desc *d, void *stream) {
