@@ -469,13 +469,13 @@ dwq8_kernel(DwQ8Args a) {
 __global__ void __launch_bounds__(kThreads)
 dwq8_generic_kernel(DwQ8Args a) {
     const unsigned cw = (unsigned)a.Cp >> 2;
-    const int64_t idx = (int64_t)blockIdx.x * kThreads + threadIdx.x;
-    if (idx >= (int64_t)a.N * a.OH * a.OW * cw) return;
+    const unsigned idx = blockIdx.x * kThreads + threadIdx.x;   // (the launcher refuses >= 2^31 threads)
+    if (idx >= (unsigned)a.N * a.OH * a.OW * cw) return;
     const int cg = (int)(idx % cw);
-    int64_t rest = idx / cw;
-    const int ox = (int)(rest % a.OW); rest /= a.OW;
-    const int oy = (int)(rest % a.OH);
-    const int n = (int)(rest / a.OH);
+    unsigned rest = idx / cw;
+    const int ox = (int)(rest % (unsigned)a.OW); rest /= (unsigned)a.OW;
+    const int oy = (int)(rest % (unsigned)a.OH);
+    const int n = (int)(rest / (unsigned)a.OH);
     const int c0 = cg * 4;
     const RangeSlot in = *a.in_slot;
     const float sx = in.scale, cx = __fmaf_rn(128.0f, sx, in.mn);
@@ -947,7 +947,7 @@ extern "C" int dfq_dw_q8(const DfqDwQ8Desc *d, void *stream) {
     if (a.pad > 1 || a.dil != 1) {
         const int64_t total = (int64_t)a.N * a.OH * a.OW * (a.Cp / 4);
         const int64_t blocks = (total + kThreads - 1) / kThreads;
-        if (blocks >= 0x7fffffffll) return (int)cudaErrorInvalidValue;
+        if (blocks >= (1ll << 23)) return (int)cudaErrorInvalidValue;
         dwq8_generic_kernel<<<(unsigned)blocks, kThreads, 0, st>>>(a);
         g_launches += 1;
         return (int)cudaGetLastError();

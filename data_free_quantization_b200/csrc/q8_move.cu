@@ -55,14 +55,14 @@ __device__ __forceinline__ void interp_word(const InterpQ8Args &a, const int8_t 
 // grid, the indices and weights computed once per 16 channels
 __global__ void __launch_bounds__(kThreads)
 interpq8_codes_kernel(InterpQ8Args a) {
-    const int chunks = a.Cp >> 4;
-    const int64_t idx = (int64_t)blockIdx.x * kThreads + threadIdx.x;
-    if (idx >= (int64_t)a.N * a.OH * a.OW * chunks) return;
+    const unsigned chunks = (unsigned)a.Cp >> 4;
+    const unsigned idx = blockIdx.x * kThreads + threadIdx.x;   // 32-bit index math (the launcher refuses >= 2^31 threads):
+    if (idx >= (unsigned)a.N * a.OH * a.OW * chunks) return;     // the 64-bit divisions were most of this kernel
     const int ch = (int)(idx % chunks);
-    int64_t rest = idx / chunks;
-    const int ox = (int)(rest % a.OW); rest /= a.OW;
-    const int oy = (int)(rest % a.OH);
-    const int n = (int)(rest / a.OH);
+    unsigned rest = idx / chunks;
+    const int ox = (int)(rest % (unsigned)a.OW); rest /= (unsigned)a.OW;
+    const int oy = (int)(rest % (unsigned)a.OH);
+    const int n = (int)(rest / (unsigned)a.OH);
     int y0, y1, x0, x1; float l1y, l1x;
     q8_interp_index(oy, a.sy, a.H, a.align, y0, y1, l1y);
     q8_interp_index(ox, a.sx, a.W, a.align, x0, x1, l1x);
@@ -104,11 +104,11 @@ interpq8_codes_kernel(InterpQ8Args a) {
 // source image is a few hundred KB of codes and stays in L1 / L2)
 __global__ void __launch_bounds__(kThreads)
 interpq8_f32_kernel(InterpQ8Args a) {
-    const int64_t idx = (int64_t)blockIdx.x * kThreads + threadIdx.x;
-    if (idx >= (int64_t)a.N * a.OH * a.OW) return;
-    const int ox = (int)(idx % a.OW);
-    const int oy = (int)((idx / a.OW) % a.OH);
-    const int n = (int)(idx / ((int64_t)a.OW * a.OH));
+    const unsigned idx = blockIdx.x * kThreads + threadIdx.x;
+    if (idx >= (unsigned)a.N * a.OH * a.OW) return;
+    const int ox = (int)(idx % (unsigned)a.OW);
+    const int oy = (int)((idx / (unsigned)a.OW) % (unsigned)a.OH);
+    const int n = (int)(idx / ((unsigned)a.OW * (unsigned)a.OH));
     int y0, y1, x0, x1; float l1y, l1x;
     q8_interp_index(oy, a.sy, a.H, a.align, y0, y1, l1y);
     q8_interp_index(ox, a.sx, a.W, a.align, x0, x1, l1x);
@@ -133,10 +133,10 @@ struct RegridQ8Args {
 
 __global__ void __launch_bounds__(kThreads)
 regridq8_kernel(RegridQ8Args a) {
-    const int64_t idx = (int64_t)blockIdx.x * kThreads + threadIdx.x;
-    if (idx >= a.G * a.words_out) return;
-    const int wi = (int)(idx % a.words_out);
-    const int64_t g = idx / a.words_out;
+    const unsigned idx = blockIdx.x * kThreads + threadIdx.x;
+    if (idx >= (unsigned)a.G * (unsigned)a.words_out) return;
+    const int wi = (int)(idx % (unsigned)a.words_out);
+    const int64_t g = idx / (unsigned)a.words_out;
     const int left = a.C - 4 * wi;                               // real channels in this word (<= 0: the padded tail)
     uint32_t w0 = 0u, w1 = 0u;
     if (left > 0) {
@@ -192,14 +192,14 @@ poolq8_kernel(const float *__restrict__ x, int64_t ld, int N, int HW, int C, int
 __global__ void __launch_bounds__(kThreads)
 padq8_kernel(const int8_t *__restrict__ x, const RangeSlot *slot, int8_t *__restrict__ y, int N, int H, int W, int Cp,
              int C, int pl, int pt, int OH, int OW) {
-    const int chunks = Cp >> 4;
-    const int64_t idx = (int64_t)blockIdx.x * kThreads + threadIdx.x;
-    if (idx >= (int64_t)N * OH * OW * chunks) return;
+    const unsigned chunks = (unsigned)Cp >> 4;
+    const unsigned idx = blockIdx.x * kThreads + threadIdx.x;
+    if (idx >= (unsigned)N * OH * OW * chunks) return;
     const int ch = (int)(idx % chunks);
-    int64_t rest = idx / chunks;
-    const int ox = (int)(rest % OW); rest /= OW;
-    const int oy = (int)(rest % OH);
-    const int n = (int)(rest / OH);
+    unsigned rest = idx / chunks;
+    const int ox = (int)(rest % (unsigned)OW); rest /= (unsigned)OW;
+    const int oy = (int)(rest % (unsigned)OH);
+    const int n = (int)(rest / (unsigned)OH);
     const int iy = oy - pt, ix = ox - pl;
     uint4 v;
     if ((unsigned)iy < (unsigned)H && (unsigned)ix < (unsigned)W) {
@@ -237,13 +237,13 @@ extern "C" int dfq_interp_q8(const int8_t *x, const float *in_slot, int N, int C
     const cudaStream_t st = (cudaStream_t)stream;
     if (y0) {
         const int64_t blocks = ((int64_t)N * OH * OW * (a.Cp / 16) + kThreads - 1) / kThreads;
-        if (blocks >= 0x7fffffffll) return (int)cudaErrorInvalidValue;
+        if (blocks >= (1ll << 23)) return (int)cudaErrorInvalidValue;      // 32-bit thread indices in the kernels
         interpq8_codes_kernel<<<(unsigned)blocks, kThreads, 0, st>>>(a);
         g_launches += 1;
     }
     if (yf) {
         const int64_t blocks = ((int64_t)N * OH * OW + kThreads - 1) / kThreads;
-        if (blocks >= 0x7fffffffll) return (int)cudaErrorInvalidValue;
+        if (blocks >= (1ll << 23)) return (int)cudaErrorInvalidValue;      // 32-bit thread indices in the kernels
         interpq8_f32_kernel<<<(unsigned)blocks, kThreads, 0, st>>>(a);
         g_launches += 1;
     }
@@ -262,7 +262,7 @@ extern "C" int dfq_regrid_q8(const int8_t *x, const float *in_slot, int64_t G, i
     // the last operand also clears the row's padding channels (buffers are recycled between tensors)
     a.words_out = fill_tail ? (cp_out - c_off) / 4 : (C + 3) / 4;
     const int64_t blocks = (G * a.words_out + kThreads - 1) / kThreads;
-    if (blocks >= 0x7fffffffll) return (int)cudaErrorInvalidValue;
+    if (blocks >= (1ll << 23)) return (int)cudaErrorInvalidValue;      // 32-bit thread indices in the kernels
     regridq8_kernel<<<(unsigned)blocks, kThreads, 0, (cudaStream_t)stream>>>(a);
     g_launches += 1;
     return (int)cudaGetLastError();
@@ -285,7 +285,7 @@ extern "C" int dfq_pad_q8(const int8_t *x, const float *slot, int N, int C, int 
         return (int)cudaErrorInvalidValue;
     const int Cp = (C + 15) / 16 * 16, OH = H + pt + pb, OW = W + pl + pr;
     const int64_t blocks = ((int64_t)N * OH * OW * (Cp / 16) + kThreads - 1) / kThreads;
-    if (blocks >= 0x7fffffffll) return (int)cudaErrorInvalidValue;
+    if (blocks >= (1ll << 23)) return (int)cudaErrorInvalidValue;      // 32-bit thread indices in the kernels
     padq8_kernel<<<(unsigned)blocks, kThreads, 0, (cudaStream_t)stream>>>(x, (const RangeSlot *)slot, y, N, H, W, Cp, C, pl,
                                                                          pt, OH, OW);
     g_launches += 1;
