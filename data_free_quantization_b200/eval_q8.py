@@ -196,7 +196,8 @@ class EvalPlanQ8(EvalPlan):
         self.refresh_static()
         # F.pad is never quantised itself (utils/layer_transform.py ignore_op): the QuantMeasure of the convolution that
         # reads the padded tensor quantises the padded zeros with it.  So the producer of x writes x on that measure's
-        # grid, and the pad op copies it into a padded code tensor whose border is code(0.0) on that grid.
+        # grid: into the interior of a pre-bordered padded tensor when it can place pixels (outs_of below), else plain,
+        # and a pad op copies it into a padded code tensor whose border is code(0.0) on that grid.
         live = steps
         slots_in = lambda st: [st[k] for k in ("slot", "slot_a", "slot_b") if st.get(k) is not None] + \
             list(st.get("slots", ()))
@@ -227,7 +228,6 @@ class EvalPlanQ8(EvalPlan):
         for i, st in enumerate(live):
             for idx in slots_in(st):
                 step_of_slot[idx] = i
-        pad_step = {id(st["out"]): i for i, st in enumerate(live) if st["kind"] == "pad"}
         slot_ptr = lambda i: self.slots[i].data_ptr()
         pool, self.codes, self.pre, self.slot_key = {}, {}, {}, {}
         self.act_bytes = 0
@@ -372,16 +372,13 @@ class EvalPlanQ8(EvalPlan):
                 self.slot_key[st["slot"]] = ("L", name)
                 w = m.weight.data
                 b = None if m.bias is None else m.bias.data
-                padinfo = None
-                rsrc = src
-                Nn, C, H, W = rsrc.shape
+                Nn, C, H, W = src.shape
                 xcodes = self.codes.get(st["slot"])
-                if rsrc is self.input:
-                    if not (kh == 3 and kw == 3 and g == 1 and C == 3 and d == 1 and m.out_channels <= 32 and y0 is not None
-                            and padinfo is None):
+                if src is self.input:
+                    if not (kh == 3 and kw == 3 and g == 1 and C == 3 and d == 1 and m.out_channels <= 32 and y0 is not None):
                         raise NotImplementedError(f"{name}: only a dense 3 x 3 stem on 3 channels reads the image")
                     desc = L.DfqStemQ8Desc()
-                    desc.x, desc.w = rsrc.buf.data_ptr(), L.dev_f32(w.contiguous(), "weight")
+                    desc.x, desc.w = src.buf.data_ptr(), L.dev_f32(w.contiguous(), "weight")
                     desc.bias = None if b is None else L.dev_f32(b, "bias")
                     desc.in_slot, desc.y0, desc.out_slot0, desc.y1, desc.out_slot1 = slot_ptr(st["slot"]), y0, s0, y1, s1
                     desc.N, desc.H, desc.W, desc.O, desc.stride, desc.pad, desc.relu = Nn, H, W, m.out_channels, s, p, st["relu"]
@@ -392,7 +389,7 @@ class EvalPlanQ8(EvalPlan):
                     self.keep_q8.append(desc)
                     fn = (lambda dd: lambda: L.check(lib.dfq_stem_q8(ctypes.byref(dd), stream()), "dfq_stem_q8"))(desc)
                     kind2 = "stem"
-                elif kh == 1 and kw == 1 and g == 1 and s == 1 and p == 0 and padinfo is None:
+                elif kh == 1 and kw == 1 and g == 1 and s == 1 and p == 0:
                     yf = None
                     if is_final or y0 is None:
                         raise NotImplementedError(f"{name}: a 1 x 1 convolution as the network's output")
@@ -419,7 +416,7 @@ class EvalPlanQ8(EvalPlan):
                     self.keep_q8 += [wrow, bp, desc]
                     fn = (lambda dd: lambda: L.check(lib.dfq_dw_q8(ctypes.byref(dd), stream()), "dfq_dw_q8"))(desc)
                     kind2 = "dw"
-                elif g == 1 and padinfo is None and y0 is not None:        # dense k x k (ASPP's atrous 3 x 3, the decoder's 3 x 3)
+                elif g == 1 and y0 is not None:        # dense k x k (ASPP's atrous 3 x 3, the decoder's 3 x 3)
                     G_out = out.shape[0] * out.shape[2] * out.shape[3]
                     # DFQ_CONV_Q8_TMA=1 selects the TMA-fed, warp-specialised form (stride 1).  Same codes out; measured
                     # SLOWER on the decoder's 304 / 256 -> 256 layers at 129 x 129 (0.71 / 0.53 ms against 0.35 / 0.33 ms):
