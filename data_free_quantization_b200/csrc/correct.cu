@@ -188,7 +188,8 @@ __device__ __forceinline__ float chunk_eps_dot_pw(const float4 *__restrict__ w4,
             float t = __fadd_rn(xs[j], c.neg_min);
             if (!kInRange) t = fminf(fmaxf(t, c.t_lo), c.t_hi);
             float d = div_const_rn(t, c.scale, c.rscale);
-            float q = rint_small(fminf(fmaxf(d, c.qmin), c.qmax));
+            // kInRange: 0 <= t <= max - min, so d lies in [0, qmax (1 + 2^-23)] and rounds into the grid unclamped
+            float q = rint_small(kInRange ? d : fminf(fmaxf(d, c.qmin), c.qmax));
             float eps = __fsub_rn(__fadd_rn(__fmul_rn(q, c.scale), c.add_back), xs[j]);   // bias_correction.py:130
             if (j & 1) acc1 = __fmaf_rn(eps, vs[j], acc1); else acc0 = __fmaf_rn(eps, vs[j], acc0);
         }
