@@ -135,3 +135,67 @@ def test_deeplab_static_plan_end_to_end(static_deeplab):
     replay()
     torch.cuda.synchronize()
     assert np.array_equal(plan.output.buf.cpu().numpy(), got)
+
+
+@pytest.mark.parametrize("N,C,H,W,O,pad,dil,relu,dual,forms", [
+    (2, 40, 19, 21, 24, 1, 1, 1, True, (0, 1, 2)),        # ragged channels / ragged tiles, all three kernels
+    (1, 304, 33, 17, 256, 1, 1, 1, False, (0, 2)),         # the decoder's channel counts on a small image
+    (3, 16, 9, 40, 272, 1, 1, 0, True, (0, 2)),            # two output passes, last one ragged
+    (1, 64, 17, 17, 48, 2, 2, 0, False, (0, 1)),           # dilated (ASPP-like): gather and TMA forms only
+])
+def test_dense_conv_q8_forms_against_float64_restatement(oracle, N, C, H, W, O, pad, dil, relu, dual, forms):
+    """dfq_conv_q8 in its three forms (register gather, TMA boxes per tap, halo tile) on random codes: the output codes
+    must be those of the float64 convolution of the dequantised operands (zero padding = exact zeros), never more than
+    one code off."""
+    import ctypes
+    import torch.nn.functional as F
+    from data_free_quantization_b200 import _lib as L, pw_i8
+    from data_free_quantization_b200.eval_q8 import (PackedConvQ8, choose_o_cap, from_codes_nhwc, pack_conv_halo,
+                                                     to_codes_nhwc)
+    from test_gpu_q8 import slot
+    rng = np.random.default_rng(N * 1000 + C + O)
+    xc = rng.integers(0, 256, (N, C, H, W)).astype(np.uint8)
+    lo_x, hi_x = -0.9, 2.3
+    in_slot, sx = slot(lo_x, hi_x)
+    w0 = (rng.standard_normal((O, C, 3, 3)) * 0.1).astype(np.float32)
+    w, _wq = oracle.fake_quant(w0, 8, float(w0.min()), float(w0.max()), want_codes=True)
+    bias = (rng.standard_normal(O) * 0.3).astype(np.float32)
+    x_hat = (xc.astype(np.float32) * np.float32(sx)).astype(np.float32) + np.float32(lo_x)          # fl(fl(q s) + min)
+    exact = F.conv2d(torch.from_numpy(x_hat).double(), torch.from_numpy(w).double(), torch.from_numpy(bias).double(),
+                     1, pad, dil).numpy()
+    if relu:
+        exact = np.maximum(exact, 0)
+    OH, OW = exact.shape[2:]
+    ranges = [(float(exact.min()) * 0.8, float(exact.max()) * 0.7), (0.0, float(exact.max()) + 0.5)]
+    want = [oracle.fake_quant(exact.astype(np.float32), 8, float(np.float32(lo)), float(np.float32(hi)), want_codes=True)[1]
+            for lo, hi in ranges]
+    s0, _ = slot(*ranges[0]); s1, _ = slot(*ranges[1])
+    wd, bd = torch.from_numpy(w).to(DEV), torch.from_numpy(bias).to(DEV)
+    x = to_codes_nhwc(torch.from_numpy(xc)).reshape(-1).to(DEV)
+    Op = (O + 15) // 16 * 16
+    for form in forms:
+        if form == 2:
+            pk = pack_conv_halo(wd)
+        elif form == 1:
+            pk = PackedConvQ8(wd, o_cap=choose_o_cap(N * OH * OW, O))
+        else:
+            pk = pw_i8.pack_weight_conv(wd, None, o_cap=pw_i8.choose_o_cap(N * OH * OW, O))
+        y0 = torch.full((N * OH * OW * Op,), 77, dtype=torch.int8, device=DEV)
+        y1 = torch.full((N * OH * OW * Op,), 77, dtype=torch.int8, device=DEV)
+        d = L.DfqConvQ8Desc()
+        d.x, d.wpk, d.wr, d.wrt, d.bias = x.data_ptr(), pk.wpk.data_ptr(), pk.wr.data_ptr(), pk.wrt.data_ptr(), bd.data_ptr()
+        d.in_slot, d.y0, d.out_slot0 = in_slot.data_ptr(), y0.data_ptr(), s0.data_ptr()
+        if dual:
+            d.y1, d.out_slot1 = y1.data_ptr(), s1.data_ptr()
+        d.N, d.C, d.H, d.W, d.O, d.OH, d.OW = N, C, H, W, O, OH, OW
+        d.kh, d.kw, d.stride, d.pad, d.dil, d.relu = 3, 3, 1, pad, dil, relu
+        d.s_w, d.c_w, d.o_cap, d.tma = pk.s_w, pk.c_w, pk.o_cap, form
+        L.check(L.lib().dfq_conv_q8(ctypes.byref(d), L.stream()), f"dfq_conv_q8 form {form}")
+        torch.cuda.synchronize()
+        for t, yb in enumerate((y0, y1)):
+            if t == 1 and not dual:
+                assert bool((y1 == 77).all())
+                break
+            got = from_codes_nhwc(yb.cpu(), (N, O, OH, OW)).numpy()
+            check_codes(got, want[t], f"form {form} grid {t}")
+            assert not yb.cpu().view(N * OH * OW, Op)[:, O:].any(), "pad channels must be s8 zero"
