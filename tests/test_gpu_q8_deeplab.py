@@ -199,3 +199,78 @@ def test_dense_conv_q8_forms_against_float64_restatement(oracle, N, C, H, W, O, 
             got = from_codes_nhwc(yb.cpu(), (N, O, OH, OW)).numpy()
             check_codes(got, want[t], f"form {form} grid {t}")
             assert not yb.cpu().view(N * OH * OW, Op)[:, O:].any(), "pad channels must be s8 zero"
+
+
+def test_movement_kernels_on_codes_against_torch(oracle):
+    """dfq_interp_q8 / dfq_regrid_q8 / dfq_pool_q8 / dfq_pad_q8 and the generic (dilated) depthwise kernel on random
+    code tensors with ragged channel counts, against torch on the dequantised values."""
+    import ctypes
+    import torch.nn.functional as F
+    from data_free_quantization_b200 import _lib as L
+    from data_free_quantization_b200.eval_q8 import from_codes_nhwc, pack_depthwise, to_codes_nhwc
+    from test_gpu_q8 import slot
+    lib = L.lib()
+    rng = np.random.default_rng(77)
+    deq = lambda codes, lo, s: (codes.astype(np.float32) * np.float32(s)).astype(np.float32) + np.float32(lo)
+    quant = lambda v, lo, hi: oracle.fake_quant(np.ascontiguousarray(v, np.float32), 8, float(np.float32(lo)),
+                                                float(np.float32(hi)), want_codes=True)[1]
+    # ---- bilinear interpolation, both align_corners modes, codes and fp32 out
+    N, C, H, W, OH, OW = 2, 21, 7, 9, 20, 13
+    xc = rng.integers(0, 256, (N, C, H, W)).astype(np.uint8)
+    lo, hi = -1.5, 3.0
+    sl, sx = slot(lo, hi)
+    so, _ = slot(-1.0, 2.5)
+    x = to_codes_nhwc(torch.from_numpy(xc)).reshape(-1).to(DEV)
+    for align in (0, 1):
+        ref = F.interpolate(torch.from_numpy(deq(xc, lo, sx)), size=(OH, OW), mode="bilinear", align_corners=bool(align)).numpy()
+        y = torch.full((N * OH * OW * 32,), 77, dtype=torch.int8, device=DEV)
+        yf = torch.full((N, C, OH, OW), float("nan"), device=DEV)
+        L.check(lib.dfq_interp_q8(x.data_ptr(), sl.data_ptr(), N, C, H, W, OH, OW, align, y.data_ptr(), so.data_ptr(), None,
+                                  None, yf.data_ptr(), L.stream()), "dfq_interp_q8")
+        torch.cuda.synchronize()
+        assert np.abs(yf.cpu().numpy() - ref).max() <= 2e-6 * np.abs(ref).max()
+        check_codes(from_codes_nhwc(y.cpu(), (N, C, OH, OW)).numpy(), quant(ref, -1.0, 2.5), f"interp align={align}")
+        assert not y.cpu().view(-1, 32)[:, C:].any()
+    # ---- one operand of a concatenation: 40 channels at offset 16 of 64-channel rows, the tail cleared
+    G, C, c_off, cp_out = 300, 40, 16, 64
+    xc = rng.integers(0, 256, (G, C)).astype(np.uint8)
+    x = to_codes_nhwc(torch.from_numpy(xc)).reshape(-1).to(DEV)
+    y = torch.full((G, cp_out), 77, dtype=torch.int8, device=DEV)
+    L.check(lib.dfq_regrid_q8(x.data_ptr(), sl.data_ptr(), G, C, y.data_ptr(), so.data_ptr(), None, None, cp_out, c_off, 1,
+                              L.stream()), "dfq_regrid_q8")
+    torch.cuda.synchronize()
+    got = y.cpu()
+    assert bool((got[:, :c_off] == 77).all()) and not got[:, c_off + C:].any()
+    want = quant(deq(xc, lo, sx), -1.0, 2.5)
+    assert np.array_equal((got[:, c_off:c_off + C].to(torch.int16) + 128).numpy(), want)      # elementwise: exact
+    # ---- global average pool of fp32 rows
+    N, HW, C = 3, 1089, 40
+    xf = (rng.standard_normal((N, HW, C)) * 2).astype(np.float32)
+    y = torch.full((N, 48), 77, dtype=torch.int8, device=DEV)
+    L.check(lib.dfq_pool_q8(torch.from_numpy(xf).to(DEV).data_ptr(), C, N, HW, C, y.data_ptr(), so.data_ptr(), None, None,
+                            L.stream()), "dfq_pool_q8")
+    torch.cuda.synchronize()
+    check_codes((y.cpu()[:, :C].to(torch.int16) + 128).numpy(), quant(xf.astype(np.float64).mean(1), -1.0, 2.5), "pool")
+    assert not y.cpu()[:, C:].any()
+    # ---- depthwise 3 x 3 with dilation 2 (generic kernel), stride 1 and 2
+    N, C, H, W = 2, 40, 15, 18
+    xc = rng.integers(0, 256, (N, C, H, W)).astype(np.uint8)
+    x = to_codes_nhwc(torch.from_numpy(xc)).reshape(-1).to(DEV)
+    w0 = (rng.standard_normal((C, 1, 3, 3)) * 0.3).astype(np.float32)
+    w, _ = oracle.fake_quant(w0, 8, float(w0.min()), float(w0.max()), want_codes=True)
+    wrow, dsw, dcw = pack_depthwise(torch.from_numpy(w).to(DEV))
+    bias = (rng.standard_normal(C) * 0.2).astype(np.float32)
+    bp = torch.zeros(48, device=DEV); bp[:C] = torch.from_numpy(bias).to(DEV)
+    for stride in (1, 2):
+        ref = F.conv2d(torch.from_numpy(deq(xc, lo, sx)).double(), torch.from_numpy(w).double(),
+                       torch.from_numpy(bias).double(), stride, 2, 2, C).numpy()
+        OHd, OWd = ref.shape[2:]
+        so2, _ = slot(float(ref.min()) * 0.9, float(ref.max()) * 0.9)
+        y = torch.full((N * OHd * OWd * 48,), 77, dtype=torch.int8, device=DEV)
+        d = L.DfqDwQ8Desc()
+        d.x, d.wrow, d.bias, d.in_slot, d.y0, d.out_slot0 = x.data_ptr(), wrow.data_ptr(), bp.data_ptr(), sl.data_ptr(), y.data_ptr(), so2.data_ptr()
+        d.N, d.H, d.W, d.C, d.stride, d.relu, d.s_w, d.c_w, d.pad, d.dil = N, H, W, C, stride, 0, dsw, dcw, 2, 2
+        L.check(lib.dfq_dw_q8(ctypes.byref(d), L.stream()), "dfq_dw_q8")
+        torch.cuda.synchronize()
+        check_codes(from_codes_nhwc(y.cpu(), (N, C, OHd, OWd)).numpy(),
+                    quant(ref, float(ref.min()) * 0.9, float(ref.max()) * 0.9), f"dilated depthwise stride {stride}")
