@@ -274,3 +274,25 @@ def test_movement_kernels_on_codes_against_torch(oracle):
         torch.cuda.synchronize()
         check_codes(from_codes_nhwc(y.cpu(), (N, C, OHd, OWd)).numpy(),
                     quant(ref, float(ref.min()) * 0.9, float(ref.max()) * 0.9), f"dilated depthwise stride {stride}")
+
+
+def test_static_plan_on_other_image_sizes(static_deeplab):
+    """Sizes no golden holds (ragged tiles, non-square images, odd batch): the u8 plan against the reference-shaped module
+    forward of the same static-mode model (QuantMeasure + F.conv2d per layer, utils/quantize.py:250-256)."""
+    from data_free_quantization_b200.eval_q8 import EvalPlanQ8
+    from data_free_quantization_b200.utils import quantize as Q
+    model, tr = static_deeplab
+    for n, h, w in ((3, 200, 264), (1, 97, 131)):
+        x = torch.randn(n, 3, h, w, generator=torch.Generator().manual_seed(n + h)).to(DEV)
+        plan = EvalPlanQ8(model, tr, batch=n, in_shape=(3, h, w))
+        got = plan(x).clone()
+        Q.FUSED_EVAL = False
+        try:
+            with torch.no_grad():
+                ref = model(x)
+        finally:
+            Q.FUSED_EVAL = True
+        agree = float((got.argmax(1) == ref.argmax(1)).float().mean())
+        shift = float((got - ref).abs().max() / ref.abs().max())
+        print(f"{n}x3x{h}x{w}: classes agree {agree:.4f}, logits {shift:.2e} of the largest")
+        assert got.shape == ref.shape and agree >= 0.998 and shift <= 0.1
