@@ -529,6 +529,7 @@ struct StemQ8Args {
     const RangeSlot *out_slot[2]; int8_t *y[2];
     int N, H, W, OH, OW, O, Cp, stride, pad, relu;
     Q8OutMap omap[2];
+    const uint32_t *wq; float s_w, c_w;       // integer form: [32][8] words of centred s8 weight codes (taps 4k .. 4k + 3)
 };
 
 __global__ void __launch_bounds__(kThreads)
@@ -620,6 +621,110 @@ stemq8_kernel(StemQ8Args a) {
             for (int j4 = 0; j4 < 4; ++j4) w4[j4] = keep_left(w4[j4], a.O - ob - 4 * j4);
             *reinterpret_cast<uint4 *>(a.y[t2] + q8_out_pixel(a.omap[t2], p) * a.Cp + ob) = make_uint4(w4[0], w4[1], w4[2], w4[3]);
         }
+    }
+}
+
+// The stem on exact integer sums (weights on a grid of <= 8 bits, which quantize_targ_layer leaves them on): the 27
+// quantised inputs of a pixel become seven words of centred s8 codes (taps in the zero padding: 0, the tap is absent in
+// the reference), and an output channel is seven dp4a against its packed weights instead of 27 FMAs on dequantised
+// values.  Same decomposition as the depthwise kernel:
+//   y = s_x s_w SUM a b + s_x c_w SUM a + c_x s_w SUM_inb b + n_inb c_x c_w + bias.
+__global__ void __launch_bounds__(kThreads, 3)
+stemq8_i8_kernel(StemQ8Args a) {
+    __shared__ __align__(16) uint32_t swq[32][8];
+    __shared__ __align__(16) float scst[32];                     // c_x s_w SUM b + 27 c_x c_w + bias (no tap in the padding)
+    __shared__ float sbias[32];
+    const RangeSlot in = *a.in_slot;
+    const float sx = in.scale, cx = __fmaf_rn(128.0f, sx, in.mn);
+    const float fa = __fmul_rn(sx, a.s_w), fb = __fmul_rn(sx, a.c_w);
+    const float cxsw = __fmul_rn(cx, a.s_w), cxcw = __fmul_rn(cx, a.c_w);
+    swq[threadIdx.x >> 3][threadIdx.x & 7] = __ldg(a.wq + threadIdx.x);            // kThreads == 32 * 8
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        int sb = 0;
+#pragma unroll
+        for (int k = 0; k < 7; ++k) sb = __dp4a((int)swq[threadIdx.x][k], 0x01010101, sb);
+        const float bias = (a.bias && threadIdx.x < a.O) ? __ldg(a.bias + threadIdx.x) : 0.0f;
+        sbias[threadIdx.x] = bias;
+        scst[threadIdx.x] = __fadd_rn(__fmaf_rn(cxsw, small_int_to_float(sb), __fmul_rn(27.0f, cxcw)), bias);
+    }
+    __syncthreads();
+    const int64_t total = (int64_t)a.N * a.OH * a.OW;
+    const QuantConsts qi = consts_from_slot(in, 8, 0, 0.f, 0.f);
+    const bool has1 = a.y[1] != nullptr;
+    const QuantConsts q0 = consts_from_slot(*a.out_slot[0], 8, 0, 0.f, 0.f);
+    QuantConsts q1 = q0;
+    if (has1) q1 = consts_from_slot(*a.out_slot[1], 8, 0, 0.f, 0.f);
+    const float floor_v = a.relu ? 0.0f : -INFINITY;
+    for (int64_t p = (int64_t)blockIdx.x * kThreads + threadIdx.x; p < total; p += (int64_t)gridDim.x * kThreads) {
+    const int ox = (int)(p % a.OW);
+    const int oy = (int)((p / a.OW) % a.OH);
+    const int n = (int)(p / ((int64_t)a.OW * a.OH));
+    float xin[28];
+    bool rok[3], cok[3];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        rok[i] = (unsigned)(oy * a.stride - a.pad + i) < (unsigned)a.H;
+        cok[i] = (unsigned)(ox * a.stride - a.pad + i) < (unsigned)a.W;
+    }
+#pragma unroll
+    for (int c = 0; c < 3; ++c)
+#pragma unroll
+        for (int i = 0; i < 3; ++i)
+#pragma unroll
+            for (int j = 0; j < 3; ++j) {
+                const int iy = oy * a.stride - a.pad + i, ix = ox * a.stride - a.pad + j;
+                xin[(c * 3 + i) * 3 + j] = (rok[i] && cok[j]) ? __ldg(a.x + (((int64_t)n * 3 + c) * a.H + iy) * a.W + ix) : 0.0f;
+            }
+    xin[27] = 0.0f;
+    uint32_t aw[7], keep[7];
+    pack_codes<28>(xin, qi, aw);                                  // utils/quantize.py:72-74 on the inputs, centred codes
+#pragma unroll
+    for (int k = 0; k < 7; ++k) {
+        keep[k] = 0u;
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+            const int t = 4 * k + b;                              // tap (c, i, j) = (t / 9, (t / 3) % 3, t % 3)
+            if (t < 27 && rok[(t / 3) % 3] && cok[t % 3]) keep[k] |= 0xffu << (8 * b);
+        }
+        aw[k] &= keep[k];
+    }
+    const int nr = (int)rok[0] + (int)rok[1] + (int)rok[2], nc = (int)cok[0] + (int)cok[1] + (int)cok[2];
+    const bool interior = nr == 3 && nc == 3;
+    int sa = 0;
+#pragma unroll
+    for (int k = 0; k < 7; ++k) sa = __dp4a((int)aw[k], 0x01010101, sa);
+    const float ninb_cxcw = __fmul_rn((float)(3 * nr * nc), cxcw);
+    for (int ob = 0; ob < a.Cp; ob += 16) {
+        float yv[16];
+#pragma unroll
+        for (int c = 0; c < 16; ++c) {
+            const uint4 w0 = *reinterpret_cast<const uint4 *>(&swq[ob + c][0]);
+            const uint4 w1 = *reinterpret_cast<const uint4 *>(&swq[ob + c][4]);
+            const uint32_t wk[7] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z};
+            int acc = 0;
+#pragma unroll
+            for (int k = 0; k < 7; ++k) acc = __dp4a((int)aw[k], (int)wk[k], acc);
+            float cst = scst[ob + c];
+            if (!interior) {                                      // border pixel: the constants count the in-bound taps only
+                int sb = 0;
+#pragma unroll
+                for (int k = 0; k < 7; ++k) sb = __dp4a((int)(keep[k] & 0x01010101u), (int)wk[k], sb);
+                cst = __fadd_rn(__fmaf_rn(cxsw, small_int_to_float(sb), ninb_cxcw), sbias[ob + c]);
+            }
+            yv[c] = fmaxf(__fmaf_rn(fa, small_int_to_float(acc), __fmaf_rn(fb, small_int_to_float(sa), cst)), floor_v);
+        }
+#pragma unroll
+        for (int t2 = 0; t2 < 2; ++t2) {
+            if (t2 && !has1) continue;
+            const QuantConsts &qc = t2 ? q1 : q0;
+            uint32_t w4[4];
+            pack_codes<16>(yv, qc, w4);
+#pragma unroll
+            for (int j4 = 0; j4 < 4; ++j4) w4[j4] = keep_left(w4[j4], a.O - ob - 4 * j4);
+            *reinterpret_cast<uint4 *>(a.y[t2] + q8_out_pixel(a.omap[t2], p) * a.Cp + ob) = make_uint4(w4[0], w4[1], w4[2], w4[3]);
+        }
+    }
     }
 }
 
@@ -985,6 +1090,13 @@ extern "C" int dfq_stem_q8(const DfqStemQ8Desc *d, void *stream) {
     a.OH = (d->H + 2 * d->pad - 3) / d->stride + 1; a.OW = (d->W + 2 * d->pad - 3) / d->stride + 1;
     a.omap[0] = q8_make_map(&d->map0); a.omap[1] = q8_make_map(&d->map1);
     const int64_t total = (int64_t)a.N * a.OH * a.OW;
+    a.wq = reinterpret_cast<const uint32_t *>(d->wq); a.s_w = d->s_w; a.c_w = d->c_w;
+    static_assert(kThreads == 256, "stemq8_i8_kernel stages its 32 x 8 weight words with one load per thread");
+    if (a.wq) {             // blocks walk the pixels grid-stride: the weight words are staged once per resident block
+        const int64_t blocks = (total + kThreads - 1) / kThreads, resident = (int64_t)sm_count() * 3 * 4;
+        stemq8_i8_kernel<<<(unsigned)(blocks < resident ? blocks : resident), kThreads, 0, (cudaStream_t)stream>>>(a);
+    }
+    else
     stemq8_kernel<<<(unsigned)((total + kThreads - 1) / kThreads), kThreads, 0, (cudaStream_t)stream>>>(a);
     g_launches += 1;
     return (int)cudaGetLastError();

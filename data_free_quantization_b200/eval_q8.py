@@ -147,6 +147,25 @@ def pack_depthwise(w):
     return torch.from_numpy(rows.view(np.int32)).to(w.device), s32 / up, float(np.float32(lo + 2 ** (bits - 1) * s32))
 
 
+def pack_stem(w):
+    """[O <= 32, 3, 3, 3] fake-quantised stem weight -> ([32][8] words of centred s8 codes (word k = taps 4k .. 4k + 3 in
+    (c, kh, kw) order, zero beyond tap 26 and beyond row O), s_w, c_w) for dfq_stem_q8's integer kernel; None when the
+    weight is not on a grid of <= 8 bits (the fp32 kernel takes it then)."""
+    rec = None
+    for b in (8, 7, 6, 5, 4, 3, 2):
+        rec = pw_i8._recover_codes(w, b)
+        if rec is not None:
+            break
+    if rec is None or w.shape[0] > 32 or tuple(w.shape[1:]) != (3, 3, 3):
+        return None
+    s32, lo, q, bits = rec
+    up = 2 ** (8 - bits)
+    codes = np.zeros((32, 32), np.int8)
+    codes[:w.shape[0], :27] = ((q - 2 ** (bits - 1)) * up).to(torch.int8).cpu().numpy().reshape(w.shape[0], 27)
+    words = np.ascontiguousarray(codes).view(np.int32).reshape(32, 8)
+    return torch.from_numpy(words.copy()).to(w.device), s32 / up, float(np.float32(lo + 2 ** (bits - 1) * s32))
+
+
 def choose_o_cap(G, O, sms=148):
     """Output channels per pass.  112 (+ the row of ones = 128 accumulator columns): two accumulators then take 256 of
     the 512 TMEM columns, so TWO CTAs -- 16 epilogue warps -- share an SM; the A tile a second pass re-reads is small
@@ -386,6 +405,10 @@ class EvalPlanQ8(EvalPlan):
                         desc.map0 = m0
                     if m1 is not None:
                         desc.map1 = m1
+                    pk = pack_stem(w) if os.environ.get("DFQ_Q8_STEM_I8", "1") != "0" else None
+                    if pk is not None:                  # weights on a grid: exact integer sums (dp4a)
+                        desc.wq, desc.s_w, desc.c_w = pk[0].data_ptr(), pk[1], pk[2]
+                        self.keep_q8.append(pk[0])
                     self.keep_q8.append(desc)
                     fn = (lambda dd: lambda: L.check(lib.dfq_stem_q8(ctypes.byref(dd), stream()), "dfq_stem_q8"))(desc)
                     kind2 = "stem"

@@ -349,3 +349,46 @@ def test_static_plan_end_to_end_against_reference(static_model):
     replay()
     torch.cuda.synchronize()
     assert np.array_equal(plan.output.buf.cpu().numpy().reshape(got.shape), got)
+
+
+@pytest.mark.parametrize("N,H,W,O,stride,dual", [(3, 64, 48, 32, 2, False), (2, 9, 7, 24, 2, True), (1, 11, 13, 32, 1, True),
+                                                 (2, 1, 1, 5, 2, False)])
+def test_stem_q8_integer_kernel(oracle, N, H, W, O, stride, dual):
+    """The stem on exact integer sums (dp4a; DfqStemQ8Desc.wq) against a float64 convolution of the fake-quantised
+    operands: borders (taps in the zero padding are absent, not code 128), ragged O, two output grids."""
+    from data_free_quantization_b200 import _lib as L
+    from data_free_quantization_b200.eval_q8 import from_codes_nhwc, pack_stem
+    lib = L.lib()
+    rng = np.random.default_rng(31 + H)
+    img = (rng.standard_normal((N, 3, H, W)) * 1.2).astype(np.float32)
+    lo_i, hi_i = -2.11790393, 2.64
+    in_slot, _ = slot(lo_i, hi_i)
+    xq = oracle.fake_quant(img, 8, float(np.float32(lo_i)), float(np.float32(hi_i)))
+    w = (rng.standard_normal((O, 3, 3, 3)) * 0.3).astype(np.float32)
+    w = oracle.fake_quant(w, 8, float(w.min()), float(w.max()))            # quantize_targ_layer: on a grid
+    bias = (rng.standard_normal(O) * 0.2).astype(np.float32)
+    ref = np.maximum(torch.nn.functional.conv2d(torch.from_numpy(xq).double(), torch.from_numpy(w).double(),
+                                                torch.from_numpy(bias).double(), stride, 1).numpy(), 0)
+    OH, OW = ref.shape[2:]
+    Cp = (O + 15) // 16 * 16
+    outs = [(0.0, float(ref.max()) * 0.95 + 0.1), (0.05, float(ref.max()) * 0.6 + 0.1)]
+    (s0, _), (s1, _) = slot(*outs[0]), slot(*outs[1])
+    xd, wd, bd = torch.from_numpy(img).to(DEV), torch.from_numpy(w).to(DEV), torch.from_numpy(bias).to(DEV)
+    pk = pack_stem(wd)
+    assert pk is not None
+    y0 = torch.full((N * OH * OW * Cp,), 3, dtype=torch.int8, device=DEV)
+    y1 = torch.full((N * OH * OW * Cp,), 3, dtype=torch.int8, device=DEV)
+    d = L.DfqStemQ8Desc()
+    d.x, d.w, d.bias, d.in_slot, d.y0, d.out_slot0 = xd.data_ptr(), wd.data_ptr(), bd.data_ptr(), in_slot.data_ptr(), y0.data_ptr(), s0.data_ptr()
+    if dual:
+        d.y1, d.out_slot1 = y1.data_ptr(), s1.data_ptr()
+    d.N, d.H, d.W, d.O, d.stride, d.pad, d.relu = N, H, W, O, stride, 1, 1
+    d.wq, d.s_w, d.c_w = pk[0].data_ptr(), pk[1], pk[2]
+    L.check(lib.dfq_stem_q8(ctypes.byref(d), L.stream()), "dfq_stem_q8")
+    torch.cuda.synchronize()
+    for yb, (lo, hi) in list(zip((y0, y1), outs))[:2 if dual else 1]:
+        _q, want = oracle.fake_quant(ref.astype(np.float32), 8, float(np.float32(lo)), float(np.float32(hi)), want_codes=True)
+        check_codes(from_codes_nhwc(yb.cpu(), ref.shape).numpy(), want, f"stem i8 {H}x{W}")
+        assert not yb.cpu().view(-1, Cp)[:, O:].any()          # padding channels: s8 zero
+    # off-grid weights are refused by the packer (the fp32 kernel takes them)
+    assert pack_stem(wd * 1.0001 + torch.randn_like(wd) * 1e-3) is None
