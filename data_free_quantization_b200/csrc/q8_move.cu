@@ -212,6 +212,132 @@ padq8_kernel(const int8_t *__restrict__ x, const RangeSlot *slot, int8_t *__rest
     reinterpret_cast<uint4 *>(y + (((int64_t)n * OH + oy) * OW + ox) * Cp)[ch] = v;
 }
 
+// ---- upscaling forms: a thread walks kInterpRows consecutive output rows of one column.  The horizontal blends
+// `top` / `bot` of the reference's expression l0y * (l0x * a00 + l1x * a01) + l1y * (l0x * a10 + l1x * a11) depend on the
+// input row pair only, so they are formed once per pair (four rows share one when the image grows 4 x, DeepLab's
+// 33 -> 129 and 129 -> 513) and an output row costs the vertical blend alone.  Same operations in the same order per
+// output value as the one-row kernels: the same bits.
+constexpr int kInterpRows = 4;
+
+__global__ void __launch_bounds__(kThreads)
+interpq8_codes_rows_kernel(InterpQ8Args a) {
+    const unsigned chunks = (unsigned)a.Cp >> 4, groups = ((unsigned)a.OH + kInterpRows - 1) / kInterpRows;
+    const unsigned idx = blockIdx.x * kThreads + threadIdx.x;
+    if (idx >= (unsigned)a.N * groups * a.OW * chunks) return;
+    const int ch = (int)(idx % chunks);
+    unsigned rest = idx / chunks;
+    const int ox = (int)(rest % (unsigned)a.OW); rest /= (unsigned)a.OW;
+    const int g = (int)(rest % groups);
+    const int n = (int)(rest / groups);
+    int x0, x1; float l1x;
+    q8_interp_index(ox, a.sx, a.W, a.align, x0, x1, l1x);
+    const float l0x = __fsub_rn(1.0f, l1x);
+    const RangeSlot in = *a.in_slot;
+    const int8_t *xn = a.x + (int64_t)n * a.H * a.W * a.Cp;
+    const int64_t rs = (int64_t)a.W * a.Cp;
+    const QuantConsts q0 = consts_from_slot(*a.out_slot[0], 8, 0, 0.f, 0.f);
+    const int left = a.C - 16 * ch;
+    int cy0 = -1, cy1 = -1;
+    float top[16], bot[16];
+#pragma unroll 1
+    for (int r = 0; r < kInterpRows; ++r) {
+        const int oy = g * kInterpRows + r;
+        if (oy >= a.OH) break;
+        int y0, y1; float l1y;
+        q8_interp_index(oy, a.sy, a.H, a.align, y0, y1, l1y);
+        if (y0 != cy0 || y1 != cy1) {
+            cy0 = y0; cy1 = y1;
+            const uint4 q00 = __ldg(reinterpret_cast<const uint4 *>(xn + y0 * rs + (int64_t)x0 * a.Cp) + ch);
+            const uint4 q01 = __ldg(reinterpret_cast<const uint4 *>(xn + y0 * rs + (int64_t)x1 * a.Cp) + ch);
+            const uint4 q10 = __ldg(reinterpret_cast<const uint4 *>(xn + y1 * rs + (int64_t)x0 * a.Cp) + ch);
+            const uint4 q11 = __ldg(reinterpret_cast<const uint4 *>(xn + y1 * rs + (int64_t)x1 * a.Cp) + ch);
+            const uint32_t w00[4] = {q00.x, q00.y, q00.z, q00.w}, w01[4] = {q01.x, q01.y, q01.z, q01.w};
+            const uint32_t w10[4] = {q10.x, q10.y, q10.z, q10.w}, w11[4] = {q11.x, q11.y, q11.z, q11.w};
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                float a00[4], a01[4], a10[4], a11[4];
+                dequant4(w00[k], in.scale, in.mn, a00); dequant4(w01[k], in.scale, in.mn, a01);
+                dequant4(w10[k], in.scale, in.mn, a10); dequant4(w11[k], in.scale, in.mn, a11);
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    top[4 * k + c] = __fadd_rn(__fmul_rn(l0x, a00[c]), __fmul_rn(l1x, a01[c]));
+                    bot[4 * k + c] = __fadd_rn(__fmul_rn(l0x, a10[c]), __fmul_rn(l1x, a11[c]));
+                }
+            }
+        }
+        const float l0y = __fsub_rn(1.0f, l1y);
+        float v[16];
+#pragma unroll
+        for (int c = 0; c < 16; ++c) v[c] = __fadd_rn(__fmul_rn(l0y, top[c]), __fmul_rn(l1y, bot[c]));
+        const int64_t off = (((int64_t)n * a.OH + oy) * a.OW + ox) * a.Cp + 16 * ch;
+        uint32_t w[4];
+        pack_codes<16>(v, q0, w);
+        *reinterpret_cast<uint4 *>(a.y[0] + off) = make_uint4(keep_left(w[0], left), keep_left(w[1], left - 4),
+                                                              keep_left(w[2], left - 8), keep_left(w[3], left - 12));
+        if (a.y[1]) {
+            pack_codes<16>(v, consts_from_slot(*a.out_slot[1], 8, 0, 0.f, 0.f), w);
+            *reinterpret_cast<uint4 *>(a.y[1] + off) = make_uint4(keep_left(w[0], left), keep_left(w[1], left - 4),
+                                                                  keep_left(w[2], left - 8), keep_left(w[3], left - 12));
+        }
+    }
+}
+
+// fp32 NCHW out, C <= 32: all channel words of the column's row pair blended once, then one vertical blend and one
+// store per channel and output row
+__global__ void __launch_bounds__(kThreads)
+interpq8_f32_rows_kernel(InterpQ8Args a) {
+    const unsigned groups = ((unsigned)a.OH + kInterpRows - 1) / kInterpRows;
+    const unsigned idx = blockIdx.x * kThreads + threadIdx.x;
+    if (idx >= (unsigned)a.N * groups * a.OW) return;
+    const int ox = (int)(idx % (unsigned)a.OW);
+    const int g = (int)((idx / (unsigned)a.OW) % groups);
+    const int n = (int)(idx / ((unsigned)a.OW * groups));
+    int x0, x1; float l1x;
+    q8_interp_index(ox, a.sx, a.W, a.align, x0, x1, l1x);
+    const float l0x = __fsub_rn(1.0f, l1x);
+    const RangeSlot in = *a.in_slot;
+    const int8_t *xn = a.x + (int64_t)n * a.H * a.W * a.Cp;
+    const int64_t rs = (int64_t)a.W * a.Cp, plane = (int64_t)a.OH * a.OW;
+    int cy0 = -1, cy1 = -1;
+    float top[32], bot[32];
+#pragma unroll 1
+    for (int r = 0; r < kInterpRows; ++r) {
+        const int oy = g * kInterpRows + r;
+        if (oy >= a.OH) break;
+        int y0, y1; float l1y;
+        q8_interp_index(oy, a.sy, a.H, a.align, y0, y1, l1y);
+        if (y0 != cy0 || y1 != cy1) {
+            cy0 = y0; cy1 = y1;
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                if (16 * h >= a.C) break;
+                const uint4 q00 = __ldg(reinterpret_cast<const uint4 *>(xn + y0 * rs + (int64_t)x0 * a.Cp) + h);
+                const uint4 q01 = __ldg(reinterpret_cast<const uint4 *>(xn + y0 * rs + (int64_t)x1 * a.Cp) + h);
+                const uint4 q10 = __ldg(reinterpret_cast<const uint4 *>(xn + y1 * rs + (int64_t)x0 * a.Cp) + h);
+                const uint4 q11 = __ldg(reinterpret_cast<const uint4 *>(xn + y1 * rs + (int64_t)x1 * a.Cp) + h);
+                const uint32_t w00[4] = {q00.x, q00.y, q00.z, q00.w}, w01[4] = {q01.x, q01.y, q01.z, q01.w};
+                const uint32_t w10[4] = {q10.x, q10.y, q10.z, q10.w}, w11[4] = {q11.x, q11.y, q11.z, q11.w};
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    float a00[4], a01[4], a10[4], a11[4];
+                    dequant4(w00[k], in.scale, in.mn, a00); dequant4(w01[k], in.scale, in.mn, a01);
+                    dequant4(w10[k], in.scale, in.mn, a10); dequant4(w11[k], in.scale, in.mn, a11);
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) {
+                        top[16 * h + 4 * k + c] = __fadd_rn(__fmul_rn(l0x, a00[c]), __fmul_rn(l1x, a01[c]));
+                        bot[16 * h + 4 * k + c] = __fadd_rn(__fmul_rn(l0x, a10[c]), __fmul_rn(l1x, a11[c]));
+                    }
+                }
+            }
+        }
+        const float l0y = __fsub_rn(1.0f, l1y);
+        float *yp = a.yf + (int64_t)n * a.C * plane + (int64_t)oy * a.OW + ox;
+#pragma unroll
+        for (int c = 0; c < 32; ++c)
+            if (c < a.C) yp[(int64_t)c * plane] = __fadd_rn(__fmul_rn(l0y, top[c]), __fmul_rn(l1y, bot[c]));
+    }
+}
+
 inline float q8_interp_scale(int in, int out, int align) {
     if (align) return out > 1 ? (float)(in - 1) / (float)(out - 1) : 0.0f;
     return out > 0 ? (float)in / (float)out : 0.0f;
@@ -235,16 +361,25 @@ extern "C" int dfq_interp_q8(const int8_t *x, const float *in_slot, int N, int C
     a.N = N; a.C = C; a.Cp = (C + 15) / 16 * 16; a.H = H; a.W = W; a.OH = OH; a.OW = OW; a.align = align_corners ? 1 : 0;
     a.sy = q8_interp_scale(H, OH, a.align); a.sx = q8_interp_scale(W, OW, a.align);
     const cudaStream_t st = (cudaStream_t)stream;
+    // growing at least 2 x vertically: the row-walking forms (DFQ_Q8_INTERP_ROWS=0: the one-row kernels, for A/B runs)
+    const char *env = getenv("DFQ_Q8_INTERP_ROWS");
+    const bool rows = OH >= 2 * H && !(env && env[0] == '0');
+    const int64_t groups = (OH + kInterpRows - 1) / kInterpRows;
     if (y0) {
-        const int64_t blocks = ((int64_t)N * OH * OW * (a.Cp / 16) + kThreads - 1) / kThreads;
-        if (blocks >= (1ll << 23)) return (int)cudaErrorInvalidValue;      // 32-bit thread indices in the kernels
-        interpq8_codes_kernel<<<(unsigned)blocks, kThreads, 0, st>>>(a);
+        const int64_t blocks = ((int64_t)N * (rows ? groups : OH) * OW * (a.Cp / 16) + kThreads - 1) / kThreads;
+        if (((int64_t)N * OH * OW * (a.Cp / 16) + kThreads - 1) / kThreads >= (1ll << 23))
+            return (int)cudaErrorInvalidValue;                             // 32-bit thread indices in the kernels
+        if (rows) interpq8_codes_rows_kernel<<<(unsigned)blocks, kThreads, 0, st>>>(a);
+        else interpq8_codes_kernel<<<(unsigned)blocks, kThreads, 0, st>>>(a);
         g_launches += 1;
     }
     if (yf) {
-        const int64_t blocks = ((int64_t)N * OH * OW + kThreads - 1) / kThreads;
-        if (blocks >= (1ll << 23)) return (int)cudaErrorInvalidValue;      // 32-bit thread indices in the kernels
-        interpq8_f32_kernel<<<(unsigned)blocks, kThreads, 0, st>>>(a);
+        const bool rows_f = rows && a.Cp <= 32;
+        const int64_t blocks = ((int64_t)N * (rows_f ? groups : OH) * OW + kThreads - 1) / kThreads;
+        if (((int64_t)N * OH * OW + kThreads - 1) / kThreads >= (1ll << 23))
+            return (int)cudaErrorInvalidValue;                             // 32-bit thread indices in the kernels
+        if (rows_f) interpq8_f32_rows_kernel<<<(unsigned)blocks, kThreads, 0, st>>>(a);
+        else interpq8_f32_kernel<<<(unsigned)blocks, kThreads, 0, st>>>(a);
         g_launches += 1;
     }
     return (int)cudaGetLastError();

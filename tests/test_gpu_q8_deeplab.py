@@ -296,3 +296,33 @@ def test_static_plan_on_other_image_sizes(static_deeplab):
         shift = float((got - ref).abs().max() / ref.abs().max())
         print(f"{n}x3x{h}x{w}: classes agree {agree:.4f}, logits {shift:.2e} of the largest")
         assert got.shape == ref.shape and agree >= 0.998 and shift <= 0.1
+
+
+@pytest.mark.parametrize("N,C,H,W,OH,OW,align", [(2, 256, 33, 33, 129, 129, 1), (1, 21, 129, 129, 513, 513, 1),
+                                                   (2, 21, 7, 9, 20, 13, 0), (3, 40, 5, 6, 17, 31, 1),
+                                                   (1, 19, 4, 4, 9, 9, 0)])
+def test_interp_row_walking_kernels_equal_the_one_row_kernels(N, C, H, W, OH, OW, align, monkeypatch):
+    """The upscaling forms of dfq_interp_q8 (a thread walks four output rows and forms the horizontal blends once per
+    input row pair) against the one-output-per-thread kernels (DFQ_Q8_INTERP_ROWS=0): same operations per value, so
+    the same bytes -- codes on two grids and the fp32 output."""
+    from data_free_quantization_b200 import _lib as L
+    from data_free_quantization_b200.eval_q8 import to_codes_nhwc
+    from test_gpu_q8 import slot
+    lib = L.lib()
+    rng = np.random.default_rng(5 + C)
+    Cp = (C + 15) // 16 * 16
+    x = to_codes_nhwc(torch.from_numpy(rng.integers(0, 256, (N, C, H, W)).astype(np.uint8))).reshape(-1).to(DEV)
+    (sl, _), (s0, _), (s1, _) = slot(-1.5, 3.0), slot(-1.0, 2.5), slot(-2.0, 3.5)
+    res = []
+    for rows in ("0", "1"):
+        monkeypatch.setenv("DFQ_Q8_INTERP_ROWS", rows)
+        y0 = torch.full((N * OH * OW * Cp,), 77, dtype=torch.int8, device=DEV)
+        y1 = torch.full((N * OH * OW * Cp,), 77, dtype=torch.int8, device=DEV)
+        yf = torch.full((N, C, OH, OW), float("nan"), device=DEV)
+        L.check(lib.dfq_interp_q8(x.data_ptr(), sl.data_ptr(), N, C, H, W, OH, OW, align, y0.data_ptr(), s0.data_ptr(),
+                                  y1.data_ptr(), s1.data_ptr(), yf.data_ptr(), L.stream()), "dfq_interp_q8")
+        torch.cuda.synchronize()
+        res.append((y0, y1, yf))
+    for a, b in zip(*res):
+        assert torch.equal(a, b)
+    assert not bool((res[1][0] == 77).all()) and not torch.isnan(res[1][2]).any()
