@@ -156,6 +156,37 @@ regridq8_kernel(RegridQ8Args a) {
     if (a.y[1]) *reinterpret_cast<uint32_t *>(a.y[1] + off) = w1;
 }
 
+// the same on whole 16-channel chunks (operand offset and row pitch multiples of 16, and either C a multiple of 16 or
+// this operand the row's last): one 128-bit load and store per thread, the slot constants formed once per 16 values
+__global__ void __launch_bounds__(kThreads)
+regridq8_v16_kernel(RegridQ8Args a) {
+    const unsigned chunks = (unsigned)(a.words_out + 3) >> 2;
+    const unsigned idx = blockIdx.x * kThreads + threadIdx.x;
+    if (idx >= (unsigned)a.G * chunks) return;
+    const int ci = (int)(idx % chunks);
+    const int64_t g = idx / chunks;
+    const int left = a.C - 16 * ci;
+    uint4 o0 = make_uint4(0u, 0u, 0u, 0u), o1 = o0;
+    if (left > 0) {
+        const RangeSlot in = *a.in_slot;
+        const uint4 q = __ldg(reinterpret_cast<const uint4 *>(a.x + g * a.cp_in) + ci);
+        const uint32_t qw[4] = {q.x, q.y, q.z, q.w};
+        float v[16];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) dequant4(qw[k], in.scale, in.mn, v + 4 * k);
+        uint32_t w[4];
+        pack_codes<16>(v, consts_from_slot(*a.out_slot[0], 8, 0, 0.f, 0.f), w);
+        o0 = make_uint4(keep_left(w[0], left), keep_left(w[1], left - 4), keep_left(w[2], left - 8), keep_left(w[3], left - 12));
+        if (a.y[1]) {
+            pack_codes<16>(v, consts_from_slot(*a.out_slot[1], 8, 0, 0.f, 0.f), w);
+            o1 = make_uint4(keep_left(w[0], left), keep_left(w[1], left - 4), keep_left(w[2], left - 8), keep_left(w[3], left - 12));
+        }
+    }
+    const int64_t off = g * a.cp_out + a.c_off + 16 * ci;
+    *reinterpret_cast<uint4 *>(a.y[0] + off) = o0;
+    if (a.y[1]) *reinterpret_cast<uint4 *>(a.y[1] + off) = o1;
+}
+
 // mean over the HW rows of x[n] ([HW][C] fp32, rows `ld` floats apart): a block per (n, 32 channels), lanes on channels
 // (coalesced 128-byte row segments), warps striding the rows; fp64 accumulation, fixed combination order
 __global__ void __launch_bounds__(kThreads)
@@ -398,6 +429,14 @@ extern "C" int dfq_regrid_q8(const int8_t *x, const float *in_slot, int64_t G, i
     a.words_out = fill_tail ? (cp_out - c_off) / 4 : (C + 3) / 4;
     const int64_t blocks = (G * a.words_out + kThreads - 1) / kThreads;
     if (blocks >= (1ll << 23)) return (int)cudaErrorInvalidValue;      // 32-bit thread indices in the kernels
+    const char *env = getenv("DFQ_Q8_REGRID_V16");                     // (=0: the word kernel, for A/B runs)
+    const bool v16 = (c_off % 16) == 0 && (cp_out % 16) == 0 && ((C % 16) == 0 || fill_tail) &&
+                     ((uintptr_t)y0 % 16) == 0 && (!y1 || ((uintptr_t)y1 % 16) == 0) && ((uintptr_t)x % 16) == 0 &&
+                     !(env && env[0] == '0');
+    if (v16) {
+        const int64_t chunks = (a.words_out + 3) / 4;
+        regridq8_v16_kernel<<<(unsigned)((G * chunks + kThreads - 1) / kThreads), kThreads, 0, (cudaStream_t)stream>>>(a);
+    } else
     regridq8_kernel<<<(unsigned)blocks, kThreads, 0, (cudaStream_t)stream>>>(a);
     g_launches += 1;
     return (int)cudaGetLastError();

@@ -326,3 +326,33 @@ def test_interp_row_walking_kernels_equal_the_one_row_kernels(N, C, H, W, OH, OW
     for a, b in zip(*res):
         assert torch.equal(a, b)
     assert not bool((res[1][0] == 77).all()) and not torch.isnan(res[1][2]).any()
+
+
+@pytest.mark.parametrize("G,C,c_off,cp_out,fill,dual", [(1089, 256, 512, 1280, 0, False), (4000, 48, 256, 304, 1, True),
+                                                          (300, 40, 16, 64, 1, False), (77, 24, 0, 64, 0, True)])
+def test_regrid_chunk_kernel_equals_the_word_kernel(G, C, c_off, cp_out, fill, dual, monkeypatch):
+    """dfq_regrid_q8 on whole 16-channel chunks against the word-per-thread kernel (DFQ_Q8_REGRID_V16=0): the same
+    bytes in the operand's slice, and nothing outside it (the last case is not eligible and stays on the word kernel)."""
+    from data_free_quantization_b200 import _lib as L
+    from data_free_quantization_b200.eval_q8 import to_codes_nhwc
+    from test_gpu_q8 import slot
+    lib = L.lib()
+    rng = np.random.default_rng(C)
+    x = to_codes_nhwc(torch.from_numpy(rng.integers(0, 256, (G, C)).astype(np.uint8))).reshape(-1).to(DEV)
+    (sl, _), (s0, _), (s1, _) = slot(-1.5, 3.0), slot(-1.0, 2.5), slot(-2.0, 3.5)
+    res = []
+    for v16 in ("0", "1"):
+        monkeypatch.setenv("DFQ_Q8_REGRID_V16", v16)
+        y0 = torch.full((G, cp_out), 77, dtype=torch.int8, device=DEV)
+        y1 = torch.full((G, cp_out), 77, dtype=torch.int8, device=DEV)
+        L.check(lib.dfq_regrid_q8(x.data_ptr(), sl.data_ptr(), G, C, y0.data_ptr(), s0.data_ptr(),
+                                  y1.data_ptr() if dual else None, s1.data_ptr() if dual else None, cp_out, c_off, fill,
+                                  L.stream()), "dfq_regrid_q8")
+        torch.cuda.synchronize()
+        res.append((y0, y1))
+    for a, b in zip(*res):
+        assert torch.equal(a, b)
+    y0 = res[1][0]
+    assert bool((y0[:, :c_off] == 77).all()) and not bool((y0[:, c_off:c_off + C] == 77).all())
+    if not fill:
+        assert bool((y0[:, c_off + (C + 3) // 4 * 4:] == 77).all())
