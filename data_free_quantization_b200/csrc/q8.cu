@@ -340,10 +340,12 @@ __device__ __forceinline__ float small_int_to_float(int v) {      // exact for |
 
 // a.pad is 1 (the convolution pads with zeros) or 0 (DeepLab: F.pad ran ahead of the QuantMeasure, the padded tensor exists
 // as codes -- dfq_pad_q8 -- and every tap is in bounds).
-template <int S, bool DUAL, int PAD>
+// DIL = 2 (stride 1, no padding: DeepLab's dilated block): the taps of a row are bytes (k, k + 2, k + 4) of the same
+// 12-byte string, eight outputs per strip.
+template <int S, bool DUAL, int PAD, int DIL = 1>
 __global__ void __launch_bounds__(kThreads, 2)
 dwq8_kernel(DwQ8Args a) {
-    constexpr int P = DwStrip<S>::value;
+    constexpr int P = DIL == 2 ? 8 : DwStrip<S>::value;
     const unsigned cw = (unsigned)a.Cp >> 2;                      // channel words per pixel
     const unsigned idx = blockIdx.x * kThreads + threadIdx.x;
     if (idx >= (unsigned)a.N * (unsigned)a.OH * cw) return;
@@ -359,8 +361,8 @@ dwq8_kernel(DwQ8Args a) {
     QuantConsts q1 = q0;
     if (DUAL) q1 = consts_from_slot(*a.out_slot[1], 8, 0, 0.f, 0.f);
     const int iy0 = oy * S - PAD;
-    const bool rowok[3] = {(unsigned)iy0 < (unsigned)a.H, (unsigned)(iy0 + 1) < (unsigned)a.H,
-                           (unsigned)(iy0 + 2) < (unsigned)a.H};
+    const bool rowok[3] = {(unsigned)iy0 < (unsigned)a.H, (unsigned)(iy0 + DIL) < (unsigned)a.H,
+                           (unsigned)(iy0 + 2 * DIL) < (unsigned)a.H};
     uint32_t wr[3][4];                                            // [row][channel] = (w0, w1, w2, 0) centred s8
 #pragma unroll
     for (int r = 0; r < 3; ++r) {
@@ -406,7 +408,7 @@ dwq8_kernel(DwQ8Args a) {
         uint32_t t[3][3][4];                                      // [row][block][channel]: 4 adjacent pixels of a channel
 #pragma unroll
         for (int r = 0; r < 3; ++r) {
-            const int8_t *xr = xn + (int64_t)(iy0 + r) * a.W * a.Cp;
+            const int8_t *xr = xn + (int64_t)(iy0 + r * DIL) * a.W * a.Cp;
 #pragma unroll
             for (int blk = 0; blk < 3; ++blk) {
                 uint32_t p[4];
@@ -429,7 +431,8 @@ dwq8_kernel(DwQ8Args a) {
             constexpr int o = 0;  (void)o;
             const int off_b = k * S;                              // byte offset of the window in the 12-byte row string
             const int wi = off_b >> 2, sh = off_b & 3;
-            const uint32_t sel = 0x3210u + 0x1111u * (uint32_t)sh;
+            const uint32_t sel = DIL == 2 ? ((uint32_t)sh | ((uint32_t)(sh + 2) << 4) | ((uint32_t)(sh + 4) << 8))
+                                          : 0x3210u + 0x1111u * (uint32_t)sh;     // (byte 3 meets a zero weight byte)
             int acc[4], sa[4];
 #pragma unroll
             for (int c = 0; c < 4; ++c) {
@@ -443,7 +446,7 @@ dwq8_kernel(DwQ8Args a) {
                 }
             }
             const int ixl = ox * S - PAD;
-            const bool lin = ixl >= 0, rin = ixl + 2 < a.W;      // left / right tap column in bounds (centre always is)
+            const bool lin = ixl >= 0, rin = ixl + 2 * DIL < a.W;  // left / right tap column in bounds (centre always is)
             float yv[4];
 #pragma unroll
             for (int c = 0; c < 4; ++c) {
@@ -1034,6 +1037,11 @@ int conv_q8_tma(const DfqConvQ8Desc *d, void *stream) {
 }
 }  // namespace dfq
 
+static bool dw_dil2_off() {                       // DFQ_Q8_DW_DIL2=0: dilated layers on the generic kernel (A/B runs)
+    const char *e = getenv("DFQ_Q8_DW_DIL2");
+    return e && e[0] == '0';
+}
+
 extern "C" int dfq_dw_q8(const DfqDwQ8Desc *d, void *stream) {
     if (!d || !d->x || !d->wrow || !d->in_slot || !d->y0 || !d->out_slot0 || (d->y1 && !d->out_slot1) || d->N <= 0 ||
         (d->stride != 1 && d->stride != 2) || d->pad < 0 || d->dil < 0)
@@ -1049,6 +1057,16 @@ extern "C" int dfq_dw_q8(const DfqDwQ8Desc *d, void *stream) {
     a.OH = (d->H + 2 * a.pad - 2 * a.dil - 1) / d->stride + 1; a.OW = (d->W + 2 * a.pad - 2 * a.dil - 1) / d->stride + 1;
     if (a.OH <= 0 || a.OW <= 0) return (int)cudaErrorInvalidValue;
     const cudaStream_t st = (cudaStream_t)stream;
+    if (a.dil == 2 && a.pad == 0 && d->stride == 1 && !dw_dil2_off()) {      // the strip kernel on dilated taps
+        a.strips = (a.OW + 7) / 8;
+        const int64_t total = (int64_t)a.N * a.OH * (a.Cp / 4);
+        if (total >= 0x7fffffffll) return (int)cudaErrorInvalidValue;
+        const unsigned grid = (unsigned)((total + kThreads - 1) / kThreads);
+        if (d->y1) dwq8_kernel<1, true, 0, 2><<<grid, kThreads, 0, st>>>(a);
+        else dwq8_kernel<1, false, 0, 2><<<grid, kThreads, 0, st>>>(a);
+        g_launches += 1;
+        return (int)cudaGetLastError();
+    }
     if (a.pad > 1 || a.dil != 1) {
         const int64_t total = (int64_t)a.N * a.OH * a.OW * (a.Cp / 4);
         const int64_t blocks = (total + kThreads - 1) / kThreads;

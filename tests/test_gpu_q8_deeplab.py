@@ -356,3 +356,52 @@ def test_regrid_chunk_kernel_equals_the_word_kernel(G, C, c_off, cp_out, fill, d
     assert bool((y0[:, :c_off] == 77).all()) and not bool((y0[:, c_off:c_off + C] == 77).all())
     if not fill:
         assert bool((y0[:, c_off + (C + 3) // 4 * 4:] == 77).all())
+
+
+@pytest.mark.parametrize("N,C,H,W,dual", [(2, 960, 37, 37, False), (1, 40, 15, 18, True), (3, 16, 5, 6, False),
+                                          (1, 100, 9, 29, True)])
+def test_dilated_depthwise_strip_kernel_equals_the_generic_kernel(oracle, N, C, H, W, dual, monkeypatch):
+    """Dilation 2, no padding, stride 1 (DeepLab's dilated block after F.pad) on the strip kernel (taps = bytes k, k + 2,
+    k + 4 of the transposed row string) against the one-pixel-per-thread kernel (DFQ_Q8_DW_DIL2=0): the same integer
+    sums in the same fp32 expression, so the same bytes; and against a float64 convolution."""
+    import ctypes
+    import torch.nn.functional as F
+    from data_free_quantization_b200 import _lib as L
+    from data_free_quantization_b200.eval_q8 import from_codes_nhwc, pack_depthwise, to_codes_nhwc
+    from test_gpu_q8 import slot
+    lib = L.lib()
+    rng = np.random.default_rng(C + W)
+    Cp = (C + 15) // 16 * 16
+    lo, hi = -1.5, 3.0
+    sl, sx = slot(lo, hi)
+    xc = rng.integers(0, 256, (N, C, H, W)).astype(np.uint8)
+    x = to_codes_nhwc(torch.from_numpy(xc)).reshape(-1).to(DEV)
+    w0 = (rng.standard_normal((C, 1, 3, 3)) * 0.3).astype(np.float32)
+    w, _ = oracle.fake_quant(w0, 8, float(w0.min()), float(w0.max()), want_codes=True)
+    wrow, dsw, dcw = pack_depthwise(torch.from_numpy(w).to(DEV))
+    bias = (rng.standard_normal(C) * 0.2).astype(np.float32)
+    bp = torch.zeros(Cp, device=DEV); bp[:C] = torch.from_numpy(bias).to(DEV)
+    xf = (xc.astype(np.float32) * np.float32(sx)).astype(np.float32) + np.float32(lo)
+    ref = np.maximum(F.conv2d(torch.from_numpy(xf).double(), torch.from_numpy(w).double(), torch.from_numpy(bias).double(),
+                              1, 0, 2, C).numpy(), 0)
+    OH, OW = ref.shape[2:]
+    outs = [(0.0, float(ref.max()) * 0.9 + 0.1), (0.02, float(ref.max()) * 0.5 + 0.1)]
+    (s0, _), (s1, _) = slot(*outs[0]), slot(*outs[1])
+    res = []
+    for fast in ("0", "1"):
+        monkeypatch.setenv("DFQ_Q8_DW_DIL2", fast)
+        y0 = torch.full((N * OH * OW * Cp,), 77, dtype=torch.int8, device=DEV)
+        y1 = torch.full((N * OH * OW * Cp,), 77, dtype=torch.int8, device=DEV)
+        d = L.DfqDwQ8Desc()
+        d.x, d.wrow, d.bias, d.in_slot, d.y0, d.out_slot0 = x.data_ptr(), wrow.data_ptr(), bp.data_ptr(), sl.data_ptr(), y0.data_ptr(), s0.data_ptr()
+        if dual:
+            d.y1, d.out_slot1 = y1.data_ptr(), s1.data_ptr()
+        d.N, d.H, d.W, d.C, d.stride, d.relu, d.s_w, d.c_w, d.pad, d.dil = N, H, W, C, 1, 1, dsw, dcw, 0, 2
+        L.check(lib.dfq_dw_q8(ctypes.byref(d), L.stream()), "dfq_dw_q8")
+        torch.cuda.synchronize()
+        res.append((y0, y1))
+    for a, b in zip(*res):
+        assert torch.equal(a, b)
+    for yb, (l, h) in list(zip(res[1], outs))[:2 if dual else 1]:
+        want = oracle.fake_quant(ref.astype(np.float32), 8, float(np.float32(l)), float(np.float32(h)), want_codes=True)[1]
+        check_codes(from_codes_nhwc(yb.cpu(), (N, C, OH, OW)).numpy(), want, "dilated depthwise, strip kernel")
