@@ -93,29 +93,35 @@ qinterp_kernel(const float *__restrict__ x, float *__restrict__ y, int C, int H,
         ytab[r] = make_int4((y0 - ys0) * W, (y1 - ys0) * W, __float_as_int(l1), 0);
     }
     __syncthreads();
-    // One output per thread and step, lanes on CONSECUTIVE outputs of the band's flat run: the column table is read
-    // conflict-free, the row table as a broadcast, the store is a coalesced 4-byte store whatever the row length (the
-    // previous form gave a thread 4 adjacent outputs for a 16-byte store: 86 thread-instructions per output, 87 %
-    // issue-active -- ncu, profiles/r1zz_move_ncu.md).  (row, column) advance by a fixed step, no division.
+    // A thread owns output COLUMNS (tid, tid + 256, ...) and walks the band's rows: its column's {x0, x1, l1x} live in
+    // registers, the row table is a broadcast, and the horizontal blends `top` / `bot` are formed once per source row
+    // pair -- when the image grows 4 x, four output rows share one, so an output costs the vertical blend, the store
+    // and the extrema (the one-output-per-step form re-read both tables and all four taps for every output: 71
+    // thread-instructions per output at 89 % issue-active under ncu).  Lanes sit on adjacent columns: coalesced 4-byte
+    // stores whatever the row length.  Same operations per value in the same order: the same bits.
     float *dst = y + ((int64_t)n * C + c) * OH * OW + (int64_t)r0 * OW;
-    const int count = (r1 - r0) * OW;
-    const int dq = kThreads / OW, dr = kThreads - dq * OW;
-    int row = (int)threadIdx.x / OW, ox = (int)threadIdx.x - row * OW;
+    const int nrows = r1 - r0;
     float lo = INFINITY, hi = -INFINITY;
-    for (int j = threadIdx.x; j < count; j += kThreads) {
+    for (int ox = threadIdx.x; ox < OW; ox += kThreads) {
         const int2 e = xtab[ox];
-        const int4 yy = ytab[row];
         const int x0 = e.x & 0xffff, x1 = e.x >> 16;
         const float l1x = __int_as_float(e.y), l0x = __fsub_rn(1.0f, l1x);
-        const float l1y = __int_as_float(yy.z), l0y = __fsub_rn(1.0f, l1y);
-        const float *s0 = src + yy.x, *s1 = src + yy.y;
-        const float top = __fadd_rn(__fmul_rn(l0x, s0[x0]), __fmul_rn(l1x, s0[x1]));
-        const float bot = __fadd_rn(__fmul_rn(l0x, s1[x0]), __fmul_rn(l1x, s1[x1]));
-        const float v = __fadd_rn(__fmul_rn(l0y, top), __fmul_rn(l1y, bot));
-        dst[j] = v;
-        lo = fminf(lo, v); hi = fmaxf(hi, v);
-        ox += dr; row += dq;
-        if (ox >= OW) { ox -= OW; ++row; }
+        int cy0 = -1, cy1 = -1;
+        float top = 0.0f, bot = 0.0f;
+        float *d = dst + ox;
+        for (int r = 0; r < nrows; ++r, d += OW) {
+            const int4 yy = ytab[r];
+            if (yy.x != cy0 || yy.y != cy1) {                      // (uniform across the block)
+                cy0 = yy.x; cy1 = yy.y;
+                const float *s0 = src + yy.x, *s1 = src + yy.y;
+                top = __fadd_rn(__fmul_rn(l0x, s0[x0]), __fmul_rn(l1x, s0[x1]));
+                bot = __fadd_rn(__fmul_rn(l0x, s1[x0]), __fmul_rn(l1x, s1[x1]));
+            }
+            const float l1y = __int_as_float(yy.z), l0y = __fsub_rn(1.0f, l1y);
+            const float v = __fadd_rn(__fmul_rn(l0y, top), __fmul_rn(l1y, bot));
+            *d = v;
+            lo = fminf(lo, v); hi = fmaxf(hi, v);
+        }
     }
     if (stats) stats_flush(stats, n, lo, hi, red);
 }
