@@ -134,11 +134,12 @@ class DfqStemQ8Desc(ctypes.Structure):
     _fields_ = [("x", c_void), ("w", c_void), ("bias", c_void), ("in_slot", c_void), ("y0", c_void),
                 ("out_slot0", c_void), ("y1", c_void), ("out_slot1", c_void)] + \
                [(k, i32) for k in ("N", "H", "W", "O", "stride", "pad", "relu", "reserved")] + \
-               [("map0", DfqQ8OutMap), ("map1", DfqQ8OutMap), ("wq", c_void), ("s_w", f32), ("c_w", f32)]
+               [("map0", DfqQ8OutMap), ("map1", DfqQ8OutMap), ("wq", c_void), ("s_w", f32), ("c_w", f32), ("yf", c_void),
+                ("out_stats", c_void)]
 
 
 Q_SYMMETRIC, Q_RANGE_F32, Q_PER_CHANNEL, Q_CLAMP_OUT = 1, 2, 4, 8
-ABI_VERSION = 22
+ABI_VERSION = 23
 
 # every symbol include/dfq_b200.h declares: (restype, argtypes)
 P = ctypes.POINTER

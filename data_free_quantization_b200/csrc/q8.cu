@@ -533,6 +533,7 @@ struct StemQ8Args {
     int N, H, W, OH, OW, O, Cp, stride, pad, relu;
     Q8OutMap omap[2];
     const uint32_t *wq; float s_w, c_w;       // integer form: [32][8] words of centred s8 weight codes (taps 4k .. 4k + 3)
+    float *yf; unsigned *stats;               // F32 form (dynamic-range plan): fp32 NCHW out + encoded per-sample extrema
 };
 
 __global__ void __launch_bounds__(kThreads)
@@ -632,6 +633,9 @@ stemq8_kernel(StemQ8Args a) {
 // the reference), and an output channel is seven dp4a against its packed weights instead of 27 FMAs on dequantised
 // values.  Same decomposition as the depthwise kernel:
 //   y = s_x s_w SUM a b + s_x c_w SUM a + c_x s_w SUM_inb b + n_inb c_x c_w + bias.
+// F32 (the dynamic-range plan, eval_plan.py): the same sums leave as fp32 NCHW with the per-sample extrema of the result
+// for the next QuantMeasure (utils/quantize.py:110-111) instead of codes.
+template <bool F32>
 __global__ void __launch_bounds__(kThreads, 3)
 stemq8_i8_kernel(StemQ8Args a) {
     __shared__ __align__(16) uint32_t swq[32][8];
@@ -654,12 +658,14 @@ stemq8_i8_kernel(StemQ8Args a) {
     __syncthreads();
     const int64_t total = (int64_t)a.N * a.OH * a.OW;
     const QuantConsts qi = consts_from_slot(in, 8, 0, 0.f, 0.f);
-    const bool has1 = a.y[1] != nullptr;
-    const QuantConsts q0 = consts_from_slot(*a.out_slot[0], 8, 0, 0.f, 0.f);
-    QuantConsts q1 = q0;
+    const bool has1 = !F32 && a.y[1] != nullptr;
+    QuantConsts q0 = qi, q1 = qi;
+    if (!F32) q0 = consts_from_slot(*a.out_slot[0], 8, 0, 0.f, 0.f);
     if (has1) q1 = consts_from_slot(*a.out_slot[1], 8, 0, 0.f, 0.f);
     const float floor_v = a.relu ? 0.0f : -INFINITY;
-    for (int64_t p = (int64_t)blockIdx.x * kThreads + threadIdx.x; p < total; p += (int64_t)gridDim.x * kThreads) {
+    for (int64_t base = (int64_t)blockIdx.x * kThreads; base < total; base += (int64_t)gridDim.x * kThreads) {
+    const bool valid = base + threadIdx.x < total;                // (the loop bound is block-uniform: F32 ends in shuffles)
+    const int64_t p = valid ? base + threadIdx.x : total - 1;
     const int ox = (int)(p % a.OW);
     const int oy = (int)((p / a.OW) % a.OH);
     const int n = (int)(p / ((int64_t)a.OW * a.OH));
@@ -698,6 +704,7 @@ stemq8_i8_kernel(StemQ8Args a) {
 #pragma unroll
     for (int k = 0; k < 7; ++k) sa = __dp4a((int)aw[k], 0x01010101, sa);
     const float ninb_cxcw = __fmul_rn((float)(3 * nr * nc), cxcw);
+    float lo = INFINITY, hi = -INFINITY;
     for (int ob = 0; ob < a.Cp; ob += 16) {
         float yv[16];
 #pragma unroll
@@ -717,6 +724,20 @@ stemq8_i8_kernel(StemQ8Args a) {
             }
             yv[c] = fmaxf(__fmaf_rn(fa, small_int_to_float(acc), __fmaf_rn(fb, small_int_to_float(sa), cst)), floor_v);
         }
+        if (F32) {
+            if (valid) {
+                const int64_t plane = (int64_t)a.OH * a.OW;
+                float *yp = a.yf + ((int64_t)n * a.O + ob) * plane + (int64_t)oy * a.OW + ox;
+#pragma unroll
+                for (int c = 0; c < 16; ++c)
+                    if (ob + c < a.O) {
+                        yp[c * plane] = yv[c];
+                        lo = fminf(lo, yv[c]); hi = fmaxf(hi, yv[c]);
+                    }
+            }
+            continue;
+        }
+        if (!valid) continue;
 #pragma unroll
         for (int t2 = 0; t2 < 2; ++t2) {
             if (t2 && !has1) continue;
@@ -726,6 +747,19 @@ stemq8_i8_kernel(StemQ8Args a) {
 #pragma unroll
             for (int j4 = 0; j4 < 4; ++j4) w4[j4] = keep_left(w4[j4], a.O - ob - 4 * j4);
             *reinterpret_cast<uint4 *>(a.y[t2] + q8_out_pixel(a.omap[t2], p) * a.Cp + ob) = make_uint4(w4[0], w4[1], w4[2], w4[3]);
+        }
+    }
+    if (F32 && a.stats) {                                         // per-sample extrema, encoded (common.cuh)
+        const int n0 = __shfl_sync(0xffffffffu, n, 0);
+        if (__all_sync(0xffffffffu, valid && n == n0)) {
+            lo = warp_min(lo); hi = warp_max(hi);
+            if ((threadIdx.x & 31) == 0 && hi >= lo) {
+                atomicMax(a.stats + 2 * n, enc_ordered(-lo));
+                atomicMax(a.stats + 2 * n + 1, enc_ordered(hi));
+            }
+        } else if (valid && hi >= lo) {
+            atomicMax(a.stats + 2 * n, enc_ordered(-lo));
+            atomicMax(a.stats + 2 * n + 1, enc_ordered(hi));
         }
     }
     }
@@ -1096,8 +1130,8 @@ extern "C" int dfq_dw_q8(const DfqDwQ8Desc *d, void *stream) {
 }
 
 extern "C" int dfq_stem_q8(const DfqStemQ8Desc *d, void *stream) {
-    if (!d || !d->x || !d->w || !d->in_slot || !d->y0 || !d->out_slot0 || (d->y1 && !d->out_slot1) || d->N <= 0 ||
-        d->O < 1 || d->O > 32)
+    if (!d || !d->x || !d->w || !d->in_slot || (d->y1 && !d->out_slot1) || d->N <= 0 || d->O < 1 || d->O > 32 ||
+        (d->yf ? (d->y0 || d->y1 || !d->wq) : (!d->y0 || !d->out_slot0)))
         return (int)cudaErrorInvalidValue;
     StemQ8Args a = {};
     a.x = d->x; a.w = d->w; a.bias = d->bias; a.in_slot = (const RangeSlot *)d->in_slot;
@@ -1112,7 +1146,10 @@ extern "C" int dfq_stem_q8(const DfqStemQ8Desc *d, void *stream) {
     static_assert(kThreads == 256, "stemq8_i8_kernel stages its 32 x 8 weight words with one load per thread");
     if (a.wq) {             // blocks walk the pixels grid-stride: the weight words are staged once per resident block
         const int64_t blocks = (total + kThreads - 1) / kThreads, resident = (int64_t)sm_count() * 3 * 4;
-        stemq8_i8_kernel<<<(unsigned)(blocks < resident ? blocks : resident), kThreads, 0, (cudaStream_t)stream>>>(a);
+        const unsigned grid = (unsigned)(blocks < resident ? blocks : resident);
+        a.yf = d->yf; a.stats = d->out_stats;
+        if (a.yf) stemq8_i8_kernel<true><<<grid, kThreads, 0, (cudaStream_t)stream>>>(a);
+        else stemq8_i8_kernel<false><<<grid, kThreads, 0, (cudaStream_t)stream>>>(a);
     }
     else
     stemq8_kernel<<<(unsigned)((total + kThreads - 1) / kThreads), kThreads, 0, (cudaStream_t)stream>>>(a);

@@ -325,6 +325,9 @@ class EvalPlan:
                     # (the 3-channel stem stays on the register-blocked direct kernel: 0.43 ms against 1.41 ms as
                     # an implicit GEMM whose 16-byte K chunks would be 13/16 padding)
                     i8 = self._conv_i8_launch(m, wq, bq, src, out, st, s, p, d)
+                elif (g == 1 and kh == 3 and kw == 3 and d == 1 and src.shape[1] == 3 and m.out_channels <= 32
+                        and st["slot"] is not None and os.environ.get("DFQ_STEM_I8", "1") != "0"):
+                    i8 = self._stem_i8_launch(m, wq, bq, src, out, st, s, p)
                 self.ops.append((st["name"], i8 or self._conv_launch(desc, st)))
             elif st["kind"] == "linear":
                 m, src, out = st["m"], st["src"], st["out"]
@@ -507,6 +510,28 @@ class EvalPlan:
         self.keep += [pk, desc, scratch]
         self.i8_layers.append(st["name"])
         return lambda: pw_i8.launch_conv(desc)
+
+    def _stem_i8_launch(self, m, wq, bq, src, out, st, stride, pad):
+        """The 3-channel 3 x 3 stem on exact integer sums (dfq_stem_q8 with fp32 output: seven dp4a per output channel
+        instead of 27 FMAs), or None when the weights are off-grid / the activations are not 8-bit."""
+        from .eval_q8 import pack_stem
+        if int(m.quant.num_bits) != 8:
+            return None
+        pk = pack_stem(wq)
+        if pk is None:
+            return None
+        lib, stream = L.lib(), L.stream
+        d = L.DfqStemQ8Desc()
+        d.x, d.w = src.buf.data_ptr(), L.dev_f32(wq.contiguous(), "weight")
+        d.bias = None if bq is None else L.dev_f32(bq, "bias")
+        d.in_slot = self.slots[st["slot"]].data_ptr()
+        d.N, d.H, d.W, d.O, d.stride, d.pad, d.relu = src.shape[0], src.shape[2], src.shape[3], m.out_channels, stride, pad, st["relu"]
+        d.wq, d.s_w, d.c_w = pk[0].data_ptr(), pk[1], pk[2]
+        d.yf = out.buf.data_ptr()
+        d.out_stats = None if out.stats is None else out.stats.data_ptr()
+        self.keep += [pk[0], d]
+        self.i8_layers.append(st["name"])
+        return lambda: L.check(lib.dfq_stem_q8(ctypes.byref(d), stream()), "dfq_stem_q8")
 
     def _conv_launch(self, desc, st):
         lib, stream = L.lib(), L.stream

@@ -23,7 +23,7 @@
 extern "C" {
 #endif
 
-#define DFQ_ABI_VERSION 22
+#define DFQ_ABI_VERSION 23
 
 #if defined(__GNUC__)
 #pragma GCC visibility push(default)   /* the library is built with -fvisibility=hidden */
@@ -449,6 +449,8 @@ typedef struct DfqStemQ8Desc {
     const int32_t *wq;       /* optional: [32][8] words of centred s8 weight codes, word k = taps 4k .. 4k + 3 in     */
     float s_w, c_w;          /* (c, kh, kw) order, rows >= O and taps >= 27 zero; w = s_w * code + c_w.  Non-NULL: the */
                              /* exact-integer (dp4a) kernel, else fp32 FMAs on the dequantised inputs                 */
+    float *yf;               /* optional (needs wq; y0 / y1 NULL): the dynamic-range plan's form -- fp32 NCHW output   */
+    uint32_t *out_stats;     /* and the encoded per-sample extrema [N][2] of it (as DfqConvDesc.out_stats), or NULL    */
 } DfqStemQ8Desc;
 /* dense 3 x 3 stem on 3 input channels, O <= 32 */
 int dfq_stem_q8(const DfqStemQ8Desc *desc_host, void *stream);

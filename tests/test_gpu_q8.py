@@ -390,5 +390,19 @@ def test_stem_q8_integer_kernel(oracle, N, H, W, O, stride, dual):
         _q, want = oracle.fake_quant(ref.astype(np.float32), 8, float(np.float32(lo)), float(np.float32(hi)), want_codes=True)
         check_codes(from_codes_nhwc(yb.cpu(), ref.shape).numpy(), want, f"stem i8 {H}x{W}")
         assert not yb.cpu().view(-1, Cp)[:, O:].any()          # padding channels: s8 zero
+    # the dynamic-range plan's form: the same sums as fp32 NCHW + encoded per-sample extrema
+    yf = torch.full((N, O, OH, OW), float("nan"), device=DEV)
+    stats = torch.zeros(N, 2, dtype=torch.int32, device=DEV)
+    d2 = L.DfqStemQ8Desc()
+    d2.x, d2.w, d2.bias, d2.in_slot = xd.data_ptr(), wd.data_ptr(), bd.data_ptr(), in_slot.data_ptr()
+    d2.N, d2.H, d2.W, d2.O, d2.stride, d2.pad, d2.relu = N, H, W, O, stride, 1, 1
+    d2.wq, d2.s_w, d2.c_w, d2.yf, d2.out_stats = pk[0].data_ptr(), pk[1], pk[2], yf.data_ptr(), stats.data_ptr()
+    L.check(lib.dfq_stem_q8(ctypes.byref(d2), L.stream()), "dfq_stem_q8 (fp32 out)")
+    torch.cuda.synchronize()
+    got = yf.cpu().numpy()
+    assert np.abs(got - ref).max() <= 2e-6 * max(1.0, np.abs(ref).max())
+    enc = stats.cpu().numpy().view(np.uint32)
+    dec = lambda u: np.where(u & 0x80000000, u ^ 0x80000000, ~u).astype(np.uint32).view(np.float32)
+    assert np.array_equal(-dec(enc[:, 0]), got.reshape(N, -1).min(1)) and np.array_equal(dec(enc[:, 1]), got.reshape(N, -1).max(1))
     # off-grid weights are refused by the packer (the fp32 kernel takes them)
     assert pack_stem(wd * 1.0001 + torch.randn_like(wd) * 1e-3) is None
