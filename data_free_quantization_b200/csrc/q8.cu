@@ -328,6 +328,7 @@ struct DwQ8Args {
     const int8_t *x; const uint32_t *wrow; const float *bias; const RangeSlot *in_slot;
     const RangeSlot *out_slot[2]; int8_t *y[2];
     int N, H, W, OH, OW, C, Cp, stride, relu, strips;
+    int segs, spp;                    // a row is walked by `segs` threads, `spp` strips each (small batches: more threads)
     float s_w, c_w;
     int pad, dil;                // generic kernel only (the dp4a kernel is pad 1, dilation 1)
 };
@@ -348,8 +349,10 @@ dwq8_kernel(DwQ8Args a) {
     constexpr int P = DIL == 2 ? 8 : DwStrip<S>::value;
     const unsigned cw = (unsigned)a.Cp >> 2;                      // channel words per pixel
     const unsigned idx = blockIdx.x * kThreads + threadIdx.x;
-    if (idx >= (unsigned)a.N * (unsigned)a.OH * cw) return;
-    const unsigned cg = idx % cw, rest = idx / cw;
+    if (idx >= (unsigned)a.N * (unsigned)a.OH * (unsigned)a.segs * cw) return;
+    const unsigned cg = idx % cw;
+    unsigned rest = idx / cw;
+    const int seg = (int)(rest % (unsigned)a.segs); rest /= (unsigned)a.segs;
     const int oy = (int)(rest % (unsigned)a.OH);
     const int n = (int)(rest / (unsigned)a.OH);
     const int c0 = (int)cg * 4;
@@ -402,7 +405,7 @@ dwq8_kernel(DwQ8Args a) {
     const float floor_v = a.relu ? 0.0f : -INFINITY;
     const int64_t orow = ((int64_t)n * a.OH + oy) * a.OW;
     const int left = a.C - c0;
-    for (int sp = 0; sp < a.strips; ++sp) {
+    for (int sp = seg * a.spp; sp < min(a.strips, (seg + 1) * a.spp); ++sp) {
         const int ox0 = sp * P, ixs = ox0 * S - PAD;
         // 12 input columns x 3 rows (zero words outside the image), transposed per 4-column block
         uint32_t t[3][3][4];                                      // [row][block][channel]: 4 adjacent pixels of a channel
@@ -1071,6 +1074,21 @@ int conv_q8_tma(const DfqConvQ8Desc *d, void *stream) {
 }
 }  // namespace dfq
 
+// Threads per output row: one walks the whole row when the launch fills the GPU anyway (batch 256); at small batches
+// (DeepLab: 16 images, 33 .. 257 rows) a row is cut into segments of whole strips until there are about three waves of
+// blocks (2 resident per SM).  DFQ_Q8_DW_SEGS=<n> forces a count (A/B runs; 1 = the one-thread-per-row form).
+static void dw_row_segments(DwQ8Args &a) {
+    const int64_t rows = (int64_t)a.N * a.OH * (a.Cp / 4);
+    const int64_t want = (int64_t)sm_count() * 2 * kThreads * 3;
+    int64_t segs = (want + rows - 1) / rows;
+    const char *e = getenv("DFQ_Q8_DW_SEGS");
+    if (e && atoi(e) > 0) segs = atoi(e);
+    if (segs > a.strips) segs = a.strips;
+    if (segs < 1) segs = 1;
+    a.spp = (int)((a.strips + segs - 1) / segs);
+    a.segs = (a.strips + a.spp - 1) / a.spp;
+}
+
 static bool dw_dil2_off() {                       // DFQ_Q8_DW_DIL2=0: dilated layers on the generic kernel (A/B runs)
     const char *e = getenv("DFQ_Q8_DW_DIL2");
     return e && e[0] == '0';
@@ -1093,7 +1111,8 @@ extern "C" int dfq_dw_q8(const DfqDwQ8Desc *d, void *stream) {
     const cudaStream_t st = (cudaStream_t)stream;
     if (a.dil == 2 && a.pad == 0 && d->stride == 1 && !dw_dil2_off()) {      // the strip kernel on dilated taps
         a.strips = (a.OW + 7) / 8;
-        const int64_t total = (int64_t)a.N * a.OH * (a.Cp / 4);
+        dw_row_segments(a);
+        const int64_t total = (int64_t)a.N * a.OH * a.segs * (a.Cp / 4);
         if (total >= 0x7fffffffll) return (int)cudaErrorInvalidValue;
         const unsigned grid = (unsigned)((total + kThreads - 1) / kThreads);
         if (d->y1) dwq8_kernel<1, true, 0, 2><<<grid, kThreads, 0, st>>>(a);
@@ -1111,7 +1130,8 @@ extern "C" int dfq_dw_q8(const DfqDwQ8Desc *d, void *stream) {
     }
     const int P = d->stride == 1 ? DwStrip<1>::value : DwStrip<2>::value;
     a.strips = (a.OW + P - 1) / P;
-    const int64_t total = (int64_t)a.N * a.OH * (a.Cp / 4);
+    dw_row_segments(a);
+    const int64_t total = (int64_t)a.N * a.OH * a.segs * (a.Cp / 4);
     if (total >= 0x7fffffffll) return (int)cudaErrorInvalidValue;
     const unsigned grid = (unsigned)((total + kThreads - 1) / kThreads);
     const int variant = (d->stride == 2 ? 4 : 0) | (d->y1 ? 2 : 0) | (a.pad ? 1 : 0);

@@ -405,3 +405,39 @@ def test_dilated_depthwise_strip_kernel_equals_the_generic_kernel(oracle, N, C, 
     for yb, (l, h) in list(zip(res[1], outs))[:2 if dual else 1]:
         want = oracle.fake_quant(ref.astype(np.float32), 8, float(np.float32(l)), float(np.float32(h)), want_codes=True)[1]
         check_codes(from_codes_nhwc(yb.cpu(), (N, C, OH, OW)).numpy(), want, "dilated depthwise, strip kernel")
+
+
+@pytest.mark.parametrize("stride,pad,dil", [(1, 1, 1), (2, 1, 1), (1, 0, 1), (2, 0, 1), (1, 0, 2)])
+def test_depthwise_row_segments_do_not_change_the_bytes(oracle, stride, pad, dil, monkeypatch):
+    """dfq_dw_q8 cuts an output row into segments of whole strips at small batches (more threads); one thread per row
+    (DFQ_Q8_DW_SEGS=1) and five segments must write the same bytes."""
+    import ctypes
+    from data_free_quantization_b200 import _lib as L
+    from data_free_quantization_b200.eval_q8 import pack_depthwise, to_codes_nhwc
+    from test_gpu_q8 import slot
+    lib = L.lib()
+    rng = np.random.default_rng(stride * 10 + pad + dil)
+    N, C, H, W = 2, 40, 23, 61
+    Cp = 48
+    sl, _ = slot(-1.5, 3.0)
+    (s0, _), (s1, _) = slot(-2.0, 2.5), slot(0.0, 1.5)
+    x = to_codes_nhwc(torch.from_numpy(rng.integers(0, 256, (N, C, H, W)).astype(np.uint8))).reshape(-1).to(DEV)
+    w0 = (rng.standard_normal((C, 1, 3, 3)) * 0.3).astype(np.float32)
+    w, _ = oracle.fake_quant(w0, 8, float(w0.min()), float(w0.max()), want_codes=True)
+    wrow, dsw, dcw = pack_depthwise(torch.from_numpy(w).to(DEV))
+    bp = torch.zeros(Cp, device=DEV); bp[:C] = torch.from_numpy((rng.standard_normal(C) * 0.2).astype(np.float32)).to(DEV)
+    OH, OW = (H + 2 * pad - 2 * dil - 1) // stride + 1, (W + 2 * pad - 2 * dil - 1) // stride + 1
+    res = []
+    for segs in ("1", "5"):
+        monkeypatch.setenv("DFQ_Q8_DW_SEGS", segs)
+        y0 = torch.full((N * OH * OW * Cp,), 77, dtype=torch.int8, device=DEV)
+        y1 = torch.full((N * OH * OW * Cp,), 77, dtype=torch.int8, device=DEV)
+        d = L.DfqDwQ8Desc()
+        d.x, d.wrow, d.bias, d.in_slot, d.y0, d.out_slot0 = x.data_ptr(), wrow.data_ptr(), bp.data_ptr(), sl.data_ptr(), y0.data_ptr(), s0.data_ptr()
+        d.y1, d.out_slot1 = y1.data_ptr(), s1.data_ptr()
+        d.N, d.H, d.W, d.C, d.stride, d.relu, d.s_w, d.c_w, d.pad, d.dil = N, H, W, C, stride, 0, dsw, dcw, pad, dil
+        L.check(lib.dfq_dw_q8(ctypes.byref(d), L.stream()), "dfq_dw_q8")
+        torch.cuda.synchronize()
+        res.append((y0, y1))
+    for a, b in zip(*res):
+        assert torch.equal(a, b) and not bool((a == 77).all())
