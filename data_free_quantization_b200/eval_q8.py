@@ -377,6 +377,7 @@ class EvalPlanQ8(EvalPlan):
                 retire(i)
                 continue
             can_map = kind == "add"
+            fork_info = None              # (source tensor, buffers read, buffers written) of a 1 x 1 / dense convolution
             if kind == "conv":
                 kh_, kw_, s_, p_, d_, g_ = st["geom"]
                 can_map = (st["src"] is self.input) or (kh_ == 1 and kw_ == 1 and g_ == 1 and s_ == 1 and p_ == 0)
@@ -421,6 +422,7 @@ class EvalPlanQ8(EvalPlan):
                     fn = self._pw(name, w.reshape(w.shape[0], -1), b, xcodes, slot_ptr(st["slot"]),
                                   Nn * H * W, y0, s0, y1, s1, st["relu"], yf, m0, m1)
                     kind2 = "pw"
+                    fork_info = (id(src), {xcodes.data_ptr()}, {y0, y1, None if yf is None else yf.data_ptr()} - {None})
                 elif kh == 3 and kw == 3 and g == C == m.out_channels and s in (1, 2) and y0 is not None:
                     if p > d:
                         raise NotImplementedError(f"{name}: depthwise padding {p} with dilation {d}")
@@ -468,6 +470,7 @@ class EvalPlanQ8(EvalPlan):
                     desc.kh, desc.kw, desc.stride, desc.pad, desc.dil, desc.relu = kh, kw, s, p, d, st["relu"]
                     desc.s_w, desc.c_w, desc.o_cap, desc.tma = pk.s_w, pk.c_w, pk.o_cap, tma
                     self.keep_q8 += [pk, desc, b]
+                    fork_info = (id(src), {xcodes.data_ptr()}, {y0, y1} - {None})
                     fn = (lambda dd: lambda: L.check(lib.dfq_conv_q8(ctypes.byref(dd), stream()), "dfq_conv_q8"))(desc)
                     kind2 = "dense"
                 else:
@@ -557,13 +560,42 @@ class EvalPlanQ8(EvalPlan):
             self.ops.append((name, fn))
             self.out_of[name] = out
             self.step_io[name] = {"kind": kind2, "in_slots": slots_in(st), "srcs": ins_of(st), "out": out,
-                                  "out_slots": oidx, "relu": st.get("relu", 0), "fn": fn}
+                                  "out_slots": oidx, "relu": st.get("relu", 0), "fn": fn, "fork": fork_info}
             retire(i)                                       # code buffers whose last reader this step was
         if self.output.buf is None:
             raise NotImplementedError("q8 plan: the network's output is not produced as fp32")
         self.op_info = {n: {"kind": io["kind"]} for n, io in self.step_io.items()}
         self.hbm_bytes = self.act_bytes
         self._fill_borders()
+        self._schedule()
+
+    def _schedule(self):
+        """Sibling convolutions -- consecutive 1 x 1 / dense convolutions of ONE tensor, e.g. the four ASPP branches,
+        each a latency-bound kernel of ~140 CTAs at 33 x 33 -- are launched side by side on forked streams (joined
+        before the next op; captured into the CUDA graph as parallel branches).  A group forms only when no member
+        writes a buffer another member reads or writes (the code-buffer pool recycles by size).  DFQ_Q8_FORK=0: one
+        stream."""
+        self.schedule, group = [], []
+        use = os.environ.get("DFQ_Q8_FORK", "1") != "0"
+
+        def flush():
+            if group:
+                self.schedule.append([fn for _name, fn, _f in group])
+                group.clear()
+        for name, fn in self.ops:
+            f = self.step_io.get(name, {}).get("fork") if use else None
+            ok = f is not None and len(group) < 4 and bool(group) and group[-1][2][0] == f[0] and all(
+                not (f[2] & (g[2][1] | g[2][2])) and not (f[1] & g[2][2]) for g in group)
+            if f is None:
+                flush()
+                self.schedule.append([fn])
+                continue
+            if not ok:
+                flush()
+            group.append((name, fn, f))
+        flush()
+        self.forked = [len(g) for g in self.schedule if len(g) > 1]
+        self.side = [torch.cuda.Stream(device=self.dev) for _ in range(3)] if self.forked else []
 
     def _fill_borders(self):
         """Border of every producer-placed padded tensor: code(0.0) on its consumer's grid, i.e. what the reference's
@@ -617,8 +649,24 @@ class EvalPlanQ8(EvalPlan):
         self._fill_borders()
 
     def launch(self):
-        for _name, fn in self.ops:
-            fn()
+        for grp in self.schedule:
+            if len(grp) == 1:
+                grp[0]()
+                continue
+            main = torch.cuda.current_stream()
+            start = torch.cuda.Event()
+            start.record(main)
+            grp[0]()
+            done = []
+            for side, fn in zip(self.side, grp[1:]):
+                side.wait_event(start)
+                with torch.cuda.stream(side):
+                    fn()
+                ev = torch.cuda.Event()
+                ev.record(side)
+                done.append(ev)
+            for ev in done:
+                main.wait_event(ev)
 
     def set_range(self, idx, lo, hi):
         p = L.DfqQuantParams()

@@ -441,3 +441,25 @@ def test_depthwise_row_segments_do_not_change_the_bytes(oracle, stride, pad, dil
         res.append((y0, y1))
     for a, b in zip(*res):
         assert torch.equal(a, b) and not bool((a == 77).all())
+
+
+def test_forked_sibling_convolutions_give_the_same_output(static_deeplab, monkeypatch):
+    """The ASPP branches launched side by side on forked streams (EvalPlanQ8._schedule) against the one-stream order:
+    same kernels, so the same logits -- eagerly and replayed from a CUDA graph, several times over."""
+    from data_free_quantization_b200.eval_q8 import EvalPlanQ8
+    model, tr = static_deeplab
+    x = torch.randn(2, 3, 129, 129, generator=torch.Generator().manual_seed(4)).to(DEV)
+    monkeypatch.setenv("DFQ_Q8_FORK", "0")
+    plain = EvalPlanQ8(model, tr, batch=2, in_shape=(3, 129, 129))
+    want = plain(x).clone()
+    monkeypatch.setenv("DFQ_Q8_FORK", "1")
+    plan = EvalPlanQ8(model, tr, batch=2, in_shape=(3, 129, 129))
+    assert not plain.forked and plan.forked and max(plan.forked) >= 3
+    for _ in range(3):
+        assert torch.equal(plan(x), want)
+    replay = plan.capture()
+    for _ in range(5):
+        plan.input.buf.copy_(x)
+        replay()
+        torch.cuda.synchronize()
+        assert torch.equal(plan.output.buf, want)
