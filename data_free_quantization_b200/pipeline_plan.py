@@ -144,6 +144,7 @@ class PipelinePlan:
         L.bump_weights_epoch()
         L.add_launches(self.launches)
         if self.mm is not None:
+            self.mm.speculate()                   # the previous pass's ranges, queued behind the graphs (see MinmaxPlan)
             self.mm.finish()                      # set_quant_minmax: host arithmetic + one H2D per range table
         return self.relations
 

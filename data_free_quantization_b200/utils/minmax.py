@@ -340,14 +340,20 @@ def _flush_pending():
         else:
             loose.append(q)
     table = None
+    uploads, complete = [], not loose
     for base, rows in pooled.values():
         if len(rows) == base.size(0):                        # every row rewritten: plain copy
-            base.copy_(torch.tensor([rows[i] for i in range(base.size(0))], dtype=torch.float32))
+            host = torch.tensor([rows[i] for i in range(base.size(0))], dtype=torch.float32)
+            base.copy_(host)
+            uploads.append((base, host))
         else:
             idx = sorted(rows)
             base.index_copy_(0, torch.tensor(idx, device=base.device),
                              torch.tensor([rows[i] for i in idx], dtype=torch.float32).to(base.device))
+            complete = False
         table = base
+    # (MinmaxPlan.speculate) what this call uploaded, when it was whole tables only
+    _ctx["uploads"] = uploads if complete and uploads else None
     if loose:
         dev = loose[0]._buffers["running_min"].device
         table = torch.tensor([pending[q] for q in loose], dtype=torch.float32).to(dev)
@@ -374,6 +380,8 @@ class MinmaxPlan:
         self.gather = _Gather(graph, bn_type)
         self.bn_pos = {m: i for i, m in enumerate(self.gather.bns)}
         self._memo = None
+        self._spec = self._spec_key = None        # uploads of the memoised ranges: [(table, pinned rows)], buffer ids
+        self._spec_done = False
 
     @staticmethod
     def _key(graph, bottoms, is_detection, bn_type, N, top):
@@ -381,6 +389,37 @@ class MinmaxPlan:
 
     def start(self):
         self.gather.start()
+
+    @staticmethod
+    def _buffers_key(rec):
+        try:
+            return tuple(id((q.node.quant if type(q) is _LayerQuant else q)._buffers["running_min"]) for q, _lo, _hi in rec)
+        except (AttributeError, KeyError):
+            return None
+
+    def speculate(self):
+        """Queue the upload of the ranges the PREVIOUS call computed, before the statistics of this call have arrived:
+        the ranges are a pure function of the BatchNorm statistics, and in the reference's flow those are the same on
+        every pass.  finish() still compares the fetched statistics with the memoised ones and recomputes + uploads
+        again when they differ, so the speculation only removes the host round trip (wait for the copy, compare,
+        upload) from the device's critical path."""
+        self._spec_done = False
+        if self._memo is None or self._spec is None or not torch.cuda.is_available():
+            return
+        if self._spec_key is None or self._buffers_key(self._memo[1]) != self._spec_key:   # measures re-bound: no shortcut
+            self._spec = None
+            return
+        for base, host in self._spec:
+            base.copy_(host, non_blocking=True)
+        self._spec_done = True
+
+    def _remember_uploads(self):
+        ups = _ctx.pop("uploads", None)
+        if ups and self._memo is not None and all(b.is_cuda for b, _h in ups):
+            self._spec = [(b, h.pin_memory()) for b, h in ups]
+            self._spec_key = self._buffers_key(self._memo[1])
+        else:
+            self._spec = self._spec_key = None
 
     def finish(self):
         stats = self.gather.fetch()
@@ -390,13 +429,18 @@ class MinmaxPlan:
         flat = self.gather.flat
         if flat is not None and self._memo is not None and flat.shape == self._memo[0].shape and \
                 np.array_equal(flat.view(np.uint32), self._memo[0].view(np.uint32)):
+            if self._spec_done:                     # speculate() already queued exactly these ranges
+                self._spec_done = False
+                return
             _ctx["pending"] = {}
             try:
                 for qref, lo, hi in self._memo[1]:
                     _set(qref, lo, hi)
             finally:
                 _flush_pending()
+                self._remember_uploads()
             return
+        self._spec_done = False
         _ctx["stats"], _ctx["pending"] = stats, {}
         _ctx["record"] = rec = []
         N, eps = self.N, self.eps
@@ -429,6 +473,7 @@ class MinmaxPlan:
             _ctx["stats"] = None
             _ctx["record"] = None
             _flush_pending()
+            self._remember_uploads()
 
 
 _plans = {}

@@ -93,3 +93,47 @@ def test_plan_not_used_when_the_model_is_not_fresh():
         case.step()
         assert PP.stats["replayed"] == n + 1
     torch.cuda.synchronize()
+
+
+def test_speculative_range_upload_is_checked_against_the_statistics():
+    """MinmaxPlan.speculate() queues the previous pass's ranges before this pass's BatchNorm statistics have arrived;
+    finish() must leave the ranges of THESE statistics: the memoised ones when nothing moved (even over a clobbered
+    table), recomputed ones when a statistic changed."""
+    import bench
+    from data_free_quantization_b200 import pipeline_plan as PP
+    PP.forget()
+    case = bench.PipelineCase(torch.device(DEV))
+    with contextlib.redirect_stdout(io.StringIO()):
+        for _ in range(4):
+            case.rearm(False)
+            case.step()
+    torch.cuda.synchronize()
+    plan = next(v for v in PP._plans.values() if isinstance(v, PP.PipelinePlan))
+    mm = plan.mm
+    assert mm._memo is not None and mm._spec, "the replays should have armed the speculation"
+    ranges = lambda: _state(case)
+    want = {k: v for k, v in ranges().items() if k.endswith(".range")}
+    for base, _host in mm._spec:                       # clobber the device tables: only the upload can restore them
+        base.fill_(123.0)
+    mm.start(); mm.speculate()
+    assert mm._spec_done
+    mm.finish()
+    torch.cuda.synchronize()
+    assert {k: v for k, v in ranges().items() if k.endswith(".range")} == want
+    # a statistic moves: the speculation is wrong and must be overwritten by the recomputed ranges
+    bn = mm.gather.bns[3]
+    bn._buffers["fake_bias"].add_(0.75)
+    mm.start(); mm.speculate(); mm.finish()
+    torch.cuda.synchronize()
+    moved = {k: v for k, v in ranges().items() if k.endswith(".range")}
+    assert moved != want
+    mm._memo = mm._spec = None                         # the same statistics without any shortcut
+    mm.start(); mm.speculate(); mm.finish()
+    torch.cuda.synchronize()
+    assert {k: v for k, v in ranges().items() if k.endswith(".range")} == moved
+    # and the shortcut is armed again for the new statistics
+    mm.start(); mm.speculate()
+    assert mm._spec_done
+    mm.finish()
+    torch.cuda.synchronize()
+    assert {k: v for k, v in ranges().items() if k.endswith(".range")} == moved
