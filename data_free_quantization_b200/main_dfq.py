@@ -129,9 +129,15 @@ def run_dfq_steps(model, graph, bottoms, args, targ_pair=(QuantConv2d, QuantLine
             PP.store(graph, ("failed", repr(exc)))
             mode = "eager"
     if mode == "replay":
-        res = plan.replay()
+        # bias_correction as wired in the reference touches nothing on the device: its host work (and
+        # its log lines) run while the graphs execute, and the wait for set_quant_minmax's statistics comes last.
+        # The other modes launch kernels on the final weights: the reference's order.
+        host_only = args.correction and getattr(args, "correction_mode", "ref") == "ref"
+        res = plan.replay(finish=not host_only)
         PP.stats["replayed"] += 1
         correction()
+        if host_only:
+            plan.finish_ranges()
         return res
     PP.stats["eager"] += 1
     res = weights_phase()
